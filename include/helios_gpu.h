@@ -1,0 +1,309 @@
+/* helios_gpu.h — C ABI of the B200-native HeliosEngine ECS hot path ("seam B5").
+ *
+ * The reference (RexarX/HeliosEngine, C++23, CPU only) has no FFI for this path: the path is the
+ * in-process C++ API of src/ecs.  This header is the thin C boundary a maintainer binds UNDER the
+ * reference-shaped C++ shim (include/helios_b200/ecs.hpp): plain pointers, sizes and int status codes,
+ * no C++/torch types.  Each entry point cites the reference interface it replaces
+ * (paths relative to /root/reference/src/ecs/include/helios/ecs/).
+ *
+ * Conventions (mirroring world.hpp:52-78 "not thread-safe"): one world = one CUDA device + one
+ * primary stream; calls on one world must be externally serialised; every function returns
+ * HELIOS_GPU_OK (0) or a negative helios_gpu_status and records a message for
+ * helios_gpu_last_error().  All device memory is owned by the library.  There is NO CPU fallback:
+ * every call that does work launches sm_100a kernels and fails with HELIOS_GPU_ERR_CUDA if it cannot.
+ */
+#ifndef HELIOS_GPU_H_
+#define HELIOS_GPU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define HELIOS_GPU_API __attribute__((visibility("default")))
+#else
+#define HELIOS_GPU_API
+#endif
+
+#define HELIOS_GPU_MAX_COMPONENTS 64       /* component types per world (archetype id = 64-bit slot mask) */
+#define HELIOS_GPU_MAX_QUERY_COMPONENTS 8  /* data components handed to one system body */
+#define HELIOS_GPU_MAX_CMD_COMPONENTS 8    /* component values carried by one Add/TryAdd command */
+
+typedef enum helios_gpu_status {
+  HELIOS_GPU_OK = 0,
+  HELIOS_GPU_ERR_INVALID_ARGUMENT = -1,
+  HELIOS_GPU_ERR_CUDA = -2,
+  HELIOS_GPU_ERR_NOT_FOUND = -3,
+  HELIOS_GPU_ERR_CAPACITY = -4,
+  HELIOS_GPU_ERR_STATE = -5,
+  HELIOS_GPU_ERR_CYCLE = -6 /* schedule ordering cycle (DagErrorKind::kCycleDetected, schedule/dag.hpp) */
+} helios_gpu_status;
+
+/* Entity{u32 index; u32 generation} (entity/entity.hpp:22-98) packed little-endian: index | generation<<32.
+ * Invalid = 0xFFFFFFFFFFFFFFFF. */
+typedef uint64_t helios_gpu_entity_t;
+#define HELIOS_GPU_INVALID_ENTITY 0xFFFFFFFFFFFFFFFFull
+
+typedef struct helios_gpu_world helios_gpu_world;
+typedef struct helios_gpu_query helios_gpu_query;
+typedef struct helios_gpu_schedule helios_gpu_schedule;
+
+typedef struct helios_gpu_world_config {
+  int32_t device;             /* CUDA device ordinal */
+  uint32_t entity_capacity;   /* hint: entity indices to pre-size the location/generation tables for */
+  uint32_t table_capacity;    /* hint: archetype tables */
+  uint32_t flags;             /* HELIOS_GPU_WORLD_* */
+} helios_gpu_world_config;
+#define HELIOS_GPU_WORLD_DEFAULT 0u
+
+/* ---- world lifetime (replaces World ctor/dtor, world.hpp:80-130) ------------------------------ */
+HELIOS_GPU_API int32_t helios_gpu_world_create(const helios_gpu_world_config* cfg, helios_gpu_world** out);
+HELIOS_GPU_API int32_t helios_gpu_world_destroy(helios_gpu_world* w);
+HELIOS_GPU_API const char* helios_gpu_last_error(const helios_gpu_world* w);
+/* Use an externally created cudaStream_t (e.g. torch's current stream) as the world's primary stream. */
+HELIOS_GPU_API int32_t helios_gpu_world_set_stream(helios_gpu_world* w, void* cuda_stream);
+HELIOS_GPU_API int32_t helios_gpu_world_synchronize(helios_gpu_world* w);
+/* Number of kernels this world has launched so far (bench.py's gpu_launches). */
+HELIOS_GPU_API uint64_t helios_gpu_world_launch_count(const helios_gpu_world* w);
+
+/* ---- components (ComponentManager::Register, component/manager.hpp:1049-1057) -------------------
+ * type_hash = TypeIndex = FNV-1a-64 of the qualified type name (utils/type_info.hpp:308-311).
+ * default_bytes = bytes of a default-constructed T (placeholder pushed by MigrateEntity,
+ * manager.hpp:1932-1938); NULL = zeros.  Returns the slot id (>= 0) or a negative status. */
+HELIOS_GPU_API int32_t helios_gpu_register_component(helios_gpu_world* w, uint64_t type_hash, uint32_t size,
+                                                     uint32_t align, const void* default_bytes);
+
+/* ---- entities (World::CreateEntity world.hpp:979-984; Commands::Spawn → ReserveEntity
+ *      entity/manager.hpp:294-305) ---------------------------------------------------------------- */
+HELIOS_GPU_API int32_t helios_gpu_create_entities(helios_gpu_world* w, uint32_t n, helios_gpu_entity_t* out);
+HELIOS_GPU_API int32_t helios_gpu_reserve_entities(helios_gpu_world* w, uint32_t n, helios_gpu_entity_t* out);
+/* Bulk form of `for i: e = CreateEntity(); AddComponents(e, c0[i], c1[i], ...)` — identical resulting
+ * ids, archetype creation order and row order.  columns[k] = host array of n values of type_hashes[k]. */
+HELIOS_GPU_API int32_t helios_gpu_spawn_batch(helios_gpu_world* w, const uint64_t* type_hashes, uint32_t ntypes,
+                                              uint64_t n, const void* const* columns,
+                                              helios_gpu_entity_t* out_entities /* may be NULL */);
+HELIOS_GPU_API int32_t helios_gpu_entity_count(helios_gpu_world* w, uint64_t* out);
+
+/* ---- snapshot (parity I/O; the reference has no serializer — SURVEY §5 "checkpoint": none) -------
+ * Canonical dump: archetypes in creation order; per archetype the sorted type-hash list, the entity
+ * array in row order and each column's raw bytes; the generation table and free list. */
+HELIOS_GPU_API int32_t helios_gpu_snapshot_archetype_count(helios_gpu_world* w, uint32_t* out);
+HELIOS_GPU_API int32_t helios_gpu_snapshot_archetype_info(helios_gpu_world* w, uint32_t archetype,
+                                                          uint64_t* type_hashes /* [MAX_COMPONENTS] */,
+                                                          uint32_t* ntypes, uint64_t* rows);
+HELIOS_GPU_API int32_t helios_gpu_snapshot_archetype_entities(helios_gpu_world* w, uint32_t archetype,
+                                                              helios_gpu_entity_t* out, uint64_t capacity);
+HELIOS_GPU_API int32_t helios_gpu_snapshot_archetype_column(helios_gpu_world* w, uint32_t archetype,
+                                                            uint64_t type_hash, void* out, uint64_t capacity_bytes);
+HELIOS_GPU_API int32_t helios_gpu_snapshot_entity_table(helios_gpu_world* w, uint32_t* next_index,
+                                                        uint32_t* generations, uint32_t gen_capacity,
+                                                        uint32_t* free_indices, uint32_t free_capacity,
+                                                        uint32_t* free_count, int64_t* free_cursor);
+/* Location of one entity (ComponentManager::EntityArchetype + Archetype::Row, archetype.hpp:604-612). */
+HELIOS_GPU_API int32_t helios_gpu_entity_location(helios_gpu_world* w, helios_gpu_entity_t e, uint32_t* archetype,
+                                                  uint32_t* row);
+
+/* ---- queries (Query<Cs..., With<..>, Without<..>>, query/query.hpp:658-1248) ---------------------- */
+typedef struct helios_gpu_query_desc {
+  uint32_t n_components;                                   /* data components handed to the body */
+  uint64_t components[HELIOS_GPU_MAX_QUERY_COMPONENTS];    /* type hashes, in body-argument order */
+  uint8_t writes[HELIOS_GPU_MAX_QUERY_COMPONENTS];         /* 1 = T& / T* (write set), 0 = const (read set) */
+  uint32_t n_with;
+  uint64_t with[HELIOS_GPU_MAX_COMPONENTS];
+  uint32_t n_without;
+  uint64_t without[HELIOS_GPU_MAX_COMPONENTS];
+} helios_gpu_query_desc;
+
+HELIOS_GPU_API int32_t helios_gpu_query_create(helios_gpu_world* w, const helios_gpu_query_desc* desc,
+                                               helios_gpu_query** out);
+HELIOS_GPU_API int32_t helios_gpu_query_destroy(helios_gpu_query* q);
+/* Device-side RefreshArchetypes (query.hpp:1732-1812): match set in archetype creation order,
+ * empty tables skipped.  Copies the matched archetype indices back for parity checks. */
+HELIOS_GPU_API int32_t helios_gpu_query_match(helios_gpu_query* q, uint32_t* out_archetypes, uint32_t capacity,
+                                              uint32_t* out_count);
+/* Query::Count (query.hpp:1652-1666). */
+HELIOS_GPU_API int32_t helios_gpu_query_count(helios_gpu_query* q, uint64_t* out);
+
+/* ---- device view handed to a system body ----------------------------------------------------------
+ * One flattened ranged launch covers every matching table: tiles of HELIOS_GPU_TILE_ROWS rows, never
+ * crossing a table boundary, so a tile's column addresses are 16-byte aligned for 128-bit access. */
+#define HELIOS_GPU_TILE_ROWS 1024u
+
+typedef struct helios_gpu_segment {
+  uint32_t archetype;   /* table index (creation order) */
+  uint32_t rows;        /* live rows in the table */
+  uint32_t tile_begin;  /* first flattened tile of this table */
+  uint32_t _pad;
+  uint64_t row_begin;   /* first flattened row of this table (ForEach visit order) */
+  const helios_gpu_entity_t* entities;
+  void* columns[HELIOS_GPU_MAX_QUERY_COMPONENTS]; /* column base per query component */
+} helios_gpu_segment;
+
+typedef struct helios_gpu_query_view {
+  uint32_t n_segments;
+  uint32_t n_tiles;
+  uint64_t n_rows;
+  const helios_gpu_segment* segments; /* device array, n_segments valid entries */
+} helios_gpu_query_view;
+
+/* ---- deferred commands (command/commands.hpp:24-109, builtin_commands.hpp:82-651) ---------------- */
+typedef enum helios_gpu_cmd_kind {
+  HELIOS_GPU_CMD_DESTROY = 0,     /* DestroyEntityCmd        builtin_commands.hpp:82-104   */
+  HELIOS_GPU_CMD_TRY_DESTROY = 1, /* TryDestroyEntityCmd     builtin_commands.hpp:106-130  */
+  HELIOS_GPU_CMD_ADD = 2,         /* AddComponentsCmd        builtin_commands.hpp:250-280  */
+  HELIOS_GPU_CMD_TRY_ADD = 3,     /* TryAddComponentsCmd     builtin_commands.hpp:282-312  */
+  HELIOS_GPU_CMD_REMOVE = 4,      /* RemoveComponentsCmd     builtin_commands.hpp:430-452  */
+  HELIOS_GPU_CMD_TRY_REMOVE = 5,  /* TryRemoveComponentsCmd  builtin_commands.hpp:454-478  */
+  HELIOS_GPU_CMD_CLEAR = 6,       /* ClearComponentsCmd      builtin_commands.hpp:620-651  */
+  HELIOS_GPU_CMD_NONE = 255       /* empty slot of a device-emitted sparse command buffer */
+} helios_gpu_cmd_kind;
+
+/* One command record (the HBM form of CallableBufferArray's [fn|dtor|reloc|payload] record,
+ * container/callable_buffer_array.hpp:330-411).  For ADD/TRY_ADD the component values live in the
+ * queue's payload buffer at payload_offset, in ascending component-slot order, each padded to 4 bytes. */
+typedef struct helios_gpu_command {
+  uint32_t kind;
+  uint32_t payload_offset;
+  helios_gpu_entity_t entity;
+  uint64_t component_mask; /* bit s = component slot s (return value of helios_gpu_register_component) */
+} helios_gpu_command;
+
+/* Enqueue into the world's global queue (World::command_queue_, world.hpp:945; executed by Flush). */
+HELIOS_GPU_API int32_t helios_gpu_commands_enqueue(helios_gpu_world* w, const helios_gpu_command* cmds, uint64_t n,
+                                                   const void* payload, uint64_t payload_bytes);
+/* World::Flush (world.hpp:957-963): reserved-entity flush, then the global queue, FIFO. */
+HELIOS_GPU_API int32_t helios_gpu_world_flush(helios_gpu_world* w);
+/* World::Update (world.hpp:950-955): Flush + MessageManager::Update(). */
+HELIOS_GPU_API int32_t helios_gpu_world_update(helios_gpu_world* w);
+
+typedef struct helios_gpu_apply_stats {
+  uint64_t commands;        /* records examined */
+  uint64_t effective;       /* records that changed the world */
+  uint64_t invalid;         /* non-Try records on a dead entity (reference: HELIOS_ASSERT) — skipped */
+  uint64_t moved_rows;      /* rows written (appends + hole fills) */
+  uint64_t moved_bytes;     /* component + entity-id bytes read+written by the row mover */
+  uint32_t resolve_rounds;  /* dependency-resolution rounds of the swap-and-pop replay (0 = none needed) */
+  uint32_t used_sequential_fallback;
+} helios_gpu_apply_stats;
+HELIOS_GPU_API int32_t helios_gpu_last_apply_stats(helios_gpu_world* w, helios_gpu_apply_stats* out);
+
+/* ---- messages (message/manager.hpp:186-547; reader.hpp:770-820; writer.hpp) ---------------------- */
+#define HELIOS_GPU_MSG_AUTOMATIC 0u /* MessageClearPolicy::kAutomatic (message/message.hpp:17-40) */
+#define HELIOS_GPU_MSG_MANUAL 1u
+HELIOS_GPU_API int32_t helios_gpu_message_register(helios_gpu_world* w, uint64_t type_hash, uint32_t size,
+                                                   uint32_t clear_policy);
+/* MessageManager::Write / WriteBulk → world current queue. */
+HELIOS_GPU_API int32_t helios_gpu_message_write(helios_gpu_world* w, uint64_t type_hash, const void* data, uint64_t n);
+HELIOS_GPU_API int32_t helios_gpu_message_counts(helios_gpu_world* w, uint64_t type_hash, uint64_t* previous,
+                                                 uint64_t* current);
+/* Copy PreviousMessages<T>() (which = 0) or CurrentMessages<T>() (which = 1) to the host. */
+HELIOS_GPU_API int32_t helios_gpu_message_read(helios_gpu_world* w, uint64_t type_hash, uint32_t which, void* out,
+                                               uint64_t capacity_bytes);
+
+/* Device views handed to system bodies. */
+typedef struct helios_gpu_msg_writer { /* SystemLocalData::message_queue for one type (param_traits.hpp:216-229) */
+  uint8_t* data;
+  unsigned long long* count; /* device counter (append ring head) */
+  uint64_t capacity;         /* elements */
+  uint32_t elem_size;
+  uint32_t _pad;
+} helios_gpu_msg_writer;
+
+typedef struct helios_gpu_msg_reader { /* MessageReader<T> = previous ++ current (reader.hpp:793-795) */
+  const uint8_t* previous;
+  const uint8_t* current;
+  const unsigned long long* previous_count; /* device counters */
+  const unsigned long long* current_count;
+  uint32_t elem_size;
+  uint32_t _pad;
+} helios_gpu_msg_reader;
+
+typedef struct helios_gpu_cmd_writer { /* SystemLocalData::cmd_queue (param_traits.hpp:163-167), sparse per-row form */
+  helios_gpu_command* records; /* one slot per flattened row x slots_per_row, pre-set to kind = NONE */
+  uint8_t* payload;            /* slot i owns payload bytes [i*payload_stride, (i+1)*payload_stride) */
+  uint64_t capacity;           /* record slots */
+  uint32_t payload_stride;
+  uint32_t slots_per_row;
+} helios_gpu_cmd_writer;
+
+/* ---- systems and schedules (schedule/schedule.hpp:334-362; src/ecs/src/schedule/schedule.cpp) ---- */
+typedef struct helios_gpu_system_ctx {
+  helios_gpu_world* world;
+  void* stream;                        /* cudaStream_t the body must launch on */
+  const helios_gpu_query_view* view;   /* DEVICE pointer; filled by the match kernel earlier on `stream` */
+  uint32_t sm_count;
+  uint32_t system_index;               /* registration index in its schedule */
+  const void* params;                  /* host copy of the bytes given at registration */
+  uint32_t params_size;
+  uint32_t _pad;
+  helios_gpu_cmd_writer commands;      /* valid if the system declared HELIOS_GPU_SYSTEM_EMITS_COMMANDS */
+  helios_gpu_msg_writer writer;        /* valid if writes_message != 0 */
+  helios_gpu_msg_reader reader;        /* valid if reads_message != 0 */
+  void* resources;                     /* device scratch of HELIOS_GPU_RESOURCE_BYTES shared by the schedule's systems */
+  void* host_user;
+} helios_gpu_system_ctx;
+#define HELIOS_GPU_RESOURCE_BYTES 4096u
+
+/* A GPU system body = a host function that enqueues sm_100a kernels on ctx->stream
+ * (the device-compilable counterpart of SystemCallable, schedule/system_storage.hpp:19-23). */
+typedef int32_t (*helios_gpu_system_fn)(const helios_gpu_system_ctx* ctx);
+
+#define HELIOS_GPU_SYSTEM_EMITS_COMMANDS 1u
+typedef struct helios_gpu_system_desc {
+  const char* name;
+  helios_gpu_query* query;         /* may be NULL */
+  helios_gpu_system_fn launch;
+  void* host_user;
+  const void* params;              /* copied at registration */
+  uint32_t params_size;
+  uint32_t flags;
+  uint32_t cmd_slots_per_row;      /* EMITS_COMMANDS: command slots per visited row */
+  uint32_t cmd_payload_stride;     /* EMITS_COMMANDS: payload bytes per slot */
+  uint64_t writes_message;         /* MessageWriter<T> type hash or 0 */
+  uint64_t reads_message;          /* MessageReader<T> type hash or 0 */
+  uint64_t writer_capacity;        /* max messages this system writes per run */
+  /* AccessPolicy beyond the query's own components (system/access_policy.hpp:172-196) */
+  uint32_t n_extra_read_components, n_extra_write_components, n_read_resources, n_write_resources;
+  uint64_t extra_read_components[8], extra_write_components[8], read_resources[8], write_resources[8];
+} helios_gpu_system_desc;
+
+HELIOS_GPU_API int32_t helios_gpu_schedule_create(helios_gpu_world* w, const char* name, helios_gpu_schedule** out);
+HELIOS_GPU_API int32_t helios_gpu_schedule_destroy(helios_gpu_schedule* s);
+/* Schedule::Add (schedule.hpp:334-336); out_index = registration index. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_add_system(helios_gpu_schedule* s, const helios_gpu_system_desc* desc,
+                                                      uint32_t* out_index);
+/* SystemHandle::Before/After ordering edge: `first` runs before `second`. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_add_order(helios_gpu_schedule* s, uint32_t first, uint32_t second);
+/* Schedule::Build (schedule.cpp:117-158): Kahn order (dag.cpp:65-126) + conflict bitmask (schedule.cpp:364-425). */
+HELIOS_GPU_API int32_t helios_gpu_schedule_build(helios_gpu_schedule* s);
+HELIOS_GPU_API int32_t helios_gpu_schedule_execution_order(helios_gpu_schedule* s, uint32_t* out, uint32_t capacity,
+                                                           uint32_t* out_count);
+/* conflict bitmask rows indexed by POSITION in the execution order (schedule.cpp:371-395). */
+HELIOS_GPU_API int32_t helios_gpu_schedule_conflicts(helios_gpu_schedule* s, uint64_t* out, uint32_t capacity);
+#define HELIOS_GPU_EXEC_SERIAL 0u  /* MainThreadExecutor analogue: one stream, execution order */
+#define HELIOS_GPU_EXEC_STREAMS 1u /* MultiThreadedExecutor analogue: conflict edges -> stream fork/join */
+#define HELIOS_GPU_EXEC_GRAPH 2u   /* same DAG captured once into a CUDA graph and replayed */
+/* Schedule::Run (schedule.cpp:55-78): asynchronous on the world's streams. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_run(helios_gpu_schedule* s, uint32_t exec_mode);
+/* Schedule::ApplyDeferred (schedule.cpp:106-115): world flush, then every system's local data in
+ * REGISTRATION order (commands, then message merge).  Synchronises. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_apply_deferred(helios_gpu_schedule* s);
+/* Schedule::RunAndWait (schedule.cpp:80-104) = run + apply_deferred. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_run_and_wait(helios_gpu_schedule* s, uint32_t exec_mode);
+/* Number of distinct streams / graph nodes the last build mapped the DAG onto. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_stream_count(helios_gpu_schedule* s, uint32_t* out);
+/* Copy the schedule's device resource scratch (HELIOS_GPU_RESOURCE_BYTES) to the host. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_read_resources(helios_gpu_schedule* s, void* out, uint32_t bytes);
+
+/* Built-in system bodies compiled into the library (bench + parity workloads); see
+ * heliosengine_b200/csrc/builtin_systems.cu for the list.  User bodies are written against
+ * heliosengine_b200/csrc/helios_gpu_device.cuh and registered through the same function type. */
+HELIOS_GPU_API int32_t helios_gpu_builtin_system(const char* name, helios_gpu_system_fn* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HELIOS_GPU_H_ */
