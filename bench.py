@@ -1,0 +1,264 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the ECS hot path on B200 (contract in the task statement / DESIGN.md §6).
+
+Workload (BASELINE.json configs[1]): 16 777 216 entities across 64 archetypes (4 mandatory + 6 optional 4-byte
+components), Query<Position&, Velocity&, const Acceleration&, const Mass&, With<Health>, Without<Frozen>>
+(16 matching tables, 4 194 304 rows), body v += a*(dt/m); p += v*dt.  One "step" = one Schedule::Run of that system
+(device-side archetype-mask match + one flattened ranged launch).  Metric = matched entity-component updates / s.
+
+  value     device-resident throughput: CUDA events around each step on the launching stream, L2 flushed between steps
+  e2e       same metric through the C ABI with HOST buffers: per step the frame's Acceleration columns are copied
+            host->device from pinned memory, the schedule runs, the Position columns are read back device->host
+  roofline  algorithmic bytes (44 B per matched entity) / kernel time vs MEASURED_PEAKS.json hbm_gbs
+  --impl reference   the CPU oracle's reference-faithful access path (B-ref) on a bounded sample
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "entity_component_updates_per_sec"
+UNIT = "updates/s"
+N_ENTITIES = 1 << 24
+WORKLOAD = ("cfg2: 16777216 entities / 64 archetypes, 4-component Query with With<Health> Without<Frozen> "
+            "(16 tables, 4194304 rows), accel-integrate body")
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--entities", type=int, default=N_ENTITIES)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--all-tables", action="store_true", help="drop the With/Without filters (cfg 2-all)")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc = device, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.device)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit())
+        mx = max([float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()] or [0])
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 9 for i in range(4) if r[5 + i].lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_reference_leg(entities, steps, warmup, threads=1, mode=1):
+    """Times the oracle's reference-faithful path (B-ref: per-entity unordered_map probe + 2 binary searches + column-map
+    find per component, serial ForEach — SURVEY §3.3) on a bounded sample of the same workload."""
+    from heliosengine_b200 import capi, worlds
+    o = capi.load_oracle()
+    w = capi.World(o)
+    sched, q = worlds.build_cfg2(w, entities, filtered=True)
+    o.fn("set_access_mode")(w.h, mode, threads)
+    matched = q.count()
+    for _ in range(warmup):
+        sched.run(0)
+    t = o.fn("time_schedule_run", __import__("ctypes").c_double)(sched.h, steps)
+    w.close()
+    return matched * steps / t, t / steps, matched
+
+
+def run_reference(args):
+    import ctypes
+    from heliosengine_b200 import capi
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample_entities = 1 << 21  # 1/8 of the workload: 524288 matched rows per step
+    steps = max(1, min(args.steps, 3))
+    warm = 1
+    v, spt, matched = cpu_reference_leg(sample_entities, steps, warm, threads=1, mode=1)
+    cores = 1
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
+        "ms_per_step": spt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": {"workload": WORKLOAD, "sample": f"{sample_entities} entities ({matched} matched rows) per step"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"1/8-scale world ({sample_entities} entities, {matched} matched rows), {steps} steps; "
+                                   "reference-faithful access path (B-ref); the reference runs one system on one core "
+                                   f"(no intra-system parallelism); host has {capi.load_oracle().fn('hardware_threads', ctypes.c_uint32)()} threads"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from heliosengine_b200 import capi, worlds
+
+    rank = int(os.environ.get("RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    if world_size > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+
+    # Entity-range sharding, weak scaling: every rank owns an independent shard of `entities` entities (rows are
+    # independent units; SURVEY §8e: no data-path collective for query iteration).
+    gpu = capi.load_gpu()
+    w = capi.World(gpu, device=local_rank, entity_capacity=args.entities + 1024)
+    stream = torch.cuda.Stream(device=dev)
+    w.set_stream(stream.cuda_stream)
+    sched, q = worlds.build_cfg2(w, args.entities, filtered=not args.all_tables)
+    matched_tables = q.match()
+    matched = q.count()
+    rows_per_table = matched // max(1, len(matched_tables))
+    bytes_per_step = matched * worlds.CFG2_BYTES_PER_ENTITY
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        for _ in range(max(3, args.warmup)):
+            sched.run(capi.EXEC_SERIAL)
+            sched.apply_deferred()
+        barrier()
+        clocks = ClockSampler(local_rank)
+        clocks.start()
+        launches0 = w.launch_count()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        t_wall0 = time.perf_counter()
+        for a, b in evs:
+            flush.fill_(1)  # L2 flush between timed iterations (outside the event pair)
+            a.record(stream)
+            sched.run(capi.EXEC_SERIAL)
+            b.record(stream)
+            sched.apply_deferred()
+        barrier()
+        t_wall = time.perf_counter() - t_wall0
+        launches = w.launch_count() - launches0
+        step_ms = [a.elapsed_time(b) for a, b in evs]
+        dev_ms = sum(step_ms)
+
+        # ---- e2e: host buffers, H2D of the frame's Acceleration, run, D2H of Position -------------------------------
+        A, P = worlds.cname("Acceleration"), worlds.cname("Position")
+        h_acc = [torch.empty(rows_per_table * 2, dtype=torch.float32).pin_memory() for _ in matched_tables]
+        h_pos = [torch.empty(rows_per_table * 2, dtype=torch.float32).pin_memory() for _ in matched_tables]
+        for t in h_acc:
+            t.uniform_(-0.125, 0.125)
+        e2e_steps = max(3, min(args.steps, 20))
+
+        def e2e_step():
+            for tbl, src in zip(matched_tables, h_acc):
+                w.column_write(tbl, A, 0, rows_per_table, src.data_ptr())
+            sched.run(capi.EXEC_SERIAL)
+            for tbl, dst in zip(matched_tables, h_pos):
+                w.column_read(tbl, P, 0, rows_per_table, dst.data_ptr())
+            sched.apply_deferred()  # synchronises the stream: results are on the host
+
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        clk = clocks.stop()
+
+    # max over ranks
+    tm = torch.tensor([dev_ms, e2e_s, t_wall], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_s, t_wall = (float(x) for x in tm.tolist())
+    total_units = matched * world_size
+    value = total_units * args.steps / (dev_ms * 1e-3)
+    e2e_value = total_units * e2e_steps / e2e_s
+    peak, peak_kind = peaks()
+    kernel_ms = dev_ms / args.steps  # the system kernel dominates the step (the match kernel is ~2 us)
+    achieved = bytes_per_step / (kernel_ms * 1e-3) / 1e9
+
+    cpu = None
+    if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
+        import ctypes
+        sample_entities = 1 << 21
+        v, spt, m = cpu_reference_leg(sample_entities, 2, 1, threads=1, mode=1)
+        nthreads = capi.load_oracle().fn("hardware_threads", ctypes.c_uint32)()
+        vopt, _, _ = cpu_reference_leg(sample_entities, 5, 1, threads=nthreads, mode=0)
+        cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+               "sample": f"1/8-scale world ({sample_entities} entities, {m} matched rows/step), 2 steps, B-ref = oracle with the "
+                         "reference's per-entity lookup path, single core (the reference has no intra-system parallelism)",
+               "b_opt": {"value": vopt, "cores": int(nthreads), "note": "direct column loops split over all host threads"}}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD if not args.all_tables else WORKLOAD + " [filters dropped: 64 tables]",
+                       "entities_per_gpu": args.entities, "matched_rows_per_gpu": matched,
+                       "parallelism": f"entity-range shards x{world_size}, no data-path collective",
+                       "l2": "256 MiB flush buffer written between timed steps", "exec_mode": "serial stream",
+                       "fma": "off (-fmad=false), bit-exact vs oracle"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_kind": peak_kind, "algorithmic_bytes_per_launch": bytes_per_step,
+                         "kernel": "helios_gpu::for_each_kernel<AccelBody,...>"},
+            "cpu_baseline": cpu,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": matched * 8, "d2h_bytes_per_step": matched * 8,
+                    "steps": e2e_steps, "note": "per step: pinned-host Acceleration columns -> device, Schedule::Run, Position columns -> host"},
+            "gpu_launches": int(launches), "clocks": clk, "wall_s_timed_region": t_wall,
+            "step_ms_min_med_max": [min(step_ms), sorted(step_ms)[len(step_ms) // 2], max(step_ms)],
+        }
+        print(json.dumps(line))
+    w.close()
+    if world_size > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

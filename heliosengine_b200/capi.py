@@ -1,0 +1,443 @@
+"""ctypes bindings over the C ABI declared in include/helios_gpu.h.
+
+`load_gpu()` binds heliosengine_b200/libhelios_gpu.so (hand-written sm_100a kernels).  There is no CPU
+fallback: if the library is missing or no CUDA device is usable the calls raise.  The same wrapper classes
+can be pointed at the test oracle (oracle/liboracle.so exports the same entry points with the prefix
+``helios_oracle_``) — that is done only by tests/, bench.py's cpu_baseline legs and smoke().
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Iterable, Sequence
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REPO_ROOT = os.path.dirname(_HERE)
+
+MAX_COMPONENTS = 64
+MAX_QUERY_COMPONENTS = 8
+TILE_ROWS = 1024
+RESOURCE_BYTES = 4096
+
+OK = 0
+ERR_INVALID_ARGUMENT, ERR_CUDA, ERR_NOT_FOUND, ERR_CAPACITY, ERR_STATE, ERR_CYCLE = -1, -2, -3, -4, -5, -6
+
+CMD_DESTROY, CMD_TRY_DESTROY, CMD_ADD, CMD_TRY_ADD, CMD_REMOVE, CMD_TRY_REMOVE, CMD_CLEAR = range(7)
+EXEC_SERIAL, EXEC_STREAMS, EXEC_GRAPH = 0, 1, 2
+MSG_AUTOMATIC, MSG_MANUAL = 0, 1
+SYSTEM_EMITS_COMMANDS = 1
+
+INVALID_ENTITY = 0xFFFFFFFFFFFFFFFF
+
+_FNV_BASIS = 14695981039346656037
+_FNV_PRIME = 1099511628211
+
+
+def fnv1a(name: str) -> int:
+    """TypeIndex of a type name: FNV-1a-64 (reference utils/hash.hpp:26-32, utils/type_info.hpp:308-311)."""
+    h = _FNV_BASIS
+    for ch in name.encode():
+        h = ((h ^ ch) * _FNV_PRIME) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+def make_entity(index, generation=1):
+    return (np.asarray(index, dtype=np.uint64) | (np.asarray(generation, dtype=np.uint64) << np.uint64(32)))
+
+
+class WorldConfig(C.Structure):
+    _fields_ = [("device", C.c_int32), ("entity_capacity", C.c_uint32), ("table_capacity", C.c_uint32), ("flags", C.c_uint32)]
+
+
+class QueryDesc(C.Structure):
+    _fields_ = [
+        ("n_components", C.c_uint32),
+        ("components", C.c_uint64 * MAX_QUERY_COMPONENTS),
+        ("writes", C.c_uint8 * MAX_QUERY_COMPONENTS),
+        ("n_with", C.c_uint32),
+        ("with_", C.c_uint64 * MAX_COMPONENTS),
+        ("n_without", C.c_uint32),
+        ("without", C.c_uint64 * MAX_COMPONENTS),
+    ]
+
+
+class Command(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("payload_offset", C.c_uint32), ("entity", C.c_uint64), ("component_mask", C.c_uint64)]
+
+
+COMMAND_DTYPE = np.dtype([("kind", "<u4"), ("payload_offset", "<u4"), ("entity", "<u8"), ("component_mask", "<u8")])
+assert COMMAND_DTYPE.itemsize == C.sizeof(Command) == 24
+
+
+class ApplyStats(C.Structure):
+    _fields_ = [
+        ("commands", C.c_uint64), ("effective", C.c_uint64), ("invalid", C.c_uint64), ("moved_rows", C.c_uint64),
+        ("moved_bytes", C.c_uint64), ("resolve_rounds", C.c_uint32), ("used_sequential_fallback", C.c_uint32),
+    ]
+
+
+class SystemDesc(C.Structure):
+    _fields_ = [
+        ("name", C.c_char_p), ("query", C.c_void_p), ("launch", C.c_void_p), ("host_user", C.c_void_p),
+        ("params", C.c_void_p), ("params_size", C.c_uint32), ("flags", C.c_uint32),
+        ("cmd_slots_per_row", C.c_uint32), ("cmd_payload_stride", C.c_uint32),
+        ("writes_message", C.c_uint64), ("reads_message", C.c_uint64), ("writer_capacity", C.c_uint64),
+        ("n_extra_read_components", C.c_uint32), ("n_extra_write_components", C.c_uint32),
+        ("n_read_resources", C.c_uint32), ("n_write_resources", C.c_uint32),
+        ("extra_read_components", C.c_uint64 * 8), ("extra_write_components", C.c_uint64 * 8),
+        ("read_resources", C.c_uint64 * 8), ("write_resources", C.c_uint64 * 8),
+    ]
+
+
+class HeliosError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"status {status}: {message}")
+        self.status = status
+
+
+class Backend:
+    """One loaded shared library + the symbol prefix of its entry points."""
+
+    def __init__(self, path: str, prefix: str):
+        if not os.path.exists(path):
+            raise FileNotFoundError(
+                f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                f"(there is no CPU fallback for the GPU path)")
+        self.lib = C.CDLL(path)
+        self.prefix = prefix
+        self.path = path
+        self.is_gpu = prefix == "helios_gpu_"
+
+    def fn(self, name: str, restype=C.c_int32):
+        f = getattr(self.lib, self.prefix + name)
+        f.restype = restype
+        return f
+
+
+_GPU = None
+_ORACLE = None
+
+
+def load_gpu() -> Backend:
+    global _GPU
+    if _GPU is None:
+        _GPU = Backend(os.path.join(_HERE, "libhelios_gpu.so"), "helios_gpu_")
+    return _GPU
+
+
+def load_oracle() -> Backend:
+    """Test infrastructure only (tests/, smoke(), bench.py cpu_baseline)."""
+    global _ORACLE
+    if _ORACLE is None:
+        _ORACLE = Backend(os.path.join(REPO_ROOT, "oracle", "liboracle.so"), "helios_oracle_")
+    return _ORACLE
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class World:
+    """helios::ecs::World-shaped handle (reference world.hpp) over one backend."""
+
+    def __init__(self, backend: Backend, device: int = 0, entity_capacity: int = 0):
+        self.b = backend
+        self.h = C.c_void_p()
+        cfg = WorldConfig(device, entity_capacity, 0, 0)
+        st = backend.fn("world_create")(C.byref(cfg), C.byref(self.h))
+        if st != OK:
+            raise HeliosError(st, "world_create failed (is a CUDA device visible? there is no CPU fallback)")
+        self.slots: dict[str, int] = {}
+        self.sizes: dict[str, int] = {}
+        self.hash_to_name: dict[int, str] = {}
+        self._keep = []
+
+    # -- plumbing ---------------------------------------------------------------------------------------
+    def _check(self, st: int):
+        if st != OK:
+            msg = self.b.fn("last_error", C.c_char_p)(self.h)
+            raise HeliosError(st, msg.decode() if msg else "")
+
+    def close(self):
+        if self.h:
+            self.b.fn("world_destroy")(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream: int):
+        self._check(self.b.fn("world_set_stream")(self.h, C.c_void_p(cuda_stream)))
+
+    def synchronize(self):
+        if self.b.is_gpu:
+            self._check(self.b.fn("world_synchronize")(self.h))
+
+    def launch_count(self) -> int:
+        return int(self.b.fn("world_launch_count", C.c_uint64)(self.h)) if self.b.is_gpu else 0
+
+    # -- components / entities ------------------------------------------------------------------------------
+    def register_component(self, name: str, size: int, align: int = 4, default: bytes | None = None) -> int:
+        buf = C.create_string_buffer(default, size) if default is not None else None
+        slot = self.b.fn("register_component")(self.h, C.c_uint64(fnv1a(name)), C.c_uint32(size), C.c_uint32(align), buf)
+        if slot < 0:
+            self._check(slot)
+        self.slots[name] = slot
+        self.sizes[name] = size
+        self.hash_to_name[fnv1a(name)] = name
+        return slot
+
+    def mask(self, names: Iterable[str]) -> int:
+        m = 0
+        for n in names:
+            m |= 1 << self.slots[n]
+        return m
+
+    def create_entities(self, n: int) -> np.ndarray:
+        out = np.empty(n, dtype=np.uint64)
+        self._check(self.b.fn("create_entities")(self.h, C.c_uint32(n), _ptr(out)))
+        return out
+
+    def reserve_entities(self, n: int) -> np.ndarray:
+        out = np.empty(n, dtype=np.uint64)
+        self._check(self.b.fn("reserve_entities")(self.h, C.c_uint32(n), _ptr(out)))
+        return out
+
+    def spawn_batch(self, names: Sequence[str], n: int, columns: Sequence[np.ndarray], want_entities: bool = True):
+        hashes = (C.c_uint64 * max(1, len(names)))(*[fnv1a(x) for x in names])
+        cols = [np.ascontiguousarray(c) for c in columns]
+        for nm, c in zip(names, cols):
+            assert c.nbytes == n * self.sizes[nm], (nm, c.nbytes, n, self.sizes[nm])
+        ptrs = (C.c_void_p * max(1, len(names)))(*[c.ctypes.data for c in cols])
+        out = np.empty(n, dtype=np.uint64) if want_entities else None
+        self._check(self.b.fn("spawn_batch")(self.h, hashes, C.c_uint32(len(names)), C.c_uint64(n), ptrs,
+                                             _ptr(out) if out is not None else None))
+        return out
+
+    def entity_count(self) -> int:
+        v = C.c_uint64()
+        self._check(self.b.fn("entity_count")(self.h, C.byref(v)))
+        return v.value
+
+    def entity_location(self, e: int):
+        a, r = C.c_uint32(), C.c_uint32()
+        st = self.b.fn("entity_location")(self.h, C.c_uint64(int(e)), C.byref(a), C.byref(r))
+        if st == ERR_NOT_FOUND:
+            return None
+        self._check(st)
+        return a.value, r.value
+
+    # -- snapshot ---------------------------------------------------------------------------------------------
+    def snapshot(self, columns: bool = True) -> dict:
+        """Canonical dump: archetypes in creation order (sorted type hashes, entities in row order, raw column bytes)
+        plus the entity tables."""
+        n = C.c_uint32()
+        self._check(self.b.fn("snapshot_archetype_count")(self.h, C.byref(n)))
+        archs = []
+        for a in range(n.value):
+            hashes = (C.c_uint64 * MAX_COMPONENTS)()
+            nt, rows = C.c_uint32(), C.c_uint64()
+            self._check(self.b.fn("snapshot_archetype_info")(self.h, C.c_uint32(a), hashes, C.byref(nt), C.byref(rows)))
+            types = [int(hashes[i]) for i in range(nt.value)]
+            ents = np.empty(rows.value, dtype=np.uint64)
+            self._check(self.b.fn("snapshot_archetype_entities")(self.h, C.c_uint32(a), _ptr(ents), C.c_uint64(rows.value)))
+            cols = {}
+            if columns:
+                for t in types:
+                    size = self.sizes[self.hash_to_name[t]]
+                    buf = np.empty(rows.value * size, dtype=np.uint8)
+                    self._check(self.b.fn("snapshot_archetype_column")(self.h, C.c_uint32(a), C.c_uint64(t), _ptr(buf), C.c_uint64(buf.nbytes)))
+                    cols[t] = buf
+            archs.append({"types": types, "entities": ents, "columns": cols})
+        nxt, fc, cur = C.c_uint32(), C.c_uint32(), C.c_int64()
+        self._check(self.b.fn("snapshot_entity_table")(self.h, C.byref(nxt), None, C.c_uint32(0), None, C.c_uint32(0), C.byref(fc), C.byref(cur)))
+        gens = np.full(nxt.value, 0xFFFFFFFF, dtype=np.uint32)
+        free = np.empty(fc.value, dtype=np.uint32)
+        self._check(self.b.fn("snapshot_entity_table")(self.h, C.byref(nxt), _ptr(gens), C.c_uint32(gens.size), _ptr(free), C.c_uint32(free.size), C.byref(fc), C.byref(cur)))
+        return {"archetypes": archs, "next_index": nxt.value, "generations": gens, "free_indices": free,
+                "free_cursor": cur.value, "entity_count": self.entity_count()}
+
+    def column_write(self, archetype: int, name: str, row0: int, rows: int, src_ptr: int):
+        self._check(self.b.fn("archetype_column_write")(self.h, C.c_uint32(archetype), C.c_uint64(fnv1a(name)),
+                                                        C.c_uint64(row0), C.c_uint64(rows), C.c_void_p(src_ptr)))
+
+    def column_read(self, archetype: int, name: str, row0: int, rows: int, dst_ptr: int):
+        self._check(self.b.fn("archetype_column_read")(self.h, C.c_uint32(archetype), C.c_uint64(fnv1a(name)),
+                                                       C.c_uint64(row0), C.c_uint64(rows), C.c_void_p(dst_ptr)))
+
+    # -- queries ----------------------------------------------------------------------------------------------
+    def query(self, components: Sequence[tuple[str, bool]], with_: Sequence[str] = (), without: Sequence[str] = ()) -> "Query":
+        return Query(self, components, with_, without)
+
+    # -- commands ---------------------------------------------------------------------------------------------
+    def enqueue(self, cmds: np.ndarray, payload: bytes | np.ndarray = b""):
+        cmds = np.ascontiguousarray(cmds, dtype=COMMAND_DTYPE)
+        pay = np.frombuffer(payload, dtype=np.uint8) if isinstance(payload, (bytes, bytearray)) else np.ascontiguousarray(payload).view(np.uint8)
+        self._check(self.b.fn("commands_enqueue")(self.h, _ptr(cmds), C.c_uint64(cmds.size), _ptr(pay) if pay.size else None, C.c_uint64(pay.size)))
+
+    def flush(self):
+        self._check(self.b.fn("world_flush")(self.h))
+
+    def update(self):
+        self._check(self.b.fn("world_update")(self.h))
+
+    def apply_stats(self) -> ApplyStats:
+        s = ApplyStats()
+        self._check(self.b.fn("last_apply_stats")(self.h, C.byref(s)))
+        return s
+
+    # -- messages ---------------------------------------------------------------------------------------------
+    def message_register(self, name: str, size: int, policy: int = MSG_AUTOMATIC):
+        self.sizes["msg:" + name] = size
+        self._check(self.b.fn("message_register")(self.h, C.c_uint64(fnv1a(name)), C.c_uint32(size), C.c_uint32(policy)))
+
+    def message_write(self, name: str, data: np.ndarray):
+        data = np.ascontiguousarray(data)
+        n = data.nbytes // self.sizes["msg:" + name]
+        self._check(self.b.fn("message_write")(self.h, C.c_uint64(fnv1a(name)), _ptr(data), C.c_uint64(n)))
+
+    def message_counts(self, name: str):
+        p, c = C.c_uint64(), C.c_uint64()
+        self._check(self.b.fn("message_counts")(self.h, C.c_uint64(fnv1a(name)), C.byref(p), C.byref(c)))
+        return p.value, c.value
+
+    def message_read(self, name: str, which: int) -> np.ndarray:
+        cnt = self.message_counts(name)[which]
+        buf = np.empty(cnt * self.sizes["msg:" + name], dtype=np.uint8)
+        self._check(self.b.fn("message_read")(self.h, C.c_uint64(fnv1a(name)), C.c_uint32(which), _ptr(buf), C.c_uint64(buf.nbytes)))
+        return buf
+
+    def schedule(self, name: str = "Update") -> "Schedule":
+        return Schedule(self, name)
+
+
+class Query:
+    """Query<Cs..., With<...>, Without<...>> (reference query/query.hpp:658-1248)."""
+
+    def __init__(self, world: World, components, with_, without):
+        self.w = world
+        d = QueryDesc()
+        d.n_components = len(components)
+        for i, (name, write) in enumerate(components):
+            d.components[i] = fnv1a(name)
+            d.writes[i] = 1 if write else 0
+        d.n_with = len(with_)
+        for i, name in enumerate(with_):
+            d.with_[i] = fnv1a(name)
+        d.n_without = len(without)
+        for i, name in enumerate(without):
+            d.without[i] = fnv1a(name)
+        self.h = C.c_void_p()
+        world._check(world.b.fn("query_create")(world.h, C.byref(d), C.byref(self.h)))
+
+    def match(self) -> list[int]:
+        out = (C.c_uint32 * 4096)()
+        n = C.c_uint32()
+        if self.w.b.is_gpu:
+            self.w._check(self.w.b.fn("query_match")(self.h, out, C.c_uint32(4096), C.byref(n)))
+        else:
+            self.w._check(self.w.b.fn("query_match_w")(self.w.h, self.h, out, C.c_uint32(4096), C.byref(n)))
+        return [out[i] for i in range(n.value)]
+
+    def count(self) -> int:
+        v = C.c_uint64()
+        if self.w.b.is_gpu:
+            self.w._check(self.w.b.fn("query_count")(self.h, C.byref(v)))
+        else:
+            self.w._check(self.w.b.fn("query_count_w")(self.w.h, self.h, C.byref(v)))
+        return v.value
+
+
+class Schedule:
+    """helios::ecs::Schedule (reference schedule/schedule.hpp, src/ecs/src/schedule/schedule.cpp)."""
+
+    def __init__(self, world: World, name: str):
+        self.w = world
+        self.h = C.c_void_p()
+        world._check(world.b.fn("schedule_create")(world.h, name.encode(), C.byref(self.h)))
+        self._keep = []
+        self.names: list[str] = []
+
+    def add_system(self, name: str, builtin: str, query: Query | None = None, params: bytes = b"", flags: int = 0,
+                   writes_message: str | None = None, reads_message: str | None = None, writer_capacity: int = 0,
+                   cmd_slots_per_row: int = 1, cmd_payload_stride: int = 0,
+                   extra_reads: Sequence[str] = (), extra_writes: Sequence[str] = (),
+                   read_resources: Sequence[str] = (), write_resources: Sequence[str] = ()) -> int:
+        fnp = C.c_void_p()
+        st = self.w.b.fn("builtin_system")(builtin.encode(), C.byref(fnp))
+        if st != OK:
+            raise HeliosError(st, f"no builtin system '{builtin}'")
+        d = SystemDesc()
+        nm = name.encode()
+        pb = C.create_string_buffer(params, len(params)) if params else None
+        self._keep += [nm, pb]
+        d.name = nm
+        d.query = query.h if query is not None else None
+        d.launch = fnp
+        d.params = C.cast(pb, C.c_void_p) if pb is not None else None
+        d.params_size = len(params)
+        d.flags = flags
+        d.cmd_slots_per_row = cmd_slots_per_row
+        d.cmd_payload_stride = cmd_payload_stride
+        d.writes_message = fnv1a(writes_message) if writes_message else 0
+        d.reads_message = fnv1a(reads_message) if reads_message else 0
+        d.writer_capacity = writer_capacity
+        for attr, cnt, names in (("extra_read_components", "n_extra_read_components", extra_reads),
+                                 ("extra_write_components", "n_extra_write_components", extra_writes),
+                                 ("read_resources", "n_read_resources", read_resources),
+                                 ("write_resources", "n_write_resources", write_resources)):
+            setattr(d, cnt, len(names))
+            arr = getattr(d, attr)
+            for i, x in enumerate(names):
+                arr[i] = fnv1a(x)
+        idx = C.c_uint32()
+        self.w._check(self.w.b.fn("schedule_add_system")(self.h, C.byref(d), C.byref(idx)))
+        self.names.append(name)
+        return idx.value
+
+    def add_order(self, first: int, second: int):
+        self.w._check(self.w.b.fn("schedule_add_order")(self.h, C.c_uint32(first), C.c_uint32(second)))
+
+    def build(self):
+        self.w._check(self.w.b.fn("schedule_build")(self.h))
+
+    def execution_order(self) -> list[int]:
+        out = (C.c_uint32 * 64)()
+        n = C.c_uint32()
+        self.w._check(self.w.b.fn("schedule_execution_order")(self.h, out, C.c_uint32(64), C.byref(n)))
+        return [out[i] for i in range(n.value)]
+
+    def conflicts(self) -> list[int]:
+        n = len(self.names)
+        out = (C.c_uint64 * 64)()
+        self.w._check(self.w.b.fn("schedule_conflicts")(self.h, out, C.c_uint32(64)))
+        return [int(out[i]) for i in range(n)]
+
+    def stream_count(self) -> int:
+        v = C.c_uint32()
+        self.w._check(self.w.b.fn("schedule_stream_count")(self.h, C.byref(v)))
+        return v.value
+
+    def run(self, mode: int = EXEC_SERIAL):
+        self.w._check(self.w.b.fn("schedule_run")(self.h, C.c_uint32(mode)))
+
+    def apply_deferred(self):
+        self.w._check(self.w.b.fn("schedule_apply_deferred")(self.h))
+
+    def run_and_wait(self, mode: int = EXEC_SERIAL):
+        self.w._check(self.w.b.fn("schedule_run_and_wait")(self.h, C.c_uint32(mode)))
+
+    def read_resources(self, nbytes: int = 64) -> np.ndarray:
+        buf = np.zeros(nbytes, dtype=np.uint8)
+        self.w._check(self.w.b.fn("schedule_read_resources")(self.h, _ptr(buf), C.c_uint32(nbytes)))
+        return buf
+
+    def close(self):
+        if self.h:
+            self.w.b.fn("schedule_destroy")(self.h)
+            self.h = C.c_void_p()

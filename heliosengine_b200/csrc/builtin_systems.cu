@@ -1,0 +1,236 @@
+// builtin_systems.cu — system bodies of the benchmark / parity workloads, written against the
+// public device API (helios_gpu_device.cuh) exactly as a user plugin would.
+//
+// Float contract: this translation unit is compiled with -fmad=false, so every a*b+c below is a separate
+// IEEE multiply and add — bit-identical to the oracle built with -ffp-contract=off.
+#include <cstring>
+
+#include "helios_gpu_device.cuh"
+
+namespace {
+
+using namespace helios_gpu;
+
+// Benchmark component set: README.md:285-293, examples/ecs/query.cpp:16-29.
+struct Position { float x, y; };
+struct Velocity { float dx, dy; };
+struct Acceleration { float ddx, ddy; };
+struct Mass { float m; };
+struct Health { int32_t hp; };
+struct Team { uint32_t id; };
+struct Tint { uint32_t rgba; };
+struct CollisionEvent {  // 24 B
+  helios_gpu_entity_t a, b;
+  float impulse;
+  uint32_t pad;
+};
+
+// ---- "integrate": README ChangePosition (README.md:305-312): Query<Position&, const Velocity&> ----------
+struct IntegrateBody {
+  __device__ void operator()(const Row&, Position& p, Velocity& v) const {
+    p.x += v.dx;
+    p.y += v.dy;
+  }
+};
+int32_t launch_integrate(const helios_gpu_system_ctx* ctx) {
+  return for_each_launch<0b01u, false, IntegrateBody, Position, Velocity>(ctx, IntegrateBody{});
+}
+
+// ---- "accel_integrate": cfg 2 body  v += a*(dt/m); p += v*dt -----------------------------------------
+struct AccelParams { float dt; };
+struct AccelBody {
+  float dt;
+  __device__ void operator()(const Row&, Position& p, Velocity& v, Acceleration& a, Mass& m) const {
+    const float s = dt / m.m;
+    v.dx = v.dx + a.ddx * s;
+    v.dy = v.dy + a.ddy * s;
+    p.x = p.x + v.dx * dt;
+    p.y = p.y + v.dy * dt;
+  }
+};
+int32_t launch_accel_integrate(const helios_gpu_system_ctx* ctx) {
+  if (ctx->params_size < sizeof(AccelParams)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  AccelParams p;
+  std::memcpy(&p, ctx->params, sizeof(p));
+  return for_each_launch<0b0011u, false, AccelBody, Position, Velocity, Acceleration, Mass>(ctx, AccelBody{p.dt});
+}
+
+// ---- "damp": Query<Velocity&>  v *= k ---------------------------------------------------------------------
+struct DampBody {
+  float k;
+  __device__ void operator()(const Row&, Velocity& v) const {
+    v.dx = v.dx * k;
+    v.dy = v.dy * k;
+  }
+};
+int32_t launch_damp(const helios_gpu_system_ctx* ctx) {
+  if (ctx->params_size < sizeof(float)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  float k;
+  std::memcpy(&k, ctx->params, sizeof(k));
+  return for_each_launch<0b1u, false, DampBody, Velocity>(ctx, DampBody{k});
+}
+
+// ---- "regen": Query<Health&>  hp = min(hp + 1, 100) ---------------------------------------------------------
+struct RegenBody {
+  __device__ void operator()(const Row&, Health& h) const { h.hp = h.hp + 1 > 100 ? 100 : h.hp + 1; }
+};
+int32_t launch_regen(const helios_gpu_system_ctx* ctx) {
+  return for_each_launch<0b1u, false, RegenBody, Health>(ctx, RegenBody{});
+}
+
+// ---- "team_tint": Query<const Team&, Tint&> -----------------------------------------------------------------
+struct TintBody {
+  __device__ void operator()(const Row&, Team& t, Tint& c) const { c.rgba = (t.id * 0x00202020u) | 0xFF000000u; }
+};
+int32_t launch_team_tint(const helios_gpu_system_ctx* ctx) {
+  return for_each_launch<0b10u, false, TintBody, Team, Tint>(ctx, TintBody{});
+}
+
+// ---- "detect": Query<const Position&, const Team&> + MessageWriter<CollisionEvent> -------------------------
+// One event per visited entity, written at slot = position in ForEach order: the device buffer then holds the
+// events in exactly the order the reference's serial ForEach would have emitted them (no atomics needed).
+struct DetectBody {
+  const helios_gpu_msg_writer* d_wr;  // device-resident view: stays valid across buffer swaps (CUDA-graph safe)
+  const helios_gpu_query_view* view;
+  __device__ void operator()(const Row& r, Position& p, Team& t) const {
+    const helios_gpu_msg_writer wr = *d_wr;
+    CollisionEvent ev;
+    ev.a = r.entity;
+    ev.b = r.entity ^ 1ull;  // synthetic partner: the entity with the neighbouring index
+    ev.impulse = p.x * 0.0078125f + float(t.id);
+    ev.pad = 0;
+    if (r.flat_row < wr.capacity) reinterpret_cast<CollisionEvent*>(wr.data)[r.flat_row] = ev;
+    if (r.flat_row == 0) *wr.count = view->n_rows < wr.capacity ? view->n_rows : wr.capacity;
+  }
+};
+int32_t launch_detect(const helios_gpu_system_ctx* ctx) {
+  if (!ctx->writer.data || ctx->writer.elem_size != sizeof(CollisionEvent)) return HELIOS_GPU_ERR_STATE;
+  return for_each_launch<0u, true, DetectBody, Position, Team>(ctx, DetectBody{ctx->d_writer, ctx->view});
+}
+
+// ---- "detect_sparse": same query, emits only when team == 0, through the warp-aggregated append ring ---------
+struct DetectSparseBody {
+  const helios_gpu_msg_writer* d_wr;
+  __device__ void operator()(const Row& r, Position& p, Team& t) const {
+    const helios_gpu_msg_writer wr = *d_wr;
+    CollisionEvent ev;
+    ev.a = r.entity;
+    ev.b = r.entity ^ 1ull;
+    ev.impulse = p.x * 0.0078125f + float(t.id);
+    ev.pad = 0;
+    message_append(wr, t.id == 0u, ev);
+  }
+};
+int32_t launch_detect_sparse(const helios_gpu_system_ctx* ctx) {
+  if (!ctx->writer.data || ctx->writer.elem_size != sizeof(CollisionEvent)) return HELIOS_GPU_ERR_STATE;
+  return for_each_launch<0u, true, DetectSparseBody, Position, Team>(ctx, DetectSparseBody{ctx->d_writer});
+}
+
+// ---- "consume": MessageReader<CollisionEvent> → Health of evt.a -= int(impulse) via Get(evt.a) ---------------
+// Integer atomics make the result independent of event order (several events may target one entity).
+struct ConsumeParams { uint32_t health_slot; };
+__global__ void __launch_bounds__(256) k_consume(const helios_gpu_msg_reader* d_rd, helios_gpu_world_view wv, uint32_t health_slot) {
+  const helios_gpu_msg_reader rd = *d_rd;
+  const unsigned long long np = *rd.previous_count, nc = *rd.current_count;
+  const unsigned long long n = np + nc;
+  for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+       i += (unsigned long long)gridDim.x * blockDim.x) {
+    // reader order = previous ++ current (reader.hpp:793-795)
+    const CollisionEvent* src = i < np ? reinterpret_cast<const CollisionEvent*>(rd.previous) + i
+                                       : reinterpret_cast<const CollisionEvent*>(rd.current) + (i - np);
+    const uint4 lo = __ldcs(reinterpret_cast<const uint4*>(src));
+    const uint2 hi = __ldcs(reinterpret_cast<const uint2*>(src) + 2);
+    const uint32_t idx = lo.x, gen = lo.y;
+    const float impulse = __uint_as_float(hi.x);
+    if (idx >= wv.entity_capacity || wv.entity_generation[idx] != gen) continue;  // stale entity: World::TryGet → null
+    const uint64_t loc = wv.entity_location[idx];
+    if (loc == 0xFFFFFFFFFFFFFFFFull) continue;
+    int32_t* col = static_cast<int32_t*>(wv.table_columns[(loc >> 32) * 64 + health_slot]);
+    if (col) atomicSub(col + uint32_t(loc), int32_t(impulse));
+  }
+}
+int32_t launch_consume(const helios_gpu_system_ctx* ctx) {
+  if (ctx->params_size < sizeof(ConsumeParams) || !ctx->d_reader) return HELIOS_GPU_ERR_STATE;
+  ConsumeParams p;
+  std::memcpy(&p, ctx->params, sizeof(p));
+  k_consume<<<ctx->sm_count * 8, 256, 0, static_cast<cudaStream_t>(ctx->stream)>>>(ctx->d_reader, ctx->world_view, p.health_slot);
+  helios_gpu_world_note_launches(ctx->world, 1);
+  return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
+}
+
+// ---- "stats": Query<const Health&> → resource[0] (u64) += Σ hp  (integer, order independent) -----------------
+struct StatsBody {
+  unsigned long long* acc;
+  __device__ void operator()(const Row&, Health& h) const {
+    // warp-level reduction first, one atomic per warp (blackwell guide §12)
+    long long v = h.hp;
+    const uint32_t m = __activemask();
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(m, v, o);
+    if ((threadIdx.x & 31u) == 0 && m == 0xFFFFFFFFu) atomicAdd(acc, (unsigned long long)v);
+    else if (m != 0xFFFFFFFFu) atomicAdd(acc, (unsigned long long)(long long)h.hp);
+  }
+};
+__global__ void k_zero_u64(unsigned long long* p, int n) {
+  if (threadIdx.x < n) p[threadIdx.x] = 0;
+}
+int32_t launch_stats(const helios_gpu_system_ctx* ctx) {
+  auto* acc = static_cast<unsigned long long*>(ctx->resources);
+  k_zero_u64<<<1, 32, 0, static_cast<cudaStream_t>(ctx->stream)>>>(acc, 1);
+  helios_gpu_world_note_launches(ctx->world, 1);
+  return for_each_launch<0u, false, StatsBody, Health>(ctx, StatsBody{acc});
+}
+
+// ---- "exit_check": resource-only system: resource[1] = (resource[0] == 0) -----------------------------------
+__global__ void k_exit_check(unsigned long long* res) {
+  if (threadIdx.x == 0) res[1] = res[0] == 0 ? 1ull : 0ull;
+}
+int32_t launch_exit_check(const helios_gpu_system_ctx* ctx) {
+  k_exit_check<<<1, 32, 0, static_cast<cudaStream_t>(ctx->stream)>>>(static_cast<unsigned long long*>(ctx->resources));
+  helios_gpu_world_note_launches(ctx->world, 1);
+  return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
+}
+
+// ---- "despawn_dead": Query<const Health&> + Commands: hp <= 0 → commands.Entity(e).Destroy() ------------------
+// One command slot per visited row, slot = ForEach position ⇒ compaction preserves the serial emission order.
+struct DespawnDeadBody {
+  helios_gpu_cmd_writer cw;
+  __device__ void operator()(const Row& r, Health& h) const {
+    if (h.hp <= 0 && r.flat_row < cw.capacity) {
+      helios_gpu_command c;
+      c.kind = HELIOS_GPU_CMD_DESTROY;
+      c.payload_offset = 0;
+      c.entity = r.entity;
+      c.component_mask = 0;
+      cw.records[r.flat_row] = c;
+    }
+  }
+};
+int32_t launch_despawn_dead(const helios_gpu_system_ctx* ctx) {
+  if (!ctx->commands.records) return HELIOS_GPU_ERR_STATE;
+  return for_each_launch<0u, true, DespawnDeadBody, Health>(ctx, DespawnDeadBody{ctx->commands});
+}
+
+struct Entry {
+  const char* name;
+  helios_gpu_system_fn fn;
+};
+const Entry kBuiltins[] = {
+    {"integrate", launch_integrate},   {"accel_integrate", launch_accel_integrate},
+    {"damp", launch_damp},             {"regen", launch_regen},
+    {"team_tint", launch_team_tint},   {"detect", launch_detect},
+    {"detect_sparse", launch_detect_sparse}, {"consume", launch_consume},
+    {"stats", launch_stats},           {"exit_check", launch_exit_check},
+    {"despawn_dead", launch_despawn_dead},
+};
+
+}  // namespace
+
+extern "C" int32_t helios_gpu_builtin_system(const char* name, helios_gpu_system_fn* out) {
+  if (!name || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  for (const Entry& e : kBuiltins)
+    if (std::strcmp(e.name, name) == 0) {
+      *out = e.fn;
+      return HELIOS_GPU_OK;
+    }
+  return HELIOS_GPU_ERR_NOT_FOUND;
+}

@@ -1,0 +1,98 @@
+// common.cuh — error handling, device buffers and launch accounting shared by the C-ABI translation units.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/helios_gpu.h"
+
+namespace hgpu {
+
+// Set the world's error string and return `code` from the enclosing function.
+#define HG_FAIL(w, code, ...)                              \
+  do {                                                     \
+    char _buf[512];                                        \
+    std::snprintf(_buf, sizeof(_buf), __VA_ARGS__);        \
+    (w)->err = _buf;                                       \
+    return (code);                                         \
+  } while (0)
+
+#define HG_CUDA(w, expr)                                                                              \
+  do {                                                                                                \
+    cudaError_t _e = (expr);                                                                          \
+    if (_e != cudaSuccess)                                                                            \
+      HG_FAIL(w, HELIOS_GPU_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+              __LINE__);                                                                              \
+  } while (0)
+
+#define HG_TRY(expr)                  \
+  do {                                \
+    int32_t _s = (expr);              \
+    if (_s != HELIOS_GPU_OK) return _s; \
+  } while (0)
+
+// Growable device allocation.  Growth preserves the first `keep` bytes with a D2D copy on `stream`;
+// the old block is released with cudaFreeAsync-like ordering by freeing after the copy is enqueued
+// (cudaFree synchronises implicitly, which is acceptable at the structural sync points where growth happens).
+struct DevBuf {
+  void* ptr = nullptr;
+  size_t bytes = 0;
+
+  DevBuf() = default;
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  DevBuf(DevBuf&& o) noexcept : ptr(o.ptr), bytes(o.bytes) { o.ptr = nullptr; o.bytes = 0; }
+  DevBuf& operator=(DevBuf&& o) noexcept {
+    if (this != &o) {
+      release();
+      ptr = o.ptr; bytes = o.bytes;
+      o.ptr = nullptr; o.bytes = 0;
+    }
+    return *this;
+  }
+  ~DevBuf() { release(); }
+
+  void release() {
+    if (ptr) cudaFree(ptr);
+    ptr = nullptr;
+    bytes = 0;
+  }
+  // Ensure capacity >= want bytes; keeps the first `keep` bytes.  Returns cudaSuccess or the error.
+  cudaError_t reserve(size_t want, size_t keep, cudaStream_t stream, bool geometric = true) {
+    if (want <= bytes) return cudaSuccess;
+    size_t cap = want;
+    if (geometric && bytes) cap = want > bytes + bytes / 2 ? want : bytes + bytes / 2;
+    cap = (cap + 255) & ~size_t(255);
+    void* np = nullptr;
+    cudaError_t e = cudaMalloc(&np, cap);
+    if (e != cudaSuccess) return e;
+    if (ptr && keep) {
+      e = cudaMemcpyAsync(np, ptr, keep, cudaMemcpyDeviceToDevice, stream);
+      if (e != cudaSuccess) { cudaFree(np); return e; }
+      e = cudaStreamSynchronize(stream);
+      if (e != cudaSuccess) { cudaFree(np); return e; }
+    }
+    if (ptr) cudaFree(ptr);
+    ptr = np;
+    bytes = cap;
+    return cudaSuccess;
+  }
+  template <typename T> T* as() const { return static_cast<T*>(ptr); }
+};
+
+constexpr uint64_t kInvalidLoc = 0xFFFFFFFFFFFFFFFFull;   // location table entry: table<<32 | row
+constexpr uint32_t kInvalidGeneration = 0xFFFFFFFFu;     // entity/entity.hpp:27-30
+
+__host__ __device__ inline uint32_t ent_index(helios_gpu_entity_t e) { return static_cast<uint32_t>(e); }
+__host__ __device__ inline uint32_t ent_gen(helios_gpu_entity_t e) { return static_cast<uint32_t>(e >> 32); }
+__host__ __device__ inline helios_gpu_entity_t make_ent(uint32_t i, uint32_t g) {
+  return static_cast<uint64_t>(i) | (static_cast<uint64_t>(g) << 32);
+}
+
+inline uint32_t div_up(uint64_t a, uint64_t b) { return static_cast<uint32_t>((a + b - 1) / b); }
+
+}  // namespace hgpu

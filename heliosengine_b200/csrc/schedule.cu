@@ -1,0 +1,476 @@
+// schedule.cu — systems, access policies, the conflict DAG and its mapping onto CUDA streams / graphs.
+// Replaces Schedule::Add/Build/Run/RunAndWait/ApplyDeferred (src/ecs/src/schedule/schedule.cpp:55-158,364-425),
+// Dag::Sort (src/ecs/src/schedule/dag.cpp:65-126), AccessPolicy::ConflictsWith
+// (system/access_policy.hpp:172-196) and MultiThreadedExecutor (executor/multi_threaded.cpp:15-115):
+// a Taskflow task per system with conflict-only edges becomes a stream per independent chain with
+// event fork/join on exactly those edges, optionally captured once into a CUDA graph and replayed.
+#include <algorithm>
+#include <queue>
+
+#include "query_internal.hpp"
+
+using namespace hgpu;
+
+namespace {
+
+struct Policy {  // sorted unique type-hash sets
+  std::vector<uint64_t> rc, wc, rr, wr;
+  static void ins(std::vector<uint64_t>& v, uint64_t h) {
+    const auto it = std::lower_bound(v.begin(), v.end(), h);
+    if (it == v.end() || *it != h) v.insert(it, h);
+  }
+  static bool hit(const std::vector<uint64_t>& a, const std::vector<uint64_t>& b) {
+    size_t i = 0, j = 0;
+    while (i < a.size() && j < b.size()) {
+      if (a[i] < b[j]) ++i;
+      else if (b[j] < a[i]) ++j;
+      else return true;
+    }
+    return false;
+  }
+  // access_policy.hpp:172-196 — W∩W ∪ W∩R ∪ R∩W on components or resources; commands/messages never conflict.
+  bool conflicts(const Policy& o) const {
+    return hit(wc, o.wc) || hit(wc, o.rc) || hit(rc, o.wc) || hit(wr, o.wr) || hit(wr, o.rr) || hit(rr, o.wr);
+  }
+};
+
+struct SysEntry {
+  std::string name;
+  helios_gpu_system_desc desc{};
+  std::vector<uint8_t> params;
+  Policy policy;
+  // SystemLocalData (schedule/system_local_data.hpp:23-31) in HBM
+  DevBuf cmd_records, cmd_payload;
+  uint64_t cmd_capacity = 0;       // record slots allocated
+  uint64_t cmd_slots_in_use = 0;   // slots armed for the current run
+  DevBuf msg_data;                 // local message buffer
+  uint64_t msg_capacity = 0;
+  DevBuf d_writer;                 // struct { helios_gpu_msg_writer wr; unsigned long long count; }
+  int stream_id = 0;
+};
+
+struct WriterDev {
+  helios_gpu_msg_writer wr;
+  unsigned long long count;
+};
+
+}  // namespace
+
+struct helios_gpu_schedule {
+  helios_gpu_world* world = nullptr;
+  std::string name;
+  std::vector<std::unique_ptr<SysEntry>> entries;       // registration order
+  std::vector<std::pair<uint32_t, uint32_t>> edges;     // explicit ordering
+  std::vector<uint32_t> order;                           // execution order (entry indices)
+  std::vector<uint64_t> conflicts;                       // by position in `order`
+  bool built = false;
+  DevBuf resources;
+  // stream mapping
+  std::vector<cudaStream_t> streams;                     // streams[0] == world stream
+  std::vector<cudaEvent_t> done;                         // one per position
+  cudaEvent_t fork_ev = nullptr;
+  uint32_t n_streams_used = 1;
+  // graph
+  cudaGraphExec_t graph_exec = nullptr;
+  uint64_t graph_epoch = ~0ull;
+  uint64_t graph_kernels = 0;
+  bool pending = false;   // Run() issued, ApplyDeferred not yet called
+};
+
+namespace {
+
+// Rows the system's query can match right now (host mirror) — sizes the sparse command / message buffers.
+uint64_t host_match_rows(helios_gpu_world* w, const helios_gpu_query* q) {
+  if (!q || q->never_matches) return 0;
+  uint64_t n = 0;
+  for (const Table& t : w->tables)
+    if (t.count && (t.mask & q->required_mask) == q->required_mask && (t.mask & q->without_mask) == 0) n += t.count;
+  return n;
+}
+
+int32_t publish_writer(helios_gpu_world* w, SysEntry& e, MsgChannel* ch) {
+  WriterDev d{};
+  auto* dev = e.d_writer.as<WriterDev>();
+  d.wr.data = e.msg_data.as<uint8_t>();
+  d.wr.count = &dev->count;
+  d.wr.capacity = e.msg_capacity;
+  d.wr.elem_size = ch->size;
+  d.count = 0;
+  HG_CUDA(w, cudaMemcpyAsync(dev, &d, sizeof(d), cudaMemcpyHostToDevice, w->stream));
+  return HELIOS_GPU_OK;
+}
+
+// Host-side preparation before a run: buffer sizing only (no launches), so that the launch pass can be captured.
+int32_t prepare(helios_gpu_schedule* s) {
+  helios_gpu_world* w = s->world;
+  HG_TRY(sync_counts_to_host(w));
+  if (!s->resources.ptr) {
+    HG_CUDA(w, s->resources.reserve(HELIOS_GPU_RESOURCE_BYTES, 0, w->stream, false));
+    HG_CUDA(w, cudaMemsetAsync(s->resources.ptr, 0, HELIOS_GPU_RESOURCE_BYTES, w->stream));
+    ++w->epoch;
+  }
+  for (auto& ep : s->entries) {
+    SysEntry& e = *ep;
+    const uint64_t rows = host_match_rows(w, e.desc.query);
+    if (e.desc.query && (e.desc.query->seg_capacity < w->dir_capacity || e.desc.query->seg_capacity == 0)) {
+      const uint32_t cap = std::max<uint32_t>(w->dir_capacity, 64u);
+      HG_CUDA(w, e.desc.query->d_segments.reserve(size_t(cap) * sizeof(helios_gpu_segment), 0, w->stream, false));
+      e.desc.query->seg_capacity = cap;
+      ++w->epoch;
+    }
+    if (e.desc.flags & HELIOS_GPU_SYSTEM_EMITS_COMMANDS) {
+      const uint64_t slots = rows * std::max<uint32_t>(1u, e.desc.cmd_slots_per_row);
+      if (slots > e.cmd_capacity) {
+        const uint64_t cap = slots + slots / 4 + 1024;
+        HG_CUDA(w, e.cmd_records.reserve(cap * sizeof(helios_gpu_command), 0, w->stream, false));
+        if (e.desc.cmd_payload_stride) HG_CUDA(w, e.cmd_payload.reserve(cap * e.desc.cmd_payload_stride, 0, w->stream, false));
+        e.cmd_capacity = cap;
+        ++w->epoch;
+      }
+      if (slots != e.cmd_slots_in_use) ++w->epoch;  // memset extent is baked into a captured graph
+      e.cmd_slots_in_use = slots;
+    }
+    if (e.desc.writes_message) {
+      MsgChannel* ch = find_channel(w, e.desc.writes_message);
+      if (!ch) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "system '%s' writes an unregistered message type", e.name.c_str());
+      const uint64_t want = e.desc.writer_capacity ? e.desc.writer_capacity : rows;
+      if (!e.d_writer.ptr) HG_CUDA(w, e.d_writer.reserve(sizeof(WriterDev), 0, w->stream, false));
+      if (want * ch->size > e.msg_data.bytes || e.msg_capacity < want) {
+        HG_CUDA(w, e.msg_data.reserve((want + want / 4 + 256) * ch->size, 0, w->stream, false));
+      }
+      e.msg_capacity = e.msg_data.bytes / ch->size;
+      HG_TRY(publish_writer(w, e, ch));  // also zeroes the counter
+    }
+    if (e.desc.reads_message && !find_channel(w, e.desc.reads_message))
+      HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "system '%s' reads an unregistered message type", e.name.c_str());
+  }
+  return HELIOS_GPU_OK;
+}
+
+// Enqueue one system on `stream`: arm its local buffers, device-side match, then the body.
+int32_t launch_system(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaStream_t stream) {
+  helios_gpu_world* w = s->world;
+  helios_gpu_system_ctx ctx{};
+  ctx.world = w;
+  ctx.stream = stream;
+  ctx.sm_count = uint32_t(w->sm_count);
+  ctx.system_index = index;
+  ctx.params = e.params.data();
+  ctx.params_size = uint32_t(e.params.size());
+  ctx.resources = s->resources.ptr;
+  ctx.host_user = e.desc.host_user;
+  ctx.world_view.entity_location = w->d_loc.as<uint64_t>();
+  ctx.world_view.entity_generation = w->d_gen.as<uint32_t>();
+  ctx.world_view.table_columns = w->d_tcols.as<void*>();
+  ctx.world_view.table_mask = w->d_tmask.as<uint64_t>();
+  ctx.world_view.entity_capacity = w->ent_capacity;
+  ctx.world_view.n_tables = uint32_t(w->tables.size());
+  if (e.desc.query) {
+    HG_TRY(query_refresh(e.desc.query, stream));
+    ctx.view = e.desc.query->d_view.as<helios_gpu_query_view>();
+  }
+  if (e.desc.flags & HELIOS_GPU_SYSTEM_EMITS_COMMANDS) {
+    if (e.cmd_slots_in_use)  // all-ones = kind NONE in every slot
+      HG_CUDA(w, cudaMemsetAsync(e.cmd_records.ptr, 0xFF, e.cmd_slots_in_use * sizeof(helios_gpu_command), stream));
+    ctx.commands.records = e.cmd_records.as<helios_gpu_command>();
+    ctx.commands.payload = e.cmd_payload.as<uint8_t>();
+    ctx.commands.capacity = e.cmd_slots_in_use;
+    ctx.commands.payload_stride = e.desc.cmd_payload_stride;
+    ctx.commands.slots_per_row = std::max<uint32_t>(1u, e.desc.cmd_slots_per_row);
+  }
+  if (e.desc.writes_message) {
+    MsgChannel* ch = find_channel(w, e.desc.writes_message);
+    auto* dev = e.d_writer.as<WriterDev>();
+    ctx.writer.data = e.msg_data.as<uint8_t>();
+    ctx.writer.count = &dev->count;
+    ctx.writer.capacity = e.msg_capacity;
+    ctx.writer.elem_size = ch->size;
+    ctx.d_writer = &dev->wr;
+  }
+  if (e.desc.reads_message) {
+    MsgChannel* ch = find_channel(w, e.desc.reads_message);
+    auto* dev = ch->d_dev.as<ChannelDev>();
+    ctx.reader.previous = ch->prev.as<uint8_t>();
+    ctx.reader.current = ch->cur.as<uint8_t>();
+    ctx.reader.previous_count = &dev->counts[0];
+    ctx.reader.current_count = &dev->counts[1];
+    ctx.reader.elem_size = ch->size;
+    ctx.d_reader = &dev->rd;
+  }
+  const int32_t st = e.desc.launch(&ctx);
+  if (st != HELIOS_GPU_OK) HG_FAIL(w, st, "system '%s' failed to launch (%d): %s", e.name.c_str(), st,
+                                   cudaGetErrorString(cudaGetLastError()));
+  return HELIOS_GPU_OK;
+}
+
+// MultiThreadedExecutor::BuildGraph (multi_threaded.cpp:79-98): edges = conflict pairs i<j in execution order.
+// Stream assignment: a system continues the stream of one of its predecessors when that predecessor is still
+// the tail of its stream, otherwise it takes the lowest-numbered stream whose tail it does not race with.
+void assign_streams(helios_gpu_schedule* s) {
+  const size_t n = s->order.size();
+  std::vector<int> tail;  // per stream: position of the last system placed on it
+  for (size_t j = 0; j < n; ++j) {
+    int chosen = -1;
+    for (size_t st = 0; st < tail.size() && chosen < 0; ++st)
+      if (s->conflicts[j] >> tail[st] & 1) chosen = int(st);  // chain onto a conflicting predecessor's stream
+    if (chosen < 0) {
+      chosen = int(tail.size());
+      tail.push_back(int(j));
+    }
+    tail[chosen] = int(j);
+    s->entries[s->order[j]]->stream_id = chosen;
+  }
+  s->n_streams_used = uint32_t(std::max<size_t>(1, tail.size()));
+}
+
+int32_t ensure_streams(helios_gpu_schedule* s) {
+  helios_gpu_world* w = s->world;
+  if (s->streams.empty()) s->streams.push_back(w->stream);
+  s->streams[0] = w->stream;
+  while (s->streams.size() < s->n_streams_used) {
+    cudaStream_t st;
+    HG_CUDA(w, cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    s->streams.push_back(st);
+  }
+  while (s->done.size() < s->order.size()) {
+    cudaEvent_t ev;
+    HG_CUDA(w, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    s->done.push_back(ev);
+  }
+  if (!s->fork_ev) HG_CUDA(w, cudaEventCreateWithFlags(&s->fork_ev, cudaEventDisableTiming));
+  return HELIOS_GPU_OK;
+}
+
+int32_t launch_all(helios_gpu_schedule* s, bool multi_stream) {
+  helios_gpu_world* w = s->world;
+  const size_t n = s->order.size();
+  if (!multi_stream || s->n_streams_used <= 1) {
+    for (size_t j = 0; j < n; ++j) HG_TRY(launch_system(s, *s->entries[s->order[j]], s->order[j], w->stream));
+    return HELIOS_GPU_OK;
+  }
+  // fork: every secondary stream waits for the point the primary stream has reached
+  HG_CUDA(w, cudaEventRecord(s->fork_ev, w->stream));
+  for (uint32_t st = 1; st < s->n_streams_used; ++st) HG_CUDA(w, cudaStreamWaitEvent(s->streams[st], s->fork_ev, 0));
+  for (size_t j = 0; j < n; ++j) {
+    SysEntry& e = *s->entries[s->order[j]];
+    cudaStream_t st = s->streams[e.stream_id];
+    for (size_t i = 0; i < j; ++i)  // conflict edges only (multi_threaded.cpp:79-98)
+      if ((s->conflicts[j] >> i & 1) && s->entries[s->order[i]]->stream_id != e.stream_id)
+        HG_CUDA(w, cudaStreamWaitEvent(st, s->done[i], 0));
+    HG_TRY(launch_system(s, e, s->order[j], st));
+    HG_CUDA(w, cudaEventRecord(s->done[j], st));
+  }
+  // join: the primary stream waits for the tail of every secondary stream
+  std::vector<int> last(s->n_streams_used, -1);
+  for (size_t j = 0; j < n; ++j) last[s->entries[s->order[j]]->stream_id] = int(j);
+  for (uint32_t st = 1; st < s->n_streams_used; ++st)
+    if (last[st] >= 0) HG_CUDA(w, cudaStreamWaitEvent(w->stream, s->done[last[st]], 0));
+  return HELIOS_GPU_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void helios_gpu_world_note_launches(helios_gpu_world* w, uint32_t n) {
+  if (w) w->launches += n;
+}
+
+int32_t helios_gpu_schedule_create(helios_gpu_world* w, const char* name, helios_gpu_schedule** out) {
+  if (!w || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  auto* s = new helios_gpu_schedule();
+  s->world = w;
+  s->name = name ? name : "";
+  w->schedules.push_back(s);
+  *out = s;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_destroy(helios_gpu_schedule* s) {
+  if (!s) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  helios_gpu_world* w = s->world;
+  cudaStreamSynchronize(w->stream);
+  for (size_t i = 1; i < s->streams.size(); ++i) {
+    cudaStreamSynchronize(s->streams[i]);
+    cudaStreamDestroy(s->streams[i]);
+  }
+  for (cudaEvent_t e : s->done) cudaEventDestroy(e);
+  if (s->fork_ev) cudaEventDestroy(s->fork_ev);
+  if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
+  auto& v = w->schedules;
+  v.erase(std::remove(v.begin(), v.end(), s), v.end());
+  delete s;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_add_system(helios_gpu_schedule* s, const helios_gpu_system_desc* d, uint32_t* out_index) {
+  if (!s || !d || !d->launch) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  helios_gpu_world* w = s->world;
+  if (d->n_extra_read_components > 8 || d->n_extra_write_components > 8 || d->n_read_resources > 8 || d->n_write_resources > 8)
+    HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "access lists hold at most 8 entries");
+  if (s->entries.size() >= 64) HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "a schedule holds at most 64 systems (conflict bitmask, schedule.cpp:367)");
+  auto e = std::make_unique<SysEntry>();
+  e->name = d->name ? d->name : "";
+  e->desc = *d;
+  e->desc.name = nullptr;
+  if (d->params && d->params_size) e->params.assign(static_cast<const uint8_t*>(d->params), static_cast<const uint8_t*>(d->params) + d->params_size);
+  e->desc.params = nullptr;
+  // SystemParamTraits<Query>::RegisterAccess (system/param_traits.hpp:55-60): mutable → write set, const → read set.
+  if (d->query)
+    for (uint32_t k = 0; k < d->query->desc.n_components; ++k)
+      Policy::ins(d->query->desc.writes[k] ? e->policy.wc : e->policy.rc, d->query->desc.components[k]);
+  for (uint32_t k = 0; k < d->n_extra_read_components; ++k) Policy::ins(e->policy.rc, d->extra_read_components[k]);
+  for (uint32_t k = 0; k < d->n_extra_write_components; ++k) Policy::ins(e->policy.wc, d->extra_write_components[k]);
+  for (uint32_t k = 0; k < d->n_read_resources; ++k) Policy::ins(e->policy.rr, d->read_resources[k]);
+  for (uint32_t k = 0; k < d->n_write_resources; ++k) Policy::ins(e->policy.wr, d->write_resources[k]);
+  if (out_index) *out_index = uint32_t(s->entries.size());
+  s->entries.push_back(std::move(e));
+  s->built = false;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_add_order(helios_gpu_schedule* s, uint32_t first, uint32_t second) {
+  if (!s) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (first >= s->entries.size() || second >= s->entries.size())
+    HG_FAIL(s->world, HELIOS_GPU_ERR_NOT_FOUND, "unknown system in ordering edge");  // DagErrorKind::kUnknownNode
+  if (first == second) HG_FAIL(s->world, HELIOS_GPU_ERR_CYCLE, "self-loop in ordering");  // dag.cpp:41-49
+  s->edges.emplace_back(first, second);
+  s->built = false;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_build(helios_gpu_schedule* s) {
+  if (!s) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  helios_gpu_world* w = s->world;
+  const size_t n = s->entries.size();
+  // Kahn with insertion-index tie-break (dag.cpp:65-126)
+  std::vector<std::vector<uint32_t>> adj(n);
+  std::vector<uint32_t> indeg(n, 0);
+  for (const auto& [a, b] : s->edges) {
+    adj[a].push_back(b);
+    ++indeg[b];
+  }
+  std::priority_queue<uint32_t, std::vector<uint32_t>, std::greater<uint32_t>> q;
+  for (uint32_t i = 0; i < n; ++i)
+    if (indeg[i] == 0) q.push(i);
+  s->order.clear();
+  while (!q.empty()) {
+    const uint32_t c = q.top();
+    q.pop();
+    s->order.push_back(c);
+    for (const uint32_t t : adj[c])
+      if (--indeg[t] == 0) q.push(t);
+  }
+  if (s->order.size() != n) HG_FAIL(w, HELIOS_GPU_ERR_CYCLE, "cycle detected in system ordering DAG");
+  // BuildConflictData (schedule.cpp:364-395)
+  s->conflicts.assign(n, 0);
+  for (size_t i = 0; i < n; ++i)
+    for (size_t j = i + 1; j < n; ++j)
+      if (s->entries[s->order[i]]->policy.conflicts(s->entries[s->order[j]]->policy)) {
+        s->conflicts[i] |= 1ull << j;
+        s->conflicts[j] |= 1ull << i;
+      }
+  assign_streams(s);
+  s->built = true;
+  s->graph_epoch = ~0ull;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_execution_order(helios_gpu_schedule* s, uint32_t* out, uint32_t cap, uint32_t* count) {
+  if (!s || !s->built) return HELIOS_GPU_ERR_STATE;
+  if (count) *count = uint32_t(s->order.size());
+  if (out) {
+    if (cap < s->order.size()) return HELIOS_GPU_ERR_CAPACITY;
+    std::copy(s->order.begin(), s->order.end(), out);
+  }
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_conflicts(helios_gpu_schedule* s, uint64_t* out, uint32_t cap) {
+  if (!s || !s->built || !out) return HELIOS_GPU_ERR_STATE;
+  if (cap < s->conflicts.size()) return HELIOS_GPU_ERR_CAPACITY;
+  std::copy(s->conflicts.begin(), s->conflicts.end(), out);
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_stream_count(helios_gpu_schedule* s, uint32_t* out) {
+  if (!s || !s->built || !out) return HELIOS_GPU_ERR_STATE;
+  *out = s->n_streams_used;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_run(helios_gpu_schedule* s, uint32_t mode) {
+  if (!s) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  helios_gpu_world* w = s->world;
+  if (!s->built) HG_FAIL(w, HELIOS_GPU_ERR_STATE, "Schedule::Run called but schedule is dirty: call build first");  // schedule.cpp:56-58
+  if (s->pending) HG_FAIL(w, HELIOS_GPU_ERR_STATE, "schedule '%s' still has unapplied local data: call apply_deferred", s->name.c_str());  // :61-66
+  HG_TRY(prepare(s));
+  HG_TRY(ensure_streams(s));
+  if (mode == HELIOS_GPU_EXEC_GRAPH) {
+    if (!s->graph_exec || s->graph_epoch != w->epoch) {
+      if (s->graph_exec) { cudaGraphExecDestroy(s->graph_exec); s->graph_exec = nullptr; }
+      cudaGraph_t g = nullptr;
+      const uint64_t launches_before = w->launches;
+      HG_CUDA(w, cudaStreamBeginCapture(w->stream, cudaStreamCaptureModeThreadLocal));
+      const int32_t st = launch_all(s, true);
+      const cudaError_t ce = cudaStreamEndCapture(w->stream, &g);
+      if (st != HELIOS_GPU_OK) { if (g) cudaGraphDestroy(g); return st; }
+      if (ce != cudaSuccess) HG_FAIL(w, HELIOS_GPU_ERR_CUDA, "graph capture failed: %s", cudaGetErrorString(ce));
+      const cudaError_t ie = cudaGraphInstantiate(&s->graph_exec, g, 0);
+      cudaGraphDestroy(g);
+      if (ie != cudaSuccess) HG_FAIL(w, HELIOS_GPU_ERR_CUDA, "graph instantiate failed: %s", cudaGetErrorString(ie));
+      s->graph_epoch = w->epoch;
+      s->graph_kernels = w->launches - launches_before;  // kernels one replay launches
+      w->launches = launches_before;
+    }
+    HG_CUDA(w, cudaGraphLaunch(s->graph_exec, w->stream));
+    w->launches += s->graph_kernels;
+  } else {
+    HG_TRY(launch_all(s, mode == HELIOS_GPU_EXEC_STREAMS));
+  }
+  s->pending = true;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_apply_deferred(helios_gpu_schedule* s) {
+  if (!s) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  helios_gpu_world* w = s->world;
+  HG_CUDA(w, cudaStreamSynchronize(w->stream));  // Executor::Wait — secondary streams are already joined into it
+  HG_TRY(helios_gpu_world_flush(w));              // schedule.cpp:111 world.Flush()
+  for (auto& ep : s->entries) {                   // schedule.cpp:112-114 REGISTRATION order
+    SysEntry& e = *ep;
+    // SystemLocalData::ExecuteCommands (system_local_data.hpp:111)
+    if ((e.desc.flags & HELIOS_GPU_SYSTEM_EMITS_COMMANDS) && e.cmd_slots_in_use && s->pending)
+      HG_TRY(apply_queue(w, e.cmd_records.as<helios_gpu_command>(), e.cmd_payload.as<uint8_t>(), e.cmd_slots_in_use,
+                         e.desc.cmd_payload_stride));
+    // SystemLocalData::MergeMessages (system_local_data.hpp:122-132)
+    HG_TRY(messages_update_from_system(w));
+    if (e.desc.writes_message && s->pending) {
+      MsgChannel* ch = find_channel(w, e.desc.writes_message);
+      unsigned long long cnt = 0;
+      HG_CUDA(w, cudaMemcpyAsync(&cnt, &e.d_writer.as<WriterDev>()->count, 8, cudaMemcpyDeviceToHost, w->stream));
+      HG_CUDA(w, cudaStreamSynchronize(w->stream));
+      const uint64_t n = std::min<uint64_t>(cnt, e.msg_capacity);
+      HG_TRY(channel_merge_local(w, ch, e.msg_data, n));
+      e.msg_capacity = ch->size ? e.msg_data.bytes / ch->size : 0;
+    }
+  }
+  s->pending = false;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_run_and_wait(helios_gpu_schedule* s, uint32_t mode) {
+  HG_TRY(helios_gpu_schedule_run(s, mode));
+  return helios_gpu_schedule_apply_deferred(s);
+}
+
+int32_t helios_gpu_schedule_read_resources(helios_gpu_schedule* s, void* out, uint32_t bytes) {
+  if (!s || !out || bytes > HELIOS_GPU_RESOURCE_BYTES) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  helios_gpu_world* w = s->world;
+  if (!s->resources.ptr) { std::memset(out, 0, bytes); return HELIOS_GPU_OK; }
+  HG_CUDA(w, cudaMemcpyAsync(out, s->resources.ptr, bytes, cudaMemcpyDeviceToHost, w->stream));
+  HG_CUDA(w, cudaStreamSynchronize(w->stream));
+  return HELIOS_GPU_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,144 @@
+// world_internal.hpp — host-side bookkeeping of the HBM-resident world.
+//
+// Data layout in HBM:
+//   * one table per archetype (component/archetype.hpp:50-340): a dense helios_gpu_entity_t column plus one
+//     contiguous SoA column per component, each a separate 256-byte-aligned allocation of `capacity` rows;
+//   * device mirrors of the table directory (mask / live row count / column base pointers) so that
+//     query matching, command classification and the row mover never leave the device;
+//   * entity tables indexed by entity index: generation (entity/manager.hpp generations_) and packed
+//     location table<<32|row (replaces unordered_map<index,Archetype&> + flat_map<index,row>,
+//     component/manager.hpp:993-999, archetype.hpp:318-325).
+#pragma once
+
+#include <memory>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "common.cuh"
+
+namespace hgpu {
+
+struct Component {
+  uint64_t hash = 0;
+  uint32_t size = 0;
+  uint32_t align = 1;
+  std::vector<uint8_t> def;  // default-constructed value
+};
+
+struct Table {
+  uint64_t mask = 0;
+  std::vector<int> slots;     // component slots sorted by type hash == ArchetypeId::Types() order
+  uint64_t count = 0;         // host mirror of the live row count
+  uint64_t capacity = 0;      // rows
+  DevBuf entities;
+  std::vector<DevBuf> cols;   // parallel to `slots`
+};
+
+struct MsgChannel {           // one registered message type: double buffer (message/manager.hpp:549-560)
+  uint64_t hash = 0;
+  uint32_t size = 0;
+  uint32_t policy = 0;
+  DevBuf cur, prev;
+  uint64_t cur_count = 0, prev_count = 0;   // host mirrors
+  DevBuf d_dev;                              // ChannelDev: reader view + {prev, cur} counters for device readers
+};
+
+struct ChannelDev {
+  helios_gpu_msg_reader rd;
+  unsigned long long counts[2];  // {previous, current}
+};
+
+struct HostCmdQueue {         // host staging of a CmdQueue (command/queue.hpp:137-163)
+  std::vector<helios_gpu_command> cmds;
+  std::vector<uint8_t> payload;
+  void clear() { cmds.clear(); payload.clear(); }
+};
+
+}  // namespace hgpu
+
+struct helios_gpu_query {
+  helios_gpu_world* world = nullptr;
+  helios_gpu_query_desc desc{};
+  int slots[HELIOS_GPU_MAX_QUERY_COMPONENTS] = {};
+  uint64_t required_mask = 0;   // With ∪ data components
+  uint64_t without_mask = 0;
+  bool never_matches = false;   // an unregistered With/required type (query.hpp:1754-1757, quirk #9)
+  hgpu::DevBuf d_view;          // helios_gpu_query_view
+  hgpu::DevBuf d_segments;      // helios_gpu_segment[table capacity]
+  uint32_t seg_capacity = 0;
+};
+
+struct helios_gpu_world {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  int sm_count = 148;
+  mutable std::string err;
+  uint64_t launches = 0;
+  uint64_t epoch = 0;          // bumped whenever a device pointer or directory size a captured graph bakes in changes
+
+  std::vector<hgpu::Component> comps;
+  std::unordered_map<uint64_t, int> slot_of;       // type hash -> slot
+
+  std::vector<hgpu::Table> tables;                 // creation order (manager.hpp:1874)
+  std::unordered_map<uint64_t, int> table_of_mask;
+  int empty_table = -1;                            // ComponentManager::empty_archetype_
+
+  // device table directory
+  uint32_t dir_capacity = 0;
+  hgpu::DevBuf d_tmask;    // uint64_t[dir_capacity]
+  hgpu::DevBuf d_tcount;   // uint32_t[dir_capacity]   authoritative live row counts
+  hgpu::DevBuf d_tents;    // helios_gpu_entity_t*[dir_capacity]
+  hgpu::DevBuf d_tcols;    // void*[dir_capacity * 64]   indexed [table*64 + slot]
+  hgpu::DevBuf d_csize;    // uint32_t[64] component sizes
+  bool counts_dirty = false;   // host Table::count mirrors stale (device applied commands)
+
+  // EntityManager state (entity/manager.hpp)
+  uint32_t next_index = 0;     // next_index_
+  uint32_t flushed_index = 0;  // indices below this have a valid generation (Flush has seen them)
+  uint32_t ent_capacity = 0;
+  hgpu::DevBuf d_gen;          // uint32_t[ent_capacity]
+  hgpu::DevBuf d_loc;          // uint64_t[ent_capacity]  table<<32|row
+  hgpu::DevBuf d_free;         // uint32_t free_indices_
+  uint64_t free_count = 0;
+  int64_t free_cursor = 0;
+  uint64_t live_count = 0;     // entity_count_
+
+  hgpu::HostCmdQueue global_queue;   // World::command_queue_
+  helios_gpu_apply_stats last_stats{};
+
+  std::vector<std::unique_ptr<hgpu::MsgChannel>> channels;
+  std::unordered_map<uint64_t, int> channel_of;
+
+  std::vector<helios_gpu_query*> queries;
+  std::vector<helios_gpu_schedule*> schedules;
+
+  // scratch for the command pipeline (commands.cu)
+  struct ApplyScratch;
+  ApplyScratch* apply = nullptr;
+};
+
+namespace hgpu {
+// world.cu
+int32_t ensure_entity_capacity(helios_gpu_world* w, uint32_t n);
+int32_t ensure_table(helios_gpu_world* w, uint64_t mask, int* out_table);
+int32_t ensure_table_rows(helios_gpu_world* w, int table, uint64_t rows);
+int32_t publish_table(helios_gpu_world* w, int table);      // refresh the device directory row of one table
+int32_t sync_counts_to_host(helios_gpu_world* w);
+int32_t set_table_count(helios_gpu_world* w, int table, uint64_t count);
+// commands.cu
+int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const uint8_t* d_payload, uint64_t n,
+                    uint32_t payload_stride_hint);
+int32_t apply_host_queue(helios_gpu_world* w, HostCmdQueue& q);
+int32_t flush_reserved(helios_gpu_world* w);
+void free_apply_scratch(helios_gpu_world* w);
+// messages.cu
+int32_t messages_update_from_system(helios_gpu_world* w);   // MessageManager::Update(consumed) manager.hpp:376-398
+int32_t messages_update(helios_gpu_world* w);               // MessageManager::Update()          manager.hpp:400-419
+MsgChannel* find_channel(helios_gpu_world* w, uint64_t hash);
+int32_t channel_append_device(helios_gpu_world* w, MsgChannel* ch, const void* d_src, uint64_t n);
+// Merge a system-local buffer into world current; adopts the buffer (pointer swap) when current is empty.
+int32_t channel_merge_local(helios_gpu_world* w, MsgChannel* ch, DevBuf& local, uint64_t n);
+int32_t publish_channel(helios_gpu_world* w, MsgChannel* ch);
+}  // namespace hgpu

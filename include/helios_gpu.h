@@ -102,6 +102,14 @@ HELIOS_GPU_API int32_t helios_gpu_snapshot_entity_table(helios_gpu_world* w, uin
                                                         uint32_t* generations, uint32_t gen_capacity,
                                                         uint32_t* free_indices, uint32_t free_capacity,
                                                         uint32_t* free_count, int64_t* free_cursor);
+/* Overwrite rows [row0, row0+rows) of one column from host memory (asynchronous on the world stream when the
+ * source is pinned) — the per-frame input path of the end-to-end measurement; Archetype::ComponentColumn<T>()
+ * (component/archetype.hpp:578-602) is the reference's closest interface. */
+HELIOS_GPU_API int32_t helios_gpu_archetype_column_write(helios_gpu_world* w, uint32_t archetype, uint64_t type_hash,
+                                                         uint64_t row0, uint64_t rows, const void* src);
+/* Asynchronous counterpart of snapshot_archetype_column for a row range (no stream synchronisation). */
+HELIOS_GPU_API int32_t helios_gpu_archetype_column_read(helios_gpu_world* w, uint32_t archetype, uint64_t type_hash,
+                                                        uint64_t row0, uint64_t rows, void* dst);
 /* Location of one entity (ComponentManager::EntityArchetype + Archetype::Row, archetype.hpp:604-612). */
 HELIOS_GPU_API int32_t helios_gpu_entity_location(helios_gpu_world* w, helios_gpu_entity_t e, uint32_t* archetype,
                                                   uint32_t* row);
@@ -229,6 +237,17 @@ typedef struct helios_gpu_cmd_writer { /* SystemLocalData::cmd_queue (param_trai
   uint32_t slots_per_row;
 } helios_gpu_cmd_writer;
 
+/* Device directory for random access by entity id — World::Get/TryGet<T>(entity) from inside a body
+ * (component/manager.hpp:1613-1635): location[index] = table<<32|row, then columns[table*64 + slot][row]. */
+typedef struct helios_gpu_world_view {
+  const uint64_t* entity_location;   /* [entity index] table<<32 | row, all-ones if not placed */
+  const uint32_t* entity_generation; /* [entity index] */
+  void* const* table_columns;        /* [table*64 + component slot] column base or NULL */
+  const uint64_t* table_mask;        /* [table] component-slot mask */
+  uint32_t entity_capacity;
+  uint32_t n_tables;
+} helios_gpu_world_view;
+
 /* ---- systems and schedules (schedule/schedule.hpp:334-362; src/ecs/src/schedule/schedule.cpp) ---- */
 typedef struct helios_gpu_system_ctx {
   helios_gpu_world* world;
@@ -240,8 +259,11 @@ typedef struct helios_gpu_system_ctx {
   uint32_t params_size;
   uint32_t _pad;
   helios_gpu_cmd_writer commands;      /* valid if the system declared HELIOS_GPU_SYSTEM_EMITS_COMMANDS */
-  helios_gpu_msg_writer writer;        /* valid if writes_message != 0 */
-  helios_gpu_msg_reader reader;        /* valid if reads_message != 0 */
+  helios_gpu_msg_writer writer;        /* valid if writes_message != 0 (host copy, valid for this launch only) */
+  helios_gpu_msg_reader reader;        /* valid if reads_message != 0 (host copy, valid for this launch only) */
+  const helios_gpu_msg_writer* d_writer; /* DEVICE copies of the two views: stable addresses whose contents the */
+  const helios_gpu_msg_reader* d_reader; /* library refreshes at every message-lifecycle step (CUDA-graph safe) */
+  helios_gpu_world_view world_view;    /* entity-id random access */
   void* resources;                     /* device scratch of HELIOS_GPU_RESOURCE_BYTES shared by the schedule's systems */
   void* host_user;
 } helios_gpu_system_ctx;
@@ -297,6 +319,9 @@ HELIOS_GPU_API int32_t helios_gpu_schedule_run_and_wait(helios_gpu_schedule* s, 
 HELIOS_GPU_API int32_t helios_gpu_schedule_stream_count(helios_gpu_schedule* s, uint32_t* out);
 /* Copy the schedule's device resource scratch (HELIOS_GPU_RESOURCE_BYTES) to the host. */
 HELIOS_GPU_API int32_t helios_gpu_schedule_read_resources(helios_gpu_schedule* s, void* out, uint32_t bytes);
+
+/* Launch accounting: a system body reports the kernels it enqueued (for_each_launch does this itself). */
+HELIOS_GPU_API void helios_gpu_world_note_launches(helios_gpu_world* w, uint32_t n);
 
 /* Built-in system bodies compiled into the library (bench + parity workloads); see
  * heliosengine_b200/csrc/builtin_systems.cu for the list.  User bodies are written against

@@ -1,0 +1,576 @@
+// oracle_capi.cpp — C entry points over the CPU oracle, mirroring include/helios_gpu.h name for name
+// (prefix helios_oracle_ instead of helios_gpu_) so that the parity tests drive both sides with identical calls.
+//
+// *** TEST INFRASTRUCTURE ONLY *** (see helios_oracle.hpp).  Built into oracle/liboracle.so by oracle/Makefile
+// with -ffp-contract=off so that float system bodies match the GPU build (-fmad=false) bit for bit.
+#include <atomic>
+#include <chrono>
+#include <cstdio>
+#include <thread>
+
+#include "../include/helios_gpu.h"
+#include "helios_oracle.hpp"
+
+namespace ho = helios_oracle;
+
+#define HO_API extern "C" __attribute__((visibility("default")))
+
+namespace {
+
+struct OQuery {
+  ho::QueryDesc desc;
+};
+
+struct OWorld;
+struct OSchedule;
+
+struct OCtx {  // what a CPU system body receives
+  OWorld* world;
+  ho::SystemLocalData* local;
+  const ho::QueryDesc* query;
+  const uint8_t* params;
+  uint32_t params_size;
+  uint64_t writes_message, reads_message;
+  uint8_t* resources;
+};
+using OSystemFn = int32_t (*)(const OCtx*);
+
+struct OWorld {
+  ho::World world;
+  std::vector<ho::TypeIndex> slot_hash;  // registration order == GPU slot ids
+  std::string err;
+  int access_mode = 0;  // 0 = direct column spans (B-opt path), 1 = reference-faithful per-entity lookups (B-ref)
+  int threads = 1;
+  std::unique_ptr<ho::FaithfulIndex> faithful;
+  std::vector<std::unique_ptr<OQuery>> queries;
+};
+
+struct OSysEntry {
+  helios_gpu_system_desc desc;
+  std::vector<uint8_t> params;
+};
+
+struct OSchedule {
+  OWorld* w;
+  ho::Schedule sched;
+  std::vector<OSysEntry> entries;
+  std::vector<uint8_t> resources = std::vector<uint8_t>(HELIOS_GPU_RESOURCE_BYTES, 0);
+  bool built = false;
+};
+
+ho::Entity E(helios_gpu_entity_t e) { return ho::Entity::Unpack(e); }
+
+// ---- benchmark components -------------------------------------------------------------
+struct Position { float x, y; };
+struct Velocity { float dx, dy; };
+struct Acceleration { float ddx, ddy; };
+struct Mass { float m; };
+struct CollisionEvent {
+  uint64_t a, b;
+  float impulse;
+  uint32_t pad;
+};
+
+// Visit helper: honours the world's access mode; in column mode optionally splits each table's rows over threads.
+template <typename Body>
+void visit(const OCtx* c, Body&& body) {
+  OWorld* w = c->world;
+  if (w->access_mode == 1) {
+    if (!w->faithful) w->faithful = std::make_unique<ho::FaithfulIndex>(w->world.components);
+    w->faithful->ForEach(*c->query, body);
+    return;
+  }
+  if (w->threads <= 1) {
+    ho::ForEach(w->world.components, *c->query, body);
+    return;
+  }
+  // B-opt: rows of every matching table split across all cores (bodies used with threads>1 are row-independent)
+  auto& cm = w->world.components;
+  const auto match = ho::MatchArchetypes(cm, *c->query);
+  std::vector<std::thread> pool;
+  const int T = w->threads;
+  for (int t = 0; t < T; ++t)
+    pool.emplace_back([&, t] {
+      std::vector<uint8_t*> ptrs(c->query->required.size());
+      for (const uint32_t ai : match) {
+        ho::Archetype& a = *cm.Archetypes()[ai];
+        std::vector<int> cols(ptrs.size());
+        for (size_t k = 0; k < cols.size(); ++k) cols[k] = a.ColumnIndex(c->query->required[k]);
+        const size_t n = a.EntityCount(), lo = n * t / T, hi = n * (t + 1) / T;
+        for (size_t r = lo; r < hi; ++r) {
+          for (size_t k = 0; k < cols.size(); ++k) ptrs[k] = &a.ColumnBytes(cols[k])[r * a.ElemSize(cols[k])];
+          body(a.Entities()[r], ptrs.data());
+        }
+      }
+    });
+  for (auto& th : pool) th.join();
+}
+
+// ---- system bodies: same arithmetic, same operation order as heliosengine_b200/csrc/builtin_systems.cu --------
+int32_t sys_integrate(const OCtx* c) {  // README.md:305-312
+  visit(c, [](ho::Entity, uint8_t** p) {
+    auto* pos = reinterpret_cast<Position*>(p[0]);
+    const auto* vel = reinterpret_cast<const Velocity*>(p[1]);
+    pos->x += vel->dx;
+    pos->y += vel->dy;
+  });
+  return 0;
+}
+int32_t sys_accel_integrate(const OCtx* c) {
+  float dt;
+  std::memcpy(&dt, c->params, 4);
+  visit(c, [dt](ho::Entity, uint8_t** p) {
+    auto* pos = reinterpret_cast<Position*>(p[0]);
+    auto* vel = reinterpret_cast<Velocity*>(p[1]);
+    const auto* acc = reinterpret_cast<const Acceleration*>(p[2]);
+    const auto* m = reinterpret_cast<const Mass*>(p[3]);
+    const float s = dt / m->m;
+    vel->dx = vel->dx + acc->ddx * s;
+    vel->dy = vel->dy + acc->ddy * s;
+    pos->x = pos->x + vel->dx * dt;
+    pos->y = pos->y + vel->dy * dt;
+  });
+  return 0;
+}
+int32_t sys_damp(const OCtx* c) {
+  float k;
+  std::memcpy(&k, c->params, 4);
+  visit(c, [k](ho::Entity, uint8_t** p) {
+    auto* vel = reinterpret_cast<Velocity*>(p[0]);
+    vel->dx = vel->dx * k;
+    vel->dy = vel->dy * k;
+  });
+  return 0;
+}
+int32_t sys_regen(const OCtx* c) {
+  visit(c, [](ho::Entity, uint8_t** p) {
+    auto* hp = reinterpret_cast<int32_t*>(p[0]);
+    *hp = *hp + 1 > 100 ? 100 : *hp + 1;
+  });
+  return 0;
+}
+int32_t sys_team_tint(const OCtx* c) {
+  visit(c, [](ho::Entity, uint8_t** p) {
+    const uint32_t team = *reinterpret_cast<const uint32_t*>(p[0]);
+    *reinterpret_cast<uint32_t*>(p[1]) = (team * 0x00202020u) | 0xFF000000u;
+  });
+  return 0;
+}
+int32_t detect_impl(const OCtx* c, bool sparse) {
+  // MessageWriter<T>::Write → system-local queue (system/param_traits.hpp:216-229); serial emission order.
+  OWorld* w = c->world;
+  const int saved_threads = w->threads;
+  w->threads = 1;
+  if (!c->local->message_queue.IsRegistered(c->writes_message))
+    c->local->message_queue.Register(c->writes_message, w->world.messages.SizeOf(c->writes_message));
+  visit(c, [&](ho::Entity e, uint8_t** p) {
+    const auto* pos = reinterpret_cast<const Position*>(p[0]);
+    const uint32_t team = *reinterpret_cast<const uint32_t*>(p[1]);
+    if (sparse && team != 0u) return;
+    CollisionEvent ev;
+    ev.a = e.Pack();
+    ev.b = e.Pack() ^ 1ull;
+    ev.impulse = pos->x * 0.0078125f + float(team);
+    ev.pad = 0;
+    c->local->message_queue.Enqueue(c->writes_message, &ev);
+  });
+  w->threads = saved_threads;
+  return 0;
+}
+int32_t sys_detect(const OCtx* c) { return detect_impl(c, false); }
+int32_t sys_detect_sparse(const OCtx* c) { return detect_impl(c, true); }
+int32_t sys_consume(const OCtx* c) {
+  // MessageReader<T> = previous ++ current of the WORLD manager (reader.hpp:793-795); Get(evt.a) → Health.
+  uint32_t health_slot;
+  std::memcpy(&health_slot, c->params, 4);
+  OWorld* w = c->world;
+  const ho::TypeIndex health = w->slot_hash[health_slot];
+  const auto bytes = w->world.messages.ReadAll(c->reads_message);
+  const size_t n = bytes.size() / sizeof(CollisionEvent);
+  for (size_t i = 0; i < n; ++i) {
+    CollisionEvent ev;
+    std::memcpy(&ev, &bytes[i * sizeof(ev)], sizeof(ev));
+    const ho::Entity a = E(ev.a);
+    if (!w->world.entities.Validate(a)) continue;
+    uint8_t* hp = w->world.components.Get(a, health);
+    if (hp) *reinterpret_cast<int32_t*>(hp) -= int32_t(ev.impulse);
+  }
+  return 0;
+}
+int32_t sys_stats(const OCtx* c) {
+  OWorld* w = c->world;
+  const int saved_threads = w->threads;
+  w->threads = 1;
+  uint64_t sum = 0;
+  visit(c, [&](ho::Entity, uint8_t** p) { sum += uint64_t(int64_t(*reinterpret_cast<const int32_t*>(p[0]))); });
+  w->threads = saved_threads;
+  std::memcpy(c->resources, &sum, 8);
+  return 0;
+}
+int32_t sys_exit_check(const OCtx* c) {
+  uint64_t r0;
+  std::memcpy(&r0, c->resources, 8);
+  const uint64_t r1 = r0 == 0 ? 1 : 0;
+  std::memcpy(c->resources + 8, &r1, 8);
+  return 0;
+}
+int32_t sys_despawn_dead(const OCtx* c) {
+  OWorld* w = c->world;
+  const int saved_threads = w->threads;
+  w->threads = 1;
+  visit(c, [&](ho::Entity e, uint8_t** p) {
+    if (*reinterpret_cast<const int32_t*>(p[0]) <= 0)
+      c->local->cmd_queue.Enqueue(ho::Command{ho::CmdKind::kDestroy, e, {}, {}});  // commands.Entity(e).Destroy()
+  });
+  w->threads = saved_threads;
+  return 0;
+}
+
+struct Builtin {
+  const char* name;
+  OSystemFn fn;
+};
+const Builtin kBuiltins[] = {
+    {"integrate", sys_integrate}, {"accel_integrate", sys_accel_integrate}, {"damp", sys_damp},
+    {"regen", sys_regen},         {"team_tint", sys_team_tint},             {"detect", sys_detect},
+    {"detect_sparse", sys_detect_sparse}, {"consume", sys_consume},         {"stats", sys_stats},
+    {"exit_check", sys_exit_check}, {"despawn_dead", sys_despawn_dead},
+};
+
+// helios_gpu_command → oracle Command (payload: ascending slot order, each value padded to 4 bytes).
+ho::Command to_command(OWorld* w, const helios_gpu_command& c, const uint8_t* payload) {
+  ho::Command out;
+  out.kind = static_cast<ho::CmdKind>(c.kind);
+  out.entity = E(c.entity);
+  uint32_t off = c.payload_offset;
+  for (uint32_t s = 0; s < w->slot_hash.size(); ++s) {
+    if (!(c.component_mask >> s & 1)) continue;
+    out.types.push_back(w->slot_hash[s]);
+    if (c.kind == HELIOS_GPU_CMD_ADD || c.kind == HELIOS_GPU_CMD_TRY_ADD) {
+      const uint32_t sz = w->world.components.Meta(w->slot_hash[s])->size;
+      out.values.emplace_back(payload + off, payload + off + sz);
+      off += (sz + 3u) & ~3u;
+    }
+  }
+  return out;
+}
+
+}  // namespace
+
+// =====================================================================================================
+// C entry points (same shapes as include/helios_gpu.h)
+// =====================================================================================================
+#define W(w) (reinterpret_cast<OWorld*>(w))
+
+HO_API int32_t helios_oracle_world_create(const helios_gpu_world_config*, void** out) {
+  *out = new OWorld();
+  return 0;
+}
+HO_API int32_t helios_oracle_world_destroy(void* w) {
+  delete W(w);
+  return 0;
+}
+HO_API const char* helios_oracle_last_error(const void* w) { return reinterpret_cast<const OWorld*>(w)->err.c_str(); }
+// access_mode 0 = direct column spans (B-opt), 1 = reference-faithful per-entity lookups (B-ref); threads for B-opt.
+HO_API int32_t helios_oracle_set_access_mode(void* w, int32_t mode, int32_t threads) {
+  W(w)->access_mode = mode;
+  W(w)->threads = threads < 1 ? 1 : threads;
+  W(w)->faithful.reset();
+  return 0;
+}
+HO_API int32_t helios_oracle_set_builtin_messages(void* w, int32_t on) {
+  W(w)->world.emit_builtin_messages = on != 0;
+  return 0;
+}
+
+HO_API int32_t helios_oracle_register_component(void* wp, uint64_t hash, uint32_t size, uint32_t align, const void* def) {
+  OWorld* w = W(wp);
+  for (size_t s = 0; s < w->slot_hash.size(); ++s)
+    if (w->slot_hash[s] == hash) return int32_t(s);
+  ho::ComponentMeta m;
+  m.type = hash;
+  m.size = size;
+  m.align = align;
+  if (def) m.default_bytes.assign(static_cast<const uint8_t*>(def), static_cast<const uint8_t*>(def) + size);
+  w->world.components.Register(m);
+  w->slot_hash.push_back(hash);
+  return int32_t(w->slot_hash.size() - 1);
+}
+
+HO_API int32_t helios_oracle_create_entities(void* wp, uint32_t n, helios_gpu_entity_t* out) {
+  for (uint32_t i = 0; i < n; ++i) {
+    const ho::Entity e = W(wp)->world.CreateEntity();
+    if (out) out[i] = e.Pack();
+  }
+  W(wp)->faithful.reset();
+  return 0;
+}
+HO_API int32_t helios_oracle_reserve_entities(void* wp, uint32_t n, helios_gpu_entity_t* out) {
+  for (uint32_t i = 0; i < n; ++i) {
+    const ho::Entity e = W(wp)->world.ReserveEntity();
+    if (out) out[i] = e.Pack();
+  }
+  return 0;
+}
+// Literally `e = CreateEntity(); AddComponents(e, c0[i], c1[i], ...)` per row.
+HO_API int32_t helios_oracle_spawn_batch(void* wp, const uint64_t* hashes, uint32_t ntypes, uint64_t n,
+                                         const void* const* columns, helios_gpu_entity_t* out) {
+  OWorld* w = W(wp);
+  std::vector<uint32_t> sizes(ntypes);
+  for (uint32_t k = 0; k < ntypes; ++k) {
+    const ho::ComponentMeta* m = w->world.components.Meta(hashes[k]);
+    if (!m) { w->err = "component not registered"; return HELIOS_GPU_ERR_NOT_FOUND; }
+    sizes[k] = m->size;
+  }
+  if (n == 0 && w->world.components.Archetypes().empty()) {  // GPU side creates `{}` eagerly; keep creation order equal
+    w->world.components.GetOrCreateArchetype(ho::ArchetypeId{});
+  }
+  std::vector<ho::CompValue> cv(ntypes);
+  for (uint64_t i = 0; i < n; ++i) {
+    const ho::Entity e = w->world.CreateEntity();
+    for (uint32_t k = 0; k < ntypes; ++k) cv[k] = {hashes[k], static_cast<const uint8_t*>(columns[k]) + i * sizes[k]};
+    if (ntypes) w->world.AddComponents(e, cv.data(), ntypes);
+    if (out) out[i] = e.Pack();
+  }
+  w->faithful.reset();
+  return 0;
+}
+HO_API int32_t helios_oracle_entity_count(void* wp, uint64_t* out) {
+  *out = W(wp)->world.EntityCount();
+  return 0;
+}
+
+// ---- snapshot ------------------------------------------------------------------------------------------
+HO_API int32_t helios_oracle_snapshot_archetype_count(void* wp, uint32_t* out) {
+  *out = uint32_t(W(wp)->world.components.Archetypes().size());
+  return 0;
+}
+HO_API int32_t helios_oracle_snapshot_archetype_info(void* wp, uint32_t a, uint64_t* hashes, uint32_t* ntypes, uint64_t* rows) {
+  const auto& list = W(wp)->world.components.Archetypes();
+  if (a >= list.size()) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  const auto& ty = list[a]->Id().Types();
+  if (hashes) std::copy(ty.begin(), ty.end(), hashes);
+  if (ntypes) *ntypes = uint32_t(ty.size());
+  if (rows) *rows = list[a]->EntityCount();
+  return 0;
+}
+HO_API int32_t helios_oracle_snapshot_archetype_entities(void* wp, uint32_t a, helios_gpu_entity_t* out, uint64_t cap) {
+  const auto& list = W(wp)->world.components.Archetypes();
+  if (a >= list.size() || cap < list[a]->EntityCount()) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  for (size_t r = 0; r < list[a]->EntityCount(); ++r) out[r] = list[a]->Entities()[r].Pack();
+  return 0;
+}
+HO_API int32_t helios_oracle_snapshot_archetype_column(void* wp, uint32_t a, uint64_t hash, void* out, uint64_t cap) {
+  const auto& list = W(wp)->world.components.Archetypes();
+  if (a >= list.size()) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  const int c = list[a]->ColumnIndex(hash);
+  if (c < 0) return HELIOS_GPU_ERR_NOT_FOUND;
+  const auto& b = list[a]->ColumnBytes(c);
+  if (cap < b.size()) return HELIOS_GPU_ERR_CAPACITY;
+  std::memcpy(out, b.data(), b.size());
+  return 0;
+}
+HO_API int32_t helios_oracle_snapshot_entity_table(void* wp, uint32_t* next_index, uint32_t* gens, uint32_t gen_cap,
+                                                   uint32_t* free_idx, uint32_t free_cap, uint32_t* free_count,
+                                                   int64_t* free_cursor) {
+  const ho::EntityManager& em = W(wp)->world.entities;
+  if (next_index) *next_index = em.NextIndex();
+  if (free_count) *free_count = uint32_t(em.FreeIndices().size());
+  if (free_cursor) *free_cursor = em.FreeCursor();
+  if (gens) std::copy_n(em.Generations().begin(), std::min<size_t>(gen_cap, em.Generations().size()), gens);
+  if (free_idx) std::copy_n(em.FreeIndices().begin(), std::min<size_t>(free_cap, em.FreeIndices().size()), free_idx);
+  return 0;
+}
+HO_API int32_t helios_oracle_entity_location(void* wp, helios_gpu_entity_t e, uint32_t* archetype, uint32_t* row) {
+  OWorld* w = W(wp);
+  const ho::Entity en = E(e);
+  if (!w->world.entities.Validate(en)) return HELIOS_GPU_ERR_NOT_FOUND;
+  ho::Archetype* a = w->world.components.EntityArchetype(en);
+  if (!a) return HELIOS_GPU_ERR_NOT_FOUND;
+  const auto& list = w->world.components.Archetypes();
+  if (archetype) *archetype = uint32_t(std::find(list.begin(), list.end(), a) - list.begin());
+  if (row) *row = a->Row(en);
+  return 0;
+}
+
+// ---- queries ----------------------------------------------------------------------------------------------
+HO_API int32_t helios_oracle_query_create(void* wp, const helios_gpu_query_desc* d, void** out) {
+  auto q = std::make_unique<OQuery>();
+  for (uint32_t k = 0; k < d->n_components; ++k) {
+    q->desc.required.push_back(d->components[k]);
+    q->desc.writes.push_back(d->writes[k]);
+  }
+  q->desc.with.assign(d->with, d->with + d->n_with);
+  q->desc.without.assign(d->without, d->without + d->n_without);
+  *out = q.get();
+  W(wp)->queries.push_back(std::move(q));
+  return 0;
+}
+HO_API int32_t helios_oracle_query_destroy(void*) { return 0; }
+// The oracle query handle does not know its world; the Python wrapper passes it explicitly.
+HO_API int32_t helios_oracle_query_match_w(void* wp, void* q, uint32_t* out, uint32_t cap, uint32_t* count) {
+  const auto m = ho::MatchArchetypes(W(wp)->world.components, reinterpret_cast<OQuery*>(q)->desc);
+  if (count) *count = uint32_t(m.size());
+  if (out) {
+    if (cap < m.size()) return HELIOS_GPU_ERR_CAPACITY;
+    std::copy(m.begin(), m.end(), out);
+  }
+  return 0;
+}
+HO_API int32_t helios_oracle_query_count_w(void* wp, void* q, uint64_t* out) {
+  *out = ho::QueryCount(W(wp)->world.components, reinterpret_cast<OQuery*>(q)->desc);
+  return 0;
+}
+
+// ---- commands ---------------------------------------------------------------------------------------------
+HO_API int32_t helios_oracle_commands_enqueue(void* wp, const helios_gpu_command* cmds, uint64_t n, const void* payload, uint64_t) {
+  OWorld* w = W(wp);
+  for (uint64_t i = 0; i < n; ++i)
+    w->world.command_queue.Enqueue(to_command(w, cmds[i], static_cast<const uint8_t*>(payload)));
+  return 0;
+}
+HO_API int32_t helios_oracle_world_flush(void* wp) {
+  W(wp)->world.Flush();
+  W(wp)->faithful.reset();
+  return 0;
+}
+HO_API int32_t helios_oracle_world_update(void* wp) {
+  W(wp)->world.Update();
+  W(wp)->faithful.reset();
+  return 0;
+}
+HO_API int32_t helios_oracle_last_apply_stats(void* wp, helios_gpu_apply_stats* out) {
+  std::memset(out, 0, sizeof(*out));
+  out->invalid = W(wp)->world.invalid_command_count;
+  out->moved_bytes = W(wp)->world.components.migrate_bytes;
+  return 0;
+}
+
+// ---- messages -----------------------------------------------------------------------------------------------
+HO_API int32_t helios_oracle_message_register(void* wp, uint64_t hash, uint32_t size, uint32_t policy) {
+  W(wp)->world.messages.Register(hash, size, policy ? ho::ClearPolicy::kManual : ho::ClearPolicy::kAutomatic);
+  return 0;
+}
+HO_API int32_t helios_oracle_message_write(void* wp, uint64_t hash, const void* data, uint64_t n) {
+  if (!W(wp)->world.messages.IsRegistered(hash)) return HELIOS_GPU_ERR_NOT_FOUND;
+  W(wp)->world.messages.Write(hash, data, n);
+  return 0;
+}
+HO_API int32_t helios_oracle_message_counts(void* wp, uint64_t hash, uint64_t* prev, uint64_t* cur) {
+  if (!W(wp)->world.messages.IsRegistered(hash)) return HELIOS_GPU_ERR_NOT_FOUND;
+  if (prev) *prev = W(wp)->world.messages.Previous().Count(hash);
+  if (cur) *cur = W(wp)->world.messages.Current().Count(hash);
+  return 0;
+}
+HO_API int32_t helios_oracle_message_read(void* wp, uint64_t hash, uint32_t which, void* out, uint64_t cap) {
+  const ho::MessageQueue& q = which ? W(wp)->world.messages.Current() : W(wp)->world.messages.Previous();
+  const auto* b = q.Bytes(hash);
+  if (!b) return HELIOS_GPU_ERR_NOT_FOUND;
+  if (cap < b->size()) return HELIOS_GPU_ERR_CAPACITY;
+  std::memcpy(out, b->data(), b->size());
+  return 0;
+}
+
+// ---- schedules ------------------------------------------------------------------------------------------------
+HO_API int32_t helios_oracle_builtin_system(const char* name, OSystemFn* out) {
+  for (const Builtin& b : kBuiltins)
+    if (std::strcmp(b.name, name) == 0) { *out = b.fn; return 0; }
+  return HELIOS_GPU_ERR_NOT_FOUND;
+}
+HO_API int32_t helios_oracle_schedule_create(void* wp, const char*, void** out) {
+  auto* s = new OSchedule();
+  s->w = W(wp);
+  *out = s;
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_destroy(void* s) {
+  delete reinterpret_cast<OSchedule*>(s);
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_add_system(void* sp, const helios_gpu_system_desc* d, uint32_t* out_index) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  OSysEntry e;
+  e.desc = *d;
+  if (d->params && d->params_size)
+    e.params.assign(static_cast<const uint8_t*>(d->params), static_cast<const uint8_t*>(d->params) + d->params_size);
+  s->entries.push_back(std::move(e));
+  const size_t idx = s->entries.size() - 1;
+  ho::AccessPolicy pol;
+  const auto* q = reinterpret_cast<const OQuery*>(d->query);
+  if (q) pol.AddQuery(q->desc);
+  for (uint32_t k = 0; k < d->n_extra_read_components; ++k) ho::AccessPolicy::InsertSorted(pol.read_components, d->extra_read_components[k]);
+  for (uint32_t k = 0; k < d->n_extra_write_components; ++k) ho::AccessPolicy::InsertSorted(pol.write_components, d->extra_write_components[k]);
+  for (uint32_t k = 0; k < d->n_read_resources; ++k) ho::AccessPolicy::InsertSorted(pol.read_resources, d->read_resources[k]);
+  for (uint32_t k = 0; k < d->n_write_resources; ++k) ho::AccessPolicy::InsertSorted(pol.write_resources, d->write_resources[k]);
+  OSchedule* sched = s;
+  s->sched.Add(d->name ? d->name : "", [sched, idx](ho::World&, ho::SystemLocalData& local) {
+    OSysEntry& en = sched->entries[idx];
+    OCtx c{sched->w, &local, en.desc.query ? &reinterpret_cast<const OQuery*>(en.desc.query)->desc : nullptr,
+           en.params.data(), uint32_t(en.params.size()), en.desc.writes_message, en.desc.reads_message,
+           sched->resources.data()};
+    reinterpret_cast<OSystemFn>(en.desc.launch)(&c);
+  }, pol);
+  if (out_index) *out_index = uint32_t(idx);
+  s->built = false;
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_add_order(void* sp, uint32_t a, uint32_t b) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  if (a >= s->entries.size() || b >= s->entries.size()) return HELIOS_GPU_ERR_NOT_FOUND;
+  if (a == b) return HELIOS_GPU_ERR_CYCLE;
+  s->sched.Order(a, b);
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_build(void* sp) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  if (!s->sched.Build()) return HELIOS_GPU_ERR_CYCLE;
+  s->built = true;
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_execution_order(void* sp, uint32_t* out, uint32_t cap, uint32_t* count) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  const auto& o = s->sched.ExecutionOrder();
+  if (count) *count = uint32_t(o.size());
+  if (out) {
+    if (cap < o.size()) return HELIOS_GPU_ERR_CAPACITY;
+    for (size_t i = 0; i < o.size(); ++i) out[i] = uint32_t(o[i]);
+  }
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_conflicts(void* sp, uint64_t* out, uint32_t cap) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  const auto& c = s->sched.ConflictMask();
+  if (cap < c.size()) return HELIOS_GPU_ERR_CAPACITY;
+  std::copy(c.begin(), c.end(), out);
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_run(void* sp, uint32_t) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  for (const size_t i : s->sched.ExecutionOrder()) s->sched.At(i).fn(s->w->world, s->sched.At(i).local);
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_apply_deferred(void* sp) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  s->sched.ApplyDeferred(s->w->world);
+  s->w->faithful.reset();
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_run_and_wait(void* sp, uint32_t m) {
+  helios_oracle_schedule_run(sp, m);
+  return helios_oracle_schedule_apply_deferred(sp);
+}
+HO_API int32_t helios_oracle_schedule_read_resources(void* sp, void* out, uint32_t bytes) {
+  std::memcpy(out, reinterpret_cast<OSchedule*>(sp)->resources.data(), bytes);
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_stream_count(void*, uint32_t* out) {
+  *out = 1;
+  return 0;
+}
+// Wall-clock seconds of `iters` executions of Schedule::Run (systems only, no ApplyDeferred) — cpu_baseline leg.
+HO_API double helios_oracle_time_schedule_run(void* sp, uint32_t iters) {
+  const auto t0 = std::chrono::steady_clock::now();
+  for (uint32_t i = 0; i < iters; ++i) helios_oracle_schedule_run(sp, 0);
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+HO_API uint32_t helios_oracle_hardware_threads() { return std::thread::hardware_concurrency(); }
