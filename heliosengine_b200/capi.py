@@ -28,6 +28,7 @@ CMD_DESTROY, CMD_TRY_DESTROY, CMD_ADD, CMD_TRY_ADD, CMD_REMOVE, CMD_TRY_REMOVE, 
 EXEC_SERIAL, EXEC_STREAMS, EXEC_GRAPH = 0, 1, 2
 MSG_AUTOMATIC, MSG_MANUAL = 0, 1
 SYSTEM_EMITS_COMMANDS = 1
+SYSTEM_NEEDS_VIEW = 2
 
 INVALID_ENTITY = 0xFFFFFFFFFFFFFFFF
 

@@ -1,10 +1,866 @@
-// apply.cu — batch application of deferred structural commands (placeholder until the replay kernels land).
+// apply.cu — batch application of deferred structural commands, bit-exact with sequential execution.
+//
+// Reference semantics being reproduced (one command at a time, FIFO — command/queue.hpp:158-163):
+//   Destroy/TryDestroy  world.hpp:986-1005   → Archetype::Remove (swap-and-pop, archetype.hpp:408-442) + generation++
+//   Add/TryAdd          world.hpp:1026-1066  → ComponentManager::Add/TryAdd → MigrateEntity (manager.hpp:1146-1248,1893-1952)
+//   Remove/TryRemove    world.hpp:1124-1164  → MigrateEntity
+//   ClearComponents     world.hpp:1189-1196  → move to the `{}` table (manager.hpp:1117-1144)
+// MigrateEntity appends the row at the destination tail and swap-fills the source hole with the table's CURRENT last
+// row, so the final row order of every table depends on the whole interleaved sequence.  DESIGN.md §5 derives the
+// parallel formulation used here:
+//   1. per-entity command chains (stable sort by entity index) give each command its source/destination archetype;
+//   2. every effective command becomes a Remove op on the source table and an Append op on the destination table;
+//      a stable sort by table yields each table's op sequence in command order, a ±1 prefix sum its size trajectory;
+//   3. a slot of a table is a stack cell: an Append at size s OPENS slot s, a Remove at size s+1 CLOSES slot s.  A
+//      stable sort by (table, slot) pairs every open with its close ("slot instances");
+//   4. the Remove that closes slot L moves L's occupant into the slot where the removed entity currently lives.
+//      That slot is found by following the entity from its home instance along already-resolved moves; chains are
+//      resolved in data-parallel rounds (an op whose predecessors are resolved resolves in that round; the earliest
+//      unresolved op always can), with a sequential per-table kernel as the worst-case fallback;
+//   5. the final occupant of every surviving slot follows from the last move that targeted it; only changed slots
+//      are rewritten: rows are gathered into a staging buffer, then scattered (no read/write hazards), then the
+//      command payloads are patched in (last writer of a component wins — the observable result of
+//      Archetype::Set before/after migration, manager.hpp:1175-1192).
+#include <algorithm>
+#include <vector>
+
+#include "primitives.cuh"
 #include "world_internal.hpp"
+
 using namespace hgpu;
-namespace hgpu {
-void free_apply_scratch(helios_gpu_world*) {}
-int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command*, const uint8_t*, uint64_t n, uint32_t) {
-  if (n == 0) return HELIOS_GPU_OK;
-  HG_FAIL(w, HELIOS_GPU_ERR_STATE, "command application not built yet");
+
+namespace {
+
+constexpr uint32_t kNone = 0xFFFFFFFFu;
+constexpr uint64_t kDeadMask = 0xFFFFFFFFFFFFFFFFull;  // destination "mask" of a destroyed entity
+constexpr uint64_t kInstA = 1ull << 63;                 // instance key tag: opened by the Append op in the low bits
+
+enum : uint32_t { F_VALID = 1u, F_MIG = 2u, F_DESTROY = 4u };
+
+struct Counters {
+  uint32_t n_valid_slots;  // K: compacted command count
+  uint32_t unknown;        // destination masks without a table
+  uint32_t invalid;        // non-Try commands on dead entities
+  uint32_t n_ops;          // M
+  uint32_t unresolved;
+  uint32_t n_changed;
+  uint32_t n_destroy;
+  uint32_t effective;
+  unsigned long long moved_bytes;
+};
+
+struct Unknown {
+  uint64_t mask;
+  uint32_t cmd;
+  uint32_t pad;
+};
+
+// ---- device mask → table hash (open addressing, host-built) --------------------------------------------------
+struct MaskHash {
+  const uint64_t* keys;
+  const uint32_t* vals;  // kNone = empty
+  uint32_t log2cap;
+};
+__host__ __device__ inline uint32_t mask_slot(uint64_t m, uint32_t log2cap) {
+  return uint32_t((m * 0x9E3779B97F4A7C15ull) >> (64 - log2cap));
 }
+__device__ inline uint32_t mask_lookup(const MaskHash& h, uint64_t m) {
+  uint32_t s = mask_slot(m, h.log2cap);
+  const uint32_t cap = 1u << h.log2cap;
+  for (uint32_t i = 0; i < cap; ++i) {
+    const uint32_t v = h.vals[s];
+    if (v == kNone) return kNone;
+    if (h.keys[s] == m) return v;
+    s = (s + 1) & (cap - 1);
+  }
+  return kNone;
+}
+
+// ---- instance → last targeting op (device-built, atomicMax) ----------------------------------------------------
+struct InstHash {
+  unsigned long long* keys;  // 0 = empty (instance keys are stored +1 so that INIT(0,0) is representable)
+  uint32_t* vals;            // op index + 1
+  uint32_t log2cap;
+};
+__device__ inline void inst_insert_max(const InstHash& h, uint64_t key, uint32_t val) {
+  const unsigned long long k = key + 1;
+  uint32_t s = mask_slot(k, h.log2cap);
+  const uint32_t cap = 1u << h.log2cap;
+  for (;;) {
+    const unsigned long long prev = atomicCAS(&h.keys[s], 0ull, k);
+    if (prev == 0ull || prev == k) {
+      atomicMax(&h.vals[s], val);
+      return;
+    }
+    s = (s + 1) & (cap - 1);
+  }
+}
+__device__ inline uint32_t inst_get(const InstHash& h, uint64_t key) {
+  const unsigned long long k = key + 1;
+  uint32_t s = mask_slot(k, h.log2cap);
+  const uint32_t cap = 1u << h.log2cap;
+  for (;;) {
+    const unsigned long long cur = h.keys[s];
+    if (cur == 0ull) return 0;
+    if (cur == k) return h.vals[s];
+    s = (s + 1) & (cap - 1);
+  }
+}
+
+}  // namespace
+
+struct helios_gpu_world::ApplyScratch {
+  DevBuf flags, cidx, partials, counters;
+  DevBuf c_cmd;
+  DevBuf skey, sval, skey_alt, sval_alt, scounts, spartials;
+  DevBuf src_mask, dst_mask, wset, wlive, home_cmd, cflags;
+  DevBuf src_t, dst_t, opcnt, opbase, dflag, dpos;
+  DevBuf mh_keys, mh_vals;
+  uint32_t mh_log2 = 0;
+  size_t mh_tables = ~size_t(0);
+  DevBuf tdelta, tfmin, tseg, tcount0;
+  DevBuf unknown;
+  DevBuf u_table, u_kind, u_cmd;
+  DevBuf op_table, op_kind, op_cmd, op_level, u2t, delta, ex;
+  DevBuf key2, p2t, t2p;
+  DevBuf J, resolved;
+  DevBuf ih_keys, ih_vals;
+  DevBuf ch_table, ch_slot, ch_ent, stage;
+  DevBuf coffset;  // uint32[64] byte offset of each component inside a staged row
+  uint32_t stage_stride = 0;
+  size_t stride_comps = 0;
+};
+
+namespace {
+
+// ================================================================================================================
+// Stage 1 — compaction of a (possibly sparse) record buffer
+// ================================================================================================================
+__global__ void k_flag_valid(const helios_gpu_command* __restrict__ cmds, uint64_t n, uint32_t* __restrict__ flags) {
+  const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+  if (i < n) flags[i] = cmds[i].kind <= HELIOS_GPU_CMD_CLEAR ? 1u : 0u;
+}
+
+__global__ void k_compact(const helios_gpu_command* __restrict__ cmds, uint64_t n, const uint32_t* __restrict__ flags,
+                          const uint32_t* __restrict__ pos, helios_gpu_command* __restrict__ out,
+                          uint64_t* __restrict__ skey, uint32_t* __restrict__ sval) {
+  const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+  if (i < n && flags[i]) {
+    const uint32_t k = pos[i];
+    const helios_gpu_command c = cmds[i];
+    out[k] = c;
+    skey[k] = ent_index(c.entity);  // sort key: entity index (stable sort keeps command order inside an entity)
+    sval[k] = k;
+  }
+}
+
+// ================================================================================================================
+// Stage 2 — per-entity command chains.  One thread per run head of the entity-sorted order walks the entity's
+// commands in FIFO order, tracking (alive, component mask) exactly as sequential execution would.
+// ================================================================================================================
+struct ChainArgs {
+  const helios_gpu_command* cmd;
+  const uint64_t* skey;
+  const uint32_t* sval;
+  uint32_t K;
+  const uint32_t* gen;
+  const uint64_t* loc;
+  const uint64_t* tmask;
+  uint32_t ent_capacity;
+  uint64_t* src_mask;
+  uint64_t* dst_mask;
+  uint64_t* wset;
+  uint64_t* wlive;
+  uint32_t* home_cmd;
+  uint32_t* cflags;
+  uint32_t* dflag;
+  Counters* counters;
+};
+
+__global__ void k_chain(ChainArgs a) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.K) return;
+  const uint64_t idx64 = a.skey[i];
+  if (i > 0 && a.skey[i - 1] == idx64) return;  // not a run head
+  const uint32_t idx = uint32_t(idx64);
+  uint32_t gen0 = kInvalidGeneration;
+  uint64_t loc0 = kInvalidLoc;
+  if (idx < a.ent_capacity) {
+    gen0 = a.gen[idx];
+    loc0 = a.loc[idx];
+  }
+  bool alive = gen0 != kInvalidGeneration && loc0 != kInvalidLoc;
+  uint64_t mask = alive ? a.tmask[loc0 >> 32] : 0;
+  uint32_t last_mig = kNone;
+  uint32_t r = i;
+  uint32_t invalid = 0;
+  for (; r < a.K && a.skey[r] == idx64; ++r) {
+    const uint32_t k = a.sval[r];
+    const helios_gpu_command c = a.cmd[k];
+    const bool v = alive && ent_gen(c.entity) == gen0;  // EntityManager::Validate (entity/manager.hpp:410-418)
+    uint64_t src = mask, dst = mask, w = 0;
+    uint32_t fl = 0;
+    if (!v) {
+      // Try* variants skip silently (world.hpp:996-1000); the others are HELIOS_ASSERT failures in the reference
+      if (c.kind != HELIOS_GPU_CMD_TRY_DESTROY && c.kind != HELIOS_GPU_CMD_TRY_ADD && c.kind != HELIOS_GPU_CMD_TRY_REMOVE) ++invalid;
+    } else {
+      fl = F_VALID;
+      switch (c.kind) {
+        case HELIOS_GPU_CMD_DESTROY:
+        case HELIOS_GPU_CMD_TRY_DESTROY:
+          fl |= F_DESTROY | F_MIG;
+          dst = kDeadMask;
+          alive = false;
+          break;
+        case HELIOS_GPU_CMD_ADD:       // manager.hpp:1146-1203 — every listed component is written
+          w = c.component_mask;
+          dst = mask | c.component_mask;
+          break;
+        case HELIOS_GPU_CMD_TRY_ADD:   // manager.hpp:1205-1248 — only the missing ones
+          w = c.component_mask & ~mask;
+          dst = mask | c.component_mask;
+          break;
+        case HELIOS_GPU_CMD_REMOVE:
+        case HELIOS_GPU_CMD_TRY_REMOVE:  // manager.hpp:1268-1312
+          dst = mask & ~c.component_mask;
+          break;
+        case HELIOS_GPU_CMD_CLEAR:       // manager.hpp:1117-1144
+          dst = 0;
+          break;
+        default: break;
+      }
+      if (!(fl & F_DESTROY) && dst != src) fl |= F_MIG;
+    }
+    a.src_mask[k] = src;
+    a.dst_mask[k] = dst;
+    a.wset[k] = w;
+    a.cflags[k] = fl;
+    a.dflag[k] = (fl & F_DESTROY) ? 1u : 0u;
+    a.home_cmd[k] = last_mig;
+    if (fl & F_MIG) {
+      last_mig = k;
+      if (!(fl & F_DESTROY)) mask = dst;
+    }
+  }
+  // backward pass: a written value survives iff no later command rewrites, removes or destroys it
+  uint64_t decided = 0;
+  for (uint32_t q = r; q-- > i;) {
+    const uint32_t k = a.sval[q];
+    const uint32_t fl = a.cflags[k];
+    uint64_t live = 0;
+    if (fl & F_VALID) {
+      const uint32_t kind = a.cmd[k].kind;
+      if (fl & F_DESTROY) decided = ~0ull;
+      else if (kind == HELIOS_GPU_CMD_ADD || kind == HELIOS_GPU_CMD_TRY_ADD) {
+        live = a.wset[k] & ~decided;
+        decided |= a.wset[k];
+      } else if (kind == HELIOS_GPU_CMD_REMOVE || kind == HELIOS_GPU_CMD_TRY_REMOVE) decided |= a.cmd[k].component_mask;
+      else if (kind == HELIOS_GPU_CMD_CLEAR) decided = ~0ull;
+    }
+    a.wlive[k] = live;
+  }
+  if (invalid) atomicAdd(&a.counters->invalid, invalid);
+}
+
+// ================================================================================================================
+// Stage 3 — archetype masks → table ids, op counts, per-table net row deltas
+// ================================================================================================================
+__global__ void k_map_tables(uint32_t K, const uint64_t* __restrict__ src_mask, const uint64_t* __restrict__ dst_mask,
+                             const uint32_t* __restrict__ cflags, MaskHash mh, uint32_t* __restrict__ src_t,
+                             uint32_t* __restrict__ dst_t, uint32_t* __restrict__ opcnt, int* __restrict__ tdelta,
+                             Unknown* __restrict__ unknown, uint32_t unknown_cap, Counters* counters) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K) return;
+  const uint32_t fl = cflags[k];
+  uint32_t st = kNone, dt = kNone, cnt = 0;
+  if (fl & F_MIG) {
+    st = mask_lookup(mh, src_mask[k]);
+    if (!(fl & F_DESTROY)) {
+      dt = mask_lookup(mh, dst_mask[k]);
+      if (dt == kNone) {  // GetOrCreateArchetype will have to create it (manager.hpp:1852-1877)
+        const uint32_t u = atomicAdd(&counters->unknown, 1u);
+        if (u < unknown_cap) unknown[u] = Unknown{dst_mask[k], k, 0};
+      }
+    }
+    if (st != kNone && (dt != kNone || (fl & F_DESTROY))) {
+      cnt = (fl & F_DESTROY) ? 1u : 2u;
+      atomicSub(&tdelta[st], 1);
+      if (dt != kNone) atomicAdd(&tdelta[dt], 1);
+    }
+    atomicAdd(&counters->effective, 1u);
+  } else if ((fl & F_VALID)) {
+    atomicAdd(&counters->effective, 1u);  // value overwrite without migration still changes the world
+  }
+  src_t[k] = st;
+  dst_t[k] = dt;
+  opcnt[k] = cnt;
+}
+
+// Remove op first, Append op second — both carry the command index as their time stamp.
+__global__ void k_emit_ops(uint32_t K, const uint32_t* __restrict__ opcnt, const uint32_t* __restrict__ opbase,
+                           const uint32_t* __restrict__ src_t, const uint32_t* __restrict__ dst_t,
+                           uint64_t* __restrict__ key, uint32_t* __restrict__ val, uint32_t* __restrict__ u_kind,
+                           uint32_t* __restrict__ u_cmd) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K || opcnt[k] == 0) return;
+  const uint32_t b = opbase[k];
+  key[b] = src_t[k]; val[b] = b; u_kind[b] = 0; u_cmd[b] = k;
+  if (opcnt[k] == 2) { key[b + 1] = dst_t[k]; val[b + 1] = b + 1; u_kind[b + 1] = 1; u_cmd[b + 1] = k; }
+}
+
+// After the stable sort by table: gather op attributes into table/time order, record u→t, segment starts, ±1 deltas.
+__global__ void k_gather_ops(uint32_t M, const uint64_t* __restrict__ skey, const uint32_t* __restrict__ sval,
+                             const uint32_t* __restrict__ u_kind, const uint32_t* __restrict__ u_cmd,
+                             uint32_t* __restrict__ op_table, uint32_t* __restrict__ op_kind, uint32_t* __restrict__ op_cmd,
+                             uint32_t* __restrict__ u2t, uint32_t* __restrict__ delta, uint32_t* __restrict__ tseg) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= M) return;
+  const uint32_t u = sval[j];
+  const uint32_t t = uint32_t(skey[j]);
+  op_table[j] = t;
+  op_kind[j] = u_kind[u];
+  op_cmd[j] = u_cmd[u];
+  u2t[u] = j;
+  delta[j] = u_kind[u] ? 1u : 0xFFFFFFFFu;  // +1 / -1 (two's complement; the scan wraps consistently)
+  if (j == 0 || uint32_t(skey[j - 1]) != t) tseg[t] = j;
+}
+
+// Size trajectory → the slot each op opens (Append at size s opens slot s) or closes (Remove at size s+1 closes s).
+__global__ void k_levels(uint32_t M, const uint32_t* __restrict__ op_table, const uint32_t* __restrict__ op_kind,
+                         const uint32_t* __restrict__ delta, const uint32_t* __restrict__ ex,
+                         const uint32_t* __restrict__ tseg, const uint32_t* __restrict__ tcount0,
+                         uint32_t* __restrict__ op_level, uint32_t* __restrict__ tfmin, uint64_t* __restrict__ key2,
+                         uint32_t* __restrict__ val2, int level_bits) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= M) return;
+  const uint32_t t = op_table[j];
+  const uint32_t size_after = tcount0[t] + (ex[j] + delta[j] - ex[tseg[t]]);
+  const uint32_t level = op_kind[j] ? size_after - 1 : size_after;
+  op_level[j] = level;
+  if (!op_kind[j]) atomicMin(&tfmin[t], level);
+  key2[j] = (uint64_t(t) << level_bits) | level;
+  val2[j] = j;
+}
+
+__global__ void k_invert(uint32_t M, const uint32_t* __restrict__ p2t, uint32_t* __restrict__ t2p) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < M) t2p[p2t[p]] = p;
+}
+
+// ================================================================================================================
+// Stage 4 — slot instances and move resolution
+// ================================================================================================================
+struct OpView {
+  uint32_t M;
+  const uint32_t* op_table;
+  const uint32_t* op_kind;   // 0 = Remove, 1 = Append
+  const uint32_t* op_cmd;
+  const uint32_t* op_level;
+  const uint32_t* u2t;
+  const uint64_t* key2;      // (table << level_bits | level) in (table, level, time) order
+  const uint32_t* p2t;
+  const uint32_t* t2p;
+  const uint32_t* tfmin;
+  int level_bits;
+  const helios_gpu_command* cmd;
+  const uint32_t* home_cmd;
+  const uint32_t* opbase;
+  const uint64_t* loc;       // locations BEFORE the batch
+  uint64_t* J;               // per Remove op: instance the removed entity lives in at that time
+  uint32_t* resolved;
+  InstHash ih;
+};
+
+__device__ __forceinline__ uint64_t inst_init(uint32_t table, uint32_t slot) { return (uint64_t(table) << 32) | slot; }
+__device__ __forceinline__ uint64_t inst_append(uint32_t j) { return kInstA | j; }
+
+// Time (t-order index) of the Remove op that closes instance I, or kNone if it survives the batch.
+__device__ uint32_t close_of(const OpView& v, uint64_t I) {
+  if (I & kInstA) {
+    const uint32_t p = v.t2p[uint32_t(I)];
+    return (p + 1 < v.M && v.key2[p + 1] == v.key2[p]) ? v.p2t[p + 1] : kNone;  // opens and closes alternate per slot
+  }
+  const uint32_t table = uint32_t(I >> 32), slot = uint32_t(I);
+  if (slot < v.tfmin[table]) return kNone;  // below the table's minimum size: the slot never becomes the tail
+  const uint64_t key = (uint64_t(table) << v.level_bits) | slot;
+  uint32_t lo = 0, hi = v.M;  // lower_bound over key2
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (v.key2[mid] < key) lo = mid + 1; else hi = mid;
+  }
+  if (lo < v.M && v.key2[lo] == key) {
+    const uint32_t j = v.p2t[lo];
+    if (v.op_kind[j] == 0) return j;  // an initially occupied slot sees a Remove first
+  }
+  return kNone;
+}
+
+// Instance closed by Remove op j (the table's tail slot at that moment).
+__device__ __forceinline__ uint64_t closed_by(const OpView& v, uint32_t j) {
+  const uint32_t p = v.t2p[j];
+  if (p > 0 && v.key2[p - 1] == v.key2[p]) return inst_append(v.p2t[p - 1]);
+  return inst_init(v.op_table[j], v.op_level[j]);
+}
+
+// Try to resolve Remove op j; returns false if a predecessor move is still unresolved.
+__device__ bool resolve_one(const OpView& v, uint32_t j) {
+  const uint32_t k = v.op_cmd[j];
+  const uint32_t hk = v.home_cmd[k];
+  uint64_t I;
+  if (hk == kNone) {
+    const uint64_t l = v.loc[ent_index(v.cmd[k].entity)];
+    I = inst_init(uint32_t(l >> 32), uint32_t(l));
+  } else {
+    I = inst_append(v.u2t[v.opbase[hk] + 1]);  // the Append of the entity's previous migration
+  }
+  for (;;) {
+    const uint32_t c = close_of(v, I);
+    if (c == kNone || c >= j) break;  // still sitting in I when op j executes (c == j: it IS the tail → plain pop)
+    if (!*reinterpret_cast<volatile uint32_t*>(&v.resolved[c])) return false;
+    __threadfence();
+    I = *reinterpret_cast<volatile uint64_t*>(&v.J[c]);  // the entity was moved there when its slot closed
+  }
+  v.J[j] = I;
+  if (I != closed_by(v, j)) inst_insert_max(v.ih, I, j + 1);  // a real move targets I at time j
+  __threadfence();
+  *reinterpret_cast<volatile uint32_t*>(&v.resolved[j]) = 1u;
+  return true;
+}
+
+__global__ void k_resolve(OpView v, Counters* counters) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= v.M || v.op_kind[j] != 0 || v.resolved[j]) return;
+  if (!resolve_one(v, j)) atomicAdd(&counters->unresolved, 1u);
+}
+
+// Worst-case fallback: one thread per table replays its Remove ops in time order (every predecessor is earlier).
+__global__ void k_resolve_sequential(OpView v, const uint32_t* __restrict__ tseg, uint32_t ntables) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= ntables || tseg[t] == kNone) return;
+  for (uint32_t j = tseg[t]; j < v.M && v.op_table[j] == t; ++j)
+    if (v.op_kind[j] == 0 && !v.resolved[j]) resolve_one(v, j);
+}
+
+// Occupant of the slot closed by Remove op j at that moment = the entity that op moves.
+__device__ helios_gpu_entity_t mover_of(const OpView& v, uint32_t j, helios_gpu_entity_t* const* tents) {
+  uint64_t I = closed_by(v, j);
+  for (;;) {
+    const uint32_t lt = inst_get(v.ih, I);
+    if (lt == 0) break;           // never re-filled: still its opener
+    I = closed_by(v, lt - 1);     // last re-fill came from the slot closed by op lt-1
+  }
+  if (I & kInstA) return v.cmd[v.op_cmd[uint32_t(I)]].entity;
+  return tents[uint32_t(I >> 32)][uint32_t(I)];
+}
+
+__device__ __forceinline__ uint32_t slot_of(const OpView& v, uint64_t I) {
+  return (I & kInstA) ? v.op_level[uint32_t(I)] : uint32_t(I);
+}
+
+// Final contents: every surviving slot whose occupant changed.
+__global__ void k_final_slots(OpView v, helios_gpu_entity_t* const* tents, uint32_t* __restrict__ ch_table,
+                              uint32_t* __restrict__ ch_slot, helios_gpu_entity_t* __restrict__ ch_ent, Counters* counters) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= v.M) return;
+  uint32_t slot = 0;
+  helios_gpu_entity_t e = 0;
+  bool emit = false;
+  if (v.op_kind[j]) {  // Append: a surviving, never re-filled instance keeps its opener
+    const uint64_t I = inst_append(j);
+    if (close_of(v, I) == kNone && inst_get(v.ih, I) == 0) {
+      emit = true;
+      slot = v.op_level[j];
+      e = v.cmd[v.op_cmd[j]].entity;
+    }
+  } else {             // Remove: the LAST move into a surviving instance decides its occupant
+    const uint64_t I = v.J[j];
+    if (I != closed_by(v, j) && inst_get(v.ih, I) == j + 1 && close_of(v, I) == kNone) {
+      emit = true;
+      slot = slot_of(v, I);
+      e = mover_of(v, j, tents);
+    }
+  }
+  if (emit) {
+    const uint32_t i = atomicAdd(&counters->n_changed, 1u);
+    ch_table[i] = v.op_table[j];
+    ch_slot[i] = slot;
+    ch_ent[i] = e;
+  }
+}
+
+// ================================================================================================================
+// Stage 5 — row mover (gather → staging → scatter), destroy bookkeeping, payload patch, count update
+// ================================================================================================================
+struct MoveArgs {
+  uint32_t n;
+  const uint32_t* ch_table;
+  const uint32_t* ch_slot;
+  const helios_gpu_entity_t* ch_ent;
+  uint64_t* loc;
+  const uint64_t* tmask;
+  void* const* tcols;
+  helios_gpu_entity_t* const* tents;
+  const uint32_t* csize;
+  const uint32_t* coffset;
+  uint8_t* stage;
+  uint32_t stride;
+  Counters* counters;
+};
+
+__device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, uint32_t sz) {
+  if ((sz & 3u) == 0 && ((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 3u) == 0) {
+    for (uint32_t b = 0; b < sz; b += 4) *reinterpret_cast<uint32_t*>(dst + b) = *reinterpret_cast<const uint32_t*>(src + b);
+  } else {
+    for (uint32_t b = 0; b < sz; ++b) dst[b] = src[b];
+  }
+}
+
+// Component values the entity carries over from where it lived BEFORE the batch (shared columns of MigrateEntity,
+// manager.hpp:1912-1925, and the swapped row of Archetype::Remove, archetype.hpp:418-431).
+__global__ void k_gather_rows(MoveArgs a) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  const uint64_t l0 = a.loc[ent_index(a.ch_ent[i])];
+  const uint32_t t0 = uint32_t(l0 >> 32), r0 = uint32_t(l0);
+  uint64_t m = a.tmask[a.ch_table[i]] & a.tmask[t0];
+  uint8_t* out = a.stage + size_t(i) * a.stride;
+  uint32_t bytes = 8;
+  while (m) {
+    const int s = __ffsll(static_cast<long long>(m)) - 1;
+    m &= m - 1;
+    const uint32_t sz = a.csize[s];
+    copy_bytes(out + a.coffset[s], static_cast<const uint8_t*>(a.tcols[size_t(t0) * 64 + s]) + size_t(r0) * sz, sz);
+    bytes += sz;
+  }
+  atomicAdd(&a.counters->moved_bytes, 2ull * bytes);
+}
+
+__global__ void k_scatter_rows(MoveArgs a) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  const helios_gpu_entity_t e = a.ch_ent[i];
+  const uint32_t t = a.ch_table[i], r = a.ch_slot[i];
+  const uint64_t l0 = a.loc[ent_index(e)];
+  uint64_t m = a.tmask[t] & a.tmask[uint32_t(l0 >> 32)];
+  const uint8_t* in = a.stage + size_t(i) * a.stride;
+  while (m) {
+    const int s = __ffsll(static_cast<long long>(m)) - 1;
+    m &= m - 1;
+    const uint32_t sz = a.csize[s];
+    copy_bytes(static_cast<uint8_t*>(a.tcols[size_t(t) * 64 + s]) + size_t(r) * sz, in + a.coffset[s], sz);
+  }
+  a.tents[t][r] = e;
+}
+
+// Locations are rewritten only after every gather/scatter thread has read the pre-batch ones.
+__global__ void k_update_locations(uint32_t n, const uint32_t* __restrict__ ch_table, const uint32_t* __restrict__ ch_slot,
+                                   const helios_gpu_entity_t* __restrict__ ch_ent, uint64_t* __restrict__ loc) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) loc[ent_index(ch_ent[i])] = (uint64_t(ch_table[i]) << 32) | ch_slot[i];
+}
+
+// EntityManager::Destroy (entity/manager.hpp:307-320): generation++, index pushed on the free list in command order.
+__global__ void k_destroy(uint32_t K, const helios_gpu_command* __restrict__ cmd, const uint32_t* __restrict__ dflag,
+                          const uint32_t* __restrict__ dpos, uint32_t* __restrict__ gen, uint64_t* __restrict__ loc,
+                          uint32_t* __restrict__ free_list, uint64_t free_base) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K || !dflag[k]) return;
+  const uint32_t idx = ent_index(cmd[k].entity);
+  gen[idx] += 1;
+  loc[idx] = kInvalidLoc;
+  free_list[free_base + dpos[k]] = idx;
+}
+
+// Archetype::Set of the command's component values (archetype.hpp:444-472); only the last surviving writer of a
+// component stores (wlive), at the entity's FINAL row.
+__global__ void k_patch(uint32_t K, const helios_gpu_command* __restrict__ cmd, const uint64_t* __restrict__ wlive,
+                        const uint8_t* __restrict__ payload, const uint64_t* __restrict__ loc, void* const* tcols,
+                        const uint32_t* __restrict__ csize) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K) return;
+  const uint64_t live = wlive[k];
+  if (!live) return;
+  const helios_gpu_command c = cmd[k];
+  const uint64_t l = loc[ent_index(c.entity)];
+  const uint32_t t = uint32_t(l >> 32), r = uint32_t(l);
+  uint64_t m = c.component_mask;
+  uint32_t off = c.payload_offset;
+  while (m) {
+    const int s = __ffsll(static_cast<long long>(m)) - 1;
+    m &= m - 1;
+    const uint32_t sz = csize[s];
+    if (live >> s & 1) copy_bytes(static_cast<uint8_t*>(tcols[size_t(t) * 64 + s]) + size_t(r) * sz, payload + off, sz);
+    off += (sz + 3u) & ~3u;
+  }
+}
+
+__global__ void k_apply_deltas(uint32_t ntables, const int* __restrict__ tdelta, uint32_t* __restrict__ tcount) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < ntables) tcount[t] = uint32_t(int(tcount[t]) + tdelta[t]);
+}
+
+}  // namespace
+
+// ================================================================================================================
+// Host driver
+// ================================================================================================================
+namespace hgpu {
+
+void free_apply_scratch(helios_gpu_world* w) {
+  delete w->apply;
+  w->apply = nullptr;
+}
+
+namespace apply_host {
+
+#define NEED(buf, bytes) HG_CUDA(w, (buf).reserve((bytes), 0, st, true))
+inline uint32_t blocks_for(uint64_t n, uint32_t threads = 256) { return uint32_t((n + threads - 1) / threads); }
+
+int32_t upload_mask_hash(helios_gpu_world* w) {
+  auto& S = *w->apply;
+  if (S.mh_tables == w->tables.size()) return HELIOS_GPU_OK;
+  cudaStream_t st = w->stream;
+  uint32_t log2 = 8;
+  while ((1u << log2) < 4 * w->tables.size()) ++log2;
+  const uint32_t cap = 1u << log2;
+  std::vector<uint64_t> keys(cap, 0);
+  std::vector<uint32_t> vals(cap, kNone);
+  for (size_t t = 0; t < w->tables.size(); ++t) {
+    uint32_t s = mask_slot(w->tables[t].mask, log2);
+    while (vals[s] != kNone) s = (s + 1) & (cap - 1);
+    keys[s] = w->tables[t].mask;
+    vals[s] = uint32_t(t);
+  }
+  NEED(S.mh_keys, cap * 8);
+  NEED(S.mh_vals, cap * 4);
+  HG_CUDA(w, cudaMemcpyAsync(S.mh_keys.ptr, keys.data(), cap * 8, cudaMemcpyHostToDevice, st));
+  HG_CUDA(w, cudaMemcpyAsync(S.mh_vals.ptr, vals.data(), cap * 4, cudaMemcpyHostToDevice, st));
+  HG_CUDA(w, cudaStreamSynchronize(st));  // the host vectors die here
+  S.mh_log2 = log2;
+  S.mh_tables = w->tables.size();
+  return HELIOS_GPU_OK;
+}
+
+int32_t upload_component_layout(helios_gpu_world* w) {
+  auto& S = *w->apply;
+  if (S.stride_comps == w->comps.size() && S.coffset.ptr) return HELIOS_GPU_OK;
+  uint32_t off[64] = {};
+  uint32_t o = 0;
+  for (size_t s = 0; s < w->comps.size(); ++s) {
+    const uint32_t al = std::min<uint32_t>(16, std::max<uint32_t>(4, w->comps[s].align));
+    o = (o + al - 1) / al * al;
+    off[s] = o;
+    o += w->comps[s].size;
+  }
+  S.stage_stride = (o + 15u) & ~15u;
+  if (S.stage_stride == 0) S.stage_stride = 16;
+  cudaStream_t st = w->stream;
+  NEED(S.coffset, 64 * 4);
+  HG_CUDA(w, cudaMemcpyAsync(S.coffset.ptr, off, sizeof(off), cudaMemcpyHostToDevice, st));
+  HG_CUDA(w, cudaStreamSynchronize(st));
+  S.stride_comps = w->comps.size();
+  return HELIOS_GPU_OK;
+}
+
+}  // namespace apply_host
+using namespace apply_host;
+
+int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const uint8_t* d_payload, uint64_t n, uint32_t) {
+  w->last_stats = helios_gpu_apply_stats{};
+  if (n == 0) return HELIOS_GPU_OK;
+  if (n >= 0x7FFFFFFFull) HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "command buffer too large");
+  if (!w->apply) w->apply = new helios_gpu_world::ApplyScratch();
+  auto& S = *w->apply;
+  cudaStream_t st = w->stream;
+  HG_TRY(sync_counts_to_host(w));
+  HG_TRY(upload_component_layout(w));
+  uint64_t launches = 0;
+
+  // ---- stage 1: compaction ------------------------------------------------------------------------------------
+  NEED(S.counters, sizeof(Counters));
+  HG_CUDA(w, cudaMemsetAsync(S.counters.ptr, 0, sizeof(Counters), st));
+  Counters* dc = S.counters.as<Counters>();
+  NEED(S.flags, n * 4);
+  NEED(S.cidx, n * 4);
+  NEED(S.partials, (n / prim::kScanTile + 2) * 4);
+  k_flag_valid<<<blocks_for(n), 256, 0, st>>>(d_cmds, n, S.flags.as<uint32_t>());
+  launches += 1 + prim::exclusive_scan_u32(S.flags.as<uint32_t>(), S.cidx.as<uint32_t>(), n, S.partials.as<uint32_t>(),
+                                           &dc->n_valid_slots, st);
+  Counters hc{};
+  HG_CUDA(w, cudaMemcpyAsync(&hc, dc, sizeof(hc), cudaMemcpyDeviceToHost, st));
+  HG_CUDA(w, cudaStreamSynchronize(st));
+  const uint32_t K = hc.n_valid_slots;
+  w->last_stats.commands = K;
+  if (K == 0) { w->launches += launches; return HELIOS_GPU_OK; }
+
+  const uint64_t maxKM = 2ull * K;
+  NEED(S.c_cmd, K * sizeof(helios_gpu_command));
+  NEED(S.skey, maxKM * 8); NEED(S.sval, maxKM * 4); NEED(S.skey_alt, maxKM * 8); NEED(S.sval_alt, maxKM * 4);
+  const uint32_t nchunks = prim::sort_chunks(maxKM);
+  NEED(S.scounts, size_t(256) * nchunks * 4);
+  NEED(S.spartials, (size_t(256) * nchunks / prim::kScanTile + 2) * 4);
+  prim::SortScratch ss{S.skey_alt.as<uint64_t>(), S.sval_alt.as<uint32_t>(), S.scounts.as<uint32_t>(), S.spartials.as<uint32_t>()};
+  k_compact<<<blocks_for(n), 256, 0, st>>>(d_cmds, n, S.flags.as<uint32_t>(), S.cidx.as<uint32_t>(),
+                                           S.c_cmd.as<helios_gpu_command>(), S.skey.as<uint64_t>(), S.sval.as<uint32_t>());
+  ++launches;
+
+  // ---- stage 2: per-entity chains -------------------------------------------------------------------------------
+  launches += prim::radix_sort_pairs(S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), K, 32, ss, st);
+  NEED(S.src_mask, K * 8); NEED(S.dst_mask, K * 8); NEED(S.wset, K * 8); NEED(S.wlive, K * 8);
+  NEED(S.home_cmd, K * 4); NEED(S.cflags, K * 4); NEED(S.dflag, K * 4); NEED(S.dpos, K * 4);
+  NEED(S.src_t, K * 4); NEED(S.dst_t, K * 4); NEED(S.opcnt, K * 4); NEED(S.opbase, K * 4);
+  ChainArgs ca{S.c_cmd.as<helios_gpu_command>(), S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), K, w->d_gen.as<uint32_t>(),
+               w->d_loc.as<uint64_t>(), w->d_tmask.as<uint64_t>(), w->ent_capacity, S.src_mask.as<uint64_t>(),
+               S.dst_mask.as<uint64_t>(), S.wset.as<uint64_t>(), S.wlive.as<uint64_t>(), S.home_cmd.as<uint32_t>(),
+               S.cflags.as<uint32_t>(), S.dflag.as<uint32_t>(), dc};
+  k_chain<<<blocks_for(K), 256, 0, st>>>(ca);
+  ++launches;
+
+  // ---- stage 3: masks → tables (creating missing archetypes in command order), op counts, net deltas ----------------
+  NEED(S.unknown, size_t(K) * sizeof(Unknown));
+  std::vector<int> hdelta;
+  uint32_t M = 0;
+  for (int attempt = 0;; ++attempt) {
+    HG_TRY(upload_mask_hash(w));
+    const uint32_t nt = uint32_t(w->tables.size());
+    NEED(S.tdelta, std::max<uint32_t>(nt, 1) * 4); NEED(S.tfmin, std::max<uint32_t>(nt, 1) * 4); NEED(S.tseg, std::max<uint32_t>(nt, 1) * 4);
+    HG_CUDA(w, cudaMemsetAsync(S.tdelta.ptr, 0, nt * 4, st));
+    HG_CUDA(w, cudaMemsetAsync(&dc->unknown, 0, 4, st));
+    HG_CUDA(w, cudaMemsetAsync(&dc->effective, 0, 4, st));
+    MaskHash mh{S.mh_keys.as<uint64_t>(), S.mh_vals.as<uint32_t>(), S.mh_log2};
+    k_map_tables<<<blocks_for(K), 256, 0, st>>>(K, S.src_mask.as<uint64_t>(), S.dst_mask.as<uint64_t>(), S.cflags.as<uint32_t>(), mh,
+                                                S.src_t.as<uint32_t>(), S.dst_t.as<uint32_t>(), S.opcnt.as<uint32_t>(),
+                                                S.tdelta.as<int>(), S.unknown.as<Unknown>(), K, dc);
+    launches += 1 + prim::exclusive_scan_u32(S.opcnt.as<uint32_t>(), S.opbase.as<uint32_t>(), K, S.partials.as<uint32_t>(), &dc->n_ops, st);
+    hdelta.assign(nt, 0);
+    HG_CUDA(w, cudaMemcpyAsync(&hc, dc, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    if (nt) HG_CUDA(w, cudaMemcpyAsync(hdelta.data(), S.tdelta.ptr, nt * 4, cudaMemcpyDeviceToHost, st));
+    HG_CUDA(w, cudaStreamSynchronize(st));
+    if (hc.unknown == 0) { M = hc.n_ops; break; }
+    if (attempt > 64) HG_FAIL(w, HELIOS_GPU_ERR_STATE, "archetype creation did not converge");
+    // GetOrCreateArchetype in command order (manager.hpp:1852-1877): first command that needs a mask creates its table
+    std::vector<Unknown> unk(std::min<uint32_t>(hc.unknown, K));
+    HG_CUDA(w, cudaMemcpyAsync(unk.data(), S.unknown.ptr, unk.size() * sizeof(Unknown), cudaMemcpyDeviceToHost, st));
+    HG_CUDA(w, cudaStreamSynchronize(st));
+    std::sort(unk.begin(), unk.end(), [](const Unknown& a, const Unknown& b) { return a.cmd < b.cmd; });
+    for (const Unknown& u : unk) {
+      int t;
+      HG_TRY(ensure_table(w, u.mask, &t));
+    }
+  }
+  w->last_stats.invalid = hc.invalid;
+  w->last_stats.effective = hc.effective;
+  const uint32_t nt = uint32_t(w->tables.size());
+  uint64_t max_rows = 0;
+  for (uint32_t t = 0; t < nt; ++t) {
+    max_rows = std::max<uint64_t>(max_rows, w->tables[t].count);
+    if (hdelta[t] > 0) HG_TRY(ensure_table_rows(w, int(t), w->tables[t].count + uint64_t(hdelta[t])));
+  }
+
+  // ---- stage 4: table op sequences, slot instances, move resolution ------------------------------------------------
+  uint32_t n_changed = 0;
+  if (M) {
+    NEED(S.u_kind, M * 4); NEED(S.u_cmd, M * 4);
+    NEED(S.op_table, M * 4); NEED(S.op_kind, M * 4); NEED(S.op_cmd, M * 4); NEED(S.op_level, M * 4);
+    NEED(S.u2t, M * 4); NEED(S.delta, M * 4); NEED(S.ex, M * 4);
+    NEED(S.key2, M * 8); NEED(S.p2t, M * 4); NEED(S.t2p, M * 4);
+    NEED(S.J, M * 8); NEED(S.resolved, M * 4);
+    k_emit_ops<<<blocks_for(K), 256, 0, st>>>(K, S.opcnt.as<uint32_t>(), S.opbase.as<uint32_t>(), S.src_t.as<uint32_t>(),
+                                              S.dst_t.as<uint32_t>(), S.skey.as<uint64_t>(), S.sval.as<uint32_t>(),
+                                              S.u_kind.as<uint32_t>(), S.u_cmd.as<uint32_t>());
+    ++launches;
+    const int table_bits = prim::bits_for(nt ? nt - 1 : 0);
+    launches += prim::radix_sort_pairs(S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), M, table_bits, ss, st);
+    HG_CUDA(w, cudaMemsetAsync(S.tseg.ptr, 0xFF, nt * 4, st));
+    HG_CUDA(w, cudaMemsetAsync(S.tfmin.ptr, 0xFF, nt * 4, st));
+    k_gather_ops<<<blocks_for(M), 256, 0, st>>>(M, S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), S.u_kind.as<uint32_t>(),
+                                                S.u_cmd.as<uint32_t>(), S.op_table.as<uint32_t>(), S.op_kind.as<uint32_t>(),
+                                                S.op_cmd.as<uint32_t>(), S.u2t.as<uint32_t>(), S.delta.as<uint32_t>(),
+                                                S.tseg.as<uint32_t>());
+    launches += 1 + prim::exclusive_scan_u32(S.delta.as<uint32_t>(), S.ex.as<uint32_t>(), M, S.partials.as<uint32_t>(), nullptr, st);
+    const int level_bits = prim::bits_for(max_rows + M + 1);
+    k_levels<<<blocks_for(M), 256, 0, st>>>(M, S.op_table.as<uint32_t>(), S.op_kind.as<uint32_t>(), S.delta.as<uint32_t>(),
+                                            S.ex.as<uint32_t>(), S.tseg.as<uint32_t>(), w->d_tcount.as<uint32_t>(),
+                                            S.op_level.as<uint32_t>(), S.tfmin.as<uint32_t>(), S.key2.as<uint64_t>(),
+                                            S.p2t.as<uint32_t>(), level_bits);
+    ++launches;
+    launches += prim::radix_sort_pairs(S.key2.as<uint64_t>(), S.p2t.as<uint32_t>(), M, level_bits + table_bits, ss, st);
+    k_invert<<<blocks_for(M), 256, 0, st>>>(M, S.p2t.as<uint32_t>(), S.t2p.as<uint32_t>());
+    ++launches;
+
+    uint32_t ih_log2 = 10;
+    while ((1ull << ih_log2) < 2ull * M) ++ih_log2;
+    NEED(S.ih_keys, (size_t(1) << ih_log2) * 8);
+    NEED(S.ih_vals, (size_t(1) << ih_log2) * 4);
+    HG_CUDA(w, cudaMemsetAsync(S.ih_keys.ptr, 0, (size_t(1) << ih_log2) * 8, st));
+    HG_CUDA(w, cudaMemsetAsync(S.ih_vals.ptr, 0, (size_t(1) << ih_log2) * 4, st));
+    HG_CUDA(w, cudaMemsetAsync(S.resolved.ptr, 0, M * 4, st));
+    OpView v{M, S.op_table.as<uint32_t>(), S.op_kind.as<uint32_t>(), S.op_cmd.as<uint32_t>(), S.op_level.as<uint32_t>(),
+             S.u2t.as<uint32_t>(), S.key2.as<uint64_t>(), S.p2t.as<uint32_t>(), S.t2p.as<uint32_t>(), S.tfmin.as<uint32_t>(),
+             level_bits, S.c_cmd.as<helios_gpu_command>(), S.home_cmd.as<uint32_t>(), S.opbase.as<uint32_t>(),
+             w->d_loc.as<uint64_t>(), S.J.as<uint64_t>(), S.resolved.as<uint32_t>(),
+             InstHash{S.ih_keys.as<unsigned long long>(), S.ih_vals.as<uint32_t>(), ih_log2}};
+    uint32_t rounds = 0;
+    constexpr uint32_t kMaxRounds = 32;
+    for (;;) {
+      HG_CUDA(w, cudaMemsetAsync(&dc->unresolved, 0, 4, st));
+      k_resolve<<<blocks_for(M), 256, 0, st>>>(v, dc);
+      ++launches; ++rounds;
+      uint32_t unresolved = 0;
+      HG_CUDA(w, cudaMemcpyAsync(&unresolved, &dc->unresolved, 4, cudaMemcpyDeviceToHost, st));
+      HG_CUDA(w, cudaStreamSynchronize(st));
+      if (unresolved == 0) break;
+      if (rounds >= kMaxRounds) {
+        k_resolve_sequential<<<blocks_for(nt, 32), 32, 0, st>>>(v, S.tseg.as<uint32_t>(), nt);
+        ++launches;
+        w->last_stats.used_sequential_fallback = 1;
+        break;
+      }
+    }
+    w->last_stats.resolve_rounds = rounds;
+
+    NEED(S.ch_table, M * 4); NEED(S.ch_slot, M * 4); NEED(S.ch_ent, M * 8);
+    k_final_slots<<<blocks_for(M), 256, 0, st>>>(v, w->d_tents.as<helios_gpu_entity_t*>(), S.ch_table.as<uint32_t>(),
+                                                 S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(), dc);
+    ++launches;
+    HG_CUDA(w, cudaMemcpyAsync(&n_changed, &dc->n_changed, 4, cudaMemcpyDeviceToHost, st));
+    HG_CUDA(w, cudaStreamSynchronize(st));
+    if (n_changed) {
+      NEED(S.stage, size_t(n_changed) * S.stage_stride);
+      MoveArgs ma{n_changed, S.ch_table.as<uint32_t>(), S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(),
+                  w->d_loc.as<uint64_t>(), w->d_tmask.as<uint64_t>(), w->d_tcols.as<void*>(),
+                  w->d_tents.as<helios_gpu_entity_t*>(), w->d_csize.as<uint32_t>(), S.coffset.as<uint32_t>(),
+                  S.stage.as<uint8_t>(), S.stage_stride, dc};
+      k_gather_rows<<<blocks_for(n_changed), 256, 0, st>>>(ma);
+      k_scatter_rows<<<blocks_for(n_changed), 256, 0, st>>>(ma);
+      k_update_locations<<<blocks_for(n_changed), 256, 0, st>>>(n_changed, S.ch_table.as<uint32_t>(), S.ch_slot.as<uint32_t>(),
+                                                                S.ch_ent.as<helios_gpu_entity_t>(), w->d_loc.as<uint64_t>());
+      launches += 3;
+    }
+  }
+
+  // ---- stage 5: destroys, payload patch, counts ------------------------------------------------------------------
+  launches += prim::exclusive_scan_u32(S.dflag.as<uint32_t>(), S.dpos.as<uint32_t>(), K, S.partials.as<uint32_t>(), &dc->n_destroy, st);
+  HG_CUDA(w, w->d_free.reserve((w->free_count + K) * 4, w->free_count * 4, st, true));
+  k_destroy<<<blocks_for(K), 256, 0, st>>>(K, S.c_cmd.as<helios_gpu_command>(), S.dflag.as<uint32_t>(), S.dpos.as<uint32_t>(),
+                                           w->d_gen.as<uint32_t>(), w->d_loc.as<uint64_t>(), w->d_free.as<uint32_t>(), w->free_count);
+  k_patch<<<blocks_for(K), 256, 0, st>>>(K, S.c_cmd.as<helios_gpu_command>(), S.wlive.as<uint64_t>(), d_payload,
+                                         w->d_loc.as<uint64_t>(), w->d_tcols.as<void*>(), w->d_csize.as<uint32_t>());
+  k_apply_deltas<<<blocks_for(nt), 256, 0, st>>>(nt, S.tdelta.as<int>(), w->d_tcount.as<uint32_t>());
+  launches += 3;
+  HG_CUDA(w, cudaMemcpyAsync(&hc, dc, sizeof(hc), cudaMemcpyDeviceToHost, st));
+  HG_CUDA(w, cudaStreamSynchronize(st));
+  HG_CUDA(w, cudaGetLastError());
+  for (uint32_t t = 0; t < nt; ++t) w->tables[t].count = uint64_t(int64_t(w->tables[t].count) + hdelta[t]);
+  if (hc.n_destroy) {
+    w->free_count += hc.n_destroy;
+    w->free_cursor = int64_t(w->free_count);  // Destroy sets free_cursor_ = free_indices_.size() (manager.hpp:317-318)
+    w->live_count -= hc.n_destroy;
+  }
+  w->last_stats.moved_rows = n_changed;
+  w->last_stats.moved_bytes = hc.moved_bytes;
+  w->launches += launches;
+  return HELIOS_GPU_OK;
+}
+
 }  // namespace hgpu

@@ -91,7 +91,6 @@ int32_t launch_team_tint(const helios_gpu_system_ctx* ctx) {
 // events in exactly the order the reference's serial ForEach would have emitted them (no atomics needed).
 struct DetectBody {
   const helios_gpu_msg_writer* d_wr;  // device-resident view: stays valid across buffer swaps (CUDA-graph safe)
-  const helios_gpu_query_view* view;
   __device__ void operator()(const Row& r, Position& p, Team& t) const {
     const helios_gpu_msg_writer wr = *d_wr;
     CollisionEvent ev;
@@ -100,12 +99,12 @@ struct DetectBody {
     ev.impulse = p.x * 0.0078125f + float(t.id);
     ev.pad = 0;
     if (r.flat_row < wr.capacity) reinterpret_cast<CollisionEvent*>(wr.data)[r.flat_row] = ev;
-    if (r.flat_row == 0) *wr.count = view->n_rows < wr.capacity ? view->n_rows : wr.capacity;
+    if (r.flat_row == 0) *wr.count = r.n_rows < wr.capacity ? r.n_rows : wr.capacity;
   }
 };
 int32_t launch_detect(const helios_gpu_system_ctx* ctx) {
   if (!ctx->writer.data || ctx->writer.elem_size != sizeof(CollisionEvent)) return HELIOS_GPU_ERR_STATE;
-  return for_each_launch<0u, true, DetectBody, Position, Team>(ctx, DetectBody{ctx->d_writer, ctx->view});
+  return for_each_launch<0u, true, DetectBody, Position, Team>(ctx, DetectBody{ctx->d_writer});
 }
 
 // ---- "detect_sparse": same query, emits only when team == 0, through the warp-aggregated append ring ---------

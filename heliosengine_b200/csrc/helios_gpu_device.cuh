@@ -31,6 +31,7 @@ static_assert(kPairs * 2 * kBlock == kTileRows, "tile geometry");
 
 struct Row {
   uint64_t flat_row;            // position in ForEach visit order over the whole match set
+  uint64_t n_rows;              // total rows the query matched (Query::Count)
   helios_gpu_entity_t entity;   // valid only in *_with_entity launches, else HELIOS_GPU_INVALID_ENTITY
   uint32_t archetype;
   uint32_t row;                 // row inside the archetype table
@@ -98,23 +99,182 @@ __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 }  // namespace detail
 
 // ---------------------------------------------------------------------------------------------------
-// for_each_kernel: persistent grid (one resident wave), CTAs stride over the flattened tile space.
+// One tile of one table: all loads first, then the body on registers, then streaming stores.
 // ---------------------------------------------------------------------------------------------------
+struct TileRef {
+  uint32_t archetype;
+  uint32_t rows;        // live rows of the table
+  uint32_t row0;        // first row of this tile inside the table
+  uint64_t row_begin;   // flattened index of the table's row 0
+  uint64_t n_rows;      // rows matched by the whole query
+  const helios_gpu_entity_t* entities;
+};
+
 template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
-__global__ void __launch_bounds__(kBlock) for_each_kernel(const helios_gpu_query_view* __restrict__ view, Body body) {
+__device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<Cs*...> cols, Body& body) {
   using namespace detail;
   constexpr int N = sizeof...(Cs);
-  static_assert(N >= 1 && N <= HELIOS_GPU_MAX_QUERY_COMPONENTS, "1..8 data components per body");
-  __shared__ helios_gpu_segment s_seg;
+  const uint32_t row0 = t.row0;
+  const uint32_t live = t.rows - row0;
+  cuda::std::tuple<CompRegs<Cs>...> regs;
+  helios_gpu_entity_t ents[kPairs][2];
 
-  const uint32_t n_tiles = view->n_tiles;
-  const uint32_t n_seg = view->n_segments;
-  const helios_gpu_segment* __restrict__ segs = view->segments;
+  auto each = [&](auto&& fn) {
+    [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
+      (fn(cuda::std::integral_constant<int, int(Is)>{}, cuda::std::get<Is>(regs), cuda::std::get<Is>(cols)), ...);
+    }(cuda::std::make_index_sequence<N>{});
+  };
+  auto call = [&](const Row& rc, int k, int j) {
+    [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
+      body(rc, cuda::std::get<Is>(regs).p[k].v[j]...);
+    }(cuda::std::make_index_sequence<N>{});
+  };
+
+  if (live >= kTileRows) {
+    each([&](auto, auto& cr, auto* col) {
+#pragma unroll
+      for (int k = 0; k < kPairs; ++k) load_pair(cr.p[k], col + row0 + k * 2 * kBlock + 2 * threadIdx.x);
+    });
+    if constexpr (kWithEntity) {
+#pragma unroll
+      for (int k = 0; k < kPairs; ++k) {
+        const uint4 e = __ldcs(reinterpret_cast<const uint4*>(t.entities + row0 + k * 2 * kBlock + 2 * threadIdx.x));
+        ents[k][0] = uint64_t(e.x) | (uint64_t(e.y) << 32);
+        ents[k][1] = uint64_t(e.z) | (uint64_t(e.w) << 32);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kPairs; ++k) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const uint32_t r = row0 + k * 2 * kBlock + 2 * threadIdx.x + j;
+        call(Row{t.row_begin + r, t.n_rows, kWithEntity ? ents[k][j] : HELIOS_GPU_INVALID_ENTITY, t.archetype, r}, k, j);
+      }
+    }
+    each([&](auto idx, auto& cr, auto* col) {
+      if constexpr ((kWriteMask >> decltype(idx)::value) & 1u) {
+#pragma unroll
+        for (int k = 0; k < kPairs; ++k) store_pair(cr.p[k], col + row0 + k * 2 * kBlock + 2 * threadIdx.x);
+      }
+    });
+  } else {
+    // ragged last tile of a table: guarded scalar path
+#pragma unroll
+    for (int k = 0; k < kPairs; ++k) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const uint32_t off = k * 2 * kBlock + 2 * threadIdx.x + j;
+        if (off < live) {
+          const uint32_t r = row0 + off;
+          each([&](auto, auto& cr, auto* col) { cr.p[k].v[j] = col[r]; });
+          call(Row{t.row_begin + r, t.n_rows, kWithEntity ? t.entities[r] : HELIOS_GPU_INVALID_ENTITY, t.archetype, r}, k, j);
+          each([&](auto idx, auto& cr, auto* col) {
+            if constexpr ((kWriteMask >> decltype(idx)::value) & 1u) col[r] = cr.p[k].v[j];
+          });
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// for_each_kernel (fused match): every CTA evaluates the archetype-mask match itself from the device table
+// directory (query.hpp:1732-1812 semantics: creation order, empty tables skipped, With ∪ data ⊆ id, Without ∩ id = ∅)
+// into shared memory, then strides over the flattened tile space.  No separate match launch, no dependency bubble.
+// ---------------------------------------------------------------------------------------------------
+constexpr int kFusedMaxTables = 1024;
+
+template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
+__global__ void __launch_bounds__(kBlock) for_each_kernel(const helios_gpu_match_args m, Body body) {
+  constexpr int N = sizeof...(Cs);
+  static_assert(N >= 1 && N <= HELIOS_GPU_MAX_QUERY_COMPONENTS, "1..8 data components per body");
+  __shared__ uint32_t s_tile_begin[kFusedMaxTables + 1];
+  __shared__ uint32_t s_table[kFusedMaxTables];
+  __shared__ uint64_t s_row_begin[kFusedMaxTables];
+  __shared__ uint32_t s_warp[3][kBlock / 32];
+  __shared__ uint32_t s_run[3];  // running {segments, tiles, rows(lo)}; rows(hi) kept in s_rows
+  __shared__ uint64_t s_rows;
+
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) { s_run[0] = 0; s_run[1] = 0; s_rows = 0; }
+  __syncthreads();
+  for (uint32_t base = 0; base < m.n_tables; base += kBlock) {
+    const uint32_t t = base + threadIdx.x;
+    uint32_t f = 0, tiles = 0, rows = 0;
+    if (t < m.n_tables) {
+      const uint64_t mask = m.table_mask[t];
+      const uint32_t c = m.table_rows[t];
+      if (c != 0 && (mask & m.required_mask) == m.required_mask && (mask & m.without_mask) == 0) {
+        f = 1; tiles = (c + kTileRows - 1) / kTileRows; rows = c;
+      }
+    }
+    // block exclusive scan of (f, tiles, rows); rows of one 256-table chunk fit 64 bits, scanned as two u32 halves is
+    // unnecessary: a chunk holds < 2^32 * 256 rows, so scan rows in 64 bits via two shuffles
+    uint32_t fi = f, ti = tiles;
+    unsigned long long ri = rows;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t a = __shfl_up_sync(0xFFFFFFFFu, fi, o), b = __shfl_up_sync(0xFFFFFFFFu, ti, o);
+      const unsigned long long c2 = __shfl_up_sync(0xFFFFFFFFu, ri, o);
+      if (lane >= uint32_t(o)) { fi += a; ti += b; ri += c2; }
+    }
+    __shared__ unsigned long long s_wrows[kBlock / 32];
+    if (lane == 31) { s_warp[0][wid] = fi; s_warp[1][wid] = ti; s_wrows[wid] = ri; }
+    __syncthreads();
+    uint32_t fo = 0, to = 0;
+    unsigned long long ro = 0;
+    for (uint32_t w2 = 0; w2 < wid; ++w2) { fo += s_warp[0][w2]; to += s_warp[1][w2]; ro += s_wrows[w2]; }
+    const uint32_t seg = s_run[0] + fo + fi - f;
+    if (f) {
+      s_table[seg] = t;
+      s_tile_begin[seg] = s_run[1] + to + ti - tiles;
+      s_row_begin[seg] = s_rows + ro + ri - rows;
+    }
+    __syncthreads();
+    if (threadIdx.x == kBlock - 1) { s_run[0] += fo + fi; s_run[1] += to + ti; s_rows += ro + ri; }
+    __syncthreads();
+  }
+  const uint32_t n_seg = s_run[0], n_tiles = s_run[1];
+  const uint64_t n_rows = s_rows;
+  if (threadIdx.x == 0) s_tile_begin[n_seg] = n_tiles;
+  __syncthreads();
 
   for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    __syncthreads();  // previous iteration finished reading s_seg
+    // upper_bound(tile) - 1 over s_tile_begin[0..n_seg]
+    uint32_t lo = 0, hi = n_seg;
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (s_tile_begin[mid] <= tile) lo = mid; else hi = mid;
+    }
+    const uint32_t t = s_table[lo];
+    TileRef tr;
+    tr.archetype = t;
+    tr.rows = __ldg(&m.table_rows[t]);
+    tr.row0 = (tile - s_tile_begin[lo]) * kTileRows;
+    tr.row_begin = s_row_begin[lo];
+    tr.n_rows = n_rows;
+    tr.entities = kWithEntity ? reinterpret_cast<const helios_gpu_entity_t*>(__ldg(reinterpret_cast<const unsigned long long*>(&m.table_entities[t]))) : nullptr;
+    void* const* dir = m.table_columns + size_t(t) * HELIOS_GPU_MAX_COMPONENTS;
+    auto cols = [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
+      return cuda::std::tuple<Cs*...>{reinterpret_cast<Cs*>(__ldg(reinterpret_cast<const unsigned long long*>(&dir[m.slots[Is]])))...};
+    }(cuda::std::make_index_sequence<N>{});
+    process_tile<kWriteMask, kWithEntity, Body, Cs...>(tr, cols, body);
+  }
+}
+
+// for_each_kernel_view: same visit over a MATERIALISED view (worlds with more than kFusedMaxTables tables).
+template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
+__global__ void __launch_bounds__(kBlock) for_each_kernel_view(const helios_gpu_query_view* __restrict__ view, Body body) {
+  using namespace detail;
+  constexpr int N = sizeof...(Cs);
+  __shared__ helios_gpu_segment s_seg;
+  const uint32_t n_tiles = view->n_tiles;
+  const uint32_t n_seg = view->n_segments;
+  const uint64_t n_rows = view->n_rows;
+  const helios_gpu_segment* __restrict__ segs = view->segments;
+  for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    __syncthreads();
     if (threadIdx.x < 32) {
-      // warp-cooperative search of the segment that owns `tile` (segments are sorted by tile_begin)
       uint32_t found = 0xFFFFFFFFu;
       for (uint32_t base = 0; base < n_seg; base += 32) {
         const uint32_t s = base + lane_id();
@@ -124,81 +284,19 @@ __global__ void __launch_bounds__(kBlock) for_each_kernel(const helios_gpu_query
           const uint32_t te = tb + (segs[s].rows + kTileRows - 1) / kTileRows;
           hit = tile >= tb && tile < te;
         }
-        const uint32_t m = __ballot_sync(0xFFFFFFFFu, hit);
-        if (m) { found = base + (__ffs(m) - 1); break; }
+        const uint32_t mm = __ballot_sync(0xFFFFFFFFu, hit);
+        if (mm) { found = base + (__ffs(mm) - 1); break; }
       }
       constexpr int kWords = sizeof(helios_gpu_segment) / 8;
       if (found != 0xFFFFFFFFu && lane_id() < kWords)
         reinterpret_cast<uint64_t*>(&s_seg)[lane_id()] = reinterpret_cast<const uint64_t*>(&segs[found])[lane_id()];
     }
     __syncthreads();
-
-    const uint32_t row0 = (tile - s_seg.tile_begin) * kTileRows;
-    const uint32_t live = s_seg.rows - row0;  // rows of the table at/after row0
-    cuda::std::tuple<CompRegs<Cs>...> regs;
-    helios_gpu_entity_t ents[kPairs][2];
-
-    auto each = [&](auto&& fn) {
-      [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
-        (fn(cuda::std::integral_constant<int, int(Is)>{}, cuda::std::get<Is>(regs),
-            static_cast<typename cuda::std::tuple_element<Is, cuda::std::tuple<Cs...>>::type*>(s_seg.columns[Is])),
-         ...);
-      }(cuda::std::make_index_sequence<N>{});
-    };
-
-    if (live >= kTileRows) {
-      // ---- full tile: vector path, every load issued before the first use --------------------------
-      each([&](auto, auto& cr, auto* col) {
-#pragma unroll
-        for (int k = 0; k < kPairs; ++k) load_pair(cr.p[k], col + row0 + k * 2 * kBlock + 2 * threadIdx.x);
-      });
-      if constexpr (kWithEntity) {
-#pragma unroll
-        for (int k = 0; k < kPairs; ++k) {
-          const uint4 e = __ldcs(reinterpret_cast<const uint4*>(s_seg.entities + row0 + k * 2 * kBlock + 2 * threadIdx.x));
-          ents[k][0] = uint64_t(e.x) | (uint64_t(e.y) << 32);
-          ents[k][1] = uint64_t(e.z) | (uint64_t(e.w) << 32);
-        }
-      }
-#pragma unroll
-      for (int k = 0; k < kPairs; ++k) {
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          const uint32_t r = row0 + k * 2 * kBlock + 2 * threadIdx.x + j;
-          const Row rowctx{s_seg.row_begin + r, kWithEntity ? ents[k][j] : HELIOS_GPU_INVALID_ENTITY, s_seg.archetype, r};
-          [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
-            body(rowctx, cuda::std::get<Is>(regs).p[k].v[j]...);
-          }(cuda::std::make_index_sequence<N>{});
-        }
-      }
-      each([&](auto idx, auto& cr, auto* col) {
-        if constexpr ((kWriteMask >> decltype(idx)::value) & 1u) {
-#pragma unroll
-          for (int k = 0; k < kPairs; ++k) store_pair(cr.p[k], col + row0 + k * 2 * kBlock + 2 * threadIdx.x);
-        }
-      });
-    } else {
-      // ---- ragged last tile of a table: guarded scalar path -----------------------------------------
-#pragma unroll
-      for (int k = 0; k < kPairs; ++k) {
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          const uint32_t off = k * 2 * kBlock + 2 * threadIdx.x + j;
-          if (off < live) {
-            const uint32_t r = row0 + off;
-            each([&](auto, auto& cr, auto* col) { cr.p[k].v[j] = col[r]; });
-            const Row rowctx{s_seg.row_begin + r, kWithEntity ? s_seg.entities[r] : HELIOS_GPU_INVALID_ENTITY,
-                             s_seg.archetype, r};
-            [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
-              body(rowctx, cuda::std::get<Is>(regs).p[k].v[j]...);
-            }(cuda::std::make_index_sequence<N>{});
-            each([&](auto idx, auto& cr, auto* col) {
-              if constexpr ((kWriteMask >> decltype(idx)::value) & 1u) col[r] = cr.p[k].v[j];
-            });
-          }
-        }
-      }
-    }
+    TileRef tr{s_seg.archetype, s_seg.rows, (tile - s_seg.tile_begin) * kTileRows, s_seg.row_begin, n_rows, s_seg.entities};
+    auto cols = [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
+      return cuda::std::tuple<Cs*...>{static_cast<Cs*>(s_seg.columns[Is])...};
+    }(cuda::std::make_index_sequence<N>{});
+    process_tile<kWriteMask, kWithEntity, Body, Cs...>(tr, cols, body);
   }
 }
 
@@ -206,13 +304,19 @@ __global__ void __launch_bounds__(kBlock) for_each_kernel(const helios_gpu_query
 template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
 inline int32_t for_each_launch(const helios_gpu_system_ctx* ctx, Body body) {
   auto kern = for_each_kernel<kWriteMask, kWithEntity, Body, Cs...>;
-  static int blocks_per_sm = 0;
-  if (blocks_per_sm == 0) {
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, kBlock, 0) != cudaSuccess || blocks_per_sm < 1)
-      blocks_per_sm = 1;
+  auto kern_view = for_each_kernel_view<kWriteMask, kWithEntity, Body, Cs...>;
+  static int bps = 0, bps_view = 0;
+  if (bps == 0) {
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, kBlock, 0) != cudaSuccess || bps < 1) bps = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_view, kern_view, kBlock, 0) != cudaSuccess || bps_view < 1) bps_view = 1;
   }
-  const uint32_t grid = ctx->sm_count * uint32_t(blocks_per_sm);
-  kern<<<grid, kBlock, 0, static_cast<cudaStream_t>(ctx->stream)>>>(ctx->view, body);
+  cudaStream_t st = static_cast<cudaStream_t>(ctx->stream);
+  if (ctx->view == nullptr) {
+    if (ctx->match.n_tables > uint32_t(kFusedMaxTables)) return HELIOS_GPU_ERR_STATE;  // the schedule materialises a view then
+    kern<<<ctx->sm_count * uint32_t(bps), kBlock, 0, st>>>(ctx->match, body);
+  } else {
+    kern_view<<<ctx->sm_count * uint32_t(bps_view), kBlock, 0, st>>>(ctx->view, body);
+  }
   helios_gpu_world_note_launches(ctx->world, 1);
   return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
 }

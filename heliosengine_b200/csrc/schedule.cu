@@ -166,8 +166,20 @@ int32_t launch_system(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaS
   ctx.world_view.entity_capacity = w->ent_capacity;
   ctx.world_view.n_tables = uint32_t(w->tables.size());
   if (e.desc.query) {
-    HG_TRY(query_refresh(e.desc.query, stream));
-    ctx.view = e.desc.query->d_view.as<helios_gpu_query_view>();
+    helios_gpu_query* q = e.desc.query;
+    ctx.match.table_mask = w->d_tmask.as<uint64_t>();
+    ctx.match.table_rows = w->d_tcount.as<uint32_t>();
+    ctx.match.table_entities = w->d_tents.as<const helios_gpu_entity_t*>();
+    ctx.match.table_columns = w->d_tcols.as<void*>();
+    ctx.match.n_tables = q->never_matches ? 0u : uint32_t(w->tables.size());
+    ctx.match.n_components = q->desc.n_components;
+    ctx.match.required_mask = q->required_mask;
+    ctx.match.without_mask = q->without_mask;
+    for (uint32_t k = 0; k < q->desc.n_components; ++k) ctx.match.slots[k] = q->slots[k];
+    if ((e.desc.flags & HELIOS_GPU_SYSTEM_NEEDS_VIEW) || w->tables.size() > HELIOS_GPU_FUSED_MATCH_MAX_TABLES) {
+      HG_TRY(query_refresh(q, stream));  // stand-alone match kernel → materialised view
+      ctx.view = q->d_view.as<helios_gpu_query_view>();
+    }
   }
   if (e.desc.flags & HELIOS_GPU_SYSTEM_EMITS_COMMANDS) {
     if (e.cmd_slots_in_use)  // all-ones = kind NONE in every slot

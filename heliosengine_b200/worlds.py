@@ -99,7 +99,7 @@ def build_lattice(world: capi.World, n: int, optional: list[str], stream_base: i
     return rows
 
 
-def build_cfg2(world: capi.World, n: int = 1 << 24, filtered: bool = False):
+def build_cfg2(world: capi.World, n: int = 1 << 24, filtered: bool = False, flags: int = 0):
     """configs[1]: n entities across 64 archetypes (4 mandatory + 6 optional 4-byte components);
     Query<Position&, Velocity&, const Acceleration&, const Mass&[, With<Health>, Without<Frozen>]>,
     body v += a*(dt/m); p += v*dt."""
@@ -107,7 +107,7 @@ def build_cfg2(world: capi.World, n: int = 1 << 24, filtered: bool = False):
     q = world.query([(cname("Position"), True), (cname("Velocity"), True), (cname("Acceleration"), False), (cname("Mass"), False)],
                     with_=[cname("Health")] if filtered else [], without=[cname("Frozen")] if filtered else [])
     s = world.schedule("Update")
-    s.add_system("AccelIntegrate", "accel_integrate", q, params=struct.pack("<f", DT))
+    s.add_system("AccelIntegrate", "accel_integrate", q, params=struct.pack("<f", DT), flags=flags)
     s.build()
     return s, q
 

@@ -237,6 +237,21 @@ typedef struct helios_gpu_cmd_writer { /* SystemLocalData::cmd_queue (param_trai
   uint32_t slots_per_row;
 } helios_gpu_cmd_writer;
 
+/* Arguments of the device-side archetype-mask match.  for_each kernels evaluate the match themselves (fused, per CTA)
+ * from the device table directory; `view` (system ctx) is only materialised for worlds with more tables than the fused
+ * path holds in shared memory or when a system asks for it (HELIOS_GPU_SYSTEM_NEEDS_VIEW). */
+typedef struct helios_gpu_match_args {
+  const uint64_t* table_mask;                          /* [table] component-slot mask */
+  const uint32_t* table_rows;                          /* [table] live rows */
+  const helios_gpu_entity_t* const* table_entities;    /* [table] entity column */
+  void* const* table_columns;                          /* [table*64 + slot] column base */
+  uint32_t n_tables;
+  uint32_t n_components;
+  uint64_t required_mask;                              /* With ∪ data components */
+  uint64_t without_mask;
+  int32_t slots[HELIOS_GPU_MAX_QUERY_COMPONENTS];      /* component slot per body argument */
+} helios_gpu_match_args;
+
 /* Device directory for random access by entity id — World::Get/TryGet<T>(entity) from inside a body
  * (component/manager.hpp:1613-1635): location[index] = table<<32|row, then columns[table*64 + slot][row]. */
 typedef struct helios_gpu_world_view {
@@ -252,7 +267,8 @@ typedef struct helios_gpu_world_view {
 typedef struct helios_gpu_system_ctx {
   helios_gpu_world* world;
   void* stream;                        /* cudaStream_t the body must launch on */
-  const helios_gpu_query_view* view;   /* DEVICE pointer; filled by the match kernel earlier on `stream` */
+  const helios_gpu_query_view* view;   /* DEVICE pointer to a materialised view, or NULL (fused match: use `match`) */
+  helios_gpu_match_args match;         /* by-value arguments of the fused device-side match */
   uint32_t sm_count;
   uint32_t system_index;               /* registration index in its schedule */
   const void* params;                  /* host copy of the bytes given at registration */
@@ -274,6 +290,8 @@ typedef struct helios_gpu_system_ctx {
 typedef int32_t (*helios_gpu_system_fn)(const helios_gpu_system_ctx* ctx);
 
 #define HELIOS_GPU_SYSTEM_EMITS_COMMANDS 1u
+#define HELIOS_GPU_SYSTEM_NEEDS_VIEW 2u /* run the stand-alone match kernel first and pass ctx->view */
+#define HELIOS_GPU_FUSED_MATCH_MAX_TABLES 1024u
 typedef struct helios_gpu_system_desc {
   const char* name;
   helios_gpu_query* query;         /* may be NULL */

@@ -68,10 +68,12 @@ def test_cfg2_match_and_iterate(gpu, oracle, n, filtered):
 
 
 def test_all_exec_modes_agree(gpu, oracle):
+    """Serial stream / multi-stream / CUDA-graph execution and the materialised-view kernel path give one answer."""
     snaps = []
-    for mode in (capi.EXEC_SERIAL, capi.EXEC_STREAMS, capi.EXEC_GRAPH):
+    for mode, flags in ((capi.EXEC_SERIAL, 0), (capi.EXEC_STREAMS, 0), (capi.EXEC_GRAPH, 0),
+                        (capi.EXEC_SERIAL, capi.SYSTEM_NEEDS_VIEW), (capi.EXEC_GRAPH, capi.SYSTEM_NEEDS_VIEW)):
         w = capi.World(gpu)
-        s, _ = worlds.build_cfg2(w, 64 * 2048, True)
+        s, _ = worlds.build_cfg2(w, 64 * 2048, True, flags=flags)
         for _ in range(3):
             s.run_and_wait(mode)
         snaps.append(w.snapshot())
