@@ -96,6 +96,13 @@ struct CompRegs {
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 
+// Typed column tuple from an array of N untyped bases.  A plain function template on purpose: nvcc 12.9 expands
+// `Cs`/`Is` in lockstep incorrectly inside a generic lambda (every element received index 0).
+template <typename... Cs, size_t... Is>
+__device__ __forceinline__ cuda::std::tuple<Cs*...> typed_columns(void* const* bases, cuda::std::index_sequence<Is...>) {
+  return cuda::std::tuple<Cs*...>{static_cast<Cs*>(bases[Is])...};
+}
+
 }  // namespace detail
 
 // ---------------------------------------------------------------------------------------------------
@@ -255,9 +262,11 @@ __global__ void __launch_bounds__(kBlock) for_each_kernel(const helios_gpu_match
     tr.n_rows = n_rows;
     tr.entities = kWithEntity ? reinterpret_cast<const helios_gpu_entity_t*>(__ldg(reinterpret_cast<const unsigned long long*>(&m.table_entities[t]))) : nullptr;
     void* const* dir = m.table_columns + size_t(t) * HELIOS_GPU_MAX_COMPONENTS;
-    auto cols = [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
-      return cuda::std::tuple<Cs*...>{reinterpret_cast<Cs*>(__ldg(reinterpret_cast<const unsigned long long*>(&dir[m.slots[Is]])))...};
-    }(cuda::std::make_index_sequence<N>{});
+    void* bases[N];
+#pragma unroll
+    for (int k = 0; k < N; ++k)
+      bases[k] = reinterpret_cast<void*>(__ldg(reinterpret_cast<const unsigned long long*>(&dir[m.slots[k]])));
+    const auto cols = detail::typed_columns<Cs...>(bases, cuda::std::make_index_sequence<N>{});
     process_tile<kWriteMask, kWithEntity, Body, Cs...>(tr, cols, body);
   }
 }
@@ -293,9 +302,10 @@ __global__ void __launch_bounds__(kBlock) for_each_kernel_view(const helios_gpu_
     }
     __syncthreads();
     TileRef tr{s_seg.archetype, s_seg.rows, (tile - s_seg.tile_begin) * kTileRows, s_seg.row_begin, n_rows, s_seg.entities};
-    auto cols = [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
-      return cuda::std::tuple<Cs*...>{static_cast<Cs*>(s_seg.columns[Is])...};
-    }(cuda::std::make_index_sequence<N>{});
+    void* bases[N];
+#pragma unroll
+    for (int k = 0; k < N; ++k) bases[k] = s_seg.columns[k];
+    const auto cols = detail::typed_columns<Cs...>(bases, cuda::std::make_index_sequence<N>{});
     process_tile<kWriteMask, kWithEntity, Body, Cs...>(tr, cols, body);
   }
 }
