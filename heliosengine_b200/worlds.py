@@ -183,8 +183,14 @@ def assemble_cfg3(world: capi.World, spawned: np.ndarray, despawn, insert, remov
     return cmds, payload.view(np.uint8)[:total + 16]
 
 
-def build_cfg4(world: capi.World, n: int = 1 << 22):
-    """configs[3]: n entities {Position, Velocity, Health, Team, Tint}; 8-system schedule with a CollisionEvent channel."""
+def build_cfg4(world: capi.World, n: int = 1 << 22, sparse_emit: bool = False):
+    """configs[3]: n entities {Position, Velocity, Health, Team, Tint}; 8-system schedule with a CollisionEvent channel.
+
+    The emitter is REGISTERED LAST on purpose: every system entry's MergeMessages moves
+    world-current into world-previous before appending its own messages (system_local_data.hpp:122-132), and the
+    per-frame World::Update clears automatic-policy `previous` (message/manager.hpp:400-419).  Only messages merged by
+    the last entry are still in `current` at World::Update, become `previous` there and are what next frame's reader
+    sees — the documented "write frame N -> read frame N+1" flow."""
     register_all(world, ["Position", "Velocity", "Health", "Team", "Tint"])
     shorts = ["Position", "Velocity", "Health", "Team", "Tint"]
     world.spawn_batch([cname(s) for s in shorts], n, [column(s, n, 7000 + i) for i, s in enumerate(shorts)], want_entities=False)
@@ -193,16 +199,22 @@ def build_cfg4(world: capi.World, n: int = 1 << 22):
     s = world.schedule("Update")
     s.add_system("S0_integrate", "integrate", world.query([(P, True), (V, False)]))
     s.add_system("S1_damp", "damp", world.query([(V, True)]), params=struct.pack("<f", 0.99))
-    s.add_system("S2_detect", "detect", world.query([(P, False), (T, False)]), writes_message=COLLISION_EVENT)
-    s.add_system("S3_regen", "regen", world.query([(H, True)]))
-    s.add_system("S4_team_tint", "team_tint", world.query([(T, False), (TI, True)]))
-    s.add_system("S5_consume", "consume", None, params=struct.pack("<I", world.slots[H]), reads_message=COLLISION_EVENT,
+    s.add_system("S2_regen", "regen", world.query([(H, True)]))
+    s.add_system("S3_team_tint", "team_tint", world.query([(T, False), (TI, True)]))
+    s.add_system("S4_consume", "consume", None, params=struct.pack("<I", world.slots[H]), reads_message=COLLISION_EVENT,
                  extra_writes=[H])
-    s.add_system("S6_stats", "stats", world.query([(H, False)]), write_resources=["helios::bench::Stats"])
-    s.add_system("S7_exit_check", "exit_check", None, read_resources=["helios::bench::Stats"],
+    s.add_system("S5_stats", "stats", world.query([(H, False)]), write_resources=["helios::bench::Stats"])
+    s.add_system("S6_exit_check", "exit_check", None, read_resources=["helios::bench::Stats"],
                  write_resources=["helios::bench::Exit"])
+    s.add_system("S7_detect", "detect_sparse" if sparse_emit else "detect", world.query([(P, False), (T, False)]),
+                 writes_message=COLLISION_EVENT, writer_capacity=n if sparse_emit else 0)
     s.build()
     return s
+
+
+# per entity: S0 24, S1 16, S2 8, S3 8, S5 4, S7 12 (+ the 8-byte entity id); per event: 24 written + 24 read + 8 Health rmw
+CFG4_COMPONENT_BYTES_PER_ENTITY = 24 + 16 + 8 + 8 + 4 + 12 + 8
+CFG4_BYTES_PER_EVENT = 24 + 24 + 8
 
 
 def snapshots_equal(a: dict, b: dict, float_cols: dict | None = None) -> list[str]:

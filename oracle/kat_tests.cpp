@@ -1,0 +1,694 @@
+// kat_tests.cpp — the reference's own known-answer tests for the hot path, re-expressed against the oracle.
+//
+// *** TEST INFRASTRUCTURE ONLY *** (see helios_oracle.hpp).  Each block cites the reference doctest case it
+// restates (paths relative to /root/reference/src/ecs/tests/).  The reference tests are template-typed; here the same
+// scenarios run through the oracle's runtime-typed API with the same values and the same expectations.  This is what
+// pins the oracle ("parity pinned by the reference's own tests" — SURVEY.md §8c); row order after mixed migrations,
+// archetype creation order and cross-system command order have no reference test and are pinned by source reading only.
+//
+// Build + run:  make -C oracle kat && oracle/kat_tests     (exit code = number of failed checks)
+#include <cstdio>
+#include <cstring>
+#include <set>
+
+#include "helios_oracle.hpp"
+
+using namespace helios_oracle;
+
+static int g_checks = 0, g_fail = 0;
+#define CHECK(x)                                                    \
+  do {                                                              \
+    ++g_checks;                                                     \
+    if (!(x)) {                                                     \
+      ++g_fail;                                                     \
+      std::printf("FAIL %s:%d  %s\n", __FILE__, __LINE__, #x);      \
+    }                                                               \
+  } while (0)
+
+namespace {
+
+struct Position { float x = 0, y = 0; };
+struct Velocity { float x = 0, y = 0; };
+struct Health { int points = 100; };
+struct Script { int id = 0; };
+
+const TypeIndex kPos = Fnv1a("Position"), kVel = Fnv1a("Velocity"), kHealth = Fnv1a("Health"), kScript = Fnv1a("Script");
+
+template <typename T>
+ComponentMeta MetaOf(TypeIndex t) {
+  ComponentMeta m;
+  m.type = t;
+  m.size = sizeof(T);
+  m.align = alignof(T);
+  T def{};
+  m.default_bytes.assign(reinterpret_cast<const uint8_t*>(&def), reinterpret_cast<const uint8_t*>(&def) + sizeof(T));
+  return m;
+}
+void RegisterAll(ComponentManager& m) {
+  m.Register(MetaOf<Position>(kPos));
+  m.Register(MetaOf<Velocity>(kVel));
+  m.Register(MetaOf<Health>(kHealth));
+  m.Register(MetaOf<Script>(kScript));
+}
+template <typename T>
+T GetAs(ComponentManager& m, Entity e, TypeIndex t) {
+  T v{};
+  const uint8_t* p = m.Get(e, t);
+  if (p) std::memcpy(&v, p, sizeof(T));
+  return v;
+}
+
+// ---- utils/hash.hpp: FNV-1a-64 published test vectors (the function is the reference's Fnv1aHash) ---------------
+void TestFnv() {
+  CHECK(Fnv1a("") == 0xcbf29ce484222325ULL);
+  CHECK(Fnv1a("a") == 0xaf63dc4c8601ec8cULL);
+  CHECK(Fnv1a("foobar") == 0x85944171f73967e8ULL);
+}
+
+// ---- entity/manager.cpp:77-131 Create, :191-289 Destroy, :427-541 Reserve/Flush/generation/edge cases ---------------
+void TestEntityManager() {
+  {
+    EntityManager m;  // :77-86
+    const Entity e = m.Create();
+    CHECK(e.Valid());
+    CHECK(m.Count() == 1);
+    CHECK(m.Validate(e));
+  }
+  {
+    EntityManager m;  // :104-122 unique indices
+    std::set<uint32_t> idx;
+    for (int i = 0; i < 100; ++i) idx.insert(m.Create().index);
+    CHECK(idx.size() == 100);
+  }
+  {
+    EntityManager m;  // :204-216 destroy multiple
+    const Entity e1 = m.Create(), e2 = m.Create(), e3 = m.Create();
+    m.Destroy(e1);
+    m.Destroy(e2);
+    CHECK(!m.Validate(e1));
+    CHECK(!m.Validate(e2));
+    CHECK(m.Validate(e3));
+    CHECK(m.Count() == 1);
+  }
+  {
+    EntityManager m;  // :231-242 destroy and recreate
+    const Entity e1 = m.Create();
+    m.Destroy(e1);
+    const Entity e2 = m.Create();
+    CHECK(e2.Valid());
+    CHECK(e1 != e2);
+    CHECK(e1.index == e2.index);
+    CHECK(e1.generation != e2.generation);
+    CHECK(e2.generation > e1.generation);  // :455-466
+  }
+  {
+    EntityManager m;  // :253-289 range destroy
+    std::vector<Entity> es;
+    for (int i = 0; i < 10; ++i) es.push_back(m.Create());
+    std::vector<Entity> first(es.begin(), es.begin() + 5);
+    m.DestroyRange(first);
+    CHECK(m.Count() == 5);
+    for (int i = 0; i < 5; ++i) CHECK(!m.Validate(es[i]));
+    for (int i = 5; i < 10; ++i) CHECK(m.Validate(es[i]));
+  }
+  {
+    EntityManager m;  // :428-451 reserve + flush
+    const Entity r1 = m.ReserveEntity(), r2 = m.ReserveEntity(), r3 = m.ReserveEntity();
+    CHECK(r1.Valid() && r2.Valid() && r3.Valid());
+    CHECK(r1 != r2);
+    CHECK(r2 != r3);
+    CHECK(!m.Validate(r1));  // metadata untouched until Flush (entity/manager.hpp:294-305)
+    int seen = 0;
+    m.Flush([&](Entity) { ++seen; });
+    CHECK(seen == 3);
+    CHECK(m.Validate(r1) && m.Validate(r2) && m.Validate(r3));
+    CHECK(m.Count() == 3);
+  }
+  {
+    EntityManager m;  // :468-479 independent generations
+    const Entity e1 = m.Create(), e2 = m.Create(), e3 = m.Create();
+    (void)e1; (void)e3;
+    m.Destroy(e2);
+    const Entity e4 = m.Create();
+    CHECK(e4.index == e2.index);
+    CHECK(e4.generation != e2.generation);
+  }
+  {
+    EntityManager m;  // :502-516 interleaved
+    const Entity e1 = m.Create(), e2 = m.Create();
+    m.Destroy(e1);
+    const Entity e3 = m.Create();
+    m.Destroy(e2);
+    const Entity e4 = m.Create();
+    CHECK(m.Count() == 2);
+    CHECK(!m.Validate(e1) && !m.Validate(e2));
+    CHECK(m.Validate(e3) && m.Validate(e4));
+  }
+}
+
+// ---- component/archetype_id.cpp: sorted/dedup, With/Without, hash equality ------------------------------------------
+void TestArchetypeId() {
+  const ArchetypeId a({kVel, kPos}), b({kPos, kVel}), c({kPos, kVel, kPos});
+  CHECK(a == b);
+  CHECK(a.Hash() == b.Hash());
+  CHECK(c == a);                       // duplicates collapse
+  CHECK(std::is_sorted(a.Types().begin(), a.Types().end()));
+  CHECK(a.Contains(kPos) && a.Contains(kVel) && !a.Contains(kHealth));
+  const ArchetypeId w = a.With(kHealth);
+  CHECK(w.Types().size() == 3 && w.Contains(kHealth));
+  CHECK(w.Without(kHealth) == a);
+  CHECK(w.Without(kHealth).Hash() == a.Hash());
+  CHECK(a.With(kPos) == a);            // With of a present type is the identity
+  CHECK(a.Without(kHealth) == a);      // Without of an absent type is the identity
+  CHECK(ArchetypeId{}.Types().empty());
+  CHECK(ArchetypeId{}.Hash() == 0);
+  CHECK(ArchetypeId({kPos}).With(kVel) == ArchetypeId({kVel}).With(kPos));
+}
+
+// ---- component/archetype.cpp:105-227 AllocateRow/Add/Remove, :349-371 Row/EntityAt ---------------------------------
+void TestArchetype() {
+  {
+    Archetype a(ArchetypeId({kPos}));  // :105-139
+    a.InitColumn(0, sizeof(Position));
+    const uint32_t r1 = a.AllocateRow(Entity{1, 0}), r2 = a.AllocateRow(Entity{2, 0});
+    CHECK(r1 != Archetype::kInvalidRow);
+    CHECK(r1 != r2);
+    CHECK(a.EntityCount() == 2);
+    CHECK(a.EntityAt(r1) == (Entity{1, 0}));
+    CHECK(a.Row(Entity{2, 0}) == r2);
+  }
+  {
+    Archetype a{ArchetypeId{}};  // :214-227 Remove
+    a.AllocateRow(Entity{1, 0});
+    a.Remove(Entity{1, 0});
+    CHECK(a.EntityCount() == 0);
+    CHECK(a.Empty());
+  }
+  {
+    // swap-and-pop order (archetype.hpp:408-442): removing a middle row moves the LAST row into the hole.
+    Archetype a(ArchetypeId({kPos}));
+    a.InitColumn(0, sizeof(Position));
+    for (uint32_t i = 0; i < 4; ++i) {
+      a.AllocateRow(Entity{i, 1});
+      const Position p{float(i), float(10 * i)};
+      a.PushBack(0, &p);
+    }
+    const Entity swapped = a.Remove(Entity{1, 1});
+    CHECK(swapped == (Entity{3, 1}));
+    CHECK(a.EntityCount() == 3);
+    CHECK(a.EntityAt(0) == (Entity{0, 1}) && a.EntityAt(1) == (Entity{3, 1}) && a.EntityAt(2) == (Entity{2, 1}));
+    Position p;
+    std::memcpy(&p, &a.ColumnBytes(0)[sizeof(Position) * 1], sizeof(p));
+    CHECK(p.x == 3.0f && p.y == 30.0f);
+    CHECK(!a.Remove(Entity{2, 1}).Valid());  // removing the tail swaps nothing
+  }
+}
+
+// ---- component/manager.cpp:208-528 Init/Remove/Clear/Add/TryAdd/Remove/TryRemove, :1412-1637 -------------------------
+void TestComponentManager() {
+  const Entity e{1, 0};
+  {
+    ComponentManager m;  // :208-245
+    RegisterAll(m);
+    CHECK(!m.Tracked(e));
+    m.InitEntity(e);
+    CHECK(m.Tracked(e));
+    CHECK(m.Archetypes().size() == 1);  // the `{}` archetype is created by the first InitEntity
+    CHECK(m.EntityArchetype(e)->Id().Types().empty());  // :1415-1422
+    m.RemoveEntity(e);                   // :250-257
+    CHECK(!m.Tracked(e));
+    CHECK(!m.TryRemoveEntity(e));        // :292-297
+  }
+  {
+    ComponentManager m;  // :338-358 add + values
+    RegisterAll(m);
+    const Position pos{3.0f, 7.0f};
+    const Velocity vel{1.0f, 2.0f};
+    m.InitEntity(e);
+    const CompValue cv[] = {{kPos, &pos}, {kVel, &vel}};
+    m.Add(e, cv, 2);
+    CHECK(m.Has(e, kPos) && m.Has(e, kVel));
+    CHECK(GetAs<Position>(m, e, kPos).x == 3.0f && GetAs<Position>(m, e, kPos).y == 7.0f);
+    CHECK(GetAs<Velocity>(m, e, kVel).x == 1.0f && GetAs<Velocity>(m, e, kVel).y == 2.0f);
+    // :360-371 migrate further
+    const Health h{};
+    const Script s{};
+    const CompValue cv2[] = {{kHealth, &h}, {kScript, &s}};
+    m.Add(e, cv2, 2);
+    CHECK(m.Has(e, kPos) && m.Has(e, kVel) && m.Has(e, kHealth) && m.Has(e, kScript));
+    CHECK(GetAs<Position>(m, e, kPos).x == 3.0f);  // shared columns move with the entity
+    CHECK(GetAs<Health>(m, e, kHealth).points == 100);
+    // :373-384 replaced on repeated add
+    const Position p9{9.0f, 9.0f};
+    const Velocity v56{5.0f, 6.0f};
+    const CompValue cv3[] = {{kPos, &p9}, {kVel, &v56}};
+    const uint64_t version = m.StructuralVersion();
+    m.Add(e, cv3, 2);
+    CHECK(GetAs<Position>(m, e, kPos).x == 9.0f && GetAs<Velocity>(m, e, kVel).y == 6.0f);
+    CHECK(m.StructuralVersion() == version);  // :1536-1547 replacing does not bump the version
+  }
+  {
+    ComponentManager m;  // :866-876 existing replaced during migration (quirk #3)
+    RegisterAll(m);
+    m.InitEntity(e);
+    const Position p12{1.0f, 2.0f}, p56{5.0f, 6.0f};
+    const Velocity v78{7.0f, 8.0f};
+    const CompValue a1[] = {{kPos, &p12}};
+    m.Add(e, a1, 1);
+    const CompValue a2[] = {{kPos, &p56}, {kVel, &v78}};
+    m.Add(e, a2, 2);
+    CHECK(GetAs<Position>(m, e, kPos).x == 5.0f && GetAs<Position>(m, e, kPos).y == 6.0f);
+    CHECK(GetAs<Velocity>(m, e, kVel).x == 7.0f && GetAs<Velocity>(m, e, kVel).y == 8.0f);
+  }
+  {
+    ComponentManager m;  // :400-422 TryAdd
+    RegisterAll(m);
+    m.InitEntity(e);
+    const Position p1{1.0f, 1.0f}, p2{2.0f, 2.0f};
+    const CompValue a1[] = {{kPos, &p1}};
+    CHECK(m.TryAdd(e, a1, 1)[0] == true);
+    const CompValue a2[] = {{kPos, &p2}};
+    CHECK(m.TryAdd(e, a2, 1)[0] == false);
+    CHECK(GetAs<Position>(m, e, kPos).x == 1.0f);  // existing value untouched
+    // :748-775 mixed bools
+    const Velocity v{};
+    const CompValue a3[] = {{kPos, &p2}, {kVel, &v}};
+    const auto r = m.TryAdd(e, a3, 2);
+    CHECK(r[0] == false && r[1] == true);
+    CHECK(GetAs<Position>(m, e, kPos).x == 1.0f);
+  }
+  {
+    ComponentManager m;  // :474-527 Remove / TryRemove
+    RegisterAll(m);
+    m.InitEntity(e);
+    const Position p{4.0f, 5.0f};
+    const Velocity v{};
+    const Health h{77};
+    const CompValue a[] = {{kPos, &p}, {kVel, &v}, {kHealth, &h}};
+    m.Add(e, a, 3);
+    const TypeIndex rm[] = {kVel};
+    m.Remove(e, rm, 1);
+    CHECK(!m.Has(e, kVel));
+    CHECK(m.Has(e, kPos) && m.Has(e, kHealth));  // :485-498 others survive
+    CHECK(GetAs<Position>(m, e, kPos).y == 5.0f && GetAs<Health>(m, e, kHealth).points == 77);
+    const TypeIndex rm2[] = {kVel, kHealth};
+    const auto r = m.TryRemove(e, rm2, 2);  // :1034-1045 mixed presence
+    CHECK(r[0] == false && r[1] == true);
+    CHECK(!m.Has(e, kHealth));
+    // :302-333 Clear(entity)
+    m.Clear(e);
+    CHECK(m.Tracked(e));
+    CHECK(!m.Has(e, kPos));
+    CHECK(m.EntityArchetype(e)->Id().Types().empty());
+  }
+  {
+    ComponentManager m;  // :1457-1505 Archetypes, :1507-1534 StructuralVersion
+    RegisterAll(m);
+    CHECK(m.StructuralVersion() == 0);
+    const Entity e1{1, 0}, e2{2, 0};
+    m.InitEntity(e1);
+    m.InitEntity(e2);
+    const uint64_t v0 = m.StructuralVersion();
+    CHECK(v0 > 0);  // the `{}` archetype was created
+    const Position p{};
+    const CompValue a[] = {{kPos, &p}};
+    m.Add(e1, a, 1);
+    CHECK(m.StructuralVersion() > v0);
+    const size_t n = m.Archetypes().size();
+    m.Add(e2, a, 1);
+    CHECK(m.Archetypes().size() == n);  // :1478-1489 same archetype reused
+    CHECK(m.EntityArchetype(e1) == m.EntityArchetype(e2));
+    // :1608-1620 removing one entity does not affect another
+    m.RemoveEntity(e1);
+    CHECK(m.Tracked(e2) && m.Has(e2, kPos));
+  }
+}
+
+// ---- query/query.cpp:114-260 Empty/Count, :1035-1123 without/read-only, :1783-2208 With/Without/combined ---------------
+void TestQuery() {
+  World w;
+  RegisterAll(w.components);
+  auto spawn = [&](bool pos, bool vel, bool health) {
+    const Entity e = w.CreateEntity();
+    std::vector<CompValue> cv;
+    static const Position p{1, 2};
+    static const Velocity v{3, 4};
+    static const Health h{50};
+    if (pos) cv.push_back({kPos, &p});
+    if (vel) cv.push_back({kVel, &v});
+    if (health) cv.push_back({kHealth, &h});
+    if (!cv.empty()) w.AddComponents(e, cv.data(), cv.size());
+    return e;
+  };
+  QueryDesc q_pos{{kPos}, {0}, {}, {}};
+  CHECK(QueryCount(w.components, q_pos) == 0);  // :114-131 empty world
+  const Entity e1 = spawn(true, false, false);
+  const Entity e2 = spawn(true, true, false);
+  const Entity e3 = spawn(true, true, true);
+  const Entity e4 = spawn(false, true, false);
+  (void)e4;
+  CHECK(QueryCount(w.components, q_pos) == 3);  // :133-170
+  QueryDesc q_pv{{kPos, kVel}, {1, 0}, {}, {}};
+  CHECK(QueryCount(w.components, q_pv) == 2);
+  QueryDesc q_with{{kPos}, {0}, {kHealth}, {}};           // :1783-1850 With
+  CHECK(QueryCount(w.components, q_with) == 1);
+  QueryDesc q_without{{kPos}, {0}, {}, {kVel}};           // :1035-1080, :1900-1990 Without
+  CHECK(QueryCount(w.components, q_without) == 1);
+  QueryDesc q_comb{{kPos}, {0}, {kVel}, {kHealth}};       // :2109-2125 combined
+  CHECK(QueryCount(w.components, q_comb) == 1);
+  // ForEach visits archetypes in creation order, rows in storage order (query.hpp:1404-1438)
+  std::vector<Entity> seen;
+  ForEach(w.components, q_pos, [&](Entity e, uint8_t**) { seen.push_back(e); });
+  CHECK(seen.size() == 3 && seen[0] == e1 && seen[1] == e2 && seen[2] == e3);
+  // :645-660 (schedule.cpp) write query modifies components
+  ForEach(w.components, q_pv, [&](Entity, uint8_t** c) {
+    auto* p = reinterpret_cast<Position*>(c[0]);
+    const auto* v = reinterpret_cast<const Velocity*>(c[1]);
+    p->x += v->x;
+    p->y += v->y;
+  });
+  CHECK(GetAs<Position>(w.components, e2, kPos).x == 4.0f && GetAs<Position>(w.components, e2, kPos).y == 6.0f);
+  CHECK(GetAs<Position>(w.components, e1, kPos).x == 1.0f);
+  // :1217-1242 dynamic refresh — a query sees entities created after its first use
+  spawn(true, false, false);
+  CHECK(QueryCount(w.components, q_pos) == 4);
+  // quirk #9: an unregistered required type matches nothing; an unregistered Without passes
+  QueryDesc q_unreg{{Fnv1a("Nope")}, {0}, {}, {}};
+  CHECK(QueryCount(w.components, q_unreg) == 0);
+  QueryDesc q_unreg_wo{{kPos}, {0}, {}, {Fnv1a("Nope")}};
+  CHECK(QueryCount(w.components, q_unreg_wo) == 4);
+  // FaithfulIndex (B-ref access path) returns the same bytes as the direct path
+  FaithfulIndex fi(w.components);
+  std::vector<Entity> seen2;
+  fi.ForEach(q_pos, [&](Entity e, uint8_t** c) {
+    seen2.push_back(e);
+    CHECK(c[0] == w.components.Get(e, kPos));
+  });
+  CHECK(seen2.size() == 4);
+}
+
+// ---- command/queue.cpp (FIFO, Merge order), builtin_commands.cpp, schedule.cpp:946-1006 ----------------------------------
+void TestCommands() {
+  {
+    World w;  // builtin_commands.cpp: Destroy / TryDestroy / Add / Remove / Clear through the queue
+    RegisterAll(w.components);
+    const Entity a = w.CreateEntity(), b = w.CreateEntity();
+    const Position p{1, 2};
+    Command add{CmdKind::kAdd, a, {kPos}, {{reinterpret_cast<const uint8_t*>(&p), reinterpret_cast<const uint8_t*>(&p) + sizeof(p)}}};
+    w.command_queue.Enqueue(add);
+    w.command_queue.Enqueue(Command{CmdKind::kDestroy, b, {}, {}});
+    CHECK(w.command_queue.Size() == 2);
+    CHECK(!w.HasComponent(a, kPos));  // deferred: nothing visible before Flush
+    w.Flush();
+    CHECK(w.command_queue.Empty());
+    CHECK(w.HasComponent(a, kPos));
+    CHECK(!w.entities.Validate(b));
+    CHECK(w.EntityCount() == 1);
+    w.command_queue.Enqueue(Command{CmdKind::kTryDestroy, b, {}, {}});  // stale entity: silently skipped
+    w.command_queue.Enqueue(Command{CmdKind::kRemove, a, {kPos}, {}});
+    w.Flush();
+    CHECK(w.invalid_command_count == 0);
+    CHECK(!w.HasComponent(a, kPos));
+    w.command_queue.Enqueue(add);
+    w.command_queue.Enqueue(Command{CmdKind::kClearComponents, a, {}, {}});
+    w.Flush();
+    CHECK(!w.HasComponent(a, kPos) && w.entities.Validate(a));
+  }
+  {
+    // command/queue.cpp Merge: other's commands run after ours, FIFO inside each (queue.hpp:146-163).  Observable
+    // through order-dependent effects: Add(x=1) then Add(x=2) leaves 2; the reverse leaves 1.
+    World w;
+    RegisterAll(w.components);
+    const Entity e = w.CreateEntity();
+    auto add_pos = [&](float x) {
+      const Position p{x, 0};
+      return Command{CmdKind::kAdd, e, {kPos}, {{reinterpret_cast<const uint8_t*>(&p), reinterpret_cast<const uint8_t*>(&p) + sizeof(p)}}};
+    };
+    CmdQueue q1, q2;
+    q1.Enqueue(add_pos(1));
+    q2.Enqueue(add_pos(2));
+    q2.Enqueue(add_pos(3));
+    q1.Merge(q2);
+    CHECK(q1.Size() == 3 && q2.Empty());
+    q1.ExecuteAll(w);
+    CHECK(GetAs<Position>(w.components, e, kPos).x == 3.0f);
+  }
+  {
+    // schedule.cpp:975-1006 Spawn().AddComponents(...) — reserved id {next_index, 1}, valid only after the flush.
+    World w;
+    RegisterAll(w.components);
+    Schedule s;
+    Entity spawned;
+    s.Add("SpawnEnemy", [&](World& world, SystemLocalData& local) {
+      spawned = world.ReserveEntity();
+      const Health h{5};
+      local.cmd_queue.Enqueue(Command{CmdKind::kAdd, spawned, {kHealth},
+                                      {{reinterpret_cast<const uint8_t*>(&h), reinterpret_cast<const uint8_t*>(&h) + sizeof(h)}}});
+    }, {});
+    CHECK(s.Build());
+    CHECK(w.EntityCount() == 0);
+    s.RunAndWait(w);
+    CHECK(w.EntityCount() == 1);
+    CHECK(spawned.index == 0 && spawned.generation == 1);
+    CHECK(w.HasComponent(spawned, kHealth));
+    CHECK(GetAs<Health>(w.components, spawned, kHealth).points == 5);
+    // :961-973 two systems each spawning once
+    World w2;
+    RegisterAll(w2.components);
+    Schedule s2;
+    auto spawn_one = [](World& world, SystemLocalData&) { world.ReserveEntity(); };
+    s2.Add("A", spawn_one, {});
+    s2.Add("B", spawn_one, {});
+    CHECK(s2.Build());
+    s2.RunAndWait(w2);
+    CHECK(w2.EntityCount() == 2);
+  }
+}
+
+// ---- message/manager.cpp:148-213 Update, :595-645 MergeLocal, :753-796 Previous/Current; reader.cpp order ----------------
+void TestMessages() {
+  const TypeIndex kMsg = Fnv1a("PositionMsg"), kManual = Fnv1a("ManualMessage"), kOther = Fnv1a("VelocityMsg");
+  {
+    MessageManager m;  // :149-162
+    m.Register(kMsg, sizeof(Position));
+    const Position p{1.0f, 2.0f};
+    m.Write(kMsg, &p);
+    CHECK(m.Current().Count(kMsg) == 1);  // :776-785
+    CHECK(m.Previous().Count(kMsg) == 0); // :754-760
+    m.Update();
+    CHECK(m.Previous().Count(kMsg) == 1);
+    CHECK(m.Current().Count(kMsg) == 0);  // :190-199, :787-796
+    Position out;
+    std::memcpy(&out, m.Previous().Bytes(kMsg)->data(), sizeof(out));
+    CHECK(out.x == 1.0f && out.y == 2.0f);
+    m.Update();  // :164-175 automatic policy: gone after two updates
+    CHECK(m.Previous().Count(kMsg) == 0 && m.Current().Count(kMsg) == 0);
+  }
+  {
+    MessageManager m;  // :177-188 manual policy survives
+    m.Register(kManual, 4, ClearPolicy::kManual);
+    const int v = 42;
+    m.Write(kManual, &v);
+    m.Update();
+    m.Update();
+    CHECK(m.Previous().Count(kManual) == 1);
+    int out = 0;
+    std::memcpy(&out, m.Previous().Bytes(kManual)->data(), 4);
+    CHECK(out == 42);
+  }
+  {
+    MessageManager m;  // :201-213 independent types
+    m.Register(kMsg, 8);
+    m.Register(kOther, 8);
+    const Position p{};
+    m.Write(kMsg, &p);
+    m.Write(kOther, &p);
+    m.Update();
+    CHECK(m.Previous().Count(kMsg) == 1 && m.Previous().Count(kOther) == 1);
+  }
+  {
+    MessageManager m;  // :596-645 MergeLocalMessages appends after what current already holds, order kept
+    m.Register(kMsg, 4);
+    const int a = 1, b = 2, c = 3;
+    m.Write(kMsg, &a);
+    MessageQueue local;
+    local.Register(kMsg, 4);
+    local.Enqueue(kMsg, &b);
+    local.Enqueue(kMsg, &c);
+    m.MergeLocal(local);
+    CHECK(m.Current().Count(kMsg) == 3);
+    CHECK(local.Count(kMsg) == 0);
+    const auto all = m.ReadAll(kMsg);
+    int v[3];
+    std::memcpy(v, all.data(), 12);
+    CHECK(v[0] == 1 && v[1] == 2 && v[2] == 3);
+    // reader order = previous ++ current (reader.hpp:793-795)
+    m.Update();
+    const int d = 4;
+    m.Write(kMsg, &d);
+    const auto all2 = m.ReadAll(kMsg);
+    int u[4];
+    std::memcpy(u, all2.data(), 16);
+    CHECK(all2.size() == 16 && u[0] == 1 && u[3] == 4);
+  }
+  {
+    // schedule.cpp:1009-1047 system-local messages: in world.current after RunAndWait; readable after world.Update
+    World w;
+    w.messages.Register(kMsg, 4);
+    Schedule s;
+    s.Add("Writer", [&](World&, SystemLocalData& local) {
+      local.message_queue.Register(kMsg, 4);
+      const int v = 99;
+      local.message_queue.Enqueue(kMsg, &v);
+    }, {});
+    CHECK(s.Build());
+    s.RunAndWait(w);
+    CHECK(w.messages.Current().Count(kMsg) == 1);
+    w.Update();
+    const auto all = w.messages.ReadAll(kMsg);
+    int v = 0;
+    std::memcpy(&v, all.data(), 4);
+    CHECK(all.size() == 4 && v == 99);
+    // quirk #12: a second system entry's merge pushes world-current into world-previous
+    World w2;
+    w2.messages.Register(kMsg, 4);
+    Schedule s2;
+    s2.Add("Writer", [&](World&, SystemLocalData& local) {
+      local.message_queue.Register(kMsg, 4);
+      const int x = 7;
+      local.message_queue.Enqueue(kMsg, &x);
+    }, {});
+    s2.Add("Idle", [](World&, SystemLocalData&) {}, {});
+    CHECK(s2.Build());
+    s2.RunAndWait(w2);
+    CHECK(w2.messages.Previous().Count(kMsg) == 1 && w2.messages.Current().Count(kMsg) == 0);
+  }
+}
+
+// ---- schedule/dag.cpp:111-193 Sort; system/access_policy.cpp ConflictsWith; schedule.cpp:507-557,597-707,820-829 ---------
+void TestScheduling() {
+  {
+    Dag d;  // dag.cpp:131-148 linear chain
+    const size_t a = d.AddNode(), b = d.AddNode(), c = d.AddNode();
+    CHECK(a == 0 && b == 1 && c == 2);  // :46-56 increasing indices
+    CHECK(d.AddEdge(a, b) && d.AddEdge(b, c));
+    CHECK(!d.AddEdge(a, a));            // :80-88 self loop
+    CHECK(!d.AddEdge(a, 7));            // :100-109 unknown node
+    std::vector<size_t> order;
+    CHECK(d.Sort(order));
+    CHECK(order == (std::vector<size_t>{0, 1, 2}));
+  }
+  {
+    Dag d;  // :150-174 diamond
+    for (int i = 0; i < 4; ++i) d.AddNode();
+    d.AddEdge(0, 1); d.AddEdge(0, 2); d.AddEdge(1, 3); d.AddEdge(2, 3);
+    std::vector<size_t> order;
+    CHECK(d.Sort(order));
+    CHECK(order.size() == 4 && order.front() == 0 && order.back() == 3);
+    CHECK(order[1] == 1 && order[2] == 2);  // insertion-index tie-break (dag.cpp:65-126)
+  }
+  {
+    Dag d;  // :176-193 cycle
+    for (int i = 0; i < 3; ++i) d.AddNode();
+    d.AddEdge(0, 1); d.AddEdge(1, 2); d.AddEdge(2, 0);
+    std::vector<size_t> order;
+    CHECK(!d.Sort(order));
+  }
+  {
+    std::vector<size_t> order;
+    CHECK(Dag{}.Sort(order) && order.empty());  // :112-118
+  }
+  {
+    // access_policy.cpp: read/read never conflicts; write/read, write/write do; resources likewise; disjoint sets do not.
+    AccessPolicy r1, r2, w1, w2, res_r, res_w, other;
+    r1.AddQuery(QueryDesc{{kPos}, {0}, {}, {}});
+    r2.AddQuery(QueryDesc{{kPos, kVel}, {0, 0}, {}, {}});
+    w1.AddQuery(QueryDesc{{kPos}, {1}, {}, {}});
+    w2.AddQuery(QueryDesc{{kPos, kVel}, {1, 0}, {}, {}});
+    other.AddQuery(QueryDesc{{kHealth}, {1}, {}, {}});
+    CHECK(!r1.ConflictsWith(r2));
+    CHECK(w1.ConflictsWith(r1) && r1.ConflictsWith(w1));
+    CHECK(w1.ConflictsWith(w2));
+    CHECK(!w1.ConflictsWith(other));
+    CHECK(!AccessPolicy{}.ConflictsWith(w1));  // Commands / MessageWriter / MessageReader add nothing (schedule.cpp:820-829)
+    AccessPolicy::InsertSorted(res_r.read_resources, Fnv1a("Counter"));
+    AccessPolicy::InsertSorted(res_w.write_resources, Fnv1a("Counter"));
+    CHECK(res_r.ConflictsWith(res_w) && res_w.ConflictsWith(res_w));
+    CHECK(!res_r.ConflictsWith(res_r));  // schedule.cpp:598-609
+    // With/Without disjointness is ignored: component sets only (quirk #11)
+    AccessPolicy wa, wb;
+    wa.AddQuery(QueryDesc{{kPos}, {1}, {kHealth}, {}});
+    wb.AddQuery(QueryDesc{{kPos}, {1}, {}, {kHealth}});
+    CHECK(wa.ConflictsWith(wb));
+  }
+  {
+    // schedule.cpp:508-557 Before/After enforce execution order
+    std::vector<int> log;
+    Schedule s;
+    const size_t a = s.Add("A", [&](World&, SystemLocalData&) { log.push_back(0); }, {});
+    const size_t b = s.Add("B", [&](World&, SystemLocalData&) { log.push_back(1); }, {});
+    s.Order(b, a);  // B before A
+    CHECK(s.Build());
+    World w;
+    s.RunAndWait(w);
+    CHECK(log == (std::vector<int>{1, 0}));
+    CHECK(s.ExecutionOrder() == (std::vector<size_t>{1, 0}));
+    Schedule cyc;
+    const size_t x = cyc.Add("X", [](World&, SystemLocalData&) {}, {});
+    const size_t y = cyc.Add("Y", [](World&, SystemLocalData&) {}, {});
+    cyc.Order(x, y);
+    cyc.Order(y, x);
+    CHECK(!cyc.Build());
+  }
+  {
+    // conflict bitmask is indexed by POSITION in the execution order (schedule.cpp:371-395)
+    AccessPolicy wp, rp, wh;
+    wp.AddQuery(QueryDesc{{kPos}, {1}, {}, {}});
+    rp.AddQuery(QueryDesc{{kPos}, {0}, {}, {}});
+    wh.AddQuery(QueryDesc{{kHealth}, {1}, {}, {}});
+    Schedule s;
+    s.Add("WritePos", [](World&, SystemLocalData&) {}, wp);
+    s.Add("WriteHealth", [](World&, SystemLocalData&) {}, wh);
+    s.Add("ReadPos", [](World&, SystemLocalData&) {}, rp);
+    CHECK(s.Build());
+    CHECK(s.ConflictMask()[0] == 0b100 && s.ConflictMask()[1] == 0 && s.ConflictMask()[2] == 0b001);
+  }
+}
+
+// ---- world.cpp + schedule.cpp:267-288 — deferred application order across the global queue and system queues -------------
+void TestApplyOrder() {
+  // schedule.cpp:106-115: world.Flush() (reserved entities, then the global queue) precedes every system-local queue, and
+  // system queues run in REGISTRATION order even when the execution order differs.
+  World w;
+  RegisterAll(w.components);
+  const Entity e = w.CreateEntity();
+  auto add_pos = [&](float x) {
+    const Position p{x, 0};
+    return Command{CmdKind::kAdd, e, {kPos}, {{reinterpret_cast<const uint8_t*>(&p), reinterpret_cast<const uint8_t*>(&p) + sizeof(p)}}};
+  };
+  Schedule s;
+  const size_t a = s.Add("A", [&](World&, SystemLocalData& l) { l.cmd_queue.Enqueue(add_pos(10)); }, {});
+  const size_t b = s.Add("B", [&](World&, SystemLocalData& l) { l.cmd_queue.Enqueue(add_pos(20)); }, {});
+  s.Order(b, a);  // B executes first, but A's queue is still applied first
+  CHECK(s.Build());
+  w.command_queue.Enqueue(add_pos(30));  // global queue: applied before both
+  s.RunAndWait(w);
+  CHECK(GetAs<Position>(w.components, e, kPos).x == 20.0f);
+}
+
+}  // namespace
+
+int main() {
+  TestFnv();
+  TestEntityManager();
+  TestArchetypeId();
+  TestArchetype();
+  TestComponentManager();
+  TestQuery();
+  TestCommands();
+  TestMessages();
+  TestScheduling();
+  TestApplyOrder();
+  std::printf("oracle KATs: %d checks, %d failed\n", g_checks, g_fail);
+  return g_fail;
+}

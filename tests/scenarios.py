@@ -1,0 +1,155 @@
+"""Seeded parity scenarios shared by the golden-fixture generator, the CPU tests (oracle) and the GPU tests.
+
+Every scenario builds a world on the given backend, drives it through the C ABI and returns a dict of SHA-256 digests of
+the canonical world snapshot (archetype order, type lists, entity rows, raw column bytes, generation table, free list) plus
+whatever else the scenario observes (match sets, message buffers, schedule resources).  Identical digests == bit-exact
+parity; tests/golden/golden.json holds the digests the oracle produced when the fixtures were generated."""
+import hashlib
+import struct
+
+import numpy as np
+
+from heliosengine_b200 import capi, worlds
+
+
+def snapshot_digest(snap: dict) -> str:
+    h = hashlib.sha256()
+    h.update(struct.pack("<IIqQ", len(snap["archetypes"]), snap["next_index"], snap["free_cursor"], snap["entity_count"]))
+    for a in snap["archetypes"]:
+        h.update(struct.pack("<II", len(a["types"]), a["entities"].size))
+        h.update(np.asarray(a["types"], dtype=np.uint64).tobytes())
+        h.update(np.ascontiguousarray(a["entities"]).tobytes())
+        for t in a["types"]:
+            h.update(np.ascontiguousarray(a["columns"][t]).tobytes())
+    h.update(np.ascontiguousarray(snap["generations"]).tobytes())
+    h.update(np.ascontiguousarray(snap["free_indices"]).tobytes())
+    return h.hexdigest()
+
+
+def _bytes_digest(*arrays) -> str:
+    h = hashlib.sha256()
+    for a in arrays:
+        h.update(np.ascontiguousarray(a).tobytes())
+    return h.hexdigest()
+
+
+def cfg1(backend, n=4099, frames=3, mode=capi.EXEC_SERIAL):
+    w = capi.World(backend)
+    s, q = worlds.build_cfg1(w, n)
+    out = {"count": q.count(), "match": q.match()}
+    for _ in range(frames):
+        s.run_and_wait(mode)
+    out["world"] = snapshot_digest(w.snapshot())
+    w.close()
+    return out
+
+
+def cfg2(backend, n=64 * 1500, filtered=True, frames=3, mode=capi.EXEC_SERIAL, flags=0):
+    w = capi.World(backend)
+    s, q = worlds.build_cfg2(w, n, filtered=filtered, flags=flags)
+    out = {"count": q.count(), "match": q.match()}
+    for _ in range(frames):
+        s.run_and_wait(mode)
+    out["world"] = snapshot_digest(w.snapshot())
+    w.close()
+    return out
+
+
+def cfg3(backend, n=16 * 2048, frac=0.10, frames=2):
+    """Structural churn.  Targets are drawn from the backend's own live lists — identical on both sides as long as parity
+    holds, so a divergence in frame k shows up in frame k's digest."""
+    w = capi.World(backend)
+    worlds.build_cfg3(w, n)
+    out = {}
+    for frame in range(frames):
+        snap = w.snapshot(columns=False)
+        ents = [a["entities"] for a in snap["archetypes"]]
+        types = [a["types"] for a in snap["archetypes"]]
+        despawn, insert, remove, n_spawn = worlds.cfg3_commands(w, ents, types, frame, int(n * frac))
+        spawned = w.reserve_entities(n_spawn)
+        cmds, payload = worlds.assemble_cfg3(w, spawned, despawn, insert, remove, frame)
+        w.enqueue(cmds, payload)
+        w.flush()
+        out[f"frame{frame}"] = snapshot_digest(w.snapshot())
+    w.close()
+    return out
+
+
+def cfg4(backend, n=8192, frames=3, mode=capi.EXEC_SERIAL):
+    """8-system schedule + CollisionEvent channel: RunAndWait + World::Update per frame."""
+    w = capi.World(backend)
+    s = worlds.build_cfg4(w, n)
+    out = {"order": s.execution_order(), "conflicts": s.conflicts()}
+    for frame in range(frames):
+        s.run_and_wait(mode)
+        prev_n, cur_n = w.message_counts(worlds.COLLISION_EVENT)
+        out[f"frame{frame}_counts_after_run"] = [prev_n, cur_n]
+        out[f"frame{frame}_messages_after_run"] = _bytes_digest(w.message_read(worlds.COLLISION_EVENT, 0),
+                                                                  w.message_read(worlds.COLLISION_EVENT, 1))
+        w.update()
+        out[f"frame{frame}_counts_after_update"] = list(w.message_counts(worlds.COLLISION_EVENT))
+        out[f"frame{frame}_resources"] = s.read_resources(16).tobytes().hex()
+    out["world"] = snapshot_digest(w.snapshot())
+    w.close()
+    return out
+
+
+def churn_small(backend, seed=3, frames=4):
+    """Many commands per entity on tiny tables: long swap-and-pop chains, tables emptied and refilled, new archetypes,
+    stale ids, Try-variants and Clear."""
+    shorts = ["Position", "Velocity", "Health", "Team", "Damping"]
+    w = capi.World(backend)
+    worlds.register_all(w, shorts)
+    tables = [(["Position", "Velocity"], 7), (["Position", "Velocity", "Health"], 5), (["Position"], 3), (["Health", "Team"], 6)]
+    for i, (sh, rows) in enumerate(tables):
+        w.spawn_batch([worlds.cname(x) for x in sh], rows, [worlds.column(x, rows, 40 + 8 * i + k, seed=seed) for k, x in enumerate(sh)])
+    out = {}
+    stale = []
+    for f in range(frames):
+        rng = np.random.default_rng(seed * 100 + f)
+        snap = w.snapshot(columns=False)
+        live = np.concatenate([a["entities"] for a in snap["archetypes"]])
+        n_cmd = 60
+        spawned = w.reserve_entities(6)
+        pool = np.concatenate([live, spawned, np.asarray(stale, dtype=np.uint64)])
+        cmds = np.zeros(n_cmd, dtype=capi.COMMAND_DTYPE)
+        payload = bytearray()
+        try_kinds = {capi.CMD_ADD: capi.CMD_TRY_ADD, capi.CMD_REMOVE: capi.CMD_TRY_REMOVE, capi.CMD_DESTROY: capi.CMD_TRY_DESTROY}
+        for i in range(n_cmd):
+            ent = int(pool[rng.integers(0, pool.size)])
+            kind = int(rng.choice([capi.CMD_ADD, capi.CMD_REMOVE, capi.CMD_DESTROY, capi.CMD_CLEAR, capi.CMD_ADD, capi.CMD_REMOVE]))
+            if kind != capi.CMD_CLEAR:
+                kind = try_kinds[kind]  # every record tolerates dead targets (the reference asserts on the non-Try forms)
+            k = int(rng.integers(1, 3))
+            sh = list(rng.choice(shorts, size=k, replace=False)) if kind in (capi.CMD_TRY_ADD, capi.CMD_TRY_REMOVE) else []
+            cmds[i]["kind"] = kind
+            cmds[i]["entity"] = ent
+            cmds[i]["component_mask"] = w.mask(worlds.cname(x) for x in sh)
+            cmds[i]["payload_offset"] = len(payload)
+            if kind == capi.CMD_TRY_ADD:
+                for x in sorted(sh, key=lambda y: w.slots[worlds.cname(y)]):
+                    payload += rng.integers(1, 2 ** 31 - 1, size=worlds.COMPONENTS[x][0] // 4, dtype=np.uint32).tobytes()
+            if kind == capi.CMD_TRY_DESTROY:
+                stale.append(ent)
+        # Clear on a dead entity is an assert in the reference: retarget those records at live entities
+        dead = set(stale)
+        for i in range(n_cmd):
+            if cmds[i]["kind"] == capi.CMD_CLEAR and (int(cmds[i]["entity"]) in dead):
+                cmds[i]["kind"] = capi.CMD_TRY_REMOVE
+        w.enqueue(cmds, bytes(payload))
+        w.flush()
+        out[f"frame{f}"] = snapshot_digest(w.snapshot())
+    w.close()
+    return out
+
+
+SCENARIOS = {
+    "cfg1_n4099": lambda b: cfg1(b),
+    "cfg1_n1": lambda b: cfg1(b, n=1),
+    "cfg2_filtered": lambda b: cfg2(b, filtered=True),
+    "cfg2_all": lambda b: cfg2(b, filtered=False),
+    "cfg3_churn": lambda b: cfg3(b),
+    "cfg4_schedule_messages": lambda b: cfg4(b),
+    "churn_small_s3": lambda b: churn_small(b, seed=3),
+    "churn_small_s11": lambda b: churn_small(b, seed=11),
+}

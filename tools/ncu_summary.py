@@ -1,0 +1,52 @@
+#!/usr/bin/env python
+"""Summarise ncu output brought back in gpurun_out/ into small text files under profiles/.
+
+  python tools/ncu_summary.py launches <launches.csv> <out.md>     per-kernel launch count / total / average / share
+  python tools/ncu_summary.py raw <report.ncu-rep> <out.md>        key roofline metrics of every captured launch
+"""
+import csv
+import subprocess
+import sys
+from collections import defaultdict
+
+KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__t_sector_hit_rate.pct", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "launch__grid_size",
+        "launch__block_size", "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
+        "smsp__warp_issue_stalled_long_scoreboard_per_warp_active.pct", "l1tex__t_sector_hit_rate.pct"]
+
+
+def launches(path, out):
+    rows = list(csv.reader(l for l in open(path) if not l.startswith("==")))
+    hdr, rows = rows[0], rows[1:]
+    ki, vi = hdr.index("Kernel Name"), hdr.index("Metric Value")
+    d = defaultdict(list)
+    for r in rows:
+        if len(r) > vi:
+            d[r[ki]].append(float(r[vi].replace(",", "")))
+    total = sum(sum(v) for v in d.values())
+    with open(out, "w") as f:
+        f.write(f"# ncu launch list summary of `{path}` (gpu__time_duration.sum, --clock-control none; cold-cache, serialised)\n\n")
+        f.write("| launches | total us | avg us | share | kernel |\n|---:|---:|---:|---:|---|\n")
+        for k, v in sorted(d.items(), key=lambda x: -sum(x[1])):
+            f.write(f"| {len(v)} | {sum(v) / 1e3:.1f} | {sum(v) / len(v) / 1e3:.2f} | {100 * sum(v) / total:.1f}% | `{k[:140]}` |\n")
+
+
+def raw(path, out):
+    txt = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(txt.splitlines()))
+    hdr, units, rows = rows[0], rows[1], rows[2:]
+    ki = hdr.index("Kernel Name")
+    with open(out, "w") as f:
+        f.write(f"# ncu --set full summary of `{path}`\n\n")
+        for r in rows:
+            f.write(f"## `{r[ki][:160]}`\n\n| metric | value | unit |\n|---|---:|---|\n")
+            for k in KEYS:
+                if k in hdr:
+                    f.write(f"| {k} | {r[hdr.index(k)]} | {units[hdr.index(k)]} |\n")
+            f.write("\n")
+
+
+if __name__ == "__main__":
+    {"launches": launches, "raw": raw}[sys.argv[1]](sys.argv[2], sys.argv[3])
