@@ -155,11 +155,11 @@ def run_b200(args):
     # in L2 are clean — otherwise the timed kernel is charged the write-back of the flush's own dirty lines.
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     flush_rd = torch.zeros(256 << 20, dtype=torch.uint8, device=dev)
-    flush_sink = torch.zeros(1, dtype=torch.int64, device=dev)
+    flush_sink = torch.zeros((), dtype=torch.int64, device=dev)
 
     def l2_flush():
         flush.fill_(1)
-        torch.sum(flush_rd, dtype=torch.int64, out=flush_sink)
+        torch.sum(flush_rd, dim=(0,), dtype=torch.int64, out=flush_sink)
 
     def barrier():
         torch.cuda.synchronize()
