@@ -36,7 +36,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--entities", type=int, default=N_ENTITIES)
+    ap.add_argument("--entities", type=int, default=0, help="entities per GPU (default: the config's BASELINE size)")
+    ap.add_argument("--config", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4"],
+                    help="cfg2 (default) is the headline workload; the others are secondary legs (bench_configs.py)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--all-tables", action="store_true", help="drop the With/Without filters (cfg 2-all)")
     return ap.parse_args()
@@ -126,10 +128,30 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def run_secondary(args):
+    """cfg1 / cfg3 / cfg4 legs (single GPU): same JSON-line shape, workload named in config."""
+    import torch
+    from heliosengine_b200 import bench_configs
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    stream = torch.cuda.Stream(device=dev)
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    line = getattr(bench_configs, "run_" + args.config)(args, torch, dev, stream, peaks())
+    line.update({"n_gpus": 1, "steps": args.steps, "warmup": max(3, args.warmup), "higher_is_better": True, "scaling": "weak",
+                 "vs_baseline": None, "data": "synthetic", "clocks": clocks.stop()})
+    print(json.dumps(line))
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
     from heliosengine_b200 import capi, worlds
+
+    args.entities = args.entities or N_ENTITIES
 
     rank = int(os.environ.get("RANK", "0"))
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
@@ -268,5 +290,7 @@ if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.config != "cfg2":
+        run_secondary(a)
     else:
         run_b200(a)

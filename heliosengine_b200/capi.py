@@ -281,6 +281,10 @@ class World:
         pay = np.frombuffer(payload, dtype=np.uint8) if isinstance(payload, (bytes, bytearray)) else np.ascontiguousarray(payload).view(np.uint8)
         self._check(self.b.fn("commands_enqueue")(self.h, _ptr(cmds), C.c_uint64(cmds.size), _ptr(pay) if pay.size else None, C.c_uint64(pay.size)))
 
+    def stage_commands(self):
+        if self.b.is_gpu:
+            self._check(self.b.fn("commands_stage")(self.h))
+
     def flush(self):
         self._check(self.b.fn("world_flush")(self.h))
 

@@ -46,6 +46,8 @@ struct Counters {
   uint32_t n_changed;
   uint32_t n_destroy;
   uint32_t effective;
+  uint32_t dups;           // commands whose entity has an earlier command in the same batch
+  uint32_t ticket;         // dynamic block index of the single-launch resolver
   unsigned long long moved_bytes;
 };
 
@@ -119,6 +121,10 @@ struct helios_gpu_world::ApplyScratch {
   uint32_t mh_log2 = 0;
   size_t mh_tables = ~size_t(0);
   DevBuf tdelta, tfmin, tseg, tcount0;
+  DevBuf trem, tapp, ic_off, init_close;   // per-table remove/append op counts; init-slot close lookup
+  DevBuf ent_first;                        // uint32[ent_capacity]: first command index per entity (kNone when idle)
+  uint32_t ent_first_cap = 0;
+  bool ent_first_dirty = false;
   DevBuf unknown;
   DevBuf u_table, u_kind, u_cmd;
   DevBuf op_table, op_kind, op_cmd, op_level, u2t, delta, ex;
@@ -152,6 +158,35 @@ __global__ void k_compact(const helios_gpu_command* __restrict__ cmds, uint64_t 
     skey[k] = ent_index(c.entity);  // sort key: entity index (stable sort keeps command order inside an entity)
     sval[k] = k;
   }
+}
+
+// Dense queues (host-enqueued: every record valid) skip the compaction.  Identity order + duplicate detection: when no
+// entity is targeted twice in the batch (the common case) every command is its own chain and the stable sort by entity
+// is not needed at all.  ent_first[idx] = smallest command index targeting entity idx (kNone when idle).
+__global__ void k_mark_first(const helios_gpu_command* __restrict__ cmds, uint32_t K, uint32_t ent_capacity,
+                             uint32_t* __restrict__ ent_first, uint64_t* __restrict__ skey, uint32_t* __restrict__ sval) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K) return;
+  const uint32_t idx = ent_index(cmds[k].entity);
+  skey[k] = idx;
+  sval[k] = k;
+  if (idx < ent_capacity) atomicMin(&ent_first[idx], k);
+}
+
+__global__ void k_count_dups(const helios_gpu_command* __restrict__ cmds, uint32_t K, uint32_t ent_capacity,
+                             const uint32_t* __restrict__ ent_first, Counters* counters) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K) return;
+  const uint32_t idx = ent_index(cmds[k].entity);
+  if (idx < ent_capacity && ent_first[idx] != k) atomicAdd(&counters->dups, 1u);  // rare by construction
+}
+
+__global__ void k_reset_first(const helios_gpu_command* __restrict__ cmds, uint32_t K, uint32_t ent_capacity,
+                              uint32_t* __restrict__ ent_first) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K) return;
+  const uint32_t idx = ent_index(cmds[k].entity);
+  if (idx < ent_capacity) ent_first[idx] = kNone;
 }
 
 // ================================================================================================================
@@ -265,35 +300,64 @@ __global__ void k_chain(ChainArgs a) {
 // ================================================================================================================
 // Stage 3 — archetype masks → table ids, op counts, per-table net row deltas
 // ================================================================================================================
-__global__ void k_map_tables(uint32_t K, const uint64_t* __restrict__ src_mask, const uint64_t* __restrict__ dst_mask,
-                             const uint32_t* __restrict__ cflags, MaskHash mh, uint32_t* __restrict__ src_t,
-                             uint32_t* __restrict__ dst_t, uint32_t* __restrict__ opcnt, int* __restrict__ tdelta,
-                             Unknown* __restrict__ unknown, uint32_t unknown_cap, Counters* counters) {
-  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= K) return;
-  const uint32_t fl = cflags[k];
-  uint32_t st = kNone, dt = kNone, cnt = 0;
-  if (fl & F_MIG) {
-    st = mask_lookup(mh, src_mask[k]);
-    if (!(fl & F_DESTROY)) {
-      dt = mask_lookup(mh, dst_mask[k]);
-      if (dt == kNone) {  // GetOrCreateArchetype will have to create it (manager.hpp:1852-1877)
-        const uint32_t u = atomicAdd(&counters->unknown, 1u);
-        if (u < unknown_cap) unknown[u] = Unknown{dst_mask[k], k, 0};
-      }
-    }
-    if (st != kNone && (dt != kNone || (fl & F_DESTROY))) {
-      cnt = (fl & F_DESTROY) ? 1u : 2u;
-      atomicSub(&tdelta[st], 1);
-      if (dt != kNone) atomicAdd(&tdelta[dt], 1);
-    }
-    atomicAdd(&counters->effective, 1u);
-  } else if ((fl & F_VALID)) {
-    atomicAdd(&counters->effective, 1u);  // value overwrite without migration still changes the world
+// Per-table remove / append op counts are accumulated in shared-memory histograms (one global atomic per table per CTA)
+// when the directory fits; worlds with more tables fall back to warp-aggregated global atomics.
+constexpr uint32_t kHistTables = 2048;
+
+__device__ __forceinline__ void count_table(uint32_t* s_hist, uint32_t* g_hist, uint32_t t, bool use_smem) {
+  if (use_smem) {
+    atomicAdd(&s_hist[t], 1u);
+  } else {
+    const uint32_t peers = __match_any_sync(__activemask(), t);
+    if ((threadIdx.x & 31u) == uint32_t(__ffs(peers) - 1)) atomicAdd(&g_hist[t], uint32_t(__popc(peers)));
   }
-  src_t[k] = st;
-  dst_t[k] = dt;
-  opcnt[k] = cnt;
+}
+
+__global__ void __launch_bounds__(256) k_map_tables(uint32_t K, const uint64_t* __restrict__ src_mask,
+                                                    const uint64_t* __restrict__ dst_mask, const uint32_t* __restrict__ cflags,
+                                                    MaskHash mh, uint32_t* __restrict__ src_t, uint32_t* __restrict__ dst_t,
+                                                    uint32_t* __restrict__ opcnt, uint32_t* __restrict__ trem,
+                                                    uint32_t* __restrict__ tapp, uint32_t ntables, Unknown* __restrict__ unknown,
+                                                    uint32_t unknown_cap, Counters* counters) {
+  extern __shared__ uint32_t s_hist[];  // [2 * ntables] when ntables <= kHistTables
+  const bool use_smem = ntables <= kHistTables;
+  if (use_smem)
+    for (uint32_t i = threadIdx.x; i < 2 * ntables; i += blockDim.x) s_hist[i] = 0;
+  __syncthreads();
+  uint32_t effective = 0;
+  for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < K; k += gridDim.x * blockDim.x) {
+    const uint32_t fl = cflags[k];
+    uint32_t st = kNone, dt = kNone, cnt = 0;
+    if (fl & F_MIG) {
+      st = mask_lookup(mh, src_mask[k]);
+      if (!(fl & F_DESTROY)) {
+        dt = mask_lookup(mh, dst_mask[k]);
+        if (dt == kNone) {  // GetOrCreateArchetype will have to create it (manager.hpp:1852-1877)
+          const uint32_t u = atomicAdd(&counters->unknown, 1u);
+          if (u < unknown_cap) unknown[u] = Unknown{dst_mask[k], k, 0};
+        }
+      }
+      if (st != kNone && (dt != kNone || (fl & F_DESTROY))) {
+        cnt = (fl & F_DESTROY) ? 1u : 2u;
+        count_table(s_hist, trem, st, use_smem);
+        if (dt != kNone) count_table(s_hist + ntables, tapp, dt, use_smem);
+      }
+      ++effective;
+    } else if (fl & F_VALID) {
+      ++effective;  // value overwrite without migration still changes the world
+    }
+    src_t[k] = st;
+    dst_t[k] = dt;
+    opcnt[k] = cnt;
+  }
+  __syncthreads();
+  if (use_smem)
+    for (uint32_t i = threadIdx.x; i < 2 * ntables; i += blockDim.x) {
+      const uint32_t c = s_hist[i];
+      if (c) atomicAdd(i < ntables ? &trem[i] : &tapp[i - ntables], c);
+    }
+  for (int o = 16; o > 0; o >>= 1) effective += __shfl_down_sync(0xFFFFFFFFu, effective, o);
+  if ((threadIdx.x & 31u) == 0 && effective) atomicAdd(&counters->effective, effective);
 }
 
 // Remove op first, Append op second — both carry the command index as their time stamp.
@@ -326,25 +390,71 @@ __global__ void k_gather_ops(uint32_t M, const uint64_t* __restrict__ skey, cons
 }
 
 // Size trajectory → the slot each op opens (Append at size s opens slot s) or closes (Remove at size s+1 closes s).
+// Sort key = (table, level relative to the lowest size the table can reach in this batch): fewer radix passes.
 __global__ void k_levels(uint32_t M, const uint32_t* __restrict__ op_table, const uint32_t* __restrict__ op_kind,
                          const uint32_t* __restrict__ delta, const uint32_t* __restrict__ ex,
                          const uint32_t* __restrict__ tseg, const uint32_t* __restrict__ tcount0,
-                         uint32_t* __restrict__ op_level, uint32_t* __restrict__ tfmin, uint64_t* __restrict__ key2,
-                         uint32_t* __restrict__ val2, int level_bits) {
+                         const uint32_t* __restrict__ trem, uint32_t* __restrict__ op_level, uint32_t* __restrict__ tfmin,
+                         uint64_t* __restrict__ key2, uint32_t* __restrict__ val2, int level_bits) {
   const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= M) return;
-  const uint32_t t = op_table[j];
-  const uint32_t size_after = tcount0[t] + (ex[j] + delta[j] - ex[tseg[t]]);
-  const uint32_t level = op_kind[j] ? size_after - 1 : size_after;
-  op_level[j] = level;
-  if (!op_kind[j]) atomicMin(&tfmin[t], level);
-  key2[j] = (uint64_t(t) << level_bits) | level;
-  val2[j] = j;
+  const bool in = j < M;
+  uint32_t t = 0xFFFFFFFFu, level = 0xFFFFFFFFu;
+  bool is_remove = false;
+  if (in) {
+    t = op_table[j];
+    const uint32_t size_after = tcount0[t] + (ex[j] + delta[j] - ex[tseg[t]]);
+    is_remove = op_kind[j] == 0;
+    level = is_remove ? size_after : size_after - 1;
+    op_level[j] = level;
+    key2[j] = (uint64_t(t) << level_bits) | (level - (tcount0[t] - trem[t]));
+    val2[j] = j;
+  }
+  // min closed level per table: ops are sorted by table, so a warp usually holds one or two tables
+  const uint32_t tt = (in && is_remove) ? t : 0xFFFFFFFFu;
+  const uint32_t peers = __match_any_sync(0xFFFFFFFFu, tt);
+  const uint32_t mn = __reduce_min_sync(peers, level);
+  if (tt != 0xFFFFFFFFu && (threadIdx.x & 31u) == uint32_t(__ffs(peers) - 1)) atomicMin(&tfmin[tt], mn);
 }
 
-__global__ void k_invert(uint32_t M, const uint32_t* __restrict__ p2t, uint32_t* __restrict__ t2p) {
+// Offsets of the per-table windows of init_close: slots [tfmin[t], count0[t]) of table t are the initially occupied
+// slots that some Remove closes during the batch.
+__global__ void __launch_bounds__(1024) k_ic_offsets(uint32_t ntables, const uint32_t* __restrict__ tcount0,
+                                                     const uint32_t* __restrict__ tfmin, uint32_t* __restrict__ ic_off) {
+  __shared__ uint32_t s_warp[32];
+  __shared__ uint32_t s_running;
+  if (threadIdx.x == 0) s_running = 0;
+  __syncthreads();
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  for (uint32_t base = 0; base < ntables; base += blockDim.x) {
+    const uint32_t t = base + threadIdx.x;
+    uint32_t v = 0;
+    if (t < ntables && tfmin[t] < tcount0[t]) v = tcount0[t] - tfmin[t];
+    uint32_t inc = prim::warp_incl_scan(v);
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    uint32_t off = 0;
+    for (uint32_t w2 = 0; w2 < wid; ++w2) off += s_warp[w2];
+    if (t < ntables) ic_off[t] = s_running + off + inc - v;
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) s_running += off + inc;
+    __syncthreads();
+  }
+}
+
+// Inverse permutation of the (table, level, time) order + the close lookup of initially occupied slots: a Remove that is
+// the FIRST op of its (table, level) group closes the slot's initial occupant.
+__global__ void k_invert(uint32_t M, const uint32_t* __restrict__ p2t, const uint64_t* __restrict__ key2,
+                         const uint32_t* __restrict__ op_kind, const uint32_t* __restrict__ op_table,
+                         const uint32_t* __restrict__ op_level, const uint32_t* __restrict__ tfmin,
+                         const uint32_t* __restrict__ ic_off, uint32_t* __restrict__ t2p, uint32_t* __restrict__ init_close) {
   const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p < M) t2p[p2t[p]] = p;
+  if (p >= M) return;
+  const uint32_t j = p2t[p];
+  t2p[j] = p;
+  if (op_kind[j] == 0 && (p == 0 || key2[p - 1] != key2[p])) {
+    const uint32_t t = op_table[j];
+    init_close[ic_off[t] + (op_level[j] - tfmin[t])] = j;
+  }
 }
 
 // ================================================================================================================
@@ -361,6 +471,9 @@ struct OpView {
   const uint32_t* p2t;
   const uint32_t* t2p;
   const uint32_t* tfmin;
+  const uint32_t* tcount0;   // live rows BEFORE the batch
+  const uint32_t* ic_off;
+  const uint32_t* init_close;
   int level_bits;
   const helios_gpu_command* cmd;
   const uint32_t* home_cmd;
@@ -381,18 +494,9 @@ __device__ uint32_t close_of(const OpView& v, uint64_t I) {
     return (p + 1 < v.M && v.key2[p + 1] == v.key2[p]) ? v.p2t[p + 1] : kNone;  // opens and closes alternate per slot
   }
   const uint32_t table = uint32_t(I >> 32), slot = uint32_t(I);
-  if (slot < v.tfmin[table]) return kNone;  // below the table's minimum size: the slot never becomes the tail
-  const uint64_t key = (uint64_t(table) << v.level_bits) | slot;
-  uint32_t lo = 0, hi = v.M;  // lower_bound over key2
-  while (lo < hi) {
-    const uint32_t mid = (lo + hi) >> 1;
-    if (v.key2[mid] < key) lo = mid + 1; else hi = mid;
-  }
-  if (lo < v.M && v.key2[lo] == key) {
-    const uint32_t j = v.p2t[lo];
-    if (v.op_kind[j] == 0) return j;  // an initially occupied slot sees a Remove first
-  }
-  return kNone;
+  const uint32_t fmin = v.tfmin[table];
+  if (slot < fmin || slot >= v.tcount0[table]) return kNone;  // below the table's minimum size: never becomes the tail
+  return v.init_close[v.ic_off[table] + (slot - fmin)];
 }
 
 // Instance closed by Remove op j (the table's tail slot at that moment).
@@ -427,18 +531,23 @@ __device__ bool resolve_one(const OpView& v, uint32_t j) {
   return true;
 }
 
-__global__ void k_resolve(OpView v, Counters* counters) {
-  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= v.M || v.op_kind[j] != 0 || v.resolved[j]) return;
-  if (!resolve_one(v, j)) atomicAdd(&counters->unresolved, 1u);
-}
-
-// Worst-case fallback: one thread per table replays its Remove ops in time order (every predecessor is earlier).
-__global__ void k_resolve_sequential(OpView v, const uint32_t* __restrict__ tseg, uint32_t ntables) {
-  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= ntables || tseg[t] == kNone) return;
-  for (uint32_t j = tseg[t]; j < v.M && v.op_table[j] == t; ++j)
-    if (v.op_kind[j] == 0 && !v.resolved[j]) resolve_one(v, j);
+// Single-launch resolver.  CTAs take their op range through a ticket, so a CTA only ever depends on CTAs that already
+// started (ops of one table are contiguous in t-order and every predecessor has a smaller index): each thread retries
+// its own op until the moves it depends on are published; nobody waits on a later CTA, so the loop always terminates.
+__global__ void __launch_bounds__(256) k_resolve_all(OpView v, Counters* counters) {
+  __shared__ uint32_t s_block;
+  if (threadIdx.x == 0) s_block = atomicAdd(&counters->ticket, 1u);
+  __syncthreads();
+  const uint32_t j = s_block * blockDim.x + threadIdx.x;
+  bool pending = j < v.M && v.op_kind[j] == 0;
+  uint32_t rounds = 0;
+  for (;;) {
+    if (pending) pending = !resolve_one(v, j);
+    if (!__syncthreads_or(pending)) break;
+    ++rounds;
+    if (pending) __nanosleep(64);
+  }
+  if (threadIdx.x == 0 && rounds) atomicMax(&counters->unresolved, rounds);  // reported as resolve_rounds
 }
 
 // Occupant of the slot closed by Remove op j at that moment = the entity that op moves.
@@ -519,20 +628,23 @@ __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, uin
 // manager.hpp:1912-1925, and the swapped row of Archetype::Remove, archetype.hpp:418-431).
 __global__ void k_gather_rows(MoveArgs a) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= a.n) return;
-  const uint64_t l0 = a.loc[ent_index(a.ch_ent[i])];
-  const uint32_t t0 = uint32_t(l0 >> 32), r0 = uint32_t(l0);
-  uint64_t m = a.tmask[a.ch_table[i]] & a.tmask[t0];
-  uint8_t* out = a.stage + size_t(i) * a.stride;
-  uint32_t bytes = 8;
-  while (m) {
-    const int s = __ffsll(static_cast<long long>(m)) - 1;
-    m &= m - 1;
-    const uint32_t sz = a.csize[s];
-    copy_bytes(out + a.coffset[s], static_cast<const uint8_t*>(a.tcols[size_t(t0) * 64 + s]) + size_t(r0) * sz, sz);
-    bytes += sz;
+  uint32_t bytes = 0;
+  if (i < a.n) {
+    const uint64_t l0 = a.loc[ent_index(a.ch_ent[i])];
+    const uint32_t t0 = uint32_t(l0 >> 32), r0 = uint32_t(l0);
+    uint64_t m = a.tmask[a.ch_table[i]] & a.tmask[t0];
+    uint8_t* out = a.stage + size_t(i) * a.stride;
+    bytes = 8;
+    while (m) {
+      const int s = __ffsll(static_cast<long long>(m)) - 1;
+      m &= m - 1;
+      const uint32_t sz = a.csize[s];
+      copy_bytes(out + a.coffset[s], static_cast<const uint8_t*>(a.tcols[size_t(t0) * 64 + s]) + size_t(r0) * sz, sz);
+      bytes += sz;
+    }
   }
-  atomicAdd(&a.counters->moved_bytes, 2ull * bytes);
+  bytes = __reduce_add_sync(0xFFFFFFFFu, bytes);  // one statistics atomic per warp
+  if ((threadIdx.x & 31u) == 0 && bytes) atomicAdd(&a.counters->moved_bytes, 2ull * bytes);
 }
 
 __global__ void k_scatter_rows(MoveArgs a) {
@@ -594,9 +706,10 @@ __global__ void k_patch(uint32_t K, const helios_gpu_command* __restrict__ cmd, 
   }
 }
 
-__global__ void k_apply_deltas(uint32_t ntables, const int* __restrict__ tdelta, uint32_t* __restrict__ tcount) {
+__global__ void k_apply_deltas(uint32_t ntables, const uint32_t* __restrict__ trem, const uint32_t* __restrict__ tapp,
+                               uint32_t* __restrict__ tcount) {
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < ntables) tcount[t] = uint32_t(int(tcount[t]) + tdelta[t]);
+  if (t < ntables) tcount[t] = tcount[t] + tapp[t] - trem[t];
 }
 
 }  // namespace
@@ -665,7 +778,8 @@ int32_t upload_component_layout(helios_gpu_world* w) {
 }  // namespace apply_host
 using namespace apply_host;
 
-int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const uint8_t* d_payload, uint64_t n, uint32_t) {
+int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const uint8_t* d_payload, uint64_t n,
+                    uint32_t dense) {
   w->last_stats = helios_gpu_apply_stats{};
   if (n == 0) return HELIOS_GPU_OK;
   if (n >= 0x7FFFFFFFull) HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "command buffer too large");
@@ -676,66 +790,103 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
   HG_TRY(upload_component_layout(w));
   uint64_t launches = 0;
 
-  // ---- stage 1: compaction ------------------------------------------------------------------------------------
   NEED(S.counters, sizeof(Counters));
   HG_CUDA(w, cudaMemsetAsync(S.counters.ptr, 0, sizeof(Counters), st));
   Counters* dc = S.counters.as<Counters>();
-  NEED(S.flags, n * 4);
-  NEED(S.cidx, n * 4);
-  NEED(S.partials, (n / prim::kScanTile + 2) * 4);
-  k_flag_valid<<<blocks_for(n), 256, 0, st>>>(d_cmds, n, S.flags.as<uint32_t>());
-  launches += 1 + prim::exclusive_scan_u32(S.flags.as<uint32_t>(), S.cidx.as<uint32_t>(), n, S.partials.as<uint32_t>(),
-                                           &dc->n_valid_slots, st);
   Counters hc{};
-  HG_CUDA(w, cudaMemcpyAsync(&hc, dc, sizeof(hc), cudaMemcpyDeviceToHost, st));
-  HG_CUDA(w, cudaStreamSynchronize(st));
-  const uint32_t K = hc.n_valid_slots;
+  NEED(S.partials, (n / prim::kScanTile + 2) * 4);
+
+  // ---- stage 1: compaction (sparse, device-emitted buffers only; host queues are dense) ---------------------------
+  uint32_t K = uint32_t(n);
+  const helios_gpu_command* cmd = d_cmds;
+  if (!dense) {
+    NEED(S.flags, n * 4);
+    NEED(S.cidx, n * 4);
+    k_flag_valid<<<blocks_for(n), 256, 0, st>>>(d_cmds, n, S.flags.as<uint32_t>());
+    launches += 1 + prim::exclusive_scan_u32(S.flags.as<uint32_t>(), S.cidx.as<uint32_t>(), n, S.partials.as<uint32_t>(),
+                                             &dc->n_valid_slots, st);
+    HG_CUDA(w, cudaMemcpyAsync(&hc, dc, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    HG_CUDA(w, cudaStreamSynchronize(st));
+    K = hc.n_valid_slots;
+  }
   w->last_stats.commands = K;
   if (K == 0) { w->launches += launches; return HELIOS_GPU_OK; }
 
   const uint64_t maxKM = 2ull * K;
-  NEED(S.c_cmd, K * sizeof(helios_gpu_command));
   NEED(S.skey, maxKM * 8); NEED(S.sval, maxKM * 4); NEED(S.skey_alt, maxKM * 8); NEED(S.sval_alt, maxKM * 4);
   const uint32_t nchunks = prim::sort_chunks(maxKM);
   NEED(S.scounts, size_t(256) * nchunks * 4);
   NEED(S.spartials, (size_t(256) * nchunks / prim::kScanTile + 2) * 4);
   prim::SortScratch ss{S.skey_alt.as<uint64_t>(), S.sval_alt.as<uint32_t>(), S.scounts.as<uint32_t>(), S.spartials.as<uint32_t>()};
-  k_compact<<<blocks_for(n), 256, 0, st>>>(d_cmds, n, S.flags.as<uint32_t>(), S.cidx.as<uint32_t>(),
-                                           S.c_cmd.as<helios_gpu_command>(), S.skey.as<uint64_t>(), S.sval.as<uint32_t>());
-  ++launches;
+  if (!dense) {
+    NEED(S.c_cmd, K * sizeof(helios_gpu_command));
+    k_compact<<<blocks_for(n), 256, 0, st>>>(d_cmds, n, S.flags.as<uint32_t>(), S.cidx.as<uint32_t>(),
+                                             S.c_cmd.as<helios_gpu_command>(), S.skey.as<uint64_t>(), S.sval.as<uint32_t>());
+    ++launches;
+    cmd = S.c_cmd.as<helios_gpu_command>();
+  }
 
-  // ---- stage 2: per-entity chains -------------------------------------------------------------------------------
-  launches += prim::radix_sort_pairs(S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), K, 32, ss, st);
+  // ---- stage 2: per-entity chains.  Speculate that no entity is targeted twice (identity order, no sort); the duplicate
+  //      count comes back with the first host read-back and the sorted path re-runs the chain when needed. ------------
+  if (S.ent_first_cap < w->ent_capacity || S.ent_first_dirty) {
+    NEED(S.ent_first, size_t(w->ent_capacity) * 4);
+    HG_CUDA(w, cudaMemsetAsync(S.ent_first.ptr, 0xFF, size_t(w->ent_capacity) * 4, st));
+    S.ent_first_cap = w->ent_capacity;
+  }
+  S.ent_first_dirty = true;
+  k_mark_first<<<blocks_for(K), 256, 0, st>>>(cmd, K, w->ent_capacity, S.ent_first.as<uint32_t>(), S.skey.as<uint64_t>(),
+                                              S.sval.as<uint32_t>());
+  k_count_dups<<<blocks_for(K), 256, 0, st>>>(cmd, K, w->ent_capacity, S.ent_first.as<uint32_t>(), dc);
+  k_reset_first<<<blocks_for(K), 256, 0, st>>>(cmd, K, w->ent_capacity, S.ent_first.as<uint32_t>());
+  launches += 3;
   NEED(S.src_mask, K * 8); NEED(S.dst_mask, K * 8); NEED(S.wset, K * 8); NEED(S.wlive, K * 8);
   NEED(S.home_cmd, K * 4); NEED(S.cflags, K * 4); NEED(S.dflag, K * 4); NEED(S.dpos, K * 4);
   NEED(S.src_t, K * 4); NEED(S.dst_t, K * 4); NEED(S.opcnt, K * 4); NEED(S.opbase, K * 4);
-  ChainArgs ca{S.c_cmd.as<helios_gpu_command>(), S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), K, w->d_gen.as<uint32_t>(),
+  ChainArgs ca{cmd, S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), K, w->d_gen.as<uint32_t>(),
                w->d_loc.as<uint64_t>(), w->d_tmask.as<uint64_t>(), w->ent_capacity, S.src_mask.as<uint64_t>(),
                S.dst_mask.as<uint64_t>(), S.wset.as<uint64_t>(), S.wlive.as<uint64_t>(), S.home_cmd.as<uint32_t>(),
                S.cflags.as<uint32_t>(), S.dflag.as<uint32_t>(), dc};
   k_chain<<<blocks_for(K), 256, 0, st>>>(ca);
   ++launches;
 
-  // ---- stage 3: masks → tables (creating missing archetypes in command order), op counts, net deltas ----------------
+  // ---- stage 3: masks → tables (creating missing archetypes in command order), per-table op counts ------------------
   NEED(S.unknown, size_t(K) * sizeof(Unknown));
-  std::vector<int> hdelta;
+  std::vector<uint32_t> hrem, happ;
   uint32_t M = 0;
+  bool sorted_by_entity = false;
   for (int attempt = 0;; ++attempt) {
     HG_TRY(upload_mask_hash(w));
     const uint32_t nt = uint32_t(w->tables.size());
-    NEED(S.tdelta, std::max<uint32_t>(nt, 1) * 4); NEED(S.tfmin, std::max<uint32_t>(nt, 1) * 4); NEED(S.tseg, std::max<uint32_t>(nt, 1) * 4);
-    HG_CUDA(w, cudaMemsetAsync(S.tdelta.ptr, 0, nt * 4, st));
+    const uint32_t ntp = std::max<uint32_t>(nt, 1);
+    NEED(S.trem, ntp * 4); NEED(S.tapp, ntp * 4); NEED(S.tfmin, ntp * 4); NEED(S.tseg, ntp * 4); NEED(S.ic_off, ntp * 4);
+    HG_CUDA(w, cudaMemsetAsync(S.trem.ptr, 0, nt * 4, st));
+    HG_CUDA(w, cudaMemsetAsync(S.tapp.ptr, 0, nt * 4, st));
     HG_CUDA(w, cudaMemsetAsync(&dc->unknown, 0, 4, st));
     HG_CUDA(w, cudaMemsetAsync(&dc->effective, 0, 4, st));
     MaskHash mh{S.mh_keys.as<uint64_t>(), S.mh_vals.as<uint32_t>(), S.mh_log2};
-    k_map_tables<<<blocks_for(K), 256, 0, st>>>(K, S.src_mask.as<uint64_t>(), S.dst_mask.as<uint64_t>(), S.cflags.as<uint32_t>(), mh,
-                                                S.src_t.as<uint32_t>(), S.dst_t.as<uint32_t>(), S.opcnt.as<uint32_t>(),
-                                                S.tdelta.as<int>(), S.unknown.as<Unknown>(), K, dc);
+    const uint32_t grid = std::min<uint32_t>(blocks_for(K), uint32_t(w->sm_count) * 8);
+    const size_t smem = nt <= kHistTables ? size_t(2) * nt * 4 : 0;
+    k_map_tables<<<grid, 256, smem, st>>>(K, S.src_mask.as<uint64_t>(), S.dst_mask.as<uint64_t>(), S.cflags.as<uint32_t>(), mh,
+                                          S.src_t.as<uint32_t>(), S.dst_t.as<uint32_t>(), S.opcnt.as<uint32_t>(),
+                                          S.trem.as<uint32_t>(), S.tapp.as<uint32_t>(), nt, S.unknown.as<Unknown>(), K, dc);
     launches += 1 + prim::exclusive_scan_u32(S.opcnt.as<uint32_t>(), S.opbase.as<uint32_t>(), K, S.partials.as<uint32_t>(), &dc->n_ops, st);
-    hdelta.assign(nt, 0);
+    hrem.assign(nt, 0);
+    happ.assign(nt, 0);
     HG_CUDA(w, cudaMemcpyAsync(&hc, dc, sizeof(hc), cudaMemcpyDeviceToHost, st));
-    if (nt) HG_CUDA(w, cudaMemcpyAsync(hdelta.data(), S.tdelta.ptr, nt * 4, cudaMemcpyDeviceToHost, st));
+    if (nt) {
+      HG_CUDA(w, cudaMemcpyAsync(hrem.data(), S.trem.ptr, nt * 4, cudaMemcpyDeviceToHost, st));
+      HG_CUDA(w, cudaMemcpyAsync(happ.data(), S.tapp.ptr, nt * 4, cudaMemcpyDeviceToHost, st));
+    }
     HG_CUDA(w, cudaStreamSynchronize(st));
+    if (hc.dups != 0 && !sorted_by_entity) {
+      // some entity carries several commands: stable sort by entity index, then redo the chains in FIFO order
+      launches += prim::radix_sort_pairs(S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), K, 32, ss, st);
+      HG_CUDA(w, cudaMemsetAsync(&dc->invalid, 0, 4, st));
+      k_chain<<<blocks_for(K), 256, 0, st>>>(ca);
+      ++launches;
+      sorted_by_entity = true;
+      continue;
+    }
     if (hc.unknown == 0) { M = hc.n_ops; break; }
     if (attempt > 64) HG_FAIL(w, HELIOS_GPU_ERR_STATE, "archetype creation did not converge");
     // GetOrCreateArchetype in command order (manager.hpp:1852-1877): first command that needs a mask creates its table
@@ -748,13 +899,15 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
       HG_TRY(ensure_table(w, u.mask, &t));
     }
   }
+  S.ent_first_dirty = false;  // k_reset_first ran to completion
   w->last_stats.invalid = hc.invalid;
   w->last_stats.effective = hc.effective;
   const uint32_t nt = uint32_t(w->tables.size());
-  uint64_t max_rows = 0;
+  uint32_t max_ops = 0;
   for (uint32_t t = 0; t < nt; ++t) {
-    max_rows = std::max<uint64_t>(max_rows, w->tables[t].count);
-    if (hdelta[t] > 0) HG_TRY(ensure_table_rows(w, int(t), w->tables[t].count + uint64_t(hdelta[t])));
+    max_ops = std::max(max_ops, hrem[t] + happ[t]);
+    // rows are only written at slots that survive the batch, so the final row count is the capacity needed
+    if (happ[t] > hrem[t]) HG_TRY(ensure_table_rows(w, int(t), w->tables[t].count + uint64_t(happ[t] - hrem[t])));
   }
 
   // ---- stage 4: table op sequences, slot instances, move resolution ------------------------------------------------
@@ -764,7 +917,7 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     NEED(S.op_table, M * 4); NEED(S.op_kind, M * 4); NEED(S.op_cmd, M * 4); NEED(S.op_level, M * 4);
     NEED(S.u2t, M * 4); NEED(S.delta, M * 4); NEED(S.ex, M * 4);
     NEED(S.key2, M * 8); NEED(S.p2t, M * 4); NEED(S.t2p, M * 4);
-    NEED(S.J, M * 8); NEED(S.resolved, M * 4);
+    NEED(S.J, M * 8); NEED(S.resolved, M * 4); NEED(S.init_close, size_t(M) * 4);
     k_emit_ops<<<blocks_for(K), 256, 0, st>>>(K, S.opcnt.as<uint32_t>(), S.opbase.as<uint32_t>(), S.src_t.as<uint32_t>(),
                                               S.dst_t.as<uint32_t>(), S.skey.as<uint64_t>(), S.sval.as<uint32_t>(),
                                               S.u_kind.as<uint32_t>(), S.u_cmd.as<uint32_t>());
@@ -773,20 +926,24 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     launches += prim::radix_sort_pairs(S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), M, table_bits, ss, st);
     HG_CUDA(w, cudaMemsetAsync(S.tseg.ptr, 0xFF, nt * 4, st));
     HG_CUDA(w, cudaMemsetAsync(S.tfmin.ptr, 0xFF, nt * 4, st));
+    HG_CUDA(w, cudaMemsetAsync(S.init_close.ptr, 0xFF, size_t(M) * 4, st));
     k_gather_ops<<<blocks_for(M), 256, 0, st>>>(M, S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), S.u_kind.as<uint32_t>(),
                                                 S.u_cmd.as<uint32_t>(), S.op_table.as<uint32_t>(), S.op_kind.as<uint32_t>(),
                                                 S.op_cmd.as<uint32_t>(), S.u2t.as<uint32_t>(), S.delta.as<uint32_t>(),
                                                 S.tseg.as<uint32_t>());
     launches += 1 + prim::exclusive_scan_u32(S.delta.as<uint32_t>(), S.ex.as<uint32_t>(), M, S.partials.as<uint32_t>(), nullptr, st);
-    const int level_bits = prim::bits_for(max_rows + M + 1);
+    const int level_bits = prim::bits_for(uint64_t(max_ops) + 1);
     k_levels<<<blocks_for(M), 256, 0, st>>>(M, S.op_table.as<uint32_t>(), S.op_kind.as<uint32_t>(), S.delta.as<uint32_t>(),
                                             S.ex.as<uint32_t>(), S.tseg.as<uint32_t>(), w->d_tcount.as<uint32_t>(),
-                                            S.op_level.as<uint32_t>(), S.tfmin.as<uint32_t>(), S.key2.as<uint64_t>(),
-                                            S.p2t.as<uint32_t>(), level_bits);
+                                            S.trem.as<uint32_t>(), S.op_level.as<uint32_t>(), S.tfmin.as<uint32_t>(),
+                                            S.key2.as<uint64_t>(), S.p2t.as<uint32_t>(), level_bits);
     ++launches;
     launches += prim::radix_sort_pairs(S.key2.as<uint64_t>(), S.p2t.as<uint32_t>(), M, level_bits + table_bits, ss, st);
-    k_invert<<<blocks_for(M), 256, 0, st>>>(M, S.p2t.as<uint32_t>(), S.t2p.as<uint32_t>());
-    ++launches;
+    k_ic_offsets<<<1, 1024, 0, st>>>(nt, w->d_tcount.as<uint32_t>(), S.tfmin.as<uint32_t>(), S.ic_off.as<uint32_t>());
+    k_invert<<<blocks_for(M), 256, 0, st>>>(M, S.p2t.as<uint32_t>(), S.key2.as<uint64_t>(), S.op_kind.as<uint32_t>(),
+                                            S.op_table.as<uint32_t>(), S.op_level.as<uint32_t>(), S.tfmin.as<uint32_t>(),
+                                            S.ic_off.as<uint32_t>(), S.t2p.as<uint32_t>(), S.init_close.as<uint32_t>());
+    launches += 2;
 
     uint32_t ih_log2 = 10;
     while ((1ull << ih_log2) < 2ull * M) ++ih_log2;
@@ -797,34 +954,21 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     HG_CUDA(w, cudaMemsetAsync(S.resolved.ptr, 0, M * 4, st));
     OpView v{M, S.op_table.as<uint32_t>(), S.op_kind.as<uint32_t>(), S.op_cmd.as<uint32_t>(), S.op_level.as<uint32_t>(),
              S.u2t.as<uint32_t>(), S.key2.as<uint64_t>(), S.p2t.as<uint32_t>(), S.t2p.as<uint32_t>(), S.tfmin.as<uint32_t>(),
-             level_bits, S.c_cmd.as<helios_gpu_command>(), S.home_cmd.as<uint32_t>(), S.opbase.as<uint32_t>(),
+             w->d_tcount.as<uint32_t>(), S.ic_off.as<uint32_t>(), S.init_close.as<uint32_t>(),
+             level_bits, cmd, S.home_cmd.as<uint32_t>(), S.opbase.as<uint32_t>(),
              w->d_loc.as<uint64_t>(), S.J.as<uint64_t>(), S.resolved.as<uint32_t>(),
              InstHash{S.ih_keys.as<unsigned long long>(), S.ih_vals.as<uint32_t>(), ih_log2}};
-    uint32_t rounds = 0;
-    constexpr uint32_t kMaxRounds = 32;
-    for (;;) {
-      HG_CUDA(w, cudaMemsetAsync(&dc->unresolved, 0, 4, st));
-      k_resolve<<<blocks_for(M), 256, 0, st>>>(v, dc);
-      ++launches; ++rounds;
-      uint32_t unresolved = 0;
-      HG_CUDA(w, cudaMemcpyAsync(&unresolved, &dc->unresolved, 4, cudaMemcpyDeviceToHost, st));
-      HG_CUDA(w, cudaStreamSynchronize(st));
-      if (unresolved == 0) break;
-      if (rounds >= kMaxRounds) {
-        k_resolve_sequential<<<blocks_for(nt, 32), 32, 0, st>>>(v, S.tseg.as<uint32_t>(), nt);
-        ++launches;
-        w->last_stats.used_sequential_fallback = 1;
-        break;
-      }
-    }
-    w->last_stats.resolve_rounds = rounds;
+    k_resolve_all<<<blocks_for(M), 256, 0, st>>>(v, dc);
+    ++launches;
 
     NEED(S.ch_table, M * 4); NEED(S.ch_slot, M * 4); NEED(S.ch_ent, M * 8);
     k_final_slots<<<blocks_for(M), 256, 0, st>>>(v, w->d_tents.as<helios_gpu_entity_t*>(), S.ch_table.as<uint32_t>(),
                                                  S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(), dc);
     ++launches;
-    HG_CUDA(w, cudaMemcpyAsync(&n_changed, &dc->n_changed, 4, cudaMemcpyDeviceToHost, st));
+    HG_CUDA(w, cudaMemcpyAsync(&hc, dc, sizeof(hc), cudaMemcpyDeviceToHost, st));
     HG_CUDA(w, cudaStreamSynchronize(st));
+    n_changed = hc.n_changed;
+    w->last_stats.resolve_rounds = hc.unresolved;
     if (n_changed) {
       NEED(S.stage, size_t(n_changed) * S.stage_stride);
       MoveArgs ma{n_changed, S.ch_table.as<uint32_t>(), S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(),
@@ -842,16 +986,16 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
   // ---- stage 5: destroys, payload patch, counts ------------------------------------------------------------------
   launches += prim::exclusive_scan_u32(S.dflag.as<uint32_t>(), S.dpos.as<uint32_t>(), K, S.partials.as<uint32_t>(), &dc->n_destroy, st);
   HG_CUDA(w, w->d_free.reserve((w->free_count + K) * 4, w->free_count * 4, st, true));
-  k_destroy<<<blocks_for(K), 256, 0, st>>>(K, S.c_cmd.as<helios_gpu_command>(), S.dflag.as<uint32_t>(), S.dpos.as<uint32_t>(),
+  k_destroy<<<blocks_for(K), 256, 0, st>>>(K, cmd, S.dflag.as<uint32_t>(), S.dpos.as<uint32_t>(),
                                            w->d_gen.as<uint32_t>(), w->d_loc.as<uint64_t>(), w->d_free.as<uint32_t>(), w->free_count);
-  k_patch<<<blocks_for(K), 256, 0, st>>>(K, S.c_cmd.as<helios_gpu_command>(), S.wlive.as<uint64_t>(), d_payload,
+  k_patch<<<blocks_for(K), 256, 0, st>>>(K, cmd, S.wlive.as<uint64_t>(), d_payload,
                                          w->d_loc.as<uint64_t>(), w->d_tcols.as<void*>(), w->d_csize.as<uint32_t>());
-  k_apply_deltas<<<blocks_for(nt), 256, 0, st>>>(nt, S.tdelta.as<int>(), w->d_tcount.as<uint32_t>());
+  k_apply_deltas<<<blocks_for(nt), 256, 0, st>>>(nt, S.trem.as<uint32_t>(), S.tapp.as<uint32_t>(), w->d_tcount.as<uint32_t>());
   launches += 3;
   HG_CUDA(w, cudaMemcpyAsync(&hc, dc, sizeof(hc), cudaMemcpyDeviceToHost, st));
   HG_CUDA(w, cudaStreamSynchronize(st));
   HG_CUDA(w, cudaGetLastError());
-  for (uint32_t t = 0; t < nt; ++t) w->tables[t].count = uint64_t(int64_t(w->tables[t].count) + hdelta[t]);
+  for (uint32_t t = 0; t < nt; ++t) w->tables[t].count = w->tables[t].count + happ[t] - hrem[t];
   if (hc.n_destroy) {
     w->free_count += hc.n_destroy;
     w->free_cursor = int64_t(w->free_count);  // Destroy sets free_cursor_ = free_indices_.size() (manager.hpp:317-318)

@@ -46,21 +46,27 @@ int32_t flush_reserved(helios_gpu_world* w) {
   return set_table_count(w, w->empty_table, tb.count + n);
 }
 
-int32_t apply_host_queue(helios_gpu_world* w, HostCmdQueue& q) {
-  if (q.cmds.empty()) return HELIOS_GPU_OK;
-  DevBuf d_cmds, d_payload;
-  HG_CUDA(w, d_cmds.reserve(q.cmds.size() * sizeof(helios_gpu_command), 0, w->stream, false));
-  HG_CUDA(w, cudaMemcpyAsync(d_cmds.ptr, q.cmds.data(), q.cmds.size() * sizeof(helios_gpu_command),
+static int32_t stage_host_queue(helios_gpu_world* w, HostCmdQueue& q) {
+  if (w->staged_n == q.cmds.size()) return HELIOS_GPU_OK;
+  HG_CUDA(w, w->staged_cmds.reserve(q.cmds.size() * sizeof(helios_gpu_command), 0, w->stream, true));
+  HG_CUDA(w, cudaMemcpyAsync(w->staged_cmds.ptr, q.cmds.data(), q.cmds.size() * sizeof(helios_gpu_command),
                              cudaMemcpyHostToDevice, w->stream));
   if (!q.payload.empty()) {
-    HG_CUDA(w, d_payload.reserve(q.payload.size(), 0, w->stream, false));
-    HG_CUDA(w, cudaMemcpyAsync(d_payload.ptr, q.payload.data(), q.payload.size(), cudaMemcpyHostToDevice, w->stream));
+    HG_CUDA(w, w->staged_payload.reserve(q.payload.size(), 0, w->stream, true));
+    HG_CUDA(w, cudaMemcpyAsync(w->staged_payload.ptr, q.payload.data(), q.payload.size(), cudaMemcpyHostToDevice, w->stream));
   }
+  HG_CUDA(w, cudaStreamSynchronize(w->stream));  // pageable host vectors: the copy must not outlive later appends
+  w->staged_n = q.cmds.size();
+  return HELIOS_GPU_OK;
+}
+
+int32_t apply_host_queue(helios_gpu_world* w, HostCmdQueue& q) {
+  if (q.cmds.empty()) return HELIOS_GPU_OK;
+  HG_TRY(stage_host_queue(w, q));
   const uint64_t n = q.cmds.size();
   q.clear();
-  const int32_t st = apply_queue(w, d_cmds.as<helios_gpu_command>(), d_payload.as<uint8_t>(), n, 0);
-  cudaStreamSynchronize(w->stream);  // the staging buffers die with this scope
-  return st;
+  w->staged_n = 0;
+  return apply_queue(w, w->staged_cmds.as<helios_gpu_command>(), w->staged_payload.as<uint8_t>(), n, /*dense=*/1);
 }
 
 }  // namespace hgpu
@@ -82,6 +88,12 @@ int32_t helios_gpu_commands_enqueue(helios_gpu_world* w, const helios_gpu_comman
   q.payload.insert(q.payload.end(), p, p + payload_bytes);
   while (q.payload.size() % 16) q.payload.push_back(0);
   return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_commands_stage(helios_gpu_world* w) {
+  if (!w) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (w->global_queue.cmds.empty()) return HELIOS_GPU_OK;
+  return stage_host_queue(w, w->global_queue);
 }
 
 int32_t helios_gpu_world_flush(helios_gpu_world* w) {

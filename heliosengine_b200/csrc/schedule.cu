@@ -454,7 +454,7 @@ int32_t helios_gpu_schedule_apply_deferred(helios_gpu_schedule* s) {
     // SystemLocalData::ExecuteCommands (system_local_data.hpp:111)
     if ((e.desc.flags & HELIOS_GPU_SYSTEM_EMITS_COMMANDS) && e.cmd_slots_in_use && s->pending)
       HG_TRY(apply_queue(w, e.cmd_records.as<helios_gpu_command>(), e.cmd_payload.as<uint8_t>(), e.cmd_slots_in_use,
-                         e.desc.cmd_payload_stride));
+                         /*dense=*/0));
     // SystemLocalData::MergeMessages (system_local_data.hpp:122-132)
     HG_TRY(messages_update_from_system(w));
     if (e.desc.writes_message && s->pending) {

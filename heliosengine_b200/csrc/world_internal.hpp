@@ -106,6 +106,8 @@ struct helios_gpu_world {
   uint64_t live_count = 0;     // entity_count_
 
   hgpu::HostCmdQueue global_queue;   // World::command_queue_
+  hgpu::DevBuf staged_cmds, staged_payload;  // device copy of global_queue made by helios_gpu_commands_stage
+  uint64_t staged_n = 0;                     // records staged (valid while == global_queue.cmds.size())
   helios_gpu_apply_stats last_stats{};
 
   std::vector<std::unique_ptr<hgpu::MsgChannel>> channels;
@@ -129,7 +131,7 @@ int32_t sync_counts_to_host(helios_gpu_world* w);
 int32_t set_table_count(helios_gpu_world* w, int table, uint64_t count);
 // commands.cu
 int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const uint8_t* d_payload, uint64_t n,
-                    uint32_t payload_stride_hint);
+                    uint32_t dense /* 1: every record is valid (host queue), 0: sparse device-emitted buffer */);
 int32_t apply_host_queue(helios_gpu_world* w, HostCmdQueue& q);
 int32_t flush_reserved(helios_gpu_world* w);
 void free_apply_scratch(helios_gpu_world* w);

@@ -217,6 +217,22 @@ CFG4_COMPONENT_BYTES_PER_ENTITY = 24 + 16 + 8 + 8 + 4 + 12 + 8
 CFG4_BYTES_PER_EVENT = 24 + 24 + 8
 
 
+def snapshot_digest(snap: dict) -> str:
+    """SHA-256 of a canonical snapshot: equal digests == bit-exact world state."""
+    import hashlib
+    h = hashlib.sha256()
+    h.update(struct.pack("<IIqQ", len(snap["archetypes"]), snap["next_index"], snap["free_cursor"], snap["entity_count"]))
+    for a in snap["archetypes"]:
+        h.update(struct.pack("<II", len(a["types"]), a["entities"].size))
+        h.update(np.asarray(a["types"], dtype=np.uint64).tobytes())
+        h.update(np.ascontiguousarray(a["entities"]).tobytes())
+        for t in a["types"]:
+            h.update(np.ascontiguousarray(a["columns"][t]).tobytes())
+    h.update(np.ascontiguousarray(snap["generations"]).tobytes())
+    h.update(np.ascontiguousarray(snap["free_indices"]).tobytes())
+    return h.hexdigest()
+
+
 def snapshots_equal(a: dict, b: dict, float_cols: dict | None = None) -> list[str]:
     """Bit-exact comparison of two canonical snapshots; returns the list of differences (empty = equal)."""
     diffs = []

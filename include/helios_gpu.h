@@ -182,6 +182,9 @@ typedef struct helios_gpu_command {
 /* Enqueue into the world's global queue (World::command_queue_, world.hpp:945; executed by Flush). */
 HELIOS_GPU_API int32_t helios_gpu_commands_enqueue(helios_gpu_world* w, const helios_gpu_command* cmds, uint64_t n,
                                                    const void* payload, uint64_t payload_bytes);
+/* Copy the pending global queue to HBM now, so that the next flush launches kernels only (no reference counterpart:
+ * CmdQueue lives in host memory there; this is the "inputs already resident" form bench.py times as `value`). */
+HELIOS_GPU_API int32_t helios_gpu_commands_stage(helios_gpu_world* w);
 /* World::Flush (world.hpp:957-963): reserved-entity flush, then the global queue, FIFO. */
 HELIOS_GPU_API int32_t helios_gpu_world_flush(helios_gpu_world* w);
 /* World::Update (world.hpp:950-955): Flush + MessageManager::Update(). */

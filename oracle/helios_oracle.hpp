@@ -368,8 +368,14 @@ public:
     Archetype* arch = EntityArchetype(e);
     assert(arch);
     const Entity swapped = arch->Remove(e);
-    if (swapped.Valid()) SetEntityArchetype(swapped.index, arch);
+    if (swapped.Valid()) {
+      SetEntityArchetype(swapped.index, arch);
+      uint64_t hb = 8;
+      for (size_t c = 0; c < arch->Id().Types().size(); ++c) hb += arch->ElemSize(static_cast<int>(c));
+      migrate_bytes += 2 * hb + 8;  // hole fill read + write, swapped entity's location entry
+    }
     SetEntityArchetype(e.index, nullptr);
+    migrate_bytes += 8 + 8;  // removed entity's location entry + generation read-modify-write (SURVEY §8d cfg 3)
   }
   // manager.hpp:1096-1115
   bool TryRemoveEntity(Entity e) {
@@ -411,6 +417,7 @@ public:
     } else {
       for (size_t i = 0; i < n; ++i) current.Set(e, current.ColumnIndex(comps[i].type), comps[i].bytes);
     }
+    for (size_t i = 0; i < n; ++i) migrate_bytes += Meta(comps[i].type)->size;  // component values written
   }
 
   // manager.hpp:1205-1248 TryAddArchetypeComponents — existing components untouched.
@@ -425,7 +432,10 @@ public:
       Archetype& target = GetOrCreateArchetype(target_id);
       MigrateEntity(e, current, target);
       for (size_t i = 0; i < n; ++i)
-        if (results[i]) target.Set(e, target.ColumnIndex(comps[i].type), comps[i].bytes);
+        if (results[i]) {
+          target.Set(e, target.ColumnIndex(comps[i].type), comps[i].bytes);
+          migrate_bytes += Meta(comps[i].type)->size;
+        }
       ++structural_version_;
     }
     return results;
@@ -500,7 +510,9 @@ public:
     structural_version_ = 0;
   }
 
-  // Algorithmic byte counter for SURVEY §8(d) cfg 3 ("bytes/cmd from the oracle's replay log").
+  // Algorithmic byte counter for SURVEY §8(d) cfg 3 ("bytes/cmd from the oracle's replay log"): moved rows (read+write,
+  // entity id included), hole fills, location entries, generation updates, component values written.  The command
+  // records themselves (24 B + payload each) are added by the C layer when a queue is executed.
   uint64_t migrate_bytes = 0;
 
 private:

@@ -425,8 +425,13 @@ HO_API int32_t helios_oracle_query_count_w(void* wp, void* q, uint64_t* out) {
 // ---- commands ---------------------------------------------------------------------------------------------
 HO_API int32_t helios_oracle_commands_enqueue(void* wp, const helios_gpu_command* cmds, uint64_t n, const void* payload, uint64_t) {
   OWorld* w = W(wp);
-  for (uint64_t i = 0; i < n; ++i)
-    w->world.command_queue.Enqueue(to_command(w, cmds[i], static_cast<const uint8_t*>(payload)));
+  for (uint64_t i = 0; i < n; ++i) {
+    ho::Command c = to_command(w, cmds[i], static_cast<const uint8_t*>(payload));
+    uint64_t rec = sizeof(helios_gpu_command);  // the record is read once when the queue executes
+    for (const auto& v : c.values) rec += v.size();
+    w->world.components.migrate_bytes += rec;
+    w->world.command_queue.Enqueue(std::move(c));
+  }
   return 0;
 }
 HO_API int32_t helios_oracle_world_flush(void* wp) {

@@ -12,18 +12,7 @@ import numpy as np
 from heliosengine_b200 import capi, worlds
 
 
-def snapshot_digest(snap: dict) -> str:
-    h = hashlib.sha256()
-    h.update(struct.pack("<IIqQ", len(snap["archetypes"]), snap["next_index"], snap["free_cursor"], snap["entity_count"]))
-    for a in snap["archetypes"]:
-        h.update(struct.pack("<II", len(a["types"]), a["entities"].size))
-        h.update(np.asarray(a["types"], dtype=np.uint64).tobytes())
-        h.update(np.ascontiguousarray(a["entities"]).tobytes())
-        for t in a["types"]:
-            h.update(np.ascontiguousarray(a["columns"][t]).tobytes())
-    h.update(np.ascontiguousarray(snap["generations"]).tobytes())
-    h.update(np.ascontiguousarray(snap["free_indices"]).tobytes())
-    return h.hexdigest()
+snapshot_digest = worlds.snapshot_digest
 
 
 def _bytes_digest(*arrays) -> str:
