@@ -129,7 +129,7 @@ struct helios_gpu_world::ApplyScratch {
   DevBuf u_table, u_kind, u_cmd;
   DevBuf op_table, op_kind, op_cmd, op_level, u2t, delta, ex;
   DevBuf key2, p2t, t2p;
-  DevBuf J, resolved;
+  DevBuf J;
   DevBuf ih_keys, ih_vals;
   DevBuf ch_table, ch_slot, ch_ent, stage;
   DevBuf coffset;  // uint32[64] byte offset of each component inside a staged row
@@ -479,8 +479,9 @@ struct OpView {
   const uint32_t* home_cmd;
   const uint32_t* opbase;
   const uint64_t* loc;       // locations BEFORE the batch
-  uint64_t* J;               // per Remove op: instance the removed entity lives in at that time
-  uint32_t* resolved;
+  uint64_t* J;               // per Remove op: instance the removed entity lives in at that time (all-ones = pending)
+  const uint32_t* trem;      // per-table Remove / Append op counts of this batch
+  const uint32_t* tapp;
   InstHash ih;
 };
 
@@ -506,28 +507,40 @@ __device__ __forceinline__ uint64_t closed_by(const OpView& v, uint32_t j) {
   return inst_init(v.op_table[j], v.op_level[j]);
 }
 
-// Try to resolve Remove op j; returns false if a predecessor move is still unresolved.
-__device__ bool resolve_one(const OpView& v, uint32_t j) {
-  const uint32_t k = v.op_cmd[j];
-  const uint32_t hk = v.home_cmd[k];
-  uint64_t I;
-  if (hk == kNone) {
-    const uint64_t l = v.loc[ent_index(v.cmd[k].entity)];
-    I = inst_init(uint32_t(l >> 32), uint32_t(l));
-  } else {
-    I = inst_append(v.u2t[v.opbase[hk] + 1]);  // the Append of the entity's previous migration
+constexpr uint64_t kUnresolvedJ = 0xFFFFFFFFFFFFFFFFull;  // J[] is memset to all-ones; no instance encodes to that
+
+__device__ __forceinline__ uint64_t load_J(const OpView& v, uint32_t c) {
+  return *reinterpret_cast<const volatile uint64_t*>(&v.J[c]);
+}
+
+// Advance Remove op j along the removed entity's move chain.  `I` carries the walk across retries (started == false on the
+// first call); returns false while a predecessor move is still unpublished.  J[c] doubles as the "resolved" flag.
+__device__ bool resolve_step(const OpView& v, uint32_t j, uint64_t& I, bool& started) {
+  if (!started) {
+    started = true;
+    const uint32_t t = v.op_table[j];
+    if (v.tcount0[t] + v.tapp[t] == v.trem[t]) {  // the table ends empty: no slot survives, its row order is moot
+      *reinterpret_cast<volatile uint64_t*>(&v.J[j]) = closed_by(v, j);
+      return true;
+    }
+    const uint32_t k = v.op_cmd[j];
+    const uint32_t hk = v.home_cmd[k];
+    if (hk == kNone) {
+      const uint64_t l = v.loc[ent_index(v.cmd[k].entity)];
+      I = inst_init(uint32_t(l >> 32), uint32_t(l));
+    } else {
+      I = inst_append(v.u2t[v.opbase[hk] + 1]);  // the Append of the entity's previous migration
+    }
   }
   for (;;) {
     const uint32_t c = close_of(v, I);
     if (c == kNone || c >= j) break;  // still sitting in I when op j executes (c == j: it IS the tail → plain pop)
-    if (!*reinterpret_cast<volatile uint32_t*>(&v.resolved[c])) return false;
-    __threadfence();
-    I = *reinterpret_cast<volatile uint64_t*>(&v.J[c]);  // the entity was moved there when its slot closed
+    const uint64_t nx = load_J(v, c);
+    if (nx == kUnresolvedJ) return false;
+    I = nx;  // the entity was moved there when its slot closed
   }
-  v.J[j] = I;
   if (I != closed_by(v, j)) inst_insert_max(v.ih, I, j + 1);  // a real move targets I at time j
-  __threadfence();
-  *reinterpret_cast<volatile uint32_t*>(&v.resolved[j]) = 1u;
+  *reinterpret_cast<volatile uint64_t*>(&v.J[j]) = I;
   return true;
 }
 
@@ -540,12 +553,13 @@ __global__ void __launch_bounds__(256) k_resolve_all(OpView v, Counters* counter
   __syncthreads();
   const uint32_t j = s_block * blockDim.x + threadIdx.x;
   bool pending = j < v.M && v.op_kind[j] == 0;
+  uint64_t I = 0;
+  bool started = false;
   uint32_t rounds = 0;
   for (;;) {
-    if (pending) pending = !resolve_one(v, j);
+    if (pending) pending = !resolve_step(v, j, I, started);
     if (!__syncthreads_or(pending)) break;
     ++rounds;
-    if (pending) __nanosleep(64);
   }
   if (threadIdx.x == 0 && rounds) atomicMax(&counters->unresolved, rounds);  // reported as resolve_rounds
 }
@@ -814,9 +828,8 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
 
   const uint64_t maxKM = 2ull * K;
   NEED(S.skey, maxKM * 8); NEED(S.sval, maxKM * 4); NEED(S.skey_alt, maxKM * 8); NEED(S.sval_alt, maxKM * 4);
-  const uint32_t nchunks = prim::sort_chunks(maxKM);
-  NEED(S.scounts, size_t(256) * nchunks * 4);
-  NEED(S.spartials, (size_t(256) * nchunks / prim::kScanTile + 2) * 4);
+  NEED(S.scounts, size_t(256) * prim::sort_tiles(maxKM) * 4);
+  NEED(S.spartials, 256 * 4);
   prim::SortScratch ss{S.skey_alt.as<uint64_t>(), S.sval_alt.as<uint32_t>(), S.scounts.as<uint32_t>(), S.spartials.as<uint32_t>()};
   if (!dense) {
     NEED(S.c_cmd, K * sizeof(helios_gpu_command));
@@ -917,7 +930,7 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     NEED(S.op_table, M * 4); NEED(S.op_kind, M * 4); NEED(S.op_cmd, M * 4); NEED(S.op_level, M * 4);
     NEED(S.u2t, M * 4); NEED(S.delta, M * 4); NEED(S.ex, M * 4);
     NEED(S.key2, M * 8); NEED(S.p2t, M * 4); NEED(S.t2p, M * 4);
-    NEED(S.J, M * 8); NEED(S.resolved, M * 4); NEED(S.init_close, size_t(M) * 4);
+    NEED(S.J, M * 8); NEED(S.init_close, size_t(M) * 4);
     k_emit_ops<<<blocks_for(K), 256, 0, st>>>(K, S.opcnt.as<uint32_t>(), S.opbase.as<uint32_t>(), S.src_t.as<uint32_t>(),
                                               S.dst_t.as<uint32_t>(), S.skey.as<uint64_t>(), S.sval.as<uint32_t>(),
                                               S.u_kind.as<uint32_t>(), S.u_cmd.as<uint32_t>());
@@ -951,12 +964,12 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     NEED(S.ih_vals, (size_t(1) << ih_log2) * 4);
     HG_CUDA(w, cudaMemsetAsync(S.ih_keys.ptr, 0, (size_t(1) << ih_log2) * 8, st));
     HG_CUDA(w, cudaMemsetAsync(S.ih_vals.ptr, 0, (size_t(1) << ih_log2) * 4, st));
-    HG_CUDA(w, cudaMemsetAsync(S.resolved.ptr, 0, M * 4, st));
+    HG_CUDA(w, cudaMemsetAsync(S.J.ptr, 0xFF, size_t(M) * 8, st));
     OpView v{M, S.op_table.as<uint32_t>(), S.op_kind.as<uint32_t>(), S.op_cmd.as<uint32_t>(), S.op_level.as<uint32_t>(),
              S.u2t.as<uint32_t>(), S.key2.as<uint64_t>(), S.p2t.as<uint32_t>(), S.t2p.as<uint32_t>(), S.tfmin.as<uint32_t>(),
              w->d_tcount.as<uint32_t>(), S.ic_off.as<uint32_t>(), S.init_close.as<uint32_t>(),
              level_bits, cmd, S.home_cmd.as<uint32_t>(), S.opbase.as<uint32_t>(),
-             w->d_loc.as<uint64_t>(), S.J.as<uint64_t>(), S.resolved.as<uint32_t>(),
+             w->d_loc.as<uint64_t>(), S.J.as<uint64_t>(), S.trem.as<uint32_t>(), S.tapp.as<uint32_t>(),
              InstHash{S.ih_keys.as<unsigned long long>(), S.ih_vals.as<uint32_t>(), ih_log2}};
     k_resolve_all<<<blocks_for(M), 256, 0, st>>>(v, dc);
     ++launches;

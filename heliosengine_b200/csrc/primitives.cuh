@@ -107,63 +107,117 @@ inline int exclusive_scan_u32(const uint32_t* in, uint32_t* out, uint64_t n, uin
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Stable LSD radix sort.  A "chunk" = kSortChunk consecutive items owned by one warp; chunks are globally ordered,
-// items inside a chunk are ranked 32 at a time in order, so equal digits keep their relative order.
+// Stable LSD radix sort, 8 bits per pass, 3 launches per pass.
+// A CTA owns a tile of kSortTile consecutive items; inside the tile every warp owns kSortWarpItems consecutive items
+// held in registers and ranks them 32 at a time with __match_any_sync, so equal digits keep their input order.
+//   k_sort_hist     per-tile digit counts               -> counts[digit * ntiles + tile]
+//   k_sort_scan     one warp per digit row: exclusive prefix over the tiles in place + the row total
+//   k_sort_scatter  digit base (block scan of the 256 row totals) + row prefix + warp offsets -> stable scatter
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kSortWarps = 8;
 constexpr int kSortThreads = kSortWarps * 32;
-constexpr int kSortChunk = 1024;
+constexpr int kSortRounds = 8;                         // items per thread
+constexpr int kSortWarpItems = 32 * kSortRounds;       // 256
+constexpr int kSortTile = kSortWarps * kSortWarpItems; // 2048
+
+__device__ __forceinline__ void sort_load_digits(const uint64_t* __restrict__ keys, uint64_t n, uint64_t warp_base, int shift,
+                                                 uint32_t lane, uint64_t (&key)[kSortRounds], uint32_t (&digit)[kSortRounds]) {
+#pragma unroll
+  for (int r = 0; r < kSortRounds; ++r) {
+    const uint64_t i = warp_base + r * 32 + lane;
+    const bool valid = i < n;
+    key[r] = valid ? keys[i] : 0;
+    digit[r] = valid ? uint32_t((key[r] >> shift) & 0xFFu) : (0x100u + lane);  // invalid lanes: unique classes
+  }
+}
+
+// Per-warp digit histogram of the register-held items into h[256] (warp-private shared memory).
+__device__ __forceinline__ void sort_warp_hist(uint32_t* h, const uint32_t (&digit)[kSortRounds], uint32_t lane) {
+  for (int i = lane; i < 256; i += 32) h[i] = 0;
+  __syncwarp();
+#pragma unroll
+  for (int r = 0; r < kSortRounds; ++r) {
+    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, digit[r]);
+    if (digit[r] < 0x100u && lane == uint32_t(__ffs(peers) - 1)) h[digit[r]] += __popc(peers);
+    __syncwarp();
+  }
+}
 
 __global__ void __launch_bounds__(kSortThreads) k_sort_hist(const uint64_t* __restrict__ keys, uint64_t n, int shift,
-                                                            uint32_t nchunks, uint32_t* __restrict__ counts) {
+                                                            uint32_t ntiles, uint32_t* __restrict__ counts) {
   __shared__ uint32_t h[kSortWarps][256];
   const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-  for (int i = lane; i < 256; i += 32) h[wid][i] = 0;
-  __syncwarp();
-  const uint32_t chunk = blockIdx.x * kSortWarps + wid;
-  if (chunk < nchunks) {
-    const uint64_t base = uint64_t(chunk) * kSortChunk;
-#pragma unroll 4
-    for (int it = 0; it < kSortChunk / 32; ++it) {
-      const uint64_t i = base + it * 32 + lane;
-      if (i < n) atomicAdd(&h[wid][(keys[i] >> shift) & 0xFFu], 1u);
-    }
-    __syncwarp();
-    for (int d = lane; d < 256; d += 32) counts[size_t(d) * nchunks + chunk] = h[wid][d];
+  uint64_t key[kSortRounds];
+  uint32_t digit[kSortRounds];
+  sort_load_digits(keys, n, uint64_t(blockIdx.x) * kSortTile + wid * kSortWarpItems, shift, lane, key, digit);
+  sort_warp_hist(h[wid], digit, lane);
+  __syncthreads();
+  uint32_t c = 0;
+#pragma unroll
+  for (int w2 = 0; w2 < kSortWarps; ++w2) c += h[w2][threadIdx.x];
+  counts[size_t(threadIdx.x) * ntiles + blockIdx.x] = c;
+}
+
+// One warp per digit row: exclusive prefix over the row's ntiles counts (in place) and the row total.
+__global__ void __launch_bounds__(256) k_sort_scan(uint32_t* __restrict__ counts, uint32_t ntiles, uint32_t* __restrict__ rowtot) {
+  const uint32_t row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
+  if (row >= 256) return;
+  uint32_t* r = counts + size_t(row) * ntiles;
+  uint32_t running = 0;
+  for (uint32_t base = 0; base < ntiles; base += 32) {
+    const uint32_t i = base + lane;
+    const uint32_t v = i < ntiles ? r[i] : 0u;
+    const uint32_t inc = warp_incl_scan(v);
+    if (i < ntiles) r[i] = running + inc - v;
+    running += __shfl_sync(0xFFFFFFFFu, inc, 31);
   }
+  if (lane == 0) rowtot[row] = running;
 }
 
 __global__ void __launch_bounds__(kSortThreads) k_sort_scatter(const uint64_t* __restrict__ keys_in,
                                                                const uint32_t* __restrict__ vals_in,
                                                                uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-                                                               uint64_t n, int shift, uint32_t nchunks,
-                                                               const uint32_t* __restrict__ offsets) {
-  __shared__ uint32_t off[kSortWarps][256];
+                                                               uint64_t n, int shift, uint32_t ntiles,
+                                                               const uint32_t* __restrict__ counts,
+                                                               const uint32_t* __restrict__ rowtot) {
+  __shared__ uint32_t h[kSortWarps][256];
   const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-  const uint32_t chunk = blockIdx.x * kSortWarps + wid;
-  if (chunk >= nchunks) return;
-  for (int d = lane; d < 256; d += 32) off[wid][d] = offsets[size_t(d) * nchunks + chunk];
-  __syncwarp();
-  const uint64_t base = uint64_t(chunk) * kSortChunk;
-  for (int it = 0; it < kSortChunk / 32; ++it) {
-    const uint64_t i = base + it * 32 + lane;
-    if (base + it * 32 >= n) break;
-    const bool valid = i < n;
-    const uint64_t key = valid ? keys_in[i] : 0;
-    const uint32_t val = valid ? vals_in[i] : 0;
-    const uint32_t digit = valid ? uint32_t((key >> shift) & 0xFFu) : (0x100u + lane);  // invalid lanes: unique class
-    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, digit);
+  const uint64_t warp_base = uint64_t(blockIdx.x) * kSortTile + wid * kSortWarpItems;
+  uint64_t key[kSortRounds];
+  uint32_t digit[kSortRounds], val[kSortRounds];
+  sort_load_digits(keys_in, n, warp_base, shift, lane, key, digit);
+#pragma unroll
+  for (int r = 0; r < kSortRounds; ++r) {
+    const uint64_t i = warp_base + r * 32 + lane;
+    val[r] = i < n ? vals_in[i] : 0u;
+  }
+  sort_warp_hist(h[wid], digit, lane);
+  // digit base = exclusive scan of the 256 row totals (thread d owns digit d)
+  uint32_t total;
+  const uint32_t digit_base = block_excl_scan(rowtot[threadIdx.x], &total);
+  uint32_t base = digit_base + counts[size_t(threadIdx.x) * ntiles + blockIdx.x];
+#pragma unroll
+  for (int w2 = 0; w2 < kSortWarps; ++w2) {  // warp w2 of this tile starts its digit-d run at base
+    const uint32_t c = h[w2][threadIdx.x];
+    h[w2][threadIdx.x] = base;
+    base += c;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < kSortRounds; ++r) {
+    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, digit[r]);
     const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
     const uint32_t leader = __ffs(peers) - 1;
+    const bool valid = digit[r] < 0x100u;
     uint32_t b = 0;
     if (valid && lane == leader) {
-      b = off[wid][digit];
-      off[wid][digit] = b + __popc(peers);
+      b = h[wid][digit[r]];
+      h[wid][digit[r]] = b + __popc(peers);
     }
     b = __shfl_sync(0xFFFFFFFFu, b, leader);
     if (valid) {
-      keys_out[b + rank] = key;
-      vals_out[b + rank] = val;
+      keys_out[b + rank] = key[r];
+      vals_out[b + rank] = val[r];
     }
     __syncwarp();
   }
@@ -172,26 +226,25 @@ __global__ void __launch_bounds__(kSortThreads) k_sort_scatter(const uint64_t* _
 struct SortScratch {
   uint64_t* keys_alt;   // n
   uint32_t* vals_alt;   // n
-  uint32_t* counts;     // 256 * nchunks
-  uint32_t* partials;   // ceil(256*nchunks / kScanTile) + 1
+  uint32_t* counts;     // 256 * sort_tiles(n)
+  uint32_t* rowtot;     // 256
 };
 
-inline uint32_t sort_chunks(uint64_t n) { return uint32_t((n + kSortChunk - 1) / kSortChunk); }
+inline uint32_t sort_tiles(uint64_t n) { return uint32_t((n + kSortTile - 1) / kSortTile); }
 
 // Sorts (keys, vals) by key bits [0, nbits) ascending, stable.  The result ends in (keys, vals) — an odd number of
 // passes is evened out by a final copy.  Returns the number of kernels launched.
 inline int radix_sort_pairs(uint64_t* keys, uint32_t* vals, uint64_t n, int nbits, const SortScratch& sc, cudaStream_t s) {
   if (n <= 1 || nbits <= 0) return 0;
-  const uint32_t nchunks = sort_chunks(n);
-  const uint32_t blocks = (nchunks + kSortWarps - 1) / kSortWarps;
+  const uint32_t ntiles = sort_tiles(n);
   uint64_t* kin = keys; uint32_t* vin = vals;
   uint64_t* kout = sc.keys_alt; uint32_t* vout = sc.vals_alt;
   int launches = 0;
   for (int shift = 0; shift < nbits; shift += 8) {
-    k_sort_hist<<<blocks, kSortThreads, 0, s>>>(kin, n, shift, nchunks, sc.counts);
-    launches += 1 + exclusive_scan_u32(sc.counts, sc.counts, uint64_t(256) * nchunks, sc.partials, nullptr, s);
-    k_sort_scatter<<<blocks, kSortThreads, 0, s>>>(kin, vin, kout, vout, n, shift, nchunks, sc.counts);
-    ++launches;
+    k_sort_hist<<<ntiles, kSortThreads, 0, s>>>(kin, n, shift, ntiles, sc.counts);
+    k_sort_scan<<<32, 256, 0, s>>>(sc.counts, ntiles, sc.rowtot);
+    k_sort_scatter<<<ntiles, kSortThreads, 0, s>>>(kin, vin, kout, vout, n, shift, ntiles, sc.counts, sc.rowtot);
+    launches += 3;
     uint64_t* tk = kin; kin = kout; kout = tk;
     uint32_t* tv = vin; vin = vout; vout = tv;
   }
