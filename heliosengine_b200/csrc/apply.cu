@@ -131,7 +131,7 @@ struct helios_gpu_world::ApplyScratch {
   DevBuf key2, p2t, t2p;
   DevBuf J;
   DevBuf ih_keys, ih_vals;
-  DevBuf ch_table, ch_slot, ch_ent, stage;
+  DevBuf ch_slot, ch_ent, stage;
   DevBuf coffset;  // uint32[64] byte offset of each component inside a staged row
   uint32_t stage_stride = 0;
   size_t stride_comps = 0;
@@ -394,32 +394,23 @@ __global__ void k_gather_ops(uint32_t M, const uint64_t* __restrict__ skey, cons
 __global__ void k_levels(uint32_t M, const uint32_t* __restrict__ op_table, const uint32_t* __restrict__ op_kind,
                          const uint32_t* __restrict__ delta, const uint32_t* __restrict__ ex,
                          const uint32_t* __restrict__ tseg, const uint32_t* __restrict__ tcount0,
-                         const uint32_t* __restrict__ trem, uint32_t* __restrict__ op_level, uint32_t* __restrict__ tfmin,
+                         const uint32_t* __restrict__ trem, uint32_t* __restrict__ op_level,
                          uint64_t* __restrict__ key2, uint32_t* __restrict__ val2, int level_bits) {
   const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool in = j < M;
-  uint32_t t = 0xFFFFFFFFu, level = 0xFFFFFFFFu;
-  bool is_remove = false;
-  if (in) {
-    t = op_table[j];
-    const uint32_t size_after = tcount0[t] + (ex[j] + delta[j] - ex[tseg[t]]);
-    is_remove = op_kind[j] == 0;
-    level = is_remove ? size_after : size_after - 1;
-    op_level[j] = level;
-    key2[j] = (uint64_t(t) << level_bits) | (level - (tcount0[t] - trem[t]));
-    val2[j] = j;
-  }
-  // min closed level per table: ops are sorted by table, so a warp usually holds one or two tables
-  const uint32_t tt = (in && is_remove) ? t : 0xFFFFFFFFu;
-  const uint32_t peers = __match_any_sync(0xFFFFFFFFu, tt);
-  const uint32_t mn = __reduce_min_sync(peers, level);
-  if (tt != 0xFFFFFFFFu && (threadIdx.x & 31u) == uint32_t(__ffs(peers) - 1)) atomicMin(&tfmin[tt], mn);
+  if (j >= M) return;
+  const uint32_t t = op_table[j];
+  const uint32_t size_after = tcount0[t] + (ex[j] + delta[j] - ex[tseg[t]]);
+  const uint32_t level = op_kind[j] ? size_after - 1 : size_after;
+  op_level[j] = level;
+  key2[j] = (uint64_t(t) << level_bits) | (level - (tcount0[t] - trem[t]));  // u32 wrap-around is consistent
+  val2[j] = j;
 }
 
-// Offsets of the per-table windows of init_close: slots [tfmin[t], count0[t]) of table t are the initially occupied
-// slots that some Remove closes during the batch.
+// Offsets of the per-table windows of init_close: slots [tlow[t], count0[t]) with tlow = max(count0 - #removes, 0) — the
+// lowest size table t can reach in this batch — cover every initially occupied slot that some Remove can close.
 __global__ void __launch_bounds__(1024) k_ic_offsets(uint32_t ntables, const uint32_t* __restrict__ tcount0,
-                                                     const uint32_t* __restrict__ tfmin, uint32_t* __restrict__ ic_off) {
+                                                     const uint32_t* __restrict__ trem, uint32_t* __restrict__ tlow,
+                                                     uint32_t* __restrict__ ic_off) {
   __shared__ uint32_t s_warp[32];
   __shared__ uint32_t s_running;
   if (threadIdx.x == 0) s_running = 0;
@@ -428,7 +419,11 @@ __global__ void __launch_bounds__(1024) k_ic_offsets(uint32_t ntables, const uin
   for (uint32_t base = 0; base < ntables; base += blockDim.x) {
     const uint32_t t = base + threadIdx.x;
     uint32_t v = 0;
-    if (t < ntables && tfmin[t] < tcount0[t]) v = tcount0[t] - tfmin[t];
+    if (t < ntables) {
+      const uint32_t c0 = tcount0[t], r = trem[t];
+      tlow[t] = c0 > r ? c0 - r : 0u;
+      v = c0 - tlow[t];
+    }
     uint32_t inc = prim::warp_incl_scan(v);
     if (lane == 31) s_warp[wid] = inc;
     __syncthreads();
@@ -580,43 +575,41 @@ __device__ __forceinline__ uint32_t slot_of(const OpView& v, uint64_t I) {
   return (I & kInstA) ? v.op_level[uint32_t(I)] : uint32_t(I);
 }
 
-// Final contents: every surviving slot whose occupant changed.
-__global__ void k_final_slots(OpView v, helios_gpu_entity_t* const* tents, uint32_t* __restrict__ ch_table,
-                              uint32_t* __restrict__ ch_slot, helios_gpu_entity_t* __restrict__ ch_ent, Counters* counters) {
+// Final contents: every surviving slot whose occupant changed, recorded per op (ch_slot[j] == kNone: op j writes no row).
+// Keeping the records in op order (table, then time) makes the appended rows of a growing table land on consecutive
+// slots, so the row mover's stores coalesce.
+__global__ void k_final_slots(OpView v, helios_gpu_entity_t* const* tents, uint32_t* __restrict__ ch_slot,
+                              helios_gpu_entity_t* __restrict__ ch_ent, Counters* counters) {
   const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= v.M) return;
-  uint32_t slot = 0;
+  uint32_t slot = kNone;
   helios_gpu_entity_t e = 0;
-  bool emit = false;
-  if (v.op_kind[j]) {  // Append: a surviving, never re-filled instance keeps its opener
-    const uint64_t I = inst_append(j);
-    if (close_of(v, I) == kNone && inst_get(v.ih, I) == 0) {
-      emit = true;
-      slot = v.op_level[j];
-      e = v.cmd[v.op_cmd[j]].entity;
+  if (j < v.M) {
+    if (v.op_kind[j]) {  // Append: a surviving, never re-filled instance keeps its opener
+      const uint64_t I = inst_append(j);
+      if (close_of(v, I) == kNone && inst_get(v.ih, I) == 0) {
+        slot = v.op_level[j];
+        e = v.cmd[v.op_cmd[j]].entity;
+      }
+    } else {             // Remove: the LAST move into a surviving instance decides its occupant
+      const uint64_t I = v.J[j];
+      if (I != closed_by(v, j) && inst_get(v.ih, I) == j + 1 && close_of(v, I) == kNone) {
+        slot = slot_of(v, I);
+        e = mover_of(v, j, tents);
+      }
     }
-  } else {             // Remove: the LAST move into a surviving instance decides its occupant
-    const uint64_t I = v.J[j];
-    if (I != closed_by(v, j) && inst_get(v.ih, I) == j + 1 && close_of(v, I) == kNone) {
-      emit = true;
-      slot = slot_of(v, I);
-      e = mover_of(v, j, tents);
-    }
+    ch_slot[j] = slot;
+    ch_ent[j] = e;
   }
-  if (emit) {
-    const uint32_t i = atomicAdd(&counters->n_changed, 1u);
-    ch_table[i] = v.op_table[j];
-    ch_slot[i] = slot;
-    ch_ent[i] = e;
-  }
+  const uint32_t n = __popc(__ballot_sync(0xFFFFFFFFu, slot != kNone));
+  if ((threadIdx.x & 31u) == 0 && n) atomicAdd(&counters->n_changed, n);
 }
 
 // ================================================================================================================
 // Stage 5 — row mover (gather → staging → scatter), destroy bookkeeping, payload patch, count update
 // ================================================================================================================
 struct MoveArgs {
-  uint32_t n;
-  const uint32_t* ch_table;
+  uint32_t M;
+  const uint32_t* op_table;
   const uint32_t* ch_slot;
   const helios_gpu_entity_t* ch_ent;
   uint64_t* loc;
@@ -638,51 +631,77 @@ __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, uin
   }
 }
 
-// Component values the entity carries over from where it lived BEFORE the batch (shared columns of MigrateEntity,
-// manager.hpp:1912-1925, and the swapped row of Archetype::Remove, archetype.hpp:418-431).
-__global__ void k_gather_rows(MoveArgs a) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+// Row mover.  A 256-thread CTA takes 32 consecutive op records at a time: lane = record, warp = component position, so
+// the 8 warps copy 8 components of the 32 rows concurrently and one warp instruction touches one column for 32
+// consecutive records (consecutive destination slots for the appended rows of a growing table).
+//   kScatter == false: component values the entity carries over from where it lived BEFORE the batch (shared columns of
+//                      MigrateEntity, manager.hpp:1912-1925; swapped row of Archetype::Remove, archetype.hpp:418-431)
+//                      are gathered into the staging buffer;
+//   kScatter == true : staged rows are written to their final slots (all gathers finished: no read/write hazard).
+template <bool kScatter>
+__global__ void __launch_bounds__(256) k_move_rows(MoveArgs a) {
+  __shared__ uint32_t s_slot[32], s_t[32], s_t0[32], s_r0[32];
+  __shared__ uint64_t s_mask[32];
+  __shared__ helios_gpu_entity_t s_ent[32];
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
   uint32_t bytes = 0;
-  if (i < a.n) {
-    const uint64_t l0 = a.loc[ent_index(a.ch_ent[i])];
-    const uint32_t t0 = uint32_t(l0 >> 32), r0 = uint32_t(l0);
-    uint64_t m = a.tmask[a.ch_table[i]] & a.tmask[t0];
-    uint8_t* out = a.stage + size_t(i) * a.stride;
-    bytes = 8;
-    while (m) {
+  const uint32_t groups = (a.M + 31u) / 32u;
+  for (uint32_t g = blockIdx.x; g < groups; g += gridDim.x) {
+    const uint32_t j = g * 32u + lane;
+    __syncthreads();
+    if (wid == 0) {
+      uint32_t slot = j < a.M ? a.ch_slot[j] : kNone;
+      if (slot != kNone) {
+        const helios_gpu_entity_t e = a.ch_ent[j];
+        const uint64_t l0 = a.loc[ent_index(e)];
+        const uint32_t t = a.op_table[j];
+        s_ent[lane] = e;
+        s_t[lane] = t;
+        s_t0[lane] = uint32_t(l0 >> 32);
+        s_r0[lane] = uint32_t(l0);
+        s_mask[lane] = a.tmask[t] & a.tmask[uint32_t(l0 >> 32)];
+      }
+      s_slot[lane] = slot;
+    }
+    __syncthreads();
+    const uint32_t slot = s_slot[lane];
+    if (slot == kNone) continue;
+    uint64_t m = s_mask[lane];
+    const uint32_t t = s_t[lane], t0 = s_t0[lane], r0 = s_r0[lane];
+    uint8_t* st = a.stage + size_t(j) * a.stride;
+    for (uint32_t pos = 0; m; ++pos) {
       const int s = __ffsll(static_cast<long long>(m)) - 1;
       m &= m - 1;
+      if ((pos & 7u) != wid) continue;
       const uint32_t sz = a.csize[s];
-      copy_bytes(out + a.coffset[s], static_cast<const uint8_t*>(a.tcols[size_t(t0) * 64 + s]) + size_t(r0) * sz, sz);
-      bytes += sz;
+      if constexpr (kScatter) {
+        copy_bytes(static_cast<uint8_t*>(a.tcols[size_t(t) * 64 + s]) + size_t(slot) * sz, st + a.coffset[s], sz);
+      } else {
+        copy_bytes(st + a.coffset[s], static_cast<const uint8_t*>(a.tcols[size_t(t0) * 64 + s]) + size_t(r0) * sz, sz);
+        bytes += sz;
+      }
+    }
+    if (wid == 0) {
+      if constexpr (kScatter) a.tents[t][slot] = s_ent[lane];
+      else bytes += 8;
     }
   }
-  bytes = __reduce_add_sync(0xFFFFFFFFu, bytes);  // one statistics atomic per warp
-  if ((threadIdx.x & 31u) == 0 && bytes) atomicAdd(&a.counters->moved_bytes, 2ull * bytes);
-}
-
-__global__ void k_scatter_rows(MoveArgs a) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= a.n) return;
-  const helios_gpu_entity_t e = a.ch_ent[i];
-  const uint32_t t = a.ch_table[i], r = a.ch_slot[i];
-  const uint64_t l0 = a.loc[ent_index(e)];
-  uint64_t m = a.tmask[t] & a.tmask[uint32_t(l0 >> 32)];
-  const uint8_t* in = a.stage + size_t(i) * a.stride;
-  while (m) {
-    const int s = __ffsll(static_cast<long long>(m)) - 1;
-    m &= m - 1;
-    const uint32_t sz = a.csize[s];
-    copy_bytes(static_cast<uint8_t*>(a.tcols[size_t(t) * 64 + s]) + size_t(r) * sz, in + a.coffset[s], sz);
+  if constexpr (!kScatter) {  // statistics: one atomic per CTA
+    __shared__ uint32_t s_bytes;
+    if (threadIdx.x == 0) s_bytes = 0;
+    __syncthreads();
+    bytes = __reduce_add_sync(0xFFFFFFFFu, bytes);
+    if (lane == 0 && bytes) atomicAdd(&s_bytes, bytes);
+    __syncthreads();
+    if (threadIdx.x == 0 && s_bytes) atomicAdd(&a.counters->moved_bytes, 2ull * s_bytes);
   }
-  a.tents[t][r] = e;
 }
 
 // Locations are rewritten only after every gather/scatter thread has read the pre-batch ones.
-__global__ void k_update_locations(uint32_t n, const uint32_t* __restrict__ ch_table, const uint32_t* __restrict__ ch_slot,
+__global__ void k_update_locations(uint32_t M, const uint32_t* __restrict__ op_table, const uint32_t* __restrict__ ch_slot,
                                    const helios_gpu_entity_t* __restrict__ ch_ent, uint64_t* __restrict__ loc) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) loc[ent_index(ch_ent[i])] = (uint64_t(ch_table[i]) << 32) | ch_slot[i];
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < M && ch_slot[j] != kNone) loc[ent_index(ch_ent[j])] = (uint64_t(op_table[j]) << 32) | ch_slot[j];
 }
 
 // EntityManager::Destroy (entity/manager.hpp:307-320): generation++, index pushed on the free list in command order.
@@ -924,7 +943,6 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
   }
 
   // ---- stage 4: table op sequences, slot instances, move resolution ------------------------------------------------
-  uint32_t n_changed = 0;
   if (M) {
     NEED(S.u_kind, M * 4); NEED(S.u_cmd, M * 4);
     NEED(S.op_table, M * 4); NEED(S.op_kind, M * 4); NEED(S.op_cmd, M * 4); NEED(S.op_level, M * 4);
@@ -938,7 +956,6 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     const int table_bits = prim::bits_for(nt ? nt - 1 : 0);
     launches += prim::radix_sort_pairs(S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), M, table_bits, ss, st);
     HG_CUDA(w, cudaMemsetAsync(S.tseg.ptr, 0xFF, nt * 4, st));
-    HG_CUDA(w, cudaMemsetAsync(S.tfmin.ptr, 0xFF, nt * 4, st));
     HG_CUDA(w, cudaMemsetAsync(S.init_close.ptr, 0xFF, size_t(M) * 4, st));
     k_gather_ops<<<blocks_for(M), 256, 0, st>>>(M, S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), S.u_kind.as<uint32_t>(),
                                                 S.u_cmd.as<uint32_t>(), S.op_table.as<uint32_t>(), S.op_kind.as<uint32_t>(),
@@ -948,11 +965,11 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     const int level_bits = prim::bits_for(uint64_t(max_ops) + 1);
     k_levels<<<blocks_for(M), 256, 0, st>>>(M, S.op_table.as<uint32_t>(), S.op_kind.as<uint32_t>(), S.delta.as<uint32_t>(),
                                             S.ex.as<uint32_t>(), S.tseg.as<uint32_t>(), w->d_tcount.as<uint32_t>(),
-                                            S.trem.as<uint32_t>(), S.op_level.as<uint32_t>(), S.tfmin.as<uint32_t>(),
+                                            S.trem.as<uint32_t>(), S.op_level.as<uint32_t>(),
                                             S.key2.as<uint64_t>(), S.p2t.as<uint32_t>(), level_bits);
     ++launches;
     launches += prim::radix_sort_pairs(S.key2.as<uint64_t>(), S.p2t.as<uint32_t>(), M, level_bits + table_bits, ss, st);
-    k_ic_offsets<<<1, 1024, 0, st>>>(nt, w->d_tcount.as<uint32_t>(), S.tfmin.as<uint32_t>(), S.ic_off.as<uint32_t>());
+    k_ic_offsets<<<1, 1024, 0, st>>>(nt, w->d_tcount.as<uint32_t>(), S.trem.as<uint32_t>(), S.tfmin.as<uint32_t>(), S.ic_off.as<uint32_t>());
     k_invert<<<blocks_for(M), 256, 0, st>>>(M, S.p2t.as<uint32_t>(), S.key2.as<uint64_t>(), S.op_kind.as<uint32_t>(),
                                             S.op_table.as<uint32_t>(), S.op_level.as<uint32_t>(), S.tfmin.as<uint32_t>(),
                                             S.ic_off.as<uint32_t>(), S.t2p.as<uint32_t>(), S.init_close.as<uint32_t>());
@@ -974,26 +991,20 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     k_resolve_all<<<blocks_for(M), 256, 0, st>>>(v, dc);
     ++launches;
 
-    NEED(S.ch_table, M * 4); NEED(S.ch_slot, M * 4); NEED(S.ch_ent, M * 8);
-    k_final_slots<<<blocks_for(M), 256, 0, st>>>(v, w->d_tents.as<helios_gpu_entity_t*>(), S.ch_table.as<uint32_t>(),
-                                                 S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(), dc);
-    ++launches;
-    HG_CUDA(w, cudaMemcpyAsync(&hc, dc, sizeof(hc), cudaMemcpyDeviceToHost, st));
-    HG_CUDA(w, cudaStreamSynchronize(st));
-    n_changed = hc.n_changed;
-    w->last_stats.resolve_rounds = hc.unresolved;
-    if (n_changed) {
-      NEED(S.stage, size_t(n_changed) * S.stage_stride);
-      MoveArgs ma{n_changed, S.ch_table.as<uint32_t>(), S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(),
-                  w->d_loc.as<uint64_t>(), w->d_tmask.as<uint64_t>(), w->d_tcols.as<void*>(),
-                  w->d_tents.as<helios_gpu_entity_t*>(), w->d_csize.as<uint32_t>(), S.coffset.as<uint32_t>(),
-                  S.stage.as<uint8_t>(), S.stage_stride, dc};
-      k_gather_rows<<<blocks_for(n_changed), 256, 0, st>>>(ma);
-      k_scatter_rows<<<blocks_for(n_changed), 256, 0, st>>>(ma);
-      k_update_locations<<<blocks_for(n_changed), 256, 0, st>>>(n_changed, S.ch_table.as<uint32_t>(), S.ch_slot.as<uint32_t>(),
-                                                                S.ch_ent.as<helios_gpu_entity_t>(), w->d_loc.as<uint64_t>());
-      launches += 3;
-    }
+    NEED(S.ch_slot, M * 4); NEED(S.ch_ent, M * 8);
+    k_final_slots<<<blocks_for(M), 256, 0, st>>>(v, w->d_tents.as<helios_gpu_entity_t*>(), S.ch_slot.as<uint32_t>(),
+                                                 S.ch_ent.as<helios_gpu_entity_t>(), dc);
+    NEED(S.stage, size_t(M) * S.stage_stride);
+    MoveArgs ma{M, S.op_table.as<uint32_t>(), S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(),
+                w->d_loc.as<uint64_t>(), w->d_tmask.as<uint64_t>(), w->d_tcols.as<void*>(),
+                w->d_tents.as<helios_gpu_entity_t*>(), w->d_csize.as<uint32_t>(), S.coffset.as<uint32_t>(),
+                S.stage.as<uint8_t>(), S.stage_stride, dc};
+    const uint32_t mover_grid = std::min<uint32_t>((M + 31u) / 32u, uint32_t(w->sm_count) * 8u);
+    k_move_rows<false><<<mover_grid, 256, 0, st>>>(ma);
+    k_move_rows<true><<<mover_grid, 256, 0, st>>>(ma);
+    k_update_locations<<<blocks_for(M), 256, 0, st>>>(M, S.op_table.as<uint32_t>(), S.ch_slot.as<uint32_t>(),
+                                                      S.ch_ent.as<helios_gpu_entity_t>(), w->d_loc.as<uint64_t>());
+    launches += 4;
   }
 
   // ---- stage 5: destroys, payload patch, counts ------------------------------------------------------------------
@@ -1014,7 +1025,8 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     w->free_cursor = int64_t(w->free_count);  // Destroy sets free_cursor_ = free_indices_.size() (manager.hpp:317-318)
     w->live_count -= hc.n_destroy;
   }
-  w->last_stats.moved_rows = n_changed;
+  w->last_stats.moved_rows = hc.n_changed;
+  w->last_stats.resolve_rounds = hc.unresolved;
   w->last_stats.moved_bytes = hc.moved_bytes;
   w->launches += launches;
   return HELIOS_GPU_OK;

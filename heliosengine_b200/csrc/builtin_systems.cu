@@ -160,13 +160,13 @@ int32_t launch_consume(const helios_gpu_system_ctx* ctx) {
 // ---- "stats": Query<const Health&> → resource[0] (u64) += Σ hp  (integer, order independent) -----------------
 struct StatsBody {
   unsigned long long* acc;
-  __device__ void operator()(const Row&, Health& h) const {
-    // warp-level reduction first, one atomic per warp (blackwell guide §12)
-    long long v = h.hp;
-    const uint32_t m = __activemask();
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(m, v, o);
-    if ((threadIdx.x & 31u) == 0 && m == 0xFFFFFFFFu) atomicAdd(acc, (unsigned long long)v);
-    else if (m != 0xFFFFFFFFu) atomicAdd(acc, (unsigned long long)(long long)h.hp);
+  long long local = 0;  // per-thread partial sum (the kernel holds a private copy of the body per thread)
+  __device__ void operator()(const Row&, Health& h) { local += h.hp; }
+  __device__ void finish() {
+    // every thread of the CTA reaches the epilogue: full-warp reduction, then one atomic per warp
+    long long v = local;
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, o);
+    if ((threadIdx.x & 31u) == 0 && v != 0) atomicAdd(acc, (unsigned long long)v);
   }
 };
 __global__ void k_zero_u64(unsigned long long* p, int n) {

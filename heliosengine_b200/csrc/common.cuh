@@ -35,9 +35,8 @@ namespace hgpu {
     if (_s != HELIOS_GPU_OK) return _s; \
   } while (0)
 
-// Growable device allocation.  Growth preserves the first `keep` bytes with a D2D copy on `stream`;
-// the old block is released with cudaFreeAsync-like ordering by freeing after the copy is enqueued
-// (cudaFree synchronises implicitly, which is acceptable at the structural sync points where growth happens).
+// Growable device allocation.  Growth preserves the first `keep` bytes with a D2D copy on `stream`; allocation, copy and
+// release of the old block are all stream-ordered (cudaMallocAsync / cudaFreeAsync).
 struct DevBuf {
   void* ptr = nullptr;
   size_t bytes = 0;
@@ -67,16 +66,16 @@ struct DevBuf {
     size_t cap = want;
     if (geometric && bytes) cap = want > bytes + bytes / 2 ? want : bytes + bytes / 2;
     cap = (cap + 255) & ~size_t(255);
+    // Stream-ordered allocation from the device's default memory pool (release threshold raised at world creation):
+    // growing a table column costs no device-wide synchronisation, the old block is recycled by the pool.
     void* np = nullptr;
-    cudaError_t e = cudaMalloc(&np, cap);
+    cudaError_t e = cudaMallocAsync(&np, cap, stream);
     if (e != cudaSuccess) return e;
     if (ptr && keep) {
       e = cudaMemcpyAsync(np, ptr, keep, cudaMemcpyDeviceToDevice, stream);
-      if (e != cudaSuccess) { cudaFree(np); return e; }
-      e = cudaStreamSynchronize(stream);
-      if (e != cudaSuccess) { cudaFree(np); return e; }
+      if (e != cudaSuccess) { cudaFreeAsync(np, stream); return e; }
     }
-    if (ptr) cudaFree(ptr);
+    if (ptr) cudaFreeAsync(ptr, stream);
     ptr = np;
     bytes = cap;
     return cudaSuccess;

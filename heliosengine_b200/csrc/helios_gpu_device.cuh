@@ -269,6 +269,9 @@ __global__ void __launch_bounds__(kBlock) for_each_kernel(const helios_gpu_match
     const auto cols = detail::typed_columns<Cs...>(bases, cuda::std::make_index_sequence<N>{});
     process_tile<kWriteMask, kWithEntity, Body, Cs...>(tr, cols, body);
   }
+  // Optional per-thread epilogue: a body that accumulates into its own members (each thread holds a private copy)
+  // folds them here once — e.g. one warp-reduced atomic per warp instead of one per row.
+  if constexpr (requires { body.finish(); }) body.finish();
 }
 
 // for_each_kernel_view: same visit over a MATERIALISED view (worlds with more than kFusedMaxTables tables).
@@ -308,6 +311,7 @@ __global__ void __launch_bounds__(kBlock) for_each_kernel_view(const helios_gpu_
     const auto cols = detail::typed_columns<Cs...>(bases, cuda::std::make_index_sequence<N>{});
     process_tile<kWriteMask, kWithEntity, Body, Cs...>(tr, cols, body);
   }
+  if constexpr (requires { body.finish(); }) body.finish();
 }
 
 // Host launcher: grid = one resident wave (SM count x occupancy), so CTAs stay put and stride over tiles.

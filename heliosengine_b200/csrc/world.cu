@@ -155,6 +155,13 @@ int32_t helios_gpu_world_create(const helios_gpu_world_config* cfg, helios_gpu_w
   }
   w->own_stream = true;
   cudaDeviceGetAttribute(&w->sm_count, cudaDevAttrMultiProcessorCount, w->device);
+  {  // keep freed blocks cached in the default pool instead of returning them to the driver at every synchronisation
+    cudaMemPool_t pool = nullptr;
+    if (cudaDeviceGetDefaultMemPool(&pool, w->device) == cudaSuccess && pool) {
+      uint64_t threshold = ~0ull;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+    }
+  }
   *out = w;
   HG_CUDA(w, w->d_csize.reserve(64 * 4, 0, w->stream, false));
   HG_CUDA(w, cudaMemsetAsync(w->d_csize.ptr, 0, 64 * 4, w->stream));
