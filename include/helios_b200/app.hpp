@@ -1,0 +1,159 @@
+// helios_b200/app.hpp — the slice of helios::app the GPU hot path plugs into (header-only, C++20).
+//
+// Mirrors (paths relative to /root/reference/src/app/): Plugin (include/helios/app/plugin.hpp:14-62), the dynamic
+// plugin C ABI `helios_create_plugin` / `helios_plugin_type_id` + PluginTypeExport
+// (include/helios/app/dynamic_plugin.hpp:27,34-36,84-88), schedule labels kPreUpdate/kUpdate/kPostUpdate
+// (include/helios/app/schedules.hpp:44-146), App::AddPlugin/AddSystem/Initialize/Update/Run
+// (include/helios/app/application.hpp:215-448, src/application.cpp:131-320) and SubApp (include/helios/app/sub_app.hpp).
+// Only what drives the ECS hot path is present: one main world on one GPU, labelled schedules run in label order, then
+// World::Update() once per frame (world.hpp:950-955).  Windowing, asset, logging and async-executor plumbing of the
+// reference App are outside the hot path and are not mirrored.
+#pragma once
+
+#include <chrono>
+#include <map>
+#include <memory>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "ecs.hpp"
+
+namespace helios::app {
+
+class App;
+
+// plugin.hpp:14-62 — same virtual interface, same order, so the vtable layout matches under the Itanium ABI.
+class Plugin {
+public:
+  virtual ~Plugin() = default;
+  virtual void Build(App& app) = 0;
+  virtual void Finish(App& /*app*/) {}
+  virtual void Destroy(App& /*app*/) {}
+  virtual void Poll(App& /*app*/) {}
+  [[nodiscard]] virtual bool IsReady(const App& /*app*/) const noexcept { return true; }
+};
+
+// dynamic_plugin.hpp:34-36
+struct PluginTypeExport {
+  uint64_t hash;
+  const char* qualified_name;
+};
+inline constexpr const char* kDefaultCreateSymbol = "helios_create_plugin";      // dynamic_plugin.hpp:27
+inline constexpr const char* kDefaultPluginIdSymbol = "helios_plugin_type_id";
+
+// schedules.hpp:44-146 — the per-frame labels the hot path uses, in execution order.
+enum class ScheduleLabel : int { kPreUpdate = 0, kUpdate = 1, kPostUpdate = 2 };
+inline constexpr ScheduleLabel kPreUpdate = ScheduleLabel::kPreUpdate;
+inline constexpr ScheduleLabel kUpdate = ScheduleLabel::kUpdate;
+inline constexpr ScheduleLabel kPostUpdate = ScheduleLabel::kPostUpdate;
+
+enum class AppExitCode : int { kSuccess = 0, kFailure = 1 };
+
+// sub_app.hpp — a world of its own plus labelled schedules; the main app is the first sub-app.
+class SubApp {
+public:
+  explicit SubApp(int device = 0, uint32_t entity_capacity = 0) : world_(device, entity_capacity) {}
+  ecs::World& GetWorld() noexcept { return world_; }
+  ecs::Schedule& GetSchedule(ScheduleLabel label) {
+    auto it = schedules_.find(label);
+    if (it == schedules_.end()) {
+      static const char* names[] = {"PreUpdate", "Update", "PostUpdate"};
+      it = schedules_.emplace(label, std::make_unique<ecs::Schedule>(world_, names[static_cast<int>(label)])).first;
+    }
+    return *it->second;
+  }
+  void Build() {
+    for (auto& [l, s] : schedules_) s->Build();
+  }
+  // One frame of this sub-app: every schedule in label order (RunAndWait = run + ApplyDeferred), then World::Update.
+  void Update() {
+    for (auto& [l, s] : schedules_) s->RunAndWait();
+    world_.Update();
+  }
+  void SetExecutor(ecs::ExecutorKind kind) {
+    for (auto& [l, s] : schedules_) s->SetExecutor(kind);
+    kind_ = kind;
+  }
+
+private:
+  ecs::World world_;  // declared first: schedules (and their queries) are destroyed before the world
+  std::map<ScheduleLabel, std::unique_ptr<ecs::Schedule>> schedules_;
+  ecs::ExecutorKind kind_ = ecs::ExecutorKind::kMultiThreaded;
+};
+
+class App {
+public:
+  explicit App(int device = 0, uint32_t entity_capacity = 0) : main_(device, entity_capacity) {}
+  ~App() {
+    for (auto it = plugins_.rbegin(); it != plugins_.rend(); ++it) (*it)->Destroy(*this);  // application.cpp DestroyPlugins
+  }
+
+  ecs::World& GetWorld() noexcept { return main_.GetWorld(); }
+  SubApp& GetMainSubApp() noexcept { return main_; }
+
+  // application.hpp AddPlugin: the app takes ownership (dynamic_plugin.hpp:583 `plugin_.reset(raw_plugin)`).
+  App& AddPlugin(std::unique_ptr<Plugin> plugin) {
+    plugins_.push_back(std::move(plugin));
+    return *this;
+  }
+  template <typename P, typename... A>
+  App& AddPlugins(A&&... args) { return AddPlugin(std::make_unique<P>(std::forward<A>(args)...)); }
+
+  // application.hpp:356-380 AddSystem(label, system) for GPU systems.
+  template <typename Q>
+  ecs::Schedule::SystemHandle AddSystem(ScheduleLabel label, const std::string& name, helios_gpu_system_fn launch,
+                                        const ecs::GpuSystemOptions& opt = {}) {
+    return main_.GetSchedule(label).AddGpu<Q>(name, launch, opt);
+  }
+  ecs::Schedule::SystemHandle AddSystem(ScheduleLabel label, const std::string& name, helios_gpu_system_fn launch,
+                                        const ecs::GpuSystemOptions& opt = {}) {
+    return main_.GetSchedule(label).AddGpu(name, launch, opt);
+  }
+
+  // application.cpp:131-320: Build every plugin, poll until all are ready (50 us -> 8 ms back-off, :24-25,209-229),
+  // Finish, build the schedules.
+  void Initialize() {
+    if (initialized_) return;
+    for (auto& p : plugins_) p->Build(*this);
+    auto wait = std::chrono::microseconds(50);
+    for (;;) {
+      bool ready = true;
+      for (auto& p : plugins_) {
+        p->Poll(*this);
+        ready = ready && p->IsReady(*this);
+      }
+      if (ready) break;
+      std::this_thread::sleep_for(wait);
+      if (wait < std::chrono::milliseconds(8)) wait *= 2;
+    }
+    for (auto& p : plugins_) p->Finish(*this);
+    main_.Build();
+    initialized_ = true;
+  }
+  void Update() {
+    Initialize();
+    main_.Update();
+    ++frame_;
+  }
+  // Runs `frames` frames (the reference runs until an AppExit message; a frame budget is the headless equivalent).
+  AppExitCode Run(uint64_t frames) {
+    for (uint64_t i = 0; i < frames; ++i) Update();
+    return AppExitCode::kSuccess;
+  }
+  uint64_t FrameCount() const noexcept { return frame_; }
+
+private:
+  SubApp main_;  // declared first: destroyed after the plugins
+  std::vector<std::unique_ptr<Plugin>> plugins_;
+  bool initialized_ = false;
+  uint64_t frame_ = 0;
+};
+
+}  // namespace helios::app
+
+// The two symbols a dynamic plugin library exports (dynamic_plugin.hpp:84-88).
+extern "C" {
+HELIOS_GPU_API helios::app::Plugin* helios_create_plugin();
+HELIOS_GPU_API const helios::app::PluginTypeExport* helios_plugin_type_id();
+}

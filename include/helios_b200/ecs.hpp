@@ -17,6 +17,7 @@
 
 #include <cstdint>
 #include <cstring>
+#include <memory>
 #include <span>
 #include <stdexcept>
 #include <string>
@@ -154,3 +155,365 @@ private:
   World* world_;
   helios_gpu_query* q_ = nullptr;
 };
+
+// ---- World (world.hpp:80-1196) ----------------------------------------------------------------------------------------
+// "Not thread-safe" exactly as the reference (world.hpp:52-78): one world = one CUDA device + one primary stream.
+class World {
+public:
+  explicit World(int device = 0, uint32_t entity_capacity = 0) {
+    helios_gpu_world_config cfg{device, entity_capacity, 0, HELIOS_GPU_WORLD_DEFAULT};
+    const int32_t st = helios_gpu_world_create(&cfg, &w_);
+    if (st != HELIOS_GPU_OK) {
+      w_ = nullptr;
+      throw GpuError(st, "helios_gpu_world_create failed: no usable CUDA device (there is no CPU fallback)");
+    }
+  }
+  World(const World&) = delete;
+  World& operator=(const World&) = delete;
+  ~World() { if (w_) helios_gpu_world_destroy(w_); }
+
+  helios_gpu_world* Handle() const noexcept { return w_; }
+  void Check(int32_t st) const {
+    if (st != HELIOS_GPU_OK) throw GpuError(st, std::string("helios_gpu: ") + helios_gpu_last_error(w_));
+  }
+
+  // ComponentManager::Register (component/manager.hpp:1049-1057); implicit on first use like the reference's Add.
+  template <details::Component T>
+  int RegisterComponent() {
+    const T def{};
+    const int32_t slot = helios_gpu_register_component(w_, TypeIndexOf<T>(), sizeof(T), alignof(T), &def);
+    if (slot < 0) Check(slot);
+    return slot;
+  }
+
+  // world.hpp:979-984
+  Entity CreateEntity() {
+    helios_gpu_entity_t e;
+    Check(helios_gpu_create_entities(w_, 1, &e));
+    return Entity::FromBits(e);
+  }
+  // Commands::Spawn → EntityManager::ReserveEntity (entity/manager.hpp:294-305)
+  Entity ReserveEntity() {
+    helios_gpu_entity_t e;
+    Check(helios_gpu_reserve_entities(w_, 1, &e));
+    return Entity::FromBits(e);
+  }
+  // Bulk form of `for i: e = CreateEntity(); AddComponents(e, c0[i], c1[i], ...)` — same ids, same archetype and row order.
+  template <details::Component... Cs>
+  std::vector<Entity> SpawnBatch(size_t n, std::span<const Cs>... columns) {
+    (RegisterComponent<Cs>(), ...);
+    const uint64_t hashes[] = {TypeIndexOf<Cs>()...};
+    const void* cols[] = {static_cast<const void*>(columns.data())...};
+    std::vector<helios_gpu_entity_t> bits(n);
+    Check(helios_gpu_spawn_batch(w_, hashes, sizeof...(Cs), n, cols, bits.data()));
+    std::vector<Entity> out(n);
+    for (size_t i = 0; i < n; ++i) out[i] = Entity::FromBits(bits[i]);
+    return out;
+  }
+
+  // Immediate structural calls (world.hpp:986-1196) = one-record queue + Flush.
+  void DestroyEntity(Entity e) { Immediate(HELIOS_GPU_CMD_DESTROY, e, 0, nullptr, 0); }
+  void TryDestroyEntity(Entity e) { Immediate(HELIOS_GPU_CMD_TRY_DESTROY, e, 0, nullptr, 0); }
+  template <details::Component... Cs>
+  void AddComponents(Entity e, const Cs&... cs) { AddImpl(HELIOS_GPU_CMD_ADD, e, cs...); }
+  template <details::Component... Cs>
+  void TryAddComponents(Entity e, const Cs&... cs) { AddImpl(HELIOS_GPU_CMD_TRY_ADD, e, cs...); }
+  template <details::Component... Cs>
+  void RemoveComponents(Entity e) { Immediate(HELIOS_GPU_CMD_REMOVE, e, MaskOf<Cs...>(), nullptr, 0); }
+  template <details::Component... Cs>
+  void TryRemoveComponents(Entity e) { Immediate(HELIOS_GPU_CMD_TRY_REMOVE, e, MaskOf<Cs...>(), nullptr, 0); }
+  void ClearComponents(Entity e) { Immediate(HELIOS_GPU_CMD_CLEAR, e, 0, nullptr, 0); }
+
+  // EntityManager::Validate through the location tables (entity/manager.hpp:410-418).
+  bool Exists(Entity e) const {
+    uint32_t a, r;
+    return helios_gpu_entity_location(w_, e.Bits(), &a, &r) == HELIOS_GPU_OK;
+  }
+  template <details::Component T>
+  bool HasComponent(Entity e) {
+    uint32_t a, r;
+    if (helios_gpu_entity_location(w_, e.Bits(), &a, &r) != HELIOS_GPU_OK) return false;
+    uint64_t hashes[HELIOS_GPU_MAX_COMPONENTS];
+    uint32_t nt = 0;
+    Check(helios_gpu_snapshot_archetype_info(w_, a, hashes, &nt, nullptr));
+    for (uint32_t i = 0; i < nt; ++i)
+      if (hashes[i] == TypeIndexOf<T>()) return true;
+    return false;
+  }
+  // World::ReadComponent (copy out of HBM; synchronises).
+  template <details::Component T>
+  T ReadComponent(Entity e) {
+    uint32_t a, r;
+    Check(helios_gpu_entity_location(w_, e.Bits(), &a, &r));
+    T v{};
+    Check(helios_gpu_archetype_column_read(w_, a, TypeIndexOf<T>(), r, 1, &v));
+    Check(helios_gpu_world_synchronize(w_));
+    return v;
+  }
+  size_t EntityCount() {
+    uint64_t n = 0;
+    Check(helios_gpu_entity_count(w_, &n));
+    return n;
+  }
+  size_t ArchetypeCount() {
+    uint32_t n = 0;
+    Check(helios_gpu_snapshot_archetype_count(w_, &n));
+    return n;
+  }
+
+  void Flush() { Check(helios_gpu_world_flush(w_)); }    // world.hpp:957-963
+  void Update() { Check(helios_gpu_world_update(w_)); }  // world.hpp:950-955
+
+  // ---- messages (world.hpp AddMessage / MessageManager::Write / Previous+CurrentMessages) ----
+  template <typename M>
+  void AddMessage(MessageClearPolicy policy = MessageClearPolicy::kAutomatic) {
+    static_assert(std::is_trivially_copyable_v<M>);
+    Check(helios_gpu_message_register(w_, TypeIndexOf<M>(), sizeof(M), static_cast<uint32_t>(policy)));
+  }
+  template <typename M>
+  void WriteMessage(const M& m) { Check(helios_gpu_message_write(w_, TypeIndexOf<M>(), &m, 1)); }
+  template <typename M>
+  void WriteMessages(std::span<const M> ms) { Check(helios_gpu_message_write(w_, TypeIndexOf<M>(), ms.data(), ms.size())); }
+  // MessageReader order: previous ++ current (message/reader.hpp:793-795).
+  template <typename M>
+  std::vector<M> ReadMessages() {
+    uint64_t p = 0, c = 0;
+    Check(helios_gpu_message_counts(w_, TypeIndexOf<M>(), &p, &c));
+    std::vector<M> out(p + c);
+    if (p) Check(helios_gpu_message_read(w_, TypeIndexOf<M>(), 0, out.data(), p * sizeof(M)));
+    if (c) Check(helios_gpu_message_read(w_, TypeIndexOf<M>(), 1, out.data() + p, c * sizeof(M)));
+    return out;
+  }
+
+  // Slot of a registered component (bit position in command masks); registers on first use.
+  template <details::Component T>
+  int SlotOf() { return RegisterComponent<T>(); }
+  template <details::Component... Cs>
+  uint64_t MaskOf() { return ((uint64_t(1) << SlotOf<Cs>()) | ... | uint64_t(0)); }
+
+  // Encode component values in ascending slot order, each padded to 4 bytes (helios_gpu.h command payload layout).
+  template <details::Component... Cs>
+  uint64_t EncodePayload(std::vector<uint8_t>& out, const Cs&... cs) {
+    struct Item { int slot; const void* p; size_t n; };
+    Item items[] = {Item{SlotOf<Cs>(), &cs, sizeof(Cs)}...};
+    for (size_t i = 1; i < sizeof...(Cs); ++i)
+      for (size_t j = i; j > 0 && items[j].slot < items[j - 1].slot; --j) std::swap(items[j], items[j - 1]);
+    uint64_t mask = 0;
+    for (const Item& it : items) {
+      mask |= uint64_t(1) << it.slot;
+      const auto* b = static_cast<const uint8_t*>(it.p);
+      out.insert(out.end(), b, b + it.n);
+      while (out.size() % 4) out.push_back(0);
+    }
+    return mask;
+  }
+
+private:
+  void Immediate(uint32_t kind, Entity e, uint64_t mask, const void* payload, uint64_t bytes) {
+    helios_gpu_command c{kind, 0, e.Bits(), mask};
+    Check(helios_gpu_commands_enqueue(w_, &c, 1, payload, bytes));
+    Flush();
+  }
+  template <typename... Cs>
+  void AddImpl(uint32_t kind, Entity e, const Cs&... cs) {
+    std::vector<uint8_t> payload;
+    const uint64_t mask = EncodePayload(payload, cs...);
+    Immediate(kind, e, mask, payload.data(), payload.size());
+  }
+  helios_gpu_world* w_ = nullptr;
+};
+
+template <typename... Args>
+Query<Args...>::Query(World& world) : world_(&world) {
+  const helios_gpu_query_desc d = Describe();
+  world.Check(helios_gpu_query_create(world.Handle(), &d, &q_));
+}
+template <typename... Args>
+uint64_t Query<Args...>::Count() {
+  uint64_t n = 0;
+  world_->Check(helios_gpu_query_count(q_, &n));
+  return n;
+}
+template <typename... Args>
+std::vector<uint32_t> Query<Args...>::MatchedArchetypes() {
+  uint32_t n = 0;
+  world_->Check(helios_gpu_query_match(q_, nullptr, 0, &n));
+  std::vector<uint32_t> out(n);
+  if (n) world_->Check(helios_gpu_query_match(q_, out.data(), n, &n));
+  return out;
+}
+
+// ---- Commands / EntityCmdBuffer (command/commands.hpp:24-109, command/entity_buffer.hpp:28-358) -----------------------
+// Host-side deferred commands: records accumulate FIFO and are appended to the world's global queue (World::Flush
+// executes it, world.hpp:957-963) when the Commands object is submitted or destroyed — the counterpart of
+// ~EntityCmdBuffer relocating its records into the owning queue (entity_buffer.hpp:61).
+class Commands {
+public:
+  explicit Commands(World& world) : world_(&world) {}
+  Commands(const Commands&) = delete;
+  Commands& operator=(const Commands&) = delete;
+  ~Commands() noexcept(false) { Submit(); }
+
+  class EntityCommands {
+  public:
+    EntityCommands(Commands& c, ecs::Entity e) : c_(&c), e_(e) {}
+    ecs::Entity GetEntity() const noexcept { return e_; }
+    template <details::Component... Cs>
+    EntityCommands& AddComponents(const Cs&... cs) { c_->PushAdd(HELIOS_GPU_CMD_ADD, e_, cs...); return *this; }
+    template <details::Component... Cs>
+    EntityCommands& TryAddComponents(const Cs&... cs) { c_->PushAdd(HELIOS_GPU_CMD_TRY_ADD, e_, cs...); return *this; }
+    template <details::Component... Cs>
+    EntityCommands& RemoveComponents() { c_->Push(HELIOS_GPU_CMD_REMOVE, e_, c_->world_->template MaskOf<Cs...>()); return *this; }
+    template <details::Component... Cs>
+    EntityCommands& TryRemoveComponents() { c_->Push(HELIOS_GPU_CMD_TRY_REMOVE, e_, c_->world_->template MaskOf<Cs...>()); return *this; }
+    EntityCommands& ClearComponents() { c_->Push(HELIOS_GPU_CMD_CLEAR, e_, 0); return *this; }
+    void Destroy() { c_->Push(HELIOS_GPU_CMD_DESTROY, e_, 0); }
+    void TryDestroy() { c_->Push(HELIOS_GPU_CMD_TRY_DESTROY, e_, 0); }
+  private:
+    Commands* c_;
+    ecs::Entity e_;
+  };
+
+  // commands.hpp Spawn(): reserves {next_index, generation 1}; the entity exists after the next flush.
+  EntityCommands Spawn() { return EntityCommands(*this, world_->ReserveEntity()); }
+  EntityCommands Entity(ecs::Entity e) { return EntityCommands(*this, e); }
+  size_t Size() const noexcept { return cmds_.size(); }
+
+  // Append the records to the world's global queue (relative payload offsets are relocated by the library).
+  void Submit() {
+    if (cmds_.empty()) return;
+    world_->Check(helios_gpu_commands_enqueue(world_->Handle(), cmds_.data(), cmds_.size(), payload_.data(), payload_.size()));
+    cmds_.clear();
+    payload_.clear();
+  }
+
+private:
+  void Push(uint32_t kind, ecs::Entity e, uint64_t mask) {
+    cmds_.push_back(helios_gpu_command{kind, uint32_t(payload_.size()), e.Bits(), mask});
+  }
+  template <typename... Cs>
+  void PushAdd(uint32_t kind, ecs::Entity e, const Cs&... cs) {
+    const uint32_t off = uint32_t(payload_.size());
+    const uint64_t mask = world_->EncodePayload(payload_, cs...);
+    cmds_.push_back(helios_gpu_command{kind, off, e.Bits(), mask});
+  }
+  World* world_;
+  std::vector<helios_gpu_command> cmds_;
+  std::vector<uint8_t> payload_;
+};
+
+// ---- Schedule / SystemHandle (schedule/schedule.hpp:334-362, src/ecs/src/schedule/schedule.cpp) -----------------------
+struct GpuSystemOptions {
+  const void* params = nullptr;     // copied at registration, handed to the launch function every run
+  uint32_t params_size = 0;
+  bool emits_commands = false;      // Commands parameter: one sparse record slot per visited row
+  uint32_t cmd_payload_stride = 0;
+  uint64_t writes_message = 0;      // MessageWriter<M>: TypeIndexOf<M>()
+  uint64_t reads_message = 0;       // MessageReader<M>
+  uint64_t writer_capacity = 0;
+  std::vector<uint64_t> extra_reads, extra_writes;        // World::Get<T>(entity) style access outside the query
+  std::vector<uint64_t> read_resources, write_resources;  // Res<T> / ResMut<T>
+};
+
+class Schedule {
+public:
+  explicit Schedule(World& world, std::string name = "Update") : world_(&world) {
+    world.Check(helios_gpu_schedule_create(world.Handle(), name.c_str(), &s_));
+  }
+  Schedule(const Schedule&) = delete;
+  Schedule& operator=(const Schedule&) = delete;
+  ~Schedule() { if (s_) helios_gpu_schedule_destroy(s_); }
+
+  class SystemHandle {  // schedule.hpp: Before/After ordering constraints
+  public:
+    SystemHandle(Schedule& s, uint32_t index) : s_(&s), index_(index) {}
+    uint32_t Index() const noexcept { return index_; }
+    SystemHandle& Before(const SystemHandle& other) {
+      s_->world_->Check(helios_gpu_schedule_add_order(s_->s_, index_, other.index_));
+      return *this;
+    }
+    SystemHandle& After(const SystemHandle& other) {
+      s_->world_->Check(helios_gpu_schedule_add_order(s_->s_, other.index_, index_));
+      return *this;
+    }
+  private:
+    Schedule* s_;
+    uint32_t index_;
+  };
+
+  // Schedule::Add for a GPU system: `Q` = Query<...> type (access policy deduced from it), `launch` enqueues the body's
+  // kernels on ctx->stream.  The Query object is owned by the schedule.
+  template <typename Q>
+  SystemHandle AddGpu(const std::string& name, helios_gpu_system_fn launch, const GpuSystemOptions& opt = {}) {
+    auto* q = new Q(*world_);
+    owned_queries_.emplace_back(q, [](void* p) { delete static_cast<Q*>(p); });
+    return AddRaw(name, q->Handle(), launch, opt);
+  }
+  // Resource-only / message-only systems (no query).
+  SystemHandle AddGpu(const std::string& name, helios_gpu_system_fn launch, const GpuSystemOptions& opt = {}) {
+    return AddRaw(name, nullptr, launch, opt);
+  }
+
+  void SetExecutor(ExecutorKind kind) noexcept { kind_ = kind; }
+  void Build() { world_->Check(helios_gpu_schedule_build(s_)); }                                     // schedule.cpp:117-158
+  void Run() { world_->Check(helios_gpu_schedule_run(s_, static_cast<uint32_t>(kind_))); }          // schedule.cpp:55-78
+  void ApplyDeferred() { world_->Check(helios_gpu_schedule_apply_deferred(s_)); }                   // schedule.cpp:106-115
+  void RunAndWait() { world_->Check(helios_gpu_schedule_run_and_wait(s_, static_cast<uint32_t>(kind_))); }  // :80-104
+
+  std::vector<uint32_t> ExecutionOrder() {
+    uint32_t n = 0;
+    world_->Check(helios_gpu_schedule_execution_order(s_, nullptr, 0, &n));
+    std::vector<uint32_t> out(n);
+    if (n) world_->Check(helios_gpu_schedule_execution_order(s_, out.data(), n, &n));
+    return out;
+  }
+  // Conflict bitmask rows indexed by position in the execution order (schedule.cpp:371-395).
+  std::vector<uint64_t> Conflicts() {
+    std::vector<uint64_t> out(64);
+    world_->Check(helios_gpu_schedule_conflicts(s_, out.data(), 64));
+    out.resize(ExecutionOrder().size());
+    return out;
+  }
+  template <typename T>
+  T ReadResource(uint32_t byte_offset = 0) {
+    uint8_t buf[HELIOS_GPU_RESOURCE_BYTES];
+    world_->Check(helios_gpu_schedule_read_resources(s_, buf, HELIOS_GPU_RESOURCE_BYTES));
+    T v;
+    std::memcpy(&v, buf + byte_offset, sizeof(T));
+    return v;
+  }
+  helios_gpu_schedule* Handle() const noexcept { return s_; }
+
+private:
+  SystemHandle AddRaw(const std::string& name, helios_gpu_query* q, helios_gpu_system_fn launch, const GpuSystemOptions& o) {
+    helios_gpu_system_desc d{};
+    d.name = name.c_str();
+    d.query = q;
+    d.launch = launch;
+    d.params = o.params;
+    d.params_size = o.params_size;
+    d.flags = o.emits_commands ? HELIOS_GPU_SYSTEM_EMITS_COMMANDS : 0u;
+    d.cmd_slots_per_row = 1;
+    d.cmd_payload_stride = o.cmd_payload_stride;
+    d.writes_message = o.writes_message;
+    d.reads_message = o.reads_message;
+    d.writer_capacity = o.writer_capacity;
+    auto fill = [](const std::vector<uint64_t>& src, uint64_t* dst, uint32_t& n) {
+      n = uint32_t(src.size() < 8 ? src.size() : 8);
+      for (uint32_t i = 0; i < n; ++i) dst[i] = src[i];
+    };
+    fill(o.extra_reads, d.extra_read_components, d.n_extra_read_components);
+    fill(o.extra_writes, d.extra_write_components, d.n_extra_write_components);
+    fill(o.read_resources, d.read_resources, d.n_read_resources);
+    fill(o.write_resources, d.write_resources, d.n_write_resources);
+    uint32_t idx = 0;
+    world_->Check(helios_gpu_schedule_add_system(s_, &d, &idx));
+    return SystemHandle(*this, idx);
+  }
+  World* world_;
+  helios_gpu_schedule* s_ = nullptr;
+  ExecutorKind kind_ = ExecutorKind::kMultiThreaded;  // reference default (schedule.cpp: kMultiThreaded)
+  std::vector<std::unique_ptr<void, void (*)(void*)>> owned_queries_;
+};
+
+}  // namespace helios::ecs

@@ -1,0 +1,164 @@
+// shim_test.cpp — exercises the reference-shaped C++ API (include/helios_b200/*.hpp) and the dynamic plugin library.
+// Scenarios mirror the reference's own examples/tests: README.md:285-341 (movement system), examples/ecs/query.cpp,
+// src/ecs/tests/schedule/schedule.cpp:946-1047 (commands / messages flushed by RunAndWait),
+// examples/app/dynamic_plugin (plugin loading through helios_create_plugin / helios_plugin_type_id).
+//   shim_test nogpu <plugin.so>   → symbol + type-id checks, and World construction must fail loudly (no CPU fallback)
+//   shim_test gpu   <plugin.so>   → full run on cuda:0
+#include <dlfcn.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/helios_b200/app.hpp"
+#include "../../include/helios_b200/bench_components.hpp"
+
+using namespace helios;
+using namespace helios::bench;
+
+static int g_fail = 0, g_checks = 0;
+#define CHECK(x)                                                             \
+  do {                                                                       \
+    ++g_checks;                                                              \
+    if (!(x)) { ++g_fail; std::printf("FAIL %s:%d  %s\n", __FILE__, __LINE__, #x); } \
+  } while (0)
+
+struct TestMessage { int value; };
+
+int main(int argc, char** argv) {
+  if (argc < 3) { std::printf("usage: shim_test gpu|nogpu <plugin.so>\n"); return 2; }
+  const bool gpu = std::strcmp(argv[1], "gpu") == 0;
+
+  // ---- type identity: TypeIndex = FNV-1a of the spelled type name (utils/type_info.hpp:308-311) ----
+  CHECK(ecs::TypeNameOf<Position>() == "helios::bench::Position");
+  CHECK(ecs::TypeIndexOf<Position>() == ecs::Fnv1a("helios::bench::Position"));
+  CHECK(ecs::TypeIndexOf<const Velocity&>() == ecs::Fnv1a("helios::bench::Velocity"));
+  // ---- Query<...> argument splitting (query/details/query_args.hpp) and access deduction (traits.hpp:73-97) ----
+  using Q = ecs::Query<Position&, Velocity&, const Acceleration&, const Mass&, ecs::With<Health>, ecs::Without<Frozen>>;
+  const helios_gpu_query_desc d = Q::Describe();
+  CHECK(d.n_components == 4 && d.n_with == 1 && d.n_without == 1);
+  CHECK(d.writes[0] == 1 && d.writes[1] == 1 && d.writes[2] == 0 && d.writes[3] == 0);
+  CHECK(d.components[2] == ecs::Fnv1a("helios::bench::Acceleration") && d.with[0] == ecs::Fnv1a("helios::bench::Health"));
+  CHECK((ecs::Entity{3, 1} < ecs::Entity{4, 0}) && (ecs::Entity{3, 1} < ecs::Entity{3, 2}) && !ecs::Entity{}.Valid());
+  CHECK(ecs::Entity::FromBits(ecs::Entity{7, 2}.Bits()) == (ecs::Entity{7, 2}));
+
+  // ---- dynamic plugin C ABI (dynamic_plugin.hpp:27,84-88) ----
+  void* lib = dlopen(argv[2], RTLD_NOW | RTLD_LOCAL);
+  CHECK(lib != nullptr);
+  if (!lib) { std::printf("dlopen: %s\n", dlerror()); return 1; }
+  auto create = reinterpret_cast<app::Plugin* (*)()>(dlsym(lib, app::kDefaultCreateSymbol));
+  auto type_id = reinterpret_cast<const app::PluginTypeExport* (*)()>(dlsym(lib, app::kDefaultPluginIdSymbol));
+  CHECK(create != nullptr && type_id != nullptr);
+  const app::PluginTypeExport* te = type_id();
+  CHECK(te && te->qualified_name && te->hash == ecs::Fnv1a(te->qualified_name));
+  CHECK(std::strcmp(te->qualified_name, "helios::gpu::GpuEcsPlugin") == 0);
+
+  if (!gpu) {
+    bool threw = false;
+    try {
+      ecs::World w;
+    } catch (const ecs::GpuError& e) {
+      threw = e.Status() == HELIOS_GPU_ERR_CUDA;
+    }
+    CHECK(threw);  // no device: fail loudly, never a silent CPU world
+    std::printf("shim_test nogpu: %d checks, %d failed\n", g_checks, g_fail);
+    return g_fail;
+  }
+
+  {
+    // ---- README movement example through App + the dynamic plugin ----
+    app::App application;
+    application.AddPlugin(std::unique_ptr<app::Plugin>(create()));  // host takes ownership (dynamic_plugin.hpp:583)
+    auto& world = application.GetWorld();
+    application.Initialize();
+    const size_t n = 5000;
+    std::vector<Position> pos(n);
+    std::vector<Velocity> vel(n);
+    for (size_t i = 0; i < n; ++i) { pos[i] = {float(i), float(2 * i)}; vel[i] = {0.5f, -0.25f}; }
+    const auto ents = world.SpawnBatch<Position, Velocity>(n, std::span<const Position>(pos), std::span<const Velocity>(vel));
+    CHECK(ents.size() == n && ents[0] == (ecs::Entity{0, 1}) && world.EntityCount() == n);
+    CHECK(application.Run(3) == app::AppExitCode::kSuccess);
+    const Position p = world.ReadComponent<Position>(ents[10]);
+    CHECK(p.x == 10.0f + 1.5f && p.y == 20.0f - 0.75f);
+    CHECK(world.HasComponent<Velocity>(ents[10]) && !world.HasComponent<Health>(ents[10]));
+
+    // ---- Commands (schedule.cpp:946-1006): spawn with components, destroy, insert, remove — visible after the flush ----
+    {
+      ecs::Commands commands(world);
+      const ecs::Entity spawned = commands.Spawn().AddComponents(Position{1, 2}, Health{5}).GetEntity();
+      commands.Entity(ents[0]).Destroy();
+      commands.Entity(ents[1]).AddComponents(Health{77});
+      commands.Entity(ents[2]).RemoveComponents<Velocity>();
+      CHECK(commands.Size() == 4 && !world.Exists(spawned));
+      commands.Submit();
+      world.Flush();
+      CHECK(world.Exists(spawned) && spawned == (ecs::Entity{uint32_t(n), 1}));
+      CHECK(world.ReadComponent<Health>(spawned).hp == 5 && world.ReadComponent<Position>(spawned).y == 2.0f);
+      CHECK(!world.Exists(ents[0]) && world.EntityCount() == n);
+      CHECK(world.ReadComponent<Health>(ents[1]).hp == 77 && world.HasComponent<Velocity>(ents[1]));
+      CHECK(!world.HasComponent<Velocity>(ents[2]) && world.HasComponent<Position>(ents[2]));
+    }
+    ecs::Query<const Position&> q_pos(world);
+    ecs::Query<const Position&, ecs::With<Health>> q_with(world);
+    ecs::Query<const Position&, ecs::Without<Velocity>> q_without(world);
+    CHECK(q_pos.Count() == n && q_with.Count() == 2 && q_without.Count() == 2);
+    // immediate World calls (world.hpp:986-1196)
+    world.AddComponents(ents[3], Health{9});
+    world.DestroyEntity(ents[4]);
+    CHECK(world.ReadComponent<Health>(ents[3]).hp == 9 && !world.Exists(ents[4]) && q_with.Count() == 3);
+    const ecs::Entity recycled = world.CreateEntity();  // LIFO recycle with a bumped generation (entity/manager.hpp:428-448)
+    CHECK(recycled == (ecs::Entity{ents[4].Index(), 2}));
+
+    // ---- messages (message/manager.cpp:148-213 through the world) ----
+    world.AddMessage<TestMessage>();
+    world.WriteMessage(TestMessage{99});
+    CHECK(world.ReadMessages<TestMessage>().size() == 1);
+    world.Update();
+    const auto msgs = world.ReadMessages<TestMessage>();
+    CHECK(msgs.size() == 1 && msgs[0].value == 99);
+    world.Update();
+    CHECK(world.ReadMessages<TestMessage>().empty());
+  }
+  {
+    // ---- Schedule: ordering constraints and the conflict matrix (schedule.cpp:507-557, access_policy.hpp:172-196) ----
+    ecs::World world;
+    world.RegisterComponent<Position>();
+    world.RegisterComponent<Velocity>();
+    world.RegisterComponent<Health>();
+    helios_gpu_system_fn integrate, damp, regen;
+    world.Check(helios_gpu_builtin_system("integrate", &integrate));
+    world.Check(helios_gpu_builtin_system("damp", &damp));
+    world.Check(helios_gpu_builtin_system("regen", &regen));
+    ecs::Schedule schedule(world);
+    const float k = 0.5f;
+    ecs::GpuSystemOptions damp_opt;
+    damp_opt.params = &k;
+    damp_opt.params_size = sizeof(k);
+    auto a = schedule.AddGpu<ecs::Query<Position&, const Velocity&>>("integrate", integrate);
+    auto b = schedule.AddGpu<ecs::Query<Velocity&>>("damp", damp, damp_opt);
+    schedule.AddGpu<ecs::Query<Health&>>("regen", regen);
+    b.Before(a);
+    schedule.Build();
+    CHECK((schedule.ExecutionOrder() == std::vector<uint32_t>{1, 2, 0}));
+    const auto c = schedule.Conflicts();  // by execution position: damp(W Vel) x integrate(R Vel)
+    CHECK(c.size() == 3 && c[0] == 0b100 && c[1] == 0 && c[2] == 0b001);
+    std::vector<Position> pos(100, Position{1, 1});
+    std::vector<Velocity> vel(100, Velocity{2, 4});
+    std::vector<Health> hp(100, Health{99});
+    const auto ents = world.SpawnBatch<Position, Velocity, Health>(100, std::span<const Position>(pos),
+                                                                  std::span<const Velocity>(vel), std::span<const Health>(hp));
+    for (auto kind : {ecs::ExecutorKind::kMainThread, ecs::ExecutorKind::kMultiThreaded, ecs::ExecutorKind::kCudaGraph}) {
+      schedule.SetExecutor(kind);
+      schedule.RunAndWait();
+    }
+    // damp runs before integrate each frame: v = 2 -> 1 -> .5 -> .25 ; x = 1 + 1 + .5 + .25
+    const Position p = world.ReadComponent<Position>(ents[42]);
+    CHECK(p.x == 2.75f && p.y == 4.5f && world.ReadComponent<Health>(ents[42]).hp == 100);
+    bool cycle = false;
+    a.Before(b);
+    try { schedule.Build(); } catch (const ecs::GpuError& e) { cycle = e.Status() == HELIOS_GPU_ERR_CYCLE; }
+    CHECK(cycle);
+  }
+  std::printf("shim_test gpu: %d checks, %d failed\n", g_checks, g_fail);
+  return g_fail;
+}
