@@ -139,9 +139,9 @@ int main(int argc, char** argv) {
     schedule.AddGpu<ecs::Query<Health&>>("regen", regen);
     b.Before(a);
     schedule.Build();
-    CHECK((schedule.ExecutionOrder() == std::vector<uint32_t>{1, 2, 0}));
+    CHECK((schedule.ExecutionOrder() == std::vector<uint32_t>{1, 0, 2}));  // Kahn, lowest ready index first (dag.cpp:65-126)
     const auto c = schedule.Conflicts();  // by execution position: damp(W Vel) x integrate(R Vel)
-    CHECK(c.size() == 3 && c[0] == 0b100 && c[1] == 0 && c[2] == 0b001);
+    CHECK(c.size() == 3 && c[0] == 0b010 && c[1] == 0b001 && c[2] == 0);
     std::vector<Position> pos(100, Position{1, 1});
     std::vector<Velocity> vel(100, Velocity{2, 4});
     std::vector<Health> hp(100, Health{99});
