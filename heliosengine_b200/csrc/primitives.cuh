@@ -47,7 +47,7 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* total)
 }
 
 // Pass 1: per-tile exclusive scan written in place to `out`, tile totals to partials[tile].
-__global__ void __launch_bounds__(kScanThreads) k_scan_tiles(const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
+static __global__ void __launch_bounds__(kScanThreads) k_scan_tiles(const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
                                                              uint32_t* __restrict__ partials, uint64_t n) {
   const uint64_t base = uint64_t(blockIdx.x) * kScanTile + threadIdx.x * kScanItems;
   uint32_t v[kScanItems];
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_tiles(const uint32_t* __r
 }
 
 // Pass 2: one block scans the tile totals (exclusive, in place) and writes the grand total.
-__global__ void __launch_bounds__(kScanThreads) k_scan_partials(uint32_t* __restrict__ partials, uint32_t nparts,
+static __global__ void __launch_bounds__(kScanThreads) k_scan_partials(uint32_t* __restrict__ partials, uint32_t nparts,
                                                                 uint32_t* __restrict__ grand_total) {
   uint32_t running = 0;
   for (uint32_t base = 0; base < nparts; base += kScanThreads) {
@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_partials(uint32_t* __rest
 }
 
 // Pass 3: add the tile offset back.
-__global__ void __launch_bounds__(kScanThreads) k_scan_add(uint32_t* __restrict__ out, const uint32_t* __restrict__ partials,
+static __global__ void __launch_bounds__(kScanThreads) k_scan_add(uint32_t* __restrict__ out, const uint32_t* __restrict__ partials,
                                                            uint64_t n) {
   const uint32_t off = partials[blockIdx.x];
   const uint64_t base = uint64_t(blockIdx.x) * kScanTile + threadIdx.x * kScanItems;
@@ -143,7 +143,7 @@ __device__ __forceinline__ void sort_warp_hist(uint32_t* h, const uint32_t (&dig
   }
 }
 
-__global__ void __launch_bounds__(kSortThreads) k_sort_hist(const uint64_t* __restrict__ keys, uint64_t n, int shift,
+static __global__ void __launch_bounds__(kSortThreads) k_sort_hist(const uint64_t* __restrict__ keys, uint64_t n, int shift,
                                                             uint32_t ntiles, uint32_t* __restrict__ counts) {
   __shared__ uint32_t h[kSortWarps][256];
   const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31u;
@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(kSortThreads) k_sort_hist(const uint64_t* __re
 }
 
 // One warp per digit row: exclusive prefix over the row's ntiles counts (in place) and the row total.
-__global__ void __launch_bounds__(256) k_sort_scan(uint32_t* __restrict__ counts, uint32_t ntiles, uint32_t* __restrict__ rowtot) {
+static __global__ void __launch_bounds__(256) k_sort_scan(uint32_t* __restrict__ counts, uint32_t ntiles, uint32_t* __restrict__ rowtot) {
   const uint32_t row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
   if (row >= 256) return;
   uint32_t* r = counts + size_t(row) * ntiles;
@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(256) k_sort_scan(uint32_t* __restrict__ counts
   if (lane == 0) rowtot[row] = running;
 }
 
-__global__ void __launch_bounds__(kSortThreads) k_sort_scatter(const uint64_t* __restrict__ keys_in,
+static __global__ void __launch_bounds__(kSortThreads) k_sort_scatter(const uint64_t* __restrict__ keys_in,
                                                                const uint32_t* __restrict__ vals_in,
                                                                uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                                uint64_t n, int shift, uint32_t ntiles,

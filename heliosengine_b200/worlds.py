@@ -30,18 +30,19 @@ def cname(short: str) -> str:
     return NS + short
 
 
-def splitmix64(seed: int, n: int, stream: int = 0) -> np.ndarray:
-    """n outputs of SplitMix64 started at seed + stream * 0x632BE59BD9B4E019."""
+def splitmix64(seed: int, n: int, stream: int = 0, offset: int = 0) -> np.ndarray:
+    """Outputs offset+1 .. offset+n of SplitMix64 started at seed + stream * 0x632BE59BD9B4E019 (random access: a shard
+    generates exactly its slice of the global sequence)."""
     with np.errstate(over="ignore"):
         s0 = np.uint64((seed + stream * 0x632BE59BD9B4E019) & 0xFFFFFFFFFFFFFFFF)
-        z = s0 + (np.arange(1, n + 1, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15))
+        z = s0 + (np.arange(offset + 1, offset + n + 1, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15))
         z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
         z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
         return z ^ (z >> np.uint64(31))
 
 
-def uniform_f32(seed: int, n: int, stream: int, lo: float, hi: float) -> np.ndarray:
-    u = (splitmix64(seed, n, stream) >> np.uint64(40)).astype(np.float64) * (2.0 ** -24)
+def uniform_f32(seed: int, n: int, stream: int, lo: float, hi: float, offset: int = 0) -> np.ndarray:
+    u = (splitmix64(seed, n, stream, offset) >> np.uint64(40)).astype(np.float64) * (2.0 ** -24)
     return (lo + (hi - lo) * u).astype(np.float32)
 
 

@@ -341,6 +341,41 @@ HELIOS_GPU_API int32_t helios_gpu_schedule_stream_count(helios_gpu_schedule* s, 
 /* Copy the schedule's device resource scratch (HELIOS_GPU_RESOURCE_BYTES) to the host. */
 HELIOS_GPU_API int32_t helios_gpu_schedule_read_resources(helios_gpu_schedule* s, void* out, uint32_t bytes);
 
+
+/* ---- boids: uniform-grid neighbour query over an entity-range shard (BASELINE configs[4]) -------
+ * The reference has no neighbour-interaction system (parity unpinned — DESIGN.md §7); in reference terms this is one
+ * system `Query<Position&, Velocity&>` whose body reads the positions/velocities of the boids in the 3x3 cell stencil.
+ * World [0, world_size)^2, cell = interaction radius = 1.  Every per-pair term is quantised to fixed point and summed in
+ * int64, so the result does not depend on the order neighbours are visited in — hence not on the binning order nor on
+ * the number of shards.  One step of one shard:
+ *   1. helios_gpu_boids_bin      count -> scan -> scatter the shard's boids into cell order; writes the shard's slab
+ *                                 {x,y,dx,dy} (16 B per boid) and its per-cell counts (u16) into caller-provided device
+ *                                 buffers — the rank's slot of the all-gather buffers;
+ *   2. (caller) all-gather slabs and counts across ranks (NCCL over NVLink; nothing to do with one shard);
+ *   3. helios_gpu_boids_step     per-shard cell tables from the counts, neighbour pass for the shard's own boids over
+ *                                 all slabs, integrate, write Position / Velocity back to the table columns. */
+typedef struct helios_gpu_boids helios_gpu_boids;
+typedef struct helios_gpu_boids_params {
+  float world_size;   /* cells per side (integer valued, <= 16384) */
+  float dt;
+  float w_separation, w_alignment, w_cohesion;
+  float max_speed;
+} helios_gpu_boids_params;
+#define HELIOS_GPU_BOIDS_MAX_SHARDS 16u
+HELIOS_GPU_API int32_t helios_gpu_boids_create(helios_gpu_world* w, uint64_t position_hash, uint64_t velocity_hash,
+                                               const helios_gpu_boids_params* params, helios_gpu_boids** out);
+HELIOS_GPU_API int32_t helios_gpu_boids_destroy(helios_gpu_boids* b);
+/* Rows of the {Position, Velocity} table = boids of this shard; cells = world_size^2. */
+HELIOS_GPU_API int32_t helios_gpu_boids_sizes(helios_gpu_boids* b, uint64_t* n_local, uint64_t* n_cells);
+/* slab: n_local * 16 bytes, counts: n_cells * 2 bytes (device pointers; asynchronous on the world stream). */
+HELIOS_GPU_API int32_t helios_gpu_boids_bin(helios_gpu_boids* b, void* slab, void* counts);
+/* slabs / counts: the all-gathered buffers (shard g at offset g * n_local * 16 and g * n_cells * 2); every shard holds
+ * n_local boids.  my_shard's slab and counts must be the ones helios_gpu_boids_bin just wrote. */
+HELIOS_GPU_API int32_t helios_gpu_boids_step(helios_gpu_boids* b, const void* slabs, const void* counts, uint32_t n_shards,
+                                             uint32_t my_shard);
+/* Single-shard convenience: bin + step on internal buffers. */
+HELIOS_GPU_API int32_t helios_gpu_boids_step_local(helios_gpu_boids* b);
+
 /* Launch accounting: a system body reports the kernels it enqueued (for_each_launch does this itself). */
 HELIOS_GPU_API void helios_gpu_world_note_launches(helios_gpu_world* w, uint32_t n);
 

@@ -5,6 +5,7 @@
 // with -ffp-contract=off so that float system bodies match the GPU build (-fmad=false) bit for bit.
 #include <atomic>
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <thread>
 
@@ -579,3 +580,184 @@ HO_API double helios_oracle_time_schedule_run(void* sp, uint32_t iters) {
   return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 HO_API uint32_t helios_oracle_hardware_threads() { return std::thread::hardware_concurrency(); }
+
+// =====================================================================================================
+// Boids (BASELINE configs[4]) — CPU statement of the sharded uniform-grid neighbour system, mirroring
+// helios_gpu_boids_* with HOST buffers.  The reference has no such system: parity for this config is UNPINNED
+// (SURVEY.md §8c); this code is the specification the CUDA kernels are checked against.
+// Deliberately different traversal from the GPU (cell by cell, shards innermost, slab in ascending row order):
+// every per-pair term is quantised and summed in int64, so the result must not depend on any of that.
+// =====================================================================================================
+namespace {
+
+struct OBoids {
+  OWorld* w;
+  helios_gpu_boids_params p;
+  ho::Archetype* table = nullptr;
+  int pos_col = -1, vel_col = -1;
+  uint32_t dim = 0;
+  uint64_t n_cells = 0;
+  std::vector<uint32_t> orig;        // slab position -> table row (of the last bin)
+  std::vector<uint8_t> own_slab, own_counts;
+};
+
+inline uint32_t o_cell_of(float x, float y, uint32_t dim) {
+  int cx = int(x), cy = int(y);
+  cx = cx < 0 ? 0 : (cx >= int(dim) ? int(dim) - 1 : cx);
+  cy = cy < 0 ? 0 : (cy >= int(dim) ? int(dim) - 1 : cy);
+  return uint32_t(cy) * dim + uint32_t(cx);
+}
+
+struct Boid4 { float x, y, dx, dy; };
+
+}  // namespace
+
+HO_API int32_t helios_oracle_boids_create(void* wp, uint64_t pos_hash, uint64_t vel_hash, const helios_gpu_boids_params* p,
+                                          void** out) {
+  OWorld* w = W(wp);
+  auto* b = new OBoids();
+  b->w = w;
+  b->p = *p;
+  for (ho::Archetype* a : w->world.components.Archetypes()) {
+    const auto& ty = a->Id().Types();
+    if (ty.size() == 2 && a->HasColumn(pos_hash) && a->HasColumn(vel_hash)) {
+      b->table = a;
+      b->pos_col = a->ColumnIndex(pos_hash);
+      b->vel_col = a->ColumnIndex(vel_hash);
+    }
+  }
+  if (!b->table || !(p->world_size >= 1.0f) || p->world_size > 16384.0f || p->world_size != float(uint32_t(p->world_size))) {
+    delete b;
+    return HELIOS_GPU_ERR_NOT_FOUND;
+  }
+  b->dim = uint32_t(p->world_size);
+  b->n_cells = uint64_t(b->dim) * b->dim;
+  *out = b;
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_destroy(void* bp) {
+  delete static_cast<OBoids*>(bp);
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_sizes(void* bp, uint64_t* n_local, uint64_t* n_cells) {
+  auto* b = static_cast<OBoids*>(bp);
+  if (n_local) *n_local = b->table->EntityCount();
+  if (n_cells) *n_cells = b->n_cells;
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_bin(void* bp, void* slab_out, void* counts_out) {
+  auto* b = static_cast<OBoids*>(bp);
+  const size_t n = b->table->EntityCount();
+  const auto* pos = reinterpret_cast<const float*>(b->table->ColumnBytes(b->pos_col).data());
+  const auto* vel = reinterpret_cast<const float*>(b->table->ColumnBytes(b->vel_col).data());
+  std::vector<uint32_t> count(b->n_cells, 0), start(b->n_cells + 1, 0);
+  for (size_t i = 0; i < n; ++i) ++count[o_cell_of(pos[2 * i], pos[2 * i + 1], b->dim)];
+  auto* counts = static_cast<uint16_t*>(counts_out);
+  for (uint64_t c = 0; c < b->n_cells; ++c) {
+    if (count[c] > 65535u) return HELIOS_GPU_ERR_CAPACITY;
+    counts[c] = uint16_t(count[c]);
+    start[c + 1] = start[c] + count[c];
+  }
+  auto* slab = static_cast<Boid4*>(slab_out);
+  b->orig.assign(n, 0);
+  std::vector<uint32_t> cursor(start.begin(), start.end() - 1);
+  for (size_t i = 0; i < n; ++i) {  // ascending row order inside a cell
+    const uint32_t slot = cursor[o_cell_of(pos[2 * i], pos[2 * i + 1], b->dim)]++;
+    slab[slot] = Boid4{pos[2 * i], pos[2 * i + 1], vel[2 * i], vel[2 * i + 1]};
+    b->orig[slot] = uint32_t(i);
+  }
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_step(void* bp, const void* slabs_in, const void* counts_in, uint32_t n_shards,
+                                        uint32_t my_shard) {
+  auto* b = static_cast<OBoids*>(bp);
+  if (n_shards == 0 || n_shards > HELIOS_GPU_BOIDS_MAX_SHARDS || my_shard >= n_shards) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  const size_t n = b->table->EntityCount();
+  const int dim = int(b->dim);
+  const auto* slabs = static_cast<const Boid4*>(slabs_in);
+  const auto* counts = static_cast<const uint16_t*>(counts_in);
+  std::vector<std::vector<uint32_t>> tables(n_shards, std::vector<uint32_t>(b->n_cells + 1, 0));
+  for (uint32_t g = 0; g < n_shards; ++g)
+    for (uint64_t c = 0; c < b->n_cells; ++c) tables[g][c + 1] = tables[g][c] + counts[uint64_t(g) * b->n_cells + c];
+  auto* pos = reinterpret_cast<float*>(b->table->ColumnBytes(b->pos_col).data());
+  auto* vel = reinterpret_cast<float*>(b->table->ColumnBytes(b->vel_col).data());
+  const helios_gpu_boids_params P = b->p;
+  const float kEps = 0.01f, kQCoh = 16777216.0f, kQAli = 1048576.0f, kQSep = 65536.0f;
+  auto work = [&](size_t lo, size_t hi_j) {
+    for (size_t j = lo; j < hi_j; ++j) {
+      const Boid4 me = slabs[size_t(my_shard) * n + j];
+      int cx = int(me.x), cy = int(me.y);
+      cx = cx < 0 ? 0 : (cx >= dim ? dim - 1 : cx);
+      cy = cy < 0 ? 0 : (cy >= dim ? dim - 1 : cy);
+      long long coh_x = 0, coh_y = 0, ali_x = 0, ali_y = 0, sep_x = 0, sep_y = 0;
+      uint32_t count = 0;
+      for (int x = cx + 1; x >= cx - 1; --x) {      // columns right-to-left, rows bottom-to-top, shards last-to-first:
+        if (x < 0 || x >= dim) continue;            // any order gives the same integer sums
+        for (int y = cy + 1; y >= cy - 1; --y) {
+          if (y < 0 || y >= dim) continue;
+          const uint64_t c = uint64_t(y) * b->dim + uint64_t(x);
+          for (uint32_t g = n_shards; g-- > 0;) {
+            for (uint32_t k = tables[g][c]; k < tables[g][c + 1]; ++k) {
+              if (g == my_shard && k == j) continue;
+              const Boid4 o = slabs[size_t(g) * n + k];
+              const float dx = o.x - me.x, dy = o.y - me.y;
+              const float d2 = dx * dx + dy * dy;
+              if (d2 < 1.0f) {
+                ++count;
+                coh_x += llrintf(dx * kQCoh);
+                coh_y += llrintf(dy * kQCoh);
+                ali_x += llrintf(o.dx * kQAli);
+                ali_y += llrintf(o.dy * kQAli);
+                const float inv = 1.0f / (d2 + kEps);
+                sep_x += llrintf((-dx * inv) * kQSep);
+                sep_y += llrintf((-dy * inv) * kQSep);
+              }
+            }
+          }
+        }
+      }
+      float vx = me.dx, vy = me.dy;
+      if (count) {
+        const float nn = float(count);
+        const float cohx = (float(coh_x) / kQCoh) / nn, cohy = (float(coh_y) / kQCoh) / nn;
+        const float alix = (float(ali_x) / kQAli) / nn - vx, aliy = (float(ali_y) / kQAli) / nn - vy;
+        const float sepx = float(sep_x) / kQSep, sepy = float(sep_y) / kQSep;
+        const float ax = P.w_cohesion * cohx + P.w_alignment * alix + P.w_separation * sepx;
+        const float ay = P.w_cohesion * cohy + P.w_alignment * aliy + P.w_separation * sepy;
+        vx = vx + ax * P.dt;
+        vy = vy + ay * P.dt;
+      }
+      const float s2 = vx * vx + vy * vy;
+      if (s2 > P.max_speed * P.max_speed) {
+        const float sc = P.max_speed / std::sqrt(s2);
+        vx = vx * sc;
+        vy = vy * sc;
+      }
+      float px = me.x + vx * P.dt, py = me.y + vy * P.dt;
+      const float hi = P.world_size - 0.00390625f;
+      px = px < 0.0f ? 0.0f : (px > hi ? hi : px);
+      py = py < 0.0f ? 0.0f : (py > hi ? hi : py);
+      const uint32_t row = b->orig[j];
+      pos[2 * row] = px;
+      pos[2 * row + 1] = py;
+      vel[2 * row] = vx;
+      vel[2 * row + 1] = vy;
+    }
+  };
+  const int T = std::max(1, b->w->threads);
+  if (T == 1) {
+    work(0, n);
+  } else {
+    std::vector<std::thread> pool;
+    for (int t = 0; t < T; ++t) pool.emplace_back(work, n * t / T, n * (t + 1) / T);
+    for (auto& th : pool) th.join();
+  }
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_step_local(void* bp) {
+  auto* b = static_cast<OBoids*>(bp);
+  b->own_slab.resize(std::max<size_t>(1, b->table->EntityCount()) * 16);
+  b->own_counts.resize(b->n_cells * 2);
+  if (const int32_t st = helios_oracle_boids_bin(bp, b->own_slab.data(), b->own_counts.data())) return st;
+  return helios_oracle_boids_step(bp, b->own_slab.data(), b->own_counts.data(), 1, 0);
+}
