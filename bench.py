@@ -37,9 +37,10 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--entities", type=int, default=0, help="entities per GPU (default: the config's BASELINE size)")
-    ap.add_argument("--config", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4"],
+    ap.add_argument("--config", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"],
                     help="cfg2 (default) is the headline workload; the others are secondary legs (bench_configs.py)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--all-tables", action="store_true", help="drop the With/Without filters (cfg 2-all)")
     return ap.parse_args()
 
@@ -129,21 +130,36 @@ def run_reference(args):
 
 
 def run_secondary(args):
-    """cfg1 / cfg3 / cfg4 legs (single GPU): same JSON-line shape, workload named in config."""
+    """cfg1 / cfg3 / cfg4 legs (single GPU) and cfg5 (boids, sharded over the ranks): same JSON-line shape."""
     import torch
     from heliosengine_b200 import bench_configs
+    rank = int(os.environ.get("RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if int(os.environ.get("RANK", "0")) != 0:
+    if args.config != "cfg5" and rank != 0:
         return
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     stream = torch.cuda.Stream(device=dev)
     clocks = ClockSampler(local_rank)
     clocks.start()
-    line = getattr(bench_configs, "run_" + args.config)(args, torch, dev, stream, peaks())
-    line.update({"n_gpus": 1, "steps": args.steps, "warmup": max(3, args.warmup), "higher_is_better": True, "scaling": "weak",
-                 "vs_baseline": None, "data": "synthetic", "clocks": clocks.stop()})
-    print(json.dumps(line))
+    if args.config == "cfg5":
+        dist = None
+        if world_size > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=dev)
+        line = bench_configs.run_cfg5(args, torch, dev, stream, peaks(), dist, rank, world_size)
+        n_gpus = world_size
+        if world_size > 1:
+            dist.destroy_process_group()
+    else:
+        line = getattr(bench_configs, "run_" + args.config)(args, torch, dev, stream, peaks())
+        n_gpus = 1
+    base = {"n_gpus": n_gpus, "steps": args.steps, "warmup": max(3, args.warmup), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "data": "synthetic", "clocks": clocks.stop()}
+    base.update(line)
+    if rank == 0:
+        print(json.dumps(base))
 
 
 def run_b200(args):

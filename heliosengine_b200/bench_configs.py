@@ -201,3 +201,122 @@ def run_cfg1(args, torch, dev, stream, peak):
                      "traffic": None, "peak_kind": peak[1], "note": "L2-resident: not an HBM measurement"},
         "modes_ms": res, "gpu_launches": steps * 2, "e2e": None, "cpu_baseline": None,
     }
+
+
+def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
+    """Boids, STRONG scaling: `--entities` boids in total (default 64M, density 4 per cell) split by entity-id range over
+    the ranks; per step: bin own shard, all-gather slabs + counts (NCCL), neighbour pass + integrate."""
+    from . import boids
+    n_total = args.entities or (1 << 26)
+    ws = int(round((n_total / 4) ** 0.5))
+    gpu = capi.load_gpu()
+    shard = boids.BoidsShard(gpu, n_total, ws, world_size, rank, device=dev.index)
+    shard.world.set_stream(stream.cuda_stream)
+    buf = boids.ExchangeBuffers(torch, dev, world_size, shard.n_local, shard.n_cells)
+    steps, warm = args.steps, max(3, args.warmup)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        for _ in range(warm):
+            boids.distributed_step(shard, buf, dist)
+        barrier()
+        l0 = shard.world.launch_count()
+        evs = _events(torch, steps)
+        for a, b in evs:
+            a.record(stream)
+            boids.distributed_step(shard, buf, dist)
+            b.record(stream)
+        barrier()
+        launches = shard.world.launch_count() - l0
+        step_ms = [a.elapsed_time(b) for a, b in evs]
+        # phase split (one extra untimed-in-`value` step): bin / exchange / neighbour pass
+        ph = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        g = shard.shard
+        ph[0].record(stream)
+        shard.bin(buf.slab_slot(g).data_ptr(), buf.counts_slot(g).data_ptr())
+        ph[1].record(stream)
+        if world_size > 1:
+            dist.all_gather_into_tensor(buf.slabs, buf.slab_slot(g))
+            dist.all_gather_into_tensor(buf.counts, buf.counts_slot(g))
+        ph[2].record(stream)
+        shard.step(buf.slabs.data_ptr(), buf.counts.data_ptr())
+        ph[3].record(stream)
+        barrier()
+        phases = {"bin_ms": ph[0].elapsed_time(ph[1]), "exchange_ms": ph[1].elapsed_time(ph[2]),
+                  "neighbour_ms": ph[2].elapsed_time(ph[3])}
+
+        # e2e: host state -> device, step, positions -> host (rank-local slices; PCIe-bound by construction)
+        e2e = None
+        if not args.no_e2e:
+            P, V = worlds.cname("Position"), worlds.cname("Velocity")
+            hp = torch.empty(shard.n_local * 2, dtype=torch.float32).pin_memory()
+            hv = torch.empty(shard.n_local * 2, dtype=torch.float32).pin_memory()
+            pos0, vel0 = boids.initial_state(n_total, ws, *boids.shard_range(n_total, world_size, rank))
+            hp.copy_(torch.from_numpy(pos0))
+            hv.copy_(torch.from_numpy(vel0))
+            ho = torch.empty(shard.n_local * 2, dtype=torch.float32).pin_memory()
+            tbl = 1  # {} is table 0, {Position, Velocity} table 1
+            e2e_steps = 3
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(e2e_steps):
+                shard.world.column_write(tbl, P, 0, shard.n_local, hp.data_ptr())
+                shard.world.column_write(tbl, V, 0, shard.n_local, hv.data_ptr())
+                boids.distributed_step(shard, buf, dist)
+                shard.world.column_read(tbl, P, 0, shard.n_local, ho.data_ptr())
+                shard.world.synchronize()
+            barrier()
+            e2e = (time.perf_counter() - t0) / e2e_steps
+
+    tm = torch.tensor([sum(step_ms), e2e or 0.0, phases["bin_ms"], phases["exchange_ms"], phases["neighbour_ms"]],
+                      dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    tot_ms, e2e_s, bin_ms, ex_ms, nb_ms = (float(x) for x in tm.tolist())
+    ms = tot_ms / steps
+    local_bytes = 64 * shard.n_local  # SURVEY §8d: compulsory HBM bytes per boid per step on the owning GPU
+    achieved = local_bytes / (ms * 1e-3) / 1e9
+
+    cpu = None
+    if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
+        o = capi.load_oracle()
+        sample_n, sample_ws = 1 << 20, 512
+        so = boids.BoidsShard(o, sample_n, sample_ws)
+        nthreads = int(o.fn("hardware_threads", ctypes.c_uint32)())
+        o.fn("set_access_mode")(so.world.h, 0, nthreads)
+        so.step_local()
+        t0 = time.perf_counter()
+        for _ in range(2):
+            so.step_local()
+        dt = (time.perf_counter() - t0) / 2
+        so.close()
+        cpu = {"value": sample_n / dt, "unit": "boid updates/s", "cores": nthreads, "kind": "port",
+               "sample": f"{sample_n} boids in a {sample_ws}^2 world (same density, 4 per cell), 2 steps; binning single-threaded, "
+                         f"neighbour pass on {nthreads} threads; no reference implementation exists for this config"}
+    line = {
+        "metric": "boid_updates_per_sec", "value": n_total / (ms * 1e-3), "unit": "boid updates/s", "ms_per_step": ms,
+        "dtype": "f32 pair terms, int64 fixed-point sums", "scaling": "strong",
+        "config": {"workload": f"cfg5: {n_total} boids, world {ws}^2, cell = radius = 1 (density 4/cell), 3x3 stencil, "
+                               f"entity-id range shards x{world_size}",
+                   "parallelism": f"{world_size} shard(s); per step 2 NCCL all-gathers (slabs 16 B/boid + u16 cell counts), "
+                                  f"{buf.exchange_bytes_per_rank} B received per rank",
+                   "l2": "per-step working set (slabs + tables) exceeds L2; no flush",
+                   "parity": "bit-exact vs the CPU statement at test sizes, any shard count; no reference implementation (unpinned)"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak[0], "unit": "GB/s", "frac": achieved / peak[0],
+                     "traffic": None, "peak_kind": peak[1], "algorithmic_bytes_per_launch": local_bytes,
+                     "kernel": "bin (count/scan/scatter) + k_boids_neighbours, per GPU; exchange excluded from the bytes",
+                     "exchange_bytes_per_rank": buf.exchange_bytes_per_rank},
+        "phases_ms": {"bin": bin_ms, "exchange": ex_ms, "neighbour": nb_ms},
+        "e2e": ({"value": n_total / e2e_s, "unit": "boid updates/s", "h2d_bytes_per_step": shard.n_local * 16,
+                 "d2h_bytes_per_step": shard.n_local * 8,
+                 "note": "per rank and step: Position+Velocity columns from pinned host memory, step, Position back"}
+                if e2e_s else None),
+        "cpu_baseline": cpu, "gpu_launches": int(launches),
+    }
+    shard.close()
+    return line
