@@ -32,11 +32,11 @@ def shard_range(n_total: int, n_shards: int, shard: int) -> tuple[int, int]:
     return shard * per, (shard + 1) * per
 
 
-def initial_state(n_total: int, world_size: int, lo: int, hi: int, seed: int = worlds.SEED):
-    """Positions uniform over [0, world_size)^2, velocities in [-1, 1)^2 for global ids [lo, hi)."""
+def initial_state(n_total: int, world_size: int, lo: int, hi: int, seed: int = worlds.SEED, vel_scale: float = 1.0):
+    """Positions uniform over [0, world_size)^2, velocities in [-vel_scale, vel_scale)^2 for global ids [lo, hi)."""
     n = hi - lo
     pos = worlds.uniform_f32(seed, 2 * n, 9101, 0.0, float(world_size), offset=2 * lo)
-    vel = worlds.uniform_f32(seed, 2 * n, 9102, -1.0, 1.0, offset=2 * lo)
+    vel = worlds.uniform_f32(seed, 2 * n, 9102, -float(vel_scale), float(vel_scale), offset=2 * lo)
     return pos, vel
 
 
@@ -44,14 +44,14 @@ class BoidsShard:
     """One rank's shard: a world holding {Position, Velocity} for its id range + the boids system."""
 
     def __init__(self, backend: capi.Backend, n_total: int, world_size: int, n_shards: int = 1, shard: int = 0, device: int = 0,
-                 params: dict | None = None):
+                 params: dict | None = None, vel_scale: float = 1.0):
         self.b = backend
         self.n_shards, self.shard = n_shards, shard
         lo, hi = shard_range(n_total, n_shards, shard)
         self.n_local = hi - lo
         self.world = capi.World(backend, device=device, entity_capacity=self.n_local + 1024)
         worlds.register_all(self.world, ["Position", "Velocity"])
-        pos, vel = initial_state(n_total, world_size, lo, hi)
+        pos, vel = initial_state(n_total, world_size, lo, hi, vel_scale=vel_scale)
         self.world.spawn_batch([worlds.cname("Position"), worlds.cname("Velocity")], self.n_local, [pos, vel], want_entities=False)
         p = dict(DEFAULT_PARAMS)
         p.update(params or {})

@@ -843,6 +843,7 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     K = hc.n_valid_slots;
   }
   w->last_stats.commands = K;
+  ++w->mutation_epoch;
   if (K == 0) { w->launches += launches; return HELIOS_GPU_OK; }
 
   const uint64_t maxKM = 2ull * K;

@@ -209,6 +209,7 @@ int32_t launch_system(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaS
     ctx.reader.elem_size = ch->size;
     ctx.d_reader = &dev->rd;
   }
+  if (!e.policy.wc.empty()) ++w->mutation_epoch;  // the body may write component columns
   const int32_t st = e.desc.launch(&ctx);
   if (st != HELIOS_GPU_OK) HG_FAIL(w, st, "system '%s' failed to launch (%d): %s", e.name.c_str(), st,
                                    cudaGetErrorString(cudaGetLastError()));

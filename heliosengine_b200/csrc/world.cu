@@ -312,6 +312,7 @@ int32_t helios_gpu_create_entities(helios_gpu_world* w, uint32_t n, helios_gpu_e
   HG_TRY(allocate_ids(w, n, rec, &base, &fresh));
   HG_TRY(place(w, w->empty_table, rec, base, fresh, out));
   w->flushed_index = w->next_index;
+  ++w->mutation_epoch;
   return HELIOS_GPU_OK;
 }
 
@@ -349,6 +350,7 @@ int32_t helios_gpu_spawn_batch(helios_gpu_world* w, const uint64_t* hashes, uint
                                cudaMemcpyHostToDevice, w->stream));
   }
   w->flushed_index = w->next_index;
+  ++w->mutation_epoch;
   HG_CUDA(w, cudaStreamSynchronize(w->stream));
   return HELIOS_GPU_OK;
 }
@@ -424,6 +426,7 @@ int32_t helios_gpu_archetype_column_write(helios_gpu_world* w, uint32_t a, uint6
   uint8_t* p;
   size_t bytes;
   HG_TRY(column_range(w, a, hash, row0, rows, &p, &bytes));
+  ++w->mutation_epoch;
   if (bytes) HG_CUDA(w, cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, w->stream));
   return HELIOS_GPU_OK;
 }

@@ -76,6 +76,8 @@ struct helios_gpu_world {
   int sm_count = 148;
   mutable std::string err;
   uint64_t launches = 0;
+  uint64_t mutation_epoch = 0; // bumped by anything that may write component columns or move rows (systems with a write
+                               // set, commands, column uploads, spawns): lets a system keep a validated cache of columns
   uint64_t epoch = 0;          // bumped whenever a device pointer or directory size a captured graph bakes in changes
 
   std::vector<hgpu::Component> comps;

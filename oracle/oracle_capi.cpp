@@ -663,7 +663,9 @@ HO_API int32_t helios_oracle_boids_bin(void* bp, void* slab_out, void* counts_ou
   std::vector<uint32_t> cursor(start.begin(), start.end() - 1);
   for (size_t i = 0; i < n; ++i) {  // ascending row order inside a cell
     const uint32_t slot = cursor[o_cell_of(pos[2 * i], pos[2 * i + 1], b->dim)]++;
-    slab[slot] = Boid4{pos[2 * i], pos[2 * i + 1], vel[2 * i], vel[2 * i + 1]};
+    // velocity components saturate at +-4 when binned (keeps every alignment term within the fixed-point range)
+    slab[slot] = Boid4{pos[2 * i], pos[2 * i + 1], std::fmin(std::fmax(vel[2 * i], -4.0f), 4.0f),
+                       std::fmin(std::fmax(vel[2 * i + 1], -4.0f), 4.0f)};
     b->orig[slot] = uint32_t(i);
   }
   return 0;
@@ -682,7 +684,7 @@ HO_API int32_t helios_oracle_boids_step(void* bp, const void* slabs_in, const vo
   auto* pos = reinterpret_cast<float*>(b->table->ColumnBytes(b->pos_col).data());
   auto* vel = reinterpret_cast<float*>(b->table->ColumnBytes(b->vel_col).data());
   const helios_gpu_boids_params P = b->p;
-  const float kEps = 0.01f, kQCoh = 16777216.0f, kQAli = 1048576.0f, kQSep = 65536.0f;
+  const float kEps = 0.01f, kQCoh = 1048576.0f, kQAli = 1048576.0f, kQSep = 65536.0f;
   auto work = [&](size_t lo, size_t hi_j) {
     for (size_t j = lo; j < hi_j; ++j) {
       const Boid4 me = slabs[size_t(my_shard) * n + j];

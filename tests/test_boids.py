@@ -19,7 +19,7 @@ def brute_force_step(pos, vel, world_size, p):
     """O(n^2) float32 numpy statement of one step (same per-pair arithmetic, int64 sums)."""
     f = np.float32
     n = pos.shape[0] // 2
-    P, V = pos.reshape(n, 2).astype(f), vel.reshape(n, 2).astype(f)
+    P, V = pos.reshape(n, 2).astype(f), np.clip(vel.reshape(n, 2).astype(f), f(-4.0), f(4.0))  # saturated when binned
     newP, newV = P.copy(), V.copy()
     dt, ws, wa, wc, vmax = (f(p[k]) for k in ("dt", "w_separation", "w_alignment", "w_cohesion", "max_speed"))
     cell = np.clip(P.astype(np.int32), 0, world_size - 1)
@@ -32,12 +32,12 @@ def brute_force_step(pos, vel, world_size, p):
         v = V[i].copy()
         if cnt:
             dn, vn, d2n = d[near], V[near], d2[near]
-            coh = np.rint((dn * f(16777216.0)).astype(f)).astype(np.int64).sum(axis=0)
+            coh = np.rint((dn * f(1048576.0)).astype(f)).astype(np.int64).sum(axis=0)
             ali = np.rint((vn * f(1048576.0)).astype(f)).astype(np.int64).sum(axis=0)
             inv = (f(1.0) / (d2n + f(0.01)).astype(f)).astype(f)
             sep = np.rint((((-dn) * inv[:, None]).astype(f) * f(65536.0)).astype(f)).astype(np.int64).sum(axis=0)
             nn = f(cnt)
-            cohf = ((coh.astype(f) / f(16777216.0)).astype(f) / nn).astype(f)
+            cohf = ((coh.astype(f) / f(1048576.0)).astype(f) / nn).astype(f)
             alif = (((ali.astype(f) / f(1048576.0)).astype(f) / nn).astype(f) - v).astype(f)
             sepf = (sep.astype(f) / f(65536.0)).astype(f)
             a = (((wc * cohf).astype(f) + (wa * alif).astype(f)).astype(f) + (ws * sepf).astype(f)).astype(f)
@@ -51,8 +51,8 @@ def brute_force_step(pos, vel, world_size, p):
     return newP.reshape(-1), newV.reshape(-1)
 
 
-def run_local(backend, n, world_size, steps, params=None):
-    s = boids.BoidsShard(backend, n, world_size, params=params)
+def run_local(backend, n, world_size, steps, params=None, vel_scale=1.0):
+    s = boids.BoidsShard(backend, n, world_size, params=params, vel_scale=vel_scale)
     for _ in range(steps):
         s.step_local()
     out = s.state()
@@ -67,6 +67,17 @@ def test_oracle_matches_brute_force(oracle):
     bp, bv = brute_force_step(pos, vel, ws, boids.DEFAULT_PARAMS)
     assert np.array_equal(p1, bp) and np.array_equal(v1, bv)
     assert not np.array_equal(p1, pos)
+
+
+def test_oracle_saturates_fast_boids(oracle):
+    """Velocities beyond +-4 (user-written; max_speed 8 keeps them alive) saturate component-wise when binned."""
+    n, ws = 300, 6
+    params = dict(boids.DEFAULT_PARAMS, max_speed=8.0)
+    pos, vel = boids.initial_state(n, ws, 0, n, vel_scale=6.0)
+    assert np.abs(vel).max() > 4.0
+    p1, v1 = run_local(oracle, n, ws, 1, params=params, vel_scale=6.0)
+    bp, bv = brute_force_step(pos, vel, ws, params)
+    assert np.array_equal(p1, bp) and np.array_equal(v1, bv)
 
 
 def test_shard_ranges():
@@ -122,6 +133,16 @@ def test_gpu_single_shard_matches_oracle(gpu, oracle, n, ws):
     steps = 3
     g, o = run_local(gpu, n, ws, steps), run_local(oracle, n, ws, steps)
     assert np.array_equal(g[0], o[0]) and np.array_equal(g[1], o[1])
+
+
+@pytest.mark.gpu
+def test_gpu_fast_boids_and_crowded_cells(gpu, oracle):
+    """Saturating velocities, and cells crowded enough (~28 boids each, ~250 candidates) for several hit-queue rounds."""
+    params = dict(boids.DEFAULT_PARAMS, max_speed=8.0)
+    for n, ws, scale in [(3000, 6, 6.0), (7000, 16, 1.0), (40000, 5, 1.0)]:
+        g = run_local(gpu, n, ws, 3, params=params, vel_scale=scale)
+        o = run_local(oracle, n, ws, 3, params=params, vel_scale=scale)
+        assert np.array_equal(g[0], o[0]) and np.array_equal(g[1], o[1])
 
 
 @pytest.mark.gpu
