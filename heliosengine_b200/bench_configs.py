@@ -214,6 +214,17 @@ def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
     shard.world.set_stream(stream.cuda_stream)
     buf = boids.ExchangeBuffers(torch, dev, world_size, shard.n_local, shard.n_cells)
     steps, warm = args.steps, max(3, args.warmup)
+    # N > 1: peer-memory exchange (merge kernels read the other GPUs' slabs over NVLink) unless --exchange nccl
+    peer = None
+    if world_size > 1 and getattr(args, "exchange", "p2p") == "p2p":
+        with torch.cuda.stream(stream):
+            peer = boids.PeerExchange(shard, torch, dist, dev)
+
+    def one_step():
+        if peer:
+            peer.step()
+        else:
+            boids.distributed_step(shard, buf, dist)
 
     def barrier():
         torch.cuda.synchronize()
@@ -223,13 +234,13 @@ def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
 
     with torch.cuda.stream(stream):
         for _ in range(warm):
-            boids.distributed_step(shard, buf, dist)
+            one_step()
         barrier()
         l0 = shard.world.launch_count()
         evs = _events(torch, steps)
         for a, b in evs:
             a.record(stream)
-            boids.distributed_step(shard, buf, dist)
+            one_step()
             b.record(stream)
         barrier()
         launches = shard.world.launch_count() - l0
@@ -238,13 +249,20 @@ def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
         ph = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
         g = shard.shard
         ph[0].record(stream)
-        shard.bin(buf.slab_slot(g).data_ptr(), buf.counts_slot(g).data_ptr())
-        ph[1].record(stream)
-        if world_size > 1:
-            dist.all_gather_into_tensor(buf.slabs, buf.slab_slot(g))
-            dist.all_gather_into_tensor(buf.counts, buf.counts_slot(g))
-        ph[2].record(stream)
-        shard.step(buf.slabs.data_ptr(), buf.counts.data_ptr())
+        if peer:
+            shard.exchange_bin()
+            ph[1].record(stream)
+            dist.all_reduce(peer.token)
+            ph[2].record(stream)
+            shard.exchange_step()
+        else:
+            shard.bin(buf.slab_slot(g).data_ptr(), buf.counts_slot(g).data_ptr())
+            ph[1].record(stream)
+            if world_size > 1:
+                dist.all_gather_into_tensor(buf.slabs, buf.slab_slot(g))
+                dist.all_gather_into_tensor(buf.counts, buf.counts_slot(g))
+            ph[2].record(stream)
+            shard.step(buf.slabs.data_ptr(), buf.counts.data_ptr())
         ph[3].record(stream)
         barrier()
         phases = {"bin_ms": ph[0].elapsed_time(ph[1]), "exchange_ms": ph[1].elapsed_time(ph[2]),
@@ -267,7 +285,7 @@ def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
             for _ in range(e2e_steps):
                 shard.world.column_write(tbl, P, 0, shard.n_local, hp.data_ptr())
                 shard.world.column_write(tbl, V, 0, shard.n_local, hv.data_ptr())
-                boids.distributed_step(shard, buf, dist)
+                one_step()
                 shard.world.column_read(tbl, P, 0, shard.n_local, ho.data_ptr())
                 shard.world.synchronize()
             barrier()
@@ -303,14 +321,17 @@ def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
         "dtype": "f32 pair terms, int64 fixed-point sums", "scaling": "strong",
         "config": {"workload": f"cfg5: {n_total} boids, world {ws}^2, cell = radius = 1 (density 4/cell), 3x3 stencil, "
                                f"entity-id range shards x{world_size}",
-                   "parallelism": f"{world_size} shard(s); per step 2 NCCL all-gathers (slabs 16 B/boid + u16 cell counts), "
-                                  f"{buf.exchange_bytes_per_rank} B received per rank",
+                   "parallelism": (f"{world_size} shard(s); peer-memory exchange: the merge kernels read the other GPUs' slabs "
+                                   f"(16 B/boid) and u16 cell counts in place over NVLink, {peer.bytes_pulled_per_step} B pulled "
+                                   f"per rank and step; one 4-byte NCCL all-reduce per step as the barrier" if peer else
+                                   f"{world_size} shard(s); per step 2 NCCL all-gathers (slabs 16 B/boid + u16 cell counts), "
+                                   f"{buf.exchange_bytes_per_rank} B received per rank"),
                    "l2": "per-step working set (slabs + tables) exceeds L2; no flush",
                    "parity": "bit-exact vs the CPU statement at test sizes, any shard count; no reference implementation (unpinned)"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak[0], "unit": "GB/s", "frac": achieved / peak[0],
                      "traffic": None, "peak_kind": peak[1], "algorithmic_bytes_per_launch": local_bytes,
                      "kernel": "bin (count/scan/scatter) + k_boids_neighbours, per GPU; exchange excluded from the bytes",
-                     "exchange_bytes_per_rank": buf.exchange_bytes_per_rank},
+                     "exchange_bytes_per_rank": peer.bytes_pulled_per_step if peer else buf.exchange_bytes_per_rank},
         "phases_ms": {"bin": bin_ms, "exchange": ex_ms, "neighbour": nb_ms},
         "e2e": ({"value": n_total / e2e_s, "unit": "boid updates/s", "h2d_bytes_per_step": shard.n_local * 16,
                  "d2h_bytes_per_step": shard.n_local * 8,
@@ -318,5 +339,7 @@ def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
                 if e2e_s else None),
         "cpu_baseline": cpu, "gpu_launches": int(launches),
     }
+    if peer:
+        peer.close()
     shard.close()
     return line

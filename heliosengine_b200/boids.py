@@ -76,6 +76,25 @@ class BoidsShard:
     def step_local(self):
         self.world._check(self.b.fn("boids_step_local")(self.h))
 
+    # -- peer-memory exchange (GPU library only) ---------------------------------------------------------------------------
+    def exchange_create(self):
+        self.world._check(self.b.fn("boids_exchange_create")(self.h, C.c_uint32(self.n_shards), C.c_uint32(self.shard)))
+
+    def exchange_local(self, generation: int) -> tuple[int, int]:
+        slab, counts = C.c_void_p(), C.c_void_p()
+        self.world._check(self.b.fn("boids_exchange_local")(self.h, C.c_uint32(generation), C.byref(slab), C.byref(counts)))
+        return slab.value, counts.value
+
+    def exchange_set_peer(self, shard: int, generation: int, slab_ptr: int, counts_ptr: int):
+        self.world._check(self.b.fn("boids_exchange_set_peer")(self.h, C.c_uint32(shard), C.c_uint32(generation),
+                                                               C.c_void_p(slab_ptr), C.c_void_p(counts_ptr)))
+
+    def exchange_bin(self):
+        self.world._check(self.b.fn("boids_exchange_bin")(self.h))
+
+    def exchange_step(self):
+        self.world._check(self.b.fn("boids_exchange_step")(self.h))
+
     def state(self) -> tuple[np.ndarray, np.ndarray]:
         """(positions, velocities) of this shard in entity-id order (the table's row order never changes)."""
         snap = self.world.snapshot()
@@ -125,6 +144,85 @@ def distributed_step(shard: BoidsShard, buf: ExchangeBuffers, dist=None, sync=No
         if sync:
             sync()
     shard.step(buf.slabs.data_ptr(), buf.counts.data_ptr())
+
+
+IPC_HANDLE_BYTES = 64
+
+
+class PeerExchange:
+    """NVLink form of the exchange, one process per GPU: every rank exports its two generations of {slab, counts} with
+    CUDA IPC, opens the other ranks' handles, and from then on a step is  bin -> 4-byte all-reduce (the barrier, on the
+    world's stream) -> merge-reading-peers + neighbour pass.  No slab ever goes through a collective."""
+
+    def __init__(self, shard: BoidsShard, torch, dist, device):
+        self.shard, self.dist = shard, dist
+        b, w = shard.b, shard.world
+        shard.exchange_create()
+        mine = torch.zeros(4 * IPC_HANDLE_BYTES, dtype=torch.uint8)
+        for gen in range(2):
+            for k, ptr in enumerate(shard.exchange_local(gen)):
+                h = (C.c_uint8 * IPC_HANDLE_BYTES)()
+                w._check(b.fn("ipc_export")(w.h, C.c_void_p(ptr), h))
+                off = (gen * 2 + k) * IPC_HANDLE_BYTES
+                mine[off:off + IPC_HANDLE_BYTES] = torch.frombuffer(bytearray(h), dtype=torch.uint8)
+        everyone = torch.empty(shard.n_shards * mine.numel(), dtype=torch.uint8, device=device)
+        dist.all_gather_into_tensor(everyone, mine.to(device))
+        everyone = everyone.cpu().numpy().reshape(shard.n_shards, 2, 2, IPC_HANDLE_BYTES)
+        self.opened = []
+        for g in range(shard.n_shards):
+            if g == shard.shard:
+                continue
+            for gen in range(2):
+                ptrs = []
+                for k in range(2):
+                    h = (C.c_uint8 * IPC_HANDLE_BYTES).from_buffer_copy(everyone[g, gen, k].tobytes())
+                    p = C.c_void_p()
+                    w._check(b.fn("ipc_open")(w.h, h, C.byref(p)))
+                    ptrs.append(p.value)
+                    self.opened.append(p.value)
+                shard.exchange_set_peer(g, gen, ptrs[0], ptrs[1])
+        self.token = torch.zeros(1, dtype=torch.int32, device=device)
+        self.bytes_pulled_per_step = (shard.n_shards - 1) * (shard.n_local * SLAB_BYTES + 2 * shard.n_cells * COUNT_BYTES)
+
+    def step(self):
+        self.shard.exchange_bin()
+        self.dist.all_reduce(self.token)  # device-side barrier: every shard's buffers of this generation are complete
+        self.shard.exchange_step()
+
+    def close(self):
+        w = self.shard.world
+        w.synchronize()
+        self.dist.barrier()  # nobody closes a mapping a peer may still be reading
+        for p in self.opened:
+            self.shard.b.fn("ipc_close")(w.h, C.c_void_p(p))
+        self.opened = []
+
+
+def emulate_shards_peer(backend: capi.Backend, n_total: int, world_size: int, n_shards: int, steps: int,
+                        params: dict | None = None):
+    """Peer-memory exchange with all shards in ONE process on one GPU: the "peer" pointers are the other shards' own
+    buffers (no IPC needed inside a process).  Returns the global (positions, velocities)."""
+    shards = [BoidsShard(backend, n_total, world_size, n_shards, g, params=params) for g in range(n_shards)]
+    for s in shards:
+        s.exchange_create()
+    for s in shards:
+        for o in shards:
+            if o is not s:
+                for gen in range(2):
+                    s.exchange_set_peer(o.shard, gen, *o.exchange_local(gen))
+    for _ in range(steps):
+        for s in shards:
+            s.exchange_bin()
+        for s in shards:  # the barrier
+            s.world.synchronize()
+        for s in shards:
+            s.exchange_step()
+        for s in shards:
+            s.world.synchronize()
+    states = [s.state() for s in shards]
+    for s in shards:
+        s.close()
+    return np.concatenate([p for p, _ in states]), np.concatenate([v for _, v in states])
 
 
 def emulate_shards(backend: capi.Backend, torch, device, n_total: int, world_size: int, n_shards: int, steps: int,

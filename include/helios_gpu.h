@@ -376,6 +376,29 @@ HELIOS_GPU_API int32_t helios_gpu_boids_step(helios_gpu_boids* b, const void* sl
 /* Single-shard convenience: bin + step on internal buffers. */
 HELIOS_GPU_API int32_t helios_gpu_boids_step_local(helios_gpu_boids* b);
 
+/* Peer-memory exchange: the NVLink form of the three calls above.  Every shard keeps its slab and counts in two
+ * generations of buffers it owns (plain cudaMalloc, exportable with helios_gpu_ipc_export); the other shards' merge
+ * kernels read them IN PLACE — P2P loads over NVLink/NVSwitch when the shard lives on another GPU — so the all-gather
+ * and the local copy of the peers' slabs disappear into the merge.  Per step, on every rank:
+ *     helios_gpu_boids_exchange_bin(b);     bin into the own buffers of the current generation
+ *     <one barrier on the world's stream>   e.g. a 4-byte NCCL all-reduce: every shard's buffers are complete
+ *     helios_gpu_boids_exchange_step(b);    merge (reading peers) + neighbour pass + integrate; flips the generation
+ * Two generations make that single barrier sufficient: a shard overwrites generation k only after the next barrier,
+ * which every peer reaches after it has finished reading generation k.  All shards must hold the same number of boids. */
+HELIOS_GPU_API int32_t helios_gpu_boids_exchange_create(helios_gpu_boids* b, uint32_t n_shards, uint32_t my_shard);
+HELIOS_GPU_API int32_t helios_gpu_boids_exchange_local(helios_gpu_boids* b, uint32_t generation, void** slab, void** counts);
+HELIOS_GPU_API int32_t helios_gpu_boids_exchange_set_peer(helios_gpu_boids* b, uint32_t shard, uint32_t generation,
+                                                          const void* slab, const void* counts);
+HELIOS_GPU_API int32_t helios_gpu_boids_exchange_bin(helios_gpu_boids* b);
+HELIOS_GPU_API int32_t helios_gpu_boids_exchange_step(helios_gpu_boids* b);
+
+/* CUDA IPC plumbing for the peer pointers (one process per GPU): export a device allocation of this process as a 64-byte
+ * handle, open a handle received from another process (peer access is enabled on first use), close it again. */
+#define HELIOS_GPU_IPC_HANDLE_BYTES 64
+HELIOS_GPU_API int32_t helios_gpu_ipc_export(helios_gpu_world* w, const void* device_ptr, uint8_t handle[HELIOS_GPU_IPC_HANDLE_BYTES]);
+HELIOS_GPU_API int32_t helios_gpu_ipc_open(helios_gpu_world* w, const uint8_t handle[HELIOS_GPU_IPC_HANDLE_BYTES], void** device_ptr);
+HELIOS_GPU_API int32_t helios_gpu_ipc_close(helios_gpu_world* w, void* device_ptr);
+
 /* Launch accounting: a system body reports the kernels it enqueued (for_each_launch does this itself). */
 HELIOS_GPU_API void helios_gpu_world_note_launches(helios_gpu_world* w, uint32_t n);
 

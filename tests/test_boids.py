@@ -156,6 +156,16 @@ def test_gpu_shards_match_single_shard_oracle(gpu, oracle, n_shards):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("n_shards", [2, 3, 8, 16])
+def test_gpu_peer_memory_exchange_matches_oracle(gpu, oracle, n_shards):
+    """helios_gpu_boids_exchange_*: shards read each other's buffers in place (peer pointers wired inside one process)."""
+    n, ws, steps = 49152, 96, 4  # 4 steps: both buffer generations are reused
+    ref = run_local(oracle, n, ws, steps)
+    got = boids.emulate_shards_peer(gpu, n, ws, n_shards, steps)
+    assert np.array_equal(ref[0], got[0]) and np.array_equal(ref[1], got[1])
+
+
+@pytest.mark.gpu
 def test_gpu_full_density_properties(gpu):
     """cfg5 density (4 boids per cell) at 4M boids: in bounds, speed-limited, deterministic across two runs."""
     n, ws = 1 << 22, 1024
