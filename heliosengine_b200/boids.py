@@ -182,7 +182,8 @@ class PeerExchange:
                     self.opened.append(p.value)
                 shard.exchange_set_peer(g, gen, ptrs[0], ptrs[1])
         self.token = torch.zeros(1, dtype=torch.int32, device=device)
-        self.bytes_pulled_per_step = (shard.n_shards - 1) * (shard.n_local * SLAB_BYTES + 2 * shard.n_cells * COUNT_BYTES)
+        # per peer: its slab, its u8 cell counts and its per-tile sums (1024-cell tiles)
+        self.bytes_pulled_per_step = (shard.n_shards - 1) * (shard.n_local * SLAB_BYTES + shard.n_cells + 4 * -(-shard.n_cells // 1024))
 
     def step(self):
         self.shard.exchange_bin()
