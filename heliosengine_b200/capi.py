@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import struct
 from typing import Iterable, Sequence
 
 import numpy as np
@@ -356,6 +357,55 @@ class Query:
         else:
             self.w._check(self.w.b.fn("query_count_w")(self.w.h, self.h, C.byref(v)))
         return v.value
+
+
+    # -- terminals (query.hpp:180,822,1040-1180) -----------------------------------------------------------------------------
+    def terminal(self, name: str, params: bytes = b"") -> "TerminalResult":
+        """Runs a built-in terminal (helios_gpu_builtin_terminal) over this query and returns its result."""
+        b = self.w.b
+        fn, flags = C.c_void_p(), C.c_uint32()
+        self.w._check(b.fn("builtin_terminal")(name.encode(), C.byref(fn), C.byref(flags)))
+        out = TerminalResult()
+        buf = C.create_string_buffer(params, len(params)) if params else None
+        if b.is_gpu:
+            self.w._check(b.fn("query_terminal")(self.h, fn, buf, C.c_uint32(len(params)), flags, C.byref(out)))
+        else:
+            self.w._check(b.fn("query_terminal_w")(self.w.h, self.h, fn, buf, C.c_uint32(len(params)), flags, C.byref(out)))
+        return out
+
+    def terminal_entities(self, group: int) -> np.ndarray:
+        """Entities of the last partition-style terminal: group 0 = predicate true, 1 = the rest (iteration order)."""
+        n = C.c_uint64()
+        rc = self.w.b.fn("query_terminal_entities")(self.h, C.c_uint32(group), None, C.c_uint64(0), C.byref(n))
+        if rc not in (0, ERR_CAPACITY):
+            self.w._check(rc)
+        out = np.empty(n.value, dtype=np.uint64)
+        if n.value:
+            self.w._check(self.w.b.fn("query_terminal_entities")(self.h, C.c_uint32(group), out.ctypes.data_as(C.c_void_p),
+                                                                 C.c_uint64(n.value), C.byref(n)))
+        return out
+
+    # reference spellings on top of the built-in predicate `Position.x > t`
+    def count_if_pos_x_gt(self, t: float) -> int:
+        return self.terminal("count_if_pos_x_gt", struct.pack("<f", t)).count
+
+    def any_pos_x_gt(self, t: float) -> bool:  # Any = Find(...).has_value()  (query.hpp:1142-1144)
+        return self.terminal("find_pos_x_gt", struct.pack("<f", t)).index != NO_ROW
+
+    def none_pos_x_gt(self, t: float) -> bool:  # None = !Any  (query.hpp:1166-1168)
+        return not self.any_pos_x_gt(t)
+
+    def all_pos_x_gt(self, t: float) -> bool:  # All: no row fails; vacuously true on an empty match set
+        r = self.terminal("count_if_pos_x_gt", struct.pack("<f", t))
+        return r.count == r.visited
+
+
+NO_ROW = 0xFFFFFFFFFFFFFFFF
+
+
+class TerminalResult(C.Structure):
+    _fields_ = [("visited", C.c_uint64), ("count", C.c_uint64), ("index", C.c_uint64), ("entity", C.c_uint64),
+                ("f64", C.c_double), ("i64", C.c_int64)]
 
 
 class Schedule:

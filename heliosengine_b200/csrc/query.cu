@@ -133,6 +133,36 @@ int32_t query_refresh(helios_gpu_query* q, cudaStream_t stream) {
   return HELIOS_GPU_OK;
 }
 
+// The query-dependent part of a system / terminal context: world view, fused-match arguments, and a materialised view
+// when the world has more tables than the fused match handles (or the caller asks for one).
+int32_t fill_query_ctx(helios_gpu_system_ctx* ctx, helios_gpu_query* q, cudaStream_t stream, bool want_view) {
+  helios_gpu_world* w = q->world;
+  ctx->world = w;
+  ctx->stream = stream;
+  ctx->sm_count = uint32_t(w->sm_count);
+  ctx->query_rows = HELIOS_GPU_NO_ROW;
+  ctx->world_view.entity_location = w->d_loc.as<uint64_t>();
+  ctx->world_view.entity_generation = w->d_gen.as<uint32_t>();
+  ctx->world_view.table_columns = w->d_tcols.as<void*>();
+  ctx->world_view.table_mask = w->d_tmask.as<uint64_t>();
+  ctx->world_view.entity_capacity = w->ent_capacity;
+  ctx->world_view.n_tables = uint32_t(w->tables.size());
+  ctx->match.table_mask = w->d_tmask.as<uint64_t>();
+  ctx->match.table_rows = w->d_tcount.as<uint32_t>();
+  ctx->match.table_entities = w->d_tents.as<const helios_gpu_entity_t*>();
+  ctx->match.table_columns = w->d_tcols.as<void*>();
+  ctx->match.n_tables = q->never_matches ? 0u : uint32_t(w->tables.size());
+  ctx->match.n_components = q->desc.n_components;
+  ctx->match.required_mask = q->required_mask;
+  ctx->match.without_mask = q->without_mask;
+  for (uint32_t k = 0; k < q->desc.n_components; ++k) ctx->match.slots[k] = q->slots[k];
+  if (want_view || w->tables.size() > HELIOS_GPU_FUSED_MATCH_MAX_TABLES) {
+    HG_TRY(query_refresh(q, stream));  // stand-alone match kernel -> materialised view
+    ctx->view = q->d_view.as<helios_gpu_query_view>();
+  }
+  return HELIOS_GPU_OK;
+}
+
 }  // namespace hgpu
 
 extern "C" {
@@ -167,6 +197,9 @@ int32_t helios_gpu_query_create(helios_gpu_world* w, const helios_gpu_query_desc
   HG_CUDA(w, q->d_view.reserve(sizeof(helios_gpu_query_view), 0, w->stream, false));
   HG_CUDA(w, cudaMemsetAsync(q->d_view.ptr, 0, sizeof(helios_gpu_query_view), w->stream));
   w->queries.push_back(q.get());
+  // scratch of the terminal-style bodies (helios_gpu_terminals.cuh): ticket + per-CTA partials; ticket starts at zero
+  HG_CUDA(w, q->scratch.reserve(4096 + 64 * 1024, 0, w->stream, false));
+  HG_CUDA(w, cudaMemsetAsync(q->scratch.ptr, 0, 64, w->stream));
   *out = q.release();
   return HELIOS_GPU_OK;
 }

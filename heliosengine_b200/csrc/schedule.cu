@@ -154,11 +154,7 @@ int32_t launch_system(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaS
   ctx.world = w;
   ctx.stream = stream;
   ctx.sm_count = uint32_t(w->sm_count);
-  ctx.system_index = index;
-  ctx.params = e.params.data();
-  ctx.params_size = uint32_t(e.params.size());
-  ctx.resources = s->resources.ptr;
-  ctx.host_user = e.desc.host_user;
+  ctx.query_rows = HELIOS_GPU_NO_ROW;
   ctx.world_view.entity_location = w->d_loc.as<uint64_t>();
   ctx.world_view.entity_generation = w->d_gen.as<uint32_t>();
   ctx.world_view.table_columns = w->d_tcols.as<void*>();
@@ -167,20 +163,17 @@ int32_t launch_system(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaS
   ctx.world_view.n_tables = uint32_t(w->tables.size());
   if (e.desc.query) {
     helios_gpu_query* q = e.desc.query;
-    ctx.match.table_mask = w->d_tmask.as<uint64_t>();
-    ctx.match.table_rows = w->d_tcount.as<uint32_t>();
-    ctx.match.table_entities = w->d_tents.as<const helios_gpu_entity_t*>();
-    ctx.match.table_columns = w->d_tcols.as<void*>();
-    ctx.match.n_tables = q->never_matches ? 0u : uint32_t(w->tables.size());
-    ctx.match.n_components = q->desc.n_components;
-    ctx.match.required_mask = q->required_mask;
-    ctx.match.without_mask = q->without_mask;
-    for (uint32_t k = 0; k < q->desc.n_components; ++k) ctx.match.slots[k] = q->slots[k];
-    if ((e.desc.flags & HELIOS_GPU_SYSTEM_NEEDS_VIEW) || w->tables.size() > HELIOS_GPU_FUSED_MATCH_MAX_TABLES) {
-      HG_TRY(query_refresh(q, stream));  // stand-alone match kernel → materialised view
-      ctx.view = q->d_view.as<helios_gpu_query_view>();
-    }
+    HG_TRY(fill_query_ctx(&ctx, q, stream, (e.desc.flags & HELIOS_GPU_SYSTEM_NEEDS_VIEW) != 0));
+    // terminal-style bodies (helios_gpu_terminals.cuh) reduce through the query's own scratch (allocated with the
+    // query): one per system, so concurrently running systems never share it
+    ctx.scratch = q->scratch.ptr;
+    ctx.scratch_bytes = q->scratch.bytes;
   }
+  ctx.system_index = index;
+  ctx.params = e.params.data();
+  ctx.params_size = uint32_t(e.params.size());
+  ctx.resources = s->resources.ptr;
+  ctx.host_user = e.desc.host_user;
   if (e.desc.flags & HELIOS_GPU_SYSTEM_EMITS_COMMANDS) {
     if (e.cmd_slots_in_use)  // all-ones = kind NONE in every slot
       HG_CUDA(w, cudaMemsetAsync(e.cmd_records.ptr, 0xFF, e.cmd_slots_in_use * sizeof(helios_gpu_command), stream));

@@ -67,6 +67,9 @@ struct helios_gpu_query {
   hgpu::DevBuf d_view;          // helios_gpu_query_view
   hgpu::DevBuf d_segments;      // helios_gpu_segment[table capacity]
   uint32_t seg_capacity = 0;
+  // query terminals (terminals.cu): reduction partials / partition arrays, the device result, the last partition's sizes
+  hgpu::DevBuf scratch, result;
+  uint64_t terminal_rows = ~0ull, terminal_yes = 0;
 };
 
 struct helios_gpu_world {

@@ -285,6 +285,11 @@ typedef struct helios_gpu_system_ctx {
   helios_gpu_world_view world_view;    /* entity-id random access */
   void* resources;                     /* device scratch of HELIOS_GPU_RESOURCE_BYTES shared by the schedule's systems */
   void* host_user;
+  /* query terminals (below): per-query device scratch (first 64 bytes zero at launch), its size, and the number of rows
+   * the query matches when the caller already knows it (HELIOS_GPU_NO_ROW otherwise) */
+  void* scratch;
+  uint64_t scratch_bytes;
+  uint64_t query_rows;
 } helios_gpu_system_ctx;
 #define HELIOS_GPU_RESOURCE_BYTES 4096u
 
@@ -341,6 +346,34 @@ HELIOS_GPU_API int32_t helios_gpu_schedule_stream_count(helios_gpu_schedule* s, 
 /* Copy the schedule's device resource scratch (HELIOS_GPU_RESOURCE_BYTES) to the host. */
 HELIOS_GPU_API int32_t helios_gpu_schedule_read_resources(helios_gpu_schedule* s, void* out, uint32_t bytes);
 
+
+/* ---- query terminals (query/query.hpp:1040-1180: Find / Any / All / None / CountIf / Fold / MinBy / MaxBy / Partition,
+ * :180 CollectEntities, :822 Filter) as device reductions and ordered compactions ------------------------------------
+ * A terminal is a launch function like a system body (written against helios_gpu_terminals.cuh: reduce_launch<> /
+ * partition_launch<>) that leaves a helios_gpu_terminal_result at ctx->resources.  helios_gpu_query_terminal runs it at
+ * once on the world's stream and returns the result; registered in a schedule it is an ordinary read-only system whose
+ * result is read with helios_gpu_schedule_read_resource.  Reference semantics kept: iteration order = archetype creation
+ * order then row order; Find = FIRST match; MinBy / MaxBy = first extremum (strict comparison, functional_adapters.hpp:
+ * 4172-4268); Any = Find has a value, None = !Any, All = no row fails (vacuously true), CountIf / Fold over every row.
+ * Floating-point Fold is a fixed-shape f64 tree, not the reference's left fold: deterministic, within rounding of it. */
+#define HELIOS_GPU_NO_ROW 0xFFFFFFFFFFFFFFFFull
+typedef struct helios_gpu_terminal_result {
+  uint64_t visited;            /* rows iterated = Query::Count() */
+  uint64_t count;              /* CountIf; Partition / Filter: size of the matching group */
+  uint64_t index;              /* Find / MinBy / MaxBy: iteration position of the result, HELIOS_GPU_NO_ROW = nullopt */
+  helios_gpu_entity_t entity;  /* ... its entity (HELIOS_GPU_INVALID_ENTITY if none) */
+  double f64;                  /* Fold over floats; MinBy / MaxBy: the winning key */
+  int64_t i64;                 /* Fold over integers (exact) */
+} helios_gpu_terminal_result;
+#define HELIOS_GPU_TERMINAL_PER_ROW_SCRATCH 1u /* the terminal needs 24 B of scratch per matched row (partition/collect) */
+HELIOS_GPU_API int32_t helios_gpu_query_terminal(helios_gpu_query* q, helios_gpu_system_fn launch, const void* params,
+                                                 uint32_t params_size, uint32_t flags, helios_gpu_terminal_result* out);
+/* Entities of the last partition-style terminal of `q`, in iteration order: group 0 = predicate true (Filter +
+ * CollectEntities), group 1 = the rest.  Returns HELIOS_GPU_ERR_CAPACITY if `capacity` is too small. */
+HELIOS_GPU_API int32_t helios_gpu_query_terminal_entities(helios_gpu_query* q, uint32_t group, helios_gpu_entity_t* out,
+                                                          uint64_t capacity, uint64_t* n_out);
+/* Terminals over the benchmark components (heliosengine_b200/csrc/terminals.cu), by name; `flags` = what to pass on. */
+HELIOS_GPU_API int32_t helios_gpu_builtin_terminal(const char* name, helios_gpu_system_fn* out, uint32_t* flags);
 
 /* ---- boids: uniform-grid neighbour query over an entity-range shard (BASELINE configs[4]) -------
  * The reference has no neighbour-interaction system (parity unpinned — DESIGN.md §7); in reference terms this is one

@@ -20,6 +20,8 @@ namespace {
 
 struct OQuery {
   ho::QueryDesc desc;
+  std::vector<helios_gpu_entity_t> terminal_groups[2];  // last partition-style terminal: (matching, rest)
+  bool terminal_ran = false;
 };
 
 struct OWorld;
@@ -420,6 +422,111 @@ HO_API int32_t helios_oracle_query_match_w(void* wp, void* q, uint32_t* out, uin
 }
 HO_API int32_t helios_oracle_query_count_w(void* wp, void* q, uint64_t* out) {
   *out = ho::QueryCount(W(wp)->world.components, reinterpret_cast<OQuery*>(q)->desc);
+  return 0;
+}
+
+// ---- query terminals: the reference's sequential definitions ------------------------------------------------
+// (query/query.hpp:1040-1180 -> utils/functional_adapters.hpp:4050-4268).  One ordered walk (ForEach order) per call.
+namespace {
+struct OTerminal {
+  const char* name;
+  uint32_t flags;
+};
+const OTerminal kTerminals[] = {
+    {"count_if_pos_x_gt", 0},  {"find_pos_x_gt", 0},      {"max_by_pos_x", 0}, {"min_by_pos_x", 0},
+    {"fold_sum_pos_x", 0},     {"fold_sum_health_hp", 0}, {"partition_pos_x_gt", HELIOS_GPU_TERMINAL_PER_ROW_SCRATCH},
+};
+}  // namespace
+HO_API int32_t helios_oracle_builtin_terminal(const char* name, const char** out, uint32_t* flags) {
+  for (const OTerminal& t : kTerminals)
+    if (std::strcmp(t.name, name) == 0) {
+      *out = t.name;  // the oracle's "launch function" is the terminal's name
+      if (flags) *flags = t.flags;
+      return 0;
+    }
+  return HELIOS_GPU_ERR_NOT_FOUND;
+}
+HO_API int32_t helios_oracle_query_terminal_w(void* wp, void* qp, const char* name, const void* params, uint32_t params_size,
+                                              uint32_t, helios_gpu_terminal_result* out) {
+  OWorld* w = W(wp);
+  auto* q = reinterpret_cast<OQuery*>(qp);
+  float t = 0.0f;
+  if (params && params_size >= 4) std::memcpy(&t, params, 4);
+  helios_gpu_terminal_result r{};
+  r.index = HELIOS_GPU_NO_ROW;
+  r.entity = HELIOS_GPU_INVALID_ENTITY;
+  const std::string n = name;
+  uint64_t i = 0;
+  if (n == "count_if_pos_x_gt") {  // CountIf: functional_adapters.hpp:4099
+    ho::ForEach(w->world.components, q->desc, [&](ho::Entity, uint8_t** p) {
+      r.count += reinterpret_cast<const Position*>(p[0])->x > t;
+      ++i;
+    });
+  } else if (n == "find_pos_x_gt") {  // Find: the FIRST match (functional_adapters.hpp:4069)
+    ho::ForEach(w->world.components, q->desc, [&](ho::Entity e, uint8_t** p) {
+      if (r.index == HELIOS_GPU_NO_ROW && reinterpret_cast<const Position*>(p[0])->x > t) {
+        r.index = i;
+        r.entity = e.Pack();
+        r.count = 1;
+      }
+      ++i;
+    });
+  } else if (n == "max_by_pos_x" || n == "min_by_pos_x") {  // strict comparison: the first extremum wins (:4172-4268)
+    const bool is_max = n[1] == 'a';
+    float best = 0.0f;
+    ho::ForEach(w->world.components, q->desc, [&](ho::Entity e, uint8_t** p) {
+      const float k = reinterpret_cast<const Position*>(p[0])->x;
+      if (i == 0 || (is_max ? k > best : k < best)) {
+        best = k;
+        r.index = i;
+        r.entity = e.Pack();
+        r.f64 = double(k);
+      }
+      ++i;
+    });
+  } else if (n == "fold_sum_pos_x") {  // Fold(0.0f, acc + pos.x): i64 carries the bits of the reference's f32 left fold
+    float acc = 0.0f;
+    ho::ForEach(w->world.components, q->desc, [&](ho::Entity, uint8_t** p) {
+      const float x = reinterpret_cast<const Position*>(p[0])->x;
+      acc = acc + x;
+      r.f64 += double(x);
+      ++i;
+    });
+    uint32_t bits;
+    std::memcpy(&bits, &acc, 4);
+    r.i64 = int64_t(bits);
+  } else if (n == "fold_sum_health_hp") {
+    ho::ForEach(w->world.components, q->desc, [&](ho::Entity, uint8_t** p) {
+      int32_t hp;
+      std::memcpy(&hp, p[0], 4);
+      r.i64 += hp;
+      ++i;
+    });
+  } else if (n == "partition_pos_x_gt") {  // Partition (:1086) / Filter + CollectEntities: both groups in iteration order
+    q->terminal_groups[0].clear();
+    q->terminal_groups[1].clear();
+    ho::ForEach(w->world.components, q->desc, [&](ho::Entity e, uint8_t** p) {
+      q->terminal_groups[reinterpret_cast<const Position*>(p[0])->x > t ? 0 : 1].push_back(e.Pack());
+      ++i;
+    });
+    q->terminal_ran = true;
+    r.count = q->terminal_groups[0].size();
+  } else {
+    return HELIOS_GPU_ERR_NOT_FOUND;
+  }
+  r.visited = i;
+  *out = r;
+  return 0;
+}
+HO_API int32_t helios_oracle_query_terminal_entities(void* qp, uint32_t group, helios_gpu_entity_t* out, uint64_t capacity,
+                                                     uint64_t* n_out) {
+  auto* q = reinterpret_cast<OQuery*>(qp);
+  if (group > 1) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (!q->terminal_ran) return HELIOS_GPU_ERR_STATE;
+  const auto& g = q->terminal_groups[group];
+  if (n_out) *n_out = g.size();
+  if (capacity < g.size()) return HELIOS_GPU_ERR_CAPACITY;
+  std::copy(g.begin(), g.end(), out);
   return 0;
 }
 
