@@ -203,6 +203,107 @@ def run_cfg1(args, torch, dev, stream, peak):
     }
 
 
+def run_terminals(args, torch, dev, stream, peak):
+    """Query terminals over the cfg2 world, `Query<const Position&>` on all 64 tables: every call goes
+    through the public immediate API (helios_gpu_query_terminal: launch, 48-byte result back, synchronise), timed with
+    CUDA events around the call; L2 flushed (write 256 MiB, read 256 MiB) between calls."""
+    n = args.entities or (1 << 24)
+    gpu = capi.load_gpu()
+    w = capi.World(gpu, device=dev.index, entity_capacity=n + 1024)
+    w.set_stream(stream.cuda_stream)
+    worlds.build_lattice(w, n, worlds.OPTIONAL)
+    q = w.query([(worlds.cname("Position"), False)])
+    steps, warm = args.steps, max(3, args.warmup)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    flush_rd = torch.ones(256 << 20, dtype=torch.uint8, device=dev)
+    sink = torch.zeros((), dtype=torch.int64, device=dev)
+    thr = __import__("struct").pack("<f", 500.0)
+    # algorithmic bytes per row: Position (8) [+ entity id (8) where the result names an entity];
+    # partition: Position + flag w/r/r + position w(scan)/r(add)/w/r + entity r/w
+    legs = [("count_if_pos_x_gt", thr, 8), ("find_pos_x_gt", thr, 16), ("max_by_pos_x", b"", 16), ("fold_sum_pos_x", b"", 8),
+            ("partition_pos_x_gt", thr, 8 + 4 * 3 + 4 * 4 + 8 + 8 + 8)]
+    out, launches = {}, 0
+    with torch.cuda.stream(stream):
+        for name, params, bpr in legs:
+            for _ in range(warm):
+                q.terminal(name, params)
+            ms = []
+            l0 = w.launch_count()
+            for _ in range(steps):
+                flush.fill_(1)
+                torch.sum(flush_rd, dim=(0,), dtype=torch.int64, out=sink)
+                torch.cuda.synchronize()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(stream)
+                r = q.terminal(name, params)
+                b.record(stream)
+                torch.cuda.synchronize()
+                ms.append(a.elapsed_time(b))
+            launches += w.launch_count() - l0
+            med = float(np.median(ms))
+            out[name] = {"ms": med, "rows_per_s": n / (med * 1e-3), "bytes_per_row": bpr,
+                         "GBps": n * bpr / (med * 1e-3) / 1e9, "frac": n * bpr / (med * 1e-3) / 1e9 / peak[0],
+                         "result": {"visited": r.visited, "count": r.count, "index": r.index}}
+        # the same reductions as systems of a schedule: no host round trip inside the timed region (device-resident `value`)
+        for name, params, bpr in legs[:4]:
+            s = w.schedule("T_" + name)
+            s.add_system(name, name, q, params=params)
+            s.build()
+            for _ in range(warm):
+                s.run_and_wait(capi.EXEC_SERIAL)
+            ms = []
+            for _ in range(steps):
+                flush.fill_(1)
+                torch.sum(flush_rd, dim=(0,), dtype=torch.int64, out=sink)
+                torch.cuda.synchronize()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(stream)
+                s.run(capi.EXEC_SERIAL)
+                b.record(stream)
+                s.apply_deferred()
+                ms.append(a.elapsed_time(b))
+            launches += steps
+            res = s.read_resources(48).view(np.uint64)
+            imm = out[name]["result"]
+            assert int(res[0]) == imm["visited"] and int(res[1]) == imm["count"] and int(res[2]) == imm["index"]
+            med = float(np.median(ms))
+            out[name].update({"system_ms": med, "system_GBps": n * bpr / (med * 1e-3) / 1e9,
+                              "system_frac": n * bpr / (med * 1e-3) / 1e9 / peak[0]})
+            s.close()
+    cpu = None
+    if not args.no_cpu_baseline:
+        o = capi.load_oracle()
+        sn = n // 8
+        wo = capi.World(o)
+        worlds.build_lattice(wo, sn, worlds.OPTIONAL)
+        qo = wo.query([(worlds.cname("Position"), False)])
+        qo.terminal("count_if_pos_x_gt", thr)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            qo.terminal("count_if_pos_x_gt", thr)
+        dt = (time.perf_counter() - t0) / 3
+        cpu = {"value": sn / dt, "unit": "rows/s", "cores": 1, "kind": "port",
+               "sample": f"CountIf over {sn} rows / 64 tables (1/8 scale), sequential ordered walk, 3 repetitions"}
+        wo.close()
+    w.close()
+    head = out["count_if_pos_x_gt"]
+    return {
+        "metric": "query_terminal_rows_per_sec", "value": n / (head["system_ms"] * 1e-3), "unit": "rows/s",
+        "ms_per_step": head["system_ms"],
+        "dtype": "f32 keys, u64 counts / positions, f64 sums",
+        "config": {"workload": f"terminals: CountIf(Position.x > 500) over {n} rows / 64 tables through helios_gpu_query_terminal "
+                               "(headline); Find, MaxBy, Fold, Partition in `terminals`",
+                   "l2": "flushed between calls: 256 MiB written, then 256 MiB read"},
+        "roofline": {"bound": "hbm", "achieved": head["system_GBps"], "peak": peak[0], "unit": "GB/s", "frac": head["system_frac"],
+                     "traffic": None, "peak_kind": peak[1], "algorithmic_bytes_per_launch": n * 8,
+                     "kernel": "helios_gpu::for_each_kernel<ReduceBody<CountIfReducer<...>>, Position> as a schedule system"},
+        "terminals": out,
+        "e2e": {"value": head["rows_per_s"], "unit": "rows/s", "h2d_bytes_per_step": 4, "d2h_bytes_per_step": 48,
+                "note": "helios_gpu_query_terminal: predicate parameter in, launch, 48-byte result back, synchronise"},
+        "cpu_baseline": cpu, "gpu_launches": int(launches),
+    }
+
+
 def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
     """Boids, STRONG scaling: `--entities` boids in total (default 64M, density 4 per cell) split by entity-id range over
     the ranks; per step: bin own shard, all-gather slabs + counts (NCCL), neighbour pass + integrate."""

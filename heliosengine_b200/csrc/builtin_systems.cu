@@ -231,5 +231,10 @@ extern "C" int32_t helios_gpu_builtin_system(const char* name, helios_gpu_system
       *out = e.fn;
       return HELIOS_GPU_OK;
     }
+  // the reduction-style terminals (terminals.cu) are ordinary read-only systems too: their result lands at offset 0 of the
+  // schedule's resources (partition-style ones need helios_gpu_query_terminal, which sizes the per-row scratch)
+  uint32_t flags = 0;
+  if (helios_gpu_builtin_terminal(name, out, &flags) == HELIOS_GPU_OK && flags == 0) return HELIOS_GPU_OK;
+  *out = nullptr;
   return HELIOS_GPU_ERR_NOT_FOUND;
 }

@@ -191,8 +191,13 @@ __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<
 // ---------------------------------------------------------------------------------------------------
 constexpr int kFusedMaxTables = 1024;
 
+// Narrow rows (<= 16 B per row over all data components) keep few bytes in flight per thread: ask for all 8 CTAs per SM
+// (<= 32 registers) so that the loads of enough threads overlap; wider queries have the memory parallelism already.
+template <bool kWithEntity, typename... Cs>
+constexpr int kForEachMinBlocks = ((0 + ... + int(sizeof(Cs))) + (kWithEntity ? 8 : 0) <= 16) ? 8 : 1;
+
 template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
-__global__ void __launch_bounds__(kBlock) for_each_kernel(const helios_gpu_match_args m, Body body) {
+__global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity, Cs...>) for_each_kernel(const helios_gpu_match_args m, Body body) {
   constexpr int N = sizeof...(Cs);
   static_assert(N >= 1 && N <= HELIOS_GPU_MAX_QUERY_COMPONENTS, "1..8 data components per body");
   __shared__ uint32_t s_tile_begin[kFusedMaxTables + 1];

@@ -47,23 +47,44 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* total)
 }
 
 // Pass 1: per-tile exclusive scan written in place to `out`, tile totals to partials[tile].
+// 8 consecutive u32 of one thread: two 128-bit accesses when the tile is whole and the pointer 16-byte aligned.
+__device__ __forceinline__ void scan_load8(const uint32_t* __restrict__ p, uint64_t base, uint64_t n, bool vec, uint32_t (&v)[kScanItems]) {
+  if (vec && base + kScanItems <= n) {
+    const uint4 a = *reinterpret_cast<const uint4*>(p + base), b = *reinterpret_cast<const uint4*>(p + base + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  } else {
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) v[i] = base + i < n ? p[base + i] : 0u;
+  }
+}
+__device__ __forceinline__ void scan_store8(uint32_t* __restrict__ p, uint64_t base, uint64_t n, bool vec, const uint32_t (&v)[kScanItems]) {
+  if (vec && base + kScanItems <= n) {
+    *reinterpret_cast<uint4*>(p + base) = make_uint4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<uint4*>(p + base + 4) = make_uint4(v[4], v[5], v[6], v[7]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i)
+      if (base + i < n) p[base + i] = v[i];
+  }
+}
+
 static __global__ void __launch_bounds__(kScanThreads) k_scan_tiles(const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
-                                                             uint32_t* __restrict__ partials, uint64_t n) {
+                                                             uint32_t* __restrict__ partials, uint64_t n, bool vec) {
   const uint64_t base = uint64_t(blockIdx.x) * kScanTile + threadIdx.x * kScanItems;
   uint32_t v[kScanItems];
+  scan_load8(in, base, n, vec, v);
   uint32_t sum = 0;
 #pragma unroll
-  for (int i = 0; i < kScanItems; ++i) {
-    v[i] = base + i < n ? in[base + i] : 0u;
-    sum += v[i];
-  }
+  for (int i = 0; i < kScanItems; ++i) sum += v[i];
   uint32_t total;
   uint32_t off = block_excl_scan(sum, &total);
 #pragma unroll
   for (int i = 0; i < kScanItems; ++i) {
-    if (base + i < n) out[base + i] = off;
-    off += v[i];
+    const uint32_t x = v[i];
+    v[i] = off;
+    off += x;
   }
+  scan_store8(out, base, n, vec, v);
   if (threadIdx.x == 0) partials[blockIdx.x] = total;
 }
 
@@ -71,12 +92,22 @@ static __global__ void __launch_bounds__(kScanThreads) k_scan_tiles(const uint32
 static __global__ void __launch_bounds__(kScanThreads) k_scan_partials(uint32_t* __restrict__ partials, uint32_t nparts,
                                                                 uint32_t* __restrict__ grand_total) {
   uint32_t running = 0;
-  for (uint32_t base = 0; base < nparts; base += kScanThreads) {
-    const uint32_t i = base + threadIdx.x;
-    const uint32_t v = i < nparts ? partials[i] : 0u;
+  for (uint32_t base = 0; base < nparts; base += kScanTile) {  // 2048 totals per round: 8 consecutive per thread
+    const uint64_t b = base + threadIdx.x * kScanItems;
+    uint32_t v[kScanItems];
+    scan_load8(partials, b, nparts, false, v);
+    uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) sum += v[i];
     uint32_t total;
-    const uint32_t ex = block_excl_scan(v, &total);
-    if (i < nparts) partials[i] = running + ex;
+    uint32_t off = running + block_excl_scan(sum, &total);
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+      const uint32_t x = v[i];
+      v[i] = off;
+      off += x;
+    }
+    scan_store8(partials, b, nparts, false, v);
     running += total;
   }
   if (threadIdx.x == 0 && grand_total) *grand_total = running;
@@ -84,12 +115,15 @@ static __global__ void __launch_bounds__(kScanThreads) k_scan_partials(uint32_t*
 
 // Pass 3: add the tile offset back.
 static __global__ void __launch_bounds__(kScanThreads) k_scan_add(uint32_t* __restrict__ out, const uint32_t* __restrict__ partials,
-                                                           uint64_t n) {
+                                                           uint64_t n, bool vec) {
   const uint32_t off = partials[blockIdx.x];
   const uint64_t base = uint64_t(blockIdx.x) * kScanTile + threadIdx.x * kScanItems;
+  if (base >= n) return;
+  uint32_t v[kScanItems];
+  scan_load8(out, base, n, vec, v);
 #pragma unroll
-  for (int i = 0; i < kScanItems; ++i)
-    if (base + i < n) out[base + i] += off;
+  for (int i = 0; i < kScanItems; ++i) v[i] += off;
+  scan_store8(out, base, n, vec, v);
 }
 
 // Host driver.  `partials` must hold ceil(n / kScanTile) + 1 uint32.  in may alias out.  Returns #kernels launched.
@@ -100,9 +134,10 @@ inline int exclusive_scan_u32(const uint32_t* in, uint32_t* out, uint64_t n, uin
     return 0;
   }
   const uint32_t tiles = uint32_t((n + kScanTile - 1) / kScanTile);
-  k_scan_tiles<<<tiles, kScanThreads, 0, s>>>(in, out, partials, n);
+  const bool vec = (reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) % 16 == 0;
+  k_scan_tiles<<<tiles, kScanThreads, 0, s>>>(in, out, partials, n, vec);
   k_scan_partials<<<1, kScanThreads, 0, s>>>(partials, tiles, d_total);
-  if (tiles > 1) k_scan_add<<<tiles, kScanThreads, 0, s>>>(out, partials, n);
+  if (tiles > 1) k_scan_add<<<tiles, kScanThreads, 0, s>>>(out, partials, n, vec);
   return tiles > 1 ? 3 : 2;
 }
 
