@@ -18,6 +18,7 @@
 #include <cstdint>
 #include <cstring>
 #include <memory>
+#include <optional>
 #include <span>
 #include <stdexcept>
 #include <string>
@@ -151,6 +152,48 @@ public:
   // RefreshArchetypes (query.hpp:1732-1812): matched archetype indices in creation order.
   std::vector<uint32_t> MatchedArchetypes();
   helios_gpu_query* Handle() const noexcept { return q_; }
+
+  // ---- terminals (query.hpp:180,822,1040-1180) as device reductions -----------------------------------------------------
+  // `launch` is a terminal written against helios_gpu_terminals.cuh (reduce_launch<> / partition_launch<>) or a
+  // built-in one (BuiltinTerminal).  The typed wrappers below spell the reference's names over such a launch:
+  //   CountIf -> result.count          Any -> Find has a value      None -> !Any      All -> count == visited
+  //   Find / MinBy / MaxBy -> optional<Entity> of result.entity     Fold -> result.f64 / result.i64
+  struct Terminal {
+    helios_gpu_system_fn launch = nullptr;
+    uint32_t flags = 0;
+  };
+  static Terminal BuiltinTerminal(const char* name) {
+    Terminal t;
+    if (helios_gpu_builtin_terminal(name, &t.launch, &t.flags) != HELIOS_GPU_OK)
+      throw GpuError(HELIOS_GPU_ERR_NOT_FOUND, std::string("no built-in terminal '") + name + "'");
+    return t;
+  }
+  template <typename Params>
+  helios_gpu_terminal_result Run(const Terminal& t, const Params& params);
+  helios_gpu_terminal_result Run(const Terminal& t);
+  template <typename Params>
+  uint64_t CountIf(const Terminal& t, const Params& p) { return Run(t, p).count; }
+  template <typename Params>
+  std::optional<Entity> Find(const Terminal& t, const Params& p) {
+    const auto r = Run(t, p);
+    return r.index == HELIOS_GPU_NO_ROW ? std::nullopt : std::optional<Entity>(Entity::FromBits(r.entity));
+  }
+  template <typename Params>
+  bool Any(const Terminal& find, const Params& p) { return Find(find, p).has_value(); }    // query.hpp:1142-1144
+  template <typename Params>
+  bool None(const Terminal& find, const Params& p) { return !Any(find, p); }                // query.hpp:1166-1168
+  template <typename Params>
+  bool All(const Terminal& count_if, const Params& p) {                                     // vacuously true when empty
+    const auto r = Run(count_if, p);
+    return r.count == r.visited;
+  }
+  std::optional<Entity> ExtremumBy(const Terminal& t) {                                      // MinBy / MaxBy
+    const auto r = Run(t);
+    return r.index == HELIOS_GPU_NO_ROW ? std::nullopt : std::optional<Entity>(Entity::FromBits(r.entity));
+  }
+  // Partition (query.hpp:1086): entities of (matching, rest), both in iteration order; first = Filter + CollectEntities.
+  template <typename Params>
+  std::pair<std::vector<Entity>, std::vector<Entity>> Partition(const Terminal& t, const Params& p);
 private:
   World* world_;
   helios_gpu_query* q_ = nullptr;
@@ -333,6 +376,36 @@ uint64_t Query<Args...>::Count() {
   uint64_t n = 0;
   world_->Check(helios_gpu_query_count(q_, &n));
   return n;
+}
+template <typename... Args>
+template <typename Params>
+helios_gpu_terminal_result Query<Args...>::Run(const Terminal& t, const Params& params) {
+  static_assert(std::is_trivially_copyable_v<Params>, "terminal parameters are copied byte-wise");
+  helios_gpu_terminal_result r{};
+  world_->Check(helios_gpu_query_terminal(q_, t.launch, &params, uint32_t(sizeof(Params)), t.flags, &r));
+  return r;
+}
+template <typename... Args>
+helios_gpu_terminal_result Query<Args...>::Run(const Terminal& t) {
+  helios_gpu_terminal_result r{};
+  world_->Check(helios_gpu_query_terminal(q_, t.launch, nullptr, 0, t.flags, &r));
+  return r;
+}
+template <typename... Args>
+template <typename Params>
+std::pair<std::vector<Entity>, std::vector<Entity>> Query<Args...>::Partition(const Terminal& t, const Params& p) {
+  const auto r = Run(t, p);
+  std::pair<std::vector<Entity>, std::vector<Entity>> out;
+  auto fetch = [&](uint32_t group, uint64_t n, std::vector<Entity>& dst) {
+    std::vector<helios_gpu_entity_t> raw(n);
+    uint64_t got = 0;
+    world_->Check(helios_gpu_query_terminal_entities(q_, group, raw.data(), n, &got));
+    dst.reserve(n);
+    for (const auto bits : raw) dst.push_back(Entity::FromBits(bits));
+  };
+  fetch(0, r.count, out.first);
+  fetch(1, r.visited - r.count, out.second);
+  return out;
 }
 template <typename... Args>
 std::vector<uint32_t> Query<Args...>::MatchedArchetypes() {

@@ -159,6 +159,27 @@ int main(int argc, char** argv) {
     try { schedule.Build(); } catch (const ecs::GpuError& e) { cycle = e.Status() == HELIOS_GPU_ERR_CYCLE; }
     CHECK(cycle);
   }
+  // ---- query terminals (tests/query/query.cpp:453-731): Find / Any / All / None / CountIf / MaxBy / MinBy / Partition ----
+  {
+    ecs::World world;
+    world.RegisterComponent<Position>();
+    const float xs[] = {5.0f, 15.0f, 25.0f, 25.0f, -1.0f};
+    std::vector<Position> pos;
+    for (float x : xs) pos.push_back(Position{x, 0});
+    const auto ents = world.SpawnBatch<Position>(pos.size(), std::span<const Position>(pos));
+    using PQ = ecs::Query<const Position&>;
+    PQ q(world);
+    const auto count_if = PQ::BuiltinTerminal("count_if_pos_x_gt"), find = PQ::BuiltinTerminal("find_pos_x_gt");
+    CHECK(q.CountIf(count_if, 10.0f) == 3 && q.CountIf(count_if, 100.0f) == 0);
+    CHECK(q.Find(find, 10.0f) == ents[1] && !q.Find(find, 100.0f).has_value());       // the FIRST match
+    CHECK(q.Any(find, 20.0f) && q.None(find, 100.0f) && q.All(count_if, -2.0f) && !q.All(count_if, 0.0f));
+    CHECK(q.ExtremumBy(PQ::BuiltinTerminal("max_by_pos_x")) == ents[2]);              // first of the two 25s
+    CHECK(q.ExtremumBy(PQ::BuiltinTerminal("min_by_pos_x")) == ents[4]);
+    const auto parts = q.Partition(PQ::BuiltinTerminal("partition_pos_x_gt"), 10.0f);
+    CHECK((parts.first == std::vector<ecs::Entity>{ents[1], ents[2], ents[3]}));
+    CHECK((parts.second == std::vector<ecs::Entity>{ents[0], ents[4]}));
+    CHECK(q.Run(PQ::BuiltinTerminal("fold_sum_pos_x")).f64 == 69.0);
+  }
   std::printf("shim_test gpu: %d checks, %d failed\n", g_checks, g_fail);
   return g_fail;
 }
