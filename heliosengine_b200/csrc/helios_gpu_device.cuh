@@ -184,6 +184,61 @@ __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<
   }
 }
 
+// Two FULL tiles of one table at once (narrow rows): the loads of both tiles are in flight before either body runs, which
+// doubles the bytes a thread keeps outstanding — a one-tile walk of 8-byte rows is bound by memory latency, not bandwidth.
+template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
+__device__ __forceinline__ void process_full_tile_pair(const TileRef& t, uint32_t row0_a, uint32_t row0_b,
+                                                       cuda::std::tuple<Cs*...> cols, Body& body) {
+  using namespace detail;
+  constexpr int N = sizeof...(Cs);
+  cuda::std::tuple<CompRegs<Cs>...> regs[2];
+  helios_gpu_entity_t ents[2][kPairs][2];
+  const uint32_t row0[2] = {row0_a, row0_b};
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
+      (([&] {
+#pragma unroll
+         for (int k = 0; k < kPairs; ++k)
+           load_pair(cuda::std::get<Is>(regs[h]).p[k], cuda::std::get<Is>(cols) + row0[h] + k * 2 * kBlock + 2 * threadIdx.x);
+       }()),
+       ...);
+    }(cuda::std::make_index_sequence<N>{});
+    if constexpr (kWithEntity) {
+#pragma unroll
+      for (int k = 0; k < kPairs; ++k) {
+        const uint4 e = __ldcs(reinterpret_cast<const uint4*>(t.entities + row0[h] + k * 2 * kBlock + 2 * threadIdx.x));
+        ents[h][k][0] = uint64_t(e.x) | (uint64_t(e.y) << 32);
+        ents[h][k][1] = uint64_t(e.z) | (uint64_t(e.w) << 32);
+      }
+    }
+  }
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+#pragma unroll
+    for (int k = 0; k < kPairs; ++k) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const uint32_t r = row0[h] + k * 2 * kBlock + 2 * threadIdx.x + j;
+        const Row rc{t.row_begin + r, t.n_rows, kWithEntity ? ents[h][k][j] : HELIOS_GPU_INVALID_ENTITY, t.archetype, r};
+        [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
+          body(rc, cuda::std::get<Is>(regs[h]).p[k].v[j]...);
+        }(cuda::std::make_index_sequence<N>{});
+      }
+    }
+    [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
+      (([&] {
+         if constexpr ((kWriteMask >> Is) & 1u) {
+#pragma unroll
+           for (int k = 0; k < kPairs; ++k)
+             store_pair(cuda::std::get<Is>(regs[h]).p[k], cuda::std::get<Is>(cols) + row0[h] + k * 2 * kBlock + 2 * threadIdx.x);
+         }
+       }()),
+       ...);
+    }(cuda::std::make_index_sequence<N>{});
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------
 // for_each_kernel (fused match): every CTA evaluates the archetype-mask match itself from the device table
 // directory (query.hpp:1732-1812 semantics: creation order, empty tables skipped, With ∪ data ⊆ id, Without ∩ id = ∅)
@@ -194,7 +249,9 @@ constexpr int kFusedMaxTables = 1024;
 // Narrow rows (<= 16 B per row over all data components) keep few bytes in flight per thread: ask for all 8 CTAs per SM
 // (<= 32 registers) so that the loads of enough threads overlap; wider queries have the memory parallelism already.
 template <bool kWithEntity, typename... Cs>
-constexpr int kForEachMinBlocks = ((0 + ... + int(sizeof(Cs))) + (kWithEntity ? 8 : 0) <= 16) ? 8 : 1;
+constexpr bool kNarrowRows = (0 + ... + int(sizeof(Cs))) + (kWithEntity ? 8 : 0) <= 16;
+template <bool kWithEntity, typename... Cs>
+constexpr int kForEachMinBlocks = !kNarrowRows<kWithEntity, Cs...> ? 1 : (kWithEntity ? 4 : 8);
 
 template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
 __global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity, Cs...>) for_each_kernel(const helios_gpu_match_args m, Body body) {
@@ -251,28 +308,57 @@ __global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity, Cs...>)
   if (threadIdx.x == 0) s_tile_begin[n_seg] = n_tiles;
   __syncthreads();
 
-  for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    // upper_bound(tile) - 1 over s_tile_begin[0..n_seg]
+  auto segment_of = [&](uint32_t tile) {  // upper_bound(tile) - 1 over s_tile_begin[0..n_seg]
     uint32_t lo = 0, hi = n_seg;
     while (hi - lo > 1) {
       const uint32_t mid = (lo + hi) >> 1;
       if (s_tile_begin[mid] <= tile) lo = mid; else hi = mid;
     }
-    const uint32_t t = s_table[lo];
-    TileRef tr;
+    return lo;
+  };
+  TileRef tr;
+  tr.n_rows = n_rows;
+  void* bases[N];
+  auto open_segment = [&](uint32_t seg) {  // table metadata: three dependent global loads, paid once per segment
+    const uint32_t t = s_table[seg];
     tr.archetype = t;
     tr.rows = __ldg(&m.table_rows[t]);
-    tr.row0 = (tile - s_tile_begin[lo]) * kTileRows;
-    tr.row_begin = s_row_begin[lo];
-    tr.n_rows = n_rows;
+    tr.row_begin = s_row_begin[seg];
     tr.entities = kWithEntity ? reinterpret_cast<const helios_gpu_entity_t*>(__ldg(reinterpret_cast<const unsigned long long*>(&m.table_entities[t]))) : nullptr;
     void* const* dir = m.table_columns + size_t(t) * HELIOS_GPU_MAX_COMPONENTS;
-    void* bases[N];
 #pragma unroll
     for (int k = 0; k < N; ++k)
       bases[k] = reinterpret_cast<void*>(__ldg(reinterpret_cast<const unsigned long long*>(&dir[m.slots[k]])));
-    const auto cols = detail::typed_columns<Cs...>(bases, cuda::std::make_index_sequence<N>{});
-    process_tile<kWriteMask, kWithEntity, Body, Cs...>(tr, cols, body);
+  };
+  if constexpr (kNarrowRows<kWithEntity, Cs...>) {
+    // Narrow rows: a tile is only a few KB, so the metadata chain above would dominate a tile-strided walk.  Each CTA
+    // takes a CONTIGUOUS run of tiles instead: consecutive tiles share their table, the chain is paid once per table.
+    const uint32_t per = (n_tiles + gridDim.x - 1) / gridDim.x;
+    const uint32_t first = blockIdx.x * per, last = first + per < n_tiles ? first + per : n_tiles;
+    if (first < last) {
+      uint32_t seg = segment_of(first);
+      open_segment(seg);
+      for (uint32_t tile = first; tile < last; ++tile) {
+        if (tile >= s_tile_begin[seg + 1]) open_segment(++seg);  // matched tables are never empty: every segment has tiles
+        tr.row0 = (tile - s_tile_begin[seg]) * kTileRows;
+        const auto cols = detail::typed_columns<Cs...>(bases, cuda::std::make_index_sequence<N>{});
+        // two full tiles of the same table: both sets of loads go out before the bodies run
+        if (tile + 1 < last && tile + 1 < s_tile_begin[seg + 1] && tr.row0 + 2 * kTileRows <= tr.rows) {
+          process_full_tile_pair<kWriteMask, kWithEntity, Body, Cs...>(tr, tr.row0, tr.row0 + kTileRows, cols, body);
+          ++tile;
+        } else {
+          process_tile<kWriteMask, kWithEntity, Body, Cs...>(tr, cols, body);
+        }
+      }
+    }
+  } else {
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      const uint32_t seg = segment_of(tile);
+      open_segment(seg);
+      tr.row0 = (tile - s_tile_begin[seg]) * kTileRows;
+      const auto cols = detail::typed_columns<Cs...>(bases, cuda::std::make_index_sequence<N>{});
+      process_tile<kWriteMask, kWithEntity, Body, Cs...>(tr, cols, body);
+    }
   }
   // Optional per-thread epilogue: a body that accumulates into its own members (each thread holds a private copy)
   // folds them here once — e.g. one warp-reduced atomic per warp instead of one per row.
