@@ -268,6 +268,11 @@ class World:
         self._check(self.b.fn("archetype_column_write")(self.h, C.c_uint32(archetype), C.c_uint64(fnv1a(name)),
                                                         C.c_uint64(row0), C.c_uint64(rows), C.c_void_p(src_ptr)))
 
+    def column_write_on(self, stream_ptr: int, archetype: int, name: str, row0: int, rows: int, src_ptr: int):
+        self._check(self.b.fn("archetype_column_write_on")(self.h, C.c_uint32(archetype), C.c_uint64(fnv1a(name)),
+                                                           C.c_uint64(row0), C.c_uint64(rows), C.c_void_p(src_ptr),
+                                                           C.c_void_p(stream_ptr)))
+
     def column_read(self, archetype: int, name: str, row0: int, rows: int, dst_ptr: int):
         self._check(self.b.fn("archetype_column_read")(self.h, C.c_uint32(archetype), C.c_uint64(fnv1a(name)),
                                                        C.c_uint64(row0), C.c_uint64(rows), C.c_void_p(dst_ptr)))

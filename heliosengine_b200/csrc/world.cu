@@ -431,6 +431,16 @@ int32_t helios_gpu_archetype_column_write(helios_gpu_world* w, uint32_t a, uint6
   return HELIOS_GPU_OK;
 }
 
+int32_t helios_gpu_archetype_column_write_on(helios_gpu_world* w, uint32_t a, uint64_t hash, uint64_t row0, uint64_t rows,
+                                             const void* src, void* stream) {
+  uint8_t* p;
+  size_t bytes;
+  HG_TRY(column_range(w, a, hash, row0, rows, &p, &bytes));
+  ++w->mutation_epoch;
+  if (bytes) HG_CUDA(w, cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+  return HELIOS_GPU_OK;
+}
+
 int32_t helios_gpu_archetype_column_read(helios_gpu_world* w, uint32_t a, uint64_t hash, uint64_t row0, uint64_t rows,
                                          void* dst) {
   uint8_t* p;

@@ -107,6 +107,11 @@ HELIOS_GPU_API int32_t helios_gpu_snapshot_entity_table(helios_gpu_world* w, uin
  * (component/archetype.hpp:578-602) is the reference's closest interface. */
 HELIOS_GPU_API int32_t helios_gpu_archetype_column_write(helios_gpu_world* w, uint32_t archetype, uint64_t type_hash,
                                                          uint64_t row0, uint64_t rows, const void* src);
+/* The same upload on a stream of the CALLER's (a copy stream), so that next frame's inputs travel while this frame's
+ * results are still being read back; ordering against the world's stream is the caller's (events), as with any CUDA
+ * copy stream: the upload must follow the last kernel that reads the column and precede the next one. */
+HELIOS_GPU_API int32_t helios_gpu_archetype_column_write_on(helios_gpu_world* w, uint32_t archetype, uint64_t type_hash,
+                                                            uint64_t row0, uint64_t rows, const void* src, void* stream);
 /* Asynchronous counterpart of snapshot_archetype_column for a row range (no stream synchronisation). */
 HELIOS_GPU_API int32_t helios_gpu_archetype_column_read(helios_gpu_world* w, uint32_t archetype, uint64_t type_hash,
                                                         uint64_t row0, uint64_t rows, void* dst);
