@@ -26,6 +26,9 @@ sys.path.insert(0, ROOT)
 METRIC = "entity_component_updates_per_sec"
 UNIT = "updates/s"
 N_ENTITIES = 1 << 24
+DEFAULT_ENTITIES = N_ENTITIES
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch of the default workload (ncu --set full, see traffic_source)
+NCU_TRAFFIC_DEFAULT = 117461760 + 21580800
 WORKLOAD = ("cfg2: 16777216 entities / 64 archetypes, 4-component Query with With<Health> Without<Frozen> "
             "(16 tables, 4194304 rows), accel-integrate body")
 
@@ -306,7 +309,11 @@ def run_b200(args):
                        "l2": "flushed between timed steps: 256 MiB written, then 256 MiB read (L2 left holding clean lines)", "exec_mode": "serial stream",
                        "fma": "off (-fmad=false), bit-exact vs oracle"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_kind": peak_kind, "algorithmic_bytes_per_launch": bytes_per_step,
+                         "traffic": NCU_TRAFFIC_DEFAULT if (args.entities == DEFAULT_ENTITIES and not args.all_tables) else None,
+                         "traffic_source": "profiles/r01_foreach_accel_full.md (ncu --set full, one launch of this workload): "
+                                           "117.46 MB read + 21.58 MB written inside the kernel; the other 45.5 MB of written "
+                                           "lines are still dirty in L2 when it ends",
+                         "peak_kind": peak_kind, "algorithmic_bytes_per_launch": bytes_per_step,
                          "kernel": "helios_gpu::for_each_kernel<AccelBody,...>"},
             "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": matched * 8, "d2h_bytes_per_step": matched * 8,
