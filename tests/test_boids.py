@@ -175,3 +175,40 @@ def test_gpu_full_density_properties(gpu):
     assert a[0].min() >= 0 and a[0].max() < ws
     v = a[1].reshape(-1, 2).astype(np.float64)
     assert np.sqrt((v * v).sum(axis=1)).max() <= 2.0 * (1 + 1e-6)
+
+
+def _nccl_peer_worker(rank, world_size, port, n, ws, steps, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world_size, device_id=dev)
+    g = capi.load_gpu()
+    shard = boids.BoidsShard(g, n, ws, world_size, rank, device=rank)
+    stream = torch.cuda.Stream(device=dev)
+    shard.world.set_stream(stream.cuda_stream)
+    with torch.cuda.stream(stream):
+        peer = boids.PeerExchange(shard, torch, dist, dev)
+        for _ in range(steps):
+            peer.step()
+        p, v = shard.state()
+        np.save(os.path.join(out_dir, f"p{rank}.npy"), p)
+        np.save(os.path.join(out_dir, f"v{rank}.npy"), v)
+        peer.close()
+    shard.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (CUDA IPC + NVLink peer access between processes)")
+def test_two_gpus_peer_memory_exchange_matches_oracle(oracle, tmp_path):
+    """One process per GPU: IPC-exported buffers, merge kernels pulling the other GPU's slab over NVLink, NCCL barrier."""
+    import torch.multiprocessing as mp
+    n, ws, steps = 262144, 256, 4
+    port = 29600 + os.getpid() % 2000
+    mp.spawn(_nccl_peer_worker, args=(2, port, n, ws, steps, str(tmp_path)), nprocs=2, join=True)
+    ref = run_local(oracle, n, ws, steps)
+    p = np.concatenate([np.load(tmp_path / f"p{r}.npy") for r in range(2)])
+    v = np.concatenate([np.load(tmp_path / f"v{r}.npy") for r in range(2)])
+    assert np.array_equal(ref[0], p) and np.array_equal(ref[1], v)
