@@ -30,6 +30,7 @@ EXEC_SERIAL, EXEC_STREAMS, EXEC_GRAPH = 0, 1, 2
 MSG_AUTOMATIC, MSG_MANUAL = 0, 1
 SYSTEM_EMITS_COMMANDS = 1
 SYSTEM_NEEDS_VIEW = 2
+SYSTEM_CONSUMES_MESSAGES = 4
 
 INVALID_ENTITY = 0xFFFFFFFFFFFFFFFF
 

@@ -157,6 +157,42 @@ int32_t launch_consume(const helios_gpu_system_ctx* ctx) {
   return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
 }
 
+// ---- "consume_strong": ConsumableMessageReader<CollisionEvent>::ConsumeIf(impulse > t) (message/reader.hpp:1035-1058):
+// events above the threshold damage Health of evt.a and are marked consumed (removed from both queues when this system's
+// local data is merged); weaker events are left for later readers.
+struct ConsumeStrongParams { uint32_t health_slot; float threshold; };
+__global__ void __launch_bounds__(256) k_consume_strong(const helios_gpu_msg_reader* d_rd, helios_gpu_world_view wv,
+                                                        ConsumeStrongParams p, uint32_t* consumed, uint64_t consumed_capacity) {
+  const helios_gpu_msg_reader rd = *d_rd;
+  const unsigned long long np = *rd.previous_count, nc = *rd.current_count;
+  const unsigned long long n = np + nc;
+  for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+       i += (unsigned long long)gridDim.x * blockDim.x) {
+    const CollisionEvent* src = i < np ? reinterpret_cast<const CollisionEvent*>(rd.previous) + i
+                                       : reinterpret_cast<const CollisionEvent*>(rd.current) + (i - np);
+    const uint4 lo = __ldcs(reinterpret_cast<const uint4*>(src));
+    const uint2 hi = __ldcs(reinterpret_cast<const uint2*>(src) + 2);
+    const float impulse = __uint_as_float(hi.x);
+    if (!(impulse > p.threshold)) continue;
+    helios_gpu::message_mark_consumed(consumed, consumed_capacity, i);
+    const uint32_t idx = lo.x, gen = lo.y;
+    if (idx >= wv.entity_capacity || wv.entity_generation[idx] != gen) continue;
+    const uint64_t loc = wv.entity_location[idx];
+    if (loc == 0xFFFFFFFFFFFFFFFFull) continue;
+    int32_t* col = static_cast<int32_t*>(wv.table_columns[(loc >> 32) * 64 + p.health_slot]);
+    if (col) atomicSub(col + uint32_t(loc), int32_t(impulse));
+  }
+}
+int32_t launch_consume_strong(const helios_gpu_system_ctx* ctx) {
+  if (ctx->params_size < sizeof(ConsumeStrongParams) || !ctx->d_reader) return HELIOS_GPU_ERR_STATE;
+  ConsumeStrongParams p;
+  std::memcpy(&p, ctx->params, sizeof(p));
+  k_consume_strong<<<ctx->sm_count * 8, 256, 0, static_cast<cudaStream_t>(ctx->stream)>>>(ctx->d_reader, ctx->world_view, p,
+                                                                                        ctx->consumed, ctx->consumed_capacity);
+  helios_gpu_world_note_launches(ctx->world, 1);
+  return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
+}
+
 // ---- "stats": Query<const Health&> → resource[0] (u64) += Σ hp  (integer, order independent) -----------------
 struct StatsBody {
   unsigned long long* acc;
@@ -218,6 +254,7 @@ const Entry kBuiltins[] = {
     {"damp", launch_damp},             {"regen", launch_regen},
     {"team_tint", launch_team_tint},   {"detect", launch_detect},
     {"detect_sparse", launch_detect_sparse}, {"consume", launch_consume},
+    {"consume_strong", launch_consume_strong},
     {"stats", launch_stats},           {"exit_check", launch_exit_check},
     {"despawn_dead", launch_despawn_dead},
 };

@@ -443,4 +443,10 @@ __device__ __forceinline__ void message_append(const helios_gpu_msg_writer& wr, 
   if (slot < wr.capacity) reinterpret_cast<Msg*>(wr.data)[slot] = m;
 }
 
+// ConsumableMessageWrapper::Consume / ConsumableMessageReader::ConsumeIf (message/reader.hpp:850-1058): mark the message
+// at `global_index` of the reader view (previous ++ current) consumed.  Idempotent; no ordering between markers.
+__device__ __forceinline__ void message_mark_consumed(uint32_t* consumed, uint64_t capacity, uint64_t global_index) {
+  if (consumed && global_index < capacity) consumed[global_index] = 1u;
+}
+
 }  // namespace helios_gpu

@@ -5,6 +5,7 @@
 // is empty, and a single D2D append otherwise — never a per-message operation.
 #include <algorithm>
 
+#include "primitives.cuh"
 #include "world_internal.hpp"
 
 using namespace hgpu;
@@ -64,6 +65,73 @@ static int32_t merge_current_into_previous(helios_gpu_world* w, MsgChannel* ch) 
   ch->prev_count += ch->cur_count;
   ch->cur_count = 0;
   return HELIOS_GPU_OK;
+}
+
+// ---- ApplyConsumed (manager.hpp:421-496 -> queue.hpp:331-360 RemoveIndices) ------------------------------------------------
+// The reference erases the consumed index ranges of both queues back to front; the survivors keep their order.  Here:
+// keep[i] = !flags[i] over previous ++ current -> exclusive scan -> every surviving message is copied word by word to
+// its new position in a fresh buffer (previous and current compact independently: the current queue's positions are
+// offset by the number of previous survivors), then the buffers are swapped in.
+namespace {
+
+__global__ void k_consumed_keep(const uint32_t* __restrict__ flags, uint64_t n_flags, uint64_t n, uint32_t* __restrict__ keep) {
+  const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+  if (i < n) keep[i] = (i < n_flags && flags[i]) ? 0u : 1u;
+}
+
+// One thread per (message, 4-byte word).  survivors[0] = previous survivors, survivors[1] = all survivors.
+__global__ void k_consumed_compact(const uint32_t* __restrict__ keep, const uint32_t* __restrict__ pos, uint64_t n_prev, uint64_t n,
+                                   uint32_t words, const uint32_t* __restrict__ prev, const uint32_t* __restrict__ cur,
+                                   uint32_t* __restrict__ prev_out, uint32_t* __restrict__ cur_out, const uint32_t* __restrict__ total,
+                                   uint32_t* __restrict__ survivors) {
+  const uint64_t t = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+  const uint32_t kept_prev = n_prev < n ? pos[n_prev] : *total;  // exclusive prefix at the first current message
+  if (t == 0) {
+    survivors[0] = kept_prev;
+    survivors[1] = *total;
+  }
+  const uint64_t i = t / words;
+  const uint32_t wd = uint32_t(t - i * words);
+  if (i >= n || !keep[i]) return;
+  const uint32_t p = pos[i];
+  if (i < n_prev) prev_out[uint64_t(p) * words + wd] = prev[i * words + wd];
+  else cur_out[uint64_t(p - kept_prev) * words + wd] = cur[(i - n_prev) * words + wd];
+}
+
+}  // namespace
+
+int32_t channel_apply_consumed(helios_gpu_world* w, MsgChannel* ch, const uint32_t* d_flags, uint64_t n_flags) {
+  if (!ch || !d_flags || n_flags == 0) return HELIOS_GPU_OK;
+  const uint64_t P = ch->prev_count, C = ch->cur_count, n = P + C;
+  if (n == 0) return HELIOS_GPU_OK;
+  if (n >= 0xFFFFFFFFull || ch->size % 4) HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "consumable messages: unsupported channel shape");
+  cudaStream_t st = w->stream;
+  const uint32_t words = ch->size / 4;
+  HG_CUDA(w, ch->keep.reserve(n * 8, 0, st, false));  // keep[n] ++ pos[n]
+  HG_CUDA(w, ch->scan_partials.reserve((n / prim::kScanTile + 2) * 4, 0, st, false));
+  HG_CUDA(w, ch->survivors.reserve(16, 0, st, false));
+  HG_CUDA(w, ch->prev_alt.reserve(std::max<uint64_t>(P, 1) * ch->size, 0, st, false));
+  HG_CUDA(w, ch->cur_alt.reserve(std::max<uint64_t>(C, 1) * ch->size, 0, st, false));
+  uint32_t* keep = ch->keep.as<uint32_t>();
+  uint32_t* pos = keep + n;
+  uint32_t* surv = ch->survivors.as<uint32_t>();
+  k_consumed_keep<<<uint32_t((n + 255) / 256), 256, 0, st>>>(d_flags, n_flags, n, keep);
+  w->launches += 1 + prim::exclusive_scan_u32(keep, pos, n, ch->scan_partials.as<uint32_t>(), surv + 2, st);
+  const uint64_t threads = n * words;
+  k_consumed_compact<<<uint32_t((threads + 255) / 256), 256, 0, st>>>(keep, pos, P, n, words, ch->prev.as<uint32_t>(),
+                                                                     ch->cur.as<uint32_t>(), ch->prev_alt.as<uint32_t>(),
+                                                                     ch->cur_alt.as<uint32_t>(), surv + 2, surv);
+  ++w->launches;
+  uint32_t h[2] = {0, 0};
+  HG_CUDA(w, cudaMemcpyAsync(h, surv, 8, cudaMemcpyDeviceToHost, st));
+  HG_CUDA(w, cudaStreamSynchronize(st));
+  if (h[1] == n) return HELIOS_GPU_OK;  // nothing was consumed: the queues stay as they are
+  std::swap(ch->prev, ch->prev_alt);
+  std::swap(ch->cur, ch->cur_alt);
+  ch->prev_count = h[0];
+  ch->cur_count = h[1] - h[0];
+  ++w->epoch;  // buffer addresses changed under any captured graph
+  return publish_channel(w, ch);
 }
 
 int32_t messages_update_from_system(helios_gpu_world* w) {

@@ -46,6 +46,9 @@ struct SysEntry {
   DevBuf msg_data;                 // local message buffer
   uint64_t msg_capacity = 0;
   DevBuf d_writer;                 // struct { helios_gpu_msg_writer wr; unsigned long long count; }
+  DevBuf consumed;                 // u32 flag per global reader index (ConsumedMessagesRegistry of this system)
+  uint64_t consumed_capacity = 0;  // flags allocated
+  uint64_t consumed_armed = 0;     // flags zeroed for the current run = reader view size at launch
   int stream_id = 0;
 };
 
@@ -143,6 +146,18 @@ int32_t prepare(helios_gpu_schedule* s) {
     }
     if (e.desc.reads_message && !find_channel(w, e.desc.reads_message))
       HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "system '%s' reads an unregistered message type", e.name.c_str());
+    if ((e.desc.flags & HELIOS_GPU_SYSTEM_CONSUMES_MESSAGES) && e.desc.reads_message) {
+      const MsgChannel* ch = find_channel(w, e.desc.reads_message);
+      const uint64_t view = ch->prev_count + ch->cur_count;  // merges only happen in ApplyDeferred: exact for this run
+      if (view > e.consumed_capacity || !e.consumed.ptr) {
+        const uint64_t cap = view + view / 2 + 1024;
+        HG_CUDA(w, e.consumed.reserve(cap * 4, 0, w->stream, false));
+        e.consumed_capacity = cap;
+        ++w->epoch;
+      }
+      if (view != e.consumed_armed) ++w->epoch;  // memset extent is baked into a captured graph
+      e.consumed_armed = view;
+    }
   }
   return HELIOS_GPU_OK;
 }
@@ -174,6 +189,11 @@ int32_t launch_system(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaS
   ctx.params_size = uint32_t(e.params.size());
   ctx.resources = s->resources.ptr;
   ctx.host_user = e.desc.host_user;
+  if ((e.desc.flags & HELIOS_GPU_SYSTEM_CONSUMES_MESSAGES) && e.consumed.ptr) {
+    if (e.consumed_armed) HG_CUDA(w, cudaMemsetAsync(e.consumed.ptr, 0, e.consumed_armed * 4, stream));
+    ctx.consumed = e.consumed.as<uint32_t>();
+    ctx.consumed_capacity = e.consumed_armed;
+  }
   if (e.desc.flags & HELIOS_GPU_SYSTEM_EMITS_COMMANDS) {
     if (e.cmd_slots_in_use)  // all-ones = kind NONE in every slot
       HG_CUDA(w, cudaMemsetAsync(e.cmd_records.ptr, 0xFF, e.cmd_slots_in_use * sizeof(helios_gpu_command), stream));
@@ -449,7 +469,9 @@ int32_t helios_gpu_schedule_apply_deferred(helios_gpu_schedule* s) {
     if ((e.desc.flags & HELIOS_GPU_SYSTEM_EMITS_COMMANDS) && e.cmd_slots_in_use && s->pending)
       HG_TRY(apply_queue(w, e.cmd_records.as<helios_gpu_command>(), e.cmd_payload.as<uint8_t>(), e.cmd_slots_in_use,
                          /*dense=*/0));
-    // SystemLocalData::MergeMessages (system_local_data.hpp:122-132)
+    // SystemLocalData::MergeMessages (system_local_data.hpp:122-132): Update(consumed) = ApplyConsumed, then merge
+    if ((e.desc.flags & HELIOS_GPU_SYSTEM_CONSUMES_MESSAGES) && e.consumed_armed && s->pending)
+      HG_TRY(channel_apply_consumed(w, find_channel(w, e.desc.reads_message), e.consumed.as<uint32_t>(), e.consumed_armed));
     HG_TRY(messages_update_from_system(w));
     if (e.desc.writes_message && s->pending) {
       MsgChannel* ch = find_channel(w, e.desc.writes_message);

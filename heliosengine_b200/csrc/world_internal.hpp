@@ -40,6 +40,7 @@ struct MsgChannel {           // one registered message type: double buffer (mes
   uint32_t size = 0;
   uint32_t policy = 0;
   DevBuf cur, prev;
+  DevBuf cur_alt, prev_alt, keep, scan_partials, survivors;  // ApplyConsumed scratch: compaction targets, flags/positions
   uint64_t cur_count = 0, prev_count = 0;   // host mirrors
   DevBuf d_dev;                              // ChannelDev: reader view + {prev, cur} counters for device readers
 };
@@ -147,5 +148,7 @@ MsgChannel* find_channel(helios_gpu_world* w, uint64_t hash);
 int32_t channel_append_device(helios_gpu_world* w, MsgChannel* ch, const void* d_src, uint64_t n);
 // Merge a system-local buffer into world current; adopts the buffer (pointer swap) when current is empty.
 int32_t channel_merge_local(helios_gpu_world* w, MsgChannel* ch, DevBuf& local, uint64_t n);
+// MessageManager::ApplyConsumed (manager.hpp:421-496): flags[i] != 0 removes position i of previous ++ current.
+int32_t channel_apply_consumed(helios_gpu_world* w, MsgChannel* ch, const uint32_t* d_flags, uint64_t n_flags);
 int32_t publish_channel(helios_gpu_world* w, MsgChannel* ch);
 }  // namespace hgpu

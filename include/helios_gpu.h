@@ -295,6 +295,11 @@ typedef struct helios_gpu_system_ctx {
   void* scratch;
   uint64_t scratch_bytes;
   uint64_t query_rows;
+  /* consumable messages (HELIOS_GPU_SYSTEM_CONSUMES_MESSAGES): one u32 flag per GLOBAL index of the reader view
+   * (previous ++ current), zero at launch; a body marks message i consumed by storing 1 at consumed[i]
+   * (ConsumedMessagesRegistry::MarkConsumed, message/consumed_registry.hpp:288-296) */
+  uint32_t* consumed;
+  uint64_t consumed_capacity;
 } helios_gpu_system_ctx;
 #define HELIOS_GPU_RESOURCE_BYTES 4096u
 
@@ -304,6 +309,10 @@ typedef int32_t (*helios_gpu_system_fn)(const helios_gpu_system_ctx* ctx);
 
 #define HELIOS_GPU_SYSTEM_EMITS_COMMANDS 1u
 #define HELIOS_GPU_SYSTEM_NEEDS_VIEW 2u /* run the stand-alone match kernel first and pass ctx->view */
+/* The system consumes messages of its reads_message type (ConsumableMessageReader, message/reader.hpp:850-1058): the
+ * marked messages are removed from both queues when the system's local data is merged (MessageManager::Update(consumed)
+ * -> ApplyConsumed, message/manager.hpp:376-398,421-496), survivors keep their order. */
+#define HELIOS_GPU_SYSTEM_CONSUMES_MESSAGES 4u
 #define HELIOS_GPU_FUSED_MATCH_MAX_TABLES 1024u
 typedef struct helios_gpu_system_desc {
   const char* name;

@@ -711,6 +711,26 @@ public:
     }
     other.buf_.clear();
   }
+  // queue.hpp:331-360 RemoveIndices: sorted unique indices, contiguous ranges erased from back to front (order of the
+  // survivors is kept).  Indices past the end — an assert in the reference — are ignored on both sides.
+  void RemoveIndices(TypeIndex t, const std::vector<size_t>& sorted_indices) {
+    const auto it = buf_.find(t);
+    if (it == buf_.end() || sorted_indices.empty() || it->second.bytes.empty()) return;
+    Buf& b = it->second;
+    const size_t count = b.bytes.size() / b.size;
+    size_t idx = sorted_indices.size();
+    while (idx > 0) {
+      --idx;
+      size_t range_end = sorted_indices[idx] + 1, range_start = sorted_indices[idx];
+      while (idx > 0 && sorted_indices[idx - 1] == range_start - 1) {
+        --idx;
+        range_start = sorted_indices[idx];
+      }
+      if (range_start >= count) continue;
+      range_end = std::min(range_end, count);
+      b.bytes.erase(b.bytes.begin() + ptrdiff_t(range_start * b.size), b.bytes.begin() + ptrdiff_t(range_end * b.size));
+    }
+  }
   void Clear(TypeIndex t) {
     if (auto it = buf_.find(t); it != buf_.end()) it->second.bytes.clear();
   }
@@ -739,6 +759,27 @@ private:
   std::map<TypeIndex, Buf> buf_;
 };
 
+// message/consumed_registry.hpp:41-296 — per-system record of consumed GLOBAL indices (previous ++ current view), kept
+// sorted and unique per type (MarkConsumed :288-296).
+class ConsumedRegistry {
+public:
+  void MarkConsumed(TypeIndex t, size_t global_index) {
+    auto& v = consumed_[t];
+    const auto pos = std::lower_bound(v.begin(), v.end(), global_index);
+    if (pos == v.end() || *pos != global_index) v.insert(pos, global_index);
+  }
+  bool Empty() const {
+    for (const auto& [t, v] : consumed_)
+      if (!v.empty()) return false;
+    return true;
+  }
+  void Clear() { consumed_.clear(); }
+  const std::map<TypeIndex, std::vector<size_t>>& Data() const { return consumed_; }
+
+private:
+  std::map<TypeIndex, std::vector<size_t>> consumed_;
+};
+
 class MessageManager {
 public:
   // manager.hpp:498-530 Register
@@ -757,6 +798,28 @@ public:
   void UpdateFromSystem() {
     previous_.Merge(current_);
     for (const auto& [t, m] : registered_) current_.Register(t, m.size);
+  }
+  // manager.hpp:421-496 ApplyConsumed: global indices [0, P) hit the previous queue, [P, P + C) the current one
+  // (offset by P); no buffer swap.
+  void ApplyConsumed(const ConsumedRegistry& consumed) {
+    for (const auto& [t, indices] : consumed.Data()) {
+      if (indices.empty() || !registered_.count(t)) continue;
+      const size_t prev_count = previous_.Count(t), curr_count = current_.Count(t);
+      if (prev_count == 0 && curr_count == 0) continue;
+      const auto part = std::lower_bound(indices.begin(), indices.end(), prev_count);
+      if (part != indices.begin()) previous_.RemoveIndices(t, std::vector<size_t>(indices.begin(), part));
+      if (part != indices.end()) {
+        std::vector<size_t> off;
+        for (auto it = part; it != indices.end(); ++it) off.push_back(*it - prev_count);
+        current_.RemoveIndices(t, off);
+      }
+    }
+  }
+  // manager.hpp:376-398 Update(consumed): remove the consumed messages, then previous.Merge(current) — the automatic
+  // previous messages are NOT cleared on this path.
+  void UpdateFromSystem(const ConsumedRegistry& consumed) {
+    if (!consumed.Empty()) ApplyConsumed(consumed);
+    UpdateFromSystem();
   }
   // manager.hpp:400-419 Update(): clear automatic-policy previous, previous.Merge(current), re-register.
   void Update() {
@@ -1038,10 +1101,12 @@ private:
 struct SystemLocalData {
   CmdQueue cmd_queue;
   MessageQueue message_queue;
+  ConsumedRegistry consumed_messages;  // system_local_data.hpp:29-30
   // system_local_data.hpp:90-96,122-132 — ExecuteCommands; MessageManager::Update(consumed); merge local.
   void Update(World& w) {
     cmd_queue.ExecuteAll(w);
-    w.messages.UpdateFromSystem();
+    w.messages.UpdateFromSystem(consumed_messages);
+    consumed_messages.Clear();
     w.messages.MergeLocal(message_queue);
   }
 };

@@ -465,6 +465,114 @@ void TestCommands() {
   }
 }
 
+// ---- message/manager.cpp:215-335 Update(consumed) / ApplyConsumed; consumed_registry.cpp MarkConsumed ----------------------
+void TestConsumedMessages() {
+  const TypeIndex kMsg = Fnv1a("PositionMsg");
+  auto x_of = [&](const MessageQueue& q, size_t i) {
+    Position p;
+    std::memcpy(&p, q.Bytes(kMsg)->data() + i * sizeof(Position), sizeof(p));
+    return p.x;
+  };
+  {
+    ConsumedRegistry r;  // consumed_registry.hpp:288-296: sorted, unique
+    r.MarkConsumed(kMsg, 5);
+    r.MarkConsumed(kMsg, 1);
+    r.MarkConsumed(kMsg, 5);
+    r.MarkConsumed(kMsg, 3);
+    CHECK((r.Data().at(kMsg) == std::vector<size_t>{1, 3, 5}));
+    CHECK(!r.Empty());
+    r.Clear();
+    CHECK(r.Empty());
+  }
+  {
+    MessageManager m;  // :216-228 consumed previous message is removed after Update
+    m.Register(kMsg, sizeof(Position));
+    const Position p{};
+    m.Write(kMsg, &p);
+    m.Update();
+    ConsumedRegistry r;
+    r.MarkConsumed(kMsg, 0);
+    m.UpdateFromSystem(r);
+    CHECK(m.Previous().Count(kMsg) == 0 && m.Current().Count(kMsg) == 0);
+  }
+  {
+    MessageManager m;  // :230-244 unconsumed messages survive
+    m.Register(kMsg, sizeof(Position));
+    const Position a{}, b{2.0f, 0.0f};
+    m.Write(kMsg, &a);
+    m.Write(kMsg, &b);
+    m.Update();
+    ConsumedRegistry r;
+    r.MarkConsumed(kMsg, 0);
+    m.UpdateFromSystem(r);
+    CHECK(m.Previous().Count(kMsg) == 1 && x_of(m.Previous(), 0) == 2.0f);
+  }
+  {
+    MessageManager m;  // :246-257 empty registry: Update(registry) keeps the (automatic) previous message
+    m.Register(kMsg, sizeof(Position));
+    const Position p{};
+    m.Write(kMsg, &p);
+    m.Update();
+    m.UpdateFromSystem(ConsumedRegistry{});
+    CHECK(m.Previous().Count(kMsg) == 1);
+  }
+  {
+    MessageManager m;  // :259-280 consumed CURRENT message is removed in the same Update cycle
+    m.Register(kMsg, sizeof(Position));
+    m.Update();
+    const Position a{}, b{20.0f, 0.0f};
+    m.Write(kMsg, &a);
+    m.Write(kMsg, &b);
+    ConsumedRegistry r;
+    r.MarkConsumed(kMsg, 0);  // prev = 0 items: global 0 -> current[0]
+    m.UpdateFromSystem(r);
+    CHECK(m.Previous().Count(kMsg) == 1 && x_of(m.Previous(), 0) == 20.0f);
+  }
+  {
+    MessageManager m;  // :284-304 ApplyConsumed removes from both queues, no buffer swap
+    m.Register(kMsg, sizeof(Position));
+    const Position a{1.0f, 0.0f}, b{2.0f, 0.0f};
+    m.Write(kMsg, &a);
+    m.Update();
+    m.Write(kMsg, &b);
+    ConsumedRegistry r;
+    r.MarkConsumed(kMsg, 0);
+    r.MarkConsumed(kMsg, 1);
+    m.ApplyConsumed(r);
+    CHECK(m.Previous().Count(kMsg) == 0 && m.Current().Count(kMsg) == 0);
+  }
+  {
+    MessageManager m;  // :306-324 ApplyConsumed does not swap buffers
+    m.Register(kMsg, sizeof(Position));
+    const Position a{10.0f, 0.0f}, b{20.0f, 0.0f};
+    m.Write(kMsg, &a);
+    m.Update();
+    m.Write(kMsg, &b);
+    ConsumedRegistry r;
+    r.MarkConsumed(kMsg, 0);
+    m.ApplyConsumed(r);
+    CHECK(m.Previous().Count(kMsg) == 0 && m.Current().Count(kMsg) == 1 && x_of(m.Current(), 0) == 20.0f);
+  }
+  {
+    MessageManager m;  // :326-335 empty registry is a no-op
+    m.Register(kMsg, sizeof(Position));
+    const Position p{};
+    m.Write(kMsg, &p);
+    m.Update();
+    m.ApplyConsumed(ConsumedRegistry{});
+    CHECK(m.Previous().Count(kMsg) == 1);
+  }
+  {
+    MessageQueue q;  // queue.hpp:331-360: ranges erased back to front, survivors keep their order
+    q.Register(kMsg, 4);
+    for (int i = 0; i < 8; ++i) q.Enqueue(kMsg, &i);
+    q.RemoveIndices(kMsg, {0, 1, 4, 6, 7});
+    int v[3];
+    std::memcpy(v, q.Bytes(kMsg)->data(), 12);
+    CHECK(q.Count(kMsg) == 3 && v[0] == 2 && v[1] == 3 && v[2] == 5);
+  }
+}
+
 // ---- message/manager.cpp:148-213 Update, :595-645 MergeLocal, :753-796 Previous/Current; reader.cpp order ----------------
 void TestMessages() {
   const TypeIndex kMsg = Fnv1a("PositionMsg"), kManual = Fnv1a("ManualMessage"), kOther = Fnv1a("VelocityMsg");
@@ -687,6 +795,7 @@ int main() {
   TestQuery();
   TestCommands();
   TestMessages();
+  TestConsumedMessages();
   TestScheduling();
   TestApplyOrder();
   std::printf("oracle KATs: %d checks, %d failed\n", g_checks, g_fail);

@@ -200,6 +200,29 @@ int32_t sys_consume(const OCtx* c) {
   }
   return 0;
 }
+int32_t sys_consume_strong(const OCtx* c) {
+  // ConsumableMessageReader<CollisionEvent>::ConsumeIf(impulse > t) (reader.hpp:1035-1058): strong events damage Health of
+  // evt.a and are marked consumed in this system's registry (global index over previous ++ current).
+  uint32_t health_slot;
+  float threshold;
+  std::memcpy(&health_slot, c->params, 4);
+  std::memcpy(&threshold, c->params + 4, 4);
+  OWorld* w = c->world;
+  const ho::TypeIndex health = w->slot_hash[health_slot];
+  const auto bytes = w->world.messages.ReadAll(c->reads_message);
+  const size_t n = bytes.size() / sizeof(CollisionEvent);
+  for (size_t i = 0; i < n; ++i) {
+    CollisionEvent ev;
+    std::memcpy(&ev, &bytes[i * sizeof(ev)], sizeof(ev));
+    if (!(ev.impulse > threshold)) continue;
+    c->local->consumed_messages.MarkConsumed(c->reads_message, i);
+    const ho::Entity a = E(ev.a);
+    if (!w->world.entities.Validate(a)) continue;
+    uint8_t* hp = w->world.components.Get(a, health);
+    if (hp) *reinterpret_cast<int32_t*>(hp) -= int32_t(ev.impulse);
+  }
+  return 0;
+}
 int32_t sys_stats(const OCtx* c) {
   OWorld* w = c->world;
   const int saved_threads = w->threads;
@@ -236,7 +259,7 @@ struct Builtin {
 const Builtin kBuiltins[] = {
     {"integrate", sys_integrate}, {"accel_integrate", sys_accel_integrate}, {"damp", sys_damp},
     {"regen", sys_regen},         {"team_tint", sys_team_tint},             {"detect", sys_detect},
-    {"detect_sparse", sys_detect_sparse}, {"consume", sys_consume},         {"stats", sys_stats},
+    {"detect_sparse", sys_detect_sparse}, {"consume", sys_consume}, {"consume_strong", sys_consume_strong},         {"stats", sys_stats},
     {"exit_check", sys_exit_check}, {"despawn_dead", sys_despawn_dead},
 };
 

@@ -83,6 +83,38 @@ def cfg4(backend, n=8192, frames=3, mode=capi.EXEC_SERIAL):
     return out
 
 
+def consumable(backend, n=4099, frames=4, mode=capi.EXEC_SERIAL):
+    """Consumable messages (manager.hpp:376-398,421-496): a MANUAL-policy CollisionEvent channel, so events live until a
+    reader consumes them.  S0 consumes the strong ones (impulse > 2.5: Health damage + MarkConsumed), S1 reads whatever
+    is left, S2 emits this frame's events (registered last, as in cfg4).  Counts and bytes of both queues are recorded
+    after every run and every World::Update."""
+    w = capi.World(backend)
+    shorts = ["Position", "Health", "Team"]
+    worlds.register_all(w, shorts)
+    w.spawn_batch([worlds.cname(x) for x in shorts], n, [worlds.column(x, n, 9000 + i) for i, x in enumerate(shorts)],
+                  want_entities=False)
+    w.message_register(worlds.COLLISION_EVENT, 24, capi.MSG_MANUAL)
+    P, H, T = (worlds.cname(x) for x in shorts)
+    s = w.schedule("Update")
+    s.add_system("S0_consume_strong", "consume_strong", None, params=struct.pack("<If", w.slots[H], 2.5),
+                 reads_message=worlds.COLLISION_EVENT, extra_writes=[H], flags=capi.SYSTEM_CONSUMES_MESSAGES)
+    s.add_system("S1_consume_rest", "consume", None, params=struct.pack("<I", w.slots[H]), reads_message=worlds.COLLISION_EVENT,
+                 extra_writes=[H])
+    s.add_system("S2_detect", "detect", w.query([(P, False), (T, False)]), writes_message=worlds.COLLISION_EVENT)
+    s.build()
+    out = {"order": s.execution_order()}
+    for frame in range(frames):
+        s.run_and_wait(mode)
+        out[f"frame{frame}_counts_after_run"] = list(w.message_counts(worlds.COLLISION_EVENT))
+        out[f"frame{frame}_messages_after_run"] = _bytes_digest(w.message_read(worlds.COLLISION_EVENT, 0),
+                                                                  w.message_read(worlds.COLLISION_EVENT, 1))
+        w.update()
+        out[f"frame{frame}_counts_after_update"] = list(w.message_counts(worlds.COLLISION_EVENT))
+    out["world"] = snapshot_digest(w.snapshot())
+    w.close()
+    return out
+
+
 def churn_small(backend, seed=3, frames=4):
     """Many commands per entity on tiny tables: long swap-and-pop chains, tables emptied and refilled, new archetypes,
     stale ids, Try-variants and Clear."""
@@ -139,6 +171,7 @@ SCENARIOS = {
     "cfg2_all": lambda b: cfg2(b, filtered=False),
     "cfg3_churn": lambda b: cfg3(b),
     "cfg4_schedule_messages": lambda b: cfg4(b),
+    "consumable_messages": lambda b: consumable(b),
     "churn_small_s3": lambda b: churn_small(b, seed=3),
     "churn_small_s11": lambda b: churn_small(b, seed=11),
 }
