@@ -91,20 +91,51 @@ int32_t launch_team_tint(const helios_gpu_system_ctx* ctx) {
 // events in exactly the order the reference's serial ForEach would have emitted them (no atomics needed).
 struct DetectBody {
   const helios_gpu_msg_writer* d_wr;  // device-resident view: stays valid across buffer swaps (CUDA-graph safe)
-  __device__ void operator()(const Row& r, Position& p, Team& t) const {
+  // A thread visits rows in adjacent pairs: the event of an even slot is held back one call and leaves together with
+  // its odd neighbour as three 16-byte streaming stores (48 contiguous, 16-byte-aligned bytes) instead of six 8-byte
+  // stores at a 24-byte stride.
+  CollisionEvent held;
+  unsigned long long held_slot = ~0ull;
+
+  __device__ __forceinline__ static void store_one(const helios_gpu_msg_writer& wr, unsigned long long slot, const CollisionEvent& ev) {
+    reinterpret_cast<CollisionEvent*>(wr.data)[slot] = ev;
+  }
+  __device__ void operator()(const Row& r, Position& p, Team& t) {
     const helios_gpu_msg_writer wr = *d_wr;
     CollisionEvent ev;
     ev.a = r.entity;
     ev.b = r.entity ^ 1ull;  // synthetic partner: the entity with the neighbouring index
     ev.impulse = p.x * 0.0078125f + float(t.id);
     ev.pad = 0;
-    if (r.flat_row < wr.capacity) reinterpret_cast<CollisionEvent*>(wr.data)[r.flat_row] = ev;
     if (r.flat_row == 0) *wr.count = r.n_rows < wr.capacity ? r.n_rows : wr.capacity;
+    const unsigned long long slot = r.flat_row;
+    if (held_slot != ~0ull) {
+      const unsigned long long hs = held_slot;
+      held_slot = ~0ull;
+      if (hs + 1 == slot && slot < wr.capacity) {
+        uint4* dst = reinterpret_cast<uint4*>(wr.data + hs * sizeof(CollisionEvent));
+        __stcs(dst + 0, make_uint4(uint32_t(held.a), uint32_t(held.a >> 32), uint32_t(held.b), uint32_t(held.b >> 32)));
+        __stcs(dst + 1, make_uint4(__float_as_uint(held.impulse), held.pad, uint32_t(ev.a), uint32_t(ev.a >> 32)));
+        __stcs(dst + 2, make_uint4(uint32_t(ev.b), uint32_t(ev.b >> 32), __float_as_uint(ev.impulse), ev.pad));
+        return;
+      }
+      store_one(wr, hs, held);  // its neighbour never came (table boundary): on its own
+    }
+    if (slot >= wr.capacity) return;
+    if ((slot & 1ull) == 0 && slot + 1 < wr.capacity) {
+      held = ev;
+      held_slot = slot;
+    } else {
+      store_one(wr, slot, ev);
+    }
+  }
+  __device__ void finish() {
+    if (held_slot != ~0ull) store_one(*d_wr, held_slot, held);
   }
 };
 int32_t launch_detect(const helios_gpu_system_ctx* ctx) {
   if (!ctx->writer.data || ctx->writer.elem_size != sizeof(CollisionEvent)) return HELIOS_GPU_ERR_STATE;
-  return for_each_launch<0u, true, DetectBody, Position, Team>(ctx, DetectBody{ctx->d_writer});
+  return for_each_launch<0u, true, DetectBody, Position, Team>(ctx, DetectBody{ctx->d_writer, CollisionEvent{}, ~0ull});
 }
 
 // ---- "detect_sparse": same query, emits only when team == 0, through the warp-aggregated append ring ---------
