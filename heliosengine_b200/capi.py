@@ -63,7 +63,14 @@ class QueryDesc(C.Structure):
         ("with_", C.c_uint64 * MAX_COMPONENTS),
         ("n_without", C.c_uint32),
         ("without", C.c_uint64 * MAX_COMPONENTS),
+        ("n_sparse_data", C.c_uint32),
+        ("sparse_data", C.c_uint64 * MAX_QUERY_COMPONENTS),
+        ("sparse_rule", C.c_uint32),
     ]
+
+
+# helios_gpu_query_desc::sparse_rule (include/helios_gpu.h)
+SPARSE_STRICT, SPARSE_FOREACH, SPARSE_WITH_ENTITY = 0, 1, 2
 
 
 class Command(C.Structure):
@@ -153,6 +160,7 @@ class World:
         if st != OK:
             raise HeliosError(st, "world_create failed (is a CUDA device visible? there is no CPU fallback)")
         self.slots: dict[str, int] = {}
+        self.sparse_names: list[str] = []
         self.sizes: dict[str, int] = {}
         self.hash_to_name: dict[int, str] = {}
         self._keep = []
@@ -194,6 +202,27 @@ class World:
         self.sizes[name] = size
         self.hash_to_name[fnv1a(name)] = name
         return slot
+
+    def register_sparse_component(self, name: str, size: int, align: int = 4) -> int:
+        """A sparse-set stored component (component/sparse_storage.hpp); size 0 = tag."""
+        slot = self.b.fn("register_sparse_component")(self.h, C.c_uint64(fnv1a(name)), C.c_uint32(size), C.c_uint32(align))
+        if slot < 0:
+            self._check(slot)
+        self.slots[name] = slot
+        self.sizes[name] = size
+        self.hash_to_name[fnv1a(name)] = name
+        self.sparse_names.append(name)
+        return slot
+
+    def snapshot_sparse(self, name: str) -> dict:
+        """Dense order of one sparse storage: reverse map (entity index per dense slot) + raw value bytes."""
+        n = C.c_uint64()
+        self._check(self.b.fn("snapshot_sparse")(self.h, C.c_uint64(fnv1a(name)), C.byref(n), None, None, C.c_uint64(0)))
+        idx = np.empty(n.value, dtype=np.uint32)
+        data = np.empty(n.value * self.sizes[name], dtype=np.uint8)
+        self._check(self.b.fn("snapshot_sparse")(self.h, C.c_uint64(fnv1a(name)), C.byref(n), _ptr(idx) if idx.size else None,
+                                                 _ptr(data) if data.size else None, C.c_uint64(n.value)))
+        return {"indices": idx, "data": data}
 
     def mask(self, names: Iterable[str]) -> int:
         m = 0
@@ -279,8 +308,9 @@ class World:
                                                        C.c_uint64(row0), C.c_uint64(rows), C.c_void_p(dst_ptr)))
 
     # -- queries ----------------------------------------------------------------------------------------------
-    def query(self, components: Sequence[tuple[str, bool]], with_: Sequence[str] = (), without: Sequence[str] = ()) -> "Query":
-        return Query(self, components, with_, without)
+    def query(self, components: Sequence[tuple[str, bool]], with_: Sequence[str] = (), without: Sequence[str] = (),
+              sparse_data: Sequence[str] = (), sparse_rule: int = SPARSE_STRICT) -> "Query":
+        return Query(self, components, with_, without, sparse_data, sparse_rule)
 
     # -- commands ---------------------------------------------------------------------------------------------
     def enqueue(self, cmds: np.ndarray, payload: bytes | np.ndarray = b""):
@@ -331,9 +361,13 @@ class World:
 class Query:
     """Query<Cs..., With<...>, Without<...>> (reference query/query.hpp:658-1248)."""
 
-    def __init__(self, world: World, components, with_, without):
+    def __init__(self, world: World, components, with_, without, sparse_data=(), sparse_rule=SPARSE_STRICT):
         self.w = world
         d = QueryDesc()
+        d.n_sparse_data = len(sparse_data)
+        for i, name in enumerate(sparse_data):
+            d.sparse_data[i] = fnv1a(name)
+        d.sparse_rule = sparse_rule
         d.n_components = len(components)
         for i, (name, write) in enumerate(components):
             d.components[i] = fnv1a(name)

@@ -22,6 +22,7 @@
 //      command payloads are patched in (last writer of a component wins — the observable result of
 //      Archetype::Set before/after migration, manager.hpp:1175-1192).
 #include <algorithm>
+#include <cstring>
 #include <vector>
 
 #include "primitives.cuh"
@@ -35,7 +36,7 @@ constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr uint64_t kDeadMask = 0xFFFFFFFFFFFFFFFFull;  // destination "mask" of a destroyed entity
 constexpr uint64_t kInstA = 1ull << 63;                 // instance key tag: opened by the Append op in the low bits
 
-enum : uint32_t { F_VALID = 1u, F_MIG = 2u, F_DESTROY = 4u };
+enum : uint32_t { F_VALID = 1u, F_MIG = 2u, F_DESTROY = 4u, F_SPLAST = 8u /* last sparse-set event of its entity */ };
 
 struct Counters {
   uint32_t n_valid_slots;  // K: compacted command count
@@ -48,6 +49,7 @@ struct Counters {
   uint32_t effective;
   uint32_t dups;           // commands whose entity has an earlier command in the same batch
   uint32_t ticket;         // dynamic block index of the single-launch resolver
+  uint32_t sparse_events;  // commands that append to / remove from / write into a sparse-set storage
   unsigned long long moved_bytes;
 };
 
@@ -132,6 +134,7 @@ struct helios_gpu_world::ApplyScratch {
   DevBuf J;
   DevBuf ih_keys, ih_vals;
   DevBuf ch_slot, ch_ent, stage;
+  DevBuf ev_app, ev_rem, ev_wr, ev_mem;  // per-command sparse-set events (ordinal masks) and membership after the command
   DevBuf coffset;  // uint32[64] byte offset of each component inside a staged row
   uint32_t stage_stride = 0;
   size_t stride_comps = 0;
@@ -210,7 +213,27 @@ struct ChainArgs {
   uint32_t* cflags;
   uint32_t* dflag;
   Counters* counters;
+  // sparse-set components (sparse.cu): slots that are sparse-stored, slot -> ordinal, the per-entity membership words,
+  // and per command the ordinal masks of the storages it appends to / removes from / writes a value into plus the
+  // entity's membership after it.  sparse_slots == 0: the world has no sparse types and none of this is touched.
+  uint64_t sparse_slots;
+  int8_t ord_of_slot[64];
+  const uint32_t* membership;
+  uint32_t* ev_app;
+  uint32_t* ev_rem;
+  uint32_t* ev_wr;
+  uint32_t* ev_mem;
 };
+
+__device__ __forceinline__ uint32_t sparse_ordinals(const ChainArgs& a, uint64_t slots) {
+  uint32_t o = 0;
+  while (slots) {
+    const int s = __ffsll(static_cast<long long>(slots)) - 1;
+    slots &= slots - 1;
+    o |= 1u << a.ord_of_slot[s];
+  }
+  return o;
+}
 
 __global__ void k_chain(ChainArgs a) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -229,12 +252,18 @@ __global__ void k_chain(ChainArgs a) {
   uint32_t last_mig = kNone;
   uint32_t r = i;
   uint32_t invalid = 0;
+  const bool sp = a.sparse_slots != 0;
+  uint32_t sm = (sp && alive) ? a.membership[idx] : 0u;  // sparse-set membership, tracked like the archetype mask
+  uint32_t last_ev = kNone, n_ev = 0;
   for (; r < a.K && a.skey[r] == idx64; ++r) {
     const uint32_t k = a.sval[r];
     const helios_gpu_command c = a.cmd[k];
     const bool v = alive && ent_gen(c.entity) == gen0;  // EntityManager::Validate (entity/manager.hpp:410-418)
     uint64_t src = mask, dst = mask, w = 0;
     uint32_t fl = 0;
+    uint32_t eapp = 0, erem = 0, ewr = 0;
+    const uint64_t cm = c.component_mask & ~a.sparse_slots;  // archetype-stored part of the command's component set
+    const uint32_t sb = (sp && (c.component_mask & a.sparse_slots)) ? sparse_ordinals(a, c.component_mask & a.sparse_slots) : 0u;
     if (!v) {
       // Try* variants skip silently (world.hpp:996-1000); the others are HELIOS_ASSERT failures in the reference
       if (c.kind != HELIOS_GPU_CMD_TRY_DESTROY && c.kind != HELIOS_GPU_CMD_TRY_ADD && c.kind != HELIOS_GPU_CMD_TRY_REMOVE) ++invalid;
@@ -246,25 +275,44 @@ __global__ void k_chain(ChainArgs a) {
           fl |= F_DESTROY | F_MIG;
           dst = kDeadMask;
           alive = false;
+          erem = sm;                   // RemoveEntity: TryRemove from every sparse storage (manager.hpp:1090-1093)
+          sm = 0;
           break;
         case HELIOS_GPU_CMD_ADD:       // manager.hpp:1146-1203 — every listed component is written
-          w = c.component_mask;
-          dst = mask | c.component_mask;
+          w = cm;
+          dst = mask | cm;
+          eapp = sb & ~sm;             // AddSparseComponent -> Set: insert or overwrite (sparse_storage.hpp:121-131)
+          ewr = sb;
+          sm |= sb;
           break;
         case HELIOS_GPU_CMD_TRY_ADD:   // manager.hpp:1205-1248 — only the missing ones
-          w = c.component_mask & ~mask;
-          dst = mask | c.component_mask;
+          w = cm & ~mask;
+          dst = mask | cm;
+          eapp = sb & ~sm;             // TrySet: present values stay untouched (sparse_storage.hpp:133-143)
+          ewr = eapp;
+          sm |= sb;
           break;
         case HELIOS_GPU_CMD_REMOVE:
         case HELIOS_GPU_CMD_TRY_REMOVE:  // manager.hpp:1268-1312
-          dst = mask & ~c.component_mask;
+          dst = mask & ~cm;
+          erem = sb & sm;              // (Try)RemoveSparseComponent (manager.hpp:1355-1377); absent = skipped
+          sm &= ~sb;
           break;
         case HELIOS_GPU_CMD_CLEAR:       // manager.hpp:1117-1144
           dst = 0;
+          erem = sm;                     // manager.hpp:1140-1143
+          sm = 0;
           break;
         default: break;
       }
       if (!(fl & F_DESTROY) && dst != src) fl |= F_MIG;
+    }
+    if (sp) {
+      a.ev_app[k] = eapp;
+      a.ev_rem[k] = erem;
+      a.ev_wr[k] = ewr;
+      a.ev_mem[k] = sm;
+      if (eapp | erem | ewr) { last_ev = k; ++n_ev; }
     }
     a.src_mask[k] = src;
     a.dst_mask[k] = dst;
@@ -276,6 +324,10 @@ __global__ void k_chain(ChainArgs a) {
       last_mig = k;
       if (!(fl & F_DESTROY)) mask = dst;
     }
+  }
+  if (last_ev != kNone) {
+    a.cflags[last_ev] |= F_SPLAST;
+    atomicAdd(&a.counters->sparse_events, n_ev);
   }
   // backward pass: a written value survives iff no later command rewrites, removes or destroys it
   uint64_t decided = 0;
@@ -879,6 +931,14 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
                w->d_loc.as<uint64_t>(), w->d_tmask.as<uint64_t>(), w->ent_capacity, S.src_mask.as<uint64_t>(),
                S.dst_mask.as<uint64_t>(), S.wset.as<uint64_t>(), S.wlive.as<uint64_t>(), S.home_cmd.as<uint32_t>(),
                S.cflags.as<uint32_t>(), S.dflag.as<uint32_t>(), dc};
+  ca.sparse_slots = w->sparse_slot_mask;
+  if (w->sparse_slot_mask) {
+    NEED(S.ev_app, K * 4); NEED(S.ev_rem, K * 4); NEED(S.ev_wr, K * 4); NEED(S.ev_mem, K * 4);
+    std::memcpy(ca.ord_of_slot, w->sparse_ord_of_slot, 64);
+    ca.membership = w->d_membership.as<uint32_t>();
+    ca.ev_app = S.ev_app.as<uint32_t>(); ca.ev_rem = S.ev_rem.as<uint32_t>();
+    ca.ev_wr = S.ev_wr.as<uint32_t>();   ca.ev_mem = S.ev_mem.as<uint32_t>();
+  }
   k_chain<<<blocks_for(K), 256, 0, st>>>(ca);
   ++launches;
 
@@ -915,6 +975,7 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
       // some entity carries several commands: stable sort by entity index, then redo the chains in FIFO order
       launches += prim::radix_sort_pairs(S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), K, 32, ss, st);
       HG_CUDA(w, cudaMemsetAsync(&dc->invalid, 0, 4, st));
+      HG_CUDA(w, cudaMemsetAsync(&dc->sparse_events, 0, 4, st));
       k_chain<<<blocks_for(K), 256, 0, st>>>(ca);
       ++launches;
       sorted_by_entity = true;
@@ -1007,6 +1068,11 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
                                                       S.ch_ent.as<helios_gpu_entity_t>(), w->d_loc.as<uint64_t>());
     launches += 4;
   }
+
+  // ---- sparse-set storages: replay the events the chains produced (sparse.cu) --------------------------------------
+  if (hc.sparse_events)
+    HG_TRY(sparse_apply_events(w, cmd, d_payload, K, S.cflags.as<uint32_t>(), S.ev_app.as<uint32_t>(), S.ev_rem.as<uint32_t>(),
+                               S.ev_wr.as<uint32_t>(), S.ev_mem.as<uint32_t>(), hc.sparse_events));
 
   // ---- stage 5: destroys, payload patch, counts ------------------------------------------------------------------
   launches += prim::exclusive_scan_u32(S.dflag.as<uint32_t>(), S.dpos.as<uint32_t>(), K, S.partials.as<uint32_t>(), &dc->n_destroy, st);

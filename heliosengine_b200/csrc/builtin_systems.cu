@@ -78,6 +78,35 @@ int32_t launch_regen(const helios_gpu_system_ctx* ctx) {
   return for_each_launch<0b1u, false, RegenBody, Health>(ctx, RegenBody{});
 }
 
+// ---- "buff_heal": Query<Health&, const SparseBuff&> — SparseBuff{i32 stacks} is sparse-set stored: the value comes from
+// its storage by entity id (iterator.hpp:88-100); rows without the component are not visited (iterator.hpp:539-556) -----
+struct BuffHealBody {
+  helios_gpu_sparse_view sv;
+  __device__ void operator()(const Row& r, Health& h) const { h.hp += *helios_gpu::sparse_try_get<int32_t>(sv, 0, r.entity); }
+};
+int32_t launch_buff_heal(const helios_gpu_system_ctx* ctx) {
+  if (!ctx->sparse.dir || !ctx->sparse_filter.membership) return HELIOS_GPU_ERR_STATE;  // the query must list sparse_data[0]
+  return for_each_launch<0b1u, true, BuffHealBody, Health>(ctx, BuffHealBody{ctx->sparse});
+}
+
+// ---- "buff_optional": Query<Health&, const SparseBuff*> — pointer access is nullable and not part of the match
+// (iterator.hpp:49-68): hp += buff ? buff->stacks : -1 ------------------------------------------------------------------
+struct BuffOptionalParams { uint64_t type_hash; uint32_t ordinal; uint32_t pad; };
+struct BuffOptionalBody {
+  const helios_gpu_sparse_dir* dir;
+  uint32_t ordinal;
+  __device__ void operator()(const Row& r, Health& h) const {
+    const int32_t* b = helios_gpu::sparse_try_get_ordinal<int32_t>(dir, ordinal, r.entity);
+    h.hp += b ? *b : -1;
+  }
+};
+int32_t launch_buff_optional(const helios_gpu_system_ctx* ctx) {
+  if (ctx->params_size < sizeof(BuffOptionalParams) || !ctx->sparse.dir) return HELIOS_GPU_ERR_STATE;
+  BuffOptionalParams p;
+  std::memcpy(&p, ctx->params, sizeof(p));
+  return for_each_launch<0b1u, true, BuffOptionalBody, Health>(ctx, BuffOptionalBody{ctx->sparse.dir, p.ordinal});
+}
+
 // ---- "team_tint": Query<const Team&, Tint&> -----------------------------------------------------------------
 struct TintBody {
   __device__ void operator()(const Row&, Team& t, Tint& c) const { c.rgba = (t.id * 0x00202020u) | 0xFF000000u; }
@@ -285,7 +314,7 @@ const Entry kBuiltins[] = {
     {"damp", launch_damp},             {"regen", launch_regen},
     {"team_tint", launch_team_tint},   {"detect", launch_detect},
     {"detect_sparse", launch_detect_sparse}, {"consume", launch_consume},
-    {"consume_strong", launch_consume_strong},
+    {"consume_strong", launch_consume_strong}, {"buff_heal", launch_buff_heal}, {"buff_optional", launch_buff_optional},
     {"stats", launch_stats},           {"exit_check", launch_exit_check},
     {"despawn_dead", launch_despawn_dead},
 };

@@ -117,10 +117,17 @@ struct TileRef {
   const helios_gpu_entity_t* entities;
 };
 
-template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
-__device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<Cs*...> cols, Body& body) {
+// Per-entity sparse-set test of a launch (helios_gpu_sparse_filter): one membership word per entity index.
+__device__ __forceinline__ bool sparse_pass(const helios_gpu_sparse_filter& sf, uint32_t membership) {
+  return (membership & sf.require) == sf.require && (membership & sf.exclude) == 0u;
+}
+
+template <uint32_t kWriteMask, bool kWithEntity, bool kSparse, typename Body, typename... Cs>
+__device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<Cs*...> cols, Body& body,
+                                             const helios_gpu_sparse_filter& sf) {
   using namespace detail;
   constexpr int N = sizeof...(Cs);
+  constexpr bool kLoadEnt = kWithEntity || kSparse;  // the sparse test is keyed by entity index
   const uint32_t row0 = t.row0;
   const uint32_t live = t.rows - row0;
   cuda::std::tuple<CompRegs<Cs>...> regs;
@@ -142,7 +149,7 @@ __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<
 #pragma unroll
       for (int k = 0; k < kPairs; ++k) load_pair(cr.p[k], col + row0 + k * 2 * kBlock + 2 * threadIdx.x);
     });
-    if constexpr (kWithEntity) {
+    if constexpr (kLoadEnt) {
 #pragma unroll
       for (int k = 0; k < kPairs; ++k) {
         const uint4 e = __ldcs(reinterpret_cast<const uint4*>(t.entities + row0 + k * 2 * kBlock + 2 * threadIdx.x));
@@ -150,12 +157,23 @@ __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<
         ents[k][1] = uint64_t(e.z) | (uint64_t(e.w) << 32);
       }
     }
+    uint32_t member[kPairs][2];
+    if constexpr (kSparse) {  // all gathers go out before the first body runs
+#pragma unroll
+      for (int k = 0; k < kPairs; ++k) {
+        member[k][0] = __ldg(&sf.membership[uint32_t(ents[k][0])]);
+        member[k][1] = __ldg(&sf.membership[uint32_t(ents[k][1])]);
+      }
+    }
 #pragma unroll
     for (int k = 0; k < kPairs; ++k) {
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
+        if constexpr (kSparse) {
+          if (!sparse_pass(sf, member[k][j])) continue;  // iterator.hpp:530-585 AdvanceToValidEntity
+        }
         const uint32_t r = row0 + k * 2 * kBlock + 2 * threadIdx.x + j;
-        call(Row{t.row_begin + r, t.n_rows, kWithEntity ? ents[k][j] : HELIOS_GPU_INVALID_ENTITY, t.archetype, r}, k, j);
+        call(Row{t.row_begin + r, t.n_rows, kLoadEnt ? ents[k][j] : HELIOS_GPU_INVALID_ENTITY, t.archetype, r}, k, j);
       }
     }
     each([&](auto idx, auto& cr, auto* col) {
@@ -173,8 +191,12 @@ __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<
         const uint32_t off = k * 2 * kBlock + 2 * threadIdx.x + j;
         if (off < live) {
           const uint32_t r = row0 + off;
+          const helios_gpu_entity_t ent = kLoadEnt ? t.entities[r] : HELIOS_GPU_INVALID_ENTITY;
+          if constexpr (kSparse) {
+            if (!sparse_pass(sf, __ldg(&sf.membership[uint32_t(ent)]))) continue;
+          }
           each([&](auto, auto& cr, auto* col) { cr.p[k].v[j] = col[r]; });
-          call(Row{t.row_begin + r, t.n_rows, kWithEntity ? t.entities[r] : HELIOS_GPU_INVALID_ENTITY, t.archetype, r}, k, j);
+          call(Row{t.row_begin + r, t.n_rows, ent, t.archetype, r}, k, j);
           each([&](auto idx, auto& cr, auto* col) {
             if constexpr ((kWriteMask >> decltype(idx)::value) & 1u) col[r] = cr.p[k].v[j];
           });
@@ -186,11 +208,13 @@ __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<
 
 // Two FULL tiles of one table at once (narrow rows): the loads of both tiles are in flight before either body runs, which
 // doubles the bytes a thread keeps outstanding — a one-tile walk of 8-byte rows is bound by memory latency, not bandwidth.
-template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
+template <uint32_t kWriteMask, bool kWithEntity, bool kSparse, typename Body, typename... Cs>
 __device__ __forceinline__ void process_full_tile_pair(const TileRef& t, uint32_t row0_a, uint32_t row0_b,
-                                                       cuda::std::tuple<Cs*...> cols, Body& body) {
+                                                       cuda::std::tuple<Cs*...> cols, Body& body,
+                                                       const helios_gpu_sparse_filter& sf) {
   using namespace detail;
   constexpr int N = sizeof...(Cs);
+  constexpr bool kLoadEnt = kWithEntity || kSparse;
   cuda::std::tuple<CompRegs<Cs>...> regs[2];
   helios_gpu_entity_t ents[2][kPairs][2];
   const uint32_t row0[2] = {row0_a, row0_b};
@@ -204,7 +228,7 @@ __device__ __forceinline__ void process_full_tile_pair(const TileRef& t, uint32_
        }()),
        ...);
     }(cuda::std::make_index_sequence<N>{});
-    if constexpr (kWithEntity) {
+    if constexpr (kLoadEnt) {
 #pragma unroll
       for (int k = 0; k < kPairs; ++k) {
         const uint4 e = __ldcs(reinterpret_cast<const uint4*>(t.entities + row0[h] + k * 2 * kBlock + 2 * threadIdx.x));
@@ -213,14 +237,27 @@ __device__ __forceinline__ void process_full_tile_pair(const TileRef& t, uint32_
       }
     }
   }
+  uint32_t member[2][kPairs][2];
+  if constexpr (kSparse) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+#pragma unroll
+      for (int k = 0; k < kPairs; ++k) {
+        member[h][k][0] = __ldg(&sf.membership[uint32_t(ents[h][k][0])]);
+        member[h][k][1] = __ldg(&sf.membership[uint32_t(ents[h][k][1])]);
+      }
+  }
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
 #pragma unroll
     for (int k = 0; k < kPairs; ++k) {
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
+        if constexpr (kSparse) {
+          if (!sparse_pass(sf, member[h][k][j])) continue;
+        }
         const uint32_t r = row0[h] + k * 2 * kBlock + 2 * threadIdx.x + j;
-        const Row rc{t.row_begin + r, t.n_rows, kWithEntity ? ents[h][k][j] : HELIOS_GPU_INVALID_ENTITY, t.archetype, r};
+        const Row rc{t.row_begin + r, t.n_rows, kLoadEnt ? ents[h][k][j] : HELIOS_GPU_INVALID_ENTITY, t.archetype, r};
         [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
           body(rc, cuda::std::get<Is>(regs[h]).p[k].v[j]...);
         }(cuda::std::make_index_sequence<N>{});
@@ -253,9 +290,11 @@ constexpr bool kNarrowRows = (0 + ... + int(sizeof(Cs))) + (kWithEntity ? 8 : 0)
 template <bool kWithEntity, typename... Cs>
 constexpr int kForEachMinBlocks = !kNarrowRows<kWithEntity, Cs...> ? 1 : (kWithEntity ? 4 : 8);
 
-template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
-__global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity, Cs...>) for_each_kernel(const helios_gpu_match_args m, Body body) {
+template <uint32_t kWriteMask, bool kWithEntity, bool kSparse, typename Body, typename... Cs>
+__global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity || kSparse, Cs...>) for_each_kernel(const helios_gpu_match_args m, Body body,
+                                                                                                const helios_gpu_sparse_filter sf) {
   constexpr int N = sizeof...(Cs);
+  constexpr bool kLoadEnt = kWithEntity || kSparse;
   static_assert(N >= 1 && N <= HELIOS_GPU_MAX_QUERY_COMPONENTS, "1..8 data components per body");
   __shared__ uint32_t s_tile_begin[kFusedMaxTables + 1];
   __shared__ uint32_t s_table[kFusedMaxTables];
@@ -324,13 +363,13 @@ __global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity, Cs...>)
     tr.archetype = t;
     tr.rows = __ldg(&m.table_rows[t]);
     tr.row_begin = s_row_begin[seg];
-    tr.entities = kWithEntity ? reinterpret_cast<const helios_gpu_entity_t*>(__ldg(reinterpret_cast<const unsigned long long*>(&m.table_entities[t]))) : nullptr;
+    tr.entities = kLoadEnt ? reinterpret_cast<const helios_gpu_entity_t*>(__ldg(reinterpret_cast<const unsigned long long*>(&m.table_entities[t]))) : nullptr;
     void* const* dir = m.table_columns + size_t(t) * HELIOS_GPU_MAX_COMPONENTS;
 #pragma unroll
     for (int k = 0; k < N; ++k)
       bases[k] = reinterpret_cast<void*>(__ldg(reinterpret_cast<const unsigned long long*>(&dir[m.slots[k]])));
   };
-  if constexpr (kNarrowRows<kWithEntity, Cs...>) {
+  if constexpr (kNarrowRows<kLoadEnt, Cs...>) {
     // Narrow rows: a tile is only a few KB, so the metadata chain above would dominate a tile-strided walk.  Each CTA
     // takes a CONTIGUOUS run of tiles instead: consecutive tiles share their table, the chain is paid once per table.
     const uint32_t per = (n_tiles + gridDim.x - 1) / gridDim.x;
@@ -344,10 +383,10 @@ __global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity, Cs...>)
         const auto cols = detail::typed_columns<Cs...>(bases, cuda::std::make_index_sequence<N>{});
         // two full tiles of the same table: both sets of loads go out before the bodies run
         if (tile + 1 < last && tile + 1 < s_tile_begin[seg + 1] && tr.row0 + 2 * kTileRows <= tr.rows) {
-          process_full_tile_pair<kWriteMask, kWithEntity, Body, Cs...>(tr, tr.row0, tr.row0 + kTileRows, cols, body);
+          process_full_tile_pair<kWriteMask, kWithEntity, kSparse, Body, Cs...>(tr, tr.row0, tr.row0 + kTileRows, cols, body, sf);
           ++tile;
         } else {
-          process_tile<kWriteMask, kWithEntity, Body, Cs...>(tr, cols, body);
+          process_tile<kWriteMask, kWithEntity, kSparse, Body, Cs...>(tr, cols, body, sf);
         }
       }
     }
@@ -357,7 +396,7 @@ __global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity, Cs...>)
       open_segment(seg);
       tr.row0 = (tile - s_tile_begin[seg]) * kTileRows;
       const auto cols = detail::typed_columns<Cs...>(bases, cuda::std::make_index_sequence<N>{});
-      process_tile<kWriteMask, kWithEntity, Body, Cs...>(tr, cols, body);
+      process_tile<kWriteMask, kWithEntity, kSparse, Body, Cs...>(tr, cols, body, sf);
     }
   }
   // Optional per-thread epilogue: a body that accumulates into its own members (each thread holds a private copy)
@@ -366,8 +405,9 @@ __global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity, Cs...>)
 }
 
 // for_each_kernel_view: same visit over a MATERIALISED view (worlds with more than kFusedMaxTables tables).
-template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
-__global__ void __launch_bounds__(kBlock) for_each_kernel_view(const helios_gpu_query_view* __restrict__ view, Body body) {
+template <uint32_t kWriteMask, bool kWithEntity, bool kSparse, typename Body, typename... Cs>
+__global__ void __launch_bounds__(kBlock) for_each_kernel_view(const helios_gpu_query_view* __restrict__ view, Body body,
+                                                               const helios_gpu_sparse_filter sf) {
   using namespace detail;
   constexpr int N = sizeof...(Cs);
   __shared__ helios_gpu_segment s_seg;
@@ -400,16 +440,16 @@ __global__ void __launch_bounds__(kBlock) for_each_kernel_view(const helios_gpu_
 #pragma unroll
     for (int k = 0; k < N; ++k) bases[k] = s_seg.columns[k];
     const auto cols = detail::typed_columns<Cs...>(bases, cuda::std::make_index_sequence<N>{});
-    process_tile<kWriteMask, kWithEntity, Body, Cs...>(tr, cols, body);
+    process_tile<kWriteMask, kWithEntity, kSparse, Body, Cs...>(tr, cols, body, sf);
   }
   if constexpr (requires { body.finish(); }) body.finish();
 }
 
 // Host launcher: grid = one resident wave (SM count x occupancy), so CTAs stay put and stride over tiles.
-template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
-inline int32_t for_each_launch(const helios_gpu_system_ctx* ctx, Body body) {
-  auto kern = for_each_kernel<kWriteMask, kWithEntity, Body, Cs...>;
-  auto kern_view = for_each_kernel_view<kWriteMask, kWithEntity, Body, Cs...>;
+template <uint32_t kWriteMask, bool kWithEntity, bool kSparse, typename Body, typename... Cs>
+inline int32_t for_each_launch_impl(const helios_gpu_system_ctx* ctx, Body body) {
+  auto kern = for_each_kernel<kWriteMask, kWithEntity, kSparse, Body, Cs...>;
+  auto kern_view = for_each_kernel_view<kWriteMask, kWithEntity, kSparse, Body, Cs...>;
   static int bps = 0, bps_view = 0;
   if (bps == 0) {
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, kBlock, 0) != cudaSuccess || bps < 1) bps = 1;
@@ -418,12 +458,38 @@ inline int32_t for_each_launch(const helios_gpu_system_ctx* ctx, Body body) {
   cudaStream_t st = static_cast<cudaStream_t>(ctx->stream);
   if (ctx->view == nullptr) {
     if (ctx->match.n_tables > uint32_t(kFusedMaxTables)) return HELIOS_GPU_ERR_STATE;  // the schedule materialises a view then
-    kern<<<ctx->sm_count * uint32_t(bps), kBlock, 0, st>>>(ctx->match, body);
+    kern<<<ctx->sm_count * uint32_t(bps), kBlock, 0, st>>>(ctx->match, body, ctx->sparse_filter);
   } else {
-    kern_view<<<ctx->sm_count * uint32_t(bps_view), kBlock, 0, st>>>(ctx->view, body);
+    kern_view<<<ctx->sm_count * uint32_t(bps_view), kBlock, 0, st>>>(ctx->view, body, ctx->sparse_filter);
   }
   helios_gpu_world_note_launches(ctx->world, 1);
   return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
+}
+
+// A query with sparse-set terms (With<Tag>, Without<Tag>, sparse data) runs the instantiation that reads every row's
+// entity id and tests its membership word; every other query runs the kernel without that code.
+template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
+inline int32_t for_each_launch(const helios_gpu_system_ctx* ctx, Body body) {
+  if (ctx->sparse_filter.membership != nullptr)
+    return for_each_launch_impl<kWriteMask, kWithEntity, true, Body, Cs...>(ctx, body);
+  return for_each_launch_impl<kWriteMask, kWithEntity, false, Body, Cs...>(ctx, body);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Sparse-set values by entity id from inside a body (iterator.hpp:49-68,88-100 FetchComponent of a sparse type;
+// SparseComponentStorage::TryGet, sparse_storage.hpp:229-241).  `k` indexes helios_gpu_query_desc::sparse_data.
+// ---------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ T* sparse_try_get_ordinal(const helios_gpu_sparse_dir* dir, uint32_t ordinal, helios_gpu_entity_t e) {
+  const uint32_t d = __ldg(&dir->sparse[ordinal][uint32_t(e)]);
+  return d == 0xFFFFFFFFu ? nullptr : reinterpret_cast<T*>(dir->dense[ordinal]) + d;
+}
+template <typename T>
+__device__ __forceinline__ T* sparse_try_get(const helios_gpu_sparse_view& v, int k, helios_gpu_entity_t e) {
+  return sparse_try_get_ordinal<T>(v.dir, v.fetch[k], e);
+}
+__device__ __forceinline__ bool sparse_has_ordinal(const helios_gpu_sparse_dir* dir, uint32_t ordinal, helios_gpu_entity_t e) {
+  return __ldg(&dir->sparse[ordinal][uint32_t(e)]) != 0xFFFFFFFFu;
 }
 
 // ---------------------------------------------------------------------------------------------------

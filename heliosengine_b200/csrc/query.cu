@@ -3,6 +3,8 @@
 // per-entity iterator walk (query/iterator.hpp:506-585) with: one single-CTA match kernel that reads the
 // device table directory (mask, live rows, column bases) and emits, in archetype CREATION order with empty
 // tables skipped, one helios_gpu_segment per matching table plus the flattened tile/row prefixes.
+#include <cstring>
+
 #include "query_internal.hpp"
 
 using namespace hgpu;
@@ -104,6 +106,25 @@ __global__ void __launch_bounds__(kMatchThreads) k_match(MatchArgs a) {
   }
 }
 
+// Query::Count with sparse-set terms: rows whose membership word passes, over the materialised view.
+__global__ void __launch_bounds__(256) k_count_sparse(const helios_gpu_query_view* __restrict__ view, const helios_gpu_sparse_filter sf,
+                                                      unsigned long long* __restrict__ out) {
+  const uint32_t nseg = view->n_segments;
+  const helios_gpu_segment* __restrict__ segs = view->segments;
+  const uint32_t stride = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t n = 0;
+  for (uint32_t s = 0; s < nseg; ++s) {
+    const uint32_t rows = segs[s].rows;
+    const helios_gpu_entity_t* __restrict__ ents = segs[s].entities;
+    for (uint32_t r = tid; r < rows; r += stride) {
+      const uint32_t mb = __ldg(&sf.membership[uint32_t(ents[r])]);
+      n += ((mb & sf.require) == sf.require && (mb & sf.exclude) == 0u) ? 1u : 0u;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) n += __shfl_down_sync(0xFFFFFFFFu, n, o);
+  if ((threadIdx.x & 31u) == 0 && n) atomicAdd(out, (unsigned long long)n);
+}
+
 }  // namespace
 
 namespace hgpu {
@@ -156,6 +177,11 @@ int32_t fill_query_ctx(helios_gpu_system_ctx* ctx, helios_gpu_query* q, cudaStre
   ctx->match.required_mask = q->required_mask;
   ctx->match.without_mask = q->without_mask;
   for (uint32_t k = 0; k < q->desc.n_components; ++k) ctx->match.slots[k] = q->slots[k];
+  ctx->sparse_filter.membership = (q->sparse_require | q->sparse_exclude) ? w->d_membership.as<uint32_t>() : nullptr;
+  ctx->sparse_filter.require = q->sparse_require;
+  ctx->sparse_filter.exclude = q->sparse_exclude;
+  ctx->sparse.dir = w->d_sparse_dir.as<helios_gpu_sparse_dir>();
+  std::memcpy(ctx->sparse.fetch, q->sparse_fetch, sizeof q->sparse_fetch);
   if (want_view || w->tables.size() > HELIOS_GPU_FUSED_MATCH_MAX_TABLES) {
     HG_TRY(query_refresh(q, stream));  // stand-alone match kernel -> materialised view
     ctx->view = q->d_view.as<helios_gpu_query_view>();
@@ -170,7 +196,8 @@ extern "C" {
 int32_t helios_gpu_query_create(helios_gpu_world* w, const helios_gpu_query_desc* d, helios_gpu_query** out) {
   if (!w || !d || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   if (d->n_components > HELIOS_GPU_MAX_QUERY_COMPONENTS || d->n_with > HELIOS_GPU_MAX_COMPONENTS ||
-      d->n_without > HELIOS_GPU_MAX_COMPONENTS)
+      d->n_without > HELIOS_GPU_MAX_COMPONENTS || d->n_sparse_data > HELIOS_GPU_MAX_QUERY_COMPONENTS ||
+      d->sparse_rule > HELIOS_GPU_SPARSE_WITH_ENTITY)
     HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "query descriptor out of range");
   auto q = std::make_unique<helios_gpu_query>();
   q->world = w;
@@ -179,20 +206,42 @@ int32_t helios_gpu_query_create(helios_gpu_world* w, const helios_gpu_query_desc
     const auto it = w->slot_of.find(h);
     return it == w->slot_of.end() ? -1 : it->second;
   };
+  // Sparse-set types pass the archetype match unconditionally (query.hpp:1758-1760,1799-1801); whether they are tested
+  // per entity depends on desc.sparse_rule (helios_gpu.h) — a membership-word test inside for_each_kernel.
+  auto is_sparse = [&](int s) { return (w->sparse_slot_mask >> s & 1ull) != 0; };
+  auto ord_bit = [&](int s) { return 1u << w->sparse_ord_of_slot[s]; };
   for (uint32_t k = 0; k < d->n_components; ++k) {
     const int s = slot(d->components[k]);
     if (s < 0) { q->never_matches = true; q->slots[k] = 0; continue; }  // quirk #9: unregistered ⇒ no match
+    if (is_sparse(s))
+      HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "component %u is sparse-stored: list it in sparse_data, not components", k);
     q->slots[k] = s;
     q->required_mask |= 1ull << s;
+  }
+  for (uint32_t k = 0; k < d->n_sparse_data; ++k) {  // required sparse data: enforced under every rule (iterator.hpp:539-556)
+    const int s = slot(d->sparse_data[k]);
+    if (s < 0) { q->never_matches = true; continue; }
+    if (!is_sparse(s)) HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "sparse_data[%u] is archetype-stored", k);
+    q->sparse_require |= ord_bit(s);
+    q->sparse_fetch[k] = uint8_t(w->sparse_ord_of_slot[s]);
   }
   for (uint32_t k = 0; k < d->n_with; ++k) {
     const int s = slot(d->with[k]);
     if (s < 0) { q->never_matches = true; continue; }
-    q->required_mask |= 1ull << s;
+    if (is_sparse(s)) {
+      if (d->sparse_rule == HELIOS_GPU_SPARSE_STRICT) q->sparse_require |= ord_bit(s);  // quirk #7 otherwise
+    } else {
+      q->required_mask |= 1ull << s;
+    }
   }
   for (uint32_t k = 0; k < d->n_without; ++k) {
     const int s = slot(d->without[k]);
-    if (s >= 0) q->without_mask |= 1ull << s;  // unregistered Without passes (query.hpp:1797-1800)
+    if (s < 0) continue;  // unregistered Without passes (query.hpp:1797-1800)
+    if (is_sparse(s)) {
+      if (d->sparse_rule != HELIOS_GPU_SPARSE_WITH_ENTITY) q->sparse_exclude |= ord_bit(s);  // iterator.hpp:558-577
+    } else {
+      q->without_mask |= 1ull << s;
+    }
   }
   HG_CUDA(w, q->d_view.reserve(sizeof(helios_gpu_query_view), 0, w->stream, false));
   HG_CUDA(w, cudaMemsetAsync(q->d_view.ptr, 0, sizeof(helios_gpu_query_view), w->stream));
@@ -238,6 +287,19 @@ int32_t helios_gpu_query_count(helios_gpu_query* q, uint64_t* out) {
   if (!q || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   helios_gpu_world* w = q->world;
   HG_TRY(query_refresh(q, w->stream));
+  if (q->sparse_require | q->sparse_exclude) {  // Count walks the entities (query.hpp:1652-1666): per-entity sparse test
+    HG_CUDA(w, q->result.reserve(sizeof(helios_gpu_terminal_result), 0, w->stream, false));
+    HG_CUDA(w, cudaMemsetAsync(q->result.ptr, 0, 8, w->stream));
+    const helios_gpu_sparse_filter sf{w->d_membership.as<uint32_t>(), q->sparse_require, q->sparse_exclude};
+    k_count_sparse<<<uint32_t(w->sm_count) * 4, 256, 0, w->stream>>>(q->d_view.as<helios_gpu_query_view>(), sf,
+                                                                      q->result.as<unsigned long long>());
+    ++w->launches;
+    unsigned long long n = 0;
+    HG_CUDA(w, cudaMemcpyAsync(&n, q->result.ptr, 8, cudaMemcpyDeviceToHost, w->stream));
+    HG_CUDA(w, cudaStreamSynchronize(w->stream));
+    *out = n;
+    return HELIOS_GPU_OK;
+  }
   helios_gpu_query_view v;
   HG_CUDA(w, cudaMemcpyAsync(&v, q->d_view.ptr, sizeof(v), cudaMemcpyDeviceToHost, w->stream));
   HG_CUDA(w, cudaStreamSynchronize(w->stream));

@@ -45,6 +45,7 @@ int32_t ensure_entity_capacity(helios_gpu_world* w, uint32_t n) {
   HG_CUDA(w, cudaMemsetAsync(w->d_loc.as<uint64_t>() + old, 0xFF, size_t(cap - old) * 8, w->stream));
   w->ent_capacity = cap;
   ++w->epoch;
+  HG_TRY(sparse_grow_entities(w, old, cap));
   return HELIOS_GPU_OK;
 }
 
@@ -145,6 +146,7 @@ int32_t helios_gpu_world_create(const helios_gpu_world_config* cfg, helios_gpu_w
   if (!out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   *out = nullptr;
   auto* w = new helios_gpu_world();
+  std::memset(w->sparse_ord_of_slot, -1, sizeof w->sparse_ord_of_slot);
   w->device = cfg ? cfg->device : 0;
   cudaError_t e = cudaSetDevice(w->device);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking);
@@ -328,6 +330,8 @@ int32_t helios_gpu_spawn_batch(helios_gpu_world* w, const uint64_t* hashes, uint
     const auto it = w->slot_of.find(hashes[k]);
     if (it == w->slot_of.end()) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "component %016llx not registered", (unsigned long long)hashes[k]);
     if (mask >> it->second & 1) HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "duplicate component type");  // utils::UniqueTypes
+    if (w->sparse_slot_mask >> it->second & 1)
+      HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "spawn_batch takes archetype-stored components; add sparse-set ones with commands");
     mask |= 1ull << it->second;
     slots[k] = it->second;
   }

@@ -35,6 +35,16 @@ struct Table {
   std::vector<DevBuf> cols;   // parallel to `slots`
 };
 
+struct SparseStore {          // one sparse-set component type (component/sparse_storage.hpp, container/sparse_set.hpp)
+  int slot = -1;              // component slot (shared slot space)
+  uint32_t elem = 0;          // value bytes, 0 = tag
+  uint64_t size = 0;          // host mirror of the live element count (exact: apply reads back the event counts)
+  uint64_t capacity = 0;      // dense slots allocated
+  DevBuf sparse;              // uint32_t[ent_capacity]  entity index -> dense slot, 0xFFFFFFFF = absent
+  DevBuf dense;               // elem * capacity bytes
+  DevBuf reverse;             // uint32_t[capacity]      dense slot -> entity index
+};
+
 struct MsgChannel {           // one registered message type: double buffer (message/manager.hpp:549-560)
   uint64_t hash = 0;
   uint32_t size = 0;
@@ -62,8 +72,10 @@ struct helios_gpu_query {
   helios_gpu_world* world = nullptr;
   helios_gpu_query_desc desc{};
   int slots[HELIOS_GPU_MAX_QUERY_COMPONENTS] = {};
-  uint64_t required_mask = 0;   // With ∪ data components
+  uint64_t required_mask = 0;   // With ∪ data components (archetype-stored types only)
   uint64_t without_mask = 0;
+  uint32_t sparse_require = 0, sparse_exclude = 0;  // per-entity membership test (sparse ordinals), after desc.sparse_rule
+  uint8_t sparse_fetch[HELIOS_GPU_MAX_QUERY_COMPONENTS] = {};
   bool never_matches = false;   // an unregistered With/required type (query.hpp:1754-1757, quirk #9)
   hgpu::DevBuf d_view;          // helios_gpu_query_view
   hgpu::DevBuf d_segments;      // helios_gpu_segment[table capacity]
@@ -111,6 +123,15 @@ struct helios_gpu_world {
   int64_t free_cursor = 0;
   uint64_t live_count = 0;     // entity_count_
 
+  // sparse-set storages (sparse.cu), in registration (= ordinal) order
+  std::vector<hgpu::SparseStore> sparse;
+  uint64_t sparse_slot_mask = 0;       // component slots that are sparse-stored
+  int8_t sparse_ord_of_slot[64];       // slot -> ordinal, -1 otherwise
+  hgpu::DevBuf d_membership;           // uint32_t[ent_capacity]
+  hgpu::DevBuf d_sparse_dir;           // helios_gpu_sparse_dir
+  hgpu::DevBuf sp_flags, sp_pos, sp_list, sp_partials, sp_counts;  // scratch of sparse_apply_events
+  uint64_t sparse_replayed_events = 0; // events applied by the sequential replay so far (stats)
+
   hgpu::HostCmdQueue global_queue;   // World::command_queue_
   hgpu::DevBuf staged_cmds, staged_payload;  // device copy of global_queue made by helios_gpu_commands_stage
   uint64_t staged_n = 0;                     // records staged (valid while == global_queue.cmds.size())
@@ -141,6 +162,16 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
 int32_t apply_host_queue(helios_gpu_world* w, HostCmdQueue& q);
 int32_t flush_reserved(helios_gpu_world* w);
 void free_apply_scratch(helios_gpu_world* w);
+// sparse.cu
+int32_t sparse_grow_entities(helios_gpu_world* w, uint32_t old_cap, uint32_t new_cap);  // called by ensure_entity_capacity
+int32_t publish_sparse_dir(helios_gpu_world* w);
+// Applies the sparse-set events the command chains produced (apply.cu k_chain): ev_app/ev_rem/ev_wr[k] = ordinal masks of
+// the storages command k appends to / removes from / writes a value into, ev_mem[k] = the entity's membership after
+// command k (committed where cflags[k] carries `last_flag`); K commands in FIFO order, n_events of them carry events.
+constexpr uint32_t kSparseLastFlag = 8u;
+int32_t sparse_apply_events(helios_gpu_world* w, const helios_gpu_command* d_cmds, const uint8_t* d_payload, uint32_t K,
+                            const uint32_t* cflags, const uint32_t* ev_app, const uint32_t* ev_rem, const uint32_t* ev_wr,
+                            const uint32_t* ev_mem, uint32_t n_events);
 // messages.cu
 int32_t messages_update_from_system(helios_gpu_world* w);   // MessageManager::Update(consumed) manager.hpp:376-398
 int32_t messages_update(helios_gpu_world* w);               // MessageManager::Update()          manager.hpp:400-419

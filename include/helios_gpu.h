@@ -76,6 +76,23 @@ HELIOS_GPU_API uint64_t helios_gpu_world_launch_count(const helios_gpu_world* w)
 HELIOS_GPU_API int32_t helios_gpu_register_component(helios_gpu_world* w, uint64_t type_hash, uint32_t size,
                                                      uint32_t align, const void* default_bytes);
 
+/* ---- sparse-set components (component/sparse_storage.hpp:24-290, container/sparse_set.hpp:529-650; storage rule
+ *      component/component.hpp:118-129: empty "tag" structs and types with kStorageType = kSparseSet) -----------------
+ * A sparse-set component never changes an entity's archetype.  Each type owns {sparse: entity index -> dense slot,
+ * dense: values in insertion order, reverse: dense slot -> entity index}; removal is swap-and-pop, destroying or
+ * clearing an entity removes it from every storage (manager.hpp:1090-1093,1140-1143).  On the device every entity also
+ * carries one 32-bit MEMBERSHIP word (bit = sparse ordinal), which is what query filters read.
+ * size may be 0 (tag).  Shares the slot space of helios_gpu_register_component (so helios_gpu_command::component_mask
+ * and the command payload layout are unchanged); at most HELIOS_GPU_MAX_SPARSE_COMPONENTS sparse types per world.
+ * Returns the slot id (>= 0) or a negative status. */
+#define HELIOS_GPU_MAX_SPARSE_COMPONENTS 32
+HELIOS_GPU_API int32_t helios_gpu_register_sparse_component(helios_gpu_world* w, uint64_t type_hash, uint32_t size,
+                                                            uint32_t align);
+/* SparseComponentStorage::Size / Data() and the sparse set's reverse map, in dense order (parity I/O).
+ * entity_indices / data may be NULL; capacity counts elements. */
+HELIOS_GPU_API int32_t helios_gpu_snapshot_sparse(helios_gpu_world* w, uint64_t type_hash, uint64_t* count,
+                                                  uint32_t* entity_indices, void* data, uint64_t capacity);
+
 /* ---- entities (World::CreateEntity world.hpp:979-984; Commands::Spawn → ReserveEntity
  *      entity/manager.hpp:294-305) ---------------------------------------------------------------- */
 HELIOS_GPU_API int32_t helios_gpu_create_entities(helios_gpu_world* w, uint32_t n, helios_gpu_entity_t* out);
@@ -128,7 +145,24 @@ typedef struct helios_gpu_query_desc {
   uint64_t with[HELIOS_GPU_MAX_COMPONENTS];
   uint32_t n_without;
   uint64_t without[HELIOS_GPU_MAX_COMPONENTS];
+  /* Sparse-set terms.  with[] / without[] may name sparse types; sparse DATA components (`T&`, `const T&` of a sparse
+   * type) are listed here instead of components[]: the body fetches them by entity with helios_gpu::sparse_get
+   * (iterator.hpp:88-100 FetchComponent), index k of this list = fetch ordinal k of helios_gpu_sparse_view.  Pointer
+   * access (`T*`, nullable, not part of the match — iterator.hpp:49-68) is the same fetch without listing the type. */
+  uint32_t n_sparse_data;
+  uint64_t sparse_data[HELIOS_GPU_MAX_QUERY_COMPONENTS];
+  uint32_t sparse_rule; /* HELIOS_GPU_SPARSE_* below */
 } helios_gpu_query_desc;
+/* How sparse terms are applied per entity (archetype matching always lets sparse types through,
+ * query.hpp:1758-1760,1799-1801).  The reference is inconsistent here; all three behaviours exist:
+ *   STRICT       sparse With, Without and data terms all enforced — what TryGetFiltered does (query.hpp:1687-1730);
+ *                the documented fix of the quirk and the default;
+ *   FOREACH      the reference's `for (r : query)` / ForEach / Count: data + Without enforced, With<sparse> ignored
+ *                (iterator.hpp:539-577 with WithoutTypes(), query.hpp:1192-1195,1652-1673);
+ *   WITH_ENTITY  the reference's ForEachWithEntity / Filter / Map ...: data only (query.hpp:1426-1430,1448-1450). */
+#define HELIOS_GPU_SPARSE_STRICT 0u
+#define HELIOS_GPU_SPARSE_FOREACH 1u
+#define HELIOS_GPU_SPARSE_WITH_ENTITY 2u
 
 HELIOS_GPU_API int32_t helios_gpu_query_create(helios_gpu_world* w, const helios_gpu_query_desc* desc,
                                                helios_gpu_query** out);
@@ -271,6 +305,32 @@ typedef struct helios_gpu_world_view {
   uint32_t n_tables;
 } helios_gpu_world_view;
 
+/* Per-entity sparse filter of a launch: a row is visited iff (membership[index] & require) == require and
+ * (membership[index] & exclude) == 0.  membership == NULL: the query has no sparse terms. */
+typedef struct helios_gpu_sparse_filter {
+  const uint32_t* membership; /* [entity index] bit o = member of sparse ordinal o */
+  uint32_t require;
+  uint32_t exclude;
+} helios_gpu_sparse_filter;
+
+/* Device directory of the sparse storages (one struct in HBM, refreshed by the library when a storage grows, so the
+ * pointer stays valid inside captured graphs). */
+typedef struct helios_gpu_sparse_dir {
+  uint32_t* sparse[HELIOS_GPU_MAX_SPARSE_COMPONENTS];  /* [entity index] dense slot or 0xFFFFFFFF */
+  uint8_t* dense[HELIOS_GPU_MAX_SPARSE_COMPONENTS];    /* values, dense order (NULL for tags) */
+  uint32_t* reverse[HELIOS_GPU_MAX_SPARSE_COMPONENTS]; /* [dense slot] entity index */
+  uint32_t elem_size[HELIOS_GPU_MAX_SPARSE_COMPONENTS];
+  uint32_t size[HELIOS_GPU_MAX_SPARSE_COMPONENTS];     /* live elements (device-authoritative) */
+} helios_gpu_sparse_dir;
+
+/* What a body uses to fetch sparse values: fetch[k] = sparse ordinal of desc.sparse_data[k]. */
+typedef struct helios_gpu_sparse_view {
+  const helios_gpu_sparse_dir* dir; /* DEVICE pointer, NULL if the world has no sparse storages */
+  uint8_t fetch[HELIOS_GPU_MAX_QUERY_COMPONENTS];
+} helios_gpu_sparse_view;
+/* Sparse ordinal of a registered sparse type (for `T*` fetches of types not in sparse_data), or negative. */
+HELIOS_GPU_API int32_t helios_gpu_sparse_ordinal(helios_gpu_world* w, uint64_t type_hash);
+
 /* ---- systems and schedules (schedule/schedule.hpp:334-362; src/ecs/src/schedule/schedule.cpp) ---- */
 typedef struct helios_gpu_system_ctx {
   helios_gpu_world* world;
@@ -300,6 +360,9 @@ typedef struct helios_gpu_system_ctx {
    * (ConsumedMessagesRegistry::MarkConsumed, message/consumed_registry.hpp:288-296) */
   uint32_t* consumed;
   uint64_t consumed_capacity;
+  /* sparse-set terms of the query (filter applied by for_each_launch) and the fetch view */
+  helios_gpu_sparse_filter sparse_filter;
+  helios_gpu_sparse_view sparse;
 } helios_gpu_system_ctx;
 #define HELIOS_GPU_RESOURCE_BYTES 4096u
 

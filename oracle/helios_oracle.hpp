@@ -334,13 +334,86 @@ private:
 };
 
 // One component value passed to Add/TryAdd.
+// ------------------------------------------------------------------------------------------------
+// container/sparse_set.hpp:529-650 + component/sparse_storage.hpp:24-290 — one sparse-set component
+// storage, keyed by entity INDEX (the generation is not part of the key): `sparse_[index]` -> dense slot,
+// `dense_` values in insertion order, `reverse_map_[dense]` -> index; Remove is swap-and-pop.
+// ------------------------------------------------------------------------------------------------
+class SparseStorage {
+public:
+  static constexpr uint32_t kInvalidDense = 0xFFFFFFFFu;
+  explicit SparseStorage(uint32_t elem_size = 0) : elem_(elem_size) {}
+
+  bool Contains(uint32_t index) const noexcept { return index < sparse_.size() && sparse_[index] != kInvalidDense; }
+  size_t Size() const noexcept { return reverse_.size(); }
+  uint32_t ElemSize() const noexcept { return elem_; }
+  const std::vector<uint32_t>& ReverseMap() const noexcept { return reverse_; }  // entity index per dense slot
+  const std::vector<uint8_t>& Data() const noexcept { return dense_; }           // SparseComponentStorage::Data()
+  uint32_t DenseIndex(uint32_t index) const noexcept { return Contains(index) ? sparse_[index] : kInvalidDense; }
+
+  // sparse_storage.hpp:121-131 Set: overwrite in place, else SparseSet::Insert (sparse_set.hpp:560-588)
+  void Set(uint32_t index, const void* bytes) {
+    if (Contains(index)) {
+      if (elem_) std::memcpy(&dense_[size_t(sparse_[index]) * elem_], bytes, elem_);
+      return;
+    }
+    if (index >= sparse_.size()) sparse_.resize(size_t(index) + 1, kInvalidDense);
+    sparse_[index] = static_cast<uint32_t>(reverse_.size());
+    if (elem_) dense_.insert(dense_.end(), static_cast<const uint8_t*>(bytes), static_cast<const uint8_t*>(bytes) + elem_);
+    reverse_.push_back(index);
+  }
+  // sparse_storage.hpp:133-143 TrySet: present -> false, value untouched
+  bool TrySet(uint32_t index, const void* bytes) {
+    if (Contains(index)) return false;
+    Set(index, bytes);
+    return true;
+  }
+  // sparse_set.hpp:623-648 Remove: last dense element moves into the hole
+  void Remove(uint32_t index) {
+    assert(Contains(index));
+    const uint32_t d = sparse_[index];
+    const uint32_t last = static_cast<uint32_t>(reverse_.size() - 1);
+    if (d != last) {
+      const uint32_t last_index = reverse_[last];
+      if (elem_) std::memcpy(&dense_[size_t(d) * elem_], &dense_[size_t(last) * elem_], elem_);
+      reverse_[d] = last_index;
+      sparse_[last_index] = d;
+    }
+    if (elem_) dense_.resize(dense_.size() - elem_);
+    reverse_.pop_back();
+    sparse_[index] = kInvalidDense;
+  }
+  // sparse_storage.hpp:110-119
+  bool TryRemove(uint32_t index) {
+    if (!Contains(index)) return false;
+    Remove(index);
+    return true;
+  }
+  // sparse_storage.hpp:229-241 TryGet; tags have no bytes: a non-null sentinel stands for "present"
+  uint8_t* TryGet(uint32_t index) {
+    if (!Contains(index)) return nullptr;
+    return elem_ ? &dense_[size_t(sparse_[index]) * elem_] : reinterpret_cast<uint8_t*>(this);
+  }
+  void Clear() {
+    std::fill(sparse_.begin(), sparse_.end(), kInvalidDense);  // sparse_set.hpp:520-526
+    dense_.clear();
+    reverse_.clear();
+  }
+
+private:
+  uint32_t elem_;
+  std::vector<uint32_t> sparse_;
+  std::vector<uint8_t> dense_;
+  std::vector<uint32_t> reverse_;
+};
+
 struct CompValue {
   TypeIndex type;
   const void* bytes;
 };
 
 // ------------------------------------------------------------------------------------------------
-// component/manager.hpp — archetype-stored components only (sparse sets are §8f "next").
+// component/manager.hpp — archetype tables + sparse-set storages (manager.hpp:114-130).
 // ------------------------------------------------------------------------------------------------
 class ComponentManager {
 public:
@@ -376,6 +449,7 @@ public:
     }
     SetEntityArchetype(e.index, nullptr);
     migrate_bytes += 8 + 8;  // removed entity's location entry + generation read-modify-write (SURVEY §8d cfg 3)
+    PurgeSparse(e);          // manager.hpp:1090-1093 — TryRemove from every sparse storage
   }
   // manager.hpp:1096-1115
   bool TryRemoveEntity(Entity e) {
@@ -396,10 +470,91 @@ public:
       SetEntityArchetype(e.index, empty_archetype_);
       ++structural_version_;
     }
+    PurgeSparse(e);  // manager.hpp:1140-1143
+  }
+
+  // manager.hpp:1379-1406 Add dispatcher: the archetype-stored subset goes through ONE AddArchetypeComponents call, then each
+  // sparse-stored component through AddSparseComponent (manager.hpp:1314-1321 -> SparseComponentStorage::Set).
+  void Add(Entity e, const CompValue* comps, size_t n) {
+    std::vector<CompValue> arch;
+    for (size_t i = 0; i < n; ++i)
+      if (!IsSparse(comps[i].type)) arch.push_back(comps[i]);
+    if (!arch.empty()) AddArchetype(e, arch.data(), arch.size());
+    for (size_t i = 0; i < n; ++i)
+      if (IsSparse(comps[i].type)) {
+        EnsureSparse(comps[i].type).Set(e.index, comps[i].bytes);
+        migrate_bytes += Meta(comps[i].type)->size;
+      }
+  }
+  // manager.hpp:1408-1468 TryAdd dispatcher (results in the caller's argument order).
+  std::vector<bool> TryAdd(Entity e, const CompValue* comps, size_t n) {
+    std::vector<bool> results(n, false);
+    std::vector<CompValue> arch;
+    std::vector<size_t> pos;
+    for (size_t i = 0; i < n; ++i)
+      if (!IsSparse(comps[i].type)) { arch.push_back(comps[i]); pos.push_back(i); }
+    if (!arch.empty()) {
+      const auto r = TryAddArchetype(e, arch.data(), arch.size());
+      for (size_t j = 0; j < pos.size(); ++j) results[pos[j]] = r[j];
+    }
+    for (size_t i = 0; i < n; ++i)
+      if (IsSparse(comps[i].type)) {  // manager.hpp:1323-1331 -> TrySet
+        results[i] = EnsureSparse(comps[i].type).TrySet(e.index, comps[i].bytes);
+        if (results[i]) migrate_bytes += Meta(comps[i].type)->size;
+      }
+    return results;
+  }
+  // manager.hpp:1512-1538 Remove dispatcher.  RemoveSparseComponent asserts presence (manager.hpp:1355-1365); like the
+  // other assert-only paths the oracle (and the GPU path) skip instead, so both sides stay comparable.
+  void Remove(Entity e, const TypeIndex* types, size_t n) {
+    std::vector<TypeIndex> arch;
+    for (size_t i = 0; i < n; ++i)
+      if (!IsSparse(types[i])) arch.push_back(types[i]);
+    if (!arch.empty()) RemoveArchetype(e, arch.data(), arch.size());
+    for (size_t i = 0; i < n; ++i)
+      if (IsSparse(types[i]))
+        if (SparseStorage* st = SparseOf(types[i])) st->TryRemove(e.index);
+  }
+  // manager.hpp:1540-1590 TryRemove dispatcher.
+  std::vector<bool> TryRemove(Entity e, const TypeIndex* types, size_t n) {
+    std::vector<bool> results(n, false);
+    std::vector<TypeIndex> arch;
+    std::vector<size_t> pos;
+    for (size_t i = 0; i < n; ++i)
+      if (!IsSparse(types[i])) { arch.push_back(types[i]); pos.push_back(i); }
+    if (!arch.empty()) {
+      const auto r = TryRemoveArchetype(e, arch.data(), arch.size());
+      for (size_t j = 0; j < pos.size(); ++j) results[pos[j]] = r[j];
+    }
+    for (size_t i = 0; i < n; ++i)
+      if (IsSparse(types[i])) {  // manager.hpp:1367-1377
+        SparseStorage* st = SparseOf(types[i]);
+        results[i] = st != nullptr && st->TryRemove(e.index);
+      }
+    return results;
+  }
+
+  bool IsSparse(TypeIndex t) const {
+    const ComponentMeta* m = Meta(t);
+    return m != nullptr && m->storage == StorageType::kSparseSet;
+  }
+  // manager.hpp:659-667,970-971 EnsureSparseStorage (created on first use)
+  SparseStorage& EnsureSparse(TypeIndex t) {
+    auto it = sparse_.find(t);
+    if (it == sparse_.end()) it = sparse_.emplace(t, SparseStorage(Meta(t) ? Meta(t)->size : 0)).first;
+    return it->second;
+  }
+  SparseStorage* SparseOf(TypeIndex t) {
+    const auto it = sparse_.find(t);
+    return it == sparse_.end() ? nullptr : &it->second;
+  }
+  const SparseStorage* SparseOf(TypeIndex t) const {
+    const auto it = sparse_.find(t);
+    return it == sparse_.end() ? nullptr : &it->second;
   }
 
   // manager.hpp:1146-1203 AddArchetypeComponents — quirk #3: overwrite existing in SOURCE first.
-  void Add(Entity e, const CompValue* comps, size_t n) {
+  void AddArchetype(Entity e, const CompValue* comps, size_t n) {
     Archetype& current = *EntityArchetype(e);
     std::vector<bool> added(n);
     ArchetypeId target_id = current.Id();
@@ -421,7 +576,7 @@ public:
   }
 
   // manager.hpp:1205-1248 TryAddArchetypeComponents — existing components untouched.
-  std::vector<bool> TryAdd(Entity e, const CompValue* comps, size_t n) {
+  std::vector<bool> TryAddArchetype(Entity e, const CompValue* comps, size_t n) {
     Archetype& current = *EntityArchetype(e);
     std::vector<bool> results(n);
     ArchetypeId target_id = current.Id();
@@ -443,7 +598,7 @@ public:
 
   // manager.hpp:1268-1287 RemoveArchetypeComponents (the reference does not assert presence here;
   // Without() of an absent type is the identity, archetype_id.hpp:245-248).
-  void Remove(Entity e, const TypeIndex* types, size_t n) {
+  void RemoveArchetype(Entity e, const TypeIndex* types, size_t n) {
     Archetype& current = *EntityArchetype(e);
     ArchetypeId target_id = current.Id();
     for (size_t i = 0; i < n; ++i) target_id = target_id.Without(types[i]);
@@ -454,20 +609,29 @@ public:
     }
   }
   // manager.hpp:1289-1312
-  std::vector<bool> TryRemove(Entity e, const TypeIndex* types, size_t n) {
+  std::vector<bool> TryRemoveArchetype(Entity e, const TypeIndex* types, size_t n) {
     Archetype& current = *EntityArchetype(e);
     std::vector<bool> results(n);
     for (size_t i = 0; i < n; ++i) results[i] = current.HasColumn(types[i]);
-    Remove(e, types, n);
+    RemoveArchetype(e, types, n);
     return results;
   }
 
+  // manager.hpp:623-636 Has — sparse types are looked up in their storage
   bool Has(Entity e, TypeIndex t) const {
+    if (IsSparse(t)) {
+      const SparseStorage* st = SparseOf(t);
+      return st != nullptr && st->Contains(e.index);
+    }
     const Archetype* a = EntityArchetype(e);
     return a != nullptr && a->HasColumn(t);
   }
   // manager.hpp:1613-1635 (Get) — returns pointer to the component bytes or nullptr.
   uint8_t* Get(Entity e, TypeIndex t) {
+    if (IsSparse(t)) {
+      SparseStorage* st = SparseOf(t);
+      return st ? st->TryGet(e.index) : nullptr;
+    }
     Archetype* a = EntityArchetype(e);
     if (a == nullptr) return nullptr;
     const int c = a->ColumnIndex(t);
@@ -505,6 +669,7 @@ public:
     archetype_map_.clear();
     archetype_list_.clear();
     storage_.clear();
+    sparse_.clear();
     metadata_.clear();
     empty_archetype_ = nullptr;
     structural_version_ = 0;
@@ -551,12 +716,17 @@ private:
     ++structural_version_;
   }
 
+  void PurgeSparse(Entity e) {
+    for (auto& kv : sparse_) kv.second.TryRemove(e.index);
+  }
+
   void SetEntityArchetype(uint32_t idx, Archetype* a) {
     if (idx >= entity_archetype_.size()) entity_archetype_.resize(std::max<size_t>(idx + 1, entity_archetype_.size() * 2), nullptr);
     entity_archetype_[idx] = a;
   }
 
   std::unordered_map<TypeIndex, ComponentMeta> metadata_;
+  std::unordered_map<TypeIndex, SparseStorage> sparse_;  // manager.hpp:885-886,1017 SparseStorageMap
   std::deque<Archetype> storage_;
   std::unordered_map<uint64_t, Archetype*> archetype_map_;
   std::vector<Archetype*> archetype_list_;
@@ -573,7 +743,38 @@ struct QueryDesc {
   std::vector<uint8_t> writes;      // per required component: 1 = mutable access (T& / T*), 0 = const
   std::vector<TypeIndex> with;
   std::vector<TypeIndex> without;
+  std::vector<TypeIndex> optional;  // pointer access `T*` / `const T*`: not part of the match, null when absent
+  // How sparse-set types in with / without / required are treated per ENTITY (archetype matching always lets them
+  // through, query.hpp:1758-1760,1799-1801):
+  //   kStrict     every sparse With / Without / required-data type is enforced — TryGetFiltered's rule
+  //               (query.hpp:1687-1730 EntityPassesFilters / EntityPassesExclusions) applied to iteration: the
+  //               documented FIX of quirk #7;
+  //   kForEach    what `for (auto&& r : query)`, ForEach and Count do (begin/end built with WithoutTypes(),
+  //               query.hpp:1192-1195,1652-1673): required sparse data + sparse Without enforced
+  //               (iterator.hpp:539-577), sparse With<> NOT enforced;
+  //   kWithEntity what ForEachWithEntity / Filter / Map / ... do (iterators built without WithoutTypes(),
+  //               query.hpp:1426-1430,1448-1450): required sparse data only.
+  enum class SparseRule : uint8_t { kStrict = 0, kForEach = 1, kWithEntity = 2 };
+  SparseRule sparse_rule = SparseRule::kStrict;
 };
+
+inline bool EntityPassesSparse(const ComponentManager& cm, const QueryDesc& q, Entity e) {
+  for (const TypeIndex t : q.required)
+    if (cm.IsSparse(t) && !cm.Has(e, t)) return false;
+  if (q.sparse_rule != QueryDesc::SparseRule::kWithEntity)
+    for (const TypeIndex t : q.without)
+      if (cm.IsSparse(t) && cm.Has(e, t)) return false;
+  if (q.sparse_rule == QueryDesc::SparseRule::kStrict)
+    for (const TypeIndex t : q.with)
+      if (cm.IsSparse(t) && !cm.Has(e, t)) return false;
+  return true;
+}
+inline bool QueryHasSparseTerms(const ComponentManager& cm, const QueryDesc& q) {
+  for (const auto* v : {&q.required, &q.with, &q.without})
+    for (const TypeIndex t : *v)
+      if (cm.IsSparse(t)) return true;
+  return false;
+}
 
 // Returns indices into ComponentManager::Archetypes() (creation order), non-empty tables only.
 inline std::vector<uint32_t> MatchArchetypes(const ComponentManager& cm, const QueryDesc& q) {
@@ -609,7 +810,12 @@ inline std::vector<uint32_t> MatchArchetypes(const ComponentManager& cm, const Q
 // query.hpp:1652-1666 Count — walks the matched tables.
 inline uint64_t QueryCount(const ComponentManager& cm, const QueryDesc& q) {
   uint64_t n = 0;
-  for (const uint32_t i : MatchArchetypes(cm, q)) n += cm.Archetypes()[i]->EntityCount();
+  const bool sparse = QueryHasSparseTerms(cm, q);
+  for (const uint32_t i : MatchArchetypes(cm, q)) {
+    const Archetype& a = *cm.Archetypes()[i];
+    if (!sparse) { n += a.EntityCount(); continue; }
+    for (const Entity e : a.Entities()) n += EntityPassesSparse(cm, q, e) ? 1 : 0;
+  }
   return n;
 }
 
@@ -618,15 +824,22 @@ inline uint64_t QueryCount(const ComponentManager& cm, const QueryDesc& q) {
 // This is the direct column-span form (B-opt access path, archetype.hpp:578-602).
 template <typename Body>
 inline void ForEach(ComponentManager& cm, const QueryDesc& q, Body&& body) {
-  std::vector<uint8_t*> ptrs(q.required.size());
+  // ptrs = one pointer per required component, then one per optional (`T*`) component (null when absent,
+  // iterator.hpp:49-68 FetchComponent pointer access)
+  std::vector<uint8_t*> ptrs(q.required.size() + q.optional.size());
+  const bool sparse = QueryHasSparseTerms(cm, q);
   for (const uint32_t i : MatchArchetypes(cm, q)) {
     Archetype& a = *cm.Archetypes()[i];
     std::vector<int> cols(q.required.size());
-    for (size_t k = 0; k < q.required.size(); ++k) cols[k] = a.ColumnIndex(q.required[k]);
+    for (size_t k = 0; k < q.required.size(); ++k) cols[k] = cm.IsSparse(q.required[k]) ? -1 : a.ColumnIndex(q.required[k]);
     const size_t n = a.EntityCount();
     for (size_t r = 0; r < n; ++r) {
-      for (size_t k = 0; k < cols.size(); ++k) ptrs[k] = &a.ColumnBytes(cols[k])[r * a.ElemSize(cols[k])];
-      body(a.Entities()[r], ptrs.data());
+      const Entity e = a.Entities()[r];
+      if (sparse && !EntityPassesSparse(cm, q, e)) continue;  // iterator.hpp:530-585 AdvanceToValidEntity
+      for (size_t k = 0; k < cols.size(); ++k)
+        ptrs[k] = cols[k] >= 0 ? &a.ColumnBytes(cols[k])[r * a.ElemSize(cols[k])] : cm.Get(e, q.required[k]);
+      for (size_t k = 0; k < q.optional.size(); ++k) ptrs[q.required.size() + k] = cm.Get(e, q.optional[k]);
+      body(e, ptrs.data());
     }
   }
 }

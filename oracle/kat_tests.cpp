@@ -13,6 +13,8 @@
 
 #include "helios_oracle.hpp"
 
+#pragma GCC diagnostic ignored "-Wmissing-field-initializers"  // QueryDesc{...} with defaulted tail members
+
 using namespace helios_oracle;
 
 static int g_checks = 0, g_fail = 0;
@@ -466,6 +468,254 @@ void TestCommands() {
 }
 
 // ---- message/manager.cpp:215-335 Update(consumed) / ApplyConsumed; consumed_registry.cpp MarkConsumed ----------------------
+// ---- sparse-set components: component/sparse_storage.cpp, container/tests/sparse_set.cpp, component/manager.cpp:529-1115,
+// ---- query/query.cpp:1140-1215,2137-2155 ------------------------------------------------------------------------------
+struct SparseBuff { int stacks = 0; };
+struct SparseFlag { int value = 0; };
+const TypeIndex kSPos = Fnv1a("SparsePosition"), kSVel = Fnv1a("SparseVelocity"), kSHealth = Fnv1a("SparseHealth"),
+                kBuff = Fnv1a("SparseBuff"), kFlag = Fnv1a("SparseFlag"), kTag = Fnv1a("PlayerTag");
+template <typename T>
+ComponentMeta SparseMetaOf(TypeIndex t) {
+  ComponentMeta m = MetaOf<T>(t);
+  m.storage = StorageType::kSparseSet;
+  return m;
+}
+void RegisterSparse(ComponentManager& m) {
+  m.Register(SparseMetaOf<Position>(kSPos));
+  m.Register(SparseMetaOf<Velocity>(kSVel));
+  m.Register(SparseMetaOf<Health>(kSHealth));
+  m.Register(SparseMetaOf<SparseBuff>(kBuff));
+  m.Register(SparseMetaOf<SparseFlag>(kFlag));
+  ComponentMeta tag;  // empty struct: tag component, sparse by default (component.hpp:118-129)
+  tag.type = kTag;
+  tag.size = 0;
+  tag.storage = StorageType::kSparseSet;
+  m.Register(tag);
+}
+
+void TestSparseSets() {
+  auto pos_at = [](const SparseStorage& st, uint32_t index) {
+    Position p;
+    std::memcpy(&p, &st.Data()[size_t(st.DenseIndex(index)) * sizeof(Position)], sizeof p);
+    return p;
+  };
+  {
+    SparseStorage st(sizeof(Position));  // sparse_storage.cpp:71-105 Remove / :138-189 Set
+    const Position p1{1, 0}, p2{2, 0};
+    st.Set(1, &p1);
+    CHECK(st.Size() == 1 && st.Contains(1));
+    st.Set(2, &p2);
+    st.Remove(1);
+    CHECK(!st.Contains(1) && st.Contains(2) && st.Size() == 1);
+    CHECK(pos_at(st, 2).x == 2.0f);
+    const Position p9{9, 9};
+    st.Set(2, &p9);  // :161-177 repeated Set replaces, size unchanged
+    CHECK(st.Size() == 1 && pos_at(st, 2).x == 9.0f);
+  }
+  {
+    SparseStorage st(sizeof(Position));  // sparse_storage.cpp:107-136 TryRemove, :191-232 TrySet
+    const Position p1{1, 2}, p2{3, 4};
+    CHECK(st.TrySet(1, &p1));
+    CHECK(!st.TrySet(1, &p2));
+    CHECK(pos_at(st, 1).x == 1.0f && st.Size() == 1);
+    CHECK(!st.TryRemove(7));
+    CHECK(st.Size() == 1);
+    CHECK(st.TryRemove(1));
+    CHECK(st.Size() == 0 && st.TryGet(1) == nullptr);  // :406-414
+  }
+  {
+    SparseStorage st(sizeof(int));  // container/tests/sparse_set.cpp:228-262 basic removal + swap-and-pop order
+    for (int i = 1; i <= 5; ++i) { const int v = i * 100; st.Set(uint32_t(i * 10), &v); }
+    st.Remove(30);  // middle: the last (50) fills the hole
+    CHECK(st.Size() == 4 && !st.Contains(30) && st.Contains(10) && st.Contains(20) && st.Contains(40) && st.Contains(50));
+    CHECK((st.ReverseMap() == std::vector<uint32_t>{10, 20, 50, 40}));
+    st.Remove(10);  // first: 40 moves to slot 0
+    CHECK((st.ReverseMap() == std::vector<uint32_t>{40, 20, 50}));
+    st.Remove(50);  // last in the dense array: plain pop
+    CHECK((st.ReverseMap() == std::vector<uint32_t>{40, 20}));
+    int v = 0;
+    std::memcpy(&v, st.TryGet(20), 4);
+    CHECK(v == 200);
+    st.Clear();  // sparse_storage.cpp:28-69
+    CHECK(st.Size() == 0 && !st.Contains(20) && st.Data().empty());
+    const int w = 7;
+    st.Set(20, &w);
+    CHECK(st.Size() == 1 && st.DenseIndex(20) == 0);
+  }
+  const Entity e{1, 0};
+  {
+    ComponentManager m;  // manager.cpp:529-570 AddSparseComponent, :572-598 TryAddSparseComponent
+    RegisterAll(m);
+    RegisterSparse(m);
+    m.InitEntity(e);
+    const Position pos{1, 2}, nine{9, 9};
+    const CompValue c9{kSPos, &nine}, c{kSPos, &pos};
+    m.Add(e, &c9, 1);
+    m.Add(e, &c, 1);  // :551-559 overwrite
+    CHECK(m.Has(e, kSPos) && GetAs<Position>(m, e, kSPos).x == 1.0f && m.SparseOf(kSPos)->Size() == 1);
+    CHECK(m.Archetypes().size() == 1);  // sparse adds never create archetypes
+    CHECK(!m.TryAdd(e, &c9, 1)[0]);
+    CHECK(GetAs<Position>(m, e, kSPos).x == 1.0f);
+    const TypeIndex t = kSPos;
+    CHECK(m.TryRemove(e, &t, 1)[0]);   // :672-695
+    CHECK(!m.TryRemove(e, &t, 1)[0]);
+    CHECK(!m.Has(e, kSPos));
+  }
+  {
+    ComponentManager m;  // manager.cpp:728-742 Add mixed; :812-828 TryAdd mixed
+    RegisterAll(m);
+    RegisterSparse(m);
+    m.InitEntity(e);
+    const Position pos{2, 4};
+    const Velocity vel{1, 3}, zero{};
+    const CompValue mixed[2] = {{kPos, &pos}, {kSVel, &vel}};
+    m.Add(e, mixed, 2);
+    CHECK(GetAs<Position>(m, e, kPos).x == 2.0f && GetAs<Velocity>(m, e, kSVel).y == 3.0f);
+    CHECK(m.Archetypes().size() == 2 && m.SparseOf(kSVel)->Size() == 1);
+    ComponentManager m2;
+    RegisterAll(m2);
+    RegisterSparse(m2);
+    m2.InitEntity(e);
+    const CompValue z{kSVel, &zero};
+    m2.Add(e, &z, 1);
+    const auto added = m2.TryAdd(e, mixed, 2);
+    CHECK(added[0] && !added[1]);
+    CHECK(GetAs<Velocity>(m2, e, kSVel).x == 0.0f && m2.Archetypes().size() == 2 && m2.SparseOf(kSVel)->Size() == 1);
+  }
+  {
+    ComponentManager m;  // manager.cpp:1006-1028 Remove sparse / mixed; :1074-1098 TryRemove result positions
+    RegisterAll(m);
+    RegisterSparse(m);
+    m.InitEntity(e);
+    const Position p{};
+    const Velocity v{};
+    const Health h{};
+    const CompValue all3[3] = {{kSPos, &p}, {kSVel, &v}, {kSHealth, &h}};
+    m.Add(e, all3, 3);
+    const TypeIndex two[2] = {kSPos, kSHealth};
+    m.Remove(e, two, 2);
+    CHECK(!m.Has(e, kSPos) && m.Has(e, kSVel) && !m.Has(e, kSHealth));
+    const CompValue cp{kPos, &p};
+    m.Add(e, &cp, 1);
+    const TypeIndex sv_first[2] = {kSHealth, kPos};
+    const auto r = m.TryRemove(e, sv_first, 2);
+    CHECK(!r[0] && r[1] && !m.Has(e, kPos));
+    // manager.cpp RemoveEntity / Clear: the entity leaves every sparse storage (manager.hpp:1090-1093,1140-1143)
+    m.Clear(e);
+    CHECK(!m.Has(e, kSVel) && m.SparseOf(kSVel)->Size() == 0);
+    m.Add(e, all3, 3);
+    m.RemoveEntity(e);
+    CHECK(m.SparseOf(kSPos)->Size() == 0 && m.SparseOf(kSVel)->Size() == 0 && m.SparseOf(kSHealth)->Size() == 0);
+  }
+  {
+    // query/query.cpp:1140-1215 (Get / TryGet / TryGetFiltered with sparse terms) and :2137-2155
+    World w;
+    RegisterAll(w.components);
+    RegisterSparse(w.components);
+    auto spawn = [&](uint32_t idx, float x, bool vel, bool health) {
+      const Entity en{idx, 0};  // the reference test drives the ComponentManager directly with literal ids
+      w.components.InitEntity(en);
+      const Position p{x, 0};
+      const Velocity v{};
+      const Health h{};
+      std::vector<CompValue> cv{{kPos, &p}};
+      if (vel) cv.push_back({kVel, &v});
+      if (health) cv.push_back({kHealth, &h});
+      w.components.Add(en, cv.data(), cv.size());
+      return en;
+    };
+    spawn(1, 1.0f, true, false);
+    spawn(2, 2.0f, true, true);
+    const Entity e3 = spawn(3, 3.0f, true, true);
+    const SparseFlag fl{};
+    const CompValue cf{kFlag, &fl};
+    w.components.Add(e3, &cf, 1);
+    QueryDesc q;  // Query<const Position&, With<Velocity, Health>, Without<SparseFlag>>
+    q.required = {kPos};
+    q.writes = {0};
+    q.with = {kVel, kHealth};
+    q.without = {kFlag};
+    q.sparse_rule = QueryDesc::SparseRule::kForEach;
+    CHECK(QueryCount(w.components, q) == 1);  // :2150
+    float sum = 0;
+    ForEach(w.components, q, [&](Entity, uint8_t** p) { sum += reinterpret_cast<Position*>(p[0])->x; });
+    CHECK(sum == 2.0f);  // :2152-2154
+    q.sparse_rule = QueryDesc::SparseRule::kWithEntity;  // query.hpp:1426-1430: no WithoutTypes() => the flag is not seen
+    sum = 0;
+    ForEach(w.components, q, [&](Entity, uint8_t** p) { sum += reinterpret_cast<Position*>(p[0])->x; });
+    CHECK(sum == 5.0f);
+    // :1188-1215 TryGetFiltered applies sparse With and Without per entity == kStrict
+    QueryDesc qw;
+    qw.required = {kPos};
+    qw.writes = {0};
+    qw.with = {kBuff};
+    const Entity e13 = spawn(13, 0, false, false), e14 = spawn(14, 0, false, false);
+    const SparseBuff b{1};
+    const CompValue cb{kBuff, &b};
+    w.components.Add(e14, &cb, 1);
+    CHECK(!EntityPassesSparse(w.components, qw, e13));
+    CHECK(EntityPassesSparse(w.components, qw, e14));
+    qw.sparse_rule = QueryDesc::SparseRule::kForEach;  // quirk #7: iteration does not enforce With<sparse>
+    CHECK(EntityPassesSparse(w.components, qw, e13));
+    CHECK(QueryCount(w.components, qw) == 5);
+    qw.sparse_rule = QueryDesc::SparseRule::kStrict;
+    CHECK(QueryCount(w.components, qw) == 1);
+    // :1141-1153 Get<const Position&, const SparseBuff&>: archetype + sparse data in one row; `T*` access is nullable
+    QueryDesc qd;
+    qd.required = {kPos, kBuff};
+    qd.writes = {0, 0};
+    int seen = 0, stacks = 0;
+    ForEach(w.components, qd, [&](Entity en, uint8_t** p) {
+      ++seen;
+      stacks = reinterpret_cast<SparseBuff*>(p[1])->stacks;
+      CHECK(en == e14);
+    });
+    CHECK(seen == 1 && stacks == 1);
+    QueryDesc qo;
+    qo.required = {kPos};
+    qo.writes = {0};
+    qo.optional = {kBuff};
+    int nulls = 0, present = 0;
+    ForEach(w.components, qo, [&](Entity, uint8_t** p) { (p[1] ? present : nulls)++; });
+    CHECK(present == 1 && nulls == 4);
+  }
+  {
+    // Commands on sparse components (builtin_commands.hpp:250-312,430-478 call World::AddComponents / RemoveComponents with
+    // whatever storage the types have): dense order after interleaved adds, removes and destroys
+    World w;
+    RegisterAll(w.components);
+    RegisterSparse(w.components);
+    std::vector<Entity> es;
+    for (int i = 0; i < 6; ++i) es.push_back(w.CreateEntity());
+    auto add = [&](Entity en, TypeIndex t, const void* bytes, uint32_t size, bool try_) {
+      Command c;
+      c.kind = try_ ? CmdKind::kTryAdd : CmdKind::kAdd;
+      c.entity = en;
+      c.types = {t};
+      c.values = {std::vector<uint8_t>(static_cast<const uint8_t*>(bytes), static_cast<const uint8_t*>(bytes) + size)};
+      w.command_queue.Enqueue(std::move(c));
+    };
+    for (int i = 0; i < 6; ++i) { const SparseBuff b{i + 10}; add(es[size_t(i)], kBuff, &b, 4, false); add(es[size_t(i)], kTag, nullptr, 0, false); }
+    Command rm; rm.kind = CmdKind::kRemove; rm.entity = es[1]; rm.types = {kBuff};
+    w.command_queue.Enqueue(rm);
+    Command ds; ds.kind = CmdKind::kDestroy; ds.entity = es[0];
+    w.command_queue.Enqueue(ds);
+    const SparseBuff again{77};
+    add(es[1], kBuff, &again, 4, true);
+    add(es[2], kBuff, &again, 4, true);  // present: TryAdd leaves 12
+    w.Flush();
+    const SparseStorage& st = *w.components.SparseOf(kBuff);
+    // appends 0..5; remove idx1 -> [0,5,2,3,4]; destroy idx0 -> [4,5,2,3]; re-add idx1 -> [4,5,2,3,1]
+    CHECK((st.ReverseMap() == std::vector<uint32_t>{4, 5, 2, 3, 1}));
+    int v[5];
+    std::memcpy(v, st.Data().data(), sizeof v);
+    CHECK(v[0] == 14 && v[1] == 15 && v[2] == 12 && v[3] == 13 && v[4] == 77);
+    // the tag storage saw 6 appends and the destroy of idx0: [5,1,2,3,4]
+    CHECK((w.components.SparseOf(kTag)->ReverseMap() == std::vector<uint32_t>{5, 1, 2, 3, 4}));
+    CHECK(w.components.SparseOf(kTag)->Data().empty());
+  }
+}
+
 void TestConsumedMessages() {
   const TypeIndex kMsg = Fnv1a("PositionMsg");
   auto x_of = [&](const MessageQueue& q, size_t i) {
@@ -795,6 +1045,7 @@ int main() {
   TestQuery();
   TestCommands();
   TestMessages();
+  TestSparseSets();
   TestConsumedMessages();
   TestScheduling();
   TestApplyOrder();

@@ -152,6 +152,20 @@ int32_t sys_regen(const OCtx* c) {
   });
   return 0;
 }
+int32_t sys_buff_heal(const OCtx* c) {  // required = {Health, SparseBuff}: p[1] comes from the sparse storage
+  visit(c, [](ho::Entity, uint8_t** p) { *reinterpret_cast<int32_t*>(p[0]) += *reinterpret_cast<const int32_t*>(p[1]); });
+  return 0;
+}
+int32_t sys_buff_optional(const OCtx* c) {  // `const SparseBuff*`: TryGet by entity, null when absent (iterator.hpp:49-68)
+  uint64_t hash;
+  std::memcpy(&hash, c->params, 8);
+  auto& cm = c->world->world.components;
+  visit(c, [&](ho::Entity e, uint8_t** p) {
+    const uint8_t* b = cm.Get(e, hash);
+    *reinterpret_cast<int32_t*>(p[0]) += b ? *reinterpret_cast<const int32_t*>(b) : -1;
+  });
+  return 0;
+}
 int32_t sys_team_tint(const OCtx* c) {
   visit(c, [](ho::Entity, uint8_t** p) {
     const uint32_t team = *reinterpret_cast<const uint32_t*>(p[0]);
@@ -261,6 +275,7 @@ const Builtin kBuiltins[] = {
     {"regen", sys_regen},         {"team_tint", sys_team_tint},             {"detect", sys_detect},
     {"detect_sparse", sys_detect_sparse}, {"consume", sys_consume}, {"consume_strong", sys_consume_strong},         {"stats", sys_stats},
     {"exit_check", sys_exit_check}, {"despawn_dead", sys_despawn_dead},
+    {"buff_heal", sys_buff_heal}, {"buff_optional", sys_buff_optional},
 };
 
 // helios_gpu_command → oracle Command (payload: ascending slot order, each value padded to 4 bytes).
@@ -274,7 +289,8 @@ ho::Command to_command(OWorld* w, const helios_gpu_command& c, const uint8_t* pa
     out.types.push_back(w->slot_hash[s]);
     if (c.kind == HELIOS_GPU_CMD_ADD || c.kind == HELIOS_GPU_CMD_TRY_ADD) {
       const uint32_t sz = w->world.components.Meta(w->slot_hash[s])->size;
-      out.values.emplace_back(payload + off, payload + off + sz);
+      if (sz) out.values.emplace_back(payload + off, payload + off + sz);
+      else out.values.emplace_back();  // tag: no bytes
       off += (sz + 3u) & ~3u;
     }
   }
@@ -321,6 +337,30 @@ HO_API int32_t helios_oracle_register_component(void* wp, uint64_t hash, uint32_
   w->world.components.Register(m);
   w->slot_hash.push_back(hash);
   return int32_t(w->slot_hash.size() - 1);
+}
+
+// component/component.hpp:118-129: tags and kStorageType = kSparseSet types live in SparseComponentStorage<T>.
+HO_API int32_t helios_oracle_register_sparse_component(void* wp, uint64_t hash, uint32_t size, uint32_t align) {
+  OWorld* w = W(wp);
+  for (size_t s = 0; s < w->slot_hash.size(); ++s)
+    if (w->slot_hash[s] == hash) return int32_t(s);
+  ho::ComponentMeta m;
+  m.type = hash;
+  m.size = size;
+  m.align = align;
+  m.storage = ho::StorageType::kSparseSet;
+  w->world.components.Register(m);
+  w->slot_hash.push_back(hash);
+  return int32_t(w->slot_hash.size() - 1);
+}
+HO_API int32_t helios_oracle_snapshot_sparse(void* wp, uint64_t hash, uint64_t* count, uint32_t* indices, void* data, uint64_t cap) {
+  const ho::SparseStorage* st = W(wp)->world.components.SparseOf(hash);
+  const uint64_t n = st ? st->Size() : 0;
+  if (count) *count = n;
+  if ((indices || data) && cap < n) return HELIOS_GPU_ERR_CAPACITY;
+  if (st && indices) std::copy(st->ReverseMap().begin(), st->ReverseMap().end(), indices);
+  if (st && data && !st->Data().empty()) std::memcpy(data, st->Data().data(), st->Data().size());
+  return 0;
 }
 
 HO_API int32_t helios_oracle_create_entities(void* wp, uint32_t n, helios_gpu_entity_t* out) {
@@ -426,8 +466,13 @@ HO_API int32_t helios_oracle_query_create(void* wp, const helios_gpu_query_desc*
     q->desc.required.push_back(d->components[k]);
     q->desc.writes.push_back(d->writes[k]);
   }
+  for (uint32_t k = 0; k < d->n_sparse_data; ++k) {  // sparse data components: required, fetched from their storage
+    q->desc.required.push_back(d->sparse_data[k]);
+    q->desc.writes.push_back(0);
+  }
   q->desc.with.assign(d->with, d->with + d->n_with);
   q->desc.without.assign(d->without, d->without + d->n_without);
+  q->desc.sparse_rule = static_cast<ho::QueryDesc::SparseRule>(d->sparse_rule);
   *out = q.get();
   W(wp)->queries.push_back(std::move(q));
   return 0;

@@ -164,6 +164,99 @@ def churn_small(backend, seed=3, frames=4):
     return out
 
 
+SPARSE_TYPES = {"PlayerTag": 0, "FrozenTag": 0, "SparseBuff": 4, "SparseVelocity": 8}
+
+
+def sparse_world(backend, rows=(37, 21, 12), entity_capacity=0):
+    """Archetype tables {Position, Health}, {Position, Health, Team}, {Health} plus four sparse-set types (two tags)."""
+    w = capi.World(backend, entity_capacity=entity_capacity)
+    worlds.register_all(w, ["Position", "Health", "Team"])
+    for name, size in SPARSE_TYPES.items():
+        w.register_sparse_component(worlds.cname(name), size)
+    tables = [["Position", "Health"], ["Position", "Health", "Team"], ["Health"]]
+    for i, (sh, n) in enumerate(zip(tables, rows)):
+        w.spawn_batch([worlds.cname(x) for x in sh], n, [worlds.column(x, n, 700 + 8 * i + k) for k, x in enumerate(sh)])
+    return w
+
+
+def sparse_commands(w, rng, pool, n_cmd, stale, arch_shorts=("Team", "Position"), allow_destroy=True):
+    """Random records over archetype AND sparse components: Add / TryAdd / Remove / TryRemove / Clear / Destroy."""
+    cmds = np.zeros(n_cmd, dtype=capi.COMMAND_DTYPE)
+    payload = bytearray()
+    names = list(SPARSE_TYPES) + list(arch_shorts)
+    sizes = {**SPARSE_TYPES, **{x: worlds.COMPONENTS[x][0] for x in arch_shorts}}
+    dead = set(stale)
+    for i in range(n_cmd):
+        ent = int(pool[rng.integers(0, pool.size)])
+        kinds = [capi.CMD_TRY_ADD, capi.CMD_TRY_ADD, capi.CMD_ADD, capi.CMD_TRY_REMOVE, capi.CMD_REMOVE, capi.CMD_CLEAR]
+        if allow_destroy:
+            kinds.append(capi.CMD_TRY_DESTROY)
+        kind = int(rng.choice(kinds))
+        if ent in dead and kind in (capi.CMD_ADD, capi.CMD_REMOVE, capi.CMD_CLEAR):
+            kind = capi.CMD_TRY_REMOVE  # the non-Try forms assert on dead entities in the reference
+        k = int(rng.integers(1, 4))
+        sh = list(rng.choice(names, size=k, replace=False)) if kind not in (capi.CMD_CLEAR, capi.CMD_TRY_DESTROY) else []
+        cmds[i]["kind"] = kind
+        cmds[i]["entity"] = ent
+        cmds[i]["component_mask"] = w.mask(worlds.cname(x) for x in sh)
+        cmds[i]["payload_offset"] = len(payload)
+        if kind in (capi.CMD_ADD, capi.CMD_TRY_ADD):
+            for x in sorted(sh, key=lambda y: w.slots[worlds.cname(y)]):
+                if sizes[x]:
+                    payload += rng.integers(1, 90, size=sizes[x] // 4, dtype=np.uint32).tobytes()
+        if kind == capi.CMD_TRY_DESTROY:
+            stale.append(ent)
+            dead.add(ent)
+    return cmds, bytes(payload)
+
+
+def sparse_state(w):
+    """Digest of the archetype snapshot plus every sparse storage in dense order (reverse map + value bytes)."""
+    parts = [snapshot_digest(w.snapshot())]
+    for name in SPARSE_TYPES:
+        sp = w.snapshot_sparse(worlds.cname(name))
+        parts.append(_bytes_digest(sp["indices"], sp["data"]))
+    return parts
+
+
+def sparse_sets(backend, seed=11, frames=4, n_cmd=90, mode=capi.EXEC_SERIAL):
+    """Sparse-set components end to end: deferred commands over tags and sparse data (dense order after swap-and-pop),
+    Destroy / Clear purging every storage, queries with sparse With / Without / data terms under the three rules of
+    helios_gpu_query_desc::sparse_rule, a nullable `T*` fetch, and systems running behind those filters."""
+    w = sparse_world(backend)
+    P, H, T = (worlds.cname(x) for x in ("Position", "Health", "Team"))
+    TAG, FROZEN, BUFF = (worlds.cname(x) for x in ("PlayerTag", "FrozenTag", "SparseBuff"))
+    queries = {}
+    for rule in (capi.SPARSE_STRICT, capi.SPARSE_FOREACH, capi.SPARSE_WITH_ENTITY):
+        queries[f"with_tag_r{rule}"] = w.query([(H, False)], with_=[TAG], sparse_rule=rule)
+        queries[f"without_frozen_r{rule}"] = w.query([(H, False)], with_=[P], without=[FROZEN], sparse_rule=rule)
+        queries[f"tag_not_frozen_buff_r{rule}"] = w.query([(H, False)], with_=[TAG], without=[FROZEN, T], sparse_data=[BUFF],
+                                                          sparse_rule=rule)
+    s = w.schedule("Update")
+    s.add_system("regen_players", "regen", w.query([(H, True)], with_=[TAG]))
+    s.add_system("buff_heal", "buff_heal", w.query([(H, True)], without=[FROZEN], sparse_data=[BUFF]))
+    ordinal = list(SPARSE_TYPES).index("SparseBuff")
+    s.add_system("buff_optional", "buff_optional", w.query([(H, True)], with_=[P]),
+                 params=struct.pack("<QII", capi.fnv1a(BUFF), ordinal, 0))
+    s.build()
+    out = {"order": s.execution_order()}
+    stale = []
+    for f in range(frames):
+        rng = np.random.default_rng(seed * 1000 + f)
+        live = np.concatenate([a["entities"] for a in w.snapshot(columns=False)["archetypes"]])
+        spawned = w.reserve_entities(5)
+        pool = np.concatenate([live, spawned, np.asarray(stale[-8:], dtype=np.uint64)])
+        cmds, payload = sparse_commands(w, rng, pool, n_cmd, stale)
+        w.enqueue(cmds, payload)
+        w.flush()
+        out[f"frame{f}_state"] = sparse_state(w)
+        out[f"frame{f}_counts"] = {k: q.count() for k, q in queries.items()}
+        s.run_and_wait(mode)
+        out[f"frame{f}_after_systems"] = snapshot_digest(w.snapshot())
+    w.close()
+    return out
+
+
 SCENARIOS = {
     "cfg1_n4099": lambda b: cfg1(b),
     "cfg1_n1": lambda b: cfg1(b, n=1),
@@ -173,5 +266,6 @@ SCENARIOS = {
     "cfg4_schedule_messages": lambda b: cfg4(b),
     "consumable_messages": lambda b: consumable(b),
     "churn_small_s3": lambda b: churn_small(b, seed=3),
+    "sparse_sets": lambda b: sparse_sets(b),
     "churn_small_s11": lambda b: churn_small(b, seed=11),
 }
