@@ -304,6 +304,127 @@ def run_terminals(args, torch, dev, stream, peak):
     }
 
 
+def run_sparse(args, torch, dev, stream, peak):
+    """Sparse-set components: `Query<Position&, const Velocity&, With<PlayerTag>, Without<FrozenTag>>`
+    (README-style tag filters; tags are sparse-set stored) over ONE table of `--entities` rows (default 16.8M).  Tags are
+    attached through deferred commands (timed: the sparse apply path), then the filtered integrate system is timed at tag
+    densities 25 % and 100 %, next to the same system without sparse terms.  L2 flushed between steps."""
+    n = args.entities or (1 << 24)
+    gpu = capi.load_gpu()
+    w = capi.World(gpu, device=dev.index, entity_capacity=n + 1024)
+    w.set_stream(stream.cuda_stream)
+    P, V = worlds.cname("Position"), worlds.cname("Velocity")
+    worlds.register_all(w, ["Position", "Velocity"])
+    TAG, FROZEN = worlds.cname("PlayerTag"), worlds.cname("FrozenTag")
+    w.register_sparse_component(TAG, 0)
+    w.register_sparse_component(FROZEN, 0)
+    ents = w.spawn_batch([P, V], n, [worlds.column("Position", n, 1), worlds.column("Velocity", n, 2)])
+    steps, warm = args.steps, max(3, args.warmup)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    flush_rd = torch.ones(256 << 20, dtype=torch.uint8, device=dev)
+    sink = torch.zeros((), dtype=torch.int64, device=dev)
+
+    def time_system(q):
+        s = w.schedule("S")
+        s.add_system("integrate", "integrate", q)
+        s.build()
+        for _ in range(warm):
+            s.run_and_wait(capi.EXEC_SERIAL)
+        ms = []
+        for _ in range(steps):
+            flush.fill_(1)
+            torch.sum(flush_rd, dim=(0,), dtype=torch.int64, out=sink)
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            s.run(capi.EXEC_SERIAL)
+            b.record(stream)
+            s.apply_deferred()
+            ms.append(a.elapsed_time(b))
+        s.close()
+        return float(np.median(ms))
+
+    def tag(entities, name):
+        cmds = np.zeros(entities.size, dtype=capi.COMMAND_DTYPE)
+        cmds["kind"] = capi.CMD_ADD
+        cmds["entity"] = entities
+        cmds["component_mask"] = w.mask([name])
+        w.enqueue(cmds)
+        w.stage_commands()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        w.flush()
+        torch.cuda.synchronize()
+        return time.perf_counter() - t0
+
+    out, launches = {}, 0
+    l0 = w.launch_count()
+    with torch.cuda.stream(stream):
+        plain = time_system(w.query([(P, True), (V, False)]))
+        out["no_sparse_terms"] = {"ms": plain, "GBps": n * 24 / (plain * 1e-3) / 1e9}
+        q = w.query([(P, True), (V, False)], with_=[TAG], without=[FROZEN])
+
+        def leg(key):
+            visited = q.count()
+            ms = time_system(q)
+            # algorithmic bytes: entity id 8 + membership word 4 per row; Position r/w + Velocity r only for rows that pass
+            nbytes = n * 12 + visited * 24
+            out[key] = {"ms": ms, "visited": visited, "GBps": nbytes / (ms * 1e-3) / 1e9, "frac": nbytes / (ms * 1e-3) / 1e9 / peak[0]}
+
+        # 0.1 %: one entity in 1024 tagged (a rare tag: the selective kernel variant); 1/64 of all entities frozen
+        tag(ents[::1024], TAG)
+        tag(ents[32::64], FROZEN)
+        leg("tagged_0.1pct")
+        # 25 %: every fourth entity
+        dt_tag = tag(ents[::4], TAG)
+        out["apply_tag_commands"] = {"commands": int(ents[::4].size), "ms": dt_tag * 1e3, "commands_per_s": ents[::4].size / dt_tag,
+                                     "note": "ADD PlayerTag through helios_gpu_world_flush (records already staged in HBM): command "
+                                             "chains + ranked parallel placement of the appends"}
+        leg("tagged_25pct")
+        tag(np.delete(ents, np.arange(0, n, 4)), TAG)
+        leg("tagged_100pct")
+    launches = w.launch_count() - l0
+    cpu = None
+    if not args.no_cpu_baseline:
+        o = capi.load_oracle()
+        sn = n // 16
+        wo = capi.World(o)
+        worlds.register_all(wo, ["Position", "Velocity"])
+        wo.register_sparse_component(TAG, 0)
+        wo.register_sparse_component(FROZEN, 0)
+        eo = wo.spawn_batch([P, V], sn, [worlds.column("Position", sn, 1), worlds.column("Velocity", sn, 2)])
+        cm = np.zeros(eo.size, dtype=capi.COMMAND_DTYPE)
+        cm["kind"] = capi.CMD_ADD
+        cm["entity"] = eo
+        cm["component_mask"] = wo.mask([TAG])
+        wo.enqueue(cm)
+        wo.flush()
+        so = wo.schedule("S")
+        so.add_system("integrate", "integrate", wo.query([(P, True), (V, False)], with_=[TAG], without=[FROZEN]))
+        so.build()
+        so.run_and_wait(capi.EXEC_SERIAL)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            so.run_and_wait(capi.EXEC_SERIAL)
+        dt = (time.perf_counter() - t0) / 3
+        cpu = {"value": sn / dt, "unit": "rows/s", "cores": 1, "kind": "port",
+               "sample": f"tag-filtered integrate over {sn} rows (1/16 scale), all tagged, 3 repetitions"}
+        wo.close()
+    w.close()
+    head = out["tagged_100pct"]
+    return {
+        "metric": "sparse_filtered_rows_per_sec", "value": n / (head["ms"] * 1e-3), "unit": "rows/s", "ms_per_step": head["ms"],
+        "dtype": "f32 bodies, u32 membership words",
+        "config": {"workload": f"sparse: integrate With<PlayerTag> Without<FrozenTag> over {n} rows, one table; tags are sparse-set "
+                               "components attached by deferred commands",
+                   "l2": "flushed between steps: 256 MiB written, then 256 MiB read"},
+        "roofline": {"bound": "hbm", "achieved": head["GBps"], "peak": peak[0], "unit": "GB/s", "frac": head["frac"], "traffic": None,
+                     "peak_kind": peak[1], "algorithmic_bytes_per_launch": int(n * 12 + head["visited"] * 24),
+                     "kernel": "helios_gpu::for_each_kernel<..., kSparse = true, IntegrateBody, Position, Velocity>"},
+        "sparse": out, "e2e": None, "cpu_baseline": cpu, "gpu_launches": int(launches),
+    }
+
+
 def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
     """Boids, STRONG scaling: `--entities` boids in total (default 64M, density 4 per cell) split by entity-id range over
     the ranks; per step: bin own shard, all-gather slabs + counts (NCCL), neighbour pass + integrate."""

@@ -122,12 +122,12 @@ __device__ __forceinline__ bool sparse_pass(const helios_gpu_sparse_filter& sf, 
   return (membership & sf.require) == sf.require && (membership & sf.exclude) == 0u;
 }
 
-template <uint32_t kWriteMask, bool kWithEntity, bool kSparse, typename Body, typename... Cs>
+template <uint32_t kWriteMask, bool kWithEntity, int kSparse, typename Body, typename... Cs>
 __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<Cs*...> cols, Body& body,
                                              const helios_gpu_sparse_filter& sf) {
   using namespace detail;
   constexpr int N = sizeof...(Cs);
-  constexpr bool kLoadEnt = kWithEntity || kSparse;  // the sparse test is keyed by entity index
+  constexpr bool kLoadEnt = kWithEntity || kSparse != 0;  // the sparse test is keyed by entity index
   const uint32_t row0 = t.row0;
   const uint32_t live = t.rows - row0;
   cuda::std::tuple<CompRegs<Cs>...> regs;
@@ -145,10 +145,6 @@ __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<
   };
 
   if (live >= kTileRows) {
-    each([&](auto, auto& cr, auto* col) {
-#pragma unroll
-      for (int k = 0; k < kPairs; ++k) load_pair(cr.p[k], col + row0 + k * 2 * kBlock + 2 * threadIdx.x);
-    });
     if constexpr (kLoadEnt) {
 #pragma unroll
       for (int k = 0; k < kPairs; ++k) {
@@ -158,7 +154,27 @@ __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<
       }
     }
     uint32_t member[kPairs][2];
-    if constexpr (kSparse) {  // all gathers go out before the first body runs
+    bool wanted[kPairs];  // kSparse == 2: does any row of this warp's 64-row slice pass?  (uniform per warp)
+#pragma unroll
+    for (int k = 0; k < kPairs; ++k) wanted[k] = true;
+    if constexpr (kSparse == 2) {
+      // selective filter (few rows pass): the membership words come FIRST and a warp whose 64 consecutive rows all fail
+      // neither loads nor stores their component columns — a rare tag costs 12 bytes per row instead of the whole row
+#pragma unroll
+      for (int k = 0; k < kPairs; ++k) {
+        member[k][0] = __ldg(&sf.membership[uint32_t(ents[k][0])]);
+        member[k][1] = __ldg(&sf.membership[uint32_t(ents[k][1])]);
+      }
+#pragma unroll
+      for (int k = 0; k < kPairs; ++k)
+        wanted[k] = __any_sync(0xFFFFFFFFu, sparse_pass(sf, member[k][0]) || sparse_pass(sf, member[k][1]));
+    }
+    each([&](auto, auto& cr, auto* col) {
+#pragma unroll
+      for (int k = 0; k < kPairs; ++k)
+        if (wanted[k]) load_pair(cr.p[k], col + row0 + k * 2 * kBlock + 2 * threadIdx.x);
+    });
+    if constexpr (kSparse == 1) {  // dense filter: every load of the tile is in flight before the first test
 #pragma unroll
       for (int k = 0; k < kPairs; ++k) {
         member[k][0] = __ldg(&sf.membership[uint32_t(ents[k][0])]);
@@ -169,7 +185,7 @@ __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<
     for (int k = 0; k < kPairs; ++k) {
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
-        if constexpr (kSparse) {
+        if constexpr (kSparse != 0) {
           if (!sparse_pass(sf, member[k][j])) continue;  // iterator.hpp:530-585 AdvanceToValidEntity
         }
         const uint32_t r = row0 + k * 2 * kBlock + 2 * threadIdx.x + j;
@@ -179,7 +195,8 @@ __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<
     each([&](auto idx, auto& cr, auto* col) {
       if constexpr ((kWriteMask >> decltype(idx)::value) & 1u) {
 #pragma unroll
-        for (int k = 0; k < kPairs; ++k) store_pair(cr.p[k], col + row0 + k * 2 * kBlock + 2 * threadIdx.x);
+        for (int k = 0; k < kPairs; ++k)
+          if (wanted[k]) store_pair(cr.p[k], col + row0 + k * 2 * kBlock + 2 * threadIdx.x);
       }
     });
   } else {
@@ -192,7 +209,7 @@ __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<
         if (off < live) {
           const uint32_t r = row0 + off;
           const helios_gpu_entity_t ent = kLoadEnt ? t.entities[r] : HELIOS_GPU_INVALID_ENTITY;
-          if constexpr (kSparse) {
+          if constexpr (kSparse != 0) {
             if (!sparse_pass(sf, __ldg(&sf.membership[uint32_t(ent)]))) continue;
           }
           each([&](auto, auto& cr, auto* col) { cr.p[k].v[j] = col[r]; });
@@ -208,13 +225,13 @@ __device__ __forceinline__ void process_tile(const TileRef& t, cuda::std::tuple<
 
 // Two FULL tiles of one table at once (narrow rows): the loads of both tiles are in flight before either body runs, which
 // doubles the bytes a thread keeps outstanding — a one-tile walk of 8-byte rows is bound by memory latency, not bandwidth.
-template <uint32_t kWriteMask, bool kWithEntity, bool kSparse, typename Body, typename... Cs>
+template <uint32_t kWriteMask, bool kWithEntity, int kSparse, typename Body, typename... Cs>
 __device__ __forceinline__ void process_full_tile_pair(const TileRef& t, uint32_t row0_a, uint32_t row0_b,
                                                        cuda::std::tuple<Cs*...> cols, Body& body,
                                                        const helios_gpu_sparse_filter& sf) {
   using namespace detail;
   constexpr int N = sizeof...(Cs);
-  constexpr bool kLoadEnt = kWithEntity || kSparse;
+  constexpr bool kLoadEnt = kWithEntity || kSparse != 0;
   cuda::std::tuple<CompRegs<Cs>...> regs[2];
   helios_gpu_entity_t ents[2][kPairs][2];
   const uint32_t row0[2] = {row0_a, row0_b};
@@ -238,7 +255,7 @@ __device__ __forceinline__ void process_full_tile_pair(const TileRef& t, uint32_
     }
   }
   uint32_t member[2][kPairs][2];
-  if constexpr (kSparse) {
+  if constexpr (kSparse != 0) {
 #pragma unroll
     for (int h = 0; h < 2; ++h)
 #pragma unroll
@@ -253,7 +270,7 @@ __device__ __forceinline__ void process_full_tile_pair(const TileRef& t, uint32_
     for (int k = 0; k < kPairs; ++k) {
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
-        if constexpr (kSparse) {
+        if constexpr (kSparse != 0) {
           if (!sparse_pass(sf, member[h][k][j])) continue;
         }
         const uint32_t r = row0[h] + k * 2 * kBlock + 2 * threadIdx.x + j;
@@ -290,11 +307,11 @@ constexpr bool kNarrowRows = (0 + ... + int(sizeof(Cs))) + (kWithEntity ? 8 : 0)
 template <bool kWithEntity, typename... Cs>
 constexpr int kForEachMinBlocks = !kNarrowRows<kWithEntity, Cs...> ? 1 : (kWithEntity ? 4 : 8);
 
-template <uint32_t kWriteMask, bool kWithEntity, bool kSparse, typename Body, typename... Cs>
-__global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity || kSparse, Cs...>) for_each_kernel(const helios_gpu_match_args m, Body body,
+template <uint32_t kWriteMask, bool kWithEntity, int kSparse, typename Body, typename... Cs>
+__global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity || kSparse != 0, Cs...>) for_each_kernel(const helios_gpu_match_args m, Body body,
                                                                                                 const helios_gpu_sparse_filter sf) {
   constexpr int N = sizeof...(Cs);
-  constexpr bool kLoadEnt = kWithEntity || kSparse;
+  constexpr bool kLoadEnt = kWithEntity || kSparse != 0;
   static_assert(N >= 1 && N <= HELIOS_GPU_MAX_QUERY_COMPONENTS, "1..8 data components per body");
   __shared__ uint32_t s_tile_begin[kFusedMaxTables + 1];
   __shared__ uint32_t s_table[kFusedMaxTables];
@@ -382,7 +399,7 @@ __global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity || kSpar
         tr.row0 = (tile - s_tile_begin[seg]) * kTileRows;
         const auto cols = detail::typed_columns<Cs...>(bases, cuda::std::make_index_sequence<N>{});
         // two full tiles of the same table: both sets of loads go out before the bodies run
-        if (tile + 1 < last && tile + 1 < s_tile_begin[seg + 1] && tr.row0 + 2 * kTileRows <= tr.rows) {
+        if (kSparse != 2 && tile + 1 < last && tile + 1 < s_tile_begin[seg + 1] && tr.row0 + 2 * kTileRows <= tr.rows) {
           process_full_tile_pair<kWriteMask, kWithEntity, kSparse, Body, Cs...>(tr, tr.row0, tr.row0 + kTileRows, cols, body, sf);
           ++tile;
         } else {
@@ -405,7 +422,7 @@ __global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity || kSpar
 }
 
 // for_each_kernel_view: same visit over a MATERIALISED view (worlds with more than kFusedMaxTables tables).
-template <uint32_t kWriteMask, bool kWithEntity, bool kSparse, typename Body, typename... Cs>
+template <uint32_t kWriteMask, bool kWithEntity, int kSparse, typename Body, typename... Cs>
 __global__ void __launch_bounds__(kBlock) for_each_kernel_view(const helios_gpu_query_view* __restrict__ view, Body body,
                                                                const helios_gpu_sparse_filter sf) {
   using namespace detail;
@@ -446,7 +463,7 @@ __global__ void __launch_bounds__(kBlock) for_each_kernel_view(const helios_gpu_
 }
 
 // Host launcher: grid = one resident wave (SM count x occupancy), so CTAs stay put and stride over tiles.
-template <uint32_t kWriteMask, bool kWithEntity, bool kSparse, typename Body, typename... Cs>
+template <uint32_t kWriteMask, bool kWithEntity, int kSparse, typename Body, typename... Cs>
 inline int32_t for_each_launch_impl(const helios_gpu_system_ctx* ctx, Body body) {
   auto kern = for_each_kernel<kWriteMask, kWithEntity, kSparse, Body, Cs...>;
   auto kern_view = for_each_kernel_view<kWriteMask, kWithEntity, kSparse, Body, Cs...>;
@@ -466,13 +483,16 @@ inline int32_t for_each_launch_impl(const helios_gpu_system_ctx* ctx, Body body)
   return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
 }
 
-// A query with sparse-set terms (With<Tag>, Without<Tag>, sparse data) runs the instantiation that reads every row's
-// entity id and tests its membership word; every other query runs the kernel without that code.
+// A query with sparse-set terms (With<Tag>, Without<Tag>, sparse data) runs an instantiation that reads every row's
+// entity id and tests its membership word — kSparse = 1 when most rows are expected to pass (all loads first), 2 when
+// few are (membership first, untouched 64-row slices skip their columns); every other query runs the kernel without
+// that code.
 template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
 inline int32_t for_each_launch(const helios_gpu_system_ctx* ctx, Body body) {
   if (ctx->sparse_filter.membership != nullptr)
-    return for_each_launch_impl<kWriteMask, kWithEntity, true, Body, Cs...>(ctx, body);
-  return for_each_launch_impl<kWriteMask, kWithEntity, false, Body, Cs...>(ctx, body);
+    return ctx->sparse_filter.selective ? for_each_launch_impl<kWriteMask, kWithEntity, 2, Body, Cs...>(ctx, body)
+                                        : for_each_launch_impl<kWriteMask, kWithEntity, 1, Body, Cs...>(ctx, body);
+  return for_each_launch_impl<kWriteMask, kWithEntity, 0, Body, Cs...>(ctx, body);
 }
 
 // ---------------------------------------------------------------------------------------------------

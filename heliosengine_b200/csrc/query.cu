@@ -180,6 +180,17 @@ int32_t fill_query_ctx(helios_gpu_system_ctx* ctx, helios_gpu_query* q, cudaStre
   ctx->sparse_filter.membership = (q->sparse_require | q->sparse_exclude) ? w->d_membership.as<uint32_t>() : nullptr;
   ctx->sparse_filter.require = q->sparse_require;
   ctx->sparse_filter.exclude = q->sparse_exclude;
+  ctx->sparse_filter.selective = 0;
+  if (ctx->sparse_filter.membership) {  // expected pass rate from the storage sizes (host mirrors are exact)
+    const double live = double(std::max<uint64_t>(w->live_count, 1));
+    double pass = 1.0;
+    for (size_t o = 0; o < w->sparse.size(); ++o) {
+      const double f = std::min(1.0, double(w->sparse[o].size) / live);
+      if (q->sparse_require >> o & 1u) pass = std::min(pass, f);
+      if (q->sparse_exclude >> o & 1u) pass = std::min(pass, 1.0 - f);
+    }
+    ctx->sparse_filter.selective = pass < 0.125 ? 1u : 0u;
+  }
   ctx->sparse.dir = w->d_sparse_dir.as<helios_gpu_sparse_dir>();
   std::memcpy(ctx->sparse.fetch, q->sparse_fetch, sizeof q->sparse_fetch);
   if (want_view || w->tables.size() > HELIOS_GPU_FUSED_MATCH_MAX_TABLES) {
@@ -290,7 +301,7 @@ int32_t helios_gpu_query_count(helios_gpu_query* q, uint64_t* out) {
   if (q->sparse_require | q->sparse_exclude) {  // Count walks the entities (query.hpp:1652-1666): per-entity sparse test
     HG_CUDA(w, q->result.reserve(sizeof(helios_gpu_terminal_result), 0, w->stream, false));
     HG_CUDA(w, cudaMemsetAsync(q->result.ptr, 0, 8, w->stream));
-    const helios_gpu_sparse_filter sf{w->d_membership.as<uint32_t>(), q->sparse_require, q->sparse_exclude};
+    const helios_gpu_sparse_filter sf{w->d_membership.as<uint32_t>(), q->sparse_require, q->sparse_exclude, 0u, 0u};
     k_count_sparse<<<uint32_t(w->sm_count) * 4, 256, 0, w->stream>>>(q->d_view.as<helios_gpu_query_view>(), sf,
                                                                       q->result.as<unsigned long long>());
     ++w->launches;

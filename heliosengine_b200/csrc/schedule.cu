@@ -342,11 +342,12 @@ int32_t helios_gpu_schedule_add_system(helios_gpu_schedule* s, const helios_gpu_
   if (d->params && d->params_size) e->params.assign(static_cast<const uint8_t*>(d->params), static_cast<const uint8_t*>(d->params) + d->params_size);
   e->desc.params = nullptr;
   // SystemParamTraits<Query>::RegisterAccess (system/param_traits.hpp:55-60): mutable → write set, const → read set.
-  if (d->query)
+  if (d->query) {
     for (uint32_t k = 0; k < d->query->desc.n_components; ++k)
       Policy::ins(d->query->desc.writes[k] ? e->policy.wc : e->policy.rc, d->query->desc.components[k]);
     for (uint32_t k = 0; k < d->query->desc.n_sparse_data; ++k)  // sparse data: const access (param_traits.hpp:43-75)
       Policy::ins(e->policy.rc, d->query->desc.sparse_data[k]);
+  }
   for (uint32_t k = 0; k < d->n_extra_read_components; ++k) Policy::ins(e->policy.rc, d->extra_read_components[k]);
   for (uint32_t k = 0; k < d->n_extra_write_components; ++k) Policy::ins(e->policy.wc, d->extra_write_components[k]);
   for (uint32_t k = 0; k < d->n_read_resources; ++k) Policy::ins(e->policy.rr, d->read_resources[k]);

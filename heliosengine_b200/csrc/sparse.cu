@@ -13,10 +13,13 @@
 // track the membership word next to the archetype mask and emit, per command, the EXACT sets of storages it appends
 // to, removes from and writes into.  Here those events are compacted in command order and replayed:
 //   * membership words are committed in parallel (each entity's last event carries its final word);
-//   * every storage is replayed by one warp of its own, sequentially over the batch's events only — the exact
-//     formulation (every swap-and-pop depends on the current last element; storages are independent of each other).
-//     Folding this into the table resolver of apply.cu (a storage is a one-column table keyed by (entity, type)) is the
-//     planned parallel form; DESIGN.md §4.6.
+//   * a storage that only sees first-time appends in a batch (the common case: tags attached at spawn) is filled in
+//     parallel: dense slot = size + rank of the event among the storage's appends in command order (flag -> scan ->
+//     scatter);
+//   * a storage with removals or value overwrites is replayed by one warp of its own, sequentially over the batch's
+//     events only — the exact formulation (every swap-and-pop depends on the current last element; storages are
+//     independent of each other).  Folding this into the table resolver of apply.cu (a storage is a one-column table
+//     keyed by (entity, type)) is the planned parallel form; DESIGN.md §4.6.
 #include <algorithm>
 #include <cstring>
 #include <vector>
@@ -40,20 +43,38 @@ __global__ void __launch_bounds__(256) k_sparse_flag(uint32_t K, const helios_gp
                                                      const uint32_t* __restrict__ cflags, const uint32_t* __restrict__ ev_app,
                                                      const uint32_t* __restrict__ ev_rem, const uint32_t* __restrict__ ev_wr,
                                                      const uint32_t* __restrict__ ev_mem, uint32_t* __restrict__ membership,
-                                                     uint32_t* __restrict__ flags, uint32_t* __restrict__ counts /* [2][32] */) {
-  __shared__ uint32_t s_cnt[2 * kMaxSparse];
-  if (threadIdx.x < 2 * kMaxSparse) s_cnt[threadIdx.x] = 0;
+                                                     uint32_t* __restrict__ flags, uint32_t* __restrict__ counts /* [3][32] */) {
+  __shared__ uint32_t s_cnt[3 * kMaxSparse];
+  if (threadIdx.x < 3 * kMaxSparse) s_cnt[threadIdx.x] = 0;
   __syncthreads();
   const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k < K) {
-    uint32_t a = ev_app[k], r = ev_rem[k];
-    flags[k] = (a | r | ev_wr[k]) ? 1u : 0u;
+    uint32_t a = ev_app[k], r = ev_rem[k], wv = ev_wr[k];
+    flags[k] = (a | r | wv) ? 1u : 0u;
     if (cflags[k] & kSparseLastFlag) membership[ent_index(cmd[k].entity)] = ev_mem[k];
-    while (a) { const int o = __ffs(a) - 1; a &= a - 1; atomicAdd(&s_cnt[o], 1u); }
-    while (r) { const int o = __ffs(r) - 1; r &= r - 1; atomicAdd(&s_cnt[kMaxSparse + o], 1u); }
+    // shared-memory histograms; lanes hitting the same storage are combined first (a batch that tags millions of entities
+    // would otherwise serialise on one counter)
+    auto count = [&](uint32_t bits, int row) {
+      while (bits) {
+        const int o = __ffs(bits) - 1;
+        bits &= bits - 1;
+        const uint32_t peers = __match_any_sync(__activemask(), o);
+        if ((threadIdx.x & 31u) == uint32_t(__ffs(peers) - 1)) atomicAdd(&s_cnt[row * kMaxSparse + o], uint32_t(__popc(peers)));
+      }
+    };
+    count(a, 0);
+    count(r, 1);
+    count(wv, 2);
   }
   __syncthreads();
-  if (threadIdx.x < 2 * kMaxSparse && s_cnt[threadIdx.x]) atomicAdd(&counts[threadIdx.x], s_cnt[threadIdx.x]);
+  if (threadIdx.x < 3 * kMaxSparse && s_cnt[threadIdx.x]) atomicAdd(&counts[threadIdx.x], s_cnt[threadIdx.x]);
+}
+
+// ---- append-only storages: flag the list entries that append to storage `bit`, then (after a scan) place them ----------
+__global__ void k_sparse_flag_storage(const uint32_t* __restrict__ list, uint32_t L, const uint32_t* __restrict__ ev_app,
+                                      uint32_t bit, uint32_t* __restrict__ flags) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < L) flags[j] = (ev_app[list[j]] & bit) ? 1u : 0u;
 }
 
 // ---- pass B: ordered compaction of the commands that carry events ------------------------------------------------------
@@ -144,6 +165,32 @@ __global__ void __launch_bounds__(32) k_sparse_replay(ReplayArgs a) {
   if (lane == 0) a.dir->size[o] = size;
 }
 
+// dense slot = size + rank among this storage's appends in command order (sparse_set.hpp:560-588 Insert, batched)
+__global__ void __launch_bounds__(256) k_sparse_append(ReplayArgs a, uint32_t o, const uint32_t* __restrict__ flags,
+                                                       const uint32_t* __restrict__ pos, uint32_t n_app) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t size0 = a.dir->size[o];  // k_sparse_bump_size publishes the new size after this kernel
+  if (j < a.L && flags[j]) {
+    const uint32_t k = a.list[j];
+    const helios_gpu_command c = a.cmd[k];
+    const uint32_t idx = ent_index(c.entity), d = size0 + pos[j];
+    a.dir->sparse[o][idx] = d;
+    a.dir->reverse[o][d] = idx;
+    const uint32_t elem = a.dir->elem_size[o];
+    if (elem) {
+      const uint8_t* src = a.payload + payload_offset_of(c, a.slot_of_ord[o], a.csize);
+      uint8_t* dst = a.dir->dense[o] + size_t(d) * elem;
+      if ((elem & 3u) == 0) {
+        for (uint32_t b = 0; b < elem; b += 4) *reinterpret_cast<uint32_t*>(dst + b) = *reinterpret_cast<const uint32_t*>(src + b);
+      } else {
+        for (uint32_t b = 0; b < elem; ++b) dst[b] = src[b];
+      }
+    }
+  }
+  (void)n_app;
+}
+__global__ void k_sparse_bump_size(helios_gpu_sparse_dir* dir, uint32_t o, uint32_t n_app) { dir->size[o] += n_app; }
+
 }  // namespace
 
 namespace hgpu {
@@ -201,20 +248,20 @@ int32_t sparse_apply_events(helios_gpu_world* w, const helios_gpu_command* d_cmd
   NEED(w->sp_pos, size_t(K) * 4);
   NEED(w->sp_list, size_t(n_events) * 4);
   NEED(w->sp_partials, (size_t(K) / prim::kScanTile + 2) * 4);
-  NEED(w->sp_counts, size_t(2 * kMaxSparse + 1) * 4);
-  HG_CUDA(w, cudaMemsetAsync(w->sp_counts.ptr, 0, size_t(2 * kMaxSparse + 1) * 4, st));
+  NEED(w->sp_counts, size_t(3 * kMaxSparse + 1) * 4);
+  HG_CUDA(w, cudaMemsetAsync(w->sp_counts.ptr, 0, size_t(3 * kMaxSparse + 1) * 4, st));
   uint32_t* counts = w->sp_counts.as<uint32_t>();
   k_sparse_flag<<<blocks_for(K), 256, 0, st>>>(K, d_cmds, cflags, ev_app, ev_rem, ev_wr, ev_mem, w->d_membership.as<uint32_t>(),
                                                w->sp_flags.as<uint32_t>(), counts);
   uint64_t launches = 1;
   launches += prim::exclusive_scan_u32(w->sp_flags.as<uint32_t>(), w->sp_pos.as<uint32_t>(), K, w->sp_partials.as<uint32_t>(),
-                                       counts + 2 * kMaxSparse, st);
+                                       counts + 3 * kMaxSparse, st);
   k_sparse_list<<<blocks_for(K), 256, 0, st>>>(K, w->sp_flags.as<uint32_t>(), w->sp_pos.as<uint32_t>(), w->sp_list.as<uint32_t>());
   ++launches;
-  uint32_t hcounts[2 * kMaxSparse + 1];
+  uint32_t hcounts[3 * kMaxSparse + 1];
   HG_CUDA(w, cudaMemcpyAsync(hcounts, counts, sizeof hcounts, cudaMemcpyDeviceToHost, st));
   HG_CUDA(w, cudaStreamSynchronize(st));
-  if (hcounts[2 * kMaxSparse] != n_events) HG_FAIL(w, HELIOS_GPU_ERR_STATE, "sparse event count mismatch");
+  if (hcounts[3 * kMaxSparse] != n_events) HG_FAIL(w, HELIOS_GPU_ERR_STATE, "sparse event count mismatch");
 
   // grow the dense sides for the appends (upper bound: every append lands before any removal)
   bool moved = false;
@@ -236,11 +283,35 @@ int32_t sparse_apply_events(helios_gpu_world* w, const helios_gpu_command* d_cmd
   ra.csize = w->d_csize.as<uint32_t>();
   std::memset(ra.slot_of_ord, -1, sizeof ra.slot_of_ord);
   for (uint32_t o = 0; o < ns; ++o) ra.slot_of_ord[o] = int8_t(w->sparse[o].slot);
-  // every storage with events goes through the exact warp replay (value overwrites of a storage have to follow the
-  // command order as well, so storages that only saw writes are included)
-  ra.sequential = ns >= 32 ? 0xFFFFFFFFu : (1u << ns) - 1u;
-  k_sparse_replay<<<ns, 32, 0, st>>>(ra);
-  ++launches;
+  // A storage that saw no removal and no overwrite (every value write belongs to an append: each (entity, type) pair is
+  // written at most once) is append-only: its appends are ranked and placed in parallel.  Everything else goes through the
+  // exact one-warp replay, which also keeps value overwrites in command order.
+  ra.sequential = 0;
+  uint32_t parallel = 0;
+  for (uint32_t o = 0; o < ns; ++o) {
+    const uint32_t napp = hcounts[o], nrem = hcounts[kMaxSparse + o], nwr = hcounts[2 * kMaxSparse + o];
+    if (!(napp | nrem | nwr)) continue;
+    const bool no_overwrite = w->sparse[o].elem == 0 || nwr == napp;  // tags carry no values: their writes are no-ops
+    if (nrem == 0 && no_overwrite && napp >= 1024) parallel |= 1u << o;
+    else ra.sequential |= 1u << o;
+  }
+  if (parallel) {
+    NEED(w->sp_flags, size_t(std::max(K, n_events)) * 4);
+    NEED(w->sp_pos, size_t(std::max(K, n_events)) * 4);
+    for (uint32_t o = 0; o < ns; ++o) {
+      if (!(parallel >> o & 1u)) continue;
+      k_sparse_flag_storage<<<blocks_for(n_events), 256, 0, st>>>(ra.list, n_events, ev_app, 1u << o, w->sp_flags.as<uint32_t>());
+      launches += 1 + prim::exclusive_scan_u32(w->sp_flags.as<uint32_t>(), w->sp_pos.as<uint32_t>(), n_events,
+                                               w->sp_partials.as<uint32_t>(), nullptr, st);
+      k_sparse_append<<<blocks_for(n_events), 256, 0, st>>>(ra, o, w->sp_flags.as<uint32_t>(), w->sp_pos.as<uint32_t>(), hcounts[o]);
+      k_sparse_bump_size<<<1, 1, 0, st>>>(ra.dir, o, hcounts[o]);
+      launches += 2;
+    }
+  }
+  if (ra.sequential) {
+    k_sparse_replay<<<ns, 32, 0, st>>>(ra);
+    ++launches;
+  }
   HG_CUDA(w, cudaGetLastError());
   for (uint32_t o = 0; o < ns; ++o) w->sparse[o].size = w->sparse[o].size + hcounts[o] - hcounts[kMaxSparse + o];
   w->sparse_replayed_events += n_events;

@@ -311,6 +311,9 @@ typedef struct helios_gpu_sparse_filter {
   const uint32_t* membership; /* [entity index] bit o = member of sparse ordinal o */
   uint32_t require;
   uint32_t exclude;
+  uint32_t selective; /* hint from the storage sizes: 1 = few rows are expected to pass (for_each_launch then tests the
+                         membership words before it touches the component columns) */
+  uint32_t _pad;
 } helios_gpu_sparse_filter;
 
 /* Device directory of the sparse storages (one struct in HBM, refreshed by the library when a storage grows, so the

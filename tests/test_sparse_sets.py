@@ -123,3 +123,44 @@ def test_gpu_sparse_registration_rules(gpu):
     with pytest.raises(capi.HeliosError):
         w.query([("Tag", False)])                          # sparse data goes in sparse_data
     w.close()
+
+
+def _bulk_tagging(backend):
+    """Append-only batches (tags and values attached to thousands of entities at once: the parallel placement path),
+    then a batch with removals over the same storages (ordered replay), then append-only again."""
+    w = scenarios.sparse_world(backend, rows=(6000, 3000, 1000))
+    TAG, BUFF, SV = (worlds.cname(x) for x in ("PlayerTag", "SparseBuff", "SparseVelocity"))
+    ents = np.concatenate([a["entities"] for a in w.snapshot(columns=False)["archetypes"]])
+    rng = np.random.default_rng(99)
+    out = []
+
+    def add(es, names, try_=False):
+        names = sorted(names, key=lambda y: w.slots[y])
+        words = sum(w.sizes[x] // 4 for x in names)
+        cmds = np.zeros(es.size, dtype=capi.COMMAND_DTYPE)
+        cmds["kind"] = capi.CMD_TRY_ADD if try_ else capi.CMD_ADD
+        cmds["entity"] = es
+        cmds["component_mask"] = w.mask(names)
+        cmds["payload_offset"] = np.arange(es.size, dtype=np.uint32) * (4 * words)
+        w.enqueue(cmds, rng.integers(1, 1 << 20, size=max(1, es.size * words), dtype=np.uint32))
+        w.flush()
+        out.append(scenarios.sparse_state(w))
+
+    add(rng.permutation(ents)[:7000], [TAG, BUFF])             # both storages append-only, >= 1024 appends
+    add(rng.permutation(ents)[:5000], [SV, TAG], try_=True)    # TAG: partly present (no event), SV: all new
+    cmds = np.zeros(3000, dtype=capi.COMMAND_DTYPE)            # removals: BUFF goes through the ordered replay
+    cmds["kind"] = capi.CMD_TRY_REMOVE
+    cmds["entity"] = rng.permutation(ents)[:3000]
+    cmds["component_mask"] = w.mask([BUFF])
+    w.enqueue(cmds)
+    w.flush()
+    out.append(scenarios.sparse_state(w))
+    add(rng.permutation(ents)[:4000], [BUFF])                  # overwrites + inserts mixed: replay again
+    add(w.reserve_entities(2000), [TAG, SV])                   # freshly spawned entities, append-only
+    w.close()
+    return out
+
+
+@pytest.mark.gpu
+def test_gpu_sparse_bulk_tagging_matches_oracle(gpu, oracle):
+    assert _bulk_tagging(gpu) == _bulk_tagging(oracle)
