@@ -307,8 +307,15 @@ constexpr bool kNarrowRows = (0 + ... + int(sizeof(Cs))) + (kWithEntity ? 8 : 0)
 template <bool kWithEntity, typename... Cs>
 constexpr int kForEachMinBlocks = !kNarrowRows<kWithEntity, Cs...> ? 1 : (kWithEntity ? 4 : 8);
 
+// The selective variant (kSparse == 2) mostly waits on the id -> membership chain: rows of <= 16 component bytes ask for 6
+// CTAs per SM (<= 42 registers) so that more of those chains overlap; wider rows keep the default (they would spill).
+template <bool kWithEntity, int kSparse, typename... Cs>
+constexpr int kForEachSparseMinBlocks =
+    (kSparse == 2 && (0 + ... + int(sizeof(Cs))) <= 16 && kForEachMinBlocks<true, Cs...> < 6) ? 6
+                                                                                              : kForEachMinBlocks<kWithEntity || kSparse != 0, Cs...>;
+
 template <uint32_t kWriteMask, bool kWithEntity, int kSparse, typename Body, typename... Cs>
-__global__ void __launch_bounds__(kBlock, kForEachMinBlocks<kWithEntity || kSparse != 0, Cs...>) for_each_kernel(const helios_gpu_match_args m, Body body,
+__global__ void __launch_bounds__(kBlock, kForEachSparseMinBlocks<kWithEntity, kSparse, Cs...>) for_each_kernel(const helios_gpu_match_args m, Body body,
                                                                                                 const helios_gpu_sparse_filter sf) {
   constexpr int N = sizeof...(Cs);
   constexpr bool kLoadEnt = kWithEntity || kSparse != 0;

@@ -371,6 +371,28 @@ int32_t helios_gpu_sparse_ordinal(helios_gpu_world* w, uint64_t hash) {
   return w->sparse_ord_of_slot[it->second];
 }
 
+int32_t helios_gpu_sparse_get(helios_gpu_world* w, uint64_t hash, helios_gpu_entity_t e, uint32_t* present, void* value) {
+  if (!w || !present) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  *present = 0;
+  const int32_t o = helios_gpu_sparse_ordinal(w, hash);
+  if (o < 0) return HELIOS_GPU_OK;  // no storage yet: nobody has the component (manager.hpp:1367-1377)
+  const uint32_t idx = ent_index(e);
+  if (idx >= w->ent_capacity) return HELIOS_GPU_OK;
+  cudaStream_t st = w->stream;
+  const SparseStore& s = w->sparse[size_t(o)];
+  uint32_t gen = kInvalidGeneration, d = kAbsent;
+  HG_CUDA(w, cudaMemcpyAsync(&gen, w->d_gen.as<uint32_t>() + idx, 4, cudaMemcpyDeviceToHost, st));
+  HG_CUDA(w, cudaMemcpyAsync(&d, s.sparse.as<uint32_t>() + idx, 4, cudaMemcpyDeviceToHost, st));
+  HG_CUDA(w, cudaStreamSynchronize(st));
+  if (gen != ent_gen(e) || d == kAbsent) return HELIOS_GPU_OK;
+  *present = 1;
+  if (value && s.elem) {
+    HG_CUDA(w, cudaMemcpyAsync(value, s.dense.as<uint8_t>() + size_t(d) * s.elem, s.elem, cudaMemcpyDeviceToHost, st));
+    HG_CUDA(w, cudaStreamSynchronize(st));
+  }
+  return HELIOS_GPU_OK;
+}
+
 int32_t helios_gpu_snapshot_sparse(helios_gpu_world* w, uint64_t hash, uint64_t* count, uint32_t* entity_indices, void* data,
                                    uint64_t capacity) {
   if (!w) return HELIOS_GPU_ERR_INVALID_ARGUMENT;

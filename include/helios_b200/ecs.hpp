@@ -82,6 +82,23 @@ private:
   GenerationType generation_ = kInvalidGeneration;
 };
 
+// ---- component storage rule (component/component.hpp:60-129): `static constexpr auto kStorageType = ...` on the type wins;
+// otherwise empty "tag" structs are sparse-set stored and everything else lives in archetype tables --------------------
+enum class ComponentStorageType : uint8_t { kArchetype = 0, kSparseSet = 1 };
+template <typename T>
+consteval ComponentStorageType ComponentStorageTypeOf() noexcept {
+  using U = std::remove_cvref_t<T>;
+  if constexpr (requires { U::kStorageType; }) return U::kStorageType;
+  else return std::is_empty_v<U> ? ComponentStorageType::kSparseSet : ComponentStorageType::kArchetype;
+}
+template <typename T>
+inline constexpr bool kIsSparse = ComponentStorageTypeOf<T>() == ComponentStorageType::kSparseSet;
+// Per-entity treatment of sparse With / Without terms (helios_gpu_query_desc::sparse_rule).
+enum class SparseRule : uint32_t {
+  kStrict = HELIOS_GPU_SPARSE_STRICT, kReferenceForEach = HELIOS_GPU_SPARSE_FOREACH,
+  kReferenceWithEntity = HELIOS_GPU_SPARSE_WITH_ENTITY
+};
+
 // ---- query filters (query/details/query_args.hpp:14-39) -------------------------------------------------------------
 template <typename... Ts> struct With {};
 template <typename... Ts> struct Without {};
@@ -98,7 +115,7 @@ template <typename T> struct IsWithout : std::false_type {};
 template <typename... Ts> struct IsWithout<Without<Ts...>> : std::true_type {};
 
 template <typename T>
-concept Component = std::is_trivially_copyable_v<std::remove_cvref_t<T>> && !std::is_empty_v<std::remove_cvref_t<T>>;
+concept Component = std::is_trivially_copyable_v<std::remove_cvref_t<T>>;
 
 // query/details/traits.hpp:73-97 — T& / T* count as write access, const T& / T / const T* as read.
 template <typename A>
@@ -123,12 +140,19 @@ template <typename A>
 void AppendArg(helios_gpu_query_desc& d) {
   if constexpr (IsWith<A>::value || IsWithout<A>::value) {
     AppendFilter(d, A{});
+  } else if constexpr (kIsSparse<ComponentOf<A>>) {
+    // sparse data: reference / value access is a required term fetched by entity (iterator.hpp:88-100); pointer access
+    // is nullable and takes no part in the match (iterator.hpp:49-68)
+    if constexpr (!std::is_pointer_v<std::remove_cvref_t<A>>) d.sparse_data[d.n_sparse_data++] = TypeIndexOf<ComponentOf<A>>();
   } else {
     d.components[d.n_components] = TypeIndexOf<ComponentOf<A>>();
     d.writes[d.n_components] = kIsWriteAccess<A> ? 1 : 0;
     ++d.n_components;
   }
 }
+// Sparse types have to be known to the world before a query over them is classified.
+template <typename A, typename W>
+void RegisterSparseArg(W& world);
 }  // namespace details
 
 class World;
@@ -142,7 +166,7 @@ public:
     (details::AppendArg<Args>(d), ...);
     return d;
   }
-  explicit Query(World& world);
+  explicit Query(World& world, SparseRule rule = SparseRule::kStrict);
   Query(const Query&) = delete;
   Query& operator=(const Query&) = delete;
   ~Query() { if (q_) helios_gpu_query_destroy(q_); }
@@ -223,8 +247,14 @@ public:
   // ComponentManager::Register (component/manager.hpp:1049-1057); implicit on first use like the reference's Add.
   template <details::Component T>
   int RegisterComponent() {
-    const T def{};
-    const int32_t slot = helios_gpu_register_component(w_, TypeIndexOf<T>(), sizeof(T), alignof(T), &def);
+    int32_t slot;
+    if constexpr (kIsSparse<T>) {  // SparseComponentStorage<T>; tags occupy no value bytes
+      slot = helios_gpu_register_sparse_component(w_, TypeIndexOf<T>(), std::is_empty_v<T> ? 0u : uint32_t(sizeof(T)), alignof(T));
+    } else {
+      static_assert(!std::is_empty_v<T>, "an empty component cannot be archetype-stored on the device");
+      const T def{};
+      slot = helios_gpu_register_component(w_, TypeIndexOf<T>(), sizeof(T), alignof(T), &def);
+    }
     if (slot < 0) Check(slot);
     return slot;
   }
@@ -244,6 +274,7 @@ public:
   // Bulk form of `for i: e = CreateEntity(); AddComponents(e, c0[i], c1[i], ...)` — same ids, same archetype and row order.
   template <details::Component... Cs>
   std::vector<Entity> SpawnBatch(size_t n, std::span<const Cs>... columns) {
+    static_assert((!kIsSparse<Cs> && ...), "SpawnBatch fills archetype tables; add sparse-set components with AddComponents");
     (RegisterComponent<Cs>(), ...);
     const uint64_t hashes[] = {TypeIndexOf<Cs>()...};
     const void* cols[] = {static_cast<const void*>(columns.data())...};
@@ -274,6 +305,11 @@ public:
   }
   template <details::Component T>
   bool HasComponent(Entity e) {
+    if constexpr (kIsSparse<T>) {  // manager.hpp:623-636 Has -> SparseComponentStorage::Contains
+      uint32_t present = 0;
+      Check(helios_gpu_sparse_get(w_, TypeIndexOf<T>(), e.Bits(), &present, nullptr));
+      return present != 0;
+    }
     uint32_t a, r;
     if (helios_gpu_entity_location(w_, e.Bits(), &a, &r) != HELIOS_GPU_OK) return false;
     uint64_t hashes[HELIOS_GPU_MAX_COMPONENTS];
@@ -286,6 +322,13 @@ public:
   // World::ReadComponent (copy out of HBM; synchronises).
   template <details::Component T>
   T ReadComponent(Entity e) {
+    if constexpr (kIsSparse<T>) {
+      T v{};
+      uint32_t present = 0;
+      Check(helios_gpu_sparse_get(w_, TypeIndexOf<T>(), e.Bits(), &present, std::is_empty_v<T> ? nullptr : static_cast<void*>(&v)));
+      if (!present) throw GpuError(HELIOS_GPU_ERR_NOT_FOUND, "entity does not have the sparse component");
+      return v;
+    }
     uint32_t a, r;
     Check(helios_gpu_entity_location(w_, e.Bits(), &a, &r));
     T v{};
@@ -338,7 +381,7 @@ public:
   template <details::Component... Cs>
   uint64_t EncodePayload(std::vector<uint8_t>& out, const Cs&... cs) {
     struct Item { int slot; const void* p; size_t n; };
-    Item items[] = {Item{SlotOf<Cs>(), &cs, sizeof(Cs)}...};
+    Item items[] = {Item{SlotOf<Cs>(), &cs, std::is_empty_v<Cs> ? size_t(0) : sizeof(Cs)}...};
     for (size_t i = 1; i < sizeof...(Cs); ++i)
       for (size_t j = i; j > 0 && items[j].slot < items[j - 1].slot; --j) std::swap(items[j], items[j - 1]);
     uint64_t mask = 0;
@@ -366,9 +409,28 @@ private:
   helios_gpu_world* w_ = nullptr;
 };
 
+namespace details {
+template <typename W>
+inline void RegisterSparseList(W&, With<>) {}
+template <typename W, typename T, typename... Ts>
+void RegisterSparseList(W& world, With<T, Ts...>) {
+  if constexpr (kIsSparse<T>) world.template RegisterComponent<T>();
+  RegisterSparseList(world, With<Ts...>{});
+}
+template <typename W, typename... Ts>
+void RegisterSparseList(W& world, Without<Ts...>) { RegisterSparseList(world, With<Ts...>{}); }
+template <typename A, typename W>
+void RegisterSparseArg(W& world) {
+  if constexpr (IsWith<A>::value || IsWithout<A>::value) RegisterSparseList(world, A{});
+  else if constexpr (kIsSparse<ComponentOf<A>>) world.template RegisterComponent<ComponentOf<A>>();
+}
+}  // namespace details
+
 template <typename... Args>
-Query<Args...>::Query(World& world) : world_(&world) {
-  const helios_gpu_query_desc d = Describe();
+Query<Args...>::Query(World& world, SparseRule rule) : world_(&world) {
+  (details::RegisterSparseArg<Args>(world), ...);
+  helios_gpu_query_desc d = Describe();
+  d.sparse_rule = static_cast<uint32_t>(rule);
   world.Check(helios_gpu_query_create(world.Handle(), &d, &q_));
 }
 template <typename... Args>

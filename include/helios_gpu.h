@@ -93,6 +93,11 @@ HELIOS_GPU_API int32_t helios_gpu_register_sparse_component(helios_gpu_world* w,
 HELIOS_GPU_API int32_t helios_gpu_snapshot_sparse(helios_gpu_world* w, uint64_t type_hash, uint64_t* count,
                                                   uint32_t* entity_indices, void* data, uint64_t capacity);
 
+/* SparseComponentStorage::Contains / TryGet for one entity (copies the value out; synchronises).  *present = 0 when the
+ * entity is not alive or not a member; value may be NULL. */
+HELIOS_GPU_API int32_t helios_gpu_sparse_get(helios_gpu_world* w, uint64_t type_hash, helios_gpu_entity_t e,
+                                             uint32_t* present, void* value);
+
 /* ---- entities (World::CreateEntity world.hpp:979-984; Commands::Spawn → ReserveEntity
  *      entity/manager.hpp:294-305) ---------------------------------------------------------------- */
 HELIOS_GPU_API int32_t helios_gpu_create_entities(helios_gpu_world* w, uint32_t n, helios_gpu_entity_t* out);

@@ -24,6 +24,12 @@ static int g_fail = 0, g_checks = 0;
   } while (0)
 
 struct TestMessage { int value; };
+// component/component.hpp:118-129: an empty struct is a tag (sparse-set stored); kStorageType on the type overrides
+struct PlayerTag {};
+struct SparseBuff {
+  static constexpr auto kStorageType = helios::ecs::ComponentStorageType::kSparseSet;
+  int stacks = 0;
+};
 
 int main(int argc, char** argv) {
   if (argc < 3) { std::printf("usage: shim_test gpu|nogpu <plugin.so>\n"); return 2; }
@@ -39,6 +45,13 @@ int main(int argc, char** argv) {
   CHECK(d.n_components == 4 && d.n_with == 1 && d.n_without == 1);
   CHECK(d.writes[0] == 1 && d.writes[1] == 1 && d.writes[2] == 0 && d.writes[3] == 0);
   CHECK(d.components[2] == ecs::Fnv1a("helios::bench::Acceleration") && d.with[0] == ecs::Fnv1a("helios::bench::Health"));
+  // storage rule + sparse query terms: tags in With/Without keep their hashes, sparse data goes to sparse_data, `T*` is
+  // not part of the match (iterator.hpp:49-68)
+  static_assert(ecs::kIsSparse<PlayerTag> && ecs::kIsSparse<SparseBuff> && !ecs::kIsSparse<Position>);
+  using SQ = ecs::Query<Position&, const SparseBuff&, ecs::With<PlayerTag>>;
+  const helios_gpu_query_desc sd = SQ::Describe();
+  CHECK(sd.n_components == 1 && sd.n_sparse_data == 1 && sd.n_with == 1 && sd.sparse_data[0] == ecs::TypeIndexOf<SparseBuff>());
+  CHECK((ecs::Query<Position&, const SparseBuff*>::Describe().n_sparse_data == 0));
   CHECK((ecs::Entity{3, 1} < ecs::Entity{4, 0}) && (ecs::Entity{3, 1} < ecs::Entity{3, 2}) && !ecs::Entity{}.Valid());
   CHECK(ecs::Entity::FromBits(ecs::Entity{7, 2}.Bits()) == (ecs::Entity{7, 2}));
 
@@ -179,6 +192,28 @@ int main(int argc, char** argv) {
     CHECK((parts.first == std::vector<ecs::Entity>{ents[1], ents[2], ents[3]}));
     CHECK((parts.second == std::vector<ecs::Entity>{ents[0], ents[4]}));
     CHECK(q.Run(PQ::BuiltinTerminal("fold_sum_pos_x")).f64 == 69.0);
+  }
+  // ---- sparse-set components (tests/query/query.cpp:1188-1215,2137-2155; tests/component/manager.cpp:529-742) ----
+  {
+    ecs::World world;
+    std::vector<Position> pos(6, Position{1.0f, 0});
+    const auto ents = world.SpawnBatch<Position>(pos.size(), std::span<const Position>(pos));
+    world.AddComponents(ents[1], PlayerTag{});
+    world.AddComponents(ents[2], PlayerTag{}, SparseBuff{.stacks = 7});
+    world.AddComponents(ents[4], SparseBuff{.stacks = 9});
+    CHECK(world.ArchetypeCount() == 2);  // `{}` + {Position}: sparse adds never create archetypes
+    CHECK(world.HasComponent<PlayerTag>(ents[1]) && !world.HasComponent<PlayerTag>(ents[0]));
+    CHECK(world.ReadComponent<SparseBuff>(ents[2]).stacks == 7 && world.ReadComponent<SparseBuff>(ents[4]).stacks == 9);
+    world.TryAddComponents(ents[2], SparseBuff{.stacks = 1});  // present: untouched (sparse_storage.hpp:133-143)
+    CHECK(world.ReadComponent<SparseBuff>(ents[2]).stacks == 7);
+    ecs::Query<const Position&, ecs::With<PlayerTag>> tagged(world);
+    ecs::Query<const Position&, ecs::With<PlayerTag>> tagged_ref(world, ecs::SparseRule::kReferenceForEach);
+    ecs::Query<const Position&, ecs::Without<PlayerTag>> untagged(world);
+    ecs::Query<const Position&, const SparseBuff&, ecs::With<PlayerTag>> tagged_buffed(world);
+    CHECK(tagged.Count() == 2 && tagged_ref.Count() == 6 /* quirk #7 */ && untagged.Count() == 4 && tagged_buffed.Count() == 1);
+    world.RemoveComponents<PlayerTag>(ents[1]);
+    world.DestroyEntity(ents[2]);  // leaves every sparse storage (manager.hpp:1090-1093)
+    CHECK(tagged.Count() == 0 && !world.HasComponent<SparseBuff>(ents[2]) && world.HasComponent<SparseBuff>(ents[4]));
   }
   std::printf("shim_test gpu: %d checks, %d failed\n", g_checks, g_fail);
   return g_fail;
