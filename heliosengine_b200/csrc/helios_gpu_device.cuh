@@ -103,6 +103,18 @@ __device__ __forceinline__ cuda::std::tuple<Cs*...> typed_columns(void* const* b
   return cuda::std::tuple<Cs*...>{static_cast<Cs*>(bases[Is])...};
 }
 
+// One row by direct gather / scatter (sparse-driven visit).  Plain function templates for the same nvcc reason as above.
+template <typename... Cs, size_t... Is>
+__device__ __forceinline__ void gather_row(cuda::std::tuple<Cs...>& vals, void* const* tdir, const int32_t* slots, uint32_t row,
+                                           cuda::std::index_sequence<Is...>) {
+  ((cuda::std::get<Is>(vals) = static_cast<const Cs*>(tdir[slots[Is]])[row]), ...);
+}
+template <uint32_t kWriteMask, typename... Cs, size_t... Is>
+__device__ __forceinline__ void scatter_row(const cuda::std::tuple<Cs...>& vals, void* const* tdir, const int32_t* slots,
+                                            uint32_t row, cuda::std::index_sequence<Is...>) {
+  ((((kWriteMask >> Is) & 1u) ? void(static_cast<Cs*>(tdir[slots[Is]])[row] = cuda::std::get<Is>(vals)) : void(0)), ...);
+}
+
 }  // namespace detail
 
 // ---------------------------------------------------------------------------------------------------
@@ -428,6 +440,78 @@ __global__ void __launch_bounds__(kBlock, kForEachSparseMinBlocks<kWithEntity, k
   if constexpr (requires { body.finish(); }) body.finish();
 }
 
+// ---------------------------------------------------------------------------------------------------
+// for_each_sparse_driven_kernel: the same visit DRIVEN FROM A SPARSE SET.  When a required sparse term is rare
+// (With<Player> over millions of rows), walking the tables costs 12 bytes per row for nothing; here the threads walk the
+// dense array of the smallest required storage instead: reverse[d] -> entity index -> membership test -> location
+// (table, row) -> the table must be in the match set -> the row's components by direct gather.  Bodies see the same Row
+// (flat_row = position among the archetype-matched rows) and the same values; only the (unspecified) visit order of
+// parallel threads differs.  The storage size is read on the device, so a captured graph stays correct as it changes.
+// ---------------------------------------------------------------------------------------------------
+template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
+__global__ void __launch_bounds__(kBlock) for_each_sparse_driven_kernel(const helios_gpu_match_args m, Body body,
+                                                                        const helios_gpu_sparse_filter sf,
+                                                                        const helios_gpu_sparse_dir* __restrict__ dir,
+                                                                        const helios_gpu_world_view wv) {
+  constexpr int N = sizeof...(Cs);
+  constexpr unsigned long long kNoTable = ~0ull;
+  __shared__ unsigned long long s_row_begin[kFusedMaxTables];  // per TABLE: flattened first row, kNoTable if not matched
+  __shared__ unsigned long long s_wsum[kBlock / 32];
+  __shared__ unsigned long long s_running;
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_running = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < m.n_tables; base += kBlock) {  // match + exclusive prefix of the matched row counts
+    const uint32_t t = base + threadIdx.x;
+    unsigned long long rows = 0;
+    bool hit = false;
+    if (t < m.n_tables) {
+      const uint64_t mask = m.table_mask[t];
+      const uint32_t c = m.table_rows[t];
+      hit = c != 0 && (mask & m.required_mask) == m.required_mask && (mask & m.without_mask) == 0;
+      rows = hit ? c : 0;
+    }
+    unsigned long long inc = rows;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned long long v = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+      if (lane >= uint32_t(o)) inc += v;
+    }
+    if (lane == 31) s_wsum[wid] = inc;
+    __syncthreads();
+    unsigned long long off = s_running;
+    for (uint32_t w2 = 0; w2 < wid; ++w2) off += s_wsum[w2];
+    if (t < m.n_tables) s_row_begin[t] = hit ? off + inc - rows : kNoTable;
+    __syncthreads();
+    if (threadIdx.x == kBlock - 1) s_running = off + inc;
+    __syncthreads();
+  }
+  const uint64_t n_rows = s_running;
+  const uint32_t o = sf.drive_ordinal;
+  const uint32_t count = dir->size[o];
+  const uint32_t* __restrict__ reverse = dir->reverse[o];
+  for (uint32_t d = blockIdx.x * kBlock + threadIdx.x; d < count; d += gridDim.x * kBlock) {
+    const uint32_t index = __ldg(&reverse[d]);
+    if (!sparse_pass(sf, __ldg(&sf.membership[index]))) continue;
+    const uint64_t loc = wv.entity_location[index];
+    if (loc == ~0ull) continue;
+    const uint32_t t = uint32_t(loc >> 32), row = uint32_t(loc);
+    if (t >= m.n_tables) continue;
+    const unsigned long long rb = s_row_begin[t];
+    if (rb == kNoTable) continue;
+    void* const* tdir = m.table_columns + size_t(t) * HELIOS_GPU_MAX_COMPONENTS;
+    cuda::std::tuple<Cs...> vals;
+    detail::gather_row<Cs...>(vals, tdir, m.slots, row, cuda::std::make_index_sequence<N>{});
+    const helios_gpu_entity_t ent = uint64_t(index) | (uint64_t(kWithEntity ? wv.entity_generation[index] : 0u) << 32);
+    const Row rc{rb + row, n_rows, kWithEntity ? ent : HELIOS_GPU_INVALID_ENTITY, t, row};
+    [&]<size_t... Is>(cuda::std::index_sequence<Is...>) {
+      body(rc, cuda::std::get<Is>(vals)...);
+    }(cuda::std::make_index_sequence<N>{});
+    detail::scatter_row<kWriteMask, Cs...>(vals, tdir, m.slots, row, cuda::std::make_index_sequence<N>{});
+  }
+  if constexpr (requires { body.finish(); }) body.finish();
+}
+
 // for_each_kernel_view: same visit over a MATERIALISED view (worlds with more than kFusedMaxTables tables).
 template <uint32_t kWriteMask, bool kWithEntity, int kSparse, typename Body, typename... Cs>
 __global__ void __launch_bounds__(kBlock) for_each_kernel_view(const helios_gpu_query_view* __restrict__ view, Body body,
@@ -493,9 +577,21 @@ inline int32_t for_each_launch_impl(const helios_gpu_system_ctx* ctx, Body body)
 // A query with sparse-set terms (With<Tag>, Without<Tag>, sparse data) runs an instantiation that reads every row's
 // entity id and tests its membership word — kSparse = 1 when most rows are expected to pass (all loads first), 2 when
 // few are (membership first, untouched 64-row slices skip their columns); every other query runs the kernel without
-// that code.
+// that code.  A query whose rarest required sparse term covers < 1/32 of the entities is driven from that storage's dense
+// array instead (for_each_sparse_driven_kernel).
 template <uint32_t kWriteMask, bool kWithEntity, typename Body, typename... Cs>
 inline int32_t for_each_launch(const helios_gpu_system_ctx* ctx, Body body) {
+  if (ctx->sparse_filter.membership != nullptr && ctx->sparse_filter.selective == 2u && ctx->view == nullptr &&
+      ctx->match.n_tables <= uint32_t(kFusedMaxTables)) {
+    // rare required term: walk its dense array instead of the tables
+    auto kern = for_each_sparse_driven_kernel<kWriteMask, kWithEntity, Body, Cs...>;
+    const uint32_t want = (ctx->sparse_filter.drive_count + kBlock - 1) / kBlock;
+    const uint32_t grid = want < 1u ? 1u : (want > ctx->sm_count * 8u ? ctx->sm_count * 8u : want);
+    kern<<<grid, kBlock, 0, static_cast<cudaStream_t>(ctx->stream)>>>(ctx->match, body, ctx->sparse_filter, ctx->sparse.dir,
+                                                                      ctx->world_view);
+    helios_gpu_world_note_launches(ctx->world, 1);
+    return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
+  }
   if (ctx->sparse_filter.membership != nullptr)
     return ctx->sparse_filter.selective ? for_each_launch_impl<kWriteMask, kWithEntity, 2, Body, Cs...>(ctx, body)
                                         : for_each_launch_impl<kWriteMask, kWithEntity, 1, Body, Cs...>(ctx, body);

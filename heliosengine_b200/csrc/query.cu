@@ -188,6 +188,8 @@ int32_t fill_query_ctx(helios_gpu_system_ctx* ctx, helios_gpu_query* q, cudaStre
   ctx->sparse_filter.require = q->sparse_require;
   ctx->sparse_filter.exclude = q->sparse_exclude;
   ctx->sparse_filter.selective = 0;
+  ctx->sparse_filter.drive_ordinal = 0;
+  ctx->sparse_filter.drive_count = 0;
   if (ctx->sparse_filter.membership) {  // expected pass rate from the storage sizes (host mirrors are exact)
     const double live = double(std::max<uint64_t>(w->live_count, 1));
     double pass = 1.0;
@@ -197,6 +199,15 @@ int32_t fill_query_ctx(helios_gpu_system_ctx* ctx, helios_gpu_query* q, cudaStre
       if (q->sparse_exclude >> o & 1u) pass = std::min(pass, 1.0 - f);
     }
     ctx->sparse_filter.selective = pass < 0.125 ? 1u : 0u;
+    // rarest REQUIRED storage below 1/32 of the entities: drive the launch from its dense array
+    int drive = -1;
+    for (size_t o = 0; o < w->sparse.size(); ++o)
+      if ((q->sparse_require >> o & 1u) && (drive < 0 || w->sparse[o].size < w->sparse[size_t(drive)].size)) drive = int(o);
+    if (drive >= 0 && double(w->sparse[size_t(drive)].size) * 32.0 < live) {
+      ctx->sparse_filter.selective = 2u;
+      ctx->sparse_filter.drive_ordinal = uint32_t(drive);
+      ctx->sparse_filter.drive_count = uint32_t(w->sparse[size_t(drive)].size);
+    }
   }
   ctx->sparse.dir = w->d_sparse_dir.as<helios_gpu_sparse_dir>();
   std::memcpy(ctx->sparse.fetch, q->sparse_fetch, sizeof q->sparse_fetch);
@@ -308,7 +319,7 @@ int32_t helios_gpu_query_count(helios_gpu_query* q, uint64_t* out) {
   if (q->sparse_require | q->sparse_exclude) {  // Count walks the entities (query.hpp:1652-1666): per-entity sparse test
     HG_CUDA(w, q->result.reserve(sizeof(helios_gpu_terminal_result), 0, w->stream, false));
     HG_CUDA(w, cudaMemsetAsync(q->result.ptr, 0, 8, w->stream));
-    const helios_gpu_sparse_filter sf{w->d_membership.as<uint32_t>(), q->sparse_require, q->sparse_exclude, 0u, 0u};
+    const helios_gpu_sparse_filter sf{w->d_membership.as<uint32_t>(), q->sparse_require, q->sparse_exclude, 0u, 0u, 0u, 0u};
     k_count_sparse<<<uint32_t(w->sm_count) * 8, 256, 0, w->stream>>>(q->d_view.as<helios_gpu_query_view>(), sf,
                                                                       q->result.as<unsigned long long>());
     ++w->launches;

@@ -317,7 +317,10 @@ typedef struct helios_gpu_sparse_filter {
   uint32_t require;
   uint32_t exclude;
   uint32_t selective; /* hint from the storage sizes: 1 = few rows are expected to pass (for_each_launch then tests the
-                         membership words before it touches the component columns) */
+                         membership words before it touches the component columns); 2 = a required storage is so small
+                         that the launch walks ITS dense array (drive_ordinal) instead of the tables */
+  uint32_t drive_ordinal; /* selective == 2: sparse ordinal of the smallest required storage */
+  uint32_t drive_count;   /* its size when the launch was prepared (grid sizing only; the kernel reads the live size) */
   uint32_t _pad;
 } helios_gpu_sparse_filter;
 

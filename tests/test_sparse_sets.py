@@ -164,3 +164,50 @@ def _bulk_tagging(backend):
 @pytest.mark.gpu
 def test_gpu_sparse_bulk_tagging_matches_oracle(gpu, oracle):
     assert _bulk_tagging(gpu) == _bulk_tagging(oracle)
+
+
+def _rare_terms(backend, mode=capi.EXEC_SERIAL):
+    """A required sparse term carried by ~1 % of the entities: on the GPU these launches are driven from the storage's dense
+    array instead of the tables (for_each_sparse_driven_kernel); results must not depend on the driver."""
+    import struct
+    w = scenarios.sparse_world(backend, rows=(12000, 6000, 2000))
+    P, H, T = (worlds.cname(x) for x in ("Position", "Health", "Team"))
+    TAG, FROZEN, BUFF = (worlds.cname(x) for x in ("PlayerTag", "FrozenTag", "SparseBuff"))
+    ents = np.concatenate([a["entities"] for a in w.snapshot(columns=False)["archetypes"]])
+    rng = np.random.default_rng(5)
+
+    def add(es, names, values=None):
+        cmds = np.zeros(es.size, dtype=capi.COMMAND_DTYPE)
+        cmds["kind"] = capi.CMD_ADD
+        cmds["entity"] = es
+        cmds["component_mask"] = w.mask(names)
+        if values is not None:
+            cmds["payload_offset"] = np.arange(es.size, dtype=np.uint32) * 4
+        w.enqueue(cmds, values if values is not None else b"")
+        w.flush()
+
+    add(rng.permutation(ents)[:200], [TAG])
+    add(rng.permutation(ents)[:300], [BUFF], rng.integers(1, 50, size=300, dtype=np.uint32))
+    add(rng.permutation(ents)[:5000], [FROZEN])
+    s = w.schedule("Update")
+    s.add_system("regen_players", "regen", w.query([(H, True)], with_=[TAG]))
+    s.add_system("buff_heal", "buff_heal", w.query([(H, True)], without=[FROZEN], sparse_data=[BUFF]))
+    s.build()
+    out = []
+    for _ in range(3):
+        s.run_and_wait(mode)
+        out.append(scenarios.snapshot_digest(w.snapshot()))
+    q = w.query([(P, False)], with_=[TAG])
+    out.append(q.count())
+    for name, params in (("count_if_pos_x_gt", struct.pack("<f", 500.0)), ("find_pos_x_gt", struct.pack("<f", 900.0)),
+                         ("max_by_pos_x", b""), ("min_by_pos_x", b"")):
+        r = q.terminal(name, params)
+        out.append((name, r.count, r.entity))
+    w.close()
+    return out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", [capi.EXEC_SERIAL, capi.EXEC_GRAPH])
+def test_gpu_rare_sparse_terms_match_oracle(gpu, oracle, mode):
+    assert _rare_terms(gpu, mode) == _rare_terms(oracle)
