@@ -430,6 +430,54 @@ def run_sparse(args, torch, dev, stream, peak):
     }
 
 
+def run_extract(args, torch, dev, stream, peak):
+    """SubApp::Extract (SURVEY.md §8f rank 3): the cfg2 main world (16.8M entities / 64 tables); every frame the render
+    sub-world is cleared and refilled with {Position, Velocity} of the rows `With<Health>, Without<Frozen>` matches
+    (16 tables, 4.19M rows) — id placement + one device-to-device gather launch on the sub-world's stream."""
+    n = args.entities or (1 << 24)
+    gpu = capi.load_gpu()
+    main = capi.World(gpu, device=dev.index, entity_capacity=n + 1024)
+    main.set_stream(stream.cuda_stream)
+    worlds.build_lattice(main, n, worlds.OPTIONAL)
+    P, V, H, F = (worlds.cname(x) for x in ("Position", "Velocity", "Health", "Frozen"))
+    q = main.query([(P, False), (V, False)], with_=[H], without=[F])
+    rows = q.count()
+    sub = capi.World(gpu, device=dev.index, entity_capacity=rows + 1024)
+    sub.set_stream(stream.cuda_stream)
+    steps, warm = args.steps, max(3, args.warmup)
+    ms, wall = [], []
+    l0 = sub.launch_count()
+    with torch.cuda.stream(stream):
+        for i in range(warm + steps):
+            sub.clear_entities()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
+            a.record(stream)
+            got = sub.extract_from(q)
+            b.record(stream)
+            torch.cuda.synchronize()
+            if i >= warm:
+                ms.append(a.elapsed_time(b))
+                wall.append((time.perf_counter() - t0) * 1e3)
+            assert got == rows
+    launches = sub.launch_count() - l0
+    med = float(np.median(ms))
+    # per row: Position + Velocity read and written (32 B), entity id written (8), location + generation written (12)
+    bpr = 16 * 2 + 8 + 12
+    main.close()
+    sub.close()
+    return {
+        "metric": "extracted_rows_per_sec", "value": rows / (med * 1e-3), "unit": "rows/s", "ms_per_step": med,
+        "dtype": "bytes", "config": {"workload": f"extract: {rows} rows x (Position, Velocity) from 16 of 64 main-world tables into a "
+                                                 "cleared sub-world", "l2": "working set 218 MB exceeds L2; no flush"},
+        "roofline": {"bound": "hbm", "achieved": rows * bpr / (med * 1e-3) / 1e9, "peak": peak[0], "unit": "GB/s",
+                     "frac": rows * bpr / (med * 1e-3) / 1e9 / peak[0], "traffic": None, "peak_kind": peak[1],
+                     "algorithmic_bytes_per_launch": rows * bpr, "kernel": "k_match + k_place_entities + k_extract_rows (one launch for every table and column)"},
+        "host_wall_ms": float(np.median(wall)), "e2e": None, "cpu_baseline": None, "gpu_launches": int(launches),
+    }
+
+
 def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
     """Boids, STRONG scaling: `--entities` boids in total (default 64M, density 4 per cell) split by entity-id range over
     the ranks; per step: bin own shard, all-gather slabs + counts (NCCL), neighbour pass + integrate."""

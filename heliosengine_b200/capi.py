@@ -251,6 +251,23 @@ class World:
                                              _ptr(out) if out is not None else None))
         return out
 
+    def clear_entities(self):
+        """World::ClearEntities (world.hpp:974-977)."""
+        self._check(self.b.fn("world_clear_entities")(self.h))
+
+    def extract_from(self, query: "Query") -> int:
+        """SubApp::Extract with the usual body: one entity here per row `query` (of another world) visits, carrying copies
+        of its data components, in visit order.  Returns the number of entities created."""
+        for name in query.component_names:  # keep this wrapper's name tables in step (the library registers on demand too)
+            if name not in self.slots:
+                self.register_component(name, query.w.sizes[name])
+        n = C.c_uint64()
+        if self.b.is_gpu:
+            self._check(self.b.fn("extract_query")(query.h, self.h, C.byref(n)))
+        else:
+            self._check(self.b.fn("extract_query_w")(query.w.h, query.h, self.h, C.byref(n)))
+        return n.value
+
     def entity_count(self) -> int:
         v = C.c_uint64()
         self._check(self.b.fn("entity_count")(self.h, C.byref(v)))
@@ -363,6 +380,7 @@ class Query:
 
     def __init__(self, world: World, components, with_, without, sparse_data=(), sparse_rule=SPARSE_STRICT):
         self.w = world
+        self.component_names = [name for name, _ in components]
         d = QueryDesc()
         d.n_sparse_data = len(sparse_data)
         for i, name in enumerate(sparse_data):

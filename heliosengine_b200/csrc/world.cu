@@ -3,6 +3,7 @@
 // GetOrCreateArchetype (component/manager.hpp:1049-1072,1852-1891), EntityManager (entity/manager.hpp).
 #include <algorithm>
 
+#include "query_internal.hpp"
 #include "world_internal.hpp"
 
 using namespace hgpu;
@@ -298,6 +299,53 @@ int32_t place(helios_gpu_world* w, int table, const std::vector<helios_gpu_entit
   return set_table_count(w, table, tb.count + n);
 }
 
+// SubApp::Extract: every matched source table's rows of every query component into the destination columns, one launch.
+// Tiles of 1024 source rows (never crossing a table); the destination row of a source row is its flattened position.
+struct ExtractArgs {
+  const helios_gpu_query_view* view;  // the source query's materialised view (k_match)
+  uint8_t* dst[HELIOS_GPU_MAX_QUERY_COMPONENTS];  // destination column base + first new row
+  uint32_t size[HELIOS_GPU_MAX_QUERY_COMPONENTS];
+  uint32_t ncomp;
+};
+__global__ void __launch_bounds__(256) k_extract_rows(ExtractArgs a) {
+  __shared__ uint32_t s_seg;
+  const uint32_t n_tiles = a.view->n_tiles, n_seg = a.view->n_segments;
+  const helios_gpu_segment* __restrict__ segs = a.view->segments;
+  for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    __syncthreads();
+    if (threadIdx.x == 0) {  // upper_bound(tile) - 1 over the segments' first tiles
+      uint32_t lo = 0, hi = n_seg;
+      while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (segs[mid].tile_begin <= tile) lo = mid; else hi = mid;
+      }
+      s_seg = lo;
+    }
+    __syncthreads();
+    const helios_gpu_segment& sg = segs[s_seg];
+    const uint32_t row0 = (tile - sg.tile_begin) * HELIOS_GPU_TILE_ROWS;
+    const uint32_t rows = min(HELIOS_GPU_TILE_ROWS, sg.rows - row0);
+    const uint64_t drow = sg.row_begin + row0;
+    for (uint32_t k = 0; k < a.ncomp; ++k) {
+      const uint32_t sz = a.size[k];
+      const uint8_t* __restrict__ src = static_cast<const uint8_t*>(sg.columns[k]) + size_t(row0) * sz;
+      uint8_t* __restrict__ dst = a.dst[k] + drow * sz;
+      const uint32_t bytes = rows * sz;
+      if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15u) == 0) {
+        const uint32_t vecs = bytes >> 4;
+        for (uint32_t i = threadIdx.x; i < vecs; i += blockDim.x)
+          __stcs(reinterpret_cast<uint4*>(dst) + i, __ldcs(reinterpret_cast<const uint4*>(src) + i));
+        for (uint32_t i = (vecs << 4) + threadIdx.x; i < bytes; i += blockDim.x) dst[i] = src[i];
+      } else if ((sz & 3u) == 0) {
+        for (uint32_t i = threadIdx.x; i < (bytes >> 2); i += blockDim.x)
+          reinterpret_cast<uint32_t*>(dst)[i] = __ldcs(reinterpret_cast<const uint32_t*>(src) + i);
+      } else {
+        for (uint32_t i = threadIdx.x; i < bytes; i += blockDim.x) dst[i] = src[i];
+      }
+    }
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -356,6 +404,114 @@ int32_t helios_gpu_spawn_batch(helios_gpu_world* w, const uint64_t* hashes, uint
   w->flushed_index = w->next_index;
   ++w->mutation_epoch;
   HG_CUDA(w, cudaStreamSynchronize(w->stream));
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_world_clear_entities(helios_gpu_world* w) {
+  if (!w) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  cudaStream_t st = w->stream;
+  HG_CUDA(w, cudaStreamSynchronize(st));
+  // ComponentManager::ClearData (manager.hpp:1036-1046): archetypes and sparse elements go, registrations stay
+  w->tables.clear();
+  w->table_of_mask.clear();
+  w->empty_table = -1;
+  w->counts_dirty = false;
+  if (w->dir_capacity) HG_CUDA(w, cudaMemsetAsync(w->d_tcount.ptr, 0, size_t(w->dir_capacity) * 4, st));
+  for (SparseStore& s : w->sparse) {
+    s.size = 0;
+    HG_CUDA(w, cudaMemsetAsync(s.sparse.ptr, 0xFF, size_t(w->ent_capacity) * 4, st));
+  }
+  if (!w->sparse.empty()) {
+    HG_CUDA(w, cudaMemsetAsync(w->d_membership.ptr, 0, size_t(w->ent_capacity) * 4, st));
+    HG_TRY(publish_sparse_dir(w));
+  }
+  // EntityManager::Clear (entity/manager.hpp:243-249)
+  w->next_index = w->flushed_index = 0;
+  w->free_count = 0;
+  w->free_cursor = 0;
+  w->live_count = 0;
+  HG_CUDA(w, cudaMemsetAsync(w->d_gen.ptr, 0xFF, size_t(w->ent_capacity) * 4, st));
+  HG_CUDA(w, cudaMemsetAsync(w->d_loc.ptr, 0xFF, size_t(w->ent_capacity) * 8, st));
+  free_apply_scratch(w);  // cached mask hash / per-entity scratch belong to the old tables
+  ++w->epoch;
+  ++w->mutation_epoch;
+  HG_CUDA(w, cudaStreamSynchronize(st));
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_extract_query(helios_gpu_query* src, helios_gpu_world* dst, uint64_t* out_rows) {
+  if (!src || !dst) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  helios_gpu_world* sw = src->world;
+  if (sw == dst) HG_FAIL(dst, HELIOS_GPU_ERR_INVALID_ARGUMENT, "extract into the source world");
+  if (sw->device != dst->device) HG_FAIL(dst, HELIOS_GPU_ERR_INVALID_ARGUMENT, "extract across devices");
+  if (src->sparse_require | src->sparse_exclude) HG_FAIL(dst, HELIOS_GPU_ERR_INVALID_ARGUMENT, "extract of a query with sparse-set terms");
+  if (dst->next_index != dst->flushed_index)
+    HG_FAIL(dst, HELIOS_GPU_ERR_STATE, "extract while reserved entities are unflushed: call helios_gpu_world_flush first");
+  HG_TRY(sync_counts_to_host(sw));
+  // RefreshArchetypes over the host mirrors (query.hpp:1732-1812): creation order, empty tables skipped
+  std::vector<int> match;
+  uint64_t n = 0;
+  if (!src->never_matches)
+    for (size_t t = 0; t < sw->tables.size(); ++t) {
+      const Table& tb = sw->tables[t];
+      if (tb.count && (tb.mask & src->required_mask) == src->required_mask && (tb.mask & src->without_mask) == 0) {
+        match.push_back(int(t));
+        n += tb.count;
+      }
+    }
+  const uint32_t nc = src->desc.n_components;
+  int dslot[HELIOS_GPU_MAX_QUERY_COMPONENTS];
+  uint64_t mask = 0;
+  for (uint32_t k = 0; k < nc; ++k) {
+    if (src->never_matches) break;
+    const Component& c = sw->comps[size_t(src->slots[k])];
+    const int32_t s = helios_gpu_register_component(dst, c.hash, c.size, c.align, c.def.data());
+    if (s < 0) return s;
+    if (dst->comps[size_t(s)].size != c.size || (dst->sparse_slot_mask >> s & 1ull))
+      HG_FAIL(dst, HELIOS_GPU_ERR_STATE, "component %016llx is laid out differently in the destination world", (unsigned long long)c.hash);
+    dslot[k] = s;
+    mask |= 1ull << s;
+  }
+  if (out_rows) *out_rows = n;
+  HG_TRY(sync_counts_to_host(dst));
+  if (dst->empty_table < 0) HG_TRY(ensure_table(dst, 0, &dst->empty_table));
+  if (n == 0) return HELIOS_GPU_OK;
+  int t;
+  HG_TRY(ensure_table(dst, mask, &t));
+  std::vector<helios_gpu_entity_t> rec;
+  uint32_t base;
+  uint64_t fresh;
+  HG_TRY(allocate_ids(dst, n, rec, &base, &fresh));
+  uint64_t row = dst->tables[size_t(t)].count;
+  HG_TRY(place(dst, t, rec, base, fresh, nullptr));
+  // the copies run on dst's stream after everything already queued on the source world's stream (the device-side match
+  // that lists the source tables included) ...
+  HG_TRY(query_refresh(src, sw->stream));
+  cudaEvent_t ev;
+  HG_CUDA(dst, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  HG_CUDA(dst, cudaEventRecord(ev, sw->stream));
+  HG_CUDA(dst, cudaStreamWaitEvent(dst->stream, ev, 0));
+  Table& dt = dst->tables[size_t(t)];
+  ExtractArgs ea{};
+  ea.view = src->d_view.as<helios_gpu_query_view>();
+  ea.ncomp = nc;
+  for (uint32_t k = 0; k < nc; ++k) {
+    const size_t sz = sw->comps[size_t(src->slots[k])].size;
+    const size_t dci = std::find(dt.slots.begin(), dt.slots.end(), dslot[k]) - dt.slots.begin();
+    ea.dst[k] = static_cast<uint8_t*>(dt.cols[dci].ptr) + row * sz;
+    ea.size[k] = uint32_t(sz);
+  }
+  if (nc) {
+    k_extract_rows<<<uint32_t(dst->sm_count) * 8, 256, 0, dst->stream>>>(ea);
+    ++dst->launches;
+    HG_CUDA(dst, cudaGetLastError());
+  }
+  // ... and whatever the source world does next waits for them (a system may overwrite the columns in the next frame)
+  HG_CUDA(dst, cudaEventRecord(ev, dst->stream));
+  HG_CUDA(dst, cudaStreamWaitEvent(sw->stream, ev, 0));
+  HG_CUDA(dst, cudaEventDestroy(ev));
+  dst->flushed_index = dst->next_index;
+  ++dst->mutation_epoch;
   return HELIOS_GPU_OK;
 }
 

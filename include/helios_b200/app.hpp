@@ -11,6 +11,7 @@
 #pragma once
 
 #include <chrono>
+#include <functional>
 #include <map>
 #include <memory>
 #include <string>
@@ -60,12 +61,15 @@ public:
     if (it == schedules_.end()) {
       static const char* names[] = {"PreUpdate", "Update", "PostUpdate"};
       it = schedules_.emplace(label, std::make_unique<ecs::Schedule>(world_, names[static_cast<int>(label)])).first;
+      built_ = false;
     }
     return *it->second;
   }
   void Build() {
     for (auto& [l, s] : schedules_) s->Build();
+    built_ = true;
   }
+  bool Built() const noexcept { return built_; }
   // One frame of this sub-app: every schedule in label order (RunAndWait = run + ApplyDeferred), then World::Update.
   void Update() {
     for (auto& [l, s] : schedules_) s->RunAndWait();
@@ -75,16 +79,26 @@ public:
     for (auto& [l, s] : schedules_) s->SetExecutor(kind);
     kind_ = kind;
   }
+  // sub_app.hpp:148-152,425-433: the function Extract calls to copy data out of the main world before this sub-app's
+  // update (the main world is passed mutable here only because device queries are created against a World&).
+  using ExtractFn = std::function<void(ecs::World& main_world, ecs::World& sub_world)>;
+  void SetExtractFunction(ExtractFn fn) { extract_fn_ = std::move(fn); }
+  // sub_app.hpp:213-220,699-...
+  void Extract(ecs::World& main_world) {
+    if (extract_fn_) extract_fn_(main_world, world_);
+  }
 
 private:
-  ecs::World world_;  // declared first: schedules (and their queries) are destroyed before the world
+  ExtractFn extract_fn_;
+  bool built_ = false;
+  ecs::World world_;  // declared before the schedules: they (and their queries) are destroyed before the world
   std::map<ScheduleLabel, std::unique_ptr<ecs::Schedule>> schedules_;
   ecs::ExecutorKind kind_ = ecs::ExecutorKind::kMultiThreaded;
 };
 
 class App {
 public:
-  explicit App(int device = 0, uint32_t entity_capacity = 0) : main_(device, entity_capacity) {}
+  explicit App(int device = 0, uint32_t entity_capacity = 0) : device_(device), main_(device, entity_capacity) {}
   ~App() {
     for (auto it = plugins_.rbegin(); it != plugins_.rend(); ++it) (*it)->Destroy(*this);  // application.cpp DestroyPlugins
   }
@@ -131,9 +145,23 @@ public:
     main_.Build();
     initialized_ = true;
   }
+  // application.hpp AddSubApp: a world of its own, fed by its extract function after every main-world frame.
+  SubApp& AddSubApp(const std::string& name, uint32_t entity_capacity = 0) {
+    auto it = sub_apps_.find(name);
+    if (it == sub_apps_.end()) it = sub_apps_.emplace(name, std::make_unique<SubApp>(device_, entity_capacity)).first;
+    return *it->second;
+  }
+  SubApp& GetSubApp(const std::string& name) { return *sub_apps_.at(name); }
+  // scheduler.cpp:60-151: main update, then the extract stage (every sub-app copies what it needs out of the main world),
+  // then the sub-app updates.
   void Update() {
     Initialize();
     main_.Update();
+    for (auto& [name, sub] : sub_apps_) sub->Extract(main_.GetWorld());
+    for (auto& [name, sub] : sub_apps_) {
+      if (!sub->Built()) sub->Build();
+      sub->Update();
+    }
     ++frame_;
   }
   // Runs `frames` frames (the reference runs until an AppExit message; a frame budget is the headless equivalent).
@@ -144,7 +172,9 @@ public:
   uint64_t FrameCount() const noexcept { return frame_; }
 
 private:
+  int device_ = 0;
   SubApp main_;  // declared first: destroyed after the plugins
+  std::map<std::string, std::unique_ptr<SubApp>> sub_apps_;
   std::vector<std::unique_ptr<Plugin>> plugins_;
   bool initialized_ = false;
   uint64_t frame_ = 0;

@@ -176,6 +176,9 @@ public:
   // RefreshArchetypes (query.hpp:1732-1812): matched archetype indices in creation order.
   std::vector<uint32_t> MatchedArchetypes();
   helios_gpu_query* Handle() const noexcept { return q_; }
+  // The usual body of a SubApp extract function (sub_app.hpp:148-152,213-220): one entity in `dst` per visited row,
+  // carrying copies of the data components, as device-to-device column copies.  Returns the rows copied.
+  uint64_t ExtractInto(World& dst);
 
   // ---- terminals (query.hpp:180,822,1040-1180) as device reductions -----------------------------------------------------
   // `launch` is a terminal written against helios_gpu_terminals.cuh (reduce_launch<> / partition_launch<>) or a
@@ -347,6 +350,7 @@ public:
     return n;
   }
 
+  void ClearEntities() { Check(helios_gpu_world_clear_entities(w_)); }  // world.hpp:974-977
   void Flush() { Check(helios_gpu_world_flush(w_)); }    // world.hpp:957-963
   void Update() { Check(helios_gpu_world_update(w_)); }  // world.hpp:950-955
 
@@ -432,6 +436,12 @@ Query<Args...>::Query(World& world, SparseRule rule) : world_(&world) {
   helios_gpu_query_desc d = Describe();
   d.sparse_rule = static_cast<uint32_t>(rule);
   world.Check(helios_gpu_query_create(world.Handle(), &d, &q_));
+}
+template <typename... Args>
+uint64_t Query<Args...>::ExtractInto(World& dst) {
+  uint64_t n = 0;
+  dst.Check(helios_gpu_extract_query(q_, dst.Handle(), &n));
+  return n;
 }
 template <typename... Args>
 uint64_t Query<Args...>::Count() {

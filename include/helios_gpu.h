@@ -108,6 +108,9 @@ HELIOS_GPU_API int32_t helios_gpu_spawn_batch(helios_gpu_world* w, const uint64_
                                               uint64_t n, const void* const* columns,
                                               helios_gpu_entity_t* out_entities /* may be NULL */);
 HELIOS_GPU_API int32_t helios_gpu_entity_count(helios_gpu_world* w, uint64_t* out);
+/* World::ClearEntities (world.hpp:974-977): every entity, archetype table and sparse-set element goes (ids restart at 0);
+ * component / message registrations, queries and schedules stay. */
+HELIOS_GPU_API int32_t helios_gpu_world_clear_entities(helios_gpu_world* w);
 
 /* ---- snapshot (parity I/O; the reference has no serializer — SURVEY §5 "checkpoint": none) -------
  * Canonical dump: archetypes in creation order; per archetype the sorted type-hash list, the entity
@@ -176,6 +179,13 @@ HELIOS_GPU_API int32_t helios_gpu_query_destroy(helios_gpu_query* q);
  * empty tables skipped.  Copies the matched archetype indices back for parity checks. */
 HELIOS_GPU_API int32_t helios_gpu_query_match(helios_gpu_query* q, uint32_t* out_archetypes, uint32_t capacity,
                                               uint32_t* out_count);
+/* SubApp::Extract (src/app/include/helios/app/sub_app.hpp:213-220,699-...; driven by src/app/src/scheduler.cpp:141-151,
+ * 204-237) with the extract function's usual body: for every row `src` visits, in visit order,
+ * `e = dst.CreateEntity(); dst.AddComponents(e, copies of the row's data components)` — executed as device-to-device column
+ * copies on dst's stream, ordered after the work already queued on the source world's stream (and the source world's later
+ * work after the copies).  dst learns the component types on demand.  Both worlds live on the same device; queries with
+ * sparse-set terms are not accepted yet.  *out_rows = entities created. */
+HELIOS_GPU_API int32_t helios_gpu_extract_query(helios_gpu_query* src, helios_gpu_world* dst, uint64_t* out_rows);
 /* Query::Count (query.hpp:1652-1666). */
 HELIOS_GPU_API int32_t helios_gpu_query_count(helios_gpu_query* q, uint64_t* out);
 

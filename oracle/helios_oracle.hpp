@@ -664,6 +664,17 @@ public:
     return a;
   }
 
+  // manager.hpp:1036-1046 ClearData — entities, archetypes and sparse elements go; registrations stay
+  void ClearData() {
+    entity_archetype_.clear();
+    archetype_map_.clear();
+    archetype_list_.clear();
+    storage_.clear();
+    for (auto& kv : sparse_) kv.second.Clear();
+    empty_archetype_ = nullptr;
+    ++structural_version_;
+  }
+
   void ClearAll() {
     entity_archetype_.clear();
     archetype_map_.clear();
@@ -1140,6 +1151,11 @@ public:
     return e;
   }
   Entity ReserveEntity() { return entities.ReserveEntity(); }
+  // world.hpp:974-977
+  void ClearEntities() {
+    components.ClearData();
+    entities.Clear();
+  }
   // world.hpp:986-994
   void DestroyEntity(Entity e) {
     if (!entities.Validate(e)) { ++invalid_command_count; return; }  // reference: HELIOS_ASSERT

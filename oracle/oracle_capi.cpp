@@ -401,6 +401,36 @@ HO_API int32_t helios_oracle_spawn_batch(void* wp, const uint64_t* hashes, uint3
   w->faithful.reset();
   return 0;
 }
+HO_API int32_t helios_oracle_world_clear_entities(void* wp) {
+  W(wp)->world.ClearEntities();
+  W(wp)->faithful.reset();
+  return 0;
+}
+// SubApp::Extract with the usual extract-function body (sub_app.hpp:213-220,699-...): for every row the main-world query
+// visits, in visit order, `e = sub.CreateEntity(); sub.AddComponents(e, copies of the row's data components)`.
+HO_API int32_t helios_oracle_extract_query_w(void* src_wp, void* qp, void* dst_wp, uint64_t* out_rows) {
+  OWorld* sw = W(src_wp);
+  OWorld* dw = W(dst_wp);
+  const ho::QueryDesc& q = reinterpret_cast<OQuery*>(qp)->desc;
+  for (const ho::TypeIndex t : q.required) {  // the sub-world learns the component types on demand
+    const ho::ComponentMeta* m = sw->world.components.Meta(t);
+    if (m && !dw->world.components.Meta(t)) {
+      dw->world.components.Register(*m);
+      dw->slot_hash.push_back(t);
+    }
+  }
+  uint64_t n = 0;
+  std::vector<ho::CompValue> cv(q.required.size());
+  ho::ForEach(sw->world.components, q, [&](ho::Entity, uint8_t** p) {
+    const ho::Entity e = dw->world.CreateEntity();
+    for (size_t k = 0; k < cv.size(); ++k) cv[k] = {q.required[k], p[k]};
+    if (!cv.empty()) dw->world.AddComponents(e, cv.data(), cv.size());
+    ++n;
+  });
+  if (out_rows) *out_rows = n;
+  dw->faithful.reset();
+  return 0;
+}
 HO_API int32_t helios_oracle_entity_count(void* wp, uint64_t* out) {
   *out = W(wp)->world.EntityCount();
   return 0;

@@ -215,6 +215,32 @@ int main(int argc, char** argv) {
     world.DestroyEntity(ents[2]);  // leaves every sparse storage (manager.hpp:1090-1093)
     CHECK(tagged.Count() == 0 && !world.HasComponent<SparseBuff>(ents[2]) && world.HasComponent<SparseBuff>(ents[4]));
   }
+  // ---- SubApp::Extract (sub_app.hpp:213-220; scheduler.cpp:141-151): a render sub-app rebuilt from the main world each frame ----
+  {
+    app::App application;
+    ecs::World& main_world = application.GetWorld();
+    std::vector<Position> pos;
+    std::vector<Velocity> vel;
+    for (int i = 0; i < 300; ++i) { pos.push_back(Position{float(i), 0}); vel.push_back(Velocity{1.0f, 2.0f}); }
+    main_world.SpawnBatch<Position, Velocity>(pos.size(), std::span<const Position>(pos), std::span<const Velocity>(vel));
+    main_world.SpawnBatch<Position>(50, std::span<const Position>(pos.data(), 50));  // no Velocity: not extracted
+    helios_gpu_system_fn integrate = nullptr;
+    main_world.Check(helios_gpu_builtin_system("integrate", &integrate));
+    application.AddSystem<ecs::Query<Position&, const Velocity&>>(app::kUpdate, "ChangePosition", integrate);
+    ecs::Query<const Position&, const Velocity&> moving(main_world);
+    app::SubApp& render = application.AddSubApp("Render");
+    render.SetExtractFunction([&moving](ecs::World&, ecs::World& sub) {
+      sub.ClearEntities();
+      moving.ExtractInto(sub);
+    });
+    application.Run(2);
+    ecs::World& sub = render.GetWorld();
+    CHECK(sub.EntityCount() == 300 && sub.ArchetypeCount() == 2);
+    // ids restart at 0 after ClearEntities; row i is a copy of main row i after two frames of p += v
+    CHECK(sub.ReadComponent<Position>(ecs::Entity{7, 1}).x == 9.0f && sub.ReadComponent<Position>(ecs::Entity{7, 1}).y == 4.0f);
+    CHECK(sub.ReadComponent<Velocity>(ecs::Entity{299, 1}).dy == 2.0f);
+    CHECK(main_world.EntityCount() == 350);
+  }
   std::printf("shim_test gpu: %d checks, %d failed\n", g_checks, g_fail);
   return g_fail;
 }
