@@ -101,6 +101,19 @@ class SystemDesc(C.Structure):
     ]
 
 
+COND_CUSTOM, COND_TERMINAL, COND_RESOURCE, COND_MESSAGES, COND_CONSTANT = 0, 1, 2, 3, 4
+COND_FIELD_VISITED, COND_FIELD_COUNT, COND_FIELD_INDEX, COND_FIELD_I64 = 0, 1, 2, 5
+CMP_EQ, CMP_NE, CMP_LT, CMP_LE, CMP_GT, CMP_GE = 0, 1, 2, 3, 4, 5
+
+
+class ConditionDesc(C.Structure):
+    _fields_ = [
+        ("name", C.c_char_p), ("kind", C.c_uint32), ("cmp", C.c_uint32), ("rhs", C.c_uint64),
+        ("field", C.c_uint32), ("offset", C.c_uint32), ("query", C.c_void_p), ("launch", C.c_void_p),
+        ("params", C.c_void_p), ("params_size", C.c_uint32), ("_pad", C.c_uint32), ("reads_message", C.c_uint64),
+    ]
+
+
 class HeliosError(RuntimeError):
     def __init__(self, status: int, message: str):
         super().__init__(f"status {status}: {message}")
@@ -512,6 +525,44 @@ class Schedule:
         self.w._check(self.w.b.fn("schedule_add_system")(self.h, C.byref(d), C.byref(idx)))
         self.names.append(name)
         return idx.value
+
+    def _condition(self, name: str, kind: int, cmp: int = CMP_NE, rhs: int = 0, field: int = 0, offset: int = 0,
+                   query: "Query | None" = None, builtin: str | None = None, params: bytes = b"",
+                   reads_message: str | None = None) -> ConditionDesc:
+        d = ConditionDesc()
+        nm = name.encode()
+        pb = C.create_string_buffer(params, len(params)) if params else None
+        self._keep += [nm, pb]
+        d.name, d.kind, d.cmp, d.rhs, d.field, d.offset = nm, kind, cmp, rhs & 0xFFFFFFFFFFFFFFFF, field, offset
+        d.query = query.h if query is not None else None
+        if builtin is not None:
+            fnp = C.c_void_p()
+            st = self.w.b.fn("builtin_condition")(builtin.encode(), C.byref(fnp))
+            if st != OK:
+                raise HeliosError(st, f"no builtin condition '{builtin}'")
+            d.launch = fnp
+        d.params = C.cast(pb, C.c_void_p) if pb is not None else None
+        d.params_size = len(params)
+        d.reads_message = fnv1a(reads_message) if reads_message else 0
+        return d
+
+    def run_if(self, system: int, name: str, kind: int, **kw):
+        """SystemHandle::RunIf (reference schedule/system_handle.hpp; run_condition.hpp:23-58)."""
+        d = self._condition(name, kind, **kw)
+        self.w._check(self.w.b.fn("schedule_add_run_condition")(self.h, C.c_uint32(system), C.byref(d)))
+
+    def set_run_if(self, set_id: int, name: str, kind: int, **kw):
+        """SystemSet::RunIf (reference schedule/system_set.hpp)."""
+        d = self._condition(name, kind, **kw)
+        self.w._check(self.w.b.fn("schedule_add_set_condition")(self.h, C.c_uint64(set_id), C.byref(d)))
+
+    def in_set(self, system: int, set_id: int):
+        self.w._check(self.w.b.fn("schedule_system_in_set")(self.h, C.c_uint32(system), C.c_uint64(set_id)))
+
+    def last_verdicts(self) -> list[int]:
+        out = (C.c_uint32 * 64)()
+        self.w._check(self.w.b.fn("schedule_last_verdicts")(self.h, out, C.c_uint32(64)))
+        return [int(out[i]) for i in range(len(self.names))]
 
     def add_order(self, first: int, second: int):
         self.w._check(self.w.b.fn("schedule_add_order")(self.h, C.c_uint32(first), C.c_uint32(second)))

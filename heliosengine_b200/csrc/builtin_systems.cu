@@ -305,10 +305,28 @@ int32_t launch_despawn_dead(const helios_gpu_system_ctx* ctx) {
   return for_each_launch<0u, true, DespawnDeadBody, Health>(ctx, DespawnDeadBody{ctx->commands});
 }
 
+// ---- run condition "entity_alive": a WorldView-style predicate (run_condition.cpp:72-74, world_view.hpp Exists):
+// the guarded system runs only while the entity named in params is alive.  HELIOS_GPU_COND_CUSTOM: veto = store 0. -------
+__global__ void k_cond_entity_alive(uint32_t* verdict, helios_gpu_world_view wv, helios_gpu_entity_t e) {
+  const uint32_t idx = uint32_t(e), gen = uint32_t(e >> 32);
+  const bool alive = e != HELIOS_GPU_INVALID_ENTITY && idx < wv.entity_capacity && gen != 0xFFFFFFFFu &&
+                     wv.entity_generation[idx] == gen;
+  if (!alive) *verdict = 0u;
+}
+int32_t launch_cond_entity_alive(const helios_gpu_system_ctx* ctx) {
+  if (!ctx->verdict || ctx->params_size < sizeof(helios_gpu_entity_t)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  helios_gpu_entity_t e;
+  std::memcpy(&e, ctx->params, sizeof(e));
+  k_cond_entity_alive<<<1, 1, 0, static_cast<cudaStream_t>(ctx->stream)>>>(ctx->verdict, ctx->world_view, e);
+  helios_gpu_world_note_launches(ctx->world, 1);
+  return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
+}
+
 struct Entry {
   const char* name;
   helios_gpu_system_fn fn;
 };
+const Entry kConditions[] = {{"entity_alive", launch_cond_entity_alive}};
 const Entry kBuiltins[] = {
     {"integrate", launch_integrate},   {"accel_integrate", launch_accel_integrate},
     {"damp", launch_damp},             {"regen", launch_regen},
@@ -320,6 +338,20 @@ const Entry kBuiltins[] = {
 };
 
 }  // namespace
+
+extern "C" int32_t helios_gpu_builtin_condition(const char* name, helios_gpu_system_fn* out) {
+  if (!name || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  for (const Entry& e : kConditions)
+    if (std::strcmp(e.name, name) == 0) {
+      *out = e.fn;
+      return HELIOS_GPU_OK;
+    }
+  // any reduction-style query terminal can serve as a HELIOS_GPU_COND_TERMINAL condition
+  uint32_t flags = 0;
+  if (helios_gpu_builtin_terminal(name, out, &flags) == HELIOS_GPU_OK && flags == 0) return HELIOS_GPU_OK;
+  *out = nullptr;
+  return HELIOS_GPU_ERR_NOT_FOUND;
+}
 
 extern "C" int32_t helios_gpu_builtin_system(const char* name, helios_gpu_system_fn* out) {
   if (!name || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;

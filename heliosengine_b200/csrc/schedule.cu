@@ -5,6 +5,7 @@
 // a Taskflow task per system with conflict-only edges becomes a stream per independent chain with
 // event fork/join on exactly those edges, optionally captured once into a CUDA graph and replayed.
 #include <algorithm>
+#include <map>
 #include <queue>
 
 #include "query_internal.hpp"
@@ -34,11 +35,26 @@ struct Policy {  // sorted unique type-hash sets
   }
 };
 
+// RunConditionStorage (schedule/run_condition.hpp:23-58) as a device predicate.
+struct CondEntry {
+  std::string name;
+  helios_gpu_condition_desc desc{};
+  std::vector<uint8_t> params;
+  DevBuf result;  // TERMINAL: the helios_gpu_terminal_result the terminal leaves behind
+};
+
 struct SysEntry {
   std::string name;
   helios_gpu_system_desc desc{};
   std::vector<uint8_t> params;
   Policy policy;
+  // run conditions: own list (SystemHandle::RunIf), set membership (InSet), and the merged list of the last build
+  std::vector<std::unique_ptr<CondEntry>> conds;
+  std::vector<uint64_t> sets;
+  std::vector<CondEntry*> merged;
+  cudaGraphExec_t cond_exec = nullptr;  // stream modes: {conditions, IF{body}} as a one-system graph
+  uint64_t cond_epoch = ~0ull;
+  uint64_t cond_kernels = 0;
   // SystemLocalData (schedule/system_local_data.hpp:23-31) in HBM
   DevBuf cmd_records, cmd_payload;
   uint64_t cmd_capacity = 0;       // record slots allocated
@@ -68,6 +84,10 @@ struct helios_gpu_schedule {
   std::vector<uint64_t> conflicts;                       // by position in `order`
   bool built = false;
   DevBuf resources;
+  DevBuf verdicts;                                       // u32 per registration index: 1 = ran, 0 = skipped
+  std::map<uint64_t, std::vector<std::unique_ptr<CondEntry>>> set_conds;  // SystemSet::RunIf
+  cudaStream_t body_stream = nullptr;                    // captures IF bodies
+  bool any_conditions = false;
   // stream mapping
   std::vector<cudaStream_t> streams;                     // streams[0] == world stream
   std::vector<cudaEvent_t> done;                         // one per position
@@ -112,6 +132,31 @@ int32_t prepare(helios_gpu_schedule* s) {
     HG_CUDA(w, cudaMemsetAsync(s->resources.ptr, 0, HELIOS_GPU_RESOURCE_BYTES, w->stream));
     ++w->epoch;
   }
+  if (!s->verdicts.ptr) {
+    HG_CUDA(w, s->verdicts.reserve(64 * sizeof(uint32_t), 0, w->stream, false));
+    ++w->epoch;
+  }
+  if (s->any_conditions) {
+    if (!s->body_stream) HG_CUDA(w, cudaStreamCreateWithFlags(&s->body_stream, cudaStreamNonBlocking));
+    for (auto& ep : s->entries)
+      for (CondEntry* c : ep->merged) {
+        if (c->desc.kind == HELIOS_GPU_COND_TERMINAL && !c->result.ptr) {
+          HG_CUDA(w, c->result.reserve(sizeof(helios_gpu_terminal_result), 0, w->stream, false));
+          ++w->epoch;
+        }
+        if (c->desc.kind == HELIOS_GPU_COND_MESSAGES && !find_channel(w, c->desc.reads_message))
+          HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "run condition '%s' reads an unregistered message type", c->name.c_str());
+        helios_gpu_query* q = c->desc.query;
+        if (q && (q->seg_capacity < w->dir_capacity || q->seg_capacity == 0)) {
+          const uint32_t cap = std::max<uint32_t>(w->dir_capacity, 64u);
+          HG_CUDA(w, q->d_segments.reserve(size_t(cap) * sizeof(helios_gpu_segment), 0, w->stream, false));
+          q->seg_capacity = cap;
+          ++w->epoch;
+        }
+      }
+  }
+  // every system starts a run as "ran"; a guarded system's condition chain overwrites its word
+  HG_CUDA(w, cudaMemsetAsync(s->verdicts.ptr, 0x01, 64 * sizeof(uint32_t), w->stream));
   for (auto& ep : s->entries) {
     SysEntry& e = *ep;
     const uint64_t rows = host_match_rows(w, e.desc.query);
@@ -163,7 +208,7 @@ int32_t prepare(helios_gpu_schedule* s) {
 }
 
 // Enqueue one system on `stream`: arm its local buffers, device-side match, then the body.
-int32_t launch_system(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaStream_t stream) {
+int32_t launch_body(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaStream_t stream) {
   helios_gpu_world* w = s->world;
   helios_gpu_system_ctx ctx{};
   ctx.world = w;
@@ -226,6 +271,166 @@ int32_t launch_system(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaS
   const int32_t st = e.desc.launch(&ctx);
   if (st != HELIOS_GPU_OK) HG_FAIL(w, st, "system '%s' failed to launch (%d): %s", e.name.c_str(), st,
                                    cudaGetErrorString(cudaGetLastError()));
+  return HELIOS_GPU_OK;
+}
+
+// ---- run conditions ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool cond_compare(uint64_t lhs, uint64_t rhs, uint32_t cmp, bool is_signed) {
+  if (is_signed) {
+    const long long a = static_cast<long long>(lhs), b = static_cast<long long>(rhs);
+    switch (cmp) {
+      case HELIOS_GPU_CMP_LT: return a < b;
+      case HELIOS_GPU_CMP_LE: return a <= b;
+      case HELIOS_GPU_CMP_GT: return a > b;
+      case HELIOS_GPU_CMP_GE: return a >= b;
+      default: break;
+    }
+  }
+  switch (cmp) {
+    case HELIOS_GPU_CMP_EQ: return lhs == rhs;
+    case HELIOS_GPU_CMP_NE: return lhs != rhs;
+    case HELIOS_GPU_CMP_LT: return lhs < rhs;
+    case HELIOS_GPU_CMP_LE: return lhs <= rhs;
+    case HELIOS_GPU_CMP_GT: return lhs > rhs;
+    default: return lhs >= rhs;
+  }
+}
+__global__ void k_cond_begin(uint32_t* verdict) { *verdict = 1u; }
+// lhs = *a (+ *b when given): a resource word, a terminal-result field, or previous + current message counts
+__global__ void k_cond_test(uint32_t* verdict, const unsigned long long* a, const unsigned long long* b, uint32_t cmp,
+                            uint64_t rhs, uint32_t is_signed) {
+  const uint64_t lhs = (a ? *a : 0ull) + (b ? *b : 0ull);
+  if (!cond_compare(lhs, rhs, cmp, is_signed != 0)) *verdict = 0u;
+}
+// the verdict becomes the IF node's condition value (defaults to 0 at every graph launch)
+__global__ void k_cond_commit(cudaGraphConditionalHandle handle, const uint32_t* verdict) {
+  cudaGraphSetConditional(handle, *verdict ? 1u : 0u);
+}
+
+// One condition on `stream`: AND its predicate into *verdict.
+int32_t eval_condition(helios_gpu_schedule* s, SysEntry& e, uint32_t index, CondEntry& c, uint32_t* verdict,
+                       cudaStream_t stream) {
+  helios_gpu_world* w = s->world;
+  const helios_gpu_condition_desc& d = c.desc;
+  switch (d.kind) {
+    case HELIOS_GPU_COND_CONSTANT:
+      k_cond_test<<<1, 1, 0, stream>>>(verdict, nullptr, nullptr, HELIOS_GPU_CMP_NE, d.rhs ? 1ull : 0ull, 0u);  // 0 != (rhs != 0)
+      ++w->launches;
+      break;
+    case HELIOS_GPU_COND_RESOURCE:
+      k_cond_test<<<1, 1, 0, stream>>>(verdict, reinterpret_cast<const unsigned long long*>(s->resources.as<uint8_t>() + d.offset),
+                                       nullptr, d.cmp, d.rhs, 0u);
+      ++w->launches;
+      break;
+    case HELIOS_GPU_COND_MESSAGES: {
+      auto* dev = find_channel(w, d.reads_message)->d_dev.as<ChannelDev>();
+      k_cond_test<<<1, 1, 0, stream>>>(verdict, &dev->counts[0], &dev->counts[1], d.cmp, d.rhs, 0u);
+      ++w->launches;
+      break;
+    }
+    case HELIOS_GPU_COND_TERMINAL:
+    case HELIOS_GPU_COND_CUSTOM: {
+      helios_gpu_system_ctx ctx{};
+      ctx.world = w;
+      ctx.stream = stream;
+      ctx.sm_count = uint32_t(w->sm_count);
+      ctx.query_rows = HELIOS_GPU_NO_ROW;
+      ctx.world_view.entity_location = w->d_loc.as<uint64_t>();
+      ctx.world_view.entity_generation = w->d_gen.as<uint32_t>();
+      ctx.world_view.table_columns = w->d_tcols.as<void*>();
+      ctx.world_view.table_mask = w->d_tmask.as<uint64_t>();
+      ctx.world_view.entity_capacity = w->ent_capacity;
+      ctx.world_view.n_tables = uint32_t(w->tables.size());
+      if (d.query) {
+        HG_TRY(fill_query_ctx(&ctx, d.query, stream, false));
+        ctx.scratch = d.query->scratch.ptr;
+        ctx.scratch_bytes = d.query->scratch.bytes;
+      }
+      ctx.system_index = index;
+      ctx.params = c.params.data();
+      ctx.params_size = uint32_t(c.params.size());
+      ctx.verdict = verdict;
+      ctx.resources = d.kind == HELIOS_GPU_COND_TERMINAL ? c.result.ptr : s->resources.ptr;
+      const int32_t st = d.launch(&ctx);
+      if (st != HELIOS_GPU_OK) HG_FAIL(w, st, "run condition '%s' of system '%s' failed to launch (%d)", c.name.c_str(), e.name.c_str(), st);
+      if (d.kind == HELIOS_GPU_COND_TERMINAL) {
+        k_cond_test<<<1, 1, 0, stream>>>(verdict, c.result.as<unsigned long long>() + d.field, nullptr, d.cmp, d.rhs,
+                                         d.field == HELIOS_GPU_COND_FIELD_I64 ? 1u : 0u);
+        ++w->launches;
+      }
+      break;
+    }
+    default:
+      HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition '%s': unknown kind %u", c.name.c_str(), d.kind);
+  }
+  HG_CUDA(w, cudaGetLastError());
+  return HELIOS_GPU_OK;
+}
+
+// `stream` is capturing: conditions as ordinary nodes, then an IF node whose body graph holds the system.
+int32_t emit_guarded(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaStream_t stream) {
+  helios_gpu_world* w = s->world;
+  uint32_t* verdict = s->verdicts.as<uint32_t>() + index;
+  k_cond_begin<<<1, 1, 0, stream>>>(verdict);
+  ++w->launches;
+  for (CondEntry* c : e.merged) HG_TRY(eval_condition(s, e, index, *c, verdict, stream));
+  cudaStreamCaptureStatus status = cudaStreamCaptureStatusNone;
+  cudaGraph_t graph = nullptr;
+  const cudaGraphNode_t* deps = nullptr;
+  size_t n_deps = 0;
+  HG_CUDA(w, cudaStreamGetCaptureInfo(stream, &status, nullptr, &graph, &deps, &n_deps));
+  if (status != cudaStreamCaptureStatusActive || !graph) HG_FAIL(w, HELIOS_GPU_ERR_STATE, "guarded system outside a capture");
+  cudaGraphConditionalHandle handle;
+  HG_CUDA(w, cudaGraphConditionalHandleCreate(&handle, graph, 0u, cudaGraphCondAssignDefault));
+  k_cond_commit<<<1, 1, 0, stream>>>(handle, verdict);
+  ++w->launches;
+  HG_CUDA(w, cudaGetLastError());
+  HG_CUDA(w, cudaStreamGetCaptureInfo(stream, &status, nullptr, &graph, &deps, &n_deps));
+  cudaGraphNodeParams np{};
+  np.type = cudaGraphNodeTypeConditional;
+  np.conditional.handle = handle;
+  np.conditional.type = cudaGraphCondTypeIf;
+  np.conditional.size = 1;
+  cudaGraphNode_t node = nullptr;
+  HG_CUDA(w, cudaGraphAddNode(&node, graph, deps, n_deps, &np));
+  cudaGraph_t body = np.conditional.phGraph_out[0];
+  HG_CUDA(w, cudaStreamUpdateCaptureDependencies(stream, &node, 1, cudaStreamSetCaptureDependencies));
+  HG_CUDA(w, cudaStreamBeginCaptureToGraph(s->body_stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+  const int32_t st = launch_body(s, e, index, s->body_stream);
+  cudaGraph_t ended = nullptr;
+  const cudaError_t ce = cudaStreamEndCapture(s->body_stream, &ended);
+  if (st != HELIOS_GPU_OK) return st;
+  if (ce != cudaSuccess) HG_FAIL(w, HELIOS_GPU_ERR_CUDA, "capture of the guarded body of '%s' failed: %s", e.name.c_str(), cudaGetErrorString(ce));
+  return HELIOS_GPU_OK;
+}
+
+// A system with run conditions.  Inside a schedule-wide capture (HELIOS_GPU_EXEC_GRAPH) the IF node joins that graph; in
+// the stream modes the system gets its own small graph, re-captured only when a buffer it bakes in has moved.
+int32_t launch_system(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaStream_t stream) {
+  if (e.merged.empty()) return launch_body(s, e, index, stream);
+  helios_gpu_world* w = s->world;
+  cudaStreamCaptureStatus status = cudaStreamCaptureStatusNone;
+  HG_CUDA(w, cudaStreamIsCapturing(stream, &status));
+  if (status == cudaStreamCaptureStatusActive) return emit_guarded(s, e, index, stream);
+  if (!e.cond_exec || e.cond_epoch != w->epoch) {
+    if (e.cond_exec) { cudaGraphExecDestroy(e.cond_exec); e.cond_exec = nullptr; }
+    const uint64_t launches_before = w->launches;
+    HG_CUDA(w, cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+    const int32_t st = emit_guarded(s, e, index, stream);
+    cudaGraph_t g = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(stream, &g);
+    if (st != HELIOS_GPU_OK) { if (g) cudaGraphDestroy(g); return st; }
+    if (ce != cudaSuccess) HG_FAIL(w, HELIOS_GPU_ERR_CUDA, "capture of guarded system '%s' failed: %s", e.name.c_str(), cudaGetErrorString(ce));
+    const cudaError_t ie = cudaGraphInstantiate(&e.cond_exec, g, 0);
+    cudaGraphDestroy(g);
+    if (ie != cudaSuccess) HG_FAIL(w, HELIOS_GPU_ERR_CUDA, "instantiate of guarded system '%s' failed: %s", e.name.c_str(), cudaGetErrorString(ie));
+    e.cond_epoch = w->epoch;
+    e.cond_kernels = w->launches - launches_before;
+    w->launches = launches_before;
+  }
+  HG_CUDA(w, cudaGraphLaunch(e.cond_exec, stream));
+  w->launches += e.cond_kernels;
+  if (!e.policy.wc.empty()) ++w->mutation_epoch;
   return HELIOS_GPU_OK;
 }
 
@@ -323,6 +528,9 @@ int32_t helios_gpu_schedule_destroy(helios_gpu_schedule* s) {
   for (cudaEvent_t e : s->done) cudaEventDestroy(e);
   if (s->fork_ev) cudaEventDestroy(s->fork_ev);
   if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
+  for (auto& e : s->entries)
+    if (e->cond_exec) cudaGraphExecDestroy(e->cond_exec);
+  if (s->body_stream) cudaStreamDestroy(s->body_stream);
   auto& v = w->schedules;
   v.erase(std::remove(v.begin(), v.end(), s), v.end());
   delete s;
@@ -400,8 +608,84 @@ int32_t helios_gpu_schedule_build(helios_gpu_schedule* s) {
         s->conflicts[j] |= 1ull << i;
       }
   assign_streams(s);
+  // MergeRunConditions (schedule.cpp:427-461): the system's own conditions, then those of each set it belongs to
+  s->any_conditions = false;
+  for (auto& ep : s->entries) {
+    ep->merged.clear();
+    for (auto& c : ep->conds) ep->merged.push_back(c.get());
+    for (const uint64_t set_id : ep->sets) {
+      const auto it = s->set_conds.find(set_id);
+      if (it == s->set_conds.end()) continue;
+      for (auto& c : it->second) ep->merged.push_back(c.get());
+    }
+    ep->cond_epoch = ~0ull;
+    s->any_conditions = s->any_conditions || !ep->merged.empty();
+  }
   s->built = true;
   s->graph_epoch = ~0ull;
+  return HELIOS_GPU_OK;
+}
+
+static int32_t make_condition(helios_gpu_schedule* s, const helios_gpu_condition_desc* d, std::unique_ptr<CondEntry>& out) {
+  helios_gpu_world* w = s->world;
+  if (d->kind > HELIOS_GPU_COND_CONSTANT || d->cmp > HELIOS_GPU_CMP_GE)
+    HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition: unknown kind or comparison");
+  if ((d->kind == HELIOS_GPU_COND_CUSTOM || d->kind == HELIOS_GPU_COND_TERMINAL) && !d->launch)
+    HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition: a custom / terminal condition needs a launch function");
+  if (d->kind == HELIOS_GPU_COND_TERMINAL && (!d->query || d->field > HELIOS_GPU_COND_FIELD_I64))
+    HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition: a terminal condition needs a query and a result field");
+  if (d->kind == HELIOS_GPU_COND_RESOURCE && (d->offset % 8 != 0 || d->offset + 8 > HELIOS_GPU_RESOURCE_BYTES))
+    HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition: resource offset must be an 8-byte word inside the block");
+  if (d->kind == HELIOS_GPU_COND_MESSAGES && !d->reads_message)
+    HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition: a message condition needs reads_message");
+  out = std::make_unique<CondEntry>();
+  out->name = d->name ? d->name : "";
+  out->desc = *d;
+  out->desc.name = nullptr;
+  if (d->params && d->params_size)
+    out->params.assign(static_cast<const uint8_t*>(d->params), static_cast<const uint8_t*>(d->params) + d->params_size);
+  out->desc.params = nullptr;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_add_run_condition(helios_gpu_schedule* s, uint32_t system_index, const helios_gpu_condition_desc* d) {
+  if (!s || !d) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (system_index >= s->entries.size()) HG_FAIL(s->world, HELIOS_GPU_ERR_NOT_FOUND, "RunIf: unknown system %u", system_index);
+  std::unique_ptr<CondEntry> c;
+  HG_TRY(make_condition(s, d, c));
+  s->entries[system_index]->conds.push_back(std::move(c));
+  s->built = false;  // RunIf marks the schedule dirty (tests/schedule/system_set_handle.cpp:190-224)
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_add_set_condition(helios_gpu_schedule* s, uint64_t set_id, const helios_gpu_condition_desc* d) {
+  if (!s || !d) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  std::unique_ptr<CondEntry> c;
+  HG_TRY(make_condition(s, d, c));
+  s->set_conds[set_id].push_back(std::move(c));
+  s->built = false;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_system_in_set(helios_gpu_schedule* s, uint32_t system_index, uint64_t set_id) {
+  if (!s) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (system_index >= s->entries.size()) HG_FAIL(s->world, HELIOS_GPU_ERR_NOT_FOUND, "InSet: unknown system %u", system_index);
+  auto& sets = s->entries[system_index]->sets;
+  if (std::find(sets.begin(), sets.end(), set_id) == sets.end()) sets.push_back(set_id);
+  s->built = false;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_last_verdicts(helios_gpu_schedule* s, uint32_t* out, uint32_t capacity) {
+  if (!s || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  helios_gpu_world* w = s->world;
+  const uint32_t n = uint32_t(s->entries.size());
+  if (capacity < n) return HELIOS_GPU_ERR_CAPACITY;
+  if (!s->verdicts.ptr) { std::fill(out, out + n, 1u); return HELIOS_GPU_OK; }
+  uint32_t host[64];
+  HG_CUDA(w, cudaMemcpyAsync(host, s->verdicts.ptr, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
+  HG_CUDA(w, cudaStreamSynchronize(w->stream));
+  for (uint32_t i = 0; i < n; ++i) out[i] = host[i] ? 1u : 0u;
   return HELIOS_GPU_OK;
 }
 

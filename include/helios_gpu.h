@@ -384,6 +384,9 @@ typedef struct helios_gpu_system_ctx {
   /* sparse-set terms of the query (filter applied by for_each_launch) and the fetch view */
   helios_gpu_sparse_filter sparse_filter;
   helios_gpu_sparse_view sparse;
+  /* run conditions (below): DEVICE pointer to the u32 verdict of the system being guarded, 1 when the first condition
+   * starts; a HELIOS_GPU_COND_CUSTOM launch stores 0 to veto.  NULL for system bodies. */
+  uint32_t* verdict;
 } helios_gpu_system_ctx;
 #define HELIOS_GPU_RESOURCE_BYTES 4096u
 
@@ -443,6 +446,59 @@ HELIOS_GPU_API int32_t helios_gpu_schedule_run_and_wait(helios_gpu_schedule* s, 
 HELIOS_GPU_API int32_t helios_gpu_schedule_stream_count(helios_gpu_schedule* s, uint32_t* out);
 /* Copy the schedule's device resource scratch (HELIOS_GPU_RESOURCE_BYTES) to the host. */
 HELIOS_GPU_API int32_t helios_gpu_schedule_read_resources(helios_gpu_schedule* s, void* out, uint32_t bytes);
+
+/* ---- run conditions (schedule/run_condition.hpp:17-58; SystemHandle::RunIf / SystemSet::RunIf; merged per system by
+ * Schedule::MergeRunConditions, src/ecs/src/schedule/schedule.cpp:427-461; evaluated by every executor right before the
+ * system, first `false` skips it: executor/main_thread.cpp:38-52, multi_threaded.cpp:52-71) ---------------------------
+ * On the GPU a condition is evaluated ON THE DEVICE, on the system's own stream, and the system's body sits inside a CUDA
+ * graph IF node (cudaGraphCondTypeIf) keyed on the verdict: a skipped system launches nothing and the host never reads
+ * the verdict back.  A skipped system leaves its local data empty (no commands, no messages, nothing consumed), exactly
+ * like a reference system whose callable was not invoked.  As in the reference (schedule.cpp:371-421 uses only the
+ * system's own policy) a condition's reads add no conflict edges: it is ordered like the system it guards.
+ * The reference stops at the first false condition; here every condition of the list is evaluated and AND-ed — the
+ * same verdict for predicates without side effects, which is all a device predicate can be. */
+#define HELIOS_GPU_COND_CUSTOM 0u   /* `launch` enqueues kernels on ctx->stream that store 0 to *ctx->verdict to veto */
+#define HELIOS_GPU_COND_TERMINAL 1u /* `launch` is a query terminal over `query`; test one field of its result */
+#define HELIOS_GPU_COND_RESOURCE 2u /* test the u64 at byte `offset` of the schedule's resource block (Res<const T>) */
+#define HELIOS_GPU_COND_MESSAGES 3u /* test the number of messages a MessageReader<reads_message> would see */
+#define HELIOS_GPU_COND_CONSTANT 4u /* verdict = (rhs != 0): AlwaysTrue / AlwaysFalse */
+#define HELIOS_GPU_COND_FIELD_VISITED 0u /* byte offsets/8 into helios_gpu_terminal_result */
+#define HELIOS_GPU_COND_FIELD_COUNT 1u
+#define HELIOS_GPU_COND_FIELD_INDEX 2u
+#define HELIOS_GPU_COND_FIELD_I64 5u
+#define HELIOS_GPU_CMP_EQ 0u
+#define HELIOS_GPU_CMP_NE 1u
+#define HELIOS_GPU_CMP_LT 2u
+#define HELIOS_GPU_CMP_LE 3u
+#define HELIOS_GPU_CMP_GT 4u
+#define HELIOS_GPU_CMP_GE 5u
+typedef struct helios_gpu_condition_desc {
+  const char* name;
+  uint32_t kind;               /* HELIOS_GPU_COND_* */
+  uint32_t cmp;                /* HELIOS_GPU_CMP_*: verdict = (lhs cmp rhs) */
+  uint64_t rhs;
+  uint32_t field;              /* TERMINAL: HELIOS_GPU_COND_FIELD_* (I64 compares signed) */
+  uint32_t offset;             /* RESOURCE: byte offset, multiple of 8 */
+  helios_gpu_query* query;     /* TERMINAL (its own query object: terminals reduce through the query's scratch) */
+  helios_gpu_system_fn launch; /* CUSTOM / TERMINAL */
+  const void* params;          /* copied at registration, handed to `launch` */
+  uint32_t params_size;
+  uint32_t _pad;
+  uint64_t reads_message;      /* MESSAGES */
+} helios_gpu_condition_desc;
+/* SystemHandle::RunIf (schedule/system_handle.hpp): appended to the system's own condition list. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_add_run_condition(helios_gpu_schedule* s, uint32_t system_index,
+                                                             const helios_gpu_condition_desc* desc);
+/* SystemSet::RunIf / SystemHandle::InSet (schedule/system_set.hpp): a set's conditions apply to every member, after
+ * the member's own conditions, sets in membership order (schedule.cpp:446-459).  `set_id` is any caller-chosen id. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_add_set_condition(helios_gpu_schedule* s, uint64_t set_id,
+                                                             const helios_gpu_condition_desc* desc);
+HELIOS_GPU_API int32_t helios_gpu_schedule_system_in_set(helios_gpu_schedule* s, uint32_t system_index, uint64_t set_id);
+/* Built-in condition launch functions by name: "entity_alive" (CUSTOM; params = one helios_gpu_entity_t) and every
+ * reduction-style built-in terminal (TERMINAL). */
+HELIOS_GPU_API int32_t helios_gpu_builtin_condition(const char* name, helios_gpu_system_fn* out);
+/* After apply_deferred: out[i] = 1 if system i (registration index) ran in the last run, 0 if a condition skipped it. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_last_verdicts(helios_gpu_schedule* s, uint32_t* out, uint32_t capacity);
 
 
 /* ---- query terminals (query/query.hpp:1040-1180: Find / Any / All / None / CountIf / Fold / MinBy / MaxBy / Partition,

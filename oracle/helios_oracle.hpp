@@ -1341,6 +1341,8 @@ struct SystemLocalData {
 };
 
 using SystemFn = std::function<void(World&, SystemLocalData&)>;
+// schedule/run_condition.hpp:17-21 — bool(World&, SystemLocalData&); the local data of a condition is its own.
+using RunCondition = std::function<bool(World&)>;
 
 class Schedule {
 public:
@@ -1349,12 +1351,25 @@ public:
     SystemFn fn;
     AccessPolicy policy;
     SystemLocalData local;
+    std::vector<RunCondition> conditions;  // SystemHandle::RunIf, in call order
+    std::vector<uint64_t> sets;            // SystemHandle::InSet, in call order
+    bool ran_last = true;
   };
   size_t Add(std::string name, SystemFn fn, AccessPolicy policy) {
-    entries_.push_back(std::make_unique<Entry>(Entry{std::move(name), std::move(fn), std::move(policy), {}}));
+    entries_.push_back(std::make_unique<Entry>(Entry{std::move(name), std::move(fn), std::move(policy), {}, {}, {}, true}));
     before_.emplace_back();
     return entries_.size() - 1;
   }
+  // SystemHandle::RunIf / SystemSet::RunIf / SystemHandle::InSet — all mark the schedule dirty
+  // (tests/schedule/system_set_handle.cpp:190-224).
+  void RunIf(size_t system, RunCondition c) { entries_[system]->conditions.push_back(std::move(c)); dirty_ = true; }
+  void SetRunIf(uint64_t set_id, RunCondition c) { set_conditions_[set_id].push_back(std::move(c)); dirty_ = true; }
+  void InSet(size_t system, uint64_t set_id) {
+    auto& v = entries_[system]->sets;
+    if (std::find(v.begin(), v.end(), set_id) == v.end()) v.push_back(set_id);
+    dirty_ = true;
+  }
+  bool Dirty() const noexcept { return dirty_; }
   // explicit ordering constraint: `a` runs before `b`.
   void Order(size_t a, size_t b) { before_[a].push_back(b); }
 
@@ -1373,7 +1388,32 @@ public:
           conflicts_[i] |= (1ULL << j);
           conflicts_[j] |= (1ULL << i);
         }
+    // schedule.cpp:427-461 MergeRunConditions: per execution slot, the system's own conditions, then the conditions of
+    // every set it is a member of (membership order).  Condition access policies add no conflicts (:371-421).
+    merged_.assign(entries_.size(), {});
+    for (size_t i = 0; i < entries_.size(); ++i) {
+      for (auto& c : entries_[i]->conditions) merged_[i].push_back(&c);
+      for (const uint64_t set_id : entries_[i]->sets) {
+        const auto it = set_conditions_.find(set_id);
+        if (it == set_conditions_.end()) continue;
+        for (auto& c : it->second) merged_[i].push_back(&c);
+      }
+    }
+    dirty_ = false;
     return true;
+  }
+  // executor/main_thread.cpp:38-52 (same in single_threaded.cpp:53-67, multi_threaded.cpp:52-71): conditions in merged
+  // order, the first false one skips the system (its callable is not invoked; later conditions are not evaluated).
+  bool ShouldRun(size_t i, World& w) const {
+    if (i >= merged_.size()) return true;
+    for (const RunCondition* c : merged_[i])
+      if (!(*c)(w)) return false;
+    return true;
+  }
+  void RunSystem(size_t i, World& w) {
+    Entry& e = *entries_[i];
+    e.ran_last = ShouldRun(i, w);
+    if (e.ran_last) e.fn(w, e.local);
   }
   const std::vector<size_t>& ExecutionOrder() const noexcept { return order_; }
   // conflict bitmask indexed by POSITION in execution order (schedule.cpp:371-395).
@@ -1382,7 +1422,7 @@ public:
   // RunAndWait with the main-thread executor (executor/main_thread.cpp:14-56): systems in execution
   // order; conflicting systems are ordered by it, non-conflicting ones commute on disjoint data.
   void RunAndWait(World& w) {
-    for (const size_t i : order_) entries_[i]->fn(w, entries_[i]->local);
+    for (const size_t i : order_) RunSystem(i, w);
     ApplyDeferred(w);
   }
   // schedule.cpp:106-115 — world.Flush(); then every entry in REGISTRATION order.
@@ -1398,6 +1438,9 @@ private:
   std::vector<std::vector<size_t>> before_;
   std::vector<size_t> order_;
   std::vector<uint64_t> conflicts_;
+  std::map<uint64_t, std::vector<RunCondition>> set_conditions_;
+  std::vector<std::vector<const RunCondition*>> merged_;  // by registration index
+  bool dirty_ = true;
 };
 
 }  // namespace helios_oracle

@@ -1034,6 +1034,83 @@ void TestApplyOrder() {
   CHECK(GetAs<Position>(w.components, e, kPos).x == 20.0f);
 }
 
+// ---- schedule/schedule.cpp:559-597,900-945; schedule/system_set_handle.cpp:190-224; executor/main_thread.cpp:38-52 ------------
+void TestRunConditions() {
+  {  // "System with passing run condition executes" / "System with failing run condition is skipped" (schedule.cpp:559-597)
+    for (const bool verdict : {true, false}) {
+      World w;
+      int counter = 0;  // CounterResource
+      Schedule s;
+      const size_t h = s.Add("IncrementSystem", [&](World&, SystemLocalData&) { ++counter; }, {});
+      s.RunIf(h, [verdict](World&) { return verdict; });
+      CHECK(s.Build());
+      s.RunAndWait(w);
+      CHECK(counter == (verdict ? 1 : 0));
+      CHECK(s.At(h).ran_last == verdict);
+    }
+  }
+  {  // "System run condition survives double Build" (schedule.cpp:903-919)
+    World w;
+    int counter = 0;
+    Schedule s;
+    const size_t h = s.Add("IncrementSystem", [&](World&, SystemLocalData&) { ++counter; }, {});
+    s.RunIf(h, [](World&) { return true; });
+    CHECK(s.Build());
+    CHECK(s.Build());
+    s.RunAndWait(w);
+    CHECK(counter == 1);
+  }
+  {  // "Set RunIf conditions apply to all members after double Build" (schedule.cpp:921-945)
+    World w;
+    int counter = 0;
+    Schedule s;
+    constexpr uint64_t kSetA = 1;
+    s.SetRunIf(kSetA, [](World&) { return true; });
+    const size_t first = s.Add("IncrementSystem", [&](World&, SystemLocalData&) { ++counter; }, {});
+    const size_t second = s.Add("IncrementSystem", [&](World&, SystemLocalData&) { ++counter; }, {});
+    s.InSet(first, kSetA);
+    s.InSet(second, kSetA);
+    CHECK(s.Build());
+    CHECK(s.Build());
+    s.RunAndWait(w);
+    CHECK(counter == 2);
+  }
+  {  // RunIf / Set RunIf / InSet mark the schedule dirty (system_set_handle.cpp:190-224, system_set.cpp:183-216)
+    Schedule s;
+    const size_t h = s.Add("A", [](World&, SystemLocalData&) {}, {});
+    CHECK(s.Build());
+    CHECK(!s.Dirty());
+    s.RunIf(h, [](World&) { return true; });
+    CHECK(s.Dirty());
+    CHECK(s.Build());
+    s.SetRunIf(7, [](World&) { return true; });
+    CHECK(s.Dirty());
+    CHECK(s.Build());
+    s.InSet(h, 7);
+    CHECK(s.Dirty());
+  }
+  {  // main_thread.cpp:38-52: own conditions first, then set conditions; the first false one ends the evaluation and the
+     // system's callable is not invoked — its local data stays empty, so ApplyDeferred applies nothing for it
+    World w;
+    RegisterAll(w.components);
+    std::vector<int> trace;
+    Schedule s;
+    const size_t h = s.Add("Spawner", [&](World& world, SystemLocalData& l) {
+      trace.push_back(99);
+      l.cmd_queue.Enqueue(Command{CmdKind::kDestroy, world.CreateEntity(), {}, {}});
+    }, {});
+    s.InSet(h, 5);
+    s.SetRunIf(5, [&](World&) { trace.push_back(3); return true; });
+    s.RunIf(h, [&](World&) { trace.push_back(1); return true; });
+    s.RunIf(h, [&](World&) { trace.push_back(2); return false; });
+    CHECK(s.Build());
+    s.RunAndWait(w);
+    CHECK((trace == std::vector<int>{1, 2}));
+    CHECK(w.entities.Count() == 0);
+    CHECK(s.At(h).local.cmd_queue.Empty());
+  }
+}
+
 }  // namespace
 
 int main() {
@@ -1049,6 +1126,7 @@ int main() {
   TestConsumedMessages();
   TestScheduling();
   TestApplyOrder();
+  TestRunConditions();
   std::printf("oracle KATs: %d checks, %d failed\n", g_checks, g_fail);
   return g_fail;
 }

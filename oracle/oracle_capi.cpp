@@ -725,6 +725,112 @@ HO_API int32_t helios_oracle_schedule_add_system(void* sp, const helios_gpu_syst
   s->built = false;
   return 0;
 }
+// ---- run conditions (schedule/run_condition.hpp; schedule.cpp:427-461; executor/main_thread.cpp:38-52) ----------------
+// Same descriptor as the GPU library; `launch` carries the NAME of the built-in (as for terminals).
+HO_API int32_t helios_oracle_builtin_condition(const char* name, const char** out) {
+  static const char* const kNames[] = {"entity_alive"};
+  for (const char* n : kNames)
+    if (std::strcmp(n, name) == 0) { *out = n; return 0; }
+  uint32_t flags = 0;
+  if (helios_oracle_builtin_terminal(name, out, &flags) == 0 && flags == 0) return 0;
+  return HELIOS_GPU_ERR_NOT_FOUND;
+}
+namespace {
+bool o_compare(uint64_t lhs, uint64_t rhs, uint32_t cmp, bool is_signed) {
+  if (is_signed) {
+    const int64_t a = int64_t(lhs), b = int64_t(rhs);
+    switch (cmp) {
+      case HELIOS_GPU_CMP_LT: return a < b;
+      case HELIOS_GPU_CMP_LE: return a <= b;
+      case HELIOS_GPU_CMP_GT: return a > b;
+      case HELIOS_GPU_CMP_GE: return a >= b;
+      default: break;
+    }
+  }
+  switch (cmp) {
+    case HELIOS_GPU_CMP_EQ: return lhs == rhs;
+    case HELIOS_GPU_CMP_NE: return lhs != rhs;
+    case HELIOS_GPU_CMP_LT: return lhs < rhs;
+    case HELIOS_GPU_CMP_LE: return lhs <= rhs;
+    case HELIOS_GPU_CMP_GT: return lhs > rhs;
+    default: return lhs >= rhs;
+  }
+}
+int32_t o_make_condition(OSchedule* s, const helios_gpu_condition_desc* d, ho::RunCondition& out) {
+  if (d->kind > HELIOS_GPU_COND_CONSTANT || d->cmp > HELIOS_GPU_CMP_GE) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if ((d->kind == HELIOS_GPU_COND_CUSTOM || d->kind == HELIOS_GPU_COND_TERMINAL) && !d->launch) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (d->kind == HELIOS_GPU_COND_TERMINAL && (!d->query || d->field > HELIOS_GPU_COND_FIELD_I64)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (d->kind == HELIOS_GPU_COND_RESOURCE && (d->offset % 8 != 0 || d->offset + 8 > HELIOS_GPU_RESOURCE_BYTES)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (d->kind == HELIOS_GPU_COND_MESSAGES && !d->reads_message) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  const helios_gpu_condition_desc desc = *d;
+  std::vector<uint8_t> params;
+  if (d->params && d->params_size)
+    params.assign(static_cast<const uint8_t*>(d->params), static_cast<const uint8_t*>(d->params) + d->params_size);
+  const std::string fn_name = (d->kind == HELIOS_GPU_COND_CUSTOM || d->kind == HELIOS_GPU_COND_TERMINAL)
+                                  ? std::string(reinterpret_cast<const char*>(d->launch)) : std::string();
+  out = [s, desc, params, fn_name](ho::World& world) -> bool {
+    switch (desc.kind) {
+      case HELIOS_GPU_COND_CONSTANT: return desc.rhs != 0;
+      case HELIOS_GPU_COND_RESOURCE: {
+        uint64_t v;
+        std::memcpy(&v, s->resources.data() + desc.offset, 8);
+        return o_compare(v, desc.rhs, desc.cmp, false);
+      }
+      case HELIOS_GPU_COND_MESSAGES: {  // what a MessageReader<T> sees: previous ++ current (message/reader.hpp:770-820)
+        const uint64_t n = world.messages.Previous().Count(desc.reads_message) + world.messages.Current().Count(desc.reads_message);
+        return o_compare(n, desc.rhs, desc.cmp, false);
+      }
+      case HELIOS_GPU_COND_TERMINAL: {
+        helios_gpu_terminal_result r{};
+        if (helios_oracle_query_terminal_w(s->w, desc.query, fn_name.c_str(), params.data(), uint32_t(params.size()), 0, &r) != 0)
+          return false;
+        uint64_t words[6];
+        std::memcpy(words, &r, sizeof(words));
+        return o_compare(words[desc.field], desc.rhs, desc.cmp, desc.field == HELIOS_GPU_COND_FIELD_I64);
+      }
+      default: {  // CUSTOM
+        if (fn_name == "entity_alive" && params.size() >= 8) {
+          helios_gpu_entity_t e;
+          std::memcpy(&e, params.data(), 8);
+          return world.entities.Validate(ho::Entity::Unpack(e));
+        }
+        return false;
+      }
+    }
+  };
+  return 0;
+}
+}  // namespace
+HO_API int32_t helios_oracle_schedule_add_run_condition(void* sp, uint32_t system, const helios_gpu_condition_desc* d) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  if (system >= s->entries.size()) return HELIOS_GPU_ERR_NOT_FOUND;
+  ho::RunCondition c;
+  if (const int32_t rc = o_make_condition(s, d, c)) return rc;
+  s->sched.RunIf(system, std::move(c));
+  s->built = false;
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_add_set_condition(void* sp, uint64_t set_id, const helios_gpu_condition_desc* d) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  ho::RunCondition c;
+  if (const int32_t rc = o_make_condition(s, d, c)) return rc;
+  s->sched.SetRunIf(set_id, std::move(c));
+  s->built = false;
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_system_in_set(void* sp, uint32_t system, uint64_t set_id) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  if (system >= s->entries.size()) return HELIOS_GPU_ERR_NOT_FOUND;
+  s->sched.InSet(system, set_id);
+  s->built = false;
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_last_verdicts(void* sp, uint32_t* out, uint32_t capacity) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  if (capacity < s->entries.size()) return HELIOS_GPU_ERR_CAPACITY;
+  for (size_t i = 0; i < s->entries.size(); ++i) out[i] = s->sched.At(i).ran_last ? 1u : 0u;
+  return 0;
+}
 HO_API int32_t helios_oracle_schedule_add_order(void* sp, uint32_t a, uint32_t b) {
   auto* s = reinterpret_cast<OSchedule*>(sp);
   if (a >= s->entries.size() || b >= s->entries.size()) return HELIOS_GPU_ERR_NOT_FOUND;
@@ -757,7 +863,8 @@ HO_API int32_t helios_oracle_schedule_conflicts(void* sp, uint64_t* out, uint32_
 }
 HO_API int32_t helios_oracle_schedule_run(void* sp, uint32_t) {
   auto* s = reinterpret_cast<OSchedule*>(sp);
-  for (const size_t i : s->sched.ExecutionOrder()) s->sched.At(i).fn(s->w->world, s->sched.At(i).local);
+  if (!s->built) return HELIOS_GPU_ERR_STATE;  // schedule.cpp:56-58: Run on a dirty schedule
+  for (const size_t i : s->sched.ExecutionOrder()) s->sched.RunSystem(i, s->w->world);
   return 0;
 }
 HO_API int32_t helios_oracle_schedule_apply_deferred(void* sp) {
@@ -767,7 +874,7 @@ HO_API int32_t helios_oracle_schedule_apply_deferred(void* sp) {
   return 0;
 }
 HO_API int32_t helios_oracle_schedule_run_and_wait(void* sp, uint32_t m) {
-  helios_oracle_schedule_run(sp, m);
+  if (const int32_t rc = helios_oracle_schedule_run(sp, m)) return rc;
   return helios_oracle_schedule_apply_deferred(sp);
 }
 HO_API int32_t helios_oracle_schedule_read_resources(void* sp, void* out, uint32_t bytes) {

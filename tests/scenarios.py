@@ -257,6 +257,71 @@ def sparse_sets(backend, seed=11, frames=4, n_cmd=90, mode=capi.EXEC_SERIAL):
     return out
 
 
+def run_conditions(backend, n=4099, frames=6, mode=capi.EXEC_SERIAL):
+    """Run conditions (run_condition.hpp; schedule.cpp:427-461; executor/main_thread.cpp:38-52) of every kind, evaluated on
+    the device: verdicts flip from frame to frame because of what the guarded systems themselves do.
+      S1 damp     — own: CountIf(pos.x > 512) > its initial value (a query terminal as the predicate); set MOVE: constant true
+      S2 regen    — Res: last frame's Σhp (written by S5) below a threshold -> stops once the world has healed
+      S3 consume  — MessageReader non-empty
+      S4 despawn  — WorldView: a sentinel entity is alive (the host destroys it before frame 3)
+      S6 ghost    — member of set OFF (constant false): never runs, its integrate never moves anything
+      S7 detect   — emits only while the channel is empty -> runs every other frame
+    Recorded per frame: which systems ran, message counts, resources, world digest."""
+    w = capi.World(backend)
+    shorts = ["Position", "Velocity", "Health", "Team"]
+    worlds.register_all(w, shorts)
+    w.spawn_batch([worlds.cname(x) for x in shorts], n, [worlds.column(x, n, 6100 + i) for i, x in enumerate(shorts)],
+                  want_entities=False)
+    T_ = worlds.cname("Team")
+    sentinel = w.spawn_batch([T_], 1, [worlds.column("Team", 1, 6200)])
+    sentinel = int(np.asarray(sentinel).reshape(-1)[0])
+    w.message_register(worlds.COLLISION_EVENT, 24)
+    P, V, H, T = (worlds.cname(x) for x in shorts)
+    hp0 = int(worlds.column("Health", n, 6102).astype(np.int64).sum())
+    probe = w.query([(P, False)])
+    count0 = probe.count_if_pos_x_gt(512.0)
+    MOVE, OFF = 11, 12
+    s = w.schedule("Update")
+    s0 = s.add_system("S0_integrate", "integrate", w.query([(P, True), (V, False)]))
+    s1 = s.add_system("S1_damp", "damp", w.query([(V, True)]), params=struct.pack("<f", 0.5))
+    s2 = s.add_system("S2_regen", "regen", w.query([(H, True)]), read_resources=["helios::bench::Stats"])
+    s3 = s.add_system("S3_consume", "consume", None, params=struct.pack("<I", w.slots[H]), reads_message=worlds.COLLISION_EVENT,
+                      extra_writes=[H])
+    s4 = s.add_system("S4_despawn_dead", "despawn_dead", w.query([(H, False)]), flags=capi.SYSTEM_EMITS_COMMANDS)
+    s.add_system("S5_stats", "stats", w.query([(H, False)]), write_resources=["helios::bench::Stats"])
+    s6 = s.add_system("S6_ghost", "integrate", w.query([(P, True), (V, False)]))
+    s7 = s.add_system("S7_detect", "detect", w.query([(P, False), (T, False)]), writes_message=worlds.COLLISION_EVENT)
+    s.set_run_if(MOVE, "AlwaysTrue", capi.COND_CONSTANT, rhs=1)
+    s.set_run_if(OFF, "AlwaysFalse", capi.COND_CONSTANT, rhs=0)
+    s.in_set(s0, MOVE)
+    s.in_set(s1, MOVE)
+    s.in_set(s6, MOVE)
+    s.in_set(s6, OFF)
+    s.run_if(s1, "MoreOnTheRight", capi.COND_TERMINAL, builtin="count_if_pos_x_gt", query=w.query([(P, False)]),
+             params=struct.pack("<f", 512.0), field=capi.COND_FIELD_COUNT, cmp=capi.CMP_GT, rhs=count0)
+    s.run_if(s2, "NotHealedYet", capi.COND_RESOURCE, offset=0, cmp=capi.CMP_LT, rhs=hp0 - hp0 // 8)
+    s.run_if(s3, "HasEvents", capi.COND_MESSAGES, reads_message=worlds.COLLISION_EVENT, cmp=capi.CMP_GT, rhs=0)
+    s.run_if(s4, "SentinelAlive", capi.COND_CUSTOM, builtin="entity_alive", params=struct.pack("<Q", sentinel))
+    s.run_if(s7, "ChannelEmpty", capi.COND_MESSAGES, reads_message=worlds.COLLISION_EVENT, cmp=capi.CMP_EQ, rhs=0)
+    s.build()
+    out = {"order": s.execution_order(), "count0": count0}
+    for frame in range(frames):
+        if frame == 3:
+            cmds = np.zeros(1, dtype=capi.COMMAND_DTYPE)
+            cmds[0]["kind"] = capi.CMD_DESTROY
+            cmds[0]["entity"] = sentinel
+            w.enqueue(cmds)
+            w.flush()
+        s.run_and_wait(mode)
+        out[f"frame{frame}_ran"] = s.last_verdicts()
+        out[f"frame{frame}_counts_after_run"] = list(w.message_counts(worlds.COLLISION_EVENT))
+        w.update()
+        out[f"frame{frame}_resources"] = s.read_resources(16).tobytes().hex()
+        out[f"frame{frame}_world"] = snapshot_digest(w.snapshot())
+    w.close()
+    return out
+
+
 SCENARIOS = {
     "cfg1_n4099": lambda b: cfg1(b),
     "cfg1_n1": lambda b: cfg1(b, n=1),
@@ -268,4 +333,5 @@ SCENARIOS = {
     "churn_small_s3": lambda b: churn_small(b, seed=3),
     "sparse_sets": lambda b: sparse_sets(b),
     "churn_small_s11": lambda b: churn_small(b, seed=11),
+    "run_conditions": lambda b: run_conditions(b),
 }
