@@ -384,6 +384,34 @@ class World:
         self._check(self.b.fn("message_read")(self.h, C.c_uint64(fnv1a(name)), C.c_uint32(which), _ptr(buf), C.c_uint64(buf.nbytes)))
         return buf
 
+    # ---- async messages (reference message/async_queue.hpp; MessageManager::WriteAsync / ManualAsyncClear) ----
+    def async_message_register(self, name: str, size: int, capacity: int = 1024):
+        self._check(self.b.fn("async_message_register")(self.h, C.c_uint64(fnv1a(name)), C.c_uint32(size), C.c_uint64(capacity)))
+        self.sizes["async:" + name] = size
+
+    def async_message_write(self, name: str, data: np.ndarray):
+        size = self.sizes["async:" + name]
+        buf = np.ascontiguousarray(data).view(np.uint8).reshape(-1)
+        self._check(self.b.fn("async_message_write")(self.h, C.c_uint64(fnv1a(name)), _ptr(buf) if buf.size else None,
+                                                      C.c_uint64(buf.size // size)))
+
+    def async_message_dequeue(self, name: str, max_count: int = 1 << 62) -> np.ndarray:
+        """AsyncMessageReader<T>::Into(out, max_count): the dequeued messages as raw bytes, queue order."""
+        size = self.sizes["async:" + name]
+        want = min(max_count, self.async_message_size(name))
+        buf = np.zeros(max(1, want) * size, dtype=np.uint8)
+        n = C.c_uint64()
+        self._check(self.b.fn("async_message_dequeue")(self.h, C.c_uint64(fnv1a(name)), _ptr(buf), C.c_uint64(want), C.byref(n)))
+        return buf[: n.value * size]
+
+    def async_message_size(self, name: str) -> int:
+        n = C.c_uint64()
+        self._check(self.b.fn("async_message_size")(self.h, C.c_uint64(fnv1a(name)), C.byref(n)))
+        return n.value
+
+    def async_message_clear(self, name: str | None = None):
+        self._check(self.b.fn("async_message_clear")(self.h, C.c_uint64(fnv1a(name) if name else 0)))
+
     def schedule(self, name: str = "Update") -> "Schedule":
         return Schedule(self, name)
 

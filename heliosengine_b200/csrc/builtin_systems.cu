@@ -305,6 +305,51 @@ int32_t launch_despawn_dead(const helios_gpu_system_ctx* ctx) {
   return for_each_launch<0u, true, DespawnDeadBody, Health>(ctx, DespawnDeadBody{ctx->commands});
 }
 
+// ---- async messages: "alert_low_health" Query<const Health&> + AsyncMessageWriter<LowHealthAlert> (hp < t → Write), and
+// "heal_alerted" AsyncMessageReader<LowHealthAlert>: drains at most max_count alerts (Into) and heals their entities -------
+struct LowHealthAlert {  // 16 B
+  helios_gpu_entity_t who;
+  int32_t hp;
+  uint32_t pad;
+};
+struct AlertParams { uint64_t type_hash; int32_t threshold; uint32_t health_slot; uint64_t max_count; };
+struct AlertBody {
+  helios_gpu_async_ring ring;
+  int32_t threshold;
+  __device__ void operator()(const Row& r, Health& h) const {
+    helios_gpu::async_push(ring, h.hp < threshold, LowHealthAlert{r.entity, h.hp, 0u});
+  }
+};
+int32_t launch_alert_low_health(const helios_gpu_system_ctx* ctx) {
+  if (ctx->params_size < sizeof(AlertParams)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  AlertParams p;
+  std::memcpy(&p, ctx->params, sizeof(p));
+  helios_gpu_async_ring ring;
+  if (const int32_t rc = helios_gpu_async_message_view(ctx->world, p.type_hash, &ring)) return rc;
+  return for_each_launch<0u, true, AlertBody, Health>(ctx, AlertBody{ring, p.threshold});
+}
+struct HealAlertedBody {
+  helios_gpu_world_view wv;
+  uint32_t health_slot;
+  __device__ void operator()(unsigned long long, const LowHealthAlert& a) const {
+    const uint32_t idx = uint32_t(a.who), gen = uint32_t(a.who >> 32);
+    if (idx >= wv.entity_capacity || wv.entity_generation[idx] != gen) return;  // stale entity: World::TryGet → null
+    const uint64_t loc = wv.entity_location[idx];
+    if (loc == 0xFFFFFFFFFFFFFFFFull) return;
+    int32_t* col = static_cast<int32_t*>(wv.table_columns[(loc >> 32) * 64 + health_slot]);
+    if (col) atomicAdd(col + uint32_t(loc), 10 + (a.hp & 3));
+  }
+};
+int32_t launch_heal_alerted(const helios_gpu_system_ctx* ctx) {
+  if (ctx->params_size < sizeof(AlertParams)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  AlertParams p;
+  std::memcpy(&p, ctx->params, sizeof(p));
+  helios_gpu_async_ring ring;
+  if (const int32_t rc = helios_gpu_async_message_view(ctx->world, p.type_hash, &ring)) return rc;
+  return helios_gpu::async_drain_launch<LowHealthAlert>(ctx, ring, HealAlertedBody{ctx->world_view, p.health_slot},
+                                                        p.max_count ? p.max_count : ~0ull);
+}
+
 // ---- run condition "entity_alive": a WorldView-style predicate (run_condition.cpp:72-74, world_view.hpp Exists):
 // the guarded system runs only while the entity named in params is alive.  HELIOS_GPU_COND_CUSTOM: veto = store 0. -------
 __global__ void k_cond_entity_alive(uint32_t* verdict, helios_gpu_world_view wv, helios_gpu_entity_t e) {
@@ -335,6 +380,7 @@ const Entry kBuiltins[] = {
     {"consume_strong", launch_consume_strong}, {"buff_heal", launch_buff_heal}, {"buff_optional", launch_buff_optional},
     {"stats", launch_stats},           {"exit_check", launch_exit_check},
     {"despawn_dead", launch_despawn_dead},
+    {"alert_low_health", launch_alert_low_health}, {"heal_alerted", launch_heal_alerted},
 };
 
 }  // namespace

@@ -632,6 +632,53 @@ __device__ __forceinline__ void message_append(const helios_gpu_msg_writer& wr, 
   if (slot < wr.capacity) reinterpret_cast<Msg*>(wr.data)[slot] = m;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Async messages (message/async_queue.hpp; AsyncMessageWriter::Write, async_writer.hpp:60-94; AsyncMessageReader::Into /
+// Dequeue, async_reader.hpp:60-131) over a helios_gpu_async_ring.
+// ---------------------------------------------------------------------------------------------------
+// Enqueue from any thread of any kernel: one atomic on the ring's tail per warp.
+template <typename Msg>
+__device__ __forceinline__ void async_push(const helios_gpu_async_ring& ring, bool active, const Msg& m) {
+  const uint32_t mask = __ballot_sync(__activemask(), active);
+  if (!active) return;
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t leader = __ffs(mask) - 1;
+  unsigned long long base = 0;
+  if (lane == leader) base = atomicAdd(ring.cursors + 1, (unsigned long long)__popc(mask));
+  base = __shfl_sync(mask, base, leader);
+  const unsigned long long pos = base + __popc(mask & ((1u << lane) - 1u));
+  // a full ring is reported by the next host call (tail - head > capacity); never write over undrained messages
+  if (pos - *reinterpret_cast<const volatile unsigned long long*>(ring.cursors) < ring.capacity)
+    reinterpret_cast<Msg*>(ring.data)[pos & (ring.capacity - 1)] = m;
+}
+
+template <typename Msg, typename Body>
+__global__ void __launch_bounds__(256) async_drain_kernel(helios_gpu_async_ring ring, unsigned long long max_count, Body body) {
+  const unsigned long long head = ring.cursors[0], tail = ring.cursors[1];
+  unsigned long long n = tail - head;
+  if (n > ring.capacity) n = ring.capacity;
+  if (n > max_count) n = max_count;
+  for (unsigned long long i = blockIdx.x * 256ull + threadIdx.x; i < n; i += gridDim.x * 256ull)
+    body(i, reinterpret_cast<const Msg*>(ring.data)[(head + i) & (ring.capacity - 1)]);
+}
+static __global__ void async_advance_kernel(helios_gpu_async_ring ring, unsigned long long max_count) {
+  const unsigned long long head = ring.cursors[0], tail = ring.cursors[1];
+  unsigned long long n = tail - head;
+  if (n > max_count) n = max_count;
+  ring.cursors[0] = head + n;
+}
+// AsyncMessageReader<T>::Into(max_count) as a launch: body(i, msg) runs once for each of the first max_count queued
+// messages (i = position in queue order), which are then removed.  Two launches: the drain and the head update.
+template <typename Msg, typename Body>
+inline int32_t async_drain_launch(const helios_gpu_system_ctx* ctx, const helios_gpu_async_ring& ring, Body body,
+                                  unsigned long long max_count = ~0ull) {
+  cudaStream_t st = static_cast<cudaStream_t>(ctx->stream);
+  async_drain_kernel<Msg, Body><<<ctx->sm_count * 4, 256, 0, st>>>(ring, max_count, body);
+  async_advance_kernel<<<1, 1, 0, st>>>(ring, max_count);
+  helios_gpu_world_note_launches(ctx->world, 2);
+  return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
+}
+
 // ConsumableMessageWrapper::Consume / ConsumableMessageReader::ConsumeIf (message/reader.hpp:850-1058): mark the message
 // at `global_index` of the reader view (previous ++ current) consumed.  Idempotent; no ordering between markers.
 __device__ __forceinline__ void message_mark_consumed(uint32_t* consumed, uint64_t capacity, uint64_t global_index) {

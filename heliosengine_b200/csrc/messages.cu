@@ -155,7 +155,116 @@ int32_t messages_update(helios_gpu_world* w) {
 
 }  // namespace hgpu
 
+namespace {
+
+AsyncChannel* find_async(helios_gpu_world* w, uint64_t hash) {
+  for (auto& c : w->async_channels)
+    if (c->hash == hash) return c.get();
+  return nullptr;
+}
+
+// Host access to a ring: the cursors come back over the world's stream, i.e. after every producer / consumer launched so
+// far has finished.
+int32_t async_cursors(helios_gpu_world* w, AsyncChannel* c, unsigned long long cur[2]) {
+  HG_CUDA(w, cudaMemcpyAsync(cur, c->cursors.ptr, 16, cudaMemcpyDeviceToHost, w->stream));
+  HG_CUDA(w, cudaStreamSynchronize(w->stream));
+  if (cur[1] - cur[0] > c->ring.capacity)
+    HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "async message ring overflow: %llu undrained messages in %llu slots (clear it to recover)",
+            cur[1] - cur[0], (unsigned long long)c->ring.capacity);
+  return HELIOS_GPU_OK;
+}
+
+}  // namespace
+
 extern "C" {
+
+int32_t helios_gpu_async_message_register(helios_gpu_world* w, uint64_t hash, uint32_t size, uint64_t capacity) {
+  if (!w || size == 0 || hash == 0) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (find_async(w, hash)) return HELIOS_GPU_OK;  // async_queue.hpp Register<T>: idempotent (tests/message/async_queue.cpp:401)
+  uint64_t cap = 1024;
+  while (cap < capacity) cap <<= 1;
+  auto c = std::make_unique<AsyncChannel>();
+  c->hash = hash;
+  HG_CUDA(w, c->data.reserve(cap * size, 0, w->stream, false));
+  HG_CUDA(w, c->cursors.reserve(64, 0, w->stream, false));
+  HG_CUDA(w, cudaMemsetAsync(c->cursors.ptr, 0, 64, w->stream));
+  c->ring.data = c->data.as<uint8_t>();
+  c->ring.cursors = c->cursors.as<unsigned long long>();
+  c->ring.capacity = cap;
+  c->ring.elem_size = size;
+  w->async_channels.push_back(std::move(c));
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_async_message_view(helios_gpu_world* w, uint64_t hash, helios_gpu_async_ring* out) {
+  if (!w || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  AsyncChannel* c = find_async(w, hash);
+  if (!c) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "async message type not registered");
+  *out = c->ring;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_async_message_write(helios_gpu_world* w, uint64_t hash, const void* data, uint64_t n) {
+  if (!w || (n && !data)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  AsyncChannel* c = find_async(w, hash);
+  if (!c) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "async message type not registered");
+  if (n == 0) return HELIOS_GPU_OK;  // "Bulk enqueue of empty range is a no-op" (tests/message/async_queue.cpp:134)
+  unsigned long long cur[2];
+  HG_TRY(async_cursors(w, c, cur));
+  const helios_gpu_async_ring& r = c->ring;
+  if (cur[1] - cur[0] + n > r.capacity)
+    HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "async message ring full: %llu queued + %llu new > %llu slots", cur[1] - cur[0],
+            (unsigned long long)n, (unsigned long long)r.capacity);
+  const uint64_t at = cur[1] & (r.capacity - 1);
+  const uint64_t first = std::min<uint64_t>(n, r.capacity - at);
+  const auto* src = static_cast<const uint8_t*>(data);
+  HG_CUDA(w, cudaMemcpyAsync(r.data + at * r.elem_size, src, first * r.elem_size, cudaMemcpyHostToDevice, w->stream));
+  if (first < n)
+    HG_CUDA(w, cudaMemcpyAsync(r.data, src + first * r.elem_size, (n - first) * r.elem_size, cudaMemcpyHostToDevice, w->stream));
+  cur[1] += n;
+  HG_CUDA(w, cudaMemcpyAsync(r.cursors + 1, &cur[1], 8, cudaMemcpyHostToDevice, w->stream));
+  HG_CUDA(w, cudaStreamSynchronize(w->stream));  // `data` and `cur` are the caller's / this frame's memory
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_async_message_dequeue(helios_gpu_world* w, uint64_t hash, void* out, uint64_t max_count, uint64_t* n_out) {
+  if (!w || (max_count && !out)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  AsyncChannel* c = find_async(w, hash);
+  if (!c) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "async message type not registered");
+  unsigned long long cur[2];
+  HG_TRY(async_cursors(w, c, cur));
+  const helios_gpu_async_ring& r = c->ring;
+  const uint64_t n = std::min<uint64_t>(max_count, cur[1] - cur[0]);  // Into(out, max_count) (async_queue.hpp:165-176)
+  if (n_out) *n_out = n;
+  if (n == 0) return HELIOS_GPU_OK;
+  const uint64_t at = cur[0] & (r.capacity - 1);
+  const uint64_t first = std::min<uint64_t>(n, r.capacity - at);
+  auto* dst = static_cast<uint8_t*>(out);
+  HG_CUDA(w, cudaMemcpyAsync(dst, r.data + at * r.elem_size, first * r.elem_size, cudaMemcpyDeviceToHost, w->stream));
+  if (first < n)
+    HG_CUDA(w, cudaMemcpyAsync(dst + first * r.elem_size, r.data, (n - first) * r.elem_size, cudaMemcpyDeviceToHost, w->stream));
+  cur[0] += n;
+  HG_CUDA(w, cudaMemcpyAsync(r.cursors, &cur[0], 8, cudaMemcpyHostToDevice, w->stream));
+  HG_CUDA(w, cudaStreamSynchronize(w->stream));
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_async_message_size(helios_gpu_world* w, uint64_t hash, uint64_t* out) {
+  if (!w || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  AsyncChannel* c = find_async(w, hash);
+  if (!c) { *out = 0; return HELIOS_GPU_OK; }  // HasAsyncMessages<T>() of an unregistered type is false (manager.hpp:243-249)
+  unsigned long long cur[2];
+  HG_TRY(async_cursors(w, c, cur));
+  *out = cur[1] - cur[0];
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_async_message_clear(helios_gpu_world* w, uint64_t hash) {
+  if (!w) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  for (auto& c : w->async_channels)  // "Clear on unregistered type is a no-op" (tests/message/async_queue.cpp:452)
+    if (hash == 0 || c->hash == hash) HG_CUDA(w, cudaMemsetAsync(c->cursors.ptr, 0, 16, w->stream));
+  return HELIOS_GPU_OK;
+}
 
 int32_t helios_gpu_message_register(helios_gpu_world* w, uint64_t hash, uint32_t size, uint32_t policy) {
   if (!w || size == 0) return HELIOS_GPU_ERR_INVALID_ARGUMENT;

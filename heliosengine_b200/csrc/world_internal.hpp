@@ -60,6 +60,12 @@ struct ChannelDev {
   unsigned long long counts[2];  // {previous, current}
 };
 
+struct AsyncChannel {          // one registered async message type (message/async_queue.hpp:40-118) as a device ring
+  uint64_t hash = 0;
+  helios_gpu_async_ring ring{};
+  DevBuf data, cursors;
+};
+
 struct HostCmdQueue {         // host staging of a CmdQueue (command/queue.hpp:137-163)
   std::vector<helios_gpu_command> cmds;
   std::vector<uint8_t> payload;
@@ -139,6 +145,7 @@ struct helios_gpu_world {
 
   std::vector<std::unique_ptr<hgpu::MsgChannel>> channels;
   std::unordered_map<uint64_t, int> channel_of;
+  std::vector<std::unique_ptr<hgpu::AsyncChannel>> async_channels;  // AsyncMessageQueue (message/manager.hpp:359)
 
   std::vector<helios_gpu_query*> queries;
   std::vector<helios_gpu_schedule*> schedules;

@@ -375,6 +375,54 @@ public:
     return out;
   }
 
+  // ---- async messages (message/async_queue.hpp; MessageManager::WriteAsync / WriteAsyncBulk / ManualAsyncClear /
+  //      HasAsyncMessages, message/manager.hpp:135-183,243-249): a device ring per type, not tied to World::Update ----
+  template <typename M>
+  void AddAsyncMessage(uint64_t ring_capacity = 1u << 16) {
+    static_assert(std::is_trivially_copyable_v<M>);
+    Check(helios_gpu_async_message_register(w_, TypeIndexOf<M>(), sizeof(M), ring_capacity));
+  }
+  template <typename M>
+  void WriteAsync(const M& m) { Check(helios_gpu_async_message_write(w_, TypeIndexOf<M>(), &m, 1)); }
+  template <typename M>
+  void WriteAsyncBulk(std::span<const M> ms) { Check(helios_gpu_async_message_write(w_, TypeIndexOf<M>(), ms.data(), ms.size())); }
+  template <typename M>
+  bool HasAsyncMessages() { return AsyncMessageCount<M>() != 0; }
+  template <typename M>
+  uint64_t AsyncMessageCount() {
+    uint64_t n = 0;
+    Check(helios_gpu_async_message_size(w_, TypeIndexOf<M>(), &n));
+    return n;
+  }
+  template <typename M>
+  void ManualAsyncClear() { Check(helios_gpu_async_message_clear(w_, TypeIndexOf<M>())); }
+  // AsyncMessageReader<M>::Dequeue(dest) (async_reader.hpp): false and `dest` untouched when the queue is empty
+  template <typename M>
+  bool DequeueAsync(M& dest) {
+    uint64_t n = 0;
+    M tmp;
+    Check(helios_gpu_async_message_dequeue(w_, TypeIndexOf<M>(), &tmp, 1, &n));
+    if (n) dest = tmp;
+    return n != 0;
+  }
+  // AsyncMessageReader<M>::Into(out, max_count)
+  template <typename M>
+  std::vector<M> DrainAsync(uint64_t max_count = ~0ull) {
+    const uint64_t want = std::min<uint64_t>(max_count, AsyncMessageCount<M>());
+    std::vector<M> out(want);
+    uint64_t n = 0;
+    if (want) Check(helios_gpu_async_message_dequeue(w_, TypeIndexOf<M>(), out.data(), want, &n));
+    out.resize(n);
+    return out;
+  }
+  // the device view a GPU system body captures (AsyncMessageWriter<M> / AsyncMessageReader<M> parameters)
+  template <typename M>
+  helios_gpu_async_ring AsyncRing() {
+    helios_gpu_async_ring r{};
+    Check(helios_gpu_async_message_view(w_, TypeIndexOf<M>(), &r));
+    return r;
+  }
+
   // Slot of a registered component (bit position in command masks); registers on first use.
   template <details::Component T>
   int SlotOf() { return RegisterComponent<T>(); }
@@ -569,7 +617,72 @@ public:
   Schedule& operator=(const Schedule&) = delete;
   ~Schedule() { if (s_) helios_gpu_schedule_destroy(s_); }
 
-  class SystemHandle {  // schedule.hpp: Before/After ordering constraints
+  // A device run condition (schedule/run_condition.hpp:23-58).  The reference builds RunConditionStorage from a host
+  // callable; a GPU predicate is one of the shapes below, evaluated on the device right before the guarded system.
+  class GpuRunCondition {
+  public:
+    // AlwaysTrue / AlwaysFalse style constants
+    static GpuRunCondition Constant(bool value, std::string name = {}) {
+      GpuRunCondition c(std::move(name), HELIOS_GPU_COND_CONSTANT);
+      c.d_.rhs = value ? 1u : 0u;
+      return c;
+    }
+    // [](Res<const T> r) { return word(r) <cmp> rhs; } over the u64 at `byte_offset` of the schedule's resource block
+    static GpuRunCondition Resource(uint32_t byte_offset, uint32_t cmp, uint64_t rhs, std::string name = {}) {
+      GpuRunCondition c(std::move(name), HELIOS_GPU_COND_RESOURCE);
+      c.d_.offset = byte_offset;
+      c.d_.cmp = cmp;
+      c.d_.rhs = rhs;
+      return c;
+    }
+    // [](MessageReader<T> r) { return r.Count() <cmp> rhs; }   (run_condition.cpp:76-80)
+    template <typename T>
+    static GpuRunCondition Messages(uint32_t cmp, uint64_t rhs, std::string name = {}) {
+      GpuRunCondition c(std::move(name), HELIOS_GPU_COND_MESSAGES);
+      c.d_.reads_message = TypeIndexOf<T>();
+      c.d_.cmp = cmp;
+      c.d_.rhs = rhs;
+      return c;
+    }
+    // [](Query<...> q) { return q.<terminal>(...).<field> <cmp> rhs; }   (run_condition.cpp:54-60): Q is instantiated and
+    // owned by the schedule when the condition is attached
+    template <typename Q>
+    static GpuRunCondition Terminal(helios_gpu_system_fn terminal, uint32_t field, uint32_t cmp, uint64_t rhs,
+                                    const void* params = nullptr, uint32_t params_size = 0, std::string name = {}) {
+      GpuRunCondition c(std::move(name), HELIOS_GPU_COND_TERMINAL);
+      c.d_.launch = terminal;
+      c.d_.field = field;
+      c.d_.cmp = cmp;
+      c.d_.rhs = rhs;
+      c.d_.params = params;
+      c.d_.params_size = params_size;
+      c.make_query_ = [](World& w) {
+        auto* q = new Q(w);
+        return std::pair<void*, helios_gpu_query*>(q, q->Handle());
+      };
+      c.drop_query_ = [](void* p) { delete static_cast<Q*>(p); };
+      return c;
+    }
+    // a user predicate: `launch` enqueues kernels on ctx->stream that store 0 to *ctx->verdict to veto
+    static GpuRunCondition Custom(helios_gpu_system_fn launch, const void* params = nullptr, uint32_t params_size = 0,
+                                  std::string name = {}) {
+      GpuRunCondition c(std::move(name), HELIOS_GPU_COND_CUSTOM);
+      c.d_.launch = launch;
+      c.d_.params = params;
+      c.d_.params_size = params_size;
+      return c;
+    }
+
+  private:
+    friend class Schedule;
+    GpuRunCondition(std::string name, uint32_t kind) : name_(std::move(name)) { d_.kind = kind; d_.cmp = HELIOS_GPU_CMP_NE; }
+    std::string name_;
+    helios_gpu_condition_desc d_{};
+    std::pair<void*, helios_gpu_query*> (*make_query_)(World&) = nullptr;
+    void (*drop_query_)(void*) = nullptr;
+  };
+
+  class SystemHandle {  // schedule.hpp: Before/After ordering constraints, RunIf, InSet
   public:
     SystemHandle(Schedule& s, uint32_t index) : s_(&s), index_(index) {}
     uint32_t Index() const noexcept { return index_; }
@@ -581,10 +694,45 @@ public:
       s_->world_->Check(helios_gpu_schedule_add_order(s_->s_, other.index_, index_));
       return *this;
     }
+    // SystemHandle::RunIf (schedule/system_handle.hpp): appended to the system's own conditions; marks the schedule dirty
+    SystemHandle& RunIf(GpuRunCondition cond) {
+      helios_gpu_condition_desc d = s_->Materialise(cond);
+      s_->world_->Check(helios_gpu_schedule_add_run_condition(s_->s_, index_, &d));
+      return *this;
+    }
+    // SystemHandle::InSet<Set>()
+    template <typename SetT>
+    SystemHandle& InSet() {
+      s_->world_->Check(helios_gpu_schedule_system_in_set(s_->s_, index_, TypeIndexOf<SetT>()));
+      return *this;
+    }
   private:
     Schedule* s_;
     uint32_t index_;
   };
+
+  class SystemSetHandle {  // schedule/system_set_handle.hpp: conditions shared by every member of the set
+  public:
+    SystemSetHandle(Schedule& s, uint64_t id) : s_(&s), id_(id) {}
+    SystemSetHandle& RunIf(GpuRunCondition cond) {
+      helios_gpu_condition_desc d = s_->Materialise(cond);
+      s_->world_->Check(helios_gpu_schedule_add_set_condition(s_->s_, id_, &d));
+      return *this;
+    }
+  private:
+    Schedule* s_;
+    uint64_t id_;
+  };
+  template <typename SetT>
+  SystemSetHandle Set() { return SystemSetHandle(*this, TypeIndexOf<SetT>()); }
+
+  // 1 = the system (registration index) ran in the last run, 0 = a run condition skipped it
+  std::vector<uint32_t> LastVerdicts() {
+    std::vector<uint32_t> out(64);
+    world_->Check(helios_gpu_schedule_last_verdicts(s_, out.data(), 64));
+    out.resize(ExecutionOrder().size());
+    return out;
+  }
 
   // Schedule::Add for a GPU system: `Q` = Query<...> type (access policy deduced from it), `launch` enqueues the body's
   // kernels on ctx->stream.  The Query object is owned by the schedule.
@@ -630,6 +778,16 @@ public:
   helios_gpu_schedule* Handle() const noexcept { return s_; }
 
 private:
+  helios_gpu_condition_desc Materialise(GpuRunCondition& c) {
+    helios_gpu_condition_desc d = c.d_;
+    d.name = c.name_.c_str();
+    if (c.make_query_) {
+      const auto made = c.make_query_(*world_);
+      owned_queries_.emplace_back(made.first, c.drop_query_);
+      d.query = made.second;
+    }
+    return d;
+  }
   SystemHandle AddRaw(const std::string& name, helios_gpu_query* q, helios_gpu_system_fn launch, const GpuSystemOptions& o) {
     helios_gpu_system_desc d{};
     d.name = name.c_str();

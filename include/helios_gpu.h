@@ -268,6 +268,39 @@ HELIOS_GPU_API int32_t helios_gpu_message_counts(helios_gpu_world* w, uint64_t t
 HELIOS_GPU_API int32_t helios_gpu_message_read(helios_gpu_world* w, uint64_t type_hash, uint32_t which, void* out,
                                                uint64_t capacity_bytes);
 
+/* ---- async messages (message/async_queue.hpp:40-330: one moodycamel MPMC queue per type; AsyncMessageWriter/Reader,
+ * async_writer.hpp:20-94, async_reader.hpp:20-131; MessageManager::WriteAsync / WriteAsyncBulk / ManualAsyncClear /
+ * HasAsyncMessages, message/manager.hpp:135-183,243-249) ---------------------------------------------------------------
+ * Not double-buffered and not tied to World::Update: a message is readable as soon as it is enqueued and is gone once
+ * dequeued.  On the GPU each type is a fixed-capacity ring in HBM {data, head, tail}: producers (the host, or any number
+ * of kernels through helios_gpu::async_push — one atomic per warp) bump `tail`; consumers (the host, or a drain launch,
+ * helios_gpu::async_drain_launch) advance `head`.  Like the reference queue the order is FIFO per producer and unspecified
+ * between concurrent producers.  Pushes become visible to kernels that start after the producing kernel has finished
+ * (stream / schedule order); a kernel never both pushes to and drains one ring.  The ring does not grow: more than
+ * `capacity` undrained messages is an error reported by the next host call on the ring (HELIOS_GPU_ERR_CAPACITY). */
+typedef struct helios_gpu_async_ring {
+  uint8_t* data;               /* capacity * elem_size bytes */
+  unsigned long long* cursors; /* [0] head = messages dequeued so far, [1] tail = messages enqueued so far */
+  uint64_t capacity;           /* slots, a power of two */
+  uint32_t elem_size;
+  uint32_t _pad;
+} helios_gpu_async_ring;
+/* AsyncMessageQueue::Register<T> (idempotent); capacity is rounded up to a power of two. */
+HELIOS_GPU_API int32_t helios_gpu_async_message_register(helios_gpu_world* w, uint64_t type_hash, uint32_t size,
+                                                         uint64_t capacity);
+/* Enqueue / EnqueueBulk from the host (MessageManager::WriteAsync / WriteAsyncBulk). */
+HELIOS_GPU_API int32_t helios_gpu_async_message_write(helios_gpu_world* w, uint64_t type_hash, const void* data, uint64_t n);
+/* Dequeue / Into(out, max_count): moves up to max_count messages to `out` in queue order; *n_out = how many. */
+HELIOS_GPU_API int32_t helios_gpu_async_message_dequeue(helios_gpu_world* w, uint64_t type_hash, void* out,
+                                                        uint64_t max_count, uint64_t* n_out);
+/* SizeApprox (exact here: the call synchronises the world's stream); Empty = (*out == 0). */
+HELIOS_GPU_API int32_t helios_gpu_async_message_size(helios_gpu_world* w, uint64_t type_hash, uint64_t* out);
+/* Clear<T>() / ManualAsyncClear<T>(); type_hash 0 = Clear() of every registered type. */
+HELIOS_GPU_API int32_t helios_gpu_async_message_clear(helios_gpu_world* w, uint64_t type_hash);
+/* The device view a system body captures (AsyncMessageWriter<T> / AsyncMessageReader<T> system parameters,
+ * param_traits.hpp): stable for the life of the world, so it may be baked into captured graphs. */
+HELIOS_GPU_API int32_t helios_gpu_async_message_view(helios_gpu_world* w, uint64_t type_hash, helios_gpu_async_ring* out);
+
 /* Device views handed to system bodies. */
 typedef struct helios_gpu_msg_writer { /* SystemLocalData::message_queue for one type (param_traits.hpp:216-229) */
   uint8_t* data;

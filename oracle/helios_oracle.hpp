@@ -1099,6 +1099,61 @@ struct Command {
   std::vector<std::vector<uint8_t>> values;  // component payloads (Add/TryAdd), parallel to types
 };
 
+// ------------------------------------------------------------------------------------------------
+// message/async_queue.hpp:40-330 — AsyncMessageQueue: one MPMC queue per async message type (moodycamel::ConcurrentQueue
+// 1.0.x, a third-party dependency that is not vendored in /root/reference).  Restated through its published contract as
+// the reference uses it: enqueue / try_dequeue are FIFO per producer (one producer here), size_approx is exact when no
+// operation is in flight.  Messages are raw bytes of the registered size.
+// ------------------------------------------------------------------------------------------------
+class AsyncMessageQueue {
+public:
+  // Register<T>() (:252-258): idempotent
+  void Register(TypeIndex t, uint32_t size) { messages_.try_emplace(t, Storage{size, {}}); }
+  bool IsRegistered(TypeIndex t) const { return messages_.count(t) != 0; }
+  // Enqueue / EnqueueBulk (:49-67,119-160): the type must be registered (HELIOS_ASSERT) → false here
+  bool Enqueue(TypeIndex t, const void* data, size_t n = 1) {
+    const auto it = messages_.find(t);
+    if (it == messages_.end()) return false;
+    const auto* p = static_cast<const uint8_t*>(data);
+    for (size_t i = 0; i < n; ++i) it->second.q.emplace_back(p + i * it->second.size, p + (i + 1) * it->second.size);
+    return true;
+  }
+  // bool Dequeue(T& dest) (:74): false and `dest` untouched when empty
+  bool Dequeue(TypeIndex t, void* dest) {
+    const auto it = messages_.find(t);
+    if (it == messages_.end() || it->second.q.empty()) return false;
+    std::memcpy(dest, it->second.q.front().data(), it->second.size);
+    it->second.q.pop_front();
+    return true;
+  }
+  // Into(out, max_count) (:165-176): dequeues while dequeued < max_count; returns how many
+  size_t Into(TypeIndex t, void* out, size_t max_count) {
+    size_t n = 0;
+    const auto it = messages_.find(t);
+    if (it == messages_.end()) return 0;
+    while (n < max_count && Dequeue(t, static_cast<uint8_t*>(out) + n * it->second.size)) ++n;
+    return n;
+  }
+  void Clear() { for (auto& [_, s] : messages_) s.q.clear(); }                 // :259-263 types stay registered
+  void Clear(TypeIndex t) { const auto it = messages_.find(t); if (it != messages_.end()) it->second.q.clear(); }  // :264-271
+  void Reset() { messages_.clear(); }                                          // :193
+  void Reset(TypeIndex t) { messages_.erase(t); }                              // :194-197
+  bool HasMessages() const { for (const auto& [_, s] : messages_) if (!s.q.empty()) return true; return false; }  // :224-227
+  bool HasMessages(TypeIndex t) const { return MessageCount(t) != 0; }         // :289-296 (false if unregistered)
+  size_t TypeCount() const { return messages_.size(); }
+  size_t MessageCount() const { size_t n = 0; for (const auto& [_, s] : messages_) n += s.q.size(); return n; }  // :297-303
+  size_t MessageCount(TypeIndex t) const { const auto it = messages_.find(t); return it == messages_.end() ? 0 : it->second.q.size(); }
+  bool Empty(TypeIndex t) const { return MessageCount(t) == 0; }               // TypedAsyncMessageStorage::Empty (:95-97)
+  uint32_t ElemSize(TypeIndex t) const { const auto it = messages_.find(t); return it == messages_.end() ? 0 : it->second.size; }
+
+private:
+  struct Storage {
+    uint32_t size;
+    std::deque<std::vector<uint8_t>> q;
+  };
+  std::map<TypeIndex, Storage> messages_;
+};
+
 class World;
 
 // command/queue.hpp:137-163 — FIFO.
@@ -1129,6 +1184,7 @@ public:
   EntityManager entities;
   ComponentManager components;
   MessageManager messages;
+  AsyncMessageQueue async_messages;  // MessageManager::async_messages_ (message/manager.hpp:359)
   CmdQueue command_queue;  // world.hpp:945 global queue
   // quirk #13: every structural call also writes a builtin message.  The 8-byte payload is the entity.
   bool emit_builtin_messages = false;

@@ -1111,6 +1111,90 @@ void TestRunConditions() {
   }
 }
 
+// ---- message/async_queue.cpp:31-520 — TypedAsyncMessageStorage / AsyncMessageQueue --------------------------------------------
+void TestAsyncMessages() {
+  struct EventMsg { int id = 0; };
+  struct OtherMsg { int v = 0; };
+  const TypeIndex kEvent = Fnv1a("EventMsg"), kOther = Fnv1a("OtherMsg");
+  auto make = [&] { AsyncMessageQueue q; q.Register(kEvent, sizeof(EventMsg)); return q; };
+  auto push = [&](AsyncMessageQueue& q, int id) { const EventMsg m{id}; return q.Enqueue(kEvent, &m); };
+  {  // ctor / Clear (:31-76)
+    AsyncMessageQueue q = make();
+    CHECK(q.Empty(kEvent) && q.MessageCount(kEvent) == 0);
+    push(q, 0); push(q, 0);
+    q.Clear(kEvent);
+    CHECK(q.Empty(kEvent) && q.MessageCount(kEvent) == 0);
+    q.Clear(kEvent);  // "Clear on already empty storage is a no-op"
+    CHECK(q.Empty(kEvent));
+  }
+  {  // Enqueue / EnqueueBulk (:78-142)
+    AsyncMessageQueue q = make();
+    push(q, 7);
+    CHECK(!q.Empty(kEvent));
+    const EventMsg batch[3] = {};
+    q.Enqueue(kEvent, batch, 3);
+    CHECK(q.MessageCount(kEvent) >= 3);
+    AsyncMessageQueue e = make();
+    e.Enqueue(kEvent, batch, 0);  // "Bulk enqueue of empty range is a no-op"
+    CHECK(e.Empty(kEvent));
+  }
+  {  // Dequeue (:144-215)
+    AsyncMessageQueue q = make();
+    push(q, 33);
+    EventMsg dest;
+    CHECK(q.Dequeue(kEvent, &dest) && dest.id == 33);
+    EventMsg keep{99};
+    CHECK(!q.Dequeue(kEvent, &keep) && keep.id == 99);  // "Returns false and leaves dest unchanged when queue is empty"
+  }
+  {  // Into (:217-287)
+    AsyncMessageQueue q = make();
+    push(q, 1); push(q, 2); push(q, 3);
+    EventMsg out[3];
+    CHECK(q.Into(kEvent, out, ~size_t(0)) == 3 && q.Empty(kEvent));
+    CHECK(out[0].id == 1 && out[1].id == 2 && out[2].id == 3);  // single producer: FIFO
+    push(q, 1); push(q, 2); push(q, 3);
+    CHECK(q.Into(kEvent, out, 2) == 2 && !q.Empty(kEvent));   // "Respects max_count limit": one message remains
+    CHECK(q.MessageCount(kEvent) == 1);
+    AsyncMessageQueue e = make();
+    CHECK(e.Into(kEvent, out, ~size_t(0)) == 0);               // "Returns zero for empty storage"
+  }
+  {  // Empty / SizeApprox (:313-351)
+    AsyncMessageQueue q = make();
+    CHECK(q.Empty(kEvent) && q.MessageCount(kEvent) == 0);
+    push(q, 1);
+    CHECK(!q.Empty(kEvent));
+    EventMsg d;
+    q.Dequeue(kEvent, &d);
+    CHECK(q.Empty(kEvent));
+    for (int i = 0; i < 5; ++i) push(q, i);
+    CHECK(q.MessageCount(kEvent) >= 5);
+  }
+  {  // AsyncMessageQueue::Register / Clear (all, typed) / Reset / HasMessages / counts (:354-520)
+    AsyncMessageQueue q;
+    CHECK(q.TypeCount() == 0 && !q.HasMessages() && q.MessageCount() == 0);
+    q.Register(kEvent, sizeof(EventMsg));
+    CHECK(q.IsRegistered(kEvent) && !q.IsRegistered(kOther));
+    q.Register(kEvent, sizeof(EventMsg));  // "Re-registering the same type is idempotent"
+    CHECK(q.TypeCount() == 1);
+    q.Register(kOther, sizeof(OtherMsg));
+    CHECK(q.TypeCount() == 2);
+    const OtherMsg o{5};
+    push(q, 1);
+    q.Enqueue(kOther, &o);
+    CHECK(q.HasMessages() && q.HasMessages(kEvent) && q.MessageCount() == 2);
+    q.Clear(kEvent);  // "Clears only the specified type"
+    CHECK(!q.HasMessages(kEvent) && q.HasMessages(kOther));
+    q.Clear(Fnv1a("Unregistered"));  // "Clear on unregistered type is a no-op"
+    q.Clear();        // "All messages are removed but types remain registered"
+    CHECK(!q.HasMessages() && q.IsRegistered(kEvent) && q.IsRegistered(kOther));
+    q.Reset(kEvent);
+    CHECK(!q.IsRegistered(kEvent) && q.IsRegistered(kOther));
+    q.Reset();
+    CHECK(q.TypeCount() == 0);
+    CHECK(!q.HasMessages(kEvent) && q.MessageCount(kEvent) == 0);  // unregistered: false / 0
+  }
+}
+
 }  // namespace
 
 int main() {
@@ -1127,6 +1211,7 @@ int main() {
   TestScheduling();
   TestApplyOrder();
   TestRunConditions();
+  TestAsyncMessages();
   std::printf("oracle KATs: %d checks, %d failed\n", g_checks, g_fail);
   return g_fail;
 }

@@ -266,6 +266,43 @@ int32_t sys_despawn_dead(const OCtx* c) {
   return 0;
 }
 
+// async messages: AsyncMessageWriter<LowHealthAlert>::Write for hp < t; AsyncMessageReader<LowHealthAlert>::Into + heal
+struct LowHealthAlert { helios_gpu_entity_t who; int32_t hp; uint32_t pad; };
+struct AlertParams { uint64_t type_hash; int32_t threshold; uint32_t health_slot; uint64_t max_count; };
+int32_t sys_alert_low_health(const OCtx* c) {
+  AlertParams p;
+  std::memcpy(&p, c->params, sizeof(p));
+  OWorld* w = c->world;
+  if (!w->world.async_messages.IsRegistered(p.type_hash)) return HELIOS_GPU_ERR_NOT_FOUND;
+  ho::ForEach(w->world.components, *c->query, [&](ho::Entity e, uint8_t** cols) {
+    int32_t hp;
+    std::memcpy(&hp, cols[0], 4);
+    if (hp < p.threshold) {
+      const LowHealthAlert a{e.Pack(), hp, 0u};
+      w->world.async_messages.Enqueue(p.type_hash, &a);
+    }
+  });
+  return 0;
+}
+int32_t sys_heal_alerted(const OCtx* c) {
+  AlertParams p;
+  std::memcpy(&p, c->params, sizeof(p));
+  OWorld* w = c->world;
+  if (!w->world.async_messages.IsRegistered(p.type_hash)) return HELIOS_GPU_ERR_NOT_FOUND;
+  const ho::TypeIndex health = w->slot_hash[p.health_slot];
+  LowHealthAlert a;
+  uint64_t n = 0;
+  const uint64_t limit = p.max_count ? p.max_count : ~0ull;
+  while (n < limit && w->world.async_messages.Dequeue(p.type_hash, &a)) {
+    ++n;
+    const ho::Entity who = E(a.who);
+    if (!w->world.entities.Validate(who)) continue;
+    uint8_t* hp = w->world.components.Get(who, health);
+    if (hp) *reinterpret_cast<int32_t*>(hp) += 10 + (a.hp & 3);
+  }
+  return 0;
+}
+
 struct Builtin {
   const char* name;
   OSystemFn fn;
@@ -276,6 +313,7 @@ const Builtin kBuiltins[] = {
     {"detect_sparse", sys_detect_sparse}, {"consume", sys_consume}, {"consume_strong", sys_consume_strong},         {"stats", sys_stats},
     {"exit_check", sys_exit_check}, {"despawn_dead", sys_despawn_dead},
     {"buff_heal", sys_buff_heal}, {"buff_optional", sys_buff_optional},
+    {"alert_low_health", sys_alert_low_health}, {"heal_alerted", sys_heal_alerted},
 };
 
 // helios_gpu_command → oracle Command (payload: ascending slot order, each value padded to 4 bytes).
@@ -679,6 +717,33 @@ HO_API int32_t helios_oracle_message_read(void* wp, uint64_t hash, uint32_t whic
   if (!b) return HELIOS_GPU_ERR_NOT_FOUND;
   if (cap < b->size()) return HELIOS_GPU_ERR_CAPACITY;
   std::memcpy(out, b->data(), b->size());
+  return 0;
+}
+
+// ---- async messages (message/async_queue.hpp; MessageManager::WriteAsync / WriteAsyncBulk / ManualAsyncClear) -------------
+HO_API int32_t helios_oracle_async_message_register(void* wp, uint64_t hash, uint32_t size, uint64_t) {
+  if (size == 0 || hash == 0) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  W(wp)->world.async_messages.Register(hash, size);
+  return 0;
+}
+HO_API int32_t helios_oracle_async_message_write(void* wp, uint64_t hash, const void* data, uint64_t n) {
+  if (!W(wp)->world.async_messages.IsRegistered(hash)) return HELIOS_GPU_ERR_NOT_FOUND;
+  W(wp)->world.async_messages.Enqueue(hash, data, n);
+  return 0;
+}
+HO_API int32_t helios_oracle_async_message_dequeue(void* wp, uint64_t hash, void* out, uint64_t max_count, uint64_t* n_out) {
+  if (!W(wp)->world.async_messages.IsRegistered(hash)) return HELIOS_GPU_ERR_NOT_FOUND;
+  const uint64_t n = W(wp)->world.async_messages.Into(hash, out, max_count);
+  if (n_out) *n_out = n;
+  return 0;
+}
+HO_API int32_t helios_oracle_async_message_size(void* wp, uint64_t hash, uint64_t* out) {
+  *out = W(wp)->world.async_messages.MessageCount(hash);
+  return 0;
+}
+HO_API int32_t helios_oracle_async_message_clear(void* wp, uint64_t hash) {
+  if (hash) W(wp)->world.async_messages.Clear(hash);
+  else W(wp)->world.async_messages.Clear();
   return 0;
 }
 

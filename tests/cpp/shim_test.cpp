@@ -172,6 +172,77 @@ int main(int argc, char** argv) {
     try { schedule.Build(); } catch (const ecs::GpuError& e) { cycle = e.Status() == HELIOS_GPU_ERR_CYCLE; }
     CHECK(cycle);
   }
+  // ---- run conditions (tests/schedule/schedule.cpp:559-597,900-945; run_condition.cpp:54-80) ----
+  {
+    struct SetA {};
+    struct SetOff {};
+    ecs::World world;
+    world.RegisterComponent<Position>();
+    world.RegisterComponent<Health>();
+    world.AddMessage<TestMessage>();
+    helios_gpu_system_fn regen, count_if;
+    world.Check(helios_gpu_builtin_system("regen", &regen));
+    world.Check(helios_gpu_builtin_condition("count_if_pos_x_gt", &count_if));
+    std::vector<Position> pos(10, Position{5, 0});
+    std::vector<Health> hp(10, Health{1});
+    const auto ents = world.SpawnBatch<Position, Health>(10, std::span<const Position>(pos), std::span<const Health>(hp));
+    using Cond = ecs::Schedule::GpuRunCondition;
+    using PQ = ecs::Query<const Position&>;
+    ecs::Schedule schedule(world);
+    const float t = 4.0f, t_high = 100.0f;
+    auto pass = schedule.AddGpu<ecs::Query<Health&>>("passes", regen);   // "System with passing run condition executes"
+    auto fail = schedule.AddGpu<ecs::Query<Health&>>("fails", regen);    // "System with failing run condition is skipped"
+    auto any = schedule.AddGpu<ecs::Query<Health&>>("any_right", regen); // QueryRunCondition: Any(pos.x > 4)
+    auto none = schedule.AddGpu<ecs::Query<Health&>>("none_far", regen); // ... Any(pos.x > 100) is false
+    auto msg = schedule.AddGpu<ecs::Query<Health&>>("has_msgs", regen);  // MessageReaderRunCondition
+    auto in_a = schedule.AddGpu<ecs::Query<Health&>>("in_set_a", regen); // "Set RunIf conditions apply to all members"
+    auto in_off = schedule.AddGpu<ecs::Query<Health&>>("in_set_a_and_off", regen);
+    pass.RunIf(Cond::Constant(true, "AlwaysTrue"));
+    fail.RunIf(Cond::Constant(true)).RunIf(Cond::Constant(false, "AlwaysFalse"));
+    any.RunIf(Cond::Terminal<PQ>(count_if, HELIOS_GPU_COND_FIELD_COUNT, HELIOS_GPU_CMP_GT, 0, &t, sizeof(t)));
+    none.RunIf(Cond::Terminal<PQ>(count_if, HELIOS_GPU_COND_FIELD_COUNT, HELIOS_GPU_CMP_GT, 0, &t_high, sizeof(t_high)));
+    msg.RunIf(Cond::Messages<TestMessage>(HELIOS_GPU_CMP_GT, 0));
+    schedule.Set<SetA>().RunIf(Cond::Constant(true));
+    schedule.Set<SetOff>().RunIf(Cond::Constant(false));
+    in_a.InSet<SetA>();
+    in_off.InSet<SetA>().InSet<SetOff>();
+    bool dirty = false;  // RunIf marks the schedule dirty: Run before Build is an error (schedule.cpp:56-58)
+    try { schedule.RunAndWait(); } catch (const ecs::GpuError& e) { dirty = e.Status() == HELIOS_GPU_ERR_STATE; }
+    CHECK(dirty);
+    schedule.Build();
+    schedule.Build();  // "survives double Build"
+    int expected_hp = 1;
+    for (auto kind : {ecs::ExecutorKind::kMainThread, ecs::ExecutorKind::kMultiThreaded, ecs::ExecutorKind::kCudaGraph}) {
+      schedule.SetExecutor(kind);
+      schedule.RunAndWait();
+      CHECK((schedule.LastVerdicts() == std::vector<uint32_t>{1, 0, 1, 0, 0, 1, 0}));
+      expected_hp += 3;
+      CHECK(world.ReadComponent<Health>(ents[7]).hp == expected_hp);
+    }
+    world.WriteMessage(TestMessage{1});  // now the reader is non-empty: the guarded system runs too
+    schedule.RunAndWait();
+    CHECK((schedule.LastVerdicts() == std::vector<uint32_t>{1, 0, 1, 0, 1, 1, 0}));
+    CHECK(world.ReadComponent<Health>(ents[7]).hp == expected_hp + 4);
+  }
+  // ---- async messages (tests/message/async_queue.cpp:144-287; manager.hpp WriteAsync / ManualAsyncClear) ----
+  {
+    struct AsyncEvent { int id = 0; };
+    ecs::World world;
+    world.AddAsyncMessage<AsyncEvent>(1024);
+    CHECK(!world.HasAsyncMessages<AsyncEvent>());
+    AsyncEvent dest{99};
+    CHECK(!world.DequeueAsync(dest) && dest.id == 99);  // empty: false, dest unchanged
+    world.WriteAsync(AsyncEvent{33});
+    CHECK(world.HasAsyncMessages<AsyncEvent>() && world.DequeueAsync(dest) && dest.id == 33);
+    const std::vector<AsyncEvent> batch = {{1}, {2}, {3}};
+    world.WriteAsyncBulk(std::span<const AsyncEvent>(batch));
+    const auto two = world.DrainAsync<AsyncEvent>(2);   // Into respects max_count: one message remains
+    CHECK(two.size() == 2 && two[0].id == 1 && two[1].id == 2 && world.AsyncMessageCount<AsyncEvent>() == 1);
+    world.Update();                                       // async queues are not cleared by World::Update
+    CHECK(world.AsyncMessageCount<AsyncEvent>() == 1);
+    world.ManualAsyncClear<AsyncEvent>();
+    CHECK(!world.HasAsyncMessages<AsyncEvent>() && world.DrainAsync<AsyncEvent>().empty());
+  }
   // ---- query terminals (tests/query/query.cpp:453-731): Find / Any / All / None / CountIf / MaxBy / MinBy / Partition ----
   {
     ecs::World world;
