@@ -111,7 +111,12 @@ def test_gpu_kernel_producers_and_consumers_match_oracle(gpu, oracle, mode):
 @pytest.mark.gpu
 def test_gpu_host_and_kernel_consumers_share_a_ring(gpu, oracle):
     got, want = (alert_world(b, 4099, 2, capi.EXEC_SERIAL, partial_host_drain=True) for b in (gpu, oracle))
-    assert got == want and got["frame0_host_took"] == 5 and got["frame0_left"] == 0
+    # WHICH five alerts the host consumer gets is unspecified between concurrent producers (as in the reference), so
+    # frame 1 sees up to five different entities still below the threshold; everything else is fixed
+    for key in ("frame0_queued", "frame0_host_took", "frame0_left", "frame1_host_took", "frame1_left"):
+        assert got[key] == want[key], key
+    assert got["frame0_host_took"] == 5 and got["frame0_left"] == 0
+    assert abs(got["frame1_queued"] - want["frame1_queued"]) <= 5
 
 
 @pytest.mark.gpu
