@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--entities", type=int, default=0, help="entities per GPU (default: the config's BASELINE size)")
-    ap.add_argument("--config", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5", "terminals", "sparse", "extract"],
+    ap.add_argument("--config", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5", "terminals", "sparse", "extract", "conditions", "async"],
                     help="cfg2 (default) is the headline workload; the others are secondary legs (bench_configs.py)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")

@@ -10,6 +10,7 @@ cfg1 — 1M-entity single-archetype integrate (launch-bound; reported, no roofli
 """
 from __future__ import annotations
 
+import struct
 import ctypes
 import time
 
@@ -475,6 +476,139 @@ def run_extract(args, torch, dev, stream, peak):
                      "frac": rows * bpr / (med * 1e-3) / 1e9 / peak[0], "traffic": None, "peak_kind": peak[1],
                      "algorithmic_bytes_per_launch": rows * bpr, "kernel": "k_match + k_place_entities + k_extract_rows (one launch for every table and column)"},
         "host_wall_ms": float(np.median(wall)), "e2e": None, "cpu_baseline": None, "gpu_launches": int(launches),
+    }
+
+
+def run_conditions(args, torch, dev, stream, peak):
+    """Run conditions: what guarding the cfg2 headline system costs.  Same world and body as the
+    headline; the system is (a) unguarded, (b) guarded by two conditions that pass — a query terminal `Any(pos.x > t)` over
+    the same 4.19M rows plus a constant — and (c) guarded by a condition that fails.  Device time of Schedule::Run per mode."""
+    n = args.entities or (1 << 24)
+    gpu = capi.load_gpu()
+    w = capi.World(gpu, device=dev.index, entity_capacity=n + 1024)
+    w.set_stream(stream.cuda_stream)
+    worlds.build_lattice(w, n, worlds.OPTIONAL)
+    P, V, A, M, H, F = (worlds.cname(x) for x in ("Position", "Velocity", "Acceleration", "Mass", "Health", "Frozen"))
+
+    def make(kind):
+        q = w.query([(P, True), (V, True), (A, False), (M, False)], with_=[H], without=[F])
+        s = w.schedule("Update_" + kind)
+        i = s.add_system("AccelIntegrate", "accel_integrate", q, params=struct.pack("<f", worlds.DT))
+        if kind == "pass":
+            s.run_if(i, "AnyOnTheRight", capi.COND_TERMINAL, builtin="count_if_pos_x_gt", query=w.query([(P, False)], with_=[H], without=[F]),
+                     params=struct.pack("<f", 512.0), field=capi.COND_FIELD_COUNT, cmp=capi.CMP_GT, rhs=0)
+            s.run_if(i, "AlwaysTrue", capi.COND_CONSTANT, rhs=1)
+        elif kind == "pass_cheap":
+            s.run_if(i, "AlwaysTrue", capi.COND_CONSTANT, rhs=1)
+        elif kind == "skip":
+            s.run_if(i, "AlwaysFalse", capi.COND_CONSTANT, rhs=0)
+        s.build()
+        return s, q
+
+    steps, warm = args.steps, max(3, args.warmup)
+    res, launches = {}, {}
+    rows = None
+    with torch.cuda.stream(stream):
+        for kind in ("unguarded", "pass_cheap", "pass", "skip"):
+            s, q = make(kind)
+            rows = q.count()
+            for mode, mname in ((capi.EXEC_SERIAL, "serial"), (capi.EXEC_GRAPH, "graph")):
+                for _ in range(warm):
+                    s.run_and_wait(mode)
+                torch.cuda.synchronize()
+                l0 = w.launch_count()
+                evs = _events(torch, steps)
+                for a, b in evs:
+                    a.record(stream)
+                    s.run(mode)
+                    b.record(stream)
+                    s.apply_deferred()
+                torch.cuda.synchronize()
+                res[f"{kind}_{mname}"] = float(np.median([a.elapsed_time(b) for a, b in evs]))
+                launches[f"{kind}_{mname}"] = (w.launch_count() - l0) / steps
+                assert s.last_verdicts() == [0 if kind == "skip" else 1]
+    ms = res["pass_cheap_graph"]
+    bytes_per_launch = rows * worlds.CFG2_BYTES_PER_ENTITY
+    achieved = bytes_per_launch / (ms * 1e-3) / 1e9
+    w.close()
+    return {
+        "metric": "entity_component_updates_per_sec", "value": rows / (ms * 1e-3), "unit": "updates/s", "ms_per_step": ms,
+        "dtype": "f32",
+        "config": {"workload": f"conditions: cfg2 filtered query ({rows} rows of {n} entities) behind device run conditions; "
+                               "value = guarded-and-passing (constant condition), CUDA-graph executor",
+                   "l2": "184 MB touched per launch exceeds L2; no flush"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak[0], "unit": "GB/s", "frac": achieved / peak[0], "traffic": None,
+                     "peak_kind": peak[1], "algorithmic_bytes_per_launch": bytes_per_launch,
+                     "kernel": "k_cond_begin + k_cond_test + k_cond_commit + IF{for_each_kernel<AccelBody>}"},
+        "modes_ms": res, "launches_per_run": launches, "e2e": None, "cpu_baseline": None,
+        "gpu_launches": int(sum(launches.values()) * steps),
+    }
+
+
+def run_async(args, torch, dev, stream, peak):
+    """Async messages: n entities {Position, Health}; `alert_low_health` pushes a 16-byte alert for
+    every hp < 40 (~39 % of the rows) through warp-aggregated appends to the device ring, `heal_alerted` drains the ring and
+    heals the entities by id (random access through the location table)."""
+    n = args.entities or (1 << 24)
+    gpu = capi.load_gpu()
+    w = capi.World(gpu, device=dev.index, entity_capacity=n + 1024)
+    w.set_stream(stream.cuda_stream)
+    worlds.register_all(w, ["Position", "Health"])
+    H = worlds.cname("Health")
+    w.spawn_batch([worlds.cname("Position"), H], n, [worlds.column("Position", n, 5100), worlds.column("Health", n, 5101)],
+                  want_entities=False)
+    ALERT = "helios::bench::LowHealthAlert"
+    w.async_message_register(ALERT, 16, capacity=n)
+    params = struct.pack("<QiIQ", capi.fnv1a(ALERT), 40, w.slots[H], 0)
+    emit = w.schedule("Emit")
+    emit.add_system("S1_alert", "alert_low_health", w.query([(H, False)]), params=params)
+    emit.build()
+    heal = w.schedule("Heal")
+    heal.add_system("S2_heal", "heal_alerted", None, params=params, extra_writes=[H])
+    heal.build()
+    steps, warm = args.steps, max(3, args.warmup)
+    t_push, t_drain, pushed = [], [], 0
+    hp0 = np.ascontiguousarray(worlds.column("Health", n, 5101))
+    arch = [i for i, a in enumerate(w.snapshot(columns=False)["archetypes"]) if a["entities"].size == n][0]
+    l0 = w.launch_count()
+    with torch.cuda.stream(stream):
+        for i in range(warm + steps):
+            a, b, c, d = (torch.cuda.Event(enable_timing=True) for _ in range(4))
+            a.record(stream)
+            emit.run(capi.EXEC_SERIAL)
+            b.record(stream)
+            emit.apply_deferred()
+            pushed = w.async_message_size(ALERT)
+            c.record(stream)
+            heal.run(capi.EXEC_SERIAL)
+            d.record(stream)
+            heal.apply_deferred()
+            torch.cuda.synchronize()
+            assert w.async_message_size(ALERT) == 0
+            if i >= warm:
+                t_push.append(a.elapsed_time(b))
+                t_drain.append(c.elapsed_time(d))
+            # undo the healing so every step pushes the same number of alerts
+            w.async_message_clear(ALERT)
+            w.column_write(arch, H, 0, n, hp0.ctypes.data)
+    launches = w.launch_count() - l0
+    push_ms, drain_ms = float(np.median(t_push)), float(np.median(t_drain))
+    push_bytes = n * (8 + 4) + pushed * 16          # entity id + Health read per row, one 16-byte alert written per push
+    drain_bytes = pushed * (16 + 8 + 4 + 4 + 4)      # alert read, location + generation read, Health read-modify-write
+    w.close()
+    return {
+        "metric": "async_messages_per_sec", "value": pushed / (push_ms * 1e-3), "unit": "messages/s", "ms_per_step": push_ms,
+        "dtype": "bytes",
+        "config": {"workload": f"async: {n} entities, {pushed} alerts of 16 B pushed per step by for_each_kernel<AlertBody> "
+                               "(one tail atomic per warp), then drained by async_drain_kernel",
+                   "l2": "201 MB scanned per push launch exceeds L2; no flush"},
+        "roofline": {"bound": "hbm", "achieved": push_bytes / (push_ms * 1e-3) / 1e9, "peak": peak[0], "unit": "GB/s",
+                     "frac": push_bytes / (push_ms * 1e-3) / 1e9 / peak[0], "traffic": None, "peak_kind": peak[1],
+                     "algorithmic_bytes_per_launch": push_bytes, "kernel": "for_each_kernel<AlertBody, Health> (push)"},
+        "drain": {"ms": drain_ms, "messages_per_sec": pushed / (drain_ms * 1e-3), "algorithmic_bytes": drain_bytes,
+                  "achieved_GBps": drain_bytes / (drain_ms * 1e-3) / 1e9,
+                  "note": "random 4-byte read-modify-writes by entity id: sector-bound, not stream-bound"},
+        "e2e": None, "cpu_baseline": None, "gpu_launches": int(launches),
     }
 
 

@@ -313,12 +313,14 @@ struct LowHealthAlert {  // 16 B
   uint32_t pad;
 };
 struct AlertParams { uint64_t type_hash; int32_t threshold; uint32_t health_slot; uint64_t max_count; };
-struct AlertBody {
+struct AlertBody {  // pushes from ~40 % of the rows: staged per warp (one tail atomic per 256 alerts), see async_push_staged
   helios_gpu_async_ring ring;
   int32_t threshold;
+  __device__ void begin() const { helios_gpu::async_stage_begin<LowHealthAlert>(); }
   __device__ void operator()(const Row& r, Health& h) const {
-    helios_gpu::async_push(ring, h.hp < threshold, LowHealthAlert{r.entity, h.hp, 0u});
+    helios_gpu::async_push_staged(ring, h.hp < threshold, LowHealthAlert{r.entity, h.hp, 0u});
   }
+  __device__ void finish() const { helios_gpu::async_stage_flush<LowHealthAlert>(ring); }
 };
 int32_t launch_alert_low_health(const helios_gpu_system_ctx* ctx) {
   if (ctx->params_size < sizeof(AlertParams)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;

@@ -329,6 +329,7 @@ constexpr int kForEachSparseMinBlocks =
 template <uint32_t kWriteMask, bool kWithEntity, int kSparse, typename Body, typename... Cs>
 __global__ void __launch_bounds__(kBlock, kForEachSparseMinBlocks<kWithEntity, kSparse, Cs...>) for_each_kernel(const helios_gpu_match_args m, Body body,
                                                                                                 const helios_gpu_sparse_filter sf) {
+  if constexpr (requires { body.begin(); }) body.begin();  // optional per-thread prologue (all threads; published by the first barrier below)
   constexpr int N = sizeof...(Cs);
   constexpr bool kLoadEnt = kWithEntity || kSparse != 0;
   static_assert(N >= 1 && N <= HELIOS_GPU_MAX_QUERY_COMPONENTS, "1..8 data components per body");
@@ -453,6 +454,7 @@ __global__ void __launch_bounds__(kBlock) for_each_sparse_driven_kernel(const he
                                                                         const helios_gpu_sparse_filter sf,
                                                                         const helios_gpu_sparse_dir* __restrict__ dir,
                                                                         const helios_gpu_world_view wv) {
+  if constexpr (requires { body.begin(); }) body.begin();  // optional per-thread prologue (all threads; published by the first barrier below)
   constexpr int N = sizeof...(Cs);
   constexpr unsigned long long kNoTable = ~0ull;
   __shared__ unsigned long long s_row_begin[kFusedMaxTables];  // per TABLE: flattened first row, kNoTable if not matched
@@ -516,6 +518,7 @@ __global__ void __launch_bounds__(kBlock) for_each_sparse_driven_kernel(const he
 template <uint32_t kWriteMask, bool kWithEntity, int kSparse, typename Body, typename... Cs>
 __global__ void __launch_bounds__(kBlock) for_each_kernel_view(const helios_gpu_query_view* __restrict__ view, Body body,
                                                                const helios_gpu_sparse_filter sf) {
+  if constexpr (requires { body.begin(); }) body.begin();  // optional per-thread prologue (all threads; published by the first barrier below)
   using namespace detail;
   constexpr int N = sizeof...(Cs);
   __shared__ helios_gpu_segment s_seg;
@@ -650,6 +653,69 @@ __device__ __forceinline__ void async_push(const helios_gpu_async_ring& ring, bo
   // a full ring is reported by the next host call (tail - head > capacity); never write over undrained messages
   if (pos - *reinterpret_cast<const volatile unsigned long long*>(ring.cursors) < ring.capacity)
     reinterpret_cast<Msg*>(ring.data)[pos & (ring.capacity - 1)] = m;
+}
+
+// Staged enqueue for bodies that push from (almost) every row: a single tail atomic per warp serialises at about two
+// nanoseconds per atomic on one address — 16.8M rows cost over a millisecond.  Here each warp collects its messages in a
+// 4 KiB slice of shared memory and publishes a full slice at once: ONE tail atomic per ~4 KiB of messages and 512-byte
+// coalesced stores into the ring.  The body calls async_stage_begin() from begin(), async_push_staged() per row and
+// async_stage_flush() from finish() (every thread of the CTA runs begin() and finish()).
+constexpr uint32_t kAsyncStageBytes = 4096;
+template <typename Msg>
+struct AsyncStage {
+  static constexpr uint32_t kSlots = kAsyncStageBytes / sizeof(Msg);
+  static_assert(sizeof(Msg) % 4 == 0 && kSlots >= 64, "staged pushes need word-sized messages of at most 64 bytes");
+  Msg slots[kBlock / 32][kSlots];
+  uint32_t count[kBlock / 32];
+};
+template <typename Msg>
+__device__ __forceinline__ AsyncStage<Msg>& async_stage() {
+  __shared__ AsyncStage<Msg> s_stage;
+  return s_stage;
+}
+template <typename Msg>
+__device__ __forceinline__ void async_stage_begin() {
+  if ((threadIdx.x & 31u) == 0) async_stage<Msg>().count[threadIdx.x >> 5] = 0;
+  __syncwarp();
+}
+// Publish the warp's slice: called converged by the lanes in `mask`.
+template <typename Msg>
+__device__ __forceinline__ void async_stage_publish(const helios_gpu_async_ring& ring, uint32_t mask) {
+  AsyncStage<Msg>& st = async_stage<Msg>();
+  const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  const uint32_t n = st.count[wid];
+  if (n == 0) return;
+  const uint32_t leader = __ffs(mask) - 1, rank = __popc(mask & ((1u << lane) - 1u)), width = __popc(mask);
+  unsigned long long base = 0;
+  if (lane == leader) base = atomicAdd(ring.cursors + 1, (unsigned long long)n);
+  base = __shfl_sync(mask, base, leader);
+  const unsigned long long head = *reinterpret_cast<const volatile unsigned long long*>(ring.cursors);
+  for (uint32_t i = rank; i < n; i += width) {
+    const unsigned long long pos = base + i;
+    if (pos - head < ring.capacity) reinterpret_cast<Msg*>(ring.data)[pos & (ring.capacity - 1)] = st.slots[wid][i];
+  }
+  __syncwarp(mask);
+  if (lane == leader) st.count[wid] = 0;
+  __syncwarp(mask);
+}
+template <typename Msg>
+__device__ __forceinline__ void async_push_staged(const helios_gpu_async_ring& ring, bool active, const Msg& m) {
+  AsyncStage<Msg>& st = async_stage<Msg>();
+  const uint32_t mask = __activemask();
+  const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  const uint32_t votes = __ballot_sync(mask, active);
+  if (votes == 0) return;
+  if (st.count[wid] + __popc(votes) > AsyncStage<Msg>::kSlots) async_stage_publish<Msg>(ring, mask);
+  const uint32_t at = st.count[wid];
+  if (active) st.slots[wid][at + __popc(votes & ((1u << lane) - 1u))] = m;
+  __syncwarp(mask);
+  if (lane == uint32_t(__ffs(mask) - 1)) st.count[wid] = at + __popc(votes);
+  __syncwarp(mask);
+}
+template <typename Msg>
+__device__ __forceinline__ void async_stage_flush(const helios_gpu_async_ring& ring) {
+  __syncwarp();
+  async_stage_publish<Msg>(ring, 0xFFFFFFFFu);
 }
 
 template <typename Msg, typename Body>

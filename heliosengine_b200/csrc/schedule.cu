@@ -296,36 +296,50 @@ __device__ __forceinline__ bool cond_compare(uint64_t lhs, uint64_t rhs, uint32_
   }
 }
 __global__ void k_cond_begin(uint32_t* verdict) { *verdict = 1u; }
-// lhs = *a (+ *b when given): a resource word, a terminal-result field, or previous + current message counts
-__global__ void k_cond_test(uint32_t* verdict, const unsigned long long* a, const unsigned long long* b, uint32_t cmp,
-                            uint64_t rhs, uint32_t is_signed) {
-  const uint64_t lhs = (a ? *a : 0ull) + (b ? *b : 0ull);
-  if (!cond_compare(lhs, rhs, cmp, is_signed != 0)) *verdict = 0u;
-}
-// the verdict becomes the IF node's condition value (defaults to 0 at every graph launch)
-__global__ void k_cond_commit(cudaGraphConditionalHandle handle, const uint32_t* verdict) {
-  cudaGraphSetConditional(handle, *verdict ? 1u : 0u);
+// One launch closes a condition chain: every comparison of the list (a resource word, a terminal-result field, previous +
+// current message counts, a constant) is AND-ed into the verdict, which then becomes the IF node's condition value (the
+// handle defaults to 0 at every graph launch).
+struct CondTest {
+  const unsigned long long* a;  // lhs = *a (+ *b when given); both NULL = 0
+  const unsigned long long* b;
+  unsigned long long rhs;
+  uint32_t cmp, is_signed;
+};
+constexpr uint32_t kMaxCondTests = 8;
+struct CondTests {
+  CondTest t[kMaxCondTests];
+  uint32_t n, keep_verdict;  // keep_verdict: custom conditions already wrote *verdict (it started at 1)
+};
+__global__ void k_cond_finish(cudaGraphConditionalHandle handle, uint32_t* verdict, const CondTests tests) {
+  bool v = tests.keep_verdict ? *verdict != 0u : true;
+  for (uint32_t i = 0; i < tests.n; ++i) {
+    const CondTest& c = tests.t[i];
+    const uint64_t lhs = (c.a ? *c.a : 0ull) + (c.b ? *c.b : 0ull);
+    v = v && cond_compare(lhs, c.rhs, c.cmp, c.is_signed != 0);
+  }
+  *verdict = v ? 1u : 0u;
+  cudaGraphSetConditional(handle, v ? 1u : 0u);
 }
 
-// One condition on `stream`: AND its predicate into *verdict.
+// One condition on `stream`: launches whatever it needs (custom predicate, query terminal) and appends its comparison.
 int32_t eval_condition(helios_gpu_schedule* s, SysEntry& e, uint32_t index, CondEntry& c, uint32_t* verdict,
-                       cudaStream_t stream) {
+                       cudaStream_t stream, CondTests& tests) {
   helios_gpu_world* w = s->world;
   const helios_gpu_condition_desc& d = c.desc;
+  CondTest t{nullptr, nullptr, d.rhs, d.cmp, 0u};
+  bool has_test = true;
   switch (d.kind) {
-    case HELIOS_GPU_COND_CONSTANT:
-      k_cond_test<<<1, 1, 0, stream>>>(verdict, nullptr, nullptr, HELIOS_GPU_CMP_NE, d.rhs ? 1ull : 0ull, 0u);  // 0 != (rhs != 0)
-      ++w->launches;
+    case HELIOS_GPU_COND_CONSTANT:  // 0 != (rhs != 0)
+      t.rhs = d.rhs ? 1ull : 0ull;
+      t.cmp = HELIOS_GPU_CMP_NE;
       break;
     case HELIOS_GPU_COND_RESOURCE:
-      k_cond_test<<<1, 1, 0, stream>>>(verdict, reinterpret_cast<const unsigned long long*>(s->resources.as<uint8_t>() + d.offset),
-                                       nullptr, d.cmp, d.rhs, 0u);
-      ++w->launches;
+      t.a = reinterpret_cast<const unsigned long long*>(s->resources.as<uint8_t>() + d.offset);
       break;
     case HELIOS_GPU_COND_MESSAGES: {
       auto* dev = find_channel(w, d.reads_message)->d_dev.as<ChannelDev>();
-      k_cond_test<<<1, 1, 0, stream>>>(verdict, &dev->counts[0], &dev->counts[1], d.cmp, d.rhs, 0u);
-      ++w->launches;
+      t.a = &dev->counts[0];
+      t.b = &dev->counts[1];
       break;
     }
     case HELIOS_GPU_COND_TERMINAL:
@@ -354,14 +368,19 @@ int32_t eval_condition(helios_gpu_schedule* s, SysEntry& e, uint32_t index, Cond
       const int32_t st = d.launch(&ctx);
       if (st != HELIOS_GPU_OK) HG_FAIL(w, st, "run condition '%s' of system '%s' failed to launch (%d)", c.name.c_str(), e.name.c_str(), st);
       if (d.kind == HELIOS_GPU_COND_TERMINAL) {
-        k_cond_test<<<1, 1, 0, stream>>>(verdict, c.result.as<unsigned long long>() + d.field, nullptr, d.cmp, d.rhs,
-                                         d.field == HELIOS_GPU_COND_FIELD_I64 ? 1u : 0u);
-        ++w->launches;
+        t.a = c.result.as<unsigned long long>() + d.field;
+        t.is_signed = d.field == HELIOS_GPU_COND_FIELD_I64 ? 1u : 0u;
+      } else {
+        has_test = false;
       }
       break;
     }
     default:
       HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition '%s': unknown kind %u", c.name.c_str(), d.kind);
+  }
+  if (has_test) {
+    if (tests.n >= kMaxCondTests) HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "system '%s' has more than %u run conditions", e.name.c_str(), kMaxCondTests);
+    tests.t[tests.n++] = t;
   }
   HG_CUDA(w, cudaGetLastError());
   return HELIOS_GPU_OK;
@@ -371,9 +390,13 @@ int32_t eval_condition(helios_gpu_schedule* s, SysEntry& e, uint32_t index, Cond
 int32_t emit_guarded(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaStream_t stream) {
   helios_gpu_world* w = s->world;
   uint32_t* verdict = s->verdicts.as<uint32_t>() + index;
-  k_cond_begin<<<1, 1, 0, stream>>>(verdict);
-  ++w->launches;
-  for (CondEntry* c : e.merged) HG_TRY(eval_condition(s, e, index, *c, verdict, stream));
+  CondTests tests{};
+  for (CondEntry* c : e.merged) tests.keep_verdict |= c->desc.kind == HELIOS_GPU_COND_CUSTOM ? 1u : 0u;
+  if (tests.keep_verdict) {
+    k_cond_begin<<<1, 1, 0, stream>>>(verdict);
+    ++w->launches;
+  }
+  for (CondEntry* c : e.merged) HG_TRY(eval_condition(s, e, index, *c, verdict, stream, tests));
   cudaStreamCaptureStatus status = cudaStreamCaptureStatusNone;
   cudaGraph_t graph = nullptr;
   const cudaGraphNode_t* deps = nullptr;
@@ -382,7 +405,7 @@ int32_t emit_guarded(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaSt
   if (status != cudaStreamCaptureStatusActive || !graph) HG_FAIL(w, HELIOS_GPU_ERR_STATE, "guarded system outside a capture");
   cudaGraphConditionalHandle handle;
   HG_CUDA(w, cudaGraphConditionalHandleCreate(&handle, graph, 0u, cudaGraphCondAssignDefault));
-  k_cond_commit<<<1, 1, 0, stream>>>(handle, verdict);
+  k_cond_finish<<<1, 1, 0, stream>>>(handle, verdict, tests);
   ++w->launches;
   HG_CUDA(w, cudaGetLastError());
   HG_CUDA(w, cudaStreamGetCaptureInfo(stream, &status, nullptr, &graph, &deps, &n_deps));
