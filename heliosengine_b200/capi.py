@@ -101,7 +101,7 @@ class SystemDesc(C.Structure):
     ]
 
 
-COND_CUSTOM, COND_TERMINAL, COND_RESOURCE, COND_MESSAGES, COND_CONSTANT = 0, 1, 2, 3, 4
+COND_CUSTOM, COND_TERMINAL, COND_RESOURCE, COND_MESSAGES, COND_CONSTANT, COND_WORLD_RESOURCE = 0, 1, 2, 3, 4, 5
 COND_FIELD_VISITED, COND_FIELD_COUNT, COND_FIELD_INDEX, COND_FIELD_I64 = 0, 1, 2, 5
 CMP_EQ, CMP_NE, CMP_LT, CMP_LE, CMP_GT, CMP_GE = 0, 1, 2, 3, 4, 5
 
@@ -111,6 +111,7 @@ class ConditionDesc(C.Structure):
         ("name", C.c_char_p), ("kind", C.c_uint32), ("cmp", C.c_uint32), ("rhs", C.c_uint64),
         ("field", C.c_uint32), ("offset", C.c_uint32), ("query", C.c_void_p), ("launch", C.c_void_p),
         ("params", C.c_void_p), ("params_size", C.c_uint32), ("_pad", C.c_uint32), ("reads_message", C.c_uint64),
+        ("resource", C.c_uint64),
     ]
 
 
@@ -384,6 +385,51 @@ class World:
         self._check(self.b.fn("message_read")(self.h, C.c_uint64(fnv1a(name)), C.c_uint32(which), _ptr(buf), C.c_uint64(buf.nbytes)))
         return buf
 
+    # ---- world resources (reference resource/manager.hpp; world.hpp:491-620) ----
+    def resource_insert(self, name: str, value: bytes):
+        buf = C.create_string_buffer(value, len(value))
+        self._check(self.b.fn("resource_insert")(self.h, C.c_uint64(fnv1a(name)), buf, C.c_uint32(len(value))))
+        self.sizes["res:" + name] = len(value)
+
+    def resource_try_insert(self, name: str, value: bytes) -> bool:
+        buf = C.create_string_buffer(value, len(value))
+        ok = C.c_uint32()
+        self._check(self.b.fn("resource_try_insert")(self.h, C.c_uint64(fnv1a(name)), buf, C.c_uint32(len(value)), C.byref(ok)))
+        if ok.value:
+            self.sizes["res:" + name] = len(value)
+        return bool(ok.value)
+
+    def resource_remove(self, name: str):
+        self._check(self.b.fn("resource_remove")(self.h, C.c_uint64(fnv1a(name))))
+
+    def resource_try_remove(self, name: str) -> bool:
+        ok = C.c_uint32()
+        self._check(self.b.fn("resource_try_remove")(self.h, C.c_uint64(fnv1a(name)), C.byref(ok)))
+        return bool(ok.value)
+
+    def resource_has(self, name: str) -> bool:
+        v = C.c_uint32()
+        self._check(self.b.fn("resource_has")(self.h, C.c_uint64(fnv1a(name)), C.byref(v)))
+        return bool(v.value)
+
+    def resource_count(self) -> int:
+        v = C.c_uint32()
+        self._check(self.b.fn("resource_count")(self.h, C.byref(v)))
+        return v.value
+
+    def resource_clear(self):
+        self._check(self.b.fn("resource_clear")(self.h))
+
+    def resource_read(self, name: str) -> bytes:
+        n = self.sizes["res:" + name]
+        buf = C.create_string_buffer(n)
+        self._check(self.b.fn("resource_read")(self.h, C.c_uint64(fnv1a(name)), buf, C.c_uint32(n)))
+        return buf.raw
+
+    def resource_write(self, name: str, value: bytes):
+        buf = C.create_string_buffer(value, len(value))
+        self._check(self.b.fn("resource_write")(self.h, C.c_uint64(fnv1a(name)), buf, C.c_uint32(len(value))))
+
     # ---- async messages (reference message/async_queue.hpp; MessageManager::WriteAsync / ManualAsyncClear) ----
     def async_message_register(self, name: str, size: int, capacity: int = 1024):
         self._check(self.b.fn("async_message_register")(self.h, C.c_uint64(fnv1a(name)), C.c_uint32(size), C.c_uint64(capacity)))
@@ -556,7 +602,7 @@ class Schedule:
 
     def _condition(self, name: str, kind: int, cmp: int = CMP_NE, rhs: int = 0, field: int = 0, offset: int = 0,
                    query: "Query | None" = None, builtin: str | None = None, params: bytes = b"",
-                   reads_message: str | None = None) -> ConditionDesc:
+                   reads_message: str | None = None, resource: str | None = None) -> ConditionDesc:
         d = ConditionDesc()
         nm = name.encode()
         pb = C.create_string_buffer(params, len(params)) if params else None
@@ -572,6 +618,7 @@ class Schedule:
         d.params = C.cast(pb, C.c_void_p) if pb is not None else None
         d.params_size = len(params)
         d.reads_message = fnv1a(reads_message) if reads_message else 0
+        d.resource = fnv1a(resource) if resource else 0
         return d
 
     def run_if(self, system: int, name: str, kind: int, **kw):

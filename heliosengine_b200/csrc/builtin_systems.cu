@@ -352,6 +352,47 @@ int32_t launch_heal_alerted(const helios_gpu_system_ctx* ctx) {
                                                         p.max_count ? p.max_count : ~0ull);
 }
 
+// ---- world resources: "apply_gravity" Query<Velocity&> + Res<const Gravity> (v += g * dt, the value is read on the device
+// every launch, so a host WriteResource between frames takes effect without re-capturing a graph), and "tick_counter"
+// ResMut<FrameCounter> (a resource-only system: ticks += 1, last = ticks * stride) -----------------------------------------
+struct Gravity { float gx, gy, dt, pad; };
+struct FrameCounter { unsigned long long ticks, last; };
+struct ResourceParams { uint64_t type_hash; uint64_t stride; };
+struct GravityBody {
+  const Gravity* g;
+  __device__ void operator()(const Row&, Velocity& v) const {
+    const Gravity gr = *g;
+    v.dx = v.dx + gr.gx * gr.dt;
+    v.dy = v.dy + gr.gy * gr.dt;
+  }
+};
+int32_t launch_apply_gravity(const helios_gpu_system_ctx* ctx) {
+  if (ctx->params_size < sizeof(ResourceParams)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  ResourceParams p;
+  std::memcpy(&p, ctx->params, sizeof(p));
+  void* g = nullptr;
+  uint32_t bytes = 0;
+  if (const int32_t rc = helios_gpu_resource_ptr(ctx->world, p.type_hash, &g, &bytes)) return rc;
+  if (bytes != sizeof(Gravity)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  return for_each_launch<0b1u, false, GravityBody, Velocity>(ctx, GravityBody{static_cast<const Gravity*>(g)});
+}
+__global__ void k_tick_counter(FrameCounter* c, unsigned long long stride) {
+  c->ticks += 1;
+  c->last = c->ticks * stride;
+}
+int32_t launch_tick_counter(const helios_gpu_system_ctx* ctx) {
+  if (ctx->params_size < sizeof(ResourceParams)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  ResourceParams p;
+  std::memcpy(&p, ctx->params, sizeof(p));
+  void* c = nullptr;
+  uint32_t bytes = 0;
+  if (const int32_t rc = helios_gpu_resource_ptr(ctx->world, p.type_hash, &c, &bytes)) return rc;
+  if (bytes != sizeof(FrameCounter)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  k_tick_counter<<<1, 1, 0, static_cast<cudaStream_t>(ctx->stream)>>>(static_cast<FrameCounter*>(c), p.stride);
+  helios_gpu_world_note_launches(ctx->world, 1);
+  return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
+}
+
 // ---- run condition "entity_alive": a WorldView-style predicate (run_condition.cpp:72-74, world_view.hpp Exists):
 // the guarded system runs only while the entity named in params is alive.  HELIOS_GPU_COND_CUSTOM: veto = store 0. -------
 __global__ void k_cond_entity_alive(uint32_t* verdict, helios_gpu_world_view wv, helios_gpu_entity_t e) {
@@ -383,6 +424,7 @@ const Entry kBuiltins[] = {
     {"stats", launch_stats},           {"exit_check", launch_exit_check},
     {"despawn_dead", launch_despawn_dead},
     {"alert_low_health", launch_alert_low_health}, {"heal_alerted", launch_heal_alerted},
+    {"apply_gravity", launch_apply_gravity}, {"tick_counter", launch_tick_counter},
 };
 
 }  // namespace

@@ -178,6 +178,109 @@ int32_t async_cursors(helios_gpu_world* w, AsyncChannel* c, unsigned long long c
 
 extern "C" {
 
+// ---- world resources (resource/manager.hpp) ---------------------------------------------------------------------------
+static WorldResource* find_resource(helios_gpu_world* w, uint64_t hash) {
+  for (auto& r : w->resources)
+    if (r->hash == hash) return r.get();
+  return nullptr;
+}
+
+int32_t helios_gpu_resource_insert(helios_gpu_world* w, uint64_t hash, const void* value, uint32_t size) {
+  if (!w || !value || size == 0 || hash == 0) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  WorldResource* r = find_resource(w, hash);
+  if (!r) {
+    auto nr = std::make_unique<WorldResource>();
+    nr->hash = hash;
+    nr->size = size;
+    HG_CUDA(w, nr->value.reserve((size + 15u) & ~15u, 0, w->stream, false));
+    r = nr.get();
+    w->resources.push_back(std::move(nr));
+    ++w->epoch;  // a new device address: graphs that resolve resources are re-captured
+  } else if (r->size != size) {
+    HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "resource re-inserted with %u bytes, registered with %u", size, r->size);
+  }
+  HG_CUDA(w, cudaMemcpyAsync(r->value.ptr, value, size, cudaMemcpyHostToDevice, w->stream));
+  HG_CUDA(w, cudaStreamSynchronize(w->stream));  // `value` is the caller's memory
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_resource_try_insert(helios_gpu_world* w, uint64_t hash, const void* value, uint32_t size, uint32_t* inserted) {
+  if (!w) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  const bool present = find_resource(w, hash) != nullptr;  // manager.hpp:83-91: false when the resource exists
+  if (inserted) *inserted = present ? 0u : 1u;
+  return present ? HELIOS_GPU_OK : helios_gpu_resource_insert(w, hash, value, size);
+}
+
+int32_t helios_gpu_resource_try_remove(helios_gpu_world* w, uint64_t hash, uint32_t* removed) {
+  if (!w) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (removed) *removed = 0;
+  for (size_t i = 0; i < w->resources.size(); ++i)
+    if (w->resources[i]->hash == hash) {
+      HG_CUDA(w, cudaStreamSynchronize(w->stream));  // kernels that hold the address have finished
+      w->resources.erase(w->resources.begin() + i);
+      ++w->epoch;
+      if (removed) *removed = 1;
+      break;
+    }
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_resource_remove(helios_gpu_world* w, uint64_t hash) {
+  uint32_t removed = 0;
+  HG_TRY(helios_gpu_resource_try_remove(w, hash, &removed));
+  if (!removed) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "resource does not exist");  // manager.hpp:112-116 HELIOS_ASSERT
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_resource_has(helios_gpu_world* w, uint64_t hash, uint32_t* out) {
+  if (!w || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  *out = find_resource(w, hash) ? 1u : 0u;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_resource_count(helios_gpu_world* w, uint32_t* out) {
+  if (!w || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  *out = uint32_t(w->resources.size());
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_resource_clear(helios_gpu_world* w) {
+  if (!w) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  HG_CUDA(w, cudaStreamSynchronize(w->stream));
+  if (!w->resources.empty()) ++w->epoch;
+  w->resources.clear();
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_resource_read(helios_gpu_world* w, uint64_t hash, void* out, uint32_t size) {
+  if (!w || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  WorldResource* r = find_resource(w, hash);
+  if (!r) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "resource does not exist");  // manager.hpp:118-133 HELIOS_ASSERT
+  if (size != r->size) HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "resource holds %u bytes, %u asked", r->size, size);
+  HG_CUDA(w, cudaMemcpyAsync(out, r->value.ptr, size, cudaMemcpyDeviceToHost, w->stream));
+  HG_CUDA(w, cudaStreamSynchronize(w->stream));
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_resource_write(helios_gpu_world* w, uint64_t hash, const void* value, uint32_t size) {
+  if (!w || !value) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  WorldResource* r = find_resource(w, hash);
+  if (!r) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "resource does not exist");
+  if (size != r->size) HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "resource holds %u bytes, %u given", r->size, size);
+  HG_CUDA(w, cudaMemcpyAsync(r->value.ptr, value, size, cudaMemcpyHostToDevice, w->stream));
+  HG_CUDA(w, cudaStreamSynchronize(w->stream));
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_resource_ptr(helios_gpu_world* w, uint64_t hash, void** device_ptr, uint32_t* size) {
+  if (!w || !device_ptr) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  WorldResource* r = find_resource(w, hash);
+  if (!r) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "resource does not exist");
+  *device_ptr = r->value.ptr;
+  if (size) *size = r->size;
+  return HELIOS_GPU_OK;
+}
+
 int32_t helios_gpu_async_message_register(helios_gpu_world* w, uint64_t hash, uint32_t size, uint64_t capacity) {
   if (!w || size == 0 || hash == 0) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   if (find_async(w, hash)) return HELIOS_GPU_OK;  // async_queue.hpp Register<T>: idempotent (tests/message/async_queue.cpp:401)

@@ -336,6 +336,14 @@ int32_t eval_condition(helios_gpu_schedule* s, SysEntry& e, uint32_t index, Cond
     case HELIOS_GPU_COND_RESOURCE:
       t.a = reinterpret_cast<const unsigned long long*>(s->resources.as<uint8_t>() + d.offset);
       break;
+    case HELIOS_GPU_COND_WORLD_RESOURCE: {
+      void* p = nullptr;
+      uint32_t bytes = 0;
+      HG_TRY(helios_gpu_resource_ptr(w, d.resource, &p, &bytes));
+      if (d.offset + 8 > bytes) HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition '%s': offset past the resource", c.name.c_str());
+      t.a = reinterpret_cast<const unsigned long long*>(static_cast<const uint8_t*>(p) + d.offset);
+      break;
+    }
     case HELIOS_GPU_COND_MESSAGES: {
       auto* dev = find_channel(w, d.reads_message)->d_dev.as<ChannelDev>();
       t.a = &dev->counts[0];
@@ -651,7 +659,7 @@ int32_t helios_gpu_schedule_build(helios_gpu_schedule* s) {
 
 static int32_t make_condition(helios_gpu_schedule* s, const helios_gpu_condition_desc* d, std::unique_ptr<CondEntry>& out) {
   helios_gpu_world* w = s->world;
-  if (d->kind > HELIOS_GPU_COND_CONSTANT || d->cmp > HELIOS_GPU_CMP_GE)
+  if (d->kind > HELIOS_GPU_COND_WORLD_RESOURCE || d->cmp > HELIOS_GPU_CMP_GE)
     HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition: unknown kind or comparison");
   if ((d->kind == HELIOS_GPU_COND_CUSTOM || d->kind == HELIOS_GPU_COND_TERMINAL) && !d->launch)
     HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition: a custom / terminal condition needs a launch function");
@@ -659,6 +667,8 @@ static int32_t make_condition(helios_gpu_schedule* s, const helios_gpu_condition
     HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition: a terminal condition needs a query and a result field");
   if (d->kind == HELIOS_GPU_COND_RESOURCE && (d->offset % 8 != 0 || d->offset + 8 > HELIOS_GPU_RESOURCE_BYTES))
     HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition: resource offset must be an 8-byte word inside the block");
+  if (d->kind == HELIOS_GPU_COND_WORLD_RESOURCE && (d->offset % 8 != 0 || !d->resource))
+    HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition: a world-resource condition needs a type hash and an 8-byte-aligned offset");
   if (d->kind == HELIOS_GPU_COND_MESSAGES && !d->reads_message)
     HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "run condition: a message condition needs reads_message");
   out = std::make_unique<CondEntry>();

@@ -66,6 +66,12 @@ struct AsyncChannel {          // one registered async message type (message/asy
   DevBuf data, cursors;
 };
 
+struct WorldResource {         // one resource value in HBM (resource/manager.hpp: TypedBuffer per type)
+  uint64_t hash = 0;
+  uint32_t size = 0;
+  DevBuf value;
+};
+
 struct HostCmdQueue {         // host staging of a CmdQueue (command/queue.hpp:137-163)
   std::vector<helios_gpu_command> cmds;
   std::vector<uint8_t> payload;
@@ -145,7 +151,8 @@ struct helios_gpu_world {
 
   std::vector<std::unique_ptr<hgpu::MsgChannel>> channels;
   std::unordered_map<uint64_t, int> channel_of;
-  std::vector<std::unique_ptr<hgpu::AsyncChannel>> async_channels;  // AsyncMessageQueue (message/manager.hpp:359)
+  std::vector<std::unique_ptr<hgpu::AsyncChannel>> async_channels;
+  std::vector<std::unique_ptr<hgpu::WorldResource>> resources;     // ResourceManager (world.hpp resources_)  // AsyncMessageQueue (message/manager.hpp:359)
 
   std::vector<helios_gpu_query*> queries;
   std::vector<helios_gpu_schedule*> schedules;

@@ -268,6 +268,31 @@ HELIOS_GPU_API int32_t helios_gpu_message_counts(helios_gpu_world* w, uint64_t t
 HELIOS_GPU_API int32_t helios_gpu_message_read(helios_gpu_world* w, uint64_t type_hash, uint32_t which, void* out,
                                                uint64_t capacity_bytes);
 
+/* ---- world resources (resource/manager.hpp:20-250; World::InsertResources / TryInsertResources / RemoveResources /
+ * TryRemoveResources / ReadResource / WriteResource / HasResource, world.hpp:491-620; system parameters Res<const T> /
+ * ResMut<T>, resource/param.hpp) -----------------------------------------------------------------------------------
+ * A resource is one trivially copyable value per type, resident in HBM at an address that is stable until the resource is
+ * removed: a system body takes the pointer (helios_gpu_resource_ptr) and its kernels read / write the value in place, so
+ * a host-side WriteResource between frames needs no re-capture of graphs.  Conflicts between systems come from the
+ * read_resources / write_resources type lists of helios_gpu_system_desc, as in the reference (access_policy.hpp:172-196). */
+/* Insert (overwrites an existing value; the size of a type is fixed by its first insertion). */
+HELIOS_GPU_API int32_t helios_gpu_resource_insert(helios_gpu_world* w, uint64_t type_hash, const void* value, uint32_t size);
+/* TryInsert: *inserted = 0 and nothing changes when the resource exists. */
+HELIOS_GPU_API int32_t helios_gpu_resource_try_insert(helios_gpu_world* w, uint64_t type_hash, const void* value,
+                                                      uint32_t size, uint32_t* inserted);
+/* Remove: HELIOS_GPU_ERR_NOT_FOUND if absent (the reference asserts); TryRemove: *removed tells. */
+HELIOS_GPU_API int32_t helios_gpu_resource_remove(helios_gpu_world* w, uint64_t type_hash);
+HELIOS_GPU_API int32_t helios_gpu_resource_try_remove(helios_gpu_world* w, uint64_t type_hash, uint32_t* removed);
+HELIOS_GPU_API int32_t helios_gpu_resource_has(helios_gpu_world* w, uint64_t type_hash, uint32_t* out);
+HELIOS_GPU_API int32_t helios_gpu_resource_count(helios_gpu_world* w, uint32_t* out);
+/* ResourceManager::Clear */
+HELIOS_GPU_API int32_t helios_gpu_resource_clear(helios_gpu_world* w);
+/* ReadResource (copies the value out; synchronises) / WriteResource; HELIOS_GPU_ERR_NOT_FOUND if absent. */
+HELIOS_GPU_API int32_t helios_gpu_resource_read(helios_gpu_world* w, uint64_t type_hash, void* out, uint32_t size);
+HELIOS_GPU_API int32_t helios_gpu_resource_write(helios_gpu_world* w, uint64_t type_hash, const void* value, uint32_t size);
+/* Res<const T> / ResMut<T>: the device address of the value. */
+HELIOS_GPU_API int32_t helios_gpu_resource_ptr(helios_gpu_world* w, uint64_t type_hash, void** device_ptr, uint32_t* size);
+
 /* ---- async messages (message/async_queue.hpp:40-330: one moodycamel MPMC queue per type; AsyncMessageWriter/Reader,
  * async_writer.hpp:20-94, async_reader.hpp:20-131; MessageManager::WriteAsync / WriteAsyncBulk / ManualAsyncClear /
  * HasAsyncMessages, message/manager.hpp:135-183,243-249) ---------------------------------------------------------------
@@ -495,6 +520,7 @@ HELIOS_GPU_API int32_t helios_gpu_schedule_read_resources(helios_gpu_schedule* s
 #define HELIOS_GPU_COND_RESOURCE 2u /* test the u64 at byte `offset` of the schedule's resource block (Res<const T>) */
 #define HELIOS_GPU_COND_MESSAGES 3u /* test the number of messages a MessageReader<reads_message> would see */
 #define HELIOS_GPU_COND_CONSTANT 4u /* verdict = (rhs != 0): AlwaysTrue / AlwaysFalse */
+#define HELIOS_GPU_COND_WORLD_RESOURCE 5u /* test the u64 at byte `offset` of world resource `resource` (Res<const T>) */
 #define HELIOS_GPU_COND_FIELD_VISITED 0u /* byte offsets/8 into helios_gpu_terminal_result */
 #define HELIOS_GPU_COND_FIELD_COUNT 1u
 #define HELIOS_GPU_COND_FIELD_INDEX 2u
@@ -518,6 +544,7 @@ typedef struct helios_gpu_condition_desc {
   uint32_t params_size;
   uint32_t _pad;
   uint64_t reads_message;      /* MESSAGES */
+  uint64_t resource;           /* WORLD_RESOURCE: resource type hash (must exist when the schedule runs) */
 } helios_gpu_condition_desc;
 /* SystemHandle::RunIf (schedule/system_handle.hpp): appended to the system's own condition list. */
 HELIOS_GPU_API int32_t helios_gpu_schedule_add_run_condition(helios_gpu_schedule* s, uint32_t system_index,

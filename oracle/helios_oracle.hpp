@@ -1154,6 +1154,35 @@ private:
   std::map<TypeIndex, Storage> messages_;
 };
 
+// ------------------------------------------------------------------------------------------------
+// resource/manager.hpp:20-250 — ResourceManager: one value per resource type (raw bytes here).
+// ------------------------------------------------------------------------------------------------
+class ResourceManager {
+public:
+  void Clear() { resources_.clear(); }                                                   // :20
+  void Insert(TypeIndex t, const void* v, size_t n) {                                     // :70-76 replaces an existing value
+    const auto* p = static_cast<const uint8_t*>(v);
+    resources_[t].assign(p, p + n);
+  }
+  bool TryInsert(TypeIndex t, const void* v, size_t n) {                                  // :78-87 false when present
+    if (Has(t)) return false;
+    Insert(t, v, n);
+    return true;
+  }
+  bool TryRemove(TypeIndex t) { return resources_.erase(t) != 0; }                        // :44-47
+  bool Remove(TypeIndex t) { return TryRemove(t); }                                       // :108-112 asserts on absence → false
+  uint8_t* TryGet(TypeIndex t) {                                                          // :134-141 nullptr when missing
+    const auto it = resources_.find(t);
+    return it == resources_.end() ? nullptr : it->second.data();
+  }
+  size_t SizeOf(TypeIndex t) const { const auto it = resources_.find(t); return it == resources_.end() ? 0 : it->second.size(); }
+  bool Has(TypeIndex t) const { return resources_.count(t) != 0; }                        // :56-59
+  size_t Count() const { return resources_.size(); }                                      // :60
+
+private:
+  std::map<TypeIndex, std::vector<uint8_t>> resources_;
+};
+
 class World;
 
 // command/queue.hpp:137-163 — FIFO.
@@ -1185,6 +1214,7 @@ public:
   ComponentManager components;
   MessageManager messages;
   AsyncMessageQueue async_messages;  // MessageManager::async_messages_ (message/manager.hpp:359)
+  ResourceManager resources;         // world.hpp resources_ (InsertResources / ReadResource / WriteResource ...)
   CmdQueue command_queue;  // world.hpp:945 global queue
   // quirk #13: every structural call also writes a builtin message.  The 8-byte payload is the entity.
   bool emit_builtin_messages = false;

@@ -303,6 +303,38 @@ int32_t sys_heal_alerted(const OCtx* c) {
   return 0;
 }
 
+// world resources: Res<const Gravity> / ResMut<FrameCounter>
+struct Gravity { float gx, gy, dt, pad; };
+struct FrameCounter { unsigned long long ticks, last; };
+struct ResourceParams { uint64_t type_hash; uint64_t stride; };
+int32_t sys_apply_gravity(const OCtx* c) {
+  ResourceParams p;
+  std::memcpy(&p, c->params, sizeof(p));
+  OWorld* w = c->world;
+  const uint8_t* raw = w->world.resources.TryGet(p.type_hash);
+  if (!raw) return HELIOS_GPU_ERR_NOT_FOUND;
+  Gravity g;
+  std::memcpy(&g, raw, sizeof(g));
+  ho::ForEach(w->world.components, *c->query, [&](ho::Entity, uint8_t** cols) {
+    auto* v = reinterpret_cast<Velocity*>(cols[0]);
+    v->dx = v->dx + g.gx * g.dt;
+    v->dy = v->dy + g.gy * g.dt;
+  });
+  return 0;
+}
+int32_t sys_tick_counter(const OCtx* c) {
+  ResourceParams p;
+  std::memcpy(&p, c->params, sizeof(p));
+  uint8_t* raw = c->world->world.resources.TryGet(p.type_hash);
+  if (!raw) return HELIOS_GPU_ERR_NOT_FOUND;
+  FrameCounter fc;
+  std::memcpy(&fc, raw, sizeof(fc));
+  fc.ticks += 1;
+  fc.last = fc.ticks * p.stride;
+  std::memcpy(raw, &fc, sizeof(fc));
+  return 0;
+}
+
 struct Builtin {
   const char* name;
   OSystemFn fn;
@@ -314,6 +346,7 @@ const Builtin kBuiltins[] = {
     {"exit_check", sys_exit_check}, {"despawn_dead", sys_despawn_dead},
     {"buff_heal", sys_buff_heal}, {"buff_optional", sys_buff_optional},
     {"alert_low_health", sys_alert_low_health}, {"heal_alerted", sys_heal_alerted},
+    {"apply_gravity", sys_apply_gravity}, {"tick_counter", sys_tick_counter},
 };
 
 // helios_gpu_command → oracle Command (payload: ascending slot order, each value padded to 4 bytes).
@@ -720,6 +753,54 @@ HO_API int32_t helios_oracle_message_read(void* wp, uint64_t hash, uint32_t whic
   return 0;
 }
 
+// ---- world resources (resource/manager.hpp; world.hpp:491-620) ---------------------------------------------------------------
+HO_API int32_t helios_oracle_resource_insert(void* wp, uint64_t hash, const void* v, uint32_t size) {
+  if (!v || size == 0 || hash == 0) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  auto& r = W(wp)->world.resources;
+  if (r.Has(hash) && r.SizeOf(hash) != size) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  r.Insert(hash, v, size);
+  return 0;
+}
+HO_API int32_t helios_oracle_resource_try_insert(void* wp, uint64_t hash, const void* v, uint32_t size, uint32_t* inserted) {
+  const bool ok = W(wp)->world.resources.TryInsert(hash, v, size);
+  if (inserted) *inserted = ok ? 1u : 0u;
+  return 0;
+}
+HO_API int32_t helios_oracle_resource_try_remove(void* wp, uint64_t hash, uint32_t* removed) {
+  const bool ok = W(wp)->world.resources.TryRemove(hash);
+  if (removed) *removed = ok ? 1u : 0u;
+  return 0;
+}
+HO_API int32_t helios_oracle_resource_remove(void* wp, uint64_t hash) {
+  return W(wp)->world.resources.Remove(hash) ? 0 : HELIOS_GPU_ERR_NOT_FOUND;
+}
+HO_API int32_t helios_oracle_resource_has(void* wp, uint64_t hash, uint32_t* out) {
+  *out = W(wp)->world.resources.Has(hash) ? 1u : 0u;
+  return 0;
+}
+HO_API int32_t helios_oracle_resource_count(void* wp, uint32_t* out) {
+  *out = uint32_t(W(wp)->world.resources.Count());
+  return 0;
+}
+HO_API int32_t helios_oracle_resource_clear(void* wp) {
+  W(wp)->world.resources.Clear();
+  return 0;
+}
+HO_API int32_t helios_oracle_resource_read(void* wp, uint64_t hash, void* out, uint32_t size) {
+  auto& r = W(wp)->world.resources;
+  if (!r.Has(hash)) return HELIOS_GPU_ERR_NOT_FOUND;
+  if (r.SizeOf(hash) != size) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  std::memcpy(out, r.TryGet(hash), size);
+  return 0;
+}
+HO_API int32_t helios_oracle_resource_write(void* wp, uint64_t hash, const void* v, uint32_t size) {
+  auto& r = W(wp)->world.resources;
+  if (!r.Has(hash)) return HELIOS_GPU_ERR_NOT_FOUND;
+  if (r.SizeOf(hash) != size) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  std::memcpy(r.TryGet(hash), v, size);
+  return 0;
+}
+
 // ---- async messages (message/async_queue.hpp; MessageManager::WriteAsync / WriteAsyncBulk / ManualAsyncClear) -------------
 HO_API int32_t helios_oracle_async_message_register(void* wp, uint64_t hash, uint32_t size, uint64_t) {
   if (size == 0 || hash == 0) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
@@ -822,7 +903,8 @@ bool o_compare(uint64_t lhs, uint64_t rhs, uint32_t cmp, bool is_signed) {
   }
 }
 int32_t o_make_condition(OSchedule* s, const helios_gpu_condition_desc* d, ho::RunCondition& out) {
-  if (d->kind > HELIOS_GPU_COND_CONSTANT || d->cmp > HELIOS_GPU_CMP_GE) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (d->kind > HELIOS_GPU_COND_WORLD_RESOURCE || d->cmp > HELIOS_GPU_CMP_GE) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (d->kind == HELIOS_GPU_COND_WORLD_RESOURCE && (d->offset % 8 != 0 || !d->resource)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   if ((d->kind == HELIOS_GPU_COND_CUSTOM || d->kind == HELIOS_GPU_COND_TERMINAL) && !d->launch) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   if (d->kind == HELIOS_GPU_COND_TERMINAL && (!d->query || d->field > HELIOS_GPU_COND_FIELD_I64)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   if (d->kind == HELIOS_GPU_COND_RESOURCE && (d->offset % 8 != 0 || d->offset + 8 > HELIOS_GPU_RESOURCE_BYTES)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
@@ -839,6 +921,13 @@ int32_t o_make_condition(OSchedule* s, const helios_gpu_condition_desc* d, ho::R
       case HELIOS_GPU_COND_RESOURCE: {
         uint64_t v;
         std::memcpy(&v, s->resources.data() + desc.offset, 8);
+        return o_compare(v, desc.rhs, desc.cmp, false);
+      }
+      case HELIOS_GPU_COND_WORLD_RESOURCE: {  // Res<const T>: missing resource = the reference's assert → false here
+        const uint8_t* raw = world.resources.TryGet(desc.resource);
+        if (!raw || desc.offset + 8 > world.resources.SizeOf(desc.resource)) return false;
+        uint64_t v;
+        std::memcpy(&v, raw + desc.offset, 8);
         return o_compare(v, desc.rhs, desc.cmp, false);
       }
       case HELIOS_GPU_COND_MESSAGES: {  // what a MessageReader<T> sees: previous ++ current (message/reader.hpp:770-820)
