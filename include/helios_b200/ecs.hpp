@@ -375,6 +375,50 @@ public:
     return out;
   }
 
+  // ---- resources (world.hpp:491-620 InsertResources / TryInsertResources / RemoveResources / TryRemoveResources /
+  //      ReadResource / WriteResource / HasResource; resource/manager.hpp): one HBM-resident value per type ----
+  template <typename R>
+  void InsertResources(const R& r) {
+    static_assert(std::is_trivially_copyable_v<R>, "a GPU resource is copied to device memory");
+    Check(helios_gpu_resource_insert(w_, TypeIndexOf<R>(), &r, sizeof(R)));
+  }
+  template <typename R>
+  bool TryInsertResources(const R& r) {
+    uint32_t ok = 0;
+    Check(helios_gpu_resource_try_insert(w_, TypeIndexOf<R>(), &r, sizeof(R), &ok));
+    return ok != 0;
+  }
+  template <typename R>
+  void RemoveResources() { Check(helios_gpu_resource_remove(w_, TypeIndexOf<R>())); }
+  template <typename R>
+  bool TryRemoveResources() {
+    uint32_t ok = 0;
+    Check(helios_gpu_resource_try_remove(w_, TypeIndexOf<R>(), &ok));
+    return ok != 0;
+  }
+  template <typename R>
+  bool HasResource() {
+    uint32_t v = 0;
+    Check(helios_gpu_resource_has(w_, TypeIndexOf<R>(), &v));
+    return v != 0;
+  }
+  // ReadResource returns a COPY (the value lives in device memory); WriteResource<R>(value) replaces it
+  template <typename R>
+  R ReadResource() {
+    R r;
+    Check(helios_gpu_resource_read(w_, TypeIndexOf<R>(), &r, sizeof(R)));
+    return r;
+  }
+  template <typename R>
+  void WriteResource(const R& r) { Check(helios_gpu_resource_write(w_, TypeIndexOf<R>(), &r, sizeof(R))); }
+  // Res<const R> / ResMut<R> of a GPU system body: the device address of the value
+  template <typename R>
+  R* ResourceDevicePtr() {
+    void* p = nullptr;
+    Check(helios_gpu_resource_ptr(w_, TypeIndexOf<R>(), &p, nullptr));
+    return static_cast<R*>(p);
+  }
+
   // ---- async messages (message/async_queue.hpp; MessageManager::WriteAsync / WriteAsyncBulk / ManualAsyncClear /
   //      HasAsyncMessages, message/manager.hpp:135-183,243-249): a device ring per type, not tied to World::Update ----
   template <typename M>
@@ -630,6 +674,16 @@ public:
     // [](Res<const T> r) { return word(r) <cmp> rhs; } over the u64 at `byte_offset` of the schedule's resource block
     static GpuRunCondition Resource(uint32_t byte_offset, uint32_t cmp, uint64_t rhs, std::string name = {}) {
       GpuRunCondition c(std::move(name), HELIOS_GPU_COND_RESOURCE);
+      c.d_.offset = byte_offset;
+      c.d_.cmp = cmp;
+      c.d_.rhs = rhs;
+      return c;
+    }
+    // [](Res<const R> r) { return word(r) <cmp> rhs; } over the u64 at `byte_offset` of the WORLD resource R
+    template <typename R>
+    static GpuRunCondition WorldResource(uint32_t byte_offset, uint32_t cmp, uint64_t rhs, std::string name = {}) {
+      GpuRunCondition c(std::move(name), HELIOS_GPU_COND_WORLD_RESOURCE);
+      c.d_.resource = TypeIndexOf<R>();
       c.d_.offset = byte_offset;
       c.d_.cmp = cmp;
       c.d_.rhs = rhs;

@@ -224,6 +224,27 @@ int main(int argc, char** argv) {
     CHECK((schedule.LastVerdicts() == std::vector<uint32_t>{1, 0, 1, 0, 1, 1, 0}));
     CHECK(world.ReadComponent<Health>(ents[7]).hp == expected_hp + 4);
   }
+  // ---- resources (tests/resource/manager.cpp:146-358; tests/schedule/schedule.cpp:559-597 CounterResource) ----
+  {
+    struct CounterResource { uint64_t value = 0; uint64_t pad = 0; };
+    struct OtherResource { float v = 0; };
+    ecs::World world;
+    CHECK(!world.HasResource<CounterResource>());
+    world.InsertResources(CounterResource{42});
+    CHECK(world.HasResource<CounterResource>() && world.ReadResource<CounterResource>().value == 42);
+    world.InsertResources(CounterResource{7});                       // Insert replaces
+    CHECK(world.ReadResource<CounterResource>().value == 7);
+    CHECK(!world.TryInsertResources(CounterResource{9}) && world.ReadResource<CounterResource>().value == 7);
+    CHECK(world.TryInsertResources(OtherResource{1.5f}) && world.ReadResource<OtherResource>().v == 1.5f);
+    world.WriteResource(CounterResource{100});
+    CHECK(world.ReadResource<CounterResource>().value == 100 && world.ResourceDevicePtr<CounterResource>() != nullptr);
+    world.RemoveResources<CounterResource>();
+    CHECK(!world.HasResource<CounterResource>() && world.HasResource<OtherResource>());
+    CHECK(!world.TryRemoveResources<CounterResource>() && world.TryRemoveResources<OtherResource>());
+    bool missing = false;
+    try { world.RemoveResources<CounterResource>(); } catch (const ecs::GpuError& e) { missing = e.Status() == HELIOS_GPU_ERR_NOT_FOUND; }
+    CHECK(missing);
+  }
   // ---- async messages (tests/message/async_queue.cpp:144-287; manager.hpp WriteAsync / ManualAsyncClear) ----
   {
     struct AsyncEvent { int id = 0; };
