@@ -1,0 +1,152 @@
+// routing.cu — cross-shard message routing (SURVEY.md §8e "Messages": entities are partitioned by entity-index range
+// across the GPUs of one box; a message whose target entity lives on another shard is sent to the shard that owns it).
+//
+// The reference runs one world in one process (world.hpp:52-78), so there is nothing to route there; the contract this
+// step keeps is the reference's message ORDER: after routing, shard g's queue holds exactly the messages keyed to
+// entities it owns, ordered by (source shard, position in the source queue) — the order a single world would hold them in
+// if the shards' systems had run one after the other.  The split below is therefore a STABLE G-way partition:
+//   k_route_hist     per 256-message tile, messages per destination            -> hist[dest * n_tiles + tile]
+//   exclusive scan   over the dest-major histogram (primitives.cuh)            -> slab offset of every (dest, tile)
+//   k_route_scatter  in-tile stable rank per destination (__match_any_sync per warp + warp prefix) -> slab
+// The exchange itself (sizes, then slabs) is the caller's all-to-all over NCCL / NVLink (heliosengine_b200/routing.py);
+// helios_gpu_message_route_merge installs what arrived, re-basing the key to the receiver's local entity indices.
+#include "primitives.cuh"
+#include "world_internal.hpp"
+
+using namespace hgpu;
+using namespace hgpu::prim;
+
+namespace {
+
+constexpr uint32_t kRouteTile = 256;
+constexpr uint32_t kRouteMaxShards = 64;
+
+__device__ __forceinline__ uint32_t owner_of(const uint8_t* msg, uint32_t key_offset, uint64_t per_shard, uint32_t n_shards) {
+  const uint32_t index = *reinterpret_cast<const uint32_t*>(msg + key_offset);  // Entity = index | generation << 32
+  const uint64_t o = uint64_t(index) / per_shard;
+  return o < n_shards ? uint32_t(o) : n_shards - 1;
+}
+
+__global__ void __launch_bounds__(kRouteTile) k_route_hist(const uint8_t* __restrict__ msgs, uint64_t n, uint32_t size,
+                                                           uint32_t key_offset, uint64_t per_shard, uint32_t n_shards,
+                                                           uint32_t n_tiles, uint32_t* __restrict__ hist) {
+  __shared__ uint32_t s_cnt[kRouteMaxShards];
+  if (threadIdx.x < n_shards) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const uint64_t i = uint64_t(blockIdx.x) * kRouteTile + threadIdx.x;
+  if (i < n) {
+    const uint32_t d = owner_of(msgs + i * size, key_offset, per_shard, n_shards);
+    const uint32_t peers = __match_any_sync(__activemask(), d);
+    if ((threadIdx.x & 31u) == uint32_t(__ffs(peers) - 1)) atomicAdd(&s_cnt[d], uint32_t(__popc(peers)));
+  }
+  __syncthreads();
+  if (threadIdx.x < n_shards) hist[size_t(threadIdx.x) * n_tiles + blockIdx.x] = s_cnt[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(kRouteTile) k_route_scatter(const uint8_t* __restrict__ msgs, uint64_t n, uint32_t size,
+                                                              uint32_t key_offset, uint64_t per_shard, uint32_t n_shards,
+                                                              uint32_t n_tiles, const uint32_t* __restrict__ offsets,
+                                                              uint8_t* __restrict__ slab) {
+  __shared__ uint32_t s_warp[kRouteTile / 32][kRouteMaxShards];  // messages of warp w bound for shard d
+  const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  for (uint32_t k = threadIdx.x; k < (kRouteTile / 32) * kRouteMaxShards; k += kRouteTile) (&s_warp[0][0])[k] = 0;
+  __syncthreads();
+  const uint64_t i = uint64_t(blockIdx.x) * kRouteTile + threadIdx.x;
+  uint32_t d = 0, rank_in_warp = 0;
+  const bool live = i < n;
+  if (live) {
+    d = owner_of(msgs + i * size, key_offset, per_shard, n_shards);
+    const uint32_t peers = __match_any_sync(__activemask(), d);
+    rank_in_warp = __popc(peers & ((1u << lane) - 1u));  // lanes are in message order: stable
+    if (lane == uint32_t(__ffs(peers) - 1)) s_warp[wid][d] = __popc(peers);
+  }
+  __syncthreads();
+  if (!live) return;
+  uint32_t before = 0;
+  for (uint32_t w2 = 0; w2 < wid; ++w2) before += s_warp[w2][d];
+  const uint64_t dst = uint64_t(offsets[size_t(d) * n_tiles + blockIdx.x]) + before + rank_in_warp;
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(msgs + i * size);
+  uint32_t* out = reinterpret_cast<uint32_t*>(slab + dst * size);
+  for (uint32_t k = 0; k < size / 4; ++k) out[k] = src[k];
+}
+
+__global__ void k_route_totals(const uint32_t* __restrict__ offsets, uint32_t n_tiles, uint32_t n_shards, uint64_t n,
+                               unsigned long long* __restrict__ counts) {
+  const uint32_t d = threadIdx.x;
+  if (d >= n_shards) return;
+  const uint64_t begin = offsets[size_t(d) * n_tiles];
+  const uint64_t end = d + 1 < n_shards ? offsets[size_t(d + 1) * n_tiles] : n;
+  counts[d] = end - begin;
+}
+
+__global__ void k_route_rebase(uint8_t* __restrict__ msgs, uint64_t n, uint32_t size, uint32_t key_offset, uint32_t rebase) {
+  const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) *reinterpret_cast<uint32_t*>(msgs + i * size + key_offset) -= rebase;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t helios_gpu_message_route_split(helios_gpu_world* w, uint64_t hash, uint32_t which, uint32_t key_offset,
+                                       uint64_t entities_per_shard, uint32_t n_shards, void* d_out_slab,
+                                       uint64_t capacity_msgs, uint64_t* out_counts) {
+  if (!w || which > 1 || !out_counts || n_shards == 0 || n_shards > kRouteMaxShards || entities_per_shard == 0)
+    return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  MsgChannel* ch = find_channel(w, hash);
+  if (!ch) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "message type not registered");
+  if (ch->size % 4 != 0 || key_offset % 4 != 0 || key_offset + 8 > ch->size)
+    HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "routing needs word-sized messages with an entity key inside them");
+  const uint64_t n = which ? ch->cur_count : ch->prev_count;
+  const uint8_t* src = (which ? ch->cur : ch->prev).as<uint8_t>();
+  for (uint32_t g = 0; g < n_shards; ++g) out_counts[g] = 0;
+  if (n == 0) return HELIOS_GPU_OK;
+  if (n > 0xFFFFFFFFull) HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "more than 2^32 messages in one queue");
+  if (capacity_msgs < n || !d_out_slab) HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "route slab holds %llu messages, %llu queued",
+                                                (unsigned long long)capacity_msgs, (unsigned long long)n);
+  const uint32_t n_tiles = uint32_t((n + kRouteTile - 1) / kRouteTile);
+  const uint64_t cells = uint64_t(n_tiles) * n_shards;
+  cudaStream_t st = w->stream;
+  HG_CUDA(w, w->route_hist.reserve(cells * 4, 0, st, false));
+  HG_CUDA(w, w->route_partials.reserve((cells / kScanTile + 2) * 4, 0, st, false));
+  HG_CUDA(w, w->route_counts.reserve(kRouteMaxShards * 8 + 16, 0, st, false));
+  k_route_hist<<<n_tiles, kRouteTile, 0, st>>>(src, n, ch->size, key_offset, entities_per_shard, n_shards, n_tiles,
+                                               w->route_hist.as<uint32_t>());
+  w->launches += 1 + exclusive_scan_u32(w->route_hist.as<uint32_t>(), w->route_hist.as<uint32_t>(), cells,
+                                        w->route_partials.as<uint32_t>(), nullptr, st);
+  k_route_scatter<<<n_tiles, kRouteTile, 0, st>>>(src, n, ch->size, key_offset, entities_per_shard, n_shards, n_tiles,
+                                                  w->route_hist.as<uint32_t>(), static_cast<uint8_t*>(d_out_slab));
+  k_route_totals<<<1, kRouteMaxShards, 0, st>>>(w->route_hist.as<uint32_t>(), n_tiles, n_shards, n,
+                                                w->route_counts.as<unsigned long long>());
+  w->launches += 2;
+  HG_CUDA(w, cudaGetLastError());
+  unsigned long long host[kRouteMaxShards];
+  HG_CUDA(w, cudaMemcpyAsync(host, w->route_counts.ptr, n_shards * 8, cudaMemcpyDeviceToHost, st));
+  HG_CUDA(w, cudaStreamSynchronize(st));  // the caller sizes its all-to-all from these
+  for (uint32_t g = 0; g < n_shards; ++g) out_counts[g] = host[g];
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_message_route_merge(helios_gpu_world* w, uint64_t hash, uint32_t which, const void* d_src, uint64_t n,
+                                       uint32_t key_offset, uint64_t index_rebase) {
+  if (!w || which > 1 || (n && !d_src)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  MsgChannel* ch = find_channel(w, hash);
+  if (!ch) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "message type not registered");
+  if (key_offset % 4 != 0 || key_offset + 8 > ch->size) HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "bad key offset");
+  DevBuf& buf = which ? ch->cur : ch->prev;
+  uint64_t& count = which ? ch->cur_count : ch->prev_count;
+  cudaStream_t st = w->stream;
+  if (n) {
+    HG_CUDA(w, buf.reserve(n * ch->size, 0, st));
+    HG_CUDA(w, cudaMemcpyAsync(buf.ptr, d_src, n * ch->size, cudaMemcpyDeviceToDevice, st));
+    if (index_rebase) {
+      k_route_rebase<<<div_up(n, 256), 256, 0, st>>>(buf.as<uint8_t>(), n, ch->size, key_offset, uint32_t(index_rebase));
+      ++w->launches;
+      HG_CUDA(w, cudaGetLastError());
+    }
+  }
+  count = n;
+  return publish_channel(w, ch);
+}
+
+}  // extern "C"

@@ -152,7 +152,8 @@ struct helios_gpu_world {
   std::vector<std::unique_ptr<hgpu::MsgChannel>> channels;
   std::unordered_map<uint64_t, int> channel_of;
   std::vector<std::unique_ptr<hgpu::AsyncChannel>> async_channels;
-  std::vector<std::unique_ptr<hgpu::WorldResource>> resources;     // ResourceManager (world.hpp resources_)  // AsyncMessageQueue (message/manager.hpp:359)
+  std::vector<std::unique_ptr<hgpu::WorldResource>> resources;     // ResourceManager (world.hpp resources_)
+  hgpu::DevBuf route_hist, route_partials, route_counts;           // cross-shard message routing scratch (routing.cu)  // AsyncMessageQueue (message/manager.hpp:359)
 
   std::vector<helios_gpu_query*> queries;
   std::vector<helios_gpu_schedule*> schedules;

@@ -268,6 +268,23 @@ HELIOS_GPU_API int32_t helios_gpu_message_counts(helios_gpu_world* w, uint64_t t
 HELIOS_GPU_API int32_t helios_gpu_message_read(helios_gpu_world* w, uint64_t type_hash, uint32_t which, void* out,
                                                uint64_t capacity_bytes);
 
+/* ---- cross-shard message routing (entities are partitioned by entity-index range over the GPUs of a
+ * box; a message keyed to an entity another shard owns travels to that shard) --------------------------------------------
+ * The key is the Entity stored at `key_offset` of every message (its low 32 bits = the GLOBAL entity index); the owner of
+ * index i is min(i / entities_per_shard, n_shards - 1).
+ * route_split: STABLE n_shards-way partition of PreviousMessages (which = 0) or CurrentMessages (which = 1) into
+ * d_out_slab (device memory of the caller, e.g. a torch tensor handed to an NCCL all-to-all): destination 0's messages in
+ * queue order, then destination 1's, ...; out_counts[g] (host) = messages for shard g.  Synchronises (the caller sizes
+ * its exchange from the counts).  The queue itself is left untouched.
+ * route_merge: the queue becomes the n messages at d_src (device memory: what the all-to-all delivered, source shards in
+ * rank order), with `index_rebase` subtracted from every key index (global -> the receiver's local indices). */
+HELIOS_GPU_API int32_t helios_gpu_message_route_split(helios_gpu_world* w, uint64_t type_hash, uint32_t which,
+                                                      uint32_t key_offset, uint64_t entities_per_shard, uint32_t n_shards,
+                                                      void* d_out_slab, uint64_t capacity_msgs, uint64_t* out_counts);
+HELIOS_GPU_API int32_t helios_gpu_message_route_merge(helios_gpu_world* w, uint64_t type_hash, uint32_t which,
+                                                      const void* d_src, uint64_t n, uint32_t key_offset,
+                                                      uint64_t index_rebase);
+
 /* ---- world resources (resource/manager.hpp:20-250; World::InsertResources / TryInsertResources / RemoveResources /
  * TryRemoveResources / ReadResource / WriteResource / HasResource, world.hpp:491-620; system parameters Res<const T> /
  * ResMut<T>, resource/param.hpp) -----------------------------------------------------------------------------------

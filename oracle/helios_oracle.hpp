@@ -1014,6 +1014,7 @@ public:
     previous_.Register(t, size);
   }
   bool IsRegistered(TypeIndex t) const { return registered_.count(t) != 0; }
+  uint32_t ElemSize(TypeIndex t) const { const auto it = registered_.find(t); return it == registered_.end() ? 0 : it->second.size; }
   // manager.hpp:532-540 Write → current
   void Write(TypeIndex t, const void* bytes, size_t count = 1) { current_.Enqueue(t, bytes, count); }
 
@@ -1057,6 +1058,13 @@ public:
 
   const MessageQueue& Current() const noexcept { return current_; }
   const MessageQueue& Previous() const noexcept { return previous_; }
+  // cross-shard routing (no reference counterpart: a sharded deployment replaces a queue by what the exchange delivered)
+  void ReplaceQueue(bool current, TypeIndex t, const void* bytes, size_t count) {
+    MessageQueue& q = current ? current_ : previous_;
+    q.Register(t, ElemSize(t));
+    q.Clear(t);
+    if (count) q.Enqueue(t, bytes, count);
+  }
   // reader.hpp:56-75,793-795 — readers see previous ++ current.
   std::vector<uint8_t> ReadAll(TypeIndex t) const {
     std::vector<uint8_t> out;

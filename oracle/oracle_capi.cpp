@@ -753,6 +753,50 @@ HO_API int32_t helios_oracle_message_read(void* wp, uint64_t hash, uint32_t whic
   return 0;
 }
 
+// ---- cross-shard message routing: the plain statement — walk the queue once per destination ----------------
+HO_API int32_t helios_oracle_message_route_split(void* wp, uint64_t hash, uint32_t which, uint32_t key_offset,
+                                                 uint64_t per_shard, uint32_t n_shards, void* out_slab, uint64_t capacity,
+                                                 uint64_t* out_counts) {
+  if (which > 1 || n_shards == 0 || per_shard == 0) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  const ho::MessageQueue& q = which ? W(wp)->world.messages.Current() : W(wp)->world.messages.Previous();
+  const auto* b = q.Bytes(hash);
+  if (!b) return HELIOS_GPU_ERR_NOT_FOUND;
+  const size_t n = q.Count(hash), size = n ? b->size() / n : 0;
+  for (uint32_t g = 0; g < n_shards; ++g) out_counts[g] = 0;
+  if (n == 0) return 0;
+  if (capacity < n) return HELIOS_GPU_ERR_CAPACITY;
+  auto* out = static_cast<uint8_t*>(out_slab);
+  size_t at = 0;
+  for (uint32_t g = 0; g < n_shards; ++g)
+    for (size_t i = 0; i < n; ++i) {
+      uint32_t index;
+      std::memcpy(&index, b->data() + i * size + key_offset, 4);
+      const uint64_t owner = std::min<uint64_t>(index / per_shard, n_shards - 1);
+      if (owner != g) continue;
+      std::memcpy(out + at * size, b->data() + i * size, size);
+      ++at;
+      ++out_counts[g];
+    }
+  return 0;
+}
+HO_API int32_t helios_oracle_message_route_merge(void* wp, uint64_t hash, uint32_t which, const void* src, uint64_t n,
+                                                 uint32_t key_offset, uint64_t index_rebase) {
+  if (!W(wp)->world.messages.IsRegistered(hash)) return HELIOS_GPU_ERR_NOT_FOUND;
+  const ho::MessageQueue& q = which ? W(wp)->world.messages.Current() : W(wp)->world.messages.Previous();
+  (void)q;
+  std::vector<uint8_t> tmp;
+  const size_t size = W(wp)->world.messages.ElemSize(hash);
+  tmp.assign(static_cast<const uint8_t*>(src), static_cast<const uint8_t*>(src) + n * size);
+  for (uint64_t i = 0; i < n; ++i) {
+    uint32_t index;
+    std::memcpy(&index, tmp.data() + i * size + key_offset, 4);
+    index -= uint32_t(index_rebase);
+    std::memcpy(tmp.data() + i * size + key_offset, &index, 4);
+  }
+  W(wp)->world.messages.ReplaceQueue(which != 0, hash, tmp.data(), n);
+  return 0;
+}
+
 // ---- world resources (resource/manager.hpp; world.hpp:491-620) ---------------------------------------------------------------
 HO_API int32_t helios_oracle_resource_insert(void* wp, uint64_t hash, const void* v, uint32_t size) {
   if (!v || size == 0 || hash == 0) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
