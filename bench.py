@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--entities", type=int, default=0, help="entities per GPU (default: the config's BASELINE size)")
-    ap.add_argument("--config", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5", "terminals", "sparse", "extract", "conditions", "async"],
+    ap.add_argument("--config", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5", "terminals", "sparse", "extract", "conditions", "async", "routing"],
                     help="cfg2 (default) is the headline workload; the others are secondary legs (bench_configs.py)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -141,19 +141,19 @@ def run_secondary(args):
     rank = int(os.environ.get("RANK", "0"))
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.config != "cfg5" and rank != 0:
+    if args.config not in ("cfg5", "routing") and rank != 0:
         return
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     stream = torch.cuda.Stream(device=dev)
     clocks = ClockSampler(local_rank)
     clocks.start()
-    if args.config == "cfg5":
+    if args.config in ("cfg5", "routing"):
         dist = None
         if world_size > 1:
             import torch.distributed as dist
             dist.init_process_group("nccl", device_id=dev)
-        line = bench_configs.run_cfg5(args, torch, dev, stream, peaks(), dist, rank, world_size)
+        line = getattr(bench_configs, "run_" + args.config)(args, torch, dev, stream, peaks(), dist, rank, world_size)
         n_gpus = world_size
         if world_size > 1:
             dist.destroy_process_group()

@@ -612,6 +612,68 @@ def run_async(args, torch, dev, stream, peak):
     }
 
 
+def run_routing(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
+    """Cross-shard message routing: every rank holds 4 194 304 CollisionEvents (cfg 4's per-frame volume)
+    keyed uniformly over the entity-index ranges of all ranks; a step = stable split by owner on the device, all-to-all of
+    counts and slabs (NCCL over NVLink), merge.  value = messages routed per second over all ranks (max-over-ranks time)."""
+    from . import routing
+    n = args.entities or (1 << 22)
+    per = 1 << 22
+    gpu = capi.load_gpu()
+    w = capi.World(gpu, device=dev.index)
+    w.set_stream(stream.cuda_stream)
+    name = worlds.COLLISION_EVENT
+    w.message_register(name, 24)
+    rng = np.random.default_rng(77 + rank)
+    ev = np.zeros(n, dtype=np.dtype([("a", "<u8"), ("b", "<u8"), ("impulse", "<f4"), ("pad", "<u4")]))
+    ev["a"] = rng.integers(0, per * world_size, n).astype(np.uint64) | (np.uint64(1) << np.uint64(32))
+    ev["pad"] = np.arange(n, dtype=np.uint32)
+    ev_dev = torch.from_numpy(ev.view(np.uint8).reshape(-1).copy()).to(dev)
+    slab = torch.empty(n * 24, dtype=torch.uint8, device=dev)
+    steps, warm = args.steps, max(3, args.warmup)
+    t_split, t_total = [], []
+    l0 = w.launch_count()
+    with torch.cuda.stream(stream):
+        for i in range(warm + steps):
+            routing.merge(w, name, 1, ev_dev, n, 0, 0)  # reload this rank's outgoing queue
+            torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
+            a, b, c = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            a.record(stream)
+            routing.split(w, name, 1, 0, per, world_size, slab)
+            b.record(stream)
+            info = routing.route(w, name, torch, dev, dist, rank, world_size, per)
+            c.record(stream)
+            torch.cuda.synchronize()
+            if i >= warm:
+                t_split.append(a.elapsed_time(b))
+                t_total.append(b.elapsed_time(c))
+    launches = w.launch_count() - l0
+    split_ms, route_ms = float(np.median(t_split)), float(np.median(t_total))
+    if dist is not None:
+        t = torch.tensor([split_ms, route_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        split_ms, route_ms = float(t[0]), float(t[1])
+    received = sum(info["received"])
+    w.close()
+    split_bytes = n * (24 + 24 + 24)  # key pass reads every sector of the 24-byte records, scatter reads + writes them
+    return {
+        "metric": "routed_messages_per_sec", "value": n * world_size / (route_ms * 1e-3), "unit": "messages/s",
+        "ms_per_step": route_ms, "dtype": "bytes",
+        "config": {"workload": f"routing: {n} CollisionEvents (24 B) per rank keyed uniformly over {world_size} entity-index shards; "
+                               "step = split + all_to_all(counts) + all_to_all(slabs) + merge",
+                   "l2": "100 MB of records per rank per pass; slabs and queue exceed L2 together; no flush",
+                   "parallelism": f"entity-range shards x{world_size}, NCCL all-to-all" if world_size > 1 else "1 rank (no exchange)"},
+        "roofline": {"bound": "hbm", "achieved": split_bytes / (split_ms * 1e-3) / 1e9, "peak": peak[0], "unit": "GB/s",
+                     "frac": split_bytes / (split_ms * 1e-3) / 1e9 / peak[0], "traffic": None, "peak_kind": peak[1],
+                     "algorithmic_bytes_per_launch": split_bytes,
+                     "kernel": "k_route_hist + scan + k_route_scatter (the split alone, incl. the count read-back)"},
+        "split_ms": split_ms, "received_last_step": received, "scaling": "weak",
+        "e2e": None, "cpu_baseline": None, "gpu_launches": int(launches),
+    }
+
+
 def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
     """Boids, STRONG scaling: `--entities` boids in total (default 64M, density 4 per cell) split by entity-id range over
     the ranks; per step: bin own shard, all-gather slabs + counts (NCCL), neighbour pass + integrate."""
