@@ -84,9 +84,220 @@ __global__ void k_route_rebase(uint8_t* __restrict__ msgs, uint64_t n, uint32_t 
   if (i < n) *reinterpret_cast<uint32_t*>(msgs + i * size + key_offset) -= rebase;
 }
 
+// ---- peer-memory form: the all-to-all fused into the scatter (P2P stores over NVLink into the owners' inboxes) -------------
+struct PeerPtrs {
+  uint8_t* inbox[kRouteMaxShards];
+  unsigned long long* matrix[kRouteMaxShards];  // [src * G + dst] messages src sends to dst, one copy per shard
+};
+
+// My row of the count matrix goes into EVERY shard's copy (G*G tiny remote stores).
+__global__ void k_route_publish(const uint32_t* __restrict__ offsets, uint32_t n_tiles, uint32_t n_shards, uint64_t n,
+                                uint32_t me, PeerPtrs peers) {
+  const uint32_t d = threadIdx.x;
+  if (d >= n_shards) return;
+  unsigned long long c = 0;
+  if (n) {
+    const uint64_t begin = offsets[size_t(d) * n_tiles];
+    const uint64_t end = d + 1 < n_shards ? offsets[size_t(d + 1) * n_tiles] : n;
+    c = end - begin;
+  }
+  for (uint32_t s2 = 0; s2 < n_shards; ++s2) peers.matrix[s2][size_t(me) * n_shards + d] = c;
+  __threadfence_system();
+}
+
+__global__ void __launch_bounds__(kRouteTile) k_route_scatter_peer(const uint8_t* __restrict__ msgs, uint64_t n, uint32_t size,
+                                                                   uint32_t key_offset, uint64_t per_shard, uint32_t n_shards,
+                                                                   uint32_t n_tiles, const uint32_t* __restrict__ offsets,
+                                                                   uint32_t me, uint64_t inbox_capacity, PeerPtrs peers) {
+  __shared__ uint32_t s_warp[kRouteTile / 32][kRouteMaxShards];
+  __shared__ unsigned long long s_base[kRouteMaxShards];  // where my run starts in destination d's inbox
+  const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  for (uint32_t k = threadIdx.x; k < (kRouteTile / 32) * kRouteMaxShards; k += kRouteTile) (&s_warp[0][0])[k] = 0;
+  if (threadIdx.x < n_shards) {
+    const unsigned long long* mine = peers.matrix[me];  // complete after the barrier
+    unsigned long long b = 0;
+    for (uint32_t r = 0; r < me; ++r) b += mine[size_t(r) * n_shards + threadIdx.x];
+    s_base[threadIdx.x] = b - offsets[size_t(threadIdx.x) * n_tiles];  // minus the start of destination d in the local order
+  }
+  __syncthreads();
+  const uint64_t i = uint64_t(blockIdx.x) * kRouteTile + threadIdx.x;
+  uint32_t d = 0, rank_in_warp = 0;
+  const bool live = i < n;
+  if (live) {
+    d = owner_of(msgs + i * size, key_offset, per_shard, n_shards);
+    const uint32_t peers_mask = __match_any_sync(__activemask(), d);
+    rank_in_warp = __popc(peers_mask & ((1u << lane) - 1u));
+    if (lane == uint32_t(__ffs(peers_mask) - 1)) s_warp[wid][d] = __popc(peers_mask);
+  }
+  __syncthreads();
+  if (!live) return;
+  uint32_t before = 0;
+  for (uint32_t w2 = 0; w2 < wid; ++w2) before += s_warp[w2][d];
+  const uint64_t dst = s_base[d] + offsets[size_t(d) * n_tiles + blockIdx.x] + before + rank_in_warp;
+  if (dst >= inbox_capacity) return;  // reported by deliver (the matrix says how many were meant to arrive)
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(msgs + i * size);
+  uint32_t* out = reinterpret_cast<uint32_t*>(peers.inbox[d] + dst * size);
+  for (uint32_t k = 0; k < size / 4; ++k) out[k] = src[k];
+}
+
+__global__ void k_route_inbox_total(const unsigned long long* __restrict__ matrix, uint32_t n_shards, uint32_t me,
+                                    unsigned long long* __restrict__ total) {
+  unsigned long long t = 0;
+  for (uint32_t r = 0; r < n_shards; ++r) t += matrix[size_t(r) * n_shards + me];
+  *total = t;
+}
+
+// inbox -> queue, keys re-based on the way (one pass)
+__global__ void __launch_bounds__(256) k_route_deliver(const uint32_t* __restrict__ inbox, uint32_t* __restrict__ queue, uint64_t n,
+                                                       uint32_t words, uint32_t key_word, uint32_t rebase) {
+  const uint64_t total = n * words;
+  for (uint64_t k = uint64_t(blockIdx.x) * 256 + threadIdx.x; k < total; k += uint64_t(gridDim.x) * 256) {
+    uint32_t v = inbox[k];
+    if (k % words == key_word) v -= rebase;
+    queue[k] = v;
+  }
+}
+
 }  // namespace
 
+struct helios_gpu_router {
+  helios_gpu_world* world = nullptr;
+  uint64_t hash = 0, per_shard = 0, capacity = 0;
+  uint32_t key_offset = 0, n_shards = 0, me = 0, generation = 0, n_tiles = 0, which = 1;
+  uint64_t n = 0;  // messages counted by the last count()
+  void* inbox[2] = {nullptr, nullptr};
+  void* matrix[2] = {nullptr, nullptr};
+  PeerPtrs peers[2] = {};
+};
+
 extern "C" {
+
+int32_t helios_gpu_router_create(helios_gpu_world* w, uint64_t hash, uint32_t key_offset, uint64_t entities_per_shard,
+                                 uint32_t n_shards, uint32_t my_shard, uint64_t inbox_capacity, helios_gpu_router** out) {
+  if (!w || !out || n_shards == 0 || n_shards > kRouteMaxShards || my_shard >= n_shards || entities_per_shard == 0 || inbox_capacity == 0)
+    return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  MsgChannel* ch = find_channel(w, hash);
+  if (!ch) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "message type not registered");
+  if (ch->size % 4 != 0 || key_offset % 4 != 0 || key_offset + 8 > ch->size)
+    HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "routing needs word-sized messages with an entity key inside them");
+  auto* r = new helios_gpu_router();
+  r->world = w;
+  r->hash = hash;
+  r->key_offset = key_offset;
+  r->per_shard = entities_per_shard;
+  r->n_shards = n_shards;
+  r->me = my_shard;
+  r->capacity = inbox_capacity;
+  for (int g = 0; g < 2; ++g) {  // plain cudaMalloc: exportable with helios_gpu_ipc_export
+    HG_CUDA(w, cudaMalloc(&r->inbox[g], inbox_capacity * ch->size));
+    HG_CUDA(w, cudaMalloc(&r->matrix[g], size_t(n_shards) * n_shards * 8));
+    HG_CUDA(w, cudaMemset(r->matrix[g], 0, size_t(n_shards) * n_shards * 8));
+    r->peers[g].inbox[my_shard] = static_cast<uint8_t*>(r->inbox[g]);
+    r->peers[g].matrix[my_shard] = static_cast<unsigned long long*>(r->matrix[g]);
+  }
+  *out = r;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_router_destroy(helios_gpu_router* r) {
+  if (!r) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  cudaStreamSynchronize(r->world->stream);
+  for (int g = 0; g < 2; ++g) {
+    cudaFree(r->inbox[g]);
+    cudaFree(r->matrix[g]);
+  }
+  delete r;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_router_local(helios_gpu_router* r, uint32_t generation, void** inbox, void** matrix) {
+  if (!r || generation > 1 || !inbox || !matrix) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  *inbox = r->inbox[generation];
+  *matrix = r->matrix[generation];
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_router_set_peer(helios_gpu_router* r, uint32_t shard, uint32_t generation, void* inbox, void* matrix) {
+  if (!r || generation > 1 || shard >= r->n_shards || !inbox || !matrix) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  r->peers[generation].inbox[shard] = static_cast<uint8_t*>(inbox);
+  r->peers[generation].matrix[shard] = static_cast<unsigned long long*>(matrix);
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_router_count(helios_gpu_router* r, uint32_t which) {
+  if (!r || which > 1) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  helios_gpu_world* w = r->world;
+  MsgChannel* ch = find_channel(w, r->hash);
+  const PeerPtrs& pp = r->peers[r->generation];
+  for (uint32_t g = 0; g < r->n_shards; ++g)
+    if (!pp.inbox[g] || !pp.matrix[g]) HG_FAIL(w, HELIOS_GPU_ERR_STATE, "router: shard %u has no peer pointers yet", g);
+  const uint64_t n = which ? ch->cur_count : ch->prev_count;
+  if (n > 0xFFFFFFFFull) HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "more than 2^32 messages in one queue");
+  const uint8_t* src = (which ? ch->cur : ch->prev).as<uint8_t>();
+  cudaStream_t st = w->stream;
+  r->which = which;
+  r->n = n;
+  r->n_tiles = uint32_t((n + kRouteTile - 1) / kRouteTile);
+  const uint64_t cells = std::max<uint64_t>(1, uint64_t(r->n_tiles) * r->n_shards);
+  HG_CUDA(w, w->route_hist.reserve(cells * 4, 0, st, false));
+  HG_CUDA(w, w->route_partials.reserve((cells / kScanTile + 2) * 4, 0, st, false));
+  if (n) {
+    k_route_hist<<<r->n_tiles, kRouteTile, 0, st>>>(src, n, ch->size, r->key_offset, r->per_shard, r->n_shards, r->n_tiles,
+                                                    w->route_hist.as<uint32_t>());
+    w->launches += 1 + exclusive_scan_u32(w->route_hist.as<uint32_t>(), w->route_hist.as<uint32_t>(), cells,
+                                          w->route_partials.as<uint32_t>(), nullptr, st);
+  }
+  k_route_publish<<<1, kRouteMaxShards, 0, st>>>(w->route_hist.as<uint32_t>(), r->n_tiles, r->n_shards, n, r->me, pp);
+  ++w->launches;
+  HG_CUDA(w, cudaGetLastError());
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_router_scatter(helios_gpu_router* r) {
+  if (!r) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  helios_gpu_world* w = r->world;
+  if (r->n == 0) return HELIOS_GPU_OK;
+  MsgChannel* ch = find_channel(w, r->hash);
+  const uint8_t* src = (r->which ? ch->cur : ch->prev).as<uint8_t>();
+  k_route_scatter_peer<<<r->n_tiles, kRouteTile, 0, w->stream>>>(src, r->n, ch->size, r->key_offset, r->per_shard, r->n_shards,
+                                                                 r->n_tiles, w->route_hist.as<uint32_t>(), r->me, r->capacity,
+                                                                 r->peers[r->generation]);
+  ++w->launches;
+  HG_CUDA(w, cudaGetLastError());
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_router_deliver(helios_gpu_router* r, uint32_t which, uint32_t rebase, uint64_t* delivered) {
+  if (!r || which > 1) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  helios_gpu_world* w = r->world;
+  MsgChannel* ch = find_channel(w, r->hash);
+  cudaStream_t st = w->stream;
+  const uint32_t g = r->generation;
+  HG_CUDA(w, w->route_counts.reserve(kRouteMaxShards * 8 + 16, 0, st, false));
+  k_route_inbox_total<<<1, 1, 0, st>>>(static_cast<const unsigned long long*>(r->matrix[g]), r->n_shards, r->me,
+                                       w->route_counts.as<unsigned long long>());
+  unsigned long long total = 0;
+  HG_CUDA(w, cudaMemcpyAsync(&total, w->route_counts.ptr, 8, cudaMemcpyDeviceToHost, st));
+  HG_CUDA(w, cudaStreamSynchronize(st));
+  if (total > r->capacity) HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "router inbox holds %llu messages, %llu arrived",
+                                   (unsigned long long)r->capacity, total);
+  DevBuf& buf = which ? ch->cur : ch->prev;
+  uint64_t& count = which ? ch->cur_count : ch->prev_count;
+  if (total) {
+    HG_CUDA(w, buf.reserve(total * ch->size, 0, st));
+    const uint32_t words = ch->size / 4;
+    const uint64_t work = total * words;
+    const uint32_t blocks = uint32_t(std::min<uint64_t>((work + 255) / 256, uint64_t(w->sm_count) * 16));
+    k_route_deliver<<<blocks, 256, 0, st>>>(static_cast<const uint32_t*>(r->inbox[g]), buf.as<uint32_t>(), total, words,
+                                            r->key_offset / 4, rebase ? uint32_t(r->me * r->per_shard) : 0u);
+    HG_CUDA(w, cudaGetLastError());
+  }
+  w->launches += 2;
+  count = total;
+  if (delivered) *delivered = total;
+  r->generation ^= 1u;
+  return publish_channel(w, ch);
+}
 
 int32_t helios_gpu_message_route_split(helios_gpu_world* w, uint64_t hash, uint32_t which, uint32_t key_offset,
                                        uint64_t entities_per_shard, uint32_t n_shards, void* d_out_slab,

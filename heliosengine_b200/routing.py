@@ -79,3 +79,93 @@ def reference_routing(queues: list[np.ndarray], size: int, key_offset: int, enti
             parts.append(sel)
         out.append(np.concatenate(parts).reshape(-1) if parts else np.zeros(0, np.uint8))
     return out
+
+
+class Router:
+    """helios_gpu_router: the peer-memory form (csrc/routing.cu).  count -> barrier -> scatter -> barrier -> deliver."""
+
+    def __init__(self, world: capi.World, name: str, n_shards: int, my_shard: int, entities_per_shard: int,
+                 inbox_capacity: int, key_offset: int = 0):
+        self.w, self.name, self.n_shards, self.me = world, name, n_shards, my_shard
+        self.h = C.c_void_p()
+        world._check(world.b.fn("router_create")(world.h, C.c_uint64(capi.fnv1a(name)), C.c_uint32(key_offset),
+                                                 C.c_uint64(entities_per_shard), C.c_uint32(n_shards), C.c_uint32(my_shard),
+                                                 C.c_uint64(inbox_capacity), C.byref(self.h)))
+
+    def local(self, generation: int) -> tuple[int, int]:
+        inbox, matrix = C.c_void_p(), C.c_void_p()
+        self.w._check(self.w.b.fn("router_local")(self.h, C.c_uint32(generation), C.byref(inbox), C.byref(matrix)))
+        return inbox.value, matrix.value
+
+    def set_peer(self, shard: int, generation: int, inbox: int, matrix: int):
+        self.w._check(self.w.b.fn("router_set_peer")(self.h, C.c_uint32(shard), C.c_uint32(generation), C.c_void_p(inbox),
+                                                     C.c_void_p(matrix)))
+
+    def count(self, which: int = 1):
+        self.w._check(self.w.b.fn("router_count")(self.h, C.c_uint32(which)))
+
+    def scatter(self):
+        self.w._check(self.w.b.fn("router_scatter")(self.h))
+
+    def deliver(self, which: int = 1, rebase: bool = True) -> int:
+        n = C.c_uint64()
+        self.w._check(self.w.b.fn("router_deliver")(self.h, C.c_uint32(which), C.c_uint32(1 if rebase else 0), C.byref(n)))
+        return n.value
+
+    def close(self):
+        if self.h:
+            self.w.b.fn("router_destroy")(self.h)
+            self.h = C.c_void_p()
+
+
+IPC_HANDLE_BYTES = 64
+
+
+class PeerRouter:
+    """One process per GPU: the inboxes and count matrices are exchanged once as CUDA IPC handles; afterwards a step is
+    count -> 4-byte all-reduce -> scatter (P2P stores over NVLink) -> 4-byte all-reduce -> deliver."""
+
+    def __init__(self, world: capi.World, name: str, torch, dist, device, rank: int, n_shards: int, entities_per_shard: int,
+                 inbox_capacity: int, key_offset: int = 0):
+        self.dist, self.w = dist, world
+        self.router = Router(world, name, n_shards, rank, entities_per_shard, inbox_capacity, key_offset)
+        b = world.b
+        mine = torch.zeros(4 * IPC_HANDLE_BYTES, dtype=torch.uint8)
+        for gen in range(2):
+            for k, ptr in enumerate(self.router.local(gen)):
+                h = (C.c_uint8 * IPC_HANDLE_BYTES)()
+                world._check(b.fn("ipc_export")(world.h, C.c_void_p(ptr), h))
+                off = (gen * 2 + k) * IPC_HANDLE_BYTES
+                mine[off:off + IPC_HANDLE_BYTES] = torch.frombuffer(bytearray(h), dtype=torch.uint8)
+        everyone = torch.empty(n_shards * mine.numel(), dtype=torch.uint8, device=device)
+        dist.all_gather_into_tensor(everyone, mine.to(device))
+        everyone = everyone.cpu().numpy().reshape(n_shards, 2, 2, IPC_HANDLE_BYTES)
+        self.opened = []
+        for g in range(n_shards):
+            if g == rank:
+                continue
+            for gen in range(2):
+                ptrs = []
+                for k in range(2):
+                    h = (C.c_uint8 * IPC_HANDLE_BYTES).from_buffer_copy(everyone[g, gen, k].tobytes())
+                    p = C.c_void_p()
+                    world._check(b.fn("ipc_open")(world.h, h, C.byref(p)))
+                    ptrs.append(p.value)
+                    self.opened.append(p.value)
+                self.router.set_peer(g, gen, ptrs[0], ptrs[1])
+        self.token = torch.zeros(1, dtype=torch.int32, device=device)
+
+    def route(self, which: int = 1, rebase: bool = True) -> int:
+        self.router.count(which)
+        self.dist.all_reduce(self.token)  # every shard's count matrix is complete
+        self.router.scatter()
+        self.dist.all_reduce(self.token)  # every shard's inbox is complete
+        return self.router.deliver(which, rebase)
+
+    def close(self):
+        self.w.synchronize()
+        self.dist.barrier()  # nobody closes a mapping a peer may still be writing through
+        for p in self.opened:
+            self.w.b.fn("ipc_close")(self.w.h, C.c_void_p(p))
+        self.opened = []
+        self.router.close()

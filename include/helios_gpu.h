@@ -285,6 +285,28 @@ HELIOS_GPU_API int32_t helios_gpu_message_route_merge(helios_gpu_world* w, uint6
                                                       const void* d_src, uint64_t n, uint32_t key_offset,
                                                       uint64_t index_rebase);
 
+/* Peer-memory form of the same routing (one process per GPU, NVLink): every shard owns two generations of an INBOX and of
+ * a G x G count matrix (plain cudaMalloc, exported with helios_gpu_ipc_export, opened by the other shards).  A step on
+ * every rank, all on the world's stream, with no slab ever going through a collective:
+ *     helios_gpu_router_count(r, which);      histogram + scan; my row of the matrix is stored into EVERY shard's copy
+ *     -- barrier (e.g. a 4-byte all-reduce on the world's stream): every matrix is complete --
+ *     helios_gpu_router_scatter(r);           each message is stored straight into its owner's inbox (P2P stores) at
+ *                                             sum of the lower-ranked sources' counts + its stable local position
+ *     -- barrier: every inbox is complete --
+ *     helios_gpu_router_deliver(r, which, rebase, &n);   the queue becomes the inbox (keys re-based); flips the generation
+ * The result is identical to route_split + all-to-all + route_merge. */
+typedef struct helios_gpu_router helios_gpu_router;
+HELIOS_GPU_API int32_t helios_gpu_router_create(helios_gpu_world* w, uint64_t type_hash, uint32_t key_offset,
+                                                uint64_t entities_per_shard, uint32_t n_shards, uint32_t my_shard,
+                                                uint64_t inbox_capacity_msgs, helios_gpu_router** out);
+HELIOS_GPU_API int32_t helios_gpu_router_destroy(helios_gpu_router* r);
+HELIOS_GPU_API int32_t helios_gpu_router_local(helios_gpu_router* r, uint32_t generation, void** inbox, void** matrix);
+HELIOS_GPU_API int32_t helios_gpu_router_set_peer(helios_gpu_router* r, uint32_t shard, uint32_t generation, void* inbox,
+                                                  void* matrix);
+HELIOS_GPU_API int32_t helios_gpu_router_count(helios_gpu_router* r, uint32_t which);
+HELIOS_GPU_API int32_t helios_gpu_router_scatter(helios_gpu_router* r);
+HELIOS_GPU_API int32_t helios_gpu_router_deliver(helios_gpu_router* r, uint32_t which, uint32_t rebase, uint64_t* delivered);
+
 /* ---- world resources (resource/manager.hpp:20-250; World::InsertResources / TryInsertResources / RemoveResources /
  * TryRemoveResources / ReadResource / WriteResource / HasResource, world.hpp:491-620; system parameters Res<const T> /
  * ResMut<T>, resource/param.hpp) -----------------------------------------------------------------------------------

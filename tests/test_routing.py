@@ -116,6 +116,81 @@ def test_gpu_single_rank_route_rebases_and_feeds_consumers(gpu, oracle):
         w.close()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("g,n", [(1, 3000), (2, 100003), (5, 70001), (8, 0)])
+def test_gpu_peer_router_matches_numpy(gpu, g, n):
+    """The peer-memory form with every shard on ONE device (the peers' pointers are ordinary device pointers): count on
+    all shards, scatter on all shards, deliver on all shards — two steps, so both buffer generations are used."""
+    per = 1 << 14
+    ws = [capi.World(gpu) for _ in range(g)]
+    for w in ws:
+        w.message_register(EVENT, SIZE)
+    routers = [routing.Router(w, EVENT, g, r, per, inbox_capacity=max(1, n) * g + 64) for r, w in enumerate(ws)]
+    for gen in range(2):
+        local = [rt.local(gen) for rt in routers]
+        for rt in routers:
+            for s2 in range(g):
+                rt.set_peer(s2, gen, *local[s2])
+    for step in range(3):
+        queues = [make_events(n + 11 * r, per * g + 99, seed=1000 * step + r) for r in range(g)]
+        for w, q in zip(ws, queues):
+            t = torch.from_numpy(q.copy()).to("cuda:0")
+            routing.merge(w, EVENT, 1, t, q.size // SIZE, 0, 0)
+        for rt in routers:
+            rt.count(1)
+        for w in ws:
+            w.synchronize()  # stands in for the barrier
+        for rt in routers:
+            rt.scatter()
+        for w in ws:
+            w.synchronize()
+        want = routing.reference_routing(queues, SIZE, 0, per)
+        for r, (w, rt) in enumerate(zip(ws, routers)):
+            assert rt.deliver(1, True) == want[r].size // SIZE
+            assert np.array_equal(w.message_read(EVENT, 1), want[r]), (step, r)
+    for rt in routers:
+        rt.close()
+    for w in ws:
+        w.close()
+
+
+def _peer_worker(rank, world_size, port, per, n, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world_size, device_id=dev)
+    g = capi.load_gpu()
+    w = capi.World(g, device=rank)
+    w.set_stream(torch.cuda.current_stream(dev).cuda_stream)  # the all-reduce barriers and the kernels share one stream
+    w.message_register(EVENT, SIZE)
+    pr = routing.PeerRouter(w, EVENT, torch, dist, dev, rank, world_size, per, inbox_capacity=2 * n + 4096)
+    for step in range(3):
+        q = make_events(n + 37 * rank, per * world_size, seed=100 * (step + 1) + rank)
+        routing.merge(w, EVENT, 1, torch.from_numpy(q.copy()).to(dev), q.size // SIZE, 0, 0)
+        pr.route()
+        np.save(os.path.join(out_dir, f"p{step}_{rank}.npy"), w.message_read(EVENT, 1))
+    pr.close()
+    w.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_two_gpus_over_peer_memory(tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    per, n = 1 << 18, 400000
+    port = 35500 + os.getpid() % 2000
+    mp.spawn(_peer_worker, args=(2, port, per, n, str(tmp_path)), nprocs=2, join=True)
+    for step in range(3):
+        want = routing.reference_routing([make_events(n + 37 * r, per * 2, seed=100 * (step + 1) + r) for r in range(2)], SIZE, 0, per)
+        for r in range(2):
+            assert np.array_equal(np.load(tmp_path / f"p{step}_{r}.npy"), want[r]), (step, r)
+
+
 def _nccl_worker(rank, world_size, port, per, n, out_dir):
     sys.path.insert(0, ROOT)
     import torch.distributed as dist
