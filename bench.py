@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--all-tables", action="store_true", help="drop the With/Without filters (cfg 2-all)")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
-                    help="cfg5 at N>1: peer-memory exchange fused into the merge kernels (default) or NCCL all-gathers")
+                    help="cfg5 / routing at N>1: peer-memory exchange fused into the kernels (default) or NCCL collectives")
     return ap.parse_args()
 
 

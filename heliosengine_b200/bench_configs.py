@@ -632,6 +632,9 @@ def run_routing(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1)
     slab = torch.empty(n * 24, dtype=torch.uint8, device=dev)
     steps, warm = args.steps, max(3, args.warmup)
     t_split, t_total = [], []
+    use_peer = dist is not None and world_size > 1 and getattr(args, "exchange", "p2p") == "p2p"
+    peer = routing.PeerRouter(w, name, torch, dist, dev, rank, world_size, per, inbox_capacity=2 * n) if use_peer else None
+    info = {"received": [0]}
     l0 = w.launch_count()
     with torch.cuda.stream(stream):
         for i in range(warm + steps):
@@ -643,12 +646,17 @@ def run_routing(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1)
             a.record(stream)
             routing.split(w, name, 1, 0, per, world_size, slab)
             b.record(stream)
-            info = routing.route(w, name, torch, dev, dist, rank, world_size, per)
+            if peer is not None:
+                info = {"received": [peer.route()]}
+            else:
+                info = routing.route(w, name, torch, dev, dist, rank, world_size, per)
             c.record(stream)
             torch.cuda.synchronize()
             if i >= warm:
                 t_split.append(a.elapsed_time(b))
                 t_total.append(b.elapsed_time(c))
+    if peer is not None:
+        peer.close()
     launches = w.launch_count() - l0
     split_ms, route_ms = float(np.median(t_split)), float(np.median(t_total))
     if dist is not None:
@@ -664,7 +672,8 @@ def run_routing(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1)
         "config": {"workload": f"routing: {n} CollisionEvents (24 B) per rank keyed uniformly over {world_size} entity-index shards; "
                                "step = split + all_to_all(counts) + all_to_all(slabs) + merge",
                    "l2": "100 MB of records per rank per pass; slabs and queue exceed L2 together; no flush",
-                   "parallelism": f"entity-range shards x{world_size}, NCCL all-to-all" if world_size > 1 else "1 rank (no exchange)"},
+                   "parallelism": (f"entity-range shards x{world_size}, " + ("peer-memory scatter over NVLink (2 four-byte all-reduce barriers)"
+                                   if use_peer else "NCCL all-to-all")) if world_size > 1 else "1 rank (no exchange)"},
         "roofline": {"bound": "hbm", "achieved": split_bytes / (split_ms * 1e-3) / 1e9, "peak": peak[0], "unit": "GB/s",
                      "frac": split_bytes / (split_ms * 1e-3) / 1e9 / peak[0], "traffic": None, "peak_kind": peak[1],
                      "algorithmic_bytes_per_launch": split_bytes,

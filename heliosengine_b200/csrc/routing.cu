@@ -43,28 +43,57 @@ __global__ void __launch_bounds__(kRouteTile) k_route_hist(const uint8_t* __rest
   if (threadIdx.x < n_shards) hist[size_t(threadIdx.x) * n_tiles + blockIdx.x] = s_cnt[threadIdx.x];
 }
 
-__global__ void __launch_bounds__(kRouteTile) k_route_scatter(const uint8_t* __restrict__ msgs, uint64_t n, uint32_t size,
-                                                              uint32_t key_offset, uint64_t per_shard, uint32_t n_shards,
-                                                              uint32_t n_tiles, const uint32_t* __restrict__ offsets,
-                                                              uint8_t* __restrict__ slab) {
-  __shared__ uint32_t s_warp[kRouteTile / 32][kRouteMaxShards];  // messages of warp w bound for shard d
+// The peer scatter reorders the tile in shared memory first (messages of one destination become one contiguous run, in
+// message order) and then streams the runs out word by word: consecutive threads store consecutive 4-byte words, so the
+// remote stores coalesce into full sectors — 24-byte pieces scattered over NVLink took 0.51 ms a step, staged 0.28 ms.
+constexpr uint32_t kRouteMaxWords = 16;  // messages of up to 64 bytes are staged; larger ones take the direct path
+
+struct TileOrder {
+  uint32_t run_begin[kRouteMaxShards + 1];  // first local slot of destination d in the staged tile
+};
+
+// Returns this thread's slot in the staged tile (or ~0u when the thread holds no message) and fills `order`.
+__device__ __forceinline__ uint32_t route_tile_rank(bool live, uint32_t d, uint32_t n_shards, uint32_t (*s_warp)[kRouteMaxShards],
+                                                    TileOrder& order) {
   const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31u;
   for (uint32_t k = threadIdx.x; k < (kRouteTile / 32) * kRouteMaxShards; k += kRouteTile) (&s_warp[0][0])[k] = 0;
   __syncthreads();
-  const uint64_t i = uint64_t(blockIdx.x) * kRouteTile + threadIdx.x;
-  uint32_t d = 0, rank_in_warp = 0;
-  const bool live = i < n;
+  uint32_t rank_in_warp = 0;
   if (live) {
-    d = owner_of(msgs + i * size, key_offset, per_shard, n_shards);
     const uint32_t peers = __match_any_sync(__activemask(), d);
     rank_in_warp = __popc(peers & ((1u << lane) - 1u));  // lanes are in message order: stable
     if (lane == uint32_t(__ffs(peers) - 1)) s_warp[wid][d] = __popc(peers);
   }
   __syncthreads();
-  if (!live) return;
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (uint32_t g = 0; g < n_shards; ++g) {
+      order.run_begin[g] = run;
+      for (uint32_t w2 = 0; w2 < kRouteTile / 32; ++w2) run += s_warp[w2][g];
+    }
+    order.run_begin[n_shards] = run;
+  }
+  __syncthreads();
+  if (!live) return 0xFFFFFFFFu;
   uint32_t before = 0;
   for (uint32_t w2 = 0; w2 < wid; ++w2) before += s_warp[w2][d];
-  const uint64_t dst = uint64_t(offsets[size_t(d) * n_tiles + blockIdx.x]) + before + rank_in_warp;
+  return order.run_begin[d] + before + rank_in_warp;
+}
+
+// Local form: direct stores (measured faster than staging when the destination is this GPU's own HBM, where L2 merges the
+// 24-byte pieces: 0.123 ms against 0.150 ms for 4.19M messages).
+__global__ void __launch_bounds__(kRouteTile) k_route_scatter(const uint8_t* __restrict__ msgs, uint64_t n, uint32_t size,
+                                                              uint32_t key_offset, uint64_t per_shard, uint32_t n_shards,
+                                                              uint32_t n_tiles, const uint32_t* __restrict__ offsets,
+                                                              uint8_t* __restrict__ slab) {
+  __shared__ uint32_t s_warp[kRouteTile / 32][kRouteMaxShards];  // messages of warp w bound for shard d
+  __shared__ TileOrder s_order;
+  const uint64_t i = uint64_t(blockIdx.x) * kRouteTile + threadIdx.x;
+  const bool live = i < n;
+  const uint32_t d = live ? owner_of(msgs + i * size, key_offset, per_shard, n_shards) : 0;
+  const uint32_t slot = route_tile_rank(live, d, n_shards, s_warp, s_order);
+  if (!live) return;
+  const uint64_t dst = uint64_t(offsets[size_t(d) * n_tiles + blockIdx.x]) + (slot - s_order.run_begin[d]);
   const uint32_t* src = reinterpret_cast<const uint32_t*>(msgs + i * size);
   uint32_t* out = reinterpret_cast<uint32_t*>(slab + dst * size);
   for (uint32_t k = 0; k < size / 4; ++k) out[k] = src[k];
@@ -110,34 +139,42 @@ __global__ void __launch_bounds__(kRouteTile) k_route_scatter_peer(const uint8_t
                                                                    uint32_t n_tiles, const uint32_t* __restrict__ offsets,
                                                                    uint32_t me, uint64_t inbox_capacity, PeerPtrs peers) {
   __shared__ uint32_t s_warp[kRouteTile / 32][kRouteMaxShards];
-  __shared__ unsigned long long s_base[kRouteMaxShards];  // where my run starts in destination d's inbox
-  const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-  for (uint32_t k = threadIdx.x; k < (kRouteTile / 32) * kRouteMaxShards; k += kRouteTile) (&s_warp[0][0])[k] = 0;
+  __shared__ TileOrder s_order;
+  __shared__ uint32_t s_stage[kRouteTile * kRouteMaxWords];
+  __shared__ unsigned long long s_base[kRouteMaxShards];  // where this tile's run starts in destination d's inbox
   if (threadIdx.x < n_shards) {
     const unsigned long long* mine = peers.matrix[me];  // complete after the barrier
     unsigned long long b = 0;
     for (uint32_t r = 0; r < me; ++r) b += mine[size_t(r) * n_shards + threadIdx.x];
-    s_base[threadIdx.x] = b - offsets[size_t(threadIdx.x) * n_tiles];  // minus the start of destination d in the local order
+    // + this tile's offset inside my messages for destination d (slab offset minus the start of d in the local order)
+    s_base[threadIdx.x] = b + offsets[size_t(threadIdx.x) * n_tiles + blockIdx.x] - offsets[size_t(threadIdx.x) * n_tiles];
   }
-  __syncthreads();
   const uint64_t i = uint64_t(blockIdx.x) * kRouteTile + threadIdx.x;
-  uint32_t d = 0, rank_in_warp = 0;
   const bool live = i < n;
-  if (live) {
-    d = owner_of(msgs + i * size, key_offset, per_shard, n_shards);
-    const uint32_t peers_mask = __match_any_sync(__activemask(), d);
-    rank_in_warp = __popc(peers_mask & ((1u << lane) - 1u));
-    if (lane == uint32_t(__ffs(peers_mask) - 1)) s_warp[wid][d] = __popc(peers_mask);
-  }
-  __syncthreads();
-  if (!live) return;
-  uint32_t before = 0;
-  for (uint32_t w2 = 0; w2 < wid; ++w2) before += s_warp[w2][d];
-  const uint64_t dst = s_base[d] + offsets[size_t(d) * n_tiles + blockIdx.x] + before + rank_in_warp;
-  if (dst >= inbox_capacity) return;  // reported by deliver (the matrix says how many were meant to arrive)
+  const uint32_t words = size / 4;
+  const uint32_t d = live ? owner_of(msgs + i * size, key_offset, per_shard, n_shards) : 0;
+  const uint32_t slot = route_tile_rank(live, d, n_shards, s_warp, s_order);  // has barriers: s_base is published too
   const uint32_t* src = reinterpret_cast<const uint32_t*>(msgs + i * size);
-  uint32_t* out = reinterpret_cast<uint32_t*>(peers.inbox[d] + dst * size);
-  for (uint32_t k = 0; k < size / 4; ++k) out[k] = src[k];
+  if (words > kRouteMaxWords) {  // direct path
+    if (!live) return;
+    const uint64_t dst = s_base[d] + (slot - s_order.run_begin[d]);
+    if (dst >= inbox_capacity) return;  // reported by deliver (the matrix says how many were meant to arrive)
+    uint32_t* out = reinterpret_cast<uint32_t*>(peers.inbox[d] + dst * size);
+    for (uint32_t k = 0; k < words; ++k) out[k] = src[k];
+    return;
+  }
+  if (live)
+    for (uint32_t k = 0; k < words; ++k) s_stage[slot * words + k] = src[k];
+  __syncthreads();
+  const uint32_t total_words = s_order.run_begin[n_shards] * words;
+  uint32_t g = 0;
+  for (uint32_t k = threadIdx.x; k < total_words; k += kRouteTile) {
+    const uint32_t m = k / words;
+    while (m >= s_order.run_begin[g + 1]) ++g;
+    const uint64_t dst_msg = s_base[g] + (m - s_order.run_begin[g]);
+    if (dst_msg >= inbox_capacity) continue;
+    reinterpret_cast<uint32_t*>(peers.inbox[g])[dst_msg * words + (k - m * words)] = s_stage[k];
+  }
 }
 
 __global__ void k_route_inbox_total(const unsigned long long* __restrict__ matrix, uint32_t n_shards, uint32_t me,
