@@ -201,6 +201,16 @@ int32_t helios_gpu_world_synchronize(helios_gpu_world* w) {
   return HELIOS_GPU_OK;
 }
 
+// SubApp::IsUpdating (src/app/include/helios/app/sub_app.hpp; scheduler.cpp:221-232): has everything enqueued on the
+// world's stream finished?  Never blocks.
+int32_t helios_gpu_world_is_idle(helios_gpu_world* w, uint32_t* idle) {
+  if (!w || !idle) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  const cudaError_t e = cudaStreamQuery(w->stream);
+  if (e != cudaSuccess && e != cudaErrorNotReady) HG_FAIL(w, HELIOS_GPU_ERR_CUDA, "cudaStreamQuery: %s", cudaGetErrorString(e));
+  *idle = e == cudaSuccess ? 1u : 0u;
+  return HELIOS_GPU_OK;
+}
+
 uint64_t helios_gpu_world_launch_count(const helios_gpu_world* w) { return w ? w->launches : 0; }
 
 int32_t helios_gpu_register_component(helios_gpu_world* w, uint64_t hash, uint32_t size, uint32_t align,

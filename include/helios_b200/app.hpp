@@ -51,6 +51,14 @@ inline constexpr ScheduleLabel kPostUpdate = ScheduleLabel::kPostUpdate;
 
 enum class AppExitCode : int { kSuccess = 0, kFailure = 1 };
 
+// How a sub-app's update relates to the main frame (scheduler.cpp:204-240 ExtractSubApp / ClassifySubApp):
+//   kBlocking     wait for the sub-app, extract, update — every frame (the default)
+//   kOverlapping  kAllowOverlappingUpdates: the update is left running on the sub-world's stream while the main world
+//                 starts its next frame; an extract stage that finds it still running is SKIPPED, at most
+//                 kMaxOverlappingUpdates times in a row (0 = no limit), after which the main loop waits
+//   kAsync        kAsync: extraction every frame; a new update pass starts whenever the previous one has finished
+enum class SubAppMode : int { kBlocking = 0, kOverlapping = 1, kAsync = 2 };
+
 // sub_app.hpp — a world of its own plus labelled schedules; the main app is the first sub-app.
 class SubApp {
 public:
@@ -72,9 +80,43 @@ public:
   bool Built() const noexcept { return built_; }
   // One frame of this sub-app: every schedule in label order (RunAndWait = run + ApplyDeferred), then World::Update.
   void Update() {
+    if (pending_) FinishUpdate();
     for (auto& [l, s] : schedules_) s->RunAndWait();
     world_.Update();
+    ++updates_;
   }
+  // The asynchronous form of Update for overlapping / async sub-apps: every schedule but the last runs to completion
+  // (ApplyDeferred needs the host), the LAST one is only enqueued (Schedule::Run) and keeps the GPU busy on this
+  // sub-world's stream while the caller goes on; FinishUpdate applies its deferred data and ends the frame.
+  void BeginUpdate() {
+    if (pending_) FinishUpdate();
+    ecs::Schedule* last = schedules_.empty() ? nullptr : schedules_.rbegin()->second.get();
+    for (auto& [l, s] : schedules_)
+      if (s.get() != last) s->RunAndWait();
+    if (last) last->Run();
+    pending_ = true;
+  }
+  void FinishUpdate() {
+    if (!pending_) return;
+    if (!schedules_.empty()) schedules_.rbegin()->second->ApplyDeferred();
+    world_.Update();
+    pending_ = false;
+    ++updates_;
+  }
+  // sub_app.hpp IsUpdating / WaitUntilFullyIdle
+  bool IsUpdating() {
+    if (!pending_) return false;
+    uint32_t idle = 0;
+    world_.Check(helios_gpu_world_is_idle(world_.Handle(), &idle));
+    return idle == 0;
+  }
+  void WaitUntilFullyIdle() { FinishUpdate(); }
+  void SetMode(SubAppMode mode, size_t max_extraction_skips = 0) { mode_ = mode; max_skips_ = max_extraction_skips; }
+  SubAppMode Mode() const noexcept { return mode_; }
+  size_t MaxExtractionSkips() const noexcept { return max_skips_; }
+  uint64_t UpdateCount() const noexcept { return updates_; }
+  uint64_t ExtractCount() const noexcept { return extracts_; }
+  uint64_t SkippedExtractCount() const noexcept { return skipped_; }
   void SetExecutor(ecs::ExecutorKind kind) {
     for (auto& [l, s] : schedules_) s->SetExecutor(kind);
     kind_ = kind;
@@ -86,9 +128,15 @@ public:
   // sub_app.hpp:213-220,699-...
   void Extract(ecs::World& main_world) {
     if (extract_fn_) extract_fn_(main_world, world_);
+    ++extracts_;
   }
 
 private:
+  friend class App;
+  SubAppMode mode_ = SubAppMode::kBlocking;
+  size_t max_skips_ = 0, consecutive_skips_ = 0;
+  bool pending_ = false;
+  uint64_t updates_ = 0, extracts_ = 0, skipped_ = 0;
   ExtractFn extract_fn_;
   bool built_ = false;
   ecs::World world_;  // declared before the schedules: they (and their queries) are destroyed before the world
@@ -157,12 +205,43 @@ public:
   void Update() {
     Initialize();
     main_.Update();
-    for (auto& [name, sub] : sub_apps_) sub->Extract(main_.GetWorld());
-    for (auto& [name, sub] : sub_apps_) {
-      if (!sub->Built()) sub->Build();
-      sub->Update();
+    for (auto& [name, subp] : sub_apps_) {
+      SubApp& sub = *subp;
+      if (!sub.Built()) sub.Build();
+      bool fresh = false;
+      switch (sub.mode_) {  // scheduler.cpp:204-240 ExtractSubApp
+        case SubAppMode::kBlocking:
+          sub.WaitUntilFullyIdle();
+          sub.Extract(main_.GetWorld());
+          fresh = true;
+          break;
+        case SubAppMode::kAsync:
+          if (!sub.IsUpdating()) sub.FinishUpdate();  // the loop's previous pass is over: close it, start the next below
+          sub.Extract(main_.GetWorld());
+          break;
+        case SubAppMode::kOverlapping:
+          if (sub.IsUpdating() && (sub.max_skips_ == 0 || sub.consecutive_skips_ < sub.max_skips_)) {
+            ++sub.consecutive_skips_;
+            ++sub.skipped_;
+            break;
+          }
+          sub.WaitUntilFullyIdle();
+          sub.Extract(main_.GetWorld());
+          sub.consecutive_skips_ = 0;
+          fresh = true;
+          break;
+      }
+      // scheduler.cpp:153-172 LaunchSubAppUpdates: blocking sub-apps update now; overlapping ones start a pass after a
+      // fresh extract and leave it running; async ones start a pass whenever none is in flight
+      if (sub.mode_ == SubAppMode::kBlocking) sub.Update();
+      else if (sub.mode_ == SubAppMode::kOverlapping && fresh) sub.BeginUpdate();
+      else if (sub.mode_ == SubAppMode::kAsync && !sub.pending_) sub.BeginUpdate();
     }
     ++frame_;
+  }
+  // Scheduler::StopAsyncUpdateLoops / WaitUntilFullyIdle of every sub-app: call before reading sub-worlds on the host.
+  void WaitForSubApps() {
+    for (auto& [name, sub] : sub_apps_) sub->WaitUntilFullyIdle();
   }
   // Runs `frames` frames (the reference runs until an AppExit message; a frame budget is the headless equivalent).
   AppExitCode Run(uint64_t frames) {

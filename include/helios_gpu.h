@@ -66,6 +66,9 @@ HELIOS_GPU_API const char* helios_gpu_last_error(const helios_gpu_world* w);
 /* Use an externally created cudaStream_t (e.g. torch's current stream) as the world's primary stream. */
 HELIOS_GPU_API int32_t helios_gpu_world_set_stream(helios_gpu_world* w, void* cuda_stream);
 HELIOS_GPU_API int32_t helios_gpu_world_synchronize(helios_gpu_world* w);
+/* *idle = 1 when everything enqueued on the world's stream has finished; never blocks (SubApp::IsUpdating of an
+ * overlapping sub-app, src/app/src/scheduler.cpp:221-232). */
+HELIOS_GPU_API int32_t helios_gpu_world_is_idle(helios_gpu_world* w, uint32_t* idle);
 /* Number of kernels this world has launched so far (bench.py's gpu_launches). */
 HELIOS_GPU_API uint64_t helios_gpu_world_launch_count(const helios_gpu_world* w);
 

@@ -333,6 +333,47 @@ int main(int argc, char** argv) {
     CHECK(sub.ReadComponent<Velocity>(ecs::Entity{299, 1}).dy == 2.0f);
     CHECK(main_world.EntityCount() == 350);
   }
+  // ---- overlapping / async sub-apps (sub_app.hpp:58-73 kAllowOverlappingUpdates / kMaxOverlappingUpdates / kAsync;
+  //      scheduler.cpp:204-240 ExtractSubApp): the sub-app's update stays on its own stream across the next main frame ----
+  for (const app::SubAppMode mode : {app::SubAppMode::kOverlapping, app::SubAppMode::kAsync}) {
+    app::App application;
+    ecs::World& main_world = application.GetWorld();
+    const size_t n = 200000;
+    std::vector<Position> pos(n, Position{0, 0});
+    std::vector<Velocity> vel(n, Velocity{1.0f, 0.5f});
+    main_world.SpawnBatch<Position, Velocity>(n, std::span<const Position>(pos), std::span<const Velocity>(vel));
+    helios_gpu_system_fn integrate = nullptr, damp = nullptr;
+    main_world.Check(helios_gpu_builtin_system("integrate", &integrate));
+    main_world.Check(helios_gpu_builtin_system("damp", &damp));
+    application.AddSystem<ecs::Query<Position&, const Velocity&>>(app::kUpdate, "ChangePosition", integrate);
+    ecs::Query<const Position&, const Velocity&> moving(main_world);
+    app::SubApp& render = application.AddSubApp("Render");
+    render.SetMode(mode, /*max_extraction_skips=*/1);
+    render.SetExtractFunction([&moving](ecs::World&, ecs::World& sub) {
+      sub.ClearEntities();
+      moving.ExtractInto(sub);
+    });
+    const float k = 0.5f;
+    ecs::GpuSystemOptions damp_opt;
+    damp_opt.params = &k;
+    damp_opt.params_size = sizeof(k);
+    render.GetSchedule(app::kUpdate).AddGpu<ecs::Query<Velocity&>>("RenderDamp", damp, damp_opt);
+    const uint64_t frames = 12;
+    application.Run(frames);
+    application.WaitForSubApps();
+    CHECK(render.ExtractCount() + render.SkippedExtractCount() == frames);
+    CHECK(render.ExtractCount() >= frames / 2);                      // at most one skip in a row (kMaxOverlappingUpdates = 1)
+    if (mode == app::SubAppMode::kAsync) CHECK(render.SkippedExtractCount() == 0);  // async: extraction every frame
+    CHECK(render.UpdateCount() >= 1 && render.UpdateCount() <= frames);
+    // the main world is never held back: 12 frames of p += v whatever the sub-app was doing
+    CHECK(main_world.ReadComponent<Position>(ecs::Entity{4242, 1}).x == 12.0f);
+    // the sub-world holds a copy of some frame's main rows (x = frame number) with its own damp applied to a fresh copy of v
+    ecs::World& sub = render.GetWorld();
+    const Position sp = sub.ReadComponent<Position>(ecs::Entity{4242, 1});
+    const Velocity sv = sub.ReadComponent<Velocity>(ecs::Entity{4242, 1});
+    CHECK(sub.EntityCount() == n && sp.x >= 1.0f && sp.x <= 12.0f && sp.y == sp.x * 0.5f);
+    CHECK(sv.dx == 0.5f || sv.dx == 1.0f);  // damped once since its extraction, or extracted after the last pass began
+  }
   std::printf("shim_test gpu: %d checks, %d failed\n", g_checks, g_fail);
   return g_fail;
 }
