@@ -109,3 +109,47 @@ def test_commands_spawn_ids_never_recycle(oracle):
     assert [(int(x) & 0xFFFFFFFF, int(x) >> 32) for x in c] == [(2, 2), (1, 2)]
     assert w.entity_count() == 6
     w.close()
+
+
+def _run_condition_host_rules(backend):
+    """RunIf / Set RunIf / InSet mark the schedule dirty (tests/schedule/system_set_handle.cpp:190-224): Run before Build is
+    an error (schedule.cpp:56-58); malformed condition descriptors are rejected; set conditions reach every member."""
+    from heliosengine_b200 import capi, worlds
+    w = capi.World(backend)
+    worlds.register_all(w, ["Health"])
+    H = worlds.cname("Health")
+    w.spawn_batch([H], 10, [np.full(10, 5, dtype=np.int32)], want_entities=False)
+    s = w.schedule("Update")
+    a = s.add_system("a", "regen", w.query([(H, True)]))
+    b = s.add_system("b", "regen", w.query([(H, True)]))
+    s.build()
+    s.run_and_wait()
+    assert s.last_verdicts() == [1, 1]
+    s.set_run_if(7, "Off", capi.COND_CONSTANT, rhs=0)
+    s.in_set(b, 7)
+    with pytest.raises(capi.HeliosError) as e:
+        s.run_and_wait()
+    assert e.value.status == capi.ERR_STATE
+    s.build()
+    s.build()  # conditions survive a double Build (tests/schedule/schedule.cpp:900-945)
+    s.run_and_wait()
+    assert s.last_verdicts() == [1, 0]
+    for bad in (dict(kind=capi.COND_RESOURCE, offset=4), dict(kind=capi.COND_RESOURCE, offset=4096),
+                dict(kind=capi.COND_MESSAGES), dict(kind=capi.COND_TERMINAL), dict(kind=capi.COND_WORLD_RESOURCE, offset=0),
+                dict(kind=capi.COND_CONSTANT, cmp=9), dict(kind=17)):
+        with pytest.raises(capi.HeliosError) as e:
+            s.run_if(a, "bad", **bad)
+        assert e.value.status == capi.ERR_INVALID_ARGUMENT, bad
+    with pytest.raises(capi.HeliosError) as e:
+        s.run_if(5, "nobody", capi.COND_CONSTANT, rhs=1)
+    assert e.value.status == capi.ERR_NOT_FOUND
+    w.close()
+
+
+def test_run_condition_host_rules_oracle(oracle):
+    _run_condition_host_rules(oracle)
+
+
+@pytest.mark.gpu
+def test_run_condition_host_rules_gpu(gpu):
+    _run_condition_host_rules(gpu)
