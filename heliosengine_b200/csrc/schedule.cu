@@ -132,7 +132,7 @@ int32_t prepare(helios_gpu_schedule* s) {
     HG_CUDA(w, cudaMemsetAsync(s->resources.ptr, 0, HELIOS_GPU_RESOURCE_BYTES, w->stream));
     ++w->epoch;
   }
-  if (!s->verdicts.ptr) {
+  if (s->any_conditions && !s->verdicts.ptr) {
     HG_CUDA(w, s->verdicts.reserve(64 * sizeof(uint32_t), 0, w->stream, false));
     ++w->epoch;
   }
@@ -155,8 +155,9 @@ int32_t prepare(helios_gpu_schedule* s) {
         }
       }
   }
-  // every system starts a run as "ran"; a guarded system's condition chain overwrites its word
-  HG_CUDA(w, cudaMemsetAsync(s->verdicts.ptr, 0x01, 64 * sizeof(uint32_t), w->stream));
+  // every system starts a run as "ran"; a guarded system's condition chain overwrites its word (a schedule without
+  // conditions pays nothing: no buffer, no memset in front of its first system)
+  if (s->any_conditions) HG_CUDA(w, cudaMemsetAsync(s->verdicts.ptr, 0x01, 64 * sizeof(uint32_t), w->stream));
   for (auto& ep : s->entries) {
     SysEntry& e = *ep;
     const uint64_t rows = host_match_rows(w, e.desc.query);
@@ -714,7 +715,7 @@ int32_t helios_gpu_schedule_last_verdicts(helios_gpu_schedule* s, uint32_t* out,
   helios_gpu_world* w = s->world;
   const uint32_t n = uint32_t(s->entries.size());
   if (capacity < n) return HELIOS_GPU_ERR_CAPACITY;
-  if (!s->verdicts.ptr) { std::fill(out, out + n, 1u); return HELIOS_GPU_OK; }
+  if (!s->verdicts.ptr || !s->any_conditions) { std::fill(out, out + n, 1u); return HELIOS_GPU_OK; }
   uint32_t host[64];
   HG_CUDA(w, cudaMemcpyAsync(host, s->verdicts.ptr, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, w->stream));
   HG_CUDA(w, cudaStreamSynchronize(w->stream));
