@@ -32,6 +32,9 @@ SYSTEM_EMITS_COMMANDS = 1
 SYSTEM_NEEDS_VIEW = 2
 SYSTEM_CONSUMES_MESSAGES = 4
 
+WORLD_NO_BUILTIN_MESSAGES = 1  # helios_gpu_world_config::flags
+BUILTIN_ENTITY_ADDED, BUILTIN_ENTITY_DESTROYED, BUILTIN_COMPONENTS_CLEARED, BUILTIN_COMPONENT_ADDED, BUILTIN_COMPONENT_REMOVED = range(5)
+
 INVALID_ENTITY = 0xFFFFFFFFFFFFFFFF
 
 _FNV_BASIS = 14695981039346656037
@@ -98,6 +101,8 @@ class SystemDesc(C.Structure):
         ("n_read_resources", C.c_uint32), ("n_write_resources", C.c_uint32),
         ("extra_read_components", C.c_uint64 * 8), ("extra_write_components", C.c_uint64 * 8),
         ("read_resources", C.c_uint64 * 8), ("write_resources", C.c_uint64 * 8),
+        ("n_more_writes", C.c_uint32), ("n_more_reads", C.c_uint32),
+        ("more_writes", C.c_uint64 * 3), ("more_writer_capacity", C.c_uint64 * 3), ("more_reads", C.c_uint64 * 3),
     ]
 
 
@@ -166,10 +171,10 @@ def _ptr(a: np.ndarray):
 class World:
     """helios::ecs::World-shaped handle (reference world.hpp) over one backend."""
 
-    def __init__(self, backend: Backend, device: int = 0, entity_capacity: int = 0):
+    def __init__(self, backend: Backend, device: int = 0, entity_capacity: int = 0, flags: int = 0):
         self.b = backend
         self.h = C.c_void_p()
-        cfg = WorldConfig(device, entity_capacity, 0, 0)
+        cfg = WorldConfig(device, entity_capacity, 0, flags)
         st = backend.fn("world_create")(C.byref(cfg), C.byref(self.h))
         if st != OK:
             raise HeliosError(st, "world_create failed (is a CUDA device visible? there is no CPU fallback)")
@@ -323,7 +328,48 @@ class World:
         free = np.empty(fc.value, dtype=np.uint32)
         self._check(self.b.fn("snapshot_entity_table")(self.h, C.byref(nxt), _ptr(gens), C.c_uint32(gens.size), _ptr(free), C.c_uint32(free.size), C.byref(fc), C.byref(cur)))
         return {"archetypes": archs, "next_index": nxt.value, "generations": gens, "free_indices": free,
-                "free_cursor": cur.value, "entity_count": self.entity_count()}
+                "free_cursor": cur.value, "entity_count": self.entity_count(), "messages": self.snapshot_messages()}
+
+    # -- message queues as part of the world state (builtin structural messages included) ----------------------------
+    def message_types(self) -> list[tuple[int, int]]:
+        """(type hash, element size) of every registered non-async message type, sorted by hash."""
+        n = C.c_uint32()
+        self._check(self.b.fn("message_types")(self.h, None, None, C.c_uint32(0), C.byref(n)))
+        hashes = (C.c_uint64 * max(1, n.value))()
+        sizes = (C.c_uint32 * max(1, n.value))()
+        self._check(self.b.fn("message_types")(self.h, hashes, sizes, C.c_uint32(n.value), C.byref(n)))
+        return sorted((int(hashes[i]), int(sizes[i])) for i in range(n.value))
+
+    def message_read_hash(self, type_hash: int, size: int, which: int) -> np.ndarray:
+        p, c = C.c_uint64(), C.c_uint64()
+        self._check(self.b.fn("message_counts")(self.h, C.c_uint64(type_hash), C.byref(p), C.byref(c)))
+        cnt = c.value if which else p.value
+        buf = np.empty(cnt * size, dtype=np.uint8)
+        self._check(self.b.fn("message_read")(self.h, C.c_uint64(type_hash), C.c_uint32(which), _ptr(buf) if buf.size else None,
+                                              C.c_uint64(buf.nbytes)))
+        return buf
+
+    def snapshot_messages(self) -> dict:
+        """{type hash: (previous bytes, current bytes)} over every registered message type."""
+        return {h: (self.message_read_hash(h, sz, 0), self.message_read_hash(h, sz, 1)) for h, sz in self.message_types()}
+
+    def builtin_message_type(self, kind: int, component: str | None = None) -> int:
+        out = C.c_uint64()
+        self._check(self.b.fn("builtin_message_type")(self.h, C.c_uint32(kind), C.c_uint64(fnv1a(component) if component else 0),
+                                                      C.byref(out)))
+        return out.value
+
+    def component_message_types(self, component: str, added_hash: int, removed_hash: int):
+        self._check(self.b.fn("component_message_types")(self.h, C.c_uint64(fnv1a(component)), C.c_uint64(added_hash),
+                                                         C.c_uint64(removed_hash)))
+
+    def builtin_messages(self, kind: int, component: str | None = None, which: int = 1) -> np.ndarray:
+        """Entities carried by the builtin messages of one kind (previous: which = 0, current: which = 1); empty if the
+        type was never registered."""
+        h = self.builtin_message_type(kind, component)
+        if h not in dict(self.message_types()):
+            return np.empty(0, dtype=np.uint64)
+        return self.message_read_hash(h, 8, which).view(np.uint64)
 
     def column_write(self, archetype: int, name: str, row0: int, rows: int, src_ptr: int):
         self._check(self.b.fn("archetype_column_write")(self.h, C.c_uint32(archetype), C.c_uint64(fnv1a(name)),
@@ -567,7 +613,9 @@ class Schedule:
                    writes_message: str | None = None, reads_message: str | None = None, writer_capacity: int = 0,
                    cmd_slots_per_row: int = 1, cmd_payload_stride: int = 0,
                    extra_reads: Sequence[str] = (), extra_writes: Sequence[str] = (),
-                   read_resources: Sequence[str] = (), write_resources: Sequence[str] = ()) -> int:
+                   read_resources: Sequence[str] = (), write_resources: Sequence[str] = (),
+                   more_writes: Sequence[tuple[str, int]] = (), more_reads: Sequence[str] = ()) -> int:
+        """more_writes: (message type, writer capacity) of the 2nd.. MessageWriter parameter; more_reads: 2nd.. reader."""
         fnp = C.c_void_p()
         st = self.w.b.fn("builtin_system")(builtin.encode(), C.byref(fnp))
         if st != OK:
@@ -587,6 +635,13 @@ class Schedule:
         d.writes_message = fnv1a(writes_message) if writes_message else 0
         d.reads_message = fnv1a(reads_message) if reads_message else 0
         d.writer_capacity = writer_capacity
+        d.n_more_writes = len(more_writes)
+        for i, (mname, mcap) in enumerate(more_writes):
+            d.more_writes[i] = fnv1a(mname)
+            d.more_writer_capacity[i] = mcap
+        d.n_more_reads = len(more_reads)
+        for i, mname in enumerate(more_reads):
+            d.more_reads[i] = fnv1a(mname)
         for attr, cnt, names in (("extra_read_components", "n_extra_read_components", extra_reads),
                                  ("extra_write_components", "n_extra_write_components", extra_writes),
                                  ("read_resources", "n_read_resources", read_resources),

@@ -36,7 +36,13 @@ constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr uint64_t kDeadMask = 0xFFFFFFFFFFFFFFFFull;  // destination "mask" of a destroyed entity
 constexpr uint64_t kInstA = 1ull << 63;                 // instance key tag: opened by the Append op in the low bits
 
-enum : uint32_t { F_VALID = 1u, F_MIG = 2u, F_DESTROY = 4u, F_SPLAST = 8u /* last sparse-set event of its entity */ };
+enum : uint32_t {
+  F_VALID = 1u, F_MIG = 2u, F_DESTROY = 4u, F_SPLAST = 8u /* last sparse-set event of its entity */,
+  // builtin structural messages the command writes (world.hpp:993,1003,1035,1060,1133,1159,1195): em[k] holds the
+  // component slots of its ComponentAddedMsg<T> (F_EM_ADD) or ComponentRemovedMsg<T> (F_EM_REM) messages;
+  // F_DESTROY = one EntityDestroyedMsg, F_EM_CLEAR = one ComponentsClearedMsg
+  F_EM_ADD = 16u, F_EM_REM = 32u, F_EM_CLEAR = 64u
+};
 
 struct Counters {
   uint32_t n_valid_slots;  // K: compacted command count
@@ -50,7 +56,11 @@ struct Counters {
   uint32_t dups;           // commands whose entity has an earlier command in the same batch
   uint32_t ticket;         // dynamic block index of the single-launch resolver
   uint32_t sparse_events;  // commands that append to / remove from / write into a sparse-set storage
+  uint32_t pad0;
   unsigned long long moved_bytes;
+  // component slots named by a valid Add/TryAdd (resp. Remove/TryRemove) command: their ComponentAdded/RemovedMsg<T>
+  // types get registered even when no message follows (AddMessages<...>() precedes the call, world.hpp:1033,1047,1131,1145)
+  unsigned long long touched_add, touched_rem;
 };
 
 struct Unknown {
@@ -135,6 +145,7 @@ struct helios_gpu_world::ApplyScratch {
   DevBuf ih_keys, ih_vals;
   DevBuf ch_slot, ch_ent, stage;
   DevBuf ev_app, ev_rem, ev_wr, ev_mem;  // per-command sparse-set events (ordinal masks) and membership after the command
+  DevBuf em, bm_matrix, bm_ex, bm_totals, bm_partials;  // builtin structural messages: per-command slots, per-(type, tile) counts
   DevBuf coffset;  // uint32[64] byte offset of each component inside a staged row
   uint32_t stage_stride = 0;
   size_t stride_comps = 0;
@@ -223,6 +234,9 @@ struct ChainArgs {
   uint32_t* ev_rem;
   uint32_t* ev_wr;
   uint32_t* ev_mem;
+  // builtin structural messages: em == nullptr when the world runs without them
+  uint64_t* em;
+  uint64_t registered_slots;  // bit s = component slot s exists
 };
 
 __device__ __forceinline__ uint32_t sparse_ordinals(const ChainArgs& a, uint64_t slots) {
@@ -233,6 +247,17 @@ __device__ __forceinline__ uint32_t sparse_ordinals(const ChainArgs& a, uint64_t
     o |= 1u << a.ord_of_slot[s];
   }
   return o;
+}
+
+// Slots (out of `slots`, all sparse-stored) whose ordinal is set in `ordinals`.
+__device__ __forceinline__ uint64_t sparse_slots_of(const ChainArgs& a, uint64_t slots, uint32_t ordinals) {
+  uint64_t out = 0;
+  while (slots) {
+    const int s = __ffsll(static_cast<long long>(slots)) - 1;
+    slots &= slots - 1;
+    if (ordinals >> a.ord_of_slot[s] & 1u) out |= 1ull << s;
+  }
+  return out;
 }
 
 __global__ void k_chain(ChainArgs a) {
@@ -255,6 +280,7 @@ __global__ void k_chain(ChainArgs a) {
   const bool sp = a.sparse_slots != 0;
   uint32_t sm = (sp && alive) ? a.membership[idx] : 0u;  // sparse-set membership, tracked like the archetype mask
   uint32_t last_ev = kNone, n_ev = 0;
+  uint64_t touched_add = 0, touched_rem = 0;
   for (; r < a.K && a.skey[r] == idx64; ++r) {
     const uint32_t k = a.sval[r];
     const helios_gpu_command c = a.cmd[k];
@@ -262,7 +288,9 @@ __global__ void k_chain(ChainArgs a) {
     uint64_t src = mask, dst = mask, w = 0;
     uint32_t fl = 0;
     uint32_t eapp = 0, erem = 0, ewr = 0;
+    uint64_t em = 0;  // builtin messages: component slots of the ComponentAdded/RemovedMsg<T> this command writes
     const uint64_t cm = c.component_mask & ~a.sparse_slots;  // archetype-stored part of the command's component set
+    const uint64_t csp = c.component_mask & a.sparse_slots;
     const uint32_t sb = (sp && (c.component_mask & a.sparse_slots)) ? sparse_ordinals(a, c.component_mask & a.sparse_slots) : 0u;
     if (!v) {
       // Try* variants skip silently (world.hpp:996-1000); the others are HELIOS_ASSERT failures in the reference
@@ -284,6 +312,9 @@ __global__ void k_chain(ChainArgs a) {
           eapp = sb & ~sm;             // AddSparseComponent -> Set: insert or overwrite (sparse_storage.hpp:121-131)
           ewr = sb;
           sm |= sb;
+          fl |= F_EM_ADD;              // world.hpp:1035 — one ComponentAddedMsg per listed type, overwrites included
+          em = c.component_mask;
+          touched_add |= c.component_mask;
           break;
         case HELIOS_GPU_CMD_TRY_ADD:   // manager.hpp:1205-1248 — only the missing ones
           w = cm & ~mask;
@@ -291,17 +322,24 @@ __global__ void k_chain(ChainArgs a) {
           eapp = sb & ~sm;             // TrySet: present values stay untouched (sparse_storage.hpp:133-143)
           ewr = eapp;
           sm |= sb;
+          fl |= F_EM_ADD;              // world.hpp:1052-1064 — only the types that were actually added
+          em = w | (csp ? sparse_slots_of(a, csp, eapp) : 0ull);
+          touched_add |= c.component_mask;
           break;
         case HELIOS_GPU_CMD_REMOVE:
         case HELIOS_GPU_CMD_TRY_REMOVE:  // manager.hpp:1268-1312
           dst = mask & ~cm;
           erem = sb & sm;              // (Try)RemoveSparseComponent (manager.hpp:1355-1377); absent = skipped
           sm &= ~sb;
+          fl |= F_EM_REM;              // world.hpp:1133 every listed type; :1148-1161 Try: only the ones removed
+          em = c.kind == HELIOS_GPU_CMD_REMOVE ? c.component_mask : ((cm & mask) | (csp ? sparse_slots_of(a, csp, erem) : 0ull));
+          touched_rem |= c.component_mask;
           break;
         case HELIOS_GPU_CMD_CLEAR:       // manager.hpp:1117-1144
           dst = 0;
           erem = sm;                     // manager.hpp:1140-1143
           sm = 0;
+          fl |= F_EM_CLEAR;              // world.hpp:1195
           break;
         default: break;
       }
@@ -314,6 +352,7 @@ __global__ void k_chain(ChainArgs a) {
       a.ev_mem[k] = sm;
       if (eapp | erem | ewr) { last_ev = k; ++n_ev; }
     }
+    if (a.em) a.em[k] = em & a.registered_slots;
     a.src_mask[k] = src;
     a.dst_mask[k] = dst;
     a.wset[k] = w;
@@ -347,6 +386,14 @@ __global__ void k_chain(ChainArgs a) {
     a.wlive[k] = live;
   }
   if (invalid) atomicAdd(&a.counters->invalid, invalid);
+  if (a.em) {  // almost always already covered by an earlier thread: one volatile read, rarely an atomic
+    touched_add &= a.registered_slots;
+    touched_rem &= a.registered_slots;
+    if (touched_add && (*reinterpret_cast<volatile unsigned long long*>(&a.counters->touched_add) & touched_add) != touched_add)
+      atomicOr(&a.counters->touched_add, touched_add);
+    if (touched_rem && (*reinterpret_cast<volatile unsigned long long*>(&a.counters->touched_rem) & touched_rem) != touched_rem)
+      atomicOr(&a.counters->touched_rem, touched_rem);
+  }
 }
 
 // ================================================================================================================
@@ -797,6 +844,116 @@ __global__ void k_apply_deltas(uint32_t ntables, const uint32_t* __restrict__ tr
   if (t < ntables) tcount[t] = tcount[t] + tapp[t] - trem[t];
 }
 
+// ================================================================================================================
+// Builtin structural messages (builtin_messages.hpp; world.hpp:993,1003,1035,1060,1133,1159,1195).  Sequential replay
+// appends one 8-byte message (the entity) per effective command and message type to the world's current queue of that
+// type.  Per type this is an ORDERED COMPACTION of the command stream: a stable multi-way partition with one "channel"
+// per message type — 0 EntityDestroyedMsg, 1 ComponentsClearedMsg, 2 + s ComponentAddedMsg<slot s>,
+// 2 + ncomps + s ComponentRemovedMsg<slot s> — done as per-tile counts -> one exclusive scan (channel-major) -> scatter.
+// ================================================================================================================
+constexpr uint32_t kBmTile = 256;       // commands per CTA
+constexpr uint32_t kBmMaxChannels = 2 + 2 * HELIOS_GPU_MAX_COMPONENTS;
+
+// Adds, for every set bit b of the warp's `bits`, the number of lanes holding it to cnt[base + b] (lane 0 stores; the row is
+// private to the warp or updated atomically by the caller's choice of `shared_row`).  All 32 lanes must call.
+__device__ __forceinline__ void bm_warp_tally(uint32_t bits, uint32_t base, uint32_t* cnt, bool atomic) {
+  uint32_t any = __reduce_or_sync(0xFFFFFFFFu, bits);
+  while (any) {
+    const int b = __ffs(any) - 1;
+    any &= any - 1;
+    const uint32_t n = __popc(__ballot_sync(0xFFFFFFFFu, (bits >> b) & 1u));
+    if ((threadIdx.x & 31u) == 0) {
+      if (atomic) atomicAdd(&cnt[base + b], n);
+      else cnt[base + b] += n;
+    }
+  }
+}
+
+struct BmBits {  // channel set of one command as five 32-bit words
+  uint32_t misc, add_lo, add_hi, rem_lo, rem_hi;
+};
+__device__ __forceinline__ BmBits bm_bits(uint32_t fl, uint64_t em) {
+  BmBits b;
+  b.misc = ((fl & F_DESTROY) ? 1u : 0u) | ((fl & F_EM_CLEAR) ? 2u : 0u);
+  const uint64_t add = (fl & F_EM_ADD) ? em : 0ull, rem = (fl & F_EM_REM) ? em : 0ull;
+  b.add_lo = uint32_t(add); b.add_hi = uint32_t(add >> 32);
+  b.rem_lo = uint32_t(rem); b.rem_hi = uint32_t(rem >> 32);
+  return b;
+}
+
+__global__ void __launch_bounds__(kBmTile) k_bm_count(uint32_t K, const uint32_t* __restrict__ cflags, const uint64_t* __restrict__ em,
+                                                      uint32_t ncomps, uint32_t ntiles, uint32_t* __restrict__ matrix) {
+  __shared__ uint32_t s_cnt[kBmMaxChannels];
+  const uint32_t C = 2 + 2 * ncomps;
+  for (uint32_t i = threadIdx.x; i < C; i += kBmTile) s_cnt[i] = 0;
+  __syncthreads();
+  const uint32_t k = blockIdx.x * kBmTile + threadIdx.x;
+  const BmBits b = k < K ? bm_bits(cflags[k], em[k]) : BmBits{0, 0, 0, 0, 0};
+  bm_warp_tally(b.misc, 0, s_cnt, true);
+  bm_warp_tally(b.add_lo, 2, s_cnt, true);
+  bm_warp_tally(b.add_hi, 2 + 32, s_cnt, true);
+  bm_warp_tally(b.rem_lo, 2 + ncomps, s_cnt, true);
+  bm_warp_tally(b.rem_hi, 2 + ncomps + 32, s_cnt, true);
+  __syncthreads();
+  for (uint32_t c = threadIdx.x; c < C; c += kBmTile) matrix[size_t(c) * ntiles + blockIdx.x] = s_cnt[c];
+}
+
+// ex = exclusive scan of the channel-major matrix, ex[C * ntiles] = grand total: messages per channel.
+__global__ void k_bm_totals(uint32_t C, uint32_t ntiles, const uint32_t* __restrict__ ex, uint32_t* __restrict__ totals) {
+  const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < C) totals[c] = ex[size_t(c + 1) * ntiles] - ex[size_t(c) * ntiles];
+}
+
+struct BmDst {
+  helios_gpu_entity_t* ptr[kBmMaxChannels];  // channel -> first free slot of the type's current queue (nullptr: no messages)
+};
+
+__device__ __forceinline__ void bm_warp_scatter(uint32_t bits, uint32_t base, const uint32_t* __restrict__ off, const BmDst& dst,
+                                                helios_gpu_entity_t e) {
+  const uint32_t lane = threadIdx.x & 31u;
+  uint32_t any = __reduce_or_sync(0xFFFFFFFFu, bits);
+  while (any) {
+    const int b = __ffs(any) - 1;
+    any &= any - 1;
+    const uint32_t votes = __ballot_sync(0xFFFFFFFFu, (bits >> b) & 1u);
+    if ((bits >> b) & 1u) dst.ptr[base + b][off[base + b] + __popc(votes & ((1u << lane) - 1u))] = e;
+  }
+}
+
+__global__ void __launch_bounds__(kBmTile) k_bm_scatter(uint32_t K, const helios_gpu_command* __restrict__ cmd,
+                                                        const uint32_t* __restrict__ cflags, const uint64_t* __restrict__ em,
+                                                        uint32_t ncomps, uint32_t ntiles, const uint32_t* __restrict__ ex,
+                                                        const BmDst dst) {
+  __shared__ uint32_t s_warp[kBmTile / 32][kBmMaxChannels];  // per-warp counts, then the warp's first position per channel
+  const uint32_t C = 2 + 2 * ncomps;
+  const uint32_t wid = threadIdx.x >> 5;
+  for (uint32_t i = threadIdx.x; i < (kBmTile / 32) * kBmMaxChannels; i += kBmTile) (&s_warp[0][0])[i] = 0;
+  __syncthreads();
+  const uint32_t k = blockIdx.x * kBmTile + threadIdx.x;
+  const BmBits b = k < K ? bm_bits(cflags[k], em[k]) : BmBits{0, 0, 0, 0, 0};
+  const helios_gpu_entity_t e = k < K ? cmd[k].entity : 0;
+  bm_warp_tally(b.misc, 0, s_warp[wid], false);
+  bm_warp_tally(b.add_lo, 2, s_warp[wid], false);
+  bm_warp_tally(b.add_hi, 2 + 32, s_warp[wid], false);
+  bm_warp_tally(b.rem_lo, 2 + ncomps, s_warp[wid], false);
+  bm_warp_tally(b.rem_hi, 2 + ncomps + 32, s_warp[wid], false);
+  __syncthreads();
+  for (uint32_t c = threadIdx.x; c < C; c += kBmTile) {  // tile base inside the channel + exclusive prefix over the warps
+    uint32_t run = ex[size_t(c) * ntiles + blockIdx.x] - ex[size_t(c) * ntiles];
+    for (uint32_t w2 = 0; w2 < kBmTile / 32; ++w2) {
+      const uint32_t n = s_warp[w2][c];
+      s_warp[w2][c] = run;
+      run += n;
+    }
+  }
+  __syncthreads();
+  bm_warp_scatter(b.misc, 0, s_warp[wid], dst, e);
+  bm_warp_scatter(b.add_lo, 2, s_warp[wid], dst, e);
+  bm_warp_scatter(b.add_hi, 2 + 32, s_warp[wid], dst, e);
+  bm_warp_scatter(b.rem_lo, 2 + ncomps, s_warp[wid], dst, e);
+  bm_warp_scatter(b.rem_hi, 2 + ncomps + 32, s_warp[wid], dst, e);
+}
+
 }  // namespace
 
 // ================================================================================================================
@@ -857,6 +1014,68 @@ int32_t upload_component_layout(helios_gpu_world* w) {
   HG_CUDA(w, cudaMemcpyAsync(S.coffset.ptr, off, sizeof(off), cudaMemcpyHostToDevice, st));
   HG_CUDA(w, cudaStreamSynchronize(st));
   S.stride_comps = w->comps.size();
+  return HELIOS_GPU_OK;
+}
+
+// Builtin structural messages, part 1 (before the pipeline's host read-back): per-(message type, tile) counts, their
+// channel-major exclusive scan and the per-type totals.  Returns the number of kernels launched.
+int32_t bm_count_pass(helios_gpu_world* w, uint32_t K, uint64_t* launches) {
+  auto& S = *w->apply;
+  cudaStream_t st = w->stream;
+  const uint32_t ncomps = uint32_t(w->comps.size());
+  const uint32_t C = 2 + 2 * ncomps;
+  const uint32_t ntiles = (K + kBmTile - 1) / kBmTile;
+  const size_t cells = size_t(C) * ntiles;
+  NEED(S.bm_matrix, cells * 4);
+  NEED(S.bm_ex, (cells + 1) * 4);
+  NEED(S.bm_totals, kBmMaxChannels * 4);
+  NEED(S.bm_partials, (cells / prim::kScanTile + 2) * 4);
+  k_bm_count<<<ntiles, kBmTile, 0, st>>>(K, S.cflags.as<uint32_t>(), S.em.as<uint64_t>(), ncomps, ntiles, S.bm_matrix.as<uint32_t>());
+  *launches += 1 + prim::exclusive_scan_u32(S.bm_matrix.as<uint32_t>(), S.bm_ex.as<uint32_t>(), cells, S.bm_partials.as<uint32_t>(),
+                                            S.bm_ex.as<uint32_t>() + cells, st);
+  k_bm_totals<<<1, kBmMaxChannels, 0, st>>>(C, ntiles, S.bm_ex.as<uint32_t>(), S.bm_totals.as<uint32_t>());
+  *launches += 1;
+  return HELIOS_GPU_OK;
+}
+
+// Part 2 (totals known on the host): register the touched ComponentAdded/RemovedMsg<T> types, grow the current queues,
+// scatter the entities in command order, publish the new counts.
+int32_t bm_scatter_pass(helios_gpu_world* w, const helios_gpu_command* cmd, uint32_t K, const uint32_t* totals,
+                        uint64_t touched_add, uint64_t touched_rem, uint64_t* launches) {
+  auto& S = *w->apply;
+  cudaStream_t st = w->stream;
+  const uint32_t ncomps = uint32_t(w->comps.size());
+  const uint32_t C = 2 + 2 * ncomps;
+  const uint32_t ntiles = (K + kBmTile - 1) / kBmTile;
+  auto hash_of = [&](uint32_t c) -> uint64_t {
+    if (c == 0) return kMsgEntityDestroyed;
+    if (c == 1) return kMsgComponentsCleared;
+    return c < 2 + ncomps ? w->comps[c - 2].added_msg : w->comps[c - 2 - ncomps].removed_msg;
+  };
+  MsgChannel* ch = nullptr;
+  for (uint32_t sl = 0; sl < ncomps; ++sl) {  // AddMessages<...>() of every valid Add / Remove call, messages or not
+    if (touched_add >> sl & 1) HG_TRY(builtin_channel(w, w->comps[sl].added_msg, &ch));
+    if (touched_rem >> sl & 1) HG_TRY(builtin_channel(w, w->comps[sl].removed_msg, &ch));
+  }
+  BmDst dst{};
+  bool any = false;
+  for (uint32_t c = 0; c < C; ++c) {
+    if (!totals[c]) continue;
+    HG_TRY(builtin_channel(w, hash_of(c), &ch));
+    HG_CUDA(w, ch->cur.reserve((ch->cur_count + totals[c]) * 8, ch->cur_count * 8, st));
+    dst.ptr[c] = ch->cur.as<helios_gpu_entity_t>() + ch->cur_count;
+    any = true;
+  }
+  if (!any) return HELIOS_GPU_OK;
+  k_bm_scatter<<<ntiles, kBmTile, 0, st>>>(K, cmd, S.cflags.as<uint32_t>(), S.em.as<uint64_t>(), ncomps, ntiles,
+                                           S.bm_ex.as<uint32_t>(), dst);
+  *launches += 1;
+  for (uint32_t c = 0; c < C; ++c) {
+    if (!totals[c]) continue;
+    ch = find_channel(w, hash_of(c));
+    ch->cur_count += totals[c];
+    HG_TRY(publish_channel(w, ch));
+  }
   return HELIOS_GPU_OK;
 }
 
@@ -939,12 +1158,18 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     ca.ev_app = S.ev_app.as<uint32_t>(); ca.ev_rem = S.ev_rem.as<uint32_t>();
     ca.ev_wr = S.ev_wr.as<uint32_t>();   ca.ev_mem = S.ev_mem.as<uint32_t>();
   }
+  if (w->builtin_messages) {
+    NEED(S.em, K * 8);
+    ca.em = S.em.as<uint64_t>();
+    ca.registered_slots = w->comps.size() >= 64 ? ~0ull : ((1ull << w->comps.size()) - 1);
+  }
   k_chain<<<blocks_for(K), 256, 0, st>>>(ca);
   ++launches;
 
   // ---- stage 3: masks → tables (creating missing archetypes in command order), per-table op counts ------------------
   NEED(S.unknown, size_t(K) * sizeof(Unknown));
   std::vector<uint32_t> hrem, happ;
+  uint32_t bm_totals[kBmMaxChannels] = {};
   uint32_t M = 0;
   bool sorted_by_entity = false;
   for (int attempt = 0;; ++attempt) {
@@ -965,6 +1190,10 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     launches += 1 + prim::exclusive_scan_u32(S.opcnt.as<uint32_t>(), S.opbase.as<uint32_t>(), K, S.partials.as<uint32_t>(), &dc->n_ops, st);
     hrem.assign(nt, 0);
     happ.assign(nt, 0);
+    if (w->builtin_messages) {
+      HG_TRY(bm_count_pass(w, K, &launches));
+      HG_CUDA(w, cudaMemcpyAsync(bm_totals, S.bm_totals.ptr, sizeof(bm_totals), cudaMemcpyDeviceToHost, st));
+    }
     HG_CUDA(w, cudaMemcpyAsync(&hc, dc, sizeof(hc), cudaMemcpyDeviceToHost, st));
     if (nt) {
       HG_CUDA(w, cudaMemcpyAsync(hrem.data(), S.trem.ptr, nt * 4, cudaMemcpyDeviceToHost, st));
@@ -994,6 +1223,7 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     }
   }
   S.ent_first_dirty = false;  // k_reset_first ran to completion
+  if (w->builtin_messages) HG_TRY(bm_scatter_pass(w, cmd, K, bm_totals, hc.touched_add, hc.touched_rem, &launches));
   w->last_stats.invalid = hc.invalid;
   w->last_stats.effective = hc.effective;
   const uint32_t nt = uint32_t(w->tables.size());

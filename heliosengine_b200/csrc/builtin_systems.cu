@@ -136,7 +136,7 @@ struct DetectBody {
     ev.b = r.entity ^ 1ull;  // synthetic partner: the entity with the neighbouring index
     ev.impulse = p.x * 0.0078125f + float(t.id);
     ev.pad = 0;
-    if (r.flat_row == 0) *wr.count = r.n_rows < wr.capacity ? r.n_rows : wr.capacity;
+    if (r.flat_row == 0) *wr.count = r.n_rows;  // the true count: a buffer smaller than that is reported, not hidden
     const unsigned long long slot = r.flat_row;
     if (held_slot != ~0ull) {
       const unsigned long long hs = held_slot;
@@ -249,6 +249,85 @@ int32_t launch_consume_strong(const helios_gpu_system_ctx* ctx) {
   std::memcpy(&p, ctx->params, sizeof(p));
   k_consume_strong<<<ctx->sm_count * 8, 256, 0, static_cast<cudaStream_t>(ctx->stream)>>>(ctx->d_reader, ctx->world_view, p,
                                                                                         ctx->consumed, ctx->consumed_capacity);
+  helios_gpu_world_note_launches(ctx->world, 1);
+  return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
+}
+
+// ---- "emit_multi": Query<const Position&, const Team&> + MessageWriter<CollisionEvent> + MessageWriter<ScoreEvent>: two
+// writer parameters in one system (system/param_traits.hpp:193-240); per visited row two CollisionEvents and one
+// ScoreEvent, written at slots derived from the ForEach position, i.e. in the reference's serial emission order ----------
+struct ScoreEvent {  // 16 B
+  helios_gpu_entity_t who;
+  int32_t points;
+  uint32_t pad;
+};
+struct EmitMultiBody {
+  const helios_gpu_msg_writer* d_w0;
+  const helios_gpu_msg_writer* d_w1;
+  __device__ void operator()(const Row& r, Position& p, Team& t) const {
+    const helios_gpu_msg_writer w0 = *d_w0, w1 = *d_w1;
+    if (r.flat_row == 0) {  // the true counts, whatever the buffers hold: overflow is reported by ApplyDeferred
+      *w0.count = 2ull * r.n_rows;
+      *w1.count = r.n_rows;
+    }
+    CollisionEvent ev;
+    ev.a = r.entity;
+    ev.b = r.entity ^ 1ull;
+    ev.impulse = p.x * 0.0078125f + float(t.id);
+    ev.pad = 0;
+    const unsigned long long s0 = 2ull * r.flat_row;
+    if (s0 < w0.capacity) reinterpret_cast<CollisionEvent*>(w0.data)[s0] = ev;
+    ev.b = r.entity ^ 2ull;
+    ev.impulse = p.y * 0.0078125f;
+    if (s0 + 1 < w0.capacity) reinterpret_cast<CollisionEvent*>(w0.data)[s0 + 1] = ev;
+    if (r.flat_row < w1.capacity) reinterpret_cast<ScoreEvent*>(w1.data)[r.flat_row] = ScoreEvent{r.entity, int32_t(t.id) + 1, 0u};
+  }
+};
+int32_t launch_emit_multi(const helios_gpu_system_ctx* ctx) {
+  if (ctx->n_writers < 2 || ctx->writers[0].elem_size != sizeof(CollisionEvent) || ctx->writers[1].elem_size != sizeof(ScoreEvent))
+    return HELIOS_GPU_ERR_STATE;
+  return for_each_launch<0u, true, EmitMultiBody, Position, Team>(ctx, EmitMultiBody{ctx->d_writers[0], ctx->d_writers[1]});
+}
+
+// ---- "consume_two": MessageReader<CollisionEvent> + MessageReader<ScoreEvent>: Health of evt.a -= int(impulse), Health of
+// score.who += points (integer atomics: independent of the order the events are visited in) ------------------------------
+__device__ __forceinline__ int32_t* health_of(const helios_gpu_world_view& wv, helios_gpu_entity_t e, uint32_t health_slot) {
+  const uint32_t idx = uint32_t(e), gen = uint32_t(e >> 32);
+  if (idx >= wv.entity_capacity || wv.entity_generation[idx] != gen) return nullptr;
+  const uint64_t loc = wv.entity_location[idx];
+  if (loc == 0xFFFFFFFFFFFFFFFFull) return nullptr;
+  int32_t* col = static_cast<int32_t*>(wv.table_columns[(loc >> 32) * 64 + health_slot]);
+  return col ? col + uint32_t(loc) : nullptr;
+}
+__global__ void __launch_bounds__(256) k_consume_two(const helios_gpu_msg_reader* d_ev, const helios_gpu_msg_reader* d_sc,
+                                                     helios_gpu_world_view wv, uint32_t health_slot) {
+  const unsigned long long tid = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  {
+    const helios_gpu_msg_reader rd = *d_ev;
+    const unsigned long long np = *rd.previous_count, n = np + *rd.current_count;
+    for (unsigned long long i = tid; i < n; i += stride) {
+      const CollisionEvent ev = i < np ? reinterpret_cast<const CollisionEvent*>(rd.previous)[i]
+                                       : reinterpret_cast<const CollisionEvent*>(rd.current)[i - np];
+      if (int32_t* hp = health_of(wv, ev.a, health_slot)) atomicSub(hp, int32_t(ev.impulse));
+    }
+  }
+  {
+    const helios_gpu_msg_reader rd = *d_sc;
+    const unsigned long long np = *rd.previous_count, n = np + *rd.current_count;
+    for (unsigned long long i = tid; i < n; i += stride) {
+      const ScoreEvent sc = i < np ? reinterpret_cast<const ScoreEvent*>(rd.previous)[i]
+                                   : reinterpret_cast<const ScoreEvent*>(rd.current)[i - np];
+      if (int32_t* hp = health_of(wv, sc.who, health_slot)) atomicAdd(hp, sc.points);
+    }
+  }
+}
+int32_t launch_consume_two(const helios_gpu_system_ctx* ctx) {
+  if (ctx->params_size < sizeof(ConsumeParams) || ctx->n_readers < 2) return HELIOS_GPU_ERR_STATE;
+  ConsumeParams p;
+  std::memcpy(&p, ctx->params, sizeof(p));
+  k_consume_two<<<ctx->sm_count * 8, 256, 0, static_cast<cudaStream_t>(ctx->stream)>>>(ctx->d_readers[0], ctx->d_readers[1],
+                                                                                     ctx->world_view, p.health_slot);
   helios_gpu_world_note_launches(ctx->world, 1);
   return cudaGetLastError() == cudaSuccess ? HELIOS_GPU_OK : HELIOS_GPU_ERR_CUDA;
 }
@@ -425,6 +504,7 @@ const Entry kBuiltins[] = {
     {"despawn_dead", launch_despawn_dead},
     {"alert_low_health", launch_alert_low_health}, {"heal_alerted", launch_heal_alerted},
     {"apply_gravity", launch_apply_gravity}, {"tick_counter", launch_tick_counter},
+    {"emit_multi", launch_emit_multi}, {"consume_two", launch_consume_two},
 };
 
 }  // namespace

@@ -92,6 +92,15 @@ __host__ __device__ inline helios_gpu_entity_t make_ent(uint32_t i, uint32_t g) 
   return static_cast<uint64_t>(i) | (static_cast<uint64_t>(g) << 32);
 }
 
+// utils/hash.hpp:26-32 FNV-1a-64 (TypeIndex of a spelled type name, utils/type_info.hpp:308-311)
+constexpr uint64_t kFnvBasis = 14695981039346656037ULL;
+constexpr uint64_t kFnvPrime = 1099511628211ULL;
+constexpr uint64_t fnv1a(const char* s) {
+  uint64_t h = kFnvBasis;
+  for (; *s; ++s) h = (h ^ static_cast<uint64_t>(static_cast<unsigned char>(*s))) * kFnvPrime;
+  return h;
+}
+
 inline uint32_t div_up(uint64_t a, uint64_t b) { return static_cast<uint32_t>((a + b - 1) / b); }
 
 }  // namespace hgpu

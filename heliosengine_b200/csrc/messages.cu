@@ -134,6 +134,27 @@ int32_t channel_apply_consumed(helios_gpu_world* w, MsgChannel* ch, const uint32
   return publish_channel(w, ch);
 }
 
+// ---- builtin structural messages (builtin_messages.hpp; written by every structural World call, world.hpp:979-1036,
+// 1124-1196).  The channels are ordinary automatic-policy message types of 8 bytes (the entity). ---------------------------
+int32_t builtin_channel(helios_gpu_world* w, uint64_t hash, MsgChannel** out) {
+  MsgChannel* ch = find_channel(w, hash);
+  if (!ch) {
+    HG_TRY(helios_gpu_message_register(w, hash, 8, HELIOS_GPU_MSG_AUTOMATIC));
+    ch = find_channel(w, hash);
+  }
+  if (ch->size != 8) HG_FAIL(w, HELIOS_GPU_ERR_STATE, "message type %016llx is registered with %u bytes, builtin messages carry 8",
+                             (unsigned long long)hash, ch->size);
+  *out = ch;
+  return HELIOS_GPU_OK;
+}
+
+int32_t builtin_emit_entities(helios_gpu_world* w, uint64_t hash, const helios_gpu_entity_t* d_ents, uint64_t n) {
+  if (!w->builtin_messages) return HELIOS_GPU_OK;
+  MsgChannel* ch = nullptr;
+  HG_TRY(builtin_channel(w, hash, &ch));
+  return channel_append_device(w, ch, d_ents, n);
+}
+
 int32_t messages_update_from_system(helios_gpu_world* w) {
   for (auto& ch : w->channels) {
     if (ch->cur_count == 0) continue;
@@ -148,6 +169,13 @@ int32_t messages_update(helios_gpu_world* w) {
     const bool changed = (ch->policy == HELIOS_GPU_MSG_AUTOMATIC && ch->prev_count) || ch->cur_count;
     if (ch->policy == HELIOS_GPU_MSG_AUTOMATIC) ch->prev_count = 0;  // previous_messages_.Clear(type) manager.hpp:405-410
     HG_TRY(merge_current_into_previous(w, ch.get()));
+    // a bulk load leaves hundreds of MB of builtin messages behind: hand an emptied large buffer back to the pool
+    // (stream-ordered, so kernels already queued on the world's stream still see valid memory)
+    constexpr size_t kKeepBytes = size_t(64) << 20;
+    bool released = false;
+    if (ch->prev_count == 0 && ch->prev.bytes > kKeepBytes) { cudaFreeAsync(ch->prev.ptr, w->stream); ch->prev.ptr = nullptr; ch->prev.bytes = 0; released = true; }
+    if (ch->cur_count == 0 && ch->cur.bytes > kKeepBytes) { cudaFreeAsync(ch->cur.ptr, w->stream); ch->cur.ptr = nullptr; ch->cur.bytes = 0; released = true; }
+    if (released) { ++w->epoch; HG_TRY(publish_channel(w, ch.get())); continue; }
     if (changed) HG_TRY(publish_channel(w, ch.get()));
   }
   return HELIOS_GPU_OK;
@@ -185,6 +213,21 @@ static WorldResource* find_resource(helios_gpu_world* w, uint64_t hash) {
   return nullptr;
 }
 
+// ResourceInsertedMsg<T> / ResourceRemovedMsg<T> (builtin_messages.hpp:198-215): empty structs, so a message is one byte.
+// World::InsertResources & co. register the type first (AddMessage, world.hpp:1232,1241,1302,1310), then write one message
+// when the call took effect.  The template-ids get the same stand-in identity as the component messages.
+static int32_t resource_message(helios_gpu_world* w, const char* tmpl, uint64_t resource_hash, bool write) {
+  if (!w->builtin_messages) return HELIOS_GPU_OK;
+  const uint64_t h = default_component_msg(tmpl, resource_hash);
+  HG_TRY(helios_gpu_message_register(w, h, 1, HELIOS_GPU_MSG_AUTOMATIC));
+  const uint8_t zero = 0;
+  if (write) {
+    HG_TRY(helios_gpu_message_write(w, h, &zero, 1));
+    HG_CUDA(w, cudaStreamSynchronize(w->stream));  // `zero` lives on this frame
+  }
+  return HELIOS_GPU_OK;
+}
+
 int32_t helios_gpu_resource_insert(helios_gpu_world* w, uint64_t hash, const void* value, uint32_t size) {
   if (!w || !value || size == 0 || hash == 0) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   WorldResource* r = find_resource(w, hash);
@@ -201,19 +244,21 @@ int32_t helios_gpu_resource_insert(helios_gpu_world* w, uint64_t hash, const voi
   }
   HG_CUDA(w, cudaMemcpyAsync(r->value.ptr, value, size, cudaMemcpyHostToDevice, w->stream));
   HG_CUDA(w, cudaStreamSynchronize(w->stream));  // `value` is the caller's memory
-  return HELIOS_GPU_OK;
+  return resource_message(w, "helios::ecs::ResourceInsertedMsg", hash, true);  // world.hpp:1230-1237
 }
 
 int32_t helios_gpu_resource_try_insert(helios_gpu_world* w, uint64_t hash, const void* value, uint32_t size, uint32_t* inserted) {
   if (!w) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   const bool present = find_resource(w, hash) != nullptr;  // manager.hpp:83-91: false when the resource exists
   if (inserted) *inserted = present ? 0u : 1u;
-  return present ? HELIOS_GPU_OK : helios_gpu_resource_insert(w, hash, value, size);
+  if (present) return resource_message(w, "helios::ecs::ResourceInsertedMsg", hash, false);  // world.hpp:1241: registered, not written
+  return helios_gpu_resource_insert(w, hash, value, size);
 }
 
 int32_t helios_gpu_resource_try_remove(helios_gpu_world* w, uint64_t hash, uint32_t* removed) {
   if (!w) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   if (removed) *removed = 0;
+  HG_TRY(resource_message(w, "helios::ecs::ResourceRemovedMsg", hash, find_resource(w, hash) != nullptr));  // world.hpp:1308-1320
   for (size_t i = 0; i < w->resources.size(); ++i)
     if (w->resources[i]->hash == hash) {
       HG_CUDA(w, cudaStreamSynchronize(w->stream));  // kernels that hold the address have finished
@@ -226,10 +271,10 @@ int32_t helios_gpu_resource_try_remove(helios_gpu_world* w, uint64_t hash, uint3
 }
 
 int32_t helios_gpu_resource_remove(helios_gpu_world* w, uint64_t hash) {
+  if (!w) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (!find_resource(w, hash)) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "resource does not exist");  // world.hpp:1278-1300 HELIOS_ASSERT
   uint32_t removed = 0;
-  HG_TRY(helios_gpu_resource_try_remove(w, hash, &removed));
-  if (!removed) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "resource does not exist");  // manager.hpp:112-116 HELIOS_ASSERT
-  return HELIOS_GPU_OK;
+  return helios_gpu_resource_try_remove(w, hash, &removed);
 }
 
 int32_t helios_gpu_resource_has(helios_gpu_world* w, uint64_t hash, uint32_t* out) {
@@ -381,6 +426,45 @@ int32_t helios_gpu_message_register(helios_gpu_world* w, uint64_t hash, uint32_t
   w->channel_of.emplace(hash, int(w->channels.size()));
   w->channels.push_back(std::move(ch));
   return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_message_types(helios_gpu_world* w, uint64_t* hashes, uint32_t* sizes, uint32_t capacity, uint32_t* count) {
+  if (!w || !count) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  *count = uint32_t(w->channels.size());
+  if (!hashes && !sizes) return HELIOS_GPU_OK;
+  if (capacity < w->channels.size()) return HELIOS_GPU_ERR_CAPACITY;
+  for (size_t i = 0; i < w->channels.size(); ++i) {
+    if (hashes) hashes[i] = w->channels[i]->hash;
+    if (sizes) sizes[i] = w->channels[i]->size;
+  }
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_component_message_types(helios_gpu_world* w, uint64_t component_hash, uint64_t added_hash, uint64_t removed_hash) {
+  if (!w || !added_hash || !removed_hash) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  const auto it = w->slot_of.find(component_hash);
+  if (it == w->slot_of.end()) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "component %016llx not registered", (unsigned long long)component_hash);
+  w->comps[size_t(it->second)].added_msg = added_hash;
+  w->comps[size_t(it->second)].removed_msg = removed_hash;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_builtin_message_type(helios_gpu_world* w, uint32_t kind, uint64_t component_hash, uint64_t* out) {
+  if (!w || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  switch (kind) {
+    case HELIOS_GPU_BUILTIN_ENTITY_ADDED: *out = kMsgEntityAdded; return HELIOS_GPU_OK;
+    case HELIOS_GPU_BUILTIN_ENTITY_DESTROYED: *out = kMsgEntityDestroyed; return HELIOS_GPU_OK;
+    case HELIOS_GPU_BUILTIN_COMPONENTS_CLEARED: *out = kMsgComponentsCleared; return HELIOS_GPU_OK;
+    case HELIOS_GPU_BUILTIN_COMPONENT_ADDED:
+    case HELIOS_GPU_BUILTIN_COMPONENT_REMOVED: {
+      const auto it = w->slot_of.find(component_hash);
+      if (it == w->slot_of.end()) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "component %016llx not registered", (unsigned long long)component_hash);
+      const Component& c = w->comps[size_t(it->second)];
+      *out = kind == HELIOS_GPU_BUILTIN_COMPONENT_ADDED ? c.added_msg : c.removed_msg;
+      return HELIOS_GPU_OK;
+    }
+    default: return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  }
 }
 
 int32_t helios_gpu_message_write(helios_gpu_world* w, uint64_t hash, const void* data, uint64_t n) {

@@ -59,18 +59,22 @@ struct SysEntry {
   DevBuf cmd_records, cmd_payload;
   uint64_t cmd_capacity = 0;       // record slots allocated
   uint64_t cmd_slots_in_use = 0;   // slots armed for the current run
-  DevBuf msg_data;                 // local message buffer
-  uint64_t msg_capacity = 0;
-  DevBuf d_writer;                 // struct { helios_gpu_msg_writer wr; unsigned long long count; }
+  // one local message buffer per MessageWriter<T> parameter (SystemLocalData::message_queue holds a buffer per type)
+  struct LocalWriter {
+    uint64_t hash = 0, hint = 0;   // message type; writer_capacity of the descriptor (0 = one message per matched row)
+    DevBuf data;
+    uint64_t capacity = 0;         // messages the buffer holds
+    uint64_t grown_to = 0;         // count observed by a run that overflowed: the next run is sized for it
+    DevBuf d_view;                 // helios_gpu_msg_writer: stable device address for captured graphs
+  };
+  LocalWriter writers[HELIOS_GPU_MAX_SYSTEM_MESSAGES];
+  uint32_t n_writers = 0;
+  uint64_t readers[HELIOS_GPU_MAX_SYSTEM_MESSAGES] = {};
+  uint32_t n_readers = 0;
   DevBuf consumed;                 // u32 flag per global reader index (ConsumedMessagesRegistry of this system)
   uint64_t consumed_capacity = 0;  // flags allocated
   uint64_t consumed_armed = 0;     // flags zeroed for the current run = reader view size at launch
   int stream_id = 0;
-};
-
-struct WriterDev {
-  helios_gpu_msg_writer wr;
-  unsigned long long count;
 };
 
 }  // namespace
@@ -85,6 +89,7 @@ struct helios_gpu_schedule {
   bool built = false;
   DevBuf resources;
   DevBuf verdicts;                                       // u32 per registration index: 1 = ran, 0 = skipped
+  DevBuf writer_counts;                                  // u64[system * MAX_SYSTEM_MESSAGES + writer]: messages written this run
   std::map<uint64_t, std::vector<std::unique_ptr<CondEntry>>> set_conds;  // SystemSet::RunIf
   cudaStream_t body_stream = nullptr;                    // captures IF bodies
   bool any_conditions = false;
@@ -111,16 +116,19 @@ uint64_t host_match_rows(helios_gpu_world* w, const helios_gpu_query* q) {
   return n;
 }
 
-int32_t publish_writer(helios_gpu_world* w, SysEntry& e, MsgChannel* ch) {
-  WriterDev d{};
-  auto* dev = e.d_writer.as<WriterDev>();
-  d.wr.data = e.msg_data.as<uint8_t>();
-  d.wr.count = &dev->count;
-  d.wr.capacity = e.msg_capacity;
-  d.wr.elem_size = ch->size;
-  d.count = 0;
-  HG_CUDA(w, cudaMemcpyAsync(dev, &d, sizeof(d), cudaMemcpyHostToDevice, w->stream));
-  return HELIOS_GPU_OK;
+constexpr uint32_t kMaxSystems = 64;
+
+unsigned long long* writer_counter(helios_gpu_schedule* s, uint32_t system, uint32_t writer) {
+  return s->writer_counts.as<unsigned long long>() + size_t(system) * HELIOS_GPU_MAX_SYSTEM_MESSAGES + writer;
+}
+
+helios_gpu_msg_writer writer_view(helios_gpu_schedule* s, uint32_t system, uint32_t k, const SysEntry::LocalWriter& lw, uint32_t elem) {
+  helios_gpu_msg_writer v{};
+  v.data = lw.data.as<uint8_t>();
+  v.count = writer_counter(s, system, k);
+  v.capacity = lw.capacity;
+  v.elem_size = elem;
+  return v;
 }
 
 // Host-side preparation before a run: buffer sizing only (no launches), so that the launch pass can be captured.
@@ -158,6 +166,7 @@ int32_t prepare(helios_gpu_schedule* s) {
   // every system starts a run as "ran"; a guarded system's condition chain overwrites its word (a schedule without
   // conditions pays nothing: no buffer, no memset in front of its first system)
   if (s->any_conditions) HG_CUDA(w, cudaMemsetAsync(s->verdicts.ptr, 0x01, 64 * sizeof(uint32_t), w->stream));
+  bool any_writer = false;
   for (auto& ep : s->entries) {
     SysEntry& e = *ep;
     const uint64_t rows = host_match_rows(w, e.desc.query);
@@ -179,19 +188,26 @@ int32_t prepare(helios_gpu_schedule* s) {
       if (slots != e.cmd_slots_in_use) ++w->epoch;  // memset extent is baked into a captured graph
       e.cmd_slots_in_use = slots;
     }
-    if (e.desc.writes_message) {
-      MsgChannel* ch = find_channel(w, e.desc.writes_message);
+    for (uint32_t k = 0; k < e.n_writers; ++k) {
+      SysEntry::LocalWriter& lw = e.writers[k];
+      MsgChannel* ch = find_channel(w, lw.hash);
       if (!ch) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "system '%s' writes an unregistered message type", e.name.c_str());
-      const uint64_t want = e.desc.writer_capacity ? e.desc.writer_capacity : rows;
-      if (!e.d_writer.ptr) HG_CUDA(w, e.d_writer.reserve(sizeof(WriterDev), 0, w->stream, false));
-      if (want * ch->size > e.msg_data.bytes || e.msg_capacity < want) {
-        HG_CUDA(w, e.msg_data.reserve((want + want / 4 + 256) * ch->size, 0, w->stream, false));
+      if (!s->writer_counts.ptr) {
+        HG_CUDA(w, s->writer_counts.reserve(size_t(kMaxSystems) * HELIOS_GPU_MAX_SYSTEM_MESSAGES * 8, 0, w->stream, false));
+        ++w->epoch;
       }
-      e.msg_capacity = e.msg_data.bytes / ch->size;
-      HG_TRY(publish_writer(w, e, ch));  // also zeroes the counter
+      const uint64_t want = std::max<uint64_t>(lw.hint ? lw.hint : rows, lw.grown_to);
+      if (!lw.d_view.ptr) HG_CUDA(w, lw.d_view.reserve(sizeof(helios_gpu_msg_writer), 0, w->stream, false));
+      if (want * ch->size > lw.data.bytes || lw.capacity < want)
+        HG_CUDA(w, lw.data.reserve((want + want / 4 + 256) * ch->size, 0, w->stream, false));
+      lw.capacity = lw.data.bytes / ch->size;
+      const helios_gpu_msg_writer v = writer_view(s, uint32_t(&ep - &s->entries[0]), k, lw, ch->size);
+      HG_CUDA(w, cudaMemcpyAsync(lw.d_view.ptr, &v, sizeof(v), cudaMemcpyHostToDevice, w->stream));
+      any_writer = true;
     }
-    if (e.desc.reads_message && !find_channel(w, e.desc.reads_message))
-      HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "system '%s' reads an unregistered message type", e.name.c_str());
+    for (uint32_t k = 0; k < e.n_readers; ++k)
+      if (!find_channel(w, e.readers[k]))
+        HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "system '%s' reads an unregistered message type", e.name.c_str());
     if ((e.desc.flags & HELIOS_GPU_SYSTEM_CONSUMES_MESSAGES) && e.desc.reads_message) {
       const MsgChannel* ch = find_channel(w, e.desc.reads_message);
       const uint64_t view = ch->prev_count + ch->cur_count;  // merges only happen in ApplyDeferred: exact for this run
@@ -205,6 +221,8 @@ int32_t prepare(helios_gpu_schedule* s) {
       e.consumed_armed = view;
     }
   }
+  if (any_writer)  // every writer starts the run empty
+    HG_CUDA(w, cudaMemsetAsync(s->writer_counts.ptr, 0, size_t(kMaxSystems) * HELIOS_GPU_MAX_SYSTEM_MESSAGES * 8, w->stream));
   return HELIOS_GPU_OK;
 }
 
@@ -249,25 +267,25 @@ int32_t launch_body(helios_gpu_schedule* s, SysEntry& e, uint32_t index, cudaStr
     ctx.commands.payload_stride = e.desc.cmd_payload_stride;
     ctx.commands.slots_per_row = std::max<uint32_t>(1u, e.desc.cmd_slots_per_row);
   }
-  if (e.desc.writes_message) {
-    MsgChannel* ch = find_channel(w, e.desc.writes_message);
-    auto* dev = e.d_writer.as<WriterDev>();
-    ctx.writer.data = e.msg_data.as<uint8_t>();
-    ctx.writer.count = &dev->count;
-    ctx.writer.capacity = e.msg_capacity;
-    ctx.writer.elem_size = ch->size;
-    ctx.d_writer = &dev->wr;
+  ctx.n_writers = e.n_writers;
+  for (uint32_t k = 0; k < e.n_writers; ++k) {
+    MsgChannel* ch = find_channel(w, e.writers[k].hash);
+    ctx.writers[k] = writer_view(s, index, k, e.writers[k], ch->size);
+    ctx.d_writers[k] = e.writers[k].d_view.as<helios_gpu_msg_writer>();
   }
-  if (e.desc.reads_message) {
-    MsgChannel* ch = find_channel(w, e.desc.reads_message);
+  ctx.n_readers = e.n_readers;
+  for (uint32_t k = 0; k < e.n_readers; ++k) {
+    MsgChannel* ch = find_channel(w, e.readers[k]);
     auto* dev = ch->d_dev.as<ChannelDev>();
-    ctx.reader.previous = ch->prev.as<uint8_t>();
-    ctx.reader.current = ch->cur.as<uint8_t>();
-    ctx.reader.previous_count = &dev->counts[0];
-    ctx.reader.current_count = &dev->counts[1];
-    ctx.reader.elem_size = ch->size;
-    ctx.d_reader = &dev->rd;
+    ctx.readers[k].previous = ch->prev.as<uint8_t>();
+    ctx.readers[k].current = ch->cur.as<uint8_t>();
+    ctx.readers[k].previous_count = &dev->counts[0];
+    ctx.readers[k].current_count = &dev->counts[1];
+    ctx.readers[k].elem_size = ch->size;
+    ctx.d_readers[k] = &dev->rd;
   }
+  if (e.n_writers) { ctx.writer = ctx.writers[0]; ctx.d_writer = ctx.d_writers[0]; }
+  if (e.n_readers) { ctx.reader = ctx.readers[0]; ctx.d_reader = ctx.d_readers[0]; }
   if (!e.policy.wc.empty()) ++w->mutation_epoch;  // the body may write component columns
   const int32_t st = e.desc.launch(&ctx);
   if (st != HELIOS_GPU_OK) HG_FAIL(w, st, "system '%s' failed to launch (%d): %s", e.name.c_str(), st,
@@ -574,6 +592,10 @@ int32_t helios_gpu_schedule_add_system(helios_gpu_schedule* s, const helios_gpu_
   helios_gpu_world* w = s->world;
   if (d->n_extra_read_components > 8 || d->n_extra_write_components > 8 || d->n_read_resources > 8 || d->n_write_resources > 8)
     HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "access lists hold at most 8 entries");
+  if (d->n_more_writes > HELIOS_GPU_MAX_SYSTEM_MESSAGES - 1 || d->n_more_reads > HELIOS_GPU_MAX_SYSTEM_MESSAGES - 1 ||
+      (d->n_more_writes && !d->writes_message) || (d->n_more_reads && !d->reads_message))
+    HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "a system takes at most %d message writers and %d readers (slot 0 first)",
+            HELIOS_GPU_MAX_SYSTEM_MESSAGES, HELIOS_GPU_MAX_SYSTEM_MESSAGES);
   if (s->entries.size() >= 64) HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "a schedule holds at most 64 systems (conflict bitmask, schedule.cpp:367)");
   auto e = std::make_unique<SysEntry>();
   e->name = d->name ? d->name : "";
@@ -581,6 +603,20 @@ int32_t helios_gpu_schedule_add_system(helios_gpu_schedule* s, const helios_gpu_
   e->desc.name = nullptr;
   if (d->params && d->params_size) e->params.assign(static_cast<const uint8_t*>(d->params), static_cast<const uint8_t*>(d->params) + d->params_size);
   e->desc.params = nullptr;
+  if (d->writes_message) {
+    e->writers[e->n_writers].hint = d->writer_capacity;
+    e->writers[e->n_writers++].hash = d->writes_message;
+    for (uint32_t k = 0; k < d->n_more_writes; ++k) {
+      for (uint32_t j = 0; j < e->n_writers; ++j)
+        if (e->writers[j].hash == d->more_writes[k]) HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "a message type is written twice by system '%s'", e->name.c_str());
+      e->writers[e->n_writers].hint = d->more_writer_capacity[k];
+      e->writers[e->n_writers++].hash = d->more_writes[k];
+    }
+  }
+  if (d->reads_message) {
+    e->readers[e->n_readers++] = d->reads_message;
+    for (uint32_t k = 0; k < d->n_more_reads; ++k) e->readers[e->n_readers++] = d->more_reads[k];
+  }
   // SystemParamTraits<Query>::RegisterAccess (system/param_traits.hpp:55-60): mutable → write set, const → read set.
   if (d->query) {
     for (uint32_t k = 0; k < d->query->desc.n_components; ++k)
@@ -782,7 +818,14 @@ int32_t helios_gpu_schedule_run(helios_gpu_schedule* s, uint32_t mode) {
 int32_t helios_gpu_schedule_apply_deferred(helios_gpu_schedule* s) {
   if (!s) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   helios_gpu_world* w = s->world;
-  HG_CUDA(w, cudaStreamSynchronize(w->stream));  // Executor::Wait — secondary streams are already joined into it
+  // Executor::Wait — secondary streams are already joined into the primary one.  Every writer's message count of this run
+  // comes back with that one synchronisation (the reference reads SystemLocalData::message_queue sizes on the host).
+  unsigned long long wcounts[kMaxSystems * HELIOS_GPU_MAX_SYSTEM_MESSAGES];
+  if (s->pending && s->writer_counts.ptr)
+    HG_CUDA(w, cudaMemcpyAsync(wcounts, s->writer_counts.ptr, s->entries.size() * HELIOS_GPU_MAX_SYSTEM_MESSAGES * 8,
+                               cudaMemcpyDeviceToHost, w->stream));
+  HG_CUDA(w, cudaStreamSynchronize(w->stream));
+  std::string overflow;
   HG_TRY(helios_gpu_world_flush(w));              // schedule.cpp:111 world.Flush()
   for (auto& ep : s->entries) {                   // schedule.cpp:112-114 REGISTRATION order
     SysEntry& e = *ep;
@@ -794,17 +837,25 @@ int32_t helios_gpu_schedule_apply_deferred(helios_gpu_schedule* s) {
     if ((e.desc.flags & HELIOS_GPU_SYSTEM_CONSUMES_MESSAGES) && e.consumed_armed && s->pending)
       HG_TRY(channel_apply_consumed(w, find_channel(w, e.desc.reads_message), e.consumed.as<uint32_t>(), e.consumed_armed));
     HG_TRY(messages_update_from_system(w));
-    if (e.desc.writes_message && s->pending) {
-      MsgChannel* ch = find_channel(w, e.desc.writes_message);
-      unsigned long long cnt = 0;
-      HG_CUDA(w, cudaMemcpyAsync(&cnt, &e.d_writer.as<WriterDev>()->count, 8, cudaMemcpyDeviceToHost, w->stream));
-      HG_CUDA(w, cudaStreamSynchronize(w->stream));
-      const uint64_t n = std::min<uint64_t>(cnt, e.msg_capacity);
-      HG_TRY(channel_merge_local(w, ch, e.msg_data, n));
-      e.msg_capacity = ch->size ? e.msg_data.bytes / ch->size : 0;
+    for (uint32_t k = 0; k < e.n_writers && s->pending; ++k) {
+      SysEntry::LocalWriter& lw = e.writers[k];
+      MsgChannel* ch = find_channel(w, lw.hash);
+      const unsigned long long cnt = wcounts[size_t(&ep - &s->entries[0]) * HELIOS_GPU_MAX_SYSTEM_MESSAGES + k];
+      if (cnt > lw.capacity) {  // never silent: the messages past the buffer are lost, say so and size the next run for them
+        char buf[256];
+        std::snprintf(buf, sizeof buf, "%ssystem '%s' wrote %llu messages of type %016llx into a writer of capacity %llu",
+                      overflow.empty() ? "" : "; ", e.name.c_str(), cnt, (unsigned long long)lw.hash, (unsigned long long)lw.capacity);
+        overflow += buf;
+        lw.grown_to = cnt;
+      }
+      const uint64_t n = std::min<uint64_t>(cnt, lw.capacity);
+      HG_TRY(channel_merge_local(w, ch, lw.data, n));
+      lw.capacity = ch->size ? lw.data.bytes / ch->size : 0;  // the buffers may have been swapped; prepare() republishes the view
     }
   }
   s->pending = false;
+  if (!overflow.empty())
+    HG_FAIL(w, HELIOS_GPU_ERR_CAPACITY, "%s: the excess was dropped; set writer_capacity (the next run is sized for this count)", overflow.c_str());
   return HELIOS_GPU_OK;
 }
 

@@ -342,6 +342,8 @@ int32_t helios_gpu_register_sparse_component(helios_gpu_world* w, uint64_t hash,
   c.size = size;
   c.align = align ? align : 1;
   c.def.assign(size, 0);
+  c.added_msg = default_component_msg("helios::ecs::ComponentAddedMsg", hash);
+  c.removed_msg = default_component_msg("helios::ecs::ComponentRemovedMsg", hash);
   const int slot = static_cast<int>(w->comps.size());
   if (w->sparse.empty()) {  // first sparse type: the membership words appear
     HG_CUDA(w, w->d_membership.reserve(size_t(w->ent_capacity) * 4, 0, st, false));

@@ -169,6 +169,11 @@ int32_t helios_gpu_world_create(const helios_gpu_world_config* cfg, helios_gpu_w
   HG_CUDA(w, w->d_csize.reserve(64 * 4, 0, w->stream, false));
   HG_CUDA(w, cudaMemsetAsync(w->d_csize.ptr, 0, 64 * 4, w->stream));
   HG_TRY(ensure_entity_capacity(w, cfg && cfg->entity_capacity ? cfg->entity_capacity : 1024));
+  // World() { AddBuiltinMessages(); } (world.hpp:42,1343-1347)
+  w->builtin_messages = !(cfg && (cfg->flags & HELIOS_GPU_WORLD_NO_BUILTIN_MESSAGES));
+  HG_TRY(helios_gpu_message_register(w, kMsgEntityAdded, 8, HELIOS_GPU_MSG_AUTOMATIC));
+  HG_TRY(helios_gpu_message_register(w, kMsgEntityDestroyed, 8, HELIOS_GPU_MSG_AUTOMATIC));
+  HG_TRY(helios_gpu_message_register(w, kMsgComponentsCleared, 8, HELIOS_GPU_MSG_AUTOMATIC));
   return HELIOS_GPU_OK;
 }
 
@@ -225,6 +230,8 @@ int32_t helios_gpu_register_component(helios_gpu_world* w, uint64_t hash, uint32
   c.align = align ? align : 1;
   c.def.assign(size, 0);
   if (def) std::memcpy(c.def.data(), def, size);
+  c.added_msg = default_component_msg("helios::ecs::ComponentAddedMsg", hash);
+  c.removed_msg = default_component_msg("helios::ecs::ComponentRemovedMsg", hash);
   const int slot = static_cast<int>(w->comps.size());
   w->comps.push_back(std::move(c));
   w->slot_of.emplace(hash, slot);
@@ -370,7 +377,10 @@ int32_t helios_gpu_create_entities(helios_gpu_world* w, uint32_t n, helios_gpu_e
   uint32_t base;
   uint64_t fresh;
   HG_TRY(allocate_ids(w, n, rec, &base, &fresh));
+  const uint64_t row0 = w->tables[size_t(w->empty_table)].count;
   HG_TRY(place(w, w->empty_table, rec, base, fresh, out));
+  // messages_.Write(EntityAddedMsg(entity)) (world.hpp:982): the new ids are the rows just placed
+  HG_TRY(builtin_emit_entities(w, kMsgEntityAdded, w->tables[size_t(w->empty_table)].entities.as<helios_gpu_entity_t>() + row0, n));
   w->flushed_index = w->next_index;
   ++w->mutation_epoch;
   return HELIOS_GPU_OK;
@@ -411,6 +421,11 @@ int32_t helios_gpu_spawn_batch(helios_gpu_world* w, const uint64_t* hashes, uint
     HG_CUDA(w, cudaMemcpyAsync(static_cast<uint8_t*>(tb.cols[ci].ptr) + row0 * sz, columns[k], n * sz,
                                cudaMemcpyHostToDevice, w->stream));
   }
+  // per entity: EntityAddedMsg (CreateEntity, world.hpp:982) and one ComponentAddedMsg<T> per type (AddComponents, :1035);
+  // each message type is its own queue, so per type this is the new ids in row order
+  const helios_gpu_entity_t* new_ids = tb.entities.as<helios_gpu_entity_t>() + row0;
+  HG_TRY(builtin_emit_entities(w, kMsgEntityAdded, new_ids, n));
+  for (uint32_t k = 0; k < ntypes; ++k) HG_TRY(builtin_emit_entities(w, w->comps[size_t(slots[k])].added_msg, new_ids, n));
   w->flushed_index = w->next_index;
   ++w->mutation_epoch;
   HG_CUDA(w, cudaStreamSynchronize(w->stream));
@@ -515,6 +530,11 @@ int32_t helios_gpu_extract_query(helios_gpu_query* src, helios_gpu_world* dst, u
     k_extract_rows<<<uint32_t(dst->sm_count) * 8, 256, 0, dst->stream>>>(ea);
     ++dst->launches;
     HG_CUDA(dst, cudaGetLastError());
+  }
+  {  // the destination's CreateEntity + AddComponents per row write their builtin messages there (world.hpp:982,1035)
+    const helios_gpu_entity_t* new_ids = dt.entities.as<helios_gpu_entity_t>() + row;
+    HG_TRY(builtin_emit_entities(dst, kMsgEntityAdded, new_ids, n));
+    for (uint32_t k = 0; k < nc; ++k) HG_TRY(builtin_emit_entities(dst, dst->comps[size_t(dslot[k])].added_msg, new_ids, n));
   }
   // ... and whatever the source world does next waits for them (a system may overwrite the columns in the next frame)
   HG_CUDA(dst, cudaEventRecord(ev, dst->stream));

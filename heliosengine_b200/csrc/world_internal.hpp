@@ -24,7 +24,17 @@ struct Component {
   uint32_t size = 0;
   uint32_t align = 1;
   std::vector<uint8_t> def;  // default-constructed value
+  uint64_t added_msg = 0;    // TypeIndex of ComponentAddedMsg<T> / ComponentRemovedMsg<T> (builtin_messages.hpp:86,124)
+  uint64_t removed_msg = 0;
 };
+
+// Builtin structural messages (builtin_messages.hpp:14,48,161): the non-template ones are the FNV-1a of their qualified names.
+constexpr uint64_t kMsgEntityAdded = fnv1a("helios::ecs::EntityAddedMsg");
+constexpr uint64_t kMsgEntityDestroyed = fnv1a("helios::ecs::EntityDestroyedMsg");
+constexpr uint64_t kMsgComponentsCleared = fnv1a("helios::ecs::ComponentsClearedMsg");
+// ComponentAddedMsg<T> / ComponentRemovedMsg<T>: the spelling of T inside the template-id is the host compiler's business
+// (helios_gpu_component_message_types tells the library); this stand-in is used until then (same formula in the oracle).
+constexpr uint64_t default_component_msg(const char* tmpl, uint64_t comp) { return fnv1a(tmpl) ^ (comp * kFnvPrime); }
 
 struct Table {
   uint64_t mask = 0;
@@ -106,6 +116,7 @@ struct helios_gpu_world {
   uint64_t launches = 0;
   uint64_t mutation_epoch = 0; // bumped by anything that may write component columns or move rows (systems with a write
                                // set, commands, column uploads, spawns): lets a system keep a validated cache of columns
+  bool builtin_messages = true; // every structural call also writes its builtin message (world.hpp:979-1036,1124-1196)
   uint64_t epoch = 0;          // bumped whenever a device pointer or directory size a captured graph bakes in changes
 
   std::vector<hgpu::Component> comps;
@@ -197,4 +208,9 @@ int32_t channel_merge_local(helios_gpu_world* w, MsgChannel* ch, DevBuf& local, 
 // MessageManager::ApplyConsumed (manager.hpp:421-496): flags[i] != 0 removes position i of previous ++ current.
 int32_t channel_apply_consumed(helios_gpu_world* w, MsgChannel* ch, const uint32_t* d_flags, uint64_t n_flags);
 int32_t publish_channel(helios_gpu_world* w, MsgChannel* ch);
+// Builtin structural messages: find-or-register the 8-byte automatic channel `hash` (World::AddMessage is idempotent).
+int32_t builtin_channel(helios_gpu_world* w, uint64_t hash, MsgChannel** out);
+// messages_.Write(Msg(entity)) for n entities already in HBM (EntityAddedMsg of CreateEntity, ComponentAddedMsg<T> of the
+// bulk loaders); no-op when the world runs without builtin messages.
+int32_t builtin_emit_entities(helios_gpu_world* w, uint64_t hash, const helios_gpu_entity_t* d_ents, uint64_t n);
 }  // namespace hgpu

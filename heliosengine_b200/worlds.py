@@ -231,6 +231,11 @@ def snapshot_digest(snap: dict) -> str:
             h.update(np.ascontiguousarray(a["columns"][t]).tobytes())
     h.update(np.ascontiguousarray(snap["generations"]).tobytes())
     h.update(np.ascontiguousarray(snap["free_indices"]).tobytes())
+    for t in sorted(snap.get("messages", {})):  # every message queue, the builtin structural messages included
+        prev, cur = snap["messages"][t]
+        h.update(struct.pack("<QQQ", t, prev.size, cur.size))
+        h.update(np.ascontiguousarray(prev).tobytes())
+        h.update(np.ascontiguousarray(cur).tobytes())
     return h.hexdigest()
 
 
@@ -256,4 +261,11 @@ def snapshots_equal(a: dict, b: dict, float_cols: dict | None = None) -> list[st
     for key in ("generations", "free_indices"):
         if a[key].shape != b[key].shape or not np.array_equal(a[key], b[key]):
             diffs.append(f"{key} differ")
+    ma, mb = a.get("messages", {}), b.get("messages", {})
+    if sorted(ma) != sorted(mb):
+        diffs.append(f"registered message types differ: {sorted(f'{t:016x}' for t in set(ma) ^ set(mb))}")
+    for t in sorted(set(ma) & set(mb)):
+        for which, (x, y) in enumerate(zip(ma[t], mb[t])):
+            if x.shape != y.shape or not np.array_equal(x, y):
+                diffs.append(f"message {t:016x} {'current' if which else 'previous'} queue differs ({x.size} vs {y.size} bytes)")
     return diffs

@@ -82,6 +82,53 @@ private:
   GenerationType generation_ = kInvalidGeneration;
 };
 
+// ---- builtin structural messages (builtin_messages.hpp:14-195): written by every structural World call; the library emits
+// them on the device (helios_gpu.h "builtin structural messages").  Read them like any message: world.ReadMessages<
+// EntityDestroyedMsg>() or a MessageReader system.  The payload is the entity. -------------------------------------------
+class EntityAddedMsg {
+public:
+  explicit constexpr EntityAddedMsg(Entity entity) noexcept : entity_(entity) {}
+  constexpr EntityAddedMsg() noexcept = default;  // std::vector<M> of the shim's ReadMessages needs it
+  [[nodiscard]] constexpr Entity GetEntity() const noexcept { return entity_; }
+private:
+  Entity entity_;
+};
+class EntityDestroyedMsg {
+public:
+  explicit constexpr EntityDestroyedMsg(Entity entity) noexcept : entity_(entity) {}
+  constexpr EntityDestroyedMsg() noexcept = default;
+  [[nodiscard]] constexpr Entity GetEntity() const noexcept { return entity_; }
+private:
+  Entity entity_;
+};
+template <typename T>
+class ComponentAddedMsg {
+public:
+  explicit constexpr ComponentAddedMsg(Entity entity) noexcept : entity_(entity) {}
+  constexpr ComponentAddedMsg() noexcept = default;
+  [[nodiscard]] constexpr Entity GetEntity() const noexcept { return entity_; }
+private:
+  Entity entity_;
+};
+template <typename T>
+class ComponentRemovedMsg {
+public:
+  explicit constexpr ComponentRemovedMsg(Entity entity) noexcept : entity_(entity) {}
+  constexpr ComponentRemovedMsg() noexcept = default;
+  [[nodiscard]] constexpr Entity GetEntity() const noexcept { return entity_; }
+private:
+  Entity entity_;
+};
+class ComponentsClearedMsg {
+public:
+  explicit constexpr ComponentsClearedMsg(Entity entity) noexcept : entity_(entity) {}
+  constexpr ComponentsClearedMsg() noexcept = default;
+  [[nodiscard]] constexpr Entity GetEntity() const noexcept { return entity_; }
+private:
+  Entity entity_;
+};
+static_assert(sizeof(EntityAddedMsg) == 8 && sizeof(ComponentAddedMsg<int>) == 8, "builtin messages carry the 8-byte entity");
+
 // ---- component storage rule (component/component.hpp:60-129): `static constexpr auto kStorageType = ...` on the type wins;
 // otherwise empty "tag" structs are sparse-set stored and everything else lives in archetype tables --------------------
 enum class ComponentStorageType : uint8_t { kArchetype = 0, kSparseSet = 1 };
@@ -259,6 +306,9 @@ public:
       slot = helios_gpu_register_component(w_, TypeIndexOf<T>(), sizeof(T), alignof(T), &def);
     }
     if (slot < 0) Check(slot);
+    // the library cannot spell ComponentAddedMsg<T>: tell it the TypeIndex of both template-ids (utils/type_info.hpp:206-226)
+    Check(helios_gpu_component_message_types(w_, TypeIndexOf<T>(), TypeIndexOf<ComponentAddedMsg<T>>(),
+                                             TypeIndexOf<ComponentRemovedMsg<T>>()));
     return slot;
   }
 
@@ -648,6 +698,10 @@ struct GpuSystemOptions {
   uint64_t writes_message = 0;      // MessageWriter<M>: TypeIndexOf<M>()
   uint64_t reads_message = 0;       // MessageReader<M>
   uint64_t writer_capacity = 0;
+  // further MessageWriter<M> / MessageReader<M> parameters (system/param_traits.hpp:193-240 allow any number):
+  // {TypeIndexOf<M>(), writer capacity} and TypeIndexOf<M>() — writers / readers 1.. of helios_gpu_system_ctx
+  std::vector<std::pair<uint64_t, uint64_t>> more_writes;
+  std::vector<uint64_t> more_reads;
   std::vector<uint64_t> extra_reads, extra_writes;        // World::Get<T>(entity) style access outside the query
   std::vector<uint64_t> read_resources, write_resources;  // Res<T> / ResMut<T>
 };
@@ -854,6 +908,15 @@ private:
     d.cmd_payload_stride = o.cmd_payload_stride;
     d.writes_message = o.writes_message;
     d.reads_message = o.reads_message;
+    if (o.more_writes.size() > HELIOS_GPU_MAX_SYSTEM_MESSAGES - 1 || o.more_reads.size() > HELIOS_GPU_MAX_SYSTEM_MESSAGES - 1)
+      throw GpuError(HELIOS_GPU_ERR_INVALID_ARGUMENT, "a GPU system takes at most 4 message writers and 4 readers");
+    d.n_more_writes = uint32_t(o.more_writes.size());
+    for (size_t i = 0; i < o.more_writes.size(); ++i) {
+      d.more_writes[i] = o.more_writes[i].first;
+      d.more_writer_capacity[i] = o.more_writes[i].second;
+    }
+    d.n_more_reads = uint32_t(o.more_reads.size());
+    for (size_t i = 0; i < o.more_reads.size(); ++i) d.more_reads[i] = o.more_reads[i];
     d.writer_capacity = o.writer_capacity;
     auto fill = [](const std::vector<uint64_t>& src, uint64_t* dst, uint32_t& n) {
       n = uint32_t(src.size() < 8 ? src.size() : 8);

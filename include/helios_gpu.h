@@ -58,6 +58,10 @@ typedef struct helios_gpu_world_config {
   uint32_t flags;             /* HELIOS_GPU_WORLD_* */
 } helios_gpu_world_config;
 #define HELIOS_GPU_WORLD_DEFAULT 0u
+/* Throughput mode: structural calls do NOT write their builtin messages (EntityAddedMsg, EntityDestroyedMsg,
+ * ComponentAddedMsg<T>, ComponentRemovedMsg<T>, ComponentsClearedMsg).  The reference always writes them
+ * (world.hpp:979-1036,1124-1196); the default here does too.  A stated deviation for callers that never read them. */
+#define HELIOS_GPU_WORLD_NO_BUILTIN_MESSAGES 1u
 
 /* ---- world lifetime (replaces World ctor/dtor, world.hpp:80-130) ------------------------------ */
 HELIOS_GPU_API int32_t helios_gpu_world_create(const helios_gpu_world_config* cfg, helios_gpu_world** out);
@@ -267,6 +271,37 @@ HELIOS_GPU_API int32_t helios_gpu_message_register(helios_gpu_world* w, uint64_t
 HELIOS_GPU_API int32_t helios_gpu_message_write(helios_gpu_world* w, uint64_t type_hash, const void* data, uint64_t n);
 HELIOS_GPU_API int32_t helios_gpu_message_counts(helios_gpu_world* w, uint64_t type_hash, uint64_t* previous,
                                                  uint64_t* current);
+/* Every registered (non-async) message type, in registration order (parity I/O: the snapshot of the message queues).
+ * hashes / sizes may be NULL to ask for the count only. */
+HELIOS_GPU_API int32_t helios_gpu_message_types(helios_gpu_world* w, uint64_t* hashes, uint32_t* sizes, uint32_t capacity,
+                                                uint32_t* count);
+
+/* ---- builtin structural messages (builtin_messages.hpp:14-195) -----------------------------------------------------
+ * Every structural World call also writes a message whose 8-byte payload is the entity: CreateEntity -> EntityAddedMsg
+ * (world.hpp:979-984; NOT the reserve + flush path of Commands::Spawn, :957-963), DestroyEntity / TryDestroyEntity ->
+ * EntityDestroyedMsg (:986-1005), AddComponents -> ComponentAddedMsg<T> per listed type, TryAddComponents -> per type
+ * actually added (:1026-1066), RemoveComponents / TryRemoveComponents -> ComponentRemovedMsg<T> likewise (:1124-1164),
+ * ClearComponents -> ComponentsClearedMsg (:1189-1196).  The library does the same: the bulk loaders append the new ids,
+ * and command application (helios_gpu_world_flush / helios_gpu_schedule_apply_deferred) emits the messages of every
+ * effective command in command order — flag, prefix scan and ordered scatter per message type — into the world's CURRENT
+ * queues, exactly where the reference's sequential replay would have left them.  The three non-template types are
+ * registered when the world is created (World::AddBuiltinMessages, world.hpp:1343-1347); ComponentAdded/RemovedMsg<T> are
+ * registered by the first valid Add / Remove command that names T (AddMessages<...>(), world.hpp:1033,1047,1131,1145).
+ * They are ordinary automatic-policy message types: read them with helios_gpu_message_read or a MessageReader system. */
+#define HELIOS_GPU_BUILTIN_ENTITY_ADDED 0u
+#define HELIOS_GPU_BUILTIN_ENTITY_DESTROYED 1u
+#define HELIOS_GPU_BUILTIN_COMPONENTS_CLEARED 2u
+#define HELIOS_GPU_BUILTIN_COMPONENT_ADDED 3u   /* of `component_hash` */
+#define HELIOS_GPU_BUILTIN_COMPONENT_REMOVED 4u /* of `component_hash` */
+/* Message type hash (TypeIndex) of a builtin message. */
+HELIOS_GPU_API int32_t helios_gpu_builtin_message_type(helios_gpu_world* w, uint32_t kind, uint64_t component_hash,
+                                                       uint64_t* out);
+/* TypeIndex of ComponentAddedMsg<T> / ComponentRemovedMsg<T> for a registered component: the FNV-1a of the template-id
+ * as the HOST compiler spells it (utils/type_info.hpp:206-226), which only the host knows.  Until it is set the library
+ * uses fnv1a("helios::ecs::ComponentAddedMsg") ^ (component_hash * FNV prime) (resp. ...RemovedMsg). */
+HELIOS_GPU_API int32_t helios_gpu_component_message_types(helios_gpu_world* w, uint64_t component_hash, uint64_t added_hash,
+                                                          uint64_t removed_hash);
+
 /* Copy PreviousMessages<T>() (which = 0) or CurrentMessages<T>() (which = 1) to the host. */
 HELIOS_GPU_API int32_t helios_gpu_message_read(helios_gpu_world* w, uint64_t type_hash, uint32_t which, void* out,
                                                uint64_t capacity_bytes);
@@ -420,6 +455,8 @@ typedef struct helios_gpu_world_view {
   uint32_t n_tables;
 } helios_gpu_world_view;
 
+#define HELIOS_GPU_MAX_SYSTEM_MESSAGES 4 /* MessageWriter<T> parameters and MessageReader<T> parameters of one system, each */
+
 /* Per-entity sparse filter of a launch: a row is visited iff (membership[index] & require) == require and
  * (membership[index] & exclude) == 0.  membership == NULL: the query has no sparse terms. */
 typedef struct helios_gpu_sparse_filter {
@@ -487,6 +524,13 @@ typedef struct helios_gpu_system_ctx {
   /* run conditions (below): DEVICE pointer to the u32 verdict of the system being guarded, 1 when the first condition
    * starts; a HELIOS_GPU_COND_CUSTOM launch stores 0 to veto.  NULL for system bodies. */
   uint32_t* verdict;
+  /* every MessageWriter<T> / MessageReader<T> parameter of the system (system/param_traits.hpp:193-240 allow any number):
+   * index 0 repeats writer / reader / d_writer / d_reader above, 1.. are helios_gpu_system_desc::more_writes / more_reads */
+  uint32_t n_writers, n_readers;
+  helios_gpu_msg_writer writers[HELIOS_GPU_MAX_SYSTEM_MESSAGES];
+  const helios_gpu_msg_writer* d_writers[HELIOS_GPU_MAX_SYSTEM_MESSAGES];
+  helios_gpu_msg_reader readers[HELIOS_GPU_MAX_SYSTEM_MESSAGES];
+  const helios_gpu_msg_reader* d_readers[HELIOS_GPU_MAX_SYSTEM_MESSAGES];
 } helios_gpu_system_ctx;
 #define HELIOS_GPU_RESOURCE_BYTES 4096u
 
@@ -513,10 +557,18 @@ typedef struct helios_gpu_system_desc {
   uint32_t cmd_payload_stride;     /* EMITS_COMMANDS: payload bytes per slot */
   uint64_t writes_message;         /* MessageWriter<T> type hash or 0 */
   uint64_t reads_message;          /* MessageReader<T> type hash or 0 */
-  uint64_t writer_capacity;        /* max messages this system writes per run */
+  uint64_t writer_capacity;        /* max messages this system writes per run (0 = one per matched row).  A run that writes
+                                      more makes helios_gpu_schedule_apply_deferred return HELIOS_GPU_ERR_CAPACITY after it has
+                                      applied everything else (the reference never loses a message: the excess is reported, not
+                                      silently dropped) and the buffer is sized for that count from the next run on */
   /* AccessPolicy beyond the query's own components (system/access_policy.hpp:172-196) */
   uint32_t n_extra_read_components, n_extra_write_components, n_read_resources, n_write_resources;
   uint64_t extra_read_components[8], extra_write_components[8], read_resources[8], write_resources[8];
+  /* further MessageWriter<T> / MessageReader<T> parameters (writers / readers 1.. of helios_gpu_system_ctx); every written
+   * type goes through the system's one local message queue and is merged with it (system_local_data.hpp:122-132) */
+  uint32_t n_more_writes, n_more_reads;
+  uint64_t more_writes[HELIOS_GPU_MAX_SYSTEM_MESSAGES - 1], more_writer_capacity[HELIOS_GPU_MAX_SYSTEM_MESSAGES - 1];
+  uint64_t more_reads[HELIOS_GPU_MAX_SYSTEM_MESSAGES - 1];
 } helios_gpu_system_desc;
 
 HELIOS_GPU_API int32_t helios_gpu_schedule_create(helios_gpu_world* w, const char* name, helios_gpu_schedule** out);

@@ -1014,6 +1014,11 @@ public:
     previous_.Register(t, size);
   }
   bool IsRegistered(TypeIndex t) const { return registered_.count(t) != 0; }
+  std::vector<std::pair<TypeIndex, uint32_t>> RegisteredTypes() const {
+    std::vector<std::pair<TypeIndex, uint32_t>> out;
+    for (const auto& [t, m] : registered_) out.emplace_back(t, m.size);
+    return out;
+  }
   uint32_t ElemSize(TypeIndex t) const { const auto it = registered_.find(t); return it == registered_.end() ? 0 : it->second.size; }
   // manager.hpp:532-540 Write → current
   void Write(TypeIndex t, const void* bytes, size_t count = 1) { current_.Enqueue(t, bytes, count); }
@@ -1210,8 +1215,12 @@ private:
   std::vector<Command> cmds_;
 };
 
-// Builtin message type hashes (builtin_messages.hpp): optional, see World::emit_builtin_messages.
+// Builtin message type identities (builtin_messages.hpp:14,48,86,124,161).  The non-template ones are the FNV-1a of their
+// qualified names, as TypeIndex::From does.  ComponentAddedMsg<T> / ComponentRemovedMsg<T> depend on how the compiler spells
+// T inside the template-id; a host that knows the spelling registers it (World::component_msg_types), everybody else gets
+// the stand-in below — the same formula as heliosengine_b200/csrc/messages.cu.
 inline TypeIndex BuiltinMsgType(std::string_view name) { return Fnv1a(name); }
+inline TypeIndex DefaultComponentMsgType(std::string_view name, TypeIndex comp) { return Fnv1a(name) ^ (comp * kFnvPrime); }
 
 // ------------------------------------------------------------------------------------------------
 // world.hpp:934-1196
@@ -1224,8 +1233,31 @@ public:
   AsyncMessageQueue async_messages;  // MessageManager::async_messages_ (message/manager.hpp:359)
   ResourceManager resources;         // world.hpp resources_ (InsertResources / ReadResource / WriteResource ...)
   CmdQueue command_queue;  // world.hpp:945 global queue
-  // quirk #13: every structural call also writes a builtin message.  The 8-byte payload is the entity.
-  bool emit_builtin_messages = false;
+  // quirk #13: every structural call also writes a builtin message (world.hpp:979-1036,1124-1196).  The 8-byte payload is
+  // the entity.  On by default, as in the reference; helios_oracle_set_builtin_messages(0) is the throughput-mode switch
+  // SURVEY.md §7.4 #13 allows (the GPU library has the same switch: HELIOS_GPU_WORLD_NO_BUILTIN_MESSAGES).
+  bool emit_builtin_messages = true;
+  // component type -> {ComponentAddedMsg<T>, ComponentRemovedMsg<T>} identities when the host registered them
+  std::map<TypeIndex, std::pair<TypeIndex, TypeIndex>> component_msg_types;
+
+  // world.hpp:42 World() { AddBuiltinMessages(); } — :1343-1347 registers the three non-template builtin messages
+  World() { AddBuiltinMessages(); }
+  void AddBuiltinMessages() {
+    messages.Register(kEntityAdded, 8);
+    messages.Register(kEntityDestroyed, 8);
+    messages.Register(kComponentsCleared, 8);
+  }
+  static inline const TypeIndex kEntityAdded = BuiltinMsgType("helios::ecs::EntityAddedMsg");
+  static inline const TypeIndex kEntityDestroyed = BuiltinMsgType("helios::ecs::EntityDestroyedMsg");
+  static inline const TypeIndex kComponentsCleared = BuiltinMsgType("helios::ecs::ComponentsClearedMsg");
+  TypeIndex ComponentAddedType(TypeIndex comp) const {
+    const auto it = component_msg_types.find(comp);
+    return it != component_msg_types.end() ? it->second.first : DefaultComponentMsgType("helios::ecs::ComponentAddedMsg", comp);
+  }
+  TypeIndex ComponentRemovedType(TypeIndex comp) const {
+    const auto it = component_msg_types.find(comp);
+    return it != component_msg_types.end() ? it->second.second : DefaultComponentMsgType("helios::ecs::ComponentRemovedMsg", comp);
+  }
 
   // world.hpp:950-955
   void Update() {
@@ -1241,7 +1273,7 @@ public:
   Entity CreateEntity() {
     const Entity e = entities.Create();
     components.InitEntity(e);
-    if (emit_builtin_messages) WriteBuiltin("helios::ecs::EntityAddedMsg", e);
+    if (emit_builtin_messages) WriteBuiltin(kEntityAdded, e);
     return e;
   }
   Entity ReserveEntity() { return entities.ReserveEntity(); }
@@ -1255,52 +1287,83 @@ public:
     if (!entities.Validate(e)) { ++invalid_command_count; return; }  // reference: HELIOS_ASSERT
     components.RemoveEntity(e);
     entities.Destroy(e);
-    if (emit_builtin_messages) WriteBuiltin("helios::ecs::EntityDestroyedMsg", e);
+    if (emit_builtin_messages) WriteBuiltin(kEntityDestroyed, e);
   }
   // world.hpp:996-1005
   void TryDestroyEntity(Entity e) {
     if (!entities.Validate(e)) return;
     components.TryRemoveEntity(e);
     entities.Destroy(e);
-    if (emit_builtin_messages) WriteBuiltin("helios::ecs::EntityDestroyedMsg", e);
+    if (emit_builtin_messages) WriteBuiltin(kEntityDestroyed, e);
   }
-  // world.hpp:1026-1036
+  // world.hpp:1026-1036 — AddMessages<ComponentAddedMsg<Ts>...>() registers the message types first (:1033), then one
+  // message per listed type, unconditionally (an overwrite counts as "added")
   void AddComponents(Entity e, const CompValue* comps, size_t n) {
     if (!entities.Validate(e)) { ++invalid_command_count; return; }
+    if (emit_builtin_messages)
+      for (size_t i = 0; i < n; ++i) RegisterBuiltin(ComponentAddedType(comps[i].type));
     components.Add(e, comps, n);
     if (emit_builtin_messages)
-      for (size_t i = 0; i < n; ++i) WriteBuiltinT("helios::ecs::ComponentAddedMsg", comps[i].type, e);
+      for (size_t i = 0; i < n; ++i) WriteBuiltin(ComponentAddedType(comps[i].type), e);
   }
-  // world.hpp:1038-1066
+  // world.hpp:1038-1066 — registration as above (:1047); a message only for the types that were actually added
   std::vector<bool> TryAddComponents(Entity e, const CompValue* comps, size_t n) {
     if (!entities.Validate(e)) { ++invalid_command_count; return std::vector<bool>(n, false); }
+    if (emit_builtin_messages)
+      for (size_t i = 0; i < n; ++i) RegisterBuiltin(ComponentAddedType(comps[i].type));
     auto added = components.TryAdd(e, comps, n);
     if (emit_builtin_messages)
       for (size_t i = 0; i < n; ++i)
-        if (added[i]) WriteBuiltinT("helios::ecs::ComponentAddedMsg", comps[i].type, e);
+        if (added[i]) WriteBuiltin(ComponentAddedType(comps[i].type), e);
     return added;
   }
-  // world.hpp:1124-1134
+  // world.hpp:1124-1134 — AddMessages<ComponentRemovedMsg<Ts>...>() (:1131), one message per listed type
   void RemoveComponents(Entity e, const TypeIndex* types, size_t n) {
     if (!entities.Validate(e)) { ++invalid_command_count; return; }
+    if (emit_builtin_messages)
+      for (size_t i = 0; i < n; ++i) RegisterBuiltin(ComponentRemovedType(types[i]));
     components.Remove(e, types, n);
     if (emit_builtin_messages)
-      for (size_t i = 0; i < n; ++i) WriteBuiltinT("helios::ecs::ComponentRemovedMsg", types[i], e);
+      for (size_t i = 0; i < n; ++i) WriteBuiltin(ComponentRemovedType(types[i]), e);
   }
-  // world.hpp:1136-1164
+  // world.hpp:1136-1164 — registration (:1145); a message only for the types that were actually removed
   std::vector<bool> TryRemoveComponents(Entity e, const TypeIndex* types, size_t n) {
     if (!entities.Validate(e)) { ++invalid_command_count; return std::vector<bool>(n, false); }
+    if (emit_builtin_messages)
+      for (size_t i = 0; i < n; ++i) RegisterBuiltin(ComponentRemovedType(types[i]));
     auto removed = components.TryRemove(e, types, n);
     if (emit_builtin_messages)
       for (size_t i = 0; i < n; ++i)
-        if (removed[i]) WriteBuiltinT("helios::ecs::ComponentRemovedMsg", types[i], e);
+        if (removed[i]) WriteBuiltin(ComponentRemovedType(types[i]), e);
     return removed;
   }
   // world.hpp:1189-1196
   void ClearComponents(Entity e) {
     if (!entities.Validate(e)) { ++invalid_command_count; return; }
     components.Clear(e);
-    if (emit_builtin_messages) WriteBuiltin("helios::ecs::ComponentsClearedMsg", e);
+    if (emit_builtin_messages) WriteBuiltin(kComponentsCleared, e);
+  }
+  // world.hpp:1230-1320 — resource calls register ResourceInsertedMsg<T> / ResourceRemovedMsg<T> (empty structs: one byte
+  // per message) and write one message when the call took effect
+  void InsertResource(TypeIndex t, const void* v, size_t n) {
+    resources.Insert(t, v, n);
+    WriteResourceMsg("helios::ecs::ResourceInsertedMsg", t, true);
+  }
+  bool TryInsertResource(TypeIndex t, const void* v, size_t n) {
+    const bool inserted = resources.TryInsert(t, v, n);
+    WriteResourceMsg("helios::ecs::ResourceInsertedMsg", t, inserted);
+    return inserted;
+  }
+  bool RemoveResource(TypeIndex t) {  // :1278-1306 asserts the resource exists -> false here, nothing registered
+    if (!resources.Has(t)) return false;
+    resources.Remove(t);
+    WriteResourceMsg("helios::ecs::ResourceRemovedMsg", t, true);
+    return true;
+  }
+  bool TryRemoveResource(TypeIndex t) {
+    const bool removed = resources.TryRemove(t);
+    WriteResourceMsg("helios::ecs::ResourceRemovedMsg", t, removed);
+    return removed;
   }
   bool HasComponent(Entity e, TypeIndex t) const { return entities.Validate(e) && components.Has(e, t); }
   size_t EntityCount() const noexcept { return entities.Count(); }
@@ -1310,15 +1373,18 @@ public:
   uint64_t invalid_command_count = 0;
 
 private:
-  void WriteBuiltin(std::string_view name, Entity e) {
-    const TypeIndex t = BuiltinMsgType(name);
-    if (!messages.IsRegistered(t)) messages.Register(t, 8);
-    const uint64_t v = e.Pack();
-    messages.Write(t, &v);
+  void WriteResourceMsg(std::string_view tmpl, TypeIndex res, bool write) {
+    if (!emit_builtin_messages) return;
+    const TypeIndex t = DefaultComponentMsgType(tmpl, res);
+    if (!messages.IsRegistered(t)) messages.Register(t, 1);
+    const uint8_t zero = 0;
+    if (write) messages.Write(t, &zero);
   }
-  void WriteBuiltinT(std::string_view name, TypeIndex comp, Entity e) {
-    const TypeIndex t = Fnv1a(name) ^ (comp * kFnvPrime);  // stand-in identity for Msg<T>
+  void RegisterBuiltin(TypeIndex t) {
     if (!messages.IsRegistered(t)) messages.Register(t, 8);
+  }
+  void WriteBuiltin(TypeIndex t, Entity e) {
+    RegisterBuiltin(t);
     const uint64_t v = e.Pack();
     messages.Write(t, &v);
   }

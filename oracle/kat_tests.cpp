@@ -1195,6 +1195,150 @@ void TestAsyncMessages() {
   }
 }
 
+// ---- builtin_messages.cpp:67-701 — every structural World call writes its builtin message ------------------------------------
+void TestBuiltinMessages() {
+  auto count = [](World& w, TypeIndex t) { return w.messages.IsRegistered(t) ? w.messages.ReadAll(t).size() / w.messages.SizeOf(t) : 0; };
+  auto prev0 = [](World& w, TypeIndex t) {
+    uint64_t v = ~0ull;
+    const auto* b = w.messages.Previous().Bytes(t);
+    if (b && b->size() >= 8) std::memcpy(&v, b->data(), 8);
+    return v;
+  };
+  const Position p0{};
+  const Velocity v0{};
+  {  // :67-78 "One message is emitted per created entity" (lands in `previous` after Update)
+    World w;
+    CHECK(w.messages.IsRegistered(World::kEntityAdded) && w.messages.IsRegistered(World::kEntityDestroyed) &&
+          w.messages.IsRegistered(World::kComponentsCleared));  // world.hpp:42,1343-1347 AddBuiltinMessages
+    const Entity e = w.CreateEntity();
+    w.Update();
+    CHECK(count(w, World::kEntityAdded) == 1);
+    CHECK(prev0(w, World::kEntityAdded) == e.Pack());
+  }
+  {  // :80-104 two entities -> two messages; :106-116 cleared after the next Update
+    World w;
+    const Entity e1 = w.CreateEntity(), e2 = w.CreateEntity();
+    w.Update();
+    CHECK(count(w, World::kEntityAdded) == 2);
+    const auto all = w.messages.ReadAll(World::kEntityAdded);
+    uint64_t a, b;
+    std::memcpy(&a, all.data(), 8);
+    std::memcpy(&b, all.data() + 8, 8);
+    CHECK(a == e1.Pack() && b == e2.Pack());
+    w.Update();
+    CHECK(count(w, World::kEntityAdded) == 0);
+  }
+  {  // Commands::Spawn = ReserveEntity + Flush: InitEntity only, NO EntityAddedMsg (world.hpp:957-963 vs :979-984)
+    World w;
+    (void)w.ReserveEntity();
+    w.Flush();
+    CHECK(w.EntityCount() == 1 && count(w, World::kEntityAdded) == 0);
+  }
+  {  // :168-181 destroy -> one EntityDestroyedMsg carrying the entity; :183-196 two; :198-210 cleared by the 2nd Update
+    World w;
+    const Entity e1 = w.CreateEntity(), e2 = w.CreateEntity();
+    w.Update();
+    w.DestroyEntity(e1);
+    w.Update();
+    CHECK(count(w, World::kEntityDestroyed) == 1 && prev0(w, World::kEntityDestroyed) == e1.Pack());
+    w.TryDestroyEntity(e2);
+    w.TryDestroyEntity(e2);  // dead now: skipped silently, no second message (world.hpp:996-1000)
+    w.Update();
+    CHECK(count(w, World::kEntityDestroyed) == 1 && prev0(w, World::kEntityDestroyed) == e2.Pack());
+    w.Update();
+    CHECK(count(w, World::kEntityDestroyed) == 0);
+  }
+  {  // :262-275 one ComponentAddedMsg<Position>; :277-291 types tracked independently; :293-305 cleared
+    World w;
+    RegisterAll(w.components);
+    const Entity e = w.CreateEntity();
+    const CompValue cp{kPos, &p0}, cv{kVel, &v0};
+    const TypeIndex addP = w.ComponentAddedType(kPos), addV = w.ComponentAddedType(kVel);
+    CHECK(!w.messages.IsRegistered(addP));  // registered by the first AddComponents (world.hpp:1033)
+    w.AddComponents(e, &cp, 1);
+    CHECK(w.messages.IsRegistered(addP) && !w.messages.IsRegistered(addV));
+    w.AddComponents(e, &cv, 1);
+    w.Update();
+    CHECK(count(w, addP) == 1 && count(w, addV) == 1 && prev0(w, addP) == e.Pack());
+    w.AddComponents(e, &cp, 1);  // overwrite: AddComponents writes the message unconditionally (world.hpp:1035)
+    CHECK(count(w, addP) == 2);
+    auto added = w.TryAddComponents(e, &cp, 1);  // present: nothing added, no message (world.hpp:1052-1056)
+    CHECK(!added[0] && count(w, addP) == 2);
+    w.Update();
+    w.Update();
+    CHECK(count(w, addP) == 0 && count(w, addV) == 0);
+  }
+  {  // :346-360 one ComponentRemovedMsg<Position>; :362-378 independent types; Try: only what was removed (world.hpp:1148-1161)
+    World w;
+    RegisterAll(w.components);
+    const Entity e = w.CreateEntity();
+    CompValue both[2] = {{kPos, &p0}, {kVel, &v0}};
+    w.AddComponents(e, both, 2);
+    const TypeIndex remP = w.ComponentRemovedType(kPos), remV = w.ComponentRemovedType(kVel);
+    w.RemoveComponents(e, &kPos, 1);
+    const TypeIndex two[2] = {kPos, kVel};
+    const auto removed = w.TryRemoveComponents(e, two, 2);  // Position is gone already
+    CHECK(!removed[0] && removed[1]);
+    w.Update();
+    CHECK(count(w, remP) == 1 && count(w, remV) == 1 && prev0(w, remP) == e.Pack());
+  }
+  {  // :420-432 ClearComponents -> ComponentsClearedMsg; :449-457 "even when entity had no components"
+    World w;
+    RegisterAll(w.components);
+    const Entity e1 = w.CreateEntity(), e2 = w.CreateEntity();
+    const CompValue cp{kPos, &p0};
+    w.AddComponents(e1, &cp, 1);
+    w.ClearComponents(e1);
+    w.ClearComponents(e2);
+    w.Update();
+    CHECK(count(w, World::kComponentsCleared) == 2 && prev0(w, World::kComponentsCleared) == e1.Pack());
+    w.Update();
+    CHECK(count(w, World::kComponentsCleared) == 0);
+  }
+  {  // :475-541 ResourceInsertedMsg<T>: insert, replace, TryInsert only when it inserts; :560-640 ResourceRemovedMsg<T>
+    World w;
+    const TypeIndex kScore = Fnv1a("Score");
+    const TypeIndex ins = DefaultComponentMsgType("helios::ecs::ResourceInsertedMsg", kScore);
+    const TypeIndex rem = DefaultComponentMsgType("helios::ecs::ResourceRemovedMsg", kScore);
+    const int v = 42;
+    w.InsertResource(kScore, &v, sizeof v);
+    w.Update();
+    CHECK(count(w, ins) == 1);
+    w.Update();
+    w.InsertResource(kScore, &v, sizeof v);  // "Replacing an existing resource also emits a message"
+    CHECK(!w.TryInsertResource(kScore, &v, sizeof v));  // present: no message
+    w.Update();
+    CHECK(count(w, ins) == 1);
+    CHECK(w.TryRemoveResource(kScore) && !w.TryRemoveResource(kScore));
+    w.Update();
+    CHECK(count(w, rem) == 1);
+  }
+  {  // the same calls through the command queue: messages in command order, per type (world.hpp:957-963 + the above)
+    World w;
+    RegisterAll(w.components);
+    const Entity a = w.CreateEntity(), b = w.CreateEntity(), c = w.CreateEntity();
+    w.Update();
+    w.Update();
+    auto add = [&](Entity e, TypeIndex t, bool try_) {
+      Command cmd{try_ ? CmdKind::kTryAdd : CmdKind::kAdd, e, {t}, {std::vector<uint8_t>(8, 0)}};
+      w.command_queue.Enqueue(std::move(cmd));
+    };
+    add(c, kPos, false);
+    add(a, kPos, false);
+    add(c, kPos, true);   // present: no message
+    add(b, kPos, true);
+    w.command_queue.Enqueue(Command{CmdKind::kDestroy, a, {}, {}});
+    w.command_queue.Enqueue(Command{CmdKind::kTryDestroy, a, {}, {}});  // dead by then
+    w.Flush();
+    const auto* cur = w.messages.Current().Bytes(w.ComponentAddedType(kPos));
+    CHECK(cur && cur->size() == 24);
+    uint64_t got[3] = {};
+    if (cur && cur->size() == 24) std::memcpy(got, cur->data(), 24);
+    CHECK(got[0] == c.Pack() && got[1] == a.Pack() && got[2] == b.Pack());
+    CHECK(count(w, World::kEntityDestroyed) == 1);
+  }
+}
+
 }  // namespace
 
 int main() {
@@ -1212,6 +1356,7 @@ int main() {
   TestApplyOrder();
   TestRunConditions();
   TestAsyncMessages();
+  TestBuiltinMessages();
   std::printf("oracle KATs: %d checks, %d failed\n", g_checks, g_fail);
   return g_fail;
 }

@@ -35,6 +35,7 @@ struct OCtx {  // what a CPU system body receives
   uint32_t params_size;
   uint64_t writes_message, reads_message;
   uint8_t* resources;
+  uint64_t writes[HELIOS_GPU_MAX_SYSTEM_MESSAGES], reads[HELIOS_GPU_MAX_SYSTEM_MESSAGES];  // every writer / reader, 0 first
 };
 using OSystemFn = int32_t (*)(const OCtx*);
 
@@ -237,6 +238,54 @@ int32_t sys_consume_strong(const OCtx* c) {
   }
   return 0;
 }
+// Two MessageWriter parameters in one system (system/param_traits.hpp:193-240): per row two CollisionEvents and one
+// ScoreEvent, serial emission order; and a system with two MessageReader parameters.
+struct ScoreEvent { uint64_t who; int32_t points; uint32_t pad; };
+int32_t sys_emit_multi(const OCtx* c) {
+  OWorld* w = c->world;
+  const int saved_threads = w->threads;
+  w->threads = 1;
+  for (int k = 0; k < 2; ++k)
+    if (!c->local->message_queue.IsRegistered(c->writes[k]))
+      c->local->message_queue.Register(c->writes[k], w->world.messages.SizeOf(c->writes[k]));
+  visit(c, [&](ho::Entity e, uint8_t** p) {
+    const auto* pos = reinterpret_cast<const Position*>(p[0]);
+    const uint32_t team = *reinterpret_cast<const uint32_t*>(p[1]);
+    CollisionEvent ev{e.Pack(), e.Pack() ^ 1ull, pos->x * 0.0078125f + float(team), 0};
+    c->local->message_queue.Enqueue(c->writes[0], &ev);
+    ev.b = e.Pack() ^ 2ull;
+    ev.impulse = pos->y * 0.0078125f;
+    c->local->message_queue.Enqueue(c->writes[0], &ev);
+    const ScoreEvent sc{e.Pack(), int32_t(team) + 1, 0};
+    c->local->message_queue.Enqueue(c->writes[1], &sc);
+  });
+  w->threads = saved_threads;
+  return 0;
+}
+int32_t sys_consume_two(const OCtx* c) {
+  uint32_t health_slot;
+  std::memcpy(&health_slot, c->params, 4);
+  OWorld* w = c->world;
+  const ho::TypeIndex health = w->slot_hash[health_slot];
+  auto hp_of = [&](uint64_t bits) -> int32_t* {
+    const ho::Entity a = E(bits);
+    if (!w->world.entities.Validate(a)) return nullptr;
+    return reinterpret_cast<int32_t*>(w->world.components.Get(a, health));
+  };
+  const auto ev_bytes = w->world.messages.ReadAll(c->reads[0]);
+  for (size_t i = 0; i + sizeof(CollisionEvent) <= ev_bytes.size(); i += sizeof(CollisionEvent)) {
+    CollisionEvent ev;
+    std::memcpy(&ev, &ev_bytes[i], sizeof(ev));
+    if (int32_t* hp = hp_of(ev.a)) *hp -= int32_t(ev.impulse);
+  }
+  const auto sc_bytes = w->world.messages.ReadAll(c->reads[1]);
+  for (size_t i = 0; i + sizeof(ScoreEvent) <= sc_bytes.size(); i += sizeof(ScoreEvent)) {
+    ScoreEvent sc;
+    std::memcpy(&sc, &sc_bytes[i], sizeof(sc));
+    if (int32_t* hp = hp_of(sc.who)) *hp += sc.points;
+  }
+  return 0;
+}
 int32_t sys_stats(const OCtx* c) {
   OWorld* w = c->world;
   const int saved_threads = w->threads;
@@ -347,6 +396,7 @@ const Builtin kBuiltins[] = {
     {"buff_heal", sys_buff_heal}, {"buff_optional", sys_buff_optional},
     {"alert_low_health", sys_alert_low_health}, {"heal_alerted", sys_heal_alerted},
     {"apply_gravity", sys_apply_gravity}, {"tick_counter", sys_tick_counter},
+    {"emit_multi", sys_emit_multi}, {"consume_two", sys_consume_two},
 };
 
 // helios_gpu_command → oracle Command (payload: ascending slot order, each value padded to 4 bytes).
@@ -375,8 +425,10 @@ ho::Command to_command(OWorld* w, const helios_gpu_command& c, const uint8_t* pa
 // =====================================================================================================
 #define W(w) (reinterpret_cast<OWorld*>(w))
 
-HO_API int32_t helios_oracle_world_create(const helios_gpu_world_config*, void** out) {
-  *out = new OWorld();
+HO_API int32_t helios_oracle_world_create(const helios_gpu_world_config* cfg, void** out) {
+  auto* w = new OWorld();
+  if (cfg && (cfg->flags & HELIOS_GPU_WORLD_NO_BUILTIN_MESSAGES)) w->world.emit_builtin_messages = false;
+  *out = w;
   return 0;
 }
 HO_API int32_t helios_oracle_world_destroy(void* w) {
@@ -733,6 +785,33 @@ HO_API int32_t helios_oracle_message_register(void* wp, uint64_t hash, uint32_t 
   W(wp)->world.messages.Register(hash, size, policy ? ho::ClearPolicy::kManual : ho::ClearPolicy::kAutomatic);
   return 0;
 }
+HO_API int32_t helios_oracle_message_types(void* wp, uint64_t* hashes, uint32_t* sizes, uint32_t capacity, uint32_t* count) {
+  const auto types = W(wp)->world.messages.RegisteredTypes();
+  *count = uint32_t(types.size());
+  if (!hashes && !sizes) return 0;
+  if (capacity < types.size()) return HELIOS_GPU_ERR_CAPACITY;
+  for (size_t i = 0; i < types.size(); ++i) {
+    if (hashes) hashes[i] = types[i].first;
+    if (sizes) sizes[i] = types[i].second;
+  }
+  return 0;
+}
+HO_API int32_t helios_oracle_component_message_types(void* wp, uint64_t comp, uint64_t added, uint64_t removed) {
+  if (!W(wp)->world.components.Meta(comp)) return HELIOS_GPU_ERR_NOT_FOUND;
+  W(wp)->world.component_msg_types[comp] = {added, removed};
+  return 0;
+}
+HO_API int32_t helios_oracle_builtin_message_type(void* wp, uint32_t kind, uint64_t comp, uint64_t* out) {
+  ho::World& w = W(wp)->world;
+  switch (kind) {
+    case HELIOS_GPU_BUILTIN_ENTITY_ADDED: *out = ho::World::kEntityAdded; return 0;
+    case HELIOS_GPU_BUILTIN_ENTITY_DESTROYED: *out = ho::World::kEntityDestroyed; return 0;
+    case HELIOS_GPU_BUILTIN_COMPONENTS_CLEARED: *out = ho::World::kComponentsCleared; return 0;
+    case HELIOS_GPU_BUILTIN_COMPONENT_ADDED: *out = w.ComponentAddedType(comp); return w.components.Meta(comp) ? 0 : HELIOS_GPU_ERR_NOT_FOUND;
+    case HELIOS_GPU_BUILTIN_COMPONENT_REMOVED: *out = w.ComponentRemovedType(comp); return w.components.Meta(comp) ? 0 : HELIOS_GPU_ERR_NOT_FOUND;
+    default: return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  }
+}
 HO_API int32_t helios_oracle_message_write(void* wp, uint64_t hash, const void* data, uint64_t n) {
   if (!W(wp)->world.messages.IsRegistered(hash)) return HELIOS_GPU_ERR_NOT_FOUND;
   W(wp)->world.messages.Write(hash, data, n);
@@ -802,21 +881,21 @@ HO_API int32_t helios_oracle_resource_insert(void* wp, uint64_t hash, const void
   if (!v || size == 0 || hash == 0) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   auto& r = W(wp)->world.resources;
   if (r.Has(hash) && r.SizeOf(hash) != size) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
-  r.Insert(hash, v, size);
+  W(wp)->world.InsertResource(hash, v, size);
   return 0;
 }
 HO_API int32_t helios_oracle_resource_try_insert(void* wp, uint64_t hash, const void* v, uint32_t size, uint32_t* inserted) {
-  const bool ok = W(wp)->world.resources.TryInsert(hash, v, size);
+  const bool ok = W(wp)->world.TryInsertResource(hash, v, size);
   if (inserted) *inserted = ok ? 1u : 0u;
   return 0;
 }
 HO_API int32_t helios_oracle_resource_try_remove(void* wp, uint64_t hash, uint32_t* removed) {
-  const bool ok = W(wp)->world.resources.TryRemove(hash);
+  const bool ok = W(wp)->world.TryRemoveResource(hash);
   if (removed) *removed = ok ? 1u : 0u;
   return 0;
 }
 HO_API int32_t helios_oracle_resource_remove(void* wp, uint64_t hash) {
-  return W(wp)->world.resources.Remove(hash) ? 0 : HELIOS_GPU_ERR_NOT_FOUND;
+  return W(wp)->world.RemoveResource(hash) ? 0 : HELIOS_GPU_ERR_NOT_FOUND;
 }
 HO_API int32_t helios_oracle_resource_has(void* wp, uint64_t hash, uint32_t* out) {
   *out = W(wp)->world.resources.Has(hash) ? 1u : 0u;
@@ -908,7 +987,11 @@ HO_API int32_t helios_oracle_schedule_add_system(void* sp, const helios_gpu_syst
     OSysEntry& en = sched->entries[idx];
     OCtx c{sched->w, &local, en.desc.query ? &reinterpret_cast<const OQuery*>(en.desc.query)->desc : nullptr,
            en.params.data(), uint32_t(en.params.size()), en.desc.writes_message, en.desc.reads_message,
-           sched->resources.data()};
+           sched->resources.data(), {}, {}};
+    c.writes[0] = en.desc.writes_message;
+    c.reads[0] = en.desc.reads_message;
+    for (uint32_t k = 0; k < en.desc.n_more_writes && k + 1 < HELIOS_GPU_MAX_SYSTEM_MESSAGES; ++k) c.writes[k + 1] = en.desc.more_writes[k];
+    for (uint32_t k = 0; k < en.desc.n_more_reads && k + 1 < HELIOS_GPU_MAX_SYSTEM_MESSAGES; ++k) c.reads[k + 1] = en.desc.more_reads[k];
     reinterpret_cast<OSystemFn>(en.desc.launch)(&c);
   }, pol);
   if (out_index) *out_index = uint32_t(idx);

@@ -110,6 +110,17 @@ int main(int argc, char** argv) {
       CHECK(!world.Exists(ents[0]) && world.EntityCount() == n);
       CHECK(world.ReadComponent<Health>(ents[1]).hp == 77 && world.HasComponent<Velocity>(ents[1]));
       CHECK(!world.HasComponent<Velocity>(ents[2]) && world.HasComponent<Position>(ents[2]));
+      // builtin structural messages of those four commands (builtin_messages.cpp:168-390): typed readers over the
+      // TypeIndex the host compiler spells (ComponentAddedMsg<helios::bench::Health> ...), current queue
+      const auto destroyed = world.ReadMessages<ecs::EntityDestroyedMsg>();
+      CHECK(destroyed.size() == 1 && destroyed[0].GetEntity() == ents[0]);
+      const auto added_h = world.ReadMessages<ecs::ComponentAddedMsg<Health>>();
+      CHECK(added_h.size() == 2 && added_h[0].GetEntity() == spawned && added_h[1].GetEntity() == ents[1]);
+      const auto removed_v = world.ReadMessages<ecs::ComponentRemovedMsg<Velocity>>();
+      CHECK(removed_v.size() == 1 && removed_v[0].GetEntity() == ents[2]);
+      // SpawnBatch = CreateEntity + AddComponents per row; Run(3) called World::Update three times since: cleared by now
+      CHECK(world.ReadMessages<ecs::EntityAddedMsg>().empty());
+      CHECK(ecs::TypeIndexOf<ecs::ComponentAddedMsg<Health>>() == ecs::Fnv1a("helios::ecs::ComponentAddedMsg<helios::bench::Health>"));
     }
     ecs::Query<const Position&> q_pos(world);
     ecs::Query<const Position&, ecs::With<Health>> q_with(world);

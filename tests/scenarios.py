@@ -322,6 +322,38 @@ def run_conditions(backend, n=4099, frames=6, mode=capi.EXEC_SERIAL):
     return out
 
 
+SCORE_EVENT = worlds.NS + "ScoreEvent"  # {Entity who; i32 points; u32 pad} = 16 B
+
+
+def multi_messages(backend, n=4099, frames=3, mode=capi.EXEC_SERIAL, tight=False):
+    """Several MessageWriter / MessageReader parameters in one system (system/param_traits.hpp:193-240): S0 reads both
+    types, S1 writes two CollisionEvents and one ScoreEvent per row (3 messages per row of two types).  `tight` leaves
+    writer 0 at its default capacity (one message per row): the run must REPORT the overflow."""
+    w = capi.World(backend)
+    shorts = ["Position", "Health", "Team"]
+    worlds.register_all(w, shorts)
+    w.spawn_batch([worlds.cname(x) for x in shorts], n, [worlds.column(x, n, 9500 + i) for i, x in enumerate(shorts)],
+                  want_entities=False)
+    w.message_register(worlds.COLLISION_EVENT, 24)
+    w.message_register(SCORE_EVENT, 16)
+    P, H, T = (worlds.cname(x) for x in shorts)
+    s = w.schedule("Update")
+    s.add_system("S0_consume_two", "consume_two", None, params=struct.pack("<I", w.slots[H]),
+                 reads_message=worlds.COLLISION_EVENT, more_reads=[SCORE_EVENT], extra_writes=[H])
+    s.add_system("S1_emit_multi", "emit_multi", w.query([(P, False), (T, False)]), writes_message=worlds.COLLISION_EVENT,
+                 writer_capacity=0 if tight else 2 * n, more_writes=[(SCORE_EVENT, 0)])
+    s.build()
+    out = {}
+    for frame in range(frames):
+        s.run_and_wait(mode)
+        out[f"frame{frame}_counts"] = [list(w.message_counts(worlds.COLLISION_EVENT)), list(w.message_counts(SCORE_EVENT))]
+        out[f"frame{frame}_messages"] = _bytes_digest(w.message_read(worlds.COLLISION_EVENT, 1), w.message_read(SCORE_EVENT, 1))
+        w.update()
+    out["world"] = snapshot_digest(w.snapshot())
+    w.close()
+    return out
+
+
 SCENARIOS = {
     "cfg1_n4099": lambda b: cfg1(b),
     "cfg1_n1": lambda b: cfg1(b, n=1),
@@ -334,4 +366,5 @@ SCENARIOS = {
     "sparse_sets": lambda b: sparse_sets(b),
     "churn_small_s11": lambda b: churn_small(b, seed=11),
     "run_conditions": lambda b: run_conditions(b),
+    "multi_messages": lambda b: multi_messages(b),
 }
