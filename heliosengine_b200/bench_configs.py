@@ -82,6 +82,11 @@ def run_cfg3(args, torch, dev, stream, peak):
                     e2e_s.append(t1 - t0)
                 else:
                     dev_ms.append(a.elapsed_time(b))
+            # end of frame: World::Update (world.hpp:950-955) ages the message queues — the builtin structural messages the
+            # commands wrote (1.47M per frame here) are dropped two frames later, as in a reference App loop
+            wg.update()
+            if verify:
+                wo.update()
     parity = None
     if verify:
         dg, do = worlds.snapshot_digest(wg.snapshot()), worlds.snapshot_digest(wo.snapshot())

@@ -32,7 +32,7 @@ SYSTEM_EMITS_COMMANDS = 1
 SYSTEM_NEEDS_VIEW = 2
 SYSTEM_CONSUMES_MESSAGES = 4
 
-WORLD_NO_BUILTIN_MESSAGES = 1  # helios_gpu_world_config::flags
+WORLD_NO_BUILTIN_MESSAGES, WORLD_GENERAL_APPLY = 1, 2  # helios_gpu_world_config::flags
 BUILTIN_ENTITY_ADDED, BUILTIN_ENTITY_DESTROYED, BUILTIN_COMPONENTS_CLEARED, BUILTIN_COMPONENT_ADDED, BUILTIN_COMPONENT_REMOVED = range(5)
 
 INVALID_ENTITY = 0xFFFFFFFFFFFFFFFF
@@ -88,6 +88,7 @@ class ApplyStats(C.Structure):
     _fields_ = [
         ("commands", C.c_uint64), ("effective", C.c_uint64), ("invalid", C.c_uint64), ("moved_rows", C.c_uint64),
         ("moved_bytes", C.c_uint64), ("resolve_rounds", C.c_uint32), ("used_sequential_fallback", C.c_uint32),
+        ("pipeline", C.c_uint32), ("fast_fallbacks", C.c_uint32),
     ]
 
 

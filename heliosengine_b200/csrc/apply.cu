@@ -964,6 +964,7 @@ namespace hgpu {
 void free_apply_scratch(helios_gpu_world* w) {
   delete w->apply;
   w->apply = nullptr;
+  free_fast_scratch(w);
 }
 
 namespace apply_host {
@@ -1091,6 +1092,12 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
   auto& S = *w->apply;
   cudaStream_t st = w->stream;
   HG_TRY(sync_counts_to_host(w));
+  if (dense && !w->force_general_apply) {  // steady-state frames: ten launches, one read-back (apply_fast.cu)
+    bool done = false;
+    HG_TRY(apply_queue_fast(w, d_cmds, d_payload, n, &done));
+    if (done) return HELIOS_GPU_OK;
+    ++w->fast_fallbacks;
+  }
   HG_TRY(upload_component_layout(w));
   uint64_t launches = 0;
 
@@ -1325,6 +1332,7 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
   w->last_stats.moved_rows = hc.n_changed;
   w->last_stats.resolve_rounds = hc.unresolved;
   w->last_stats.moved_bytes = hc.moved_bytes;
+  w->last_stats.fast_fallbacks = uint32_t(w->fast_fallbacks);
   w->launches += launches;
   return HELIOS_GPU_OK;
 }

@@ -171,6 +171,7 @@ int32_t helios_gpu_world_create(const helios_gpu_world_config* cfg, helios_gpu_w
   HG_TRY(ensure_entity_capacity(w, cfg && cfg->entity_capacity ? cfg->entity_capacity : 1024));
   // World() { AddBuiltinMessages(); } (world.hpp:42,1343-1347)
   w->builtin_messages = !(cfg && (cfg->flags & HELIOS_GPU_WORLD_NO_BUILTIN_MESSAGES));
+  w->force_general_apply = cfg && (cfg->flags & HELIOS_GPU_WORLD_GENERAL_APPLY);
   HG_TRY(helios_gpu_message_register(w, kMsgEntityAdded, 8, HELIOS_GPU_MSG_AUTOMATIC));
   HG_TRY(helios_gpu_message_register(w, kMsgEntityDestroyed, 8, HELIOS_GPU_MSG_AUTOMATIC));
   HG_TRY(helios_gpu_message_register(w, kMsgComponentsCleared, 8, HELIOS_GPU_MSG_AUTOMATIC));

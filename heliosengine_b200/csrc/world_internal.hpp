@@ -116,6 +116,8 @@ struct helios_gpu_world {
   uint64_t launches = 0;
   uint64_t mutation_epoch = 0; // bumped by anything that may write component columns or move rows (systems with a write
                                // set, commands, column uploads, spawns): lets a system keep a validated cache of columns
+  bool force_general_apply = false;  // HELIOS_GPU_WORLD_GENERAL_APPLY: never take the steady-state command pipeline
+  uint64_t fast_fallbacks = 0;       // dense batches the steady-state pipeline handed to the general one
   bool builtin_messages = true; // every structural call also writes its builtin message (world.hpp:979-1036,1124-1196)
   uint64_t epoch = 0;          // bumped whenever a device pointer or directory size a captured graph bakes in changes
 
@@ -172,6 +174,8 @@ struct helios_gpu_world {
   // scratch for the command pipeline (commands.cu)
   struct ApplyScratch;
   ApplyScratch* apply = nullptr;
+  struct FastScratch;            // apply_fast.cu: the steady-state (one command per entity, no new archetype) pipeline
+  FastScratch* fast = nullptr;
 };
 
 namespace hgpu {
@@ -188,6 +192,10 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
 int32_t apply_host_queue(helios_gpu_world* w, HostCmdQueue& q);
 int32_t flush_reserved(helios_gpu_world* w);
 void free_apply_scratch(helios_gpu_world* w);
+// apply_fast.cu: tries the ten-launch steady-state pipeline; *done = false (nothing written) when the batch needs the
+// general one (several commands per entity, a new archetype, sparse-set components, no room in a table or message queue)
+int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, const uint8_t* d_payload, uint64_t n, bool* done);
+void free_fast_scratch(helios_gpu_world* w);
 // sparse.cu
 int32_t sparse_grow_entities(helios_gpu_world* w, uint32_t old_cap, uint32_t new_cap);  // called by ensure_entity_capacity
 int32_t publish_sparse_dir(helios_gpu_world* w);

@@ -62,6 +62,9 @@ typedef struct helios_gpu_world_config {
  * ComponentAddedMsg<T>, ComponentRemovedMsg<T>, ComponentsClearedMsg).  The reference always writes them
  * (world.hpp:979-1036,1124-1196); the default here does too.  A stated deviation for callers that never read them. */
 #define HELIOS_GPU_WORLD_NO_BUILTIN_MESSAGES 1u
+/* Always apply commands with the general pipeline (apply.cu), never the steady-state one (apply_fast.cu).  Both compute
+ * the same world state; the flag exists so that tests can hold one against the other. */
+#define HELIOS_GPU_WORLD_GENERAL_APPLY 2u
 
 /* ---- world lifetime (replaces World ctor/dtor, world.hpp:80-130) ------------------------------ */
 HELIOS_GPU_API int32_t helios_gpu_world_create(const helios_gpu_world_config* cfg, helios_gpu_world** out);
@@ -259,6 +262,8 @@ typedef struct helios_gpu_apply_stats {
   uint64_t moved_bytes;     /* component + entity-id bytes read+written by the row mover */
   uint32_t resolve_rounds;  /* dependency-resolution rounds of the swap-and-pop replay (0 = none needed) */
   uint32_t used_sequential_fallback;
+  uint32_t pipeline;        /* 1 = steady-state pipeline (ten launches, one read-back), 0 = general pipeline */
+  uint32_t fast_fallbacks;  /* dense batches this world handed from the steady-state pipeline to the general one so far */
 } helios_gpu_apply_stats;
 HELIOS_GPU_API int32_t helios_gpu_last_apply_stats(helios_gpu_world* w, helios_gpu_apply_stats* out);
 
