@@ -50,7 +50,7 @@ constexpr uint32_t kTile = 1024;         // commands per CTA in K1 / K3 / K10 (8
 constexpr uint32_t kChunk = 1024;        // ops per CTA in K4
 
 enum : uint32_t { F_VALID = 1u, F_MIG = 2u, F_DESTROY = 4u, F_EM_ADD = 16u, F_EM_REM = 32u, F_EM_CLEAR = 64u };
-enum : uint32_t { A_DUPS = 1u, A_UNKNOWN = 2u, A_TABLE_ROOM = 4u, A_CHANNEL_ROOM = 8u, A_BAD_MASK = 16u };
+enum : uint32_t { A_DUPS = 1u, A_UNKNOWN = 2u, A_TABLE_ROOM = 4u, A_CHANNEL_ROOM = 8u, A_BAD_MASK = 16u, A_STUCK = 32u };
 
 struct FastCounters {
   uint32_t abort;
@@ -600,7 +600,10 @@ __global__ void __launch_bounds__(256) k_resolve(const ResolveView v) {
   for (;;) {
     if (pending) pending = !resolve_step(v, j, I, pred, started);
     if (!__syncthreads_or(pending)) break;
-    ++rounds;
+    if (++rounds > (1u << 20)) {  // cannot happen for a consistent op list; nothing has been written yet, so the general
+      if (threadIdx.x == 0) atomicOr(&v.counters->abort, A_STUCK);  // pipeline can still take the batch
+      break;
+    }
   }
   if (threadIdx.x == 0 && rounds) atomicMax(&v.counters->rounds, rounds);
 }

@@ -32,13 +32,16 @@
 
 namespace helios::ecs {
 
-// ---- utils/hash.hpp:26-32 FNV-1a-64; utils/type_info.hpp:206-226,308-311 TypeIndex = hash of the spelled type name ----
+// ---- utils/hash.hpp:26-32 FNV-1a-64; utils/type_info.hpp:206-226,308-311 TypeIndex = hash of the spelled type name.
+// The helpers live in helios::utils like the reference's: GCC spells a type RELATIVE to the namespace of the function whose
+// __PRETTY_FUNCTION__ is read, so only from outside helios::ecs does helios::ecs::EntityDestroyedMsg keep its full name.
+}  // namespace helios::ecs
+namespace helios::utils {
 constexpr uint64_t Fnv1a(std::string_view s) noexcept {
   uint64_t h = 14695981039346656037ULL;
   for (const char c : s) h = (h ^ static_cast<uint64_t>(static_cast<unsigned char>(c))) * 1099511628211ULL;
   return h;
 }
-
 template <typename T>
 constexpr std::string_view TypeNameOf() noexcept {
   // GCC: "... [with T = ns::Type; std::string_view = ...]" — same extraction rule as the reference's GCC branch.
@@ -50,6 +53,11 @@ constexpr std::string_view TypeNameOf() noexcept {
 }
 template <typename T>
 constexpr uint64_t TypeIndexOf() noexcept { return Fnv1a(TypeNameOf<std::remove_cvref_t<T>>()); }
+}  // namespace helios::utils
+namespace helios::ecs {
+using utils::Fnv1a;
+using utils::TypeIndexOf;
+using utils::TypeNameOf;
 
 class GpuError : public std::runtime_error {
 public:
