@@ -141,7 +141,7 @@ __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, uin
 
 struct helios_gpu_world::FastScratch {
   DevBuf counters, stamp, info, srcloc, wlive, em, matrix, rowtot, obase, tfmin, ic_off;
-  DevBuf op_ck, op_level, op_table, next, prev, J, has_succ, cmin, submin, init_close, last_target;
+  DevBuf op_ck, op_level, op_table, next, prev, J, has_succ, cmin, submin, cmin_last, tfirst, tlast, init_close, last_target;
   DevBuf ch_slot, ch_ent, ch_src, stage, coffset, mh_keys, mh_vals;
   uint32_t stamp_cap = 0, batch = 0, mh_log2 = 0, stage_stride = 0;
   size_t mh_tables = ~size_t(0), stride_comps = 0;
@@ -179,58 +179,80 @@ __global__ void __launch_bounds__(256) k_classify(ClassifyArgs a) {
   __syncthreads();
   uint32_t invalid = 0, effective = 0, abort = 0;
   uint64_t touched_add = 0, touched_rem = 0;
-  for (uint32_t r = 0; r < kTile / 256; ++r) {
+  constexpr int R = kTile / 256;
+  // four commands per thread, every phase unrolled: the record loads, then the three random per-entity accesses
+  // (generation, location, batch stamp) of all four are in flight before the first dependent table-mask load
+  helios_gpu_command c[R];
+  uint32_t gen0[R], stamp0[R];
+  uint64_t loc0[R], mask[R];
+  bool in[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const uint32_t k = blockIdx.x * kTile + r * 256 + threadIdx.x;
+    in[r] = k < a.K;
+    c[r] = helios_gpu_command{};
+    if (in[r]) c[r] = a.cmd[k];
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const uint32_t idx = ent_index(c[r].entity);
+    gen0[r] = kInvalidGeneration; loc0[r] = kInvalidLoc; stamp0[r] = 0;
+    if (in[r] && idx < a.ent_capacity) {
+      gen0[r] = a.gen[idx];
+      loc0[r] = a.loc[idx];
+      stamp0[r] = atomicExch(&a.stamp[idx], a.batch);
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    mask[r] = 0;
+    if (in[r] && loc0[r] != kInvalidLoc && gen0[r] != kInvalidGeneration) mask[r] = a.tmask[uint32_t(loc0[r] >> 32)];
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
     const uint32_t k = blockIdx.x * kTile + r * 256 + threadIdx.x;
     uint32_t st = kNoTable, dt = kNoTable, fl = 0;
     uint64_t em = 0;
-    if (k < a.K) {
-      const helios_gpu_command c = a.cmd[k];
-      const uint32_t idx = ent_index(c.entity);
-      uint32_t gen0 = kInvalidGeneration;
-      uint64_t loc0 = kInvalidLoc;
-      if (idx < a.ent_capacity) {
-        gen0 = a.gen[idx];
-        loc0 = a.loc[idx];
-        if (atomicExch(&a.stamp[idx], a.batch) == a.batch) abort |= A_DUPS;  // a second command names this entity
-      }
-      const bool alive = gen0 != kInvalidGeneration && loc0 != kInvalidLoc;
-      const bool v = alive && ent_gen(c.entity) == gen0;  // EntityManager::Validate (entity/manager.hpp:410-418)
-      const uint64_t cm = c.component_mask;
+    if (in[r]) {
+      if (stamp0[r] == a.batch) abort |= A_DUPS;  // a second command names this entity
+      const bool alive = gen0[r] != kInvalidGeneration && loc0[r] != kInvalidLoc;
+      const bool v = alive && ent_gen(c[r].entity) == gen0[r];  // EntityManager::Validate (entity/manager.hpp:410-418)
+      const uint64_t cm = c[r].component_mask;
+      const uint32_t kind = c[r].kind;
       uint64_t w = 0;
       if (cm & ~a.registered_slots) abort |= A_BAD_MASK;
       if (!v) {
-        if (c.kind != HELIOS_GPU_CMD_TRY_DESTROY && c.kind != HELIOS_GPU_CMD_TRY_ADD && c.kind != HELIOS_GPU_CMD_TRY_REMOVE) ++invalid;
+        if (kind != HELIOS_GPU_CMD_TRY_DESTROY && kind != HELIOS_GPU_CMD_TRY_ADD && kind != HELIOS_GPU_CMD_TRY_REMOVE) ++invalid;
       } else {
-        const uint32_t t0 = uint32_t(loc0 >> 32);
-        const uint64_t mask = a.tmask[t0];
-        uint64_t dst = mask;
+        const uint64_t m0 = mask[r];
+        uint64_t dst = m0;
         fl = F_VALID;
         ++effective;
-        switch (c.kind) {
+        switch (kind) {
           case HELIOS_GPU_CMD_DESTROY:
           case HELIOS_GPU_CMD_TRY_DESTROY: fl |= F_DESTROY | F_MIG; break;
           case HELIOS_GPU_CMD_ADD:  // manager.hpp:1146-1203: every listed component written; world.hpp:1035 one message each
-            w = cm; dst = mask | cm; fl |= F_EM_ADD; em = cm; touched_add |= cm; break;
+            w = cm; dst = m0 | cm; fl |= F_EM_ADD; em = cm; touched_add |= cm; break;
           case HELIOS_GPU_CMD_TRY_ADD:  // manager.hpp:1205-1248: only the missing ones
-            w = cm & ~mask; dst = mask | cm; fl |= F_EM_ADD; em = w; touched_add |= cm; break;
+            w = cm & ~m0; dst = m0 | cm; fl |= F_EM_ADD; em = w; touched_add |= cm; break;
           case HELIOS_GPU_CMD_REMOVE:
-            dst = mask & ~cm; fl |= F_EM_REM; em = cm; touched_rem |= cm; break;
+            dst = m0 & ~cm; fl |= F_EM_REM; em = cm; touched_rem |= cm; break;
           case HELIOS_GPU_CMD_TRY_REMOVE:
-            dst = mask & ~cm; fl |= F_EM_REM; em = cm & mask; touched_rem |= cm; break;
+            dst = m0 & ~cm; fl |= F_EM_REM; em = cm & m0; touched_rem |= cm; break;
           case HELIOS_GPU_CMD_CLEAR: dst = 0; fl |= F_EM_CLEAR; break;
           default: break;
         }
-        if (!(fl & F_DESTROY) && dst != mask) fl |= F_MIG;
+        if (!(fl & F_DESTROY) && dst != m0) fl |= F_MIG;
         if (fl & F_MIG) {
-          st = t0;
+          st = uint32_t(loc0[r] >> 32);
           if (!(fl & F_DESTROY)) {
             dt = mask_lookup(a.mh, dst);
             if (dt == kNone) { abort |= A_UNKNOWN; dt = kNoTable; }  // GetOrCreateArchetype must create it: general path
           }
         }
       }
-      a.info[k] = pack_info(st, dt, fl, c.kind);
-      a.srcloc[k] = loc0;
+      a.info[k] = pack_info(st, dt, fl, kind);
+      a.srcloc[k] = loc0[r];
       a.wlive[k] = w;
       if (a.em) a.em[k] = em;
     }
@@ -278,20 +300,25 @@ struct ScanArgs {
 
 __global__ void __launch_bounds__(256) k_rowscan(const ScanArgs a) {
   __shared__ uint32_t s_last;
-  const uint32_t T = a.ntables, C = 2 + 2 * a.ncomps, nrows = 2 * T + C;
-  const uint32_t lane = threadIdx.x & 31u;
-  const uint32_t row = blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (row < nrows) {
-    uint32_t* r = a.matrix + size_t(row) * a.ntiles;
+  const uint32_t T = a.ntables, C = 2 + 2 * a.ncomps;
+  {  // one CTA per matrix row: exclusive prefix over the tiles, four consecutive tiles per thread and round
+    uint32_t* r = a.matrix + size_t(blockIdx.x) * a.ntiles;
     uint32_t running = 0;
-    for (uint32_t base = 0; base < a.ntiles; base += 32) {
-      const uint32_t i = base + lane;
-      const uint32_t v = i < a.ntiles ? r[i] : 0u;
-      const uint32_t inc = prim::warp_incl_scan(v);
-      if (i < a.ntiles) r[i] = running + inc - v;
-      running += __shfl_sync(0xFFFFFFFFu, inc, 31);
+    for (uint32_t base = 0; base < a.ntiles; base += 1024) {
+      const uint32_t i0 = base + threadIdx.x * 4;
+      uint32_t v[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) v[q] = i0 + q < a.ntiles ? r[i0 + q] : 0u;
+      uint32_t total;
+      uint32_t off = running + prim::block_excl_scan(v[0] + v[1] + v[2] + v[3], &total);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (i0 + q < a.ntiles) r[i0 + q] = off;
+        off += v[q];
+      }
+      running += total;
     }
-    if (lane == 0) a.rowtot[row] = running;
+    if (threadIdx.x == 0) a.rowtot[blockIdx.x] = running;
   }
   __threadfence();
   __syncthreads();
@@ -346,17 +373,19 @@ struct EmitArgs {
 };
 
 __global__ void __launch_bounds__(256) k_emit_ops(const EmitArgs a) {
-  extern __shared__ uint32_t s_mem[];  // s_w[8][2T] | s_obase[T] | s_c0[T]
+  extern __shared__ uint32_t s_mem[];  // s_w[8][2T] | s_m[8][2T] | s_obase[T] | s_c0[T]
   if (a.counters->abort) return;
   const uint32_t T = a.ntables;
   uint32_t* s_w = s_mem;
-  uint32_t* s_obase = s_mem + 8 * 2 * T;
+  uint32_t* s_m = s_mem + 8 * 2 * T;
+  uint32_t* s_obase = s_m + 8 * 2 * T;
   uint32_t* s_c0 = s_obase + T;
   const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-  for (uint32_t i = threadIdx.x; i < 8 * 2 * T; i += 256) s_w[i] = 0;
+  for (uint32_t i = threadIdx.x; i < 2 * 8 * 2 * T; i += 256) s_mem[i] = 0;
   for (uint32_t i = threadIdx.x; i < T; i += 256) { s_obase[i] = a.obase[i]; s_c0[i] = a.tcount0[i]; }
   __syncthreads();
-  uint32_t* my = s_w + wid * 2 * T;
+  uint32_t* my = s_w + wid * 2 * T;   // ops of each (kind, table) row before the warp's current round
+  uint32_t* mm = s_m + wid * 2 * T;   // lane masks of the current round per (kind, table); zero between rounds
   uint32_t st[4], dt[4];
   const uint32_t k0 = blockIdx.x * kTile + wid * 128 + lane;
 #pragma unroll
@@ -387,30 +416,39 @@ __global__ void __launch_bounds__(256) k_emit_ops(const EmitArgs a) {
   for (int r = 0; r < 4; ++r) {
     const uint32_t k = k0 + r * 32;
     const bool hasR = st[r] != kNoTable, hasA = dt[r] != kNoTable;
-    uint32_t todoR = __ballot_sync(0xFFFFFFFFu, hasR), todoA = __ballot_sync(0xFFFFFFFFu, hasA);
-    while (todoR | todoA) {  // one iteration per distinct table named by the warp's 32 commands
-      const uint32_t key = todoR ? __shfl_sync(0xFFFFFFFFu, st[r], __ffs(todoR) - 1) : __shfl_sync(0xFFFFFFFFu, dt[r], __ffs(todoA) - 1);
-      const uint32_t mR = __ballot_sync(0xFFFFFFFFu, hasR && st[r] == key);
-      const uint32_t mA = __ballot_sync(0xFFFFFFFFu, hasA && dt[r] == key);
-      const uint32_t baseR = my[key], baseA = my[T + key];
-      const bool inR = (mR >> lane) & 1u, inA = (mA >> lane) & 1u;
-      if (inR || inA) {
-        const uint32_t rb = baseR + __popc(mR & lt), ab = baseA + __popc(mA & lt);  // ops of this table before mine
-        const uint32_t j = s_obase[key] + rb + ab;
-        const uint32_t size_before = s_c0[key] + ab - rb;
-        a.op_ck[j] = (k << 1) | (inA ? 1u : 0u);
-        a.op_level[j] = inA ? size_before : size_before - 1u;
-        a.op_table[j] = key;
-        a.next[j] = kNone;
-        a.J[j] = kUnresolved;
-        a.has_succ[j] = 0;
-      }
-      __syncwarp();
-      if (lane == 0) { my[key] = baseR + __popc(mR); my[T + key] = baseA + __popc(mA); }
-      __syncwarp();
-      todoR &= ~mR;
-      todoA &= ~mA;
+    // lanes removing from / appending to the same table as me; the group leaders publish the masks so that the lanes of the
+    // OTHER kind can count them too (a table's sequence interleaves its Removes and Appends in command order)
+    const uint32_t pR = __match_any_sync(0xFFFFFFFFu, st[r]), pA = __match_any_sync(0xFFFFFFFFu, dt[r]);
+    const bool leadR = hasR && lane == uint32_t(__ffs(pR) - 1), leadA = hasA && lane == uint32_t(__ffs(pA) - 1);
+    if (leadR) mm[st[r]] = pR;
+    if (leadA) mm[T + dt[r]] = pA;
+    __syncwarp();
+    if (hasR) {
+      const uint32_t key = st[r];
+      const uint32_t rb = my[key] + __popc(pR & lt), ab = my[T + key] + __popc(mm[T + key] & lt);
+      const uint32_t j = s_obase[key] + rb + ab;
+      a.op_ck[j] = k << 1;
+      a.op_level[j] = s_c0[key] + ab - rb - 1u;  // closes the tail slot: size before - 1
+      a.op_table[j] = key;
+      a.next[j] = kNone;
+      a.J[j] = kUnresolved;
+      a.has_succ[j] = 0;
     }
+    if (hasA) {
+      const uint32_t key = dt[r];
+      const uint32_t rb = my[key] + __popc(mm[key] & lt), ab = my[T + key] + __popc(pA & lt);
+      const uint32_t j = s_obase[key] + rb + ab;
+      a.op_ck[j] = (k << 1) | 1u;
+      a.op_level[j] = s_c0[key] + ab - rb;       // opens the slot at the current size
+      a.op_table[j] = key;
+      a.next[j] = kNone;
+      a.J[j] = kUnresolved;
+      a.has_succ[j] = 0;
+    }
+    __syncwarp();
+    if (leadR) { my[st[r]] += __popc(pR); mm[st[r]] = 0; }
+    if (leadA) { my[T + dt[r]] += __popc(pA); mm[T + dt[r]] = 0; }
+    __syncwarp();
   }
 }
 
@@ -426,8 +464,11 @@ struct PairArgs {
   const uint32_t* op_table;
   uint32_t* prev;
   uint32_t* next;
-  uint64_t* cmin;     // [chunk] min V
-  uint64_t* submin;   // [op / 32] min V
+  uint64_t* cmin;       // [chunk] min V over the chunk
+  uint64_t* submin;     // [op / 32] min V
+  uint64_t* cmin_last;  // [chunk] min V over the ops of the chunk's LAST table
+  uint32_t* tfirst;     // [chunk] table of the chunk's first / last op
+  uint32_t* tlast;
   const uint32_t* tfmin;
   const uint32_t* ic_off;
   uint32_t* init_close;  // window slot -> the Remove that closes the initially occupied slot
@@ -437,8 +478,16 @@ struct PairArgs {
 __device__ __forceinline__ uint64_t op_value(const PairArgs& a, uint32_t i) {
   return (uint64_t(a.op_table[i]) << 32) | (a.op_level[i] + ((a.op_ck[i] & 1u) ? 0u : 1u));
 }
-__device__ __forceinline__ void pair_found(const PairArgs& a, uint32_t j, uint32_t t, uint32_t s, uint32_t i, uint64_t vi) {
-  if (i != kNone && uint32_t(vi >> 32) == t) {
+__device__ __forceinline__ uint64_t warp_min_u64(uint64_t m) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const uint64_t x = __shfl_xor_sync(0xFFFFFFFFu, m, o);
+    m = x < m ? x : m;
+  }
+  return m;
+}
+__device__ __forceinline__ void pair_found(const PairArgs& a, uint32_t j, uint32_t t, uint32_t s, uint32_t i) {
+  if (i != kNone) {
     a.prev[j] = i;
     a.next[i] = j;
   } else {  // nothing of this table before j at or below s: the Remove closes the slot's initial occupant
@@ -447,9 +496,43 @@ __device__ __forceinline__ void pair_found(const PairArgs& a, uint32_t j, uint32
   }
 }
 
-__global__ void __launch_bounds__(kChunk) k_pair_local(const PairArgs a) {
+// K4: per-chunk and per-32 minima of V (a chunk = 1024 consecutive ops of the (table, command) order).
+__global__ void __launch_bounds__(kChunk) k_chunk_min(const PairArgs a) {
+  __shared__ uint64_t s_sub[kChunk / 32], s_sub_last[kChunk / 32];
+  __shared__ uint32_t s_tlast;
+  if (a.counters->abort) return;
+  const uint32_t M = a.counters->M;
+  const uint32_t base = blockIdx.x * kChunk;
+  if (base >= M) return;
+  const uint32_t tid = threadIdx.x, wid = tid >> 5, lane = tid & 31u;
+  const uint32_t j = base + tid;
+  const uint32_t last = min(base + kChunk, M) - 1;
+  if (tid == 0) {
+    s_tlast = a.op_table[last];
+    a.tfirst[blockIdx.x] = a.op_table[base];
+    a.tlast[blockIdx.x] = s_tlast;
+  }
+  __syncthreads();
+  uint64_t v = ~0ull;
+  if (j < M) v = op_value(a, j);
+  const uint64_t m = warp_min_u64(v);
+  const uint64_t ml = warp_min_u64(uint32_t(v >> 32) == s_tlast ? v : ~0ull);
+  if (lane == 0) { s_sub[wid] = m; s_sub_last[wid] = ml; a.submin[base / 32 + wid] = m; }
+  __syncthreads();
+  if (wid == 0) {
+    const uint64_t c = warp_min_u64(s_sub[lane]), cl = warp_min_u64(s_sub_last[lane]);
+    if (lane == 0) { a.cmin[blockIdx.x] = c; a.cmin_last[blockIdx.x] = cl; }
+  }
+}
+
+// K5: the pairing itself.  Inside the chunk from shared memory; a Remove with no opener in its chunk first compares its slot
+// with the lowest size its table reached in all EARLIER chunks (a prefix minimum over the chunk minima, one warp per
+// CTA): below that, no earlier op can have opened the slot — the common case of a shrinking table — and only otherwise
+// the opener is searched in the earlier chunks.
+__global__ void __launch_bounds__(kChunk) k_pair(const PairArgs a) {
   __shared__ uint64_t s_v[kChunk];
   __shared__ uint64_t s_sub[kChunk / 32];
+  __shared__ uint64_t s_pm;  // min V of the first table's ops in earlier chunks (all-ones: none)
   if (a.counters->abort) return;
   const uint32_t M = a.counters->M;
   const uint32_t base = blockIdx.x * kChunk;
@@ -463,23 +546,35 @@ __global__ void __launch_bounds__(kChunk) k_pair_local(const PairArgs a) {
     v = (uint64_t(t) << 32) | (level + ((ck & 1u) ? 0u : 1u));
   }
   s_v[tid] = v;
-  uint64_t m = v;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const uint64_t x = __shfl_xor_sync(0xFFFFFFFFu, m, o);
-    m = x < m ? x : m;
-  }
-  if (lane == 0) { s_sub[wid] = m; a.submin[base / 32 + wid] = m; }
-  __syncthreads();
-  if (wid == 0) {
-    uint64_t c = s_sub[lane];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const uint64_t x = __shfl_xor_sync(0xFFFFFFFFu, c, o);
-      c = x < c ? x : c;
+  const uint64_t m = warp_min_u64(v);
+  if (lane == 0) s_sub[wid] = m;
+  const uint32_t t_first = a.tfirst[blockIdx.x];
+  if (wid == 0) {  // prefix minimum of the first table over the earlier chunks, 32 chunks per step, newest first
+    uint64_t pm = ~0ull;
+    for (int c0 = int(blockIdx.x) - 1; c0 >= 0; c0 -= 32) {
+      const int c = c0 - int(lane);
+      uint64_t x = ~0ull;
+      bool stop = false;
+      if (c >= 0) {
+        if (a.tlast[c] == t_first) {
+          x = a.cmin_last[c];
+          stop = a.tfirst[c] != t_first;  // the table starts inside chunk c
+        } else {
+          stop = true;  // chunk c ends with an earlier table: the segment starts at a later chunk
+        }
+      } else {
+        stop = true;
+      }
+      const uint32_t stops = __ballot_sync(0xFFFFFFFFu, stop);
+      // only the chunks newer than (and including, if it holds ops of the table) the first stopping chunk count
+      const uint32_t first_stop = stops ? uint32_t(__ffs(stops) - 1) : 32u;
+      if (lane > first_stop) x = ~0ull;
+      pm = min(pm, warp_min_u64(x));
+      if (stops) break;
     }
-    if (lane == 0) a.cmin[blockIdx.x] = c;
+    if (lane == 0) s_pm = pm;
   }
+  __syncthreads();
   if (j >= M || (ck & 1u)) return;  // only Removes ask
   const uint64_t target = (uint64_t(t) << 32) | level;
   int found = -1;
@@ -492,29 +587,28 @@ __global__ void __launch_bounds__(kChunk) k_pair_local(const PairArgs a) {
           if (s_v[i] <= target) { found = i; break; }
         break;
       }
-  if (found >= 0) pair_found(a, j, t, level, base + uint32_t(found), s_v[found]);
-  else if (base == 0) pair_found(a, j, t, level, kNone, 0);
-  else a.prev[j] = kPending;  // the opener, if any, lies in an earlier chunk
-}
-
-__global__ void __launch_bounds__(256) k_pair_far(const PairArgs a) {
-  if (a.counters->abort) return;
-  const uint32_t M = a.counters->M;
-  const uint32_t j = blockIdx.x * 256 + threadIdx.x;
-  if (j >= M || (a.op_ck[j] & 1u) || a.prev[j] != kPending) return;
-  const uint32_t t = a.op_table[j], s = a.op_level[j];
-  const uint64_t target = (uint64_t(t) << 32) | s;
-  for (int c = int(j / kChunk) - 1; c >= 0; --c) {
+  if (found >= 0) {
+    pair_found(a, j, t, level, uint32_t(s_v[found] >> 32) == t ? base + uint32_t(found) : kNone);
+    return;
+  }
+  if (t != t_first || s_pm > target) {  // the table starts inside this chunk, or never was that small before
+    pair_found(a, j, t, level, kNone);
+    return;
+  }
+  for (int c = int(blockIdx.x) - 1; c >= 0; --c) {  // rare: the opener lies in an earlier chunk
     if (a.cmin[c] > target) continue;
     for (int b = c * int(kChunk / 32) + int(kChunk / 32) - 1; b >= c * int(kChunk / 32); --b) {
       if (a.submin[b] > target) continue;
       for (int i = b * 32 + 31; i >= b * 32; --i) {
         const uint64_t vi = op_value(a, uint32_t(i));
-        if (vi <= target) { pair_found(a, j, t, s, uint32_t(i), vi); return; }
+        if (vi <= target) {
+          pair_found(a, j, t, level, uint32_t(vi >> 32) == t ? uint32_t(i) : kNone);
+          return;
+        }
       }
     }
   }
-  pair_found(a, j, t, s, kNone, 0);
+  pair_found(a, j, t, level, kNone);
 }
 
 // ================================================================================================================
@@ -608,22 +702,69 @@ __global__ void __launch_bounds__(256) k_resolve(const ResolveView v) {
   if (threadIdx.x == 0 && rounds) atomicMax(&v.counters->rounds, rounds);
 }
 
-struct FinalArgs {
+// ================================================================================================================
+// K8 / K9 — final occupants + row mover.  K8, one thread per op: which slot does the op fill for good, with which entity,
+// and where do that entity's component values sit (its pre-batch row: shared columns of MigrateEntity, manager.hpp:1912-
+// 1925; the swapped row of Archetype::Remove, archetype.hpp:418-431) — then the row is copied at once.  A destination slot
+// at or above the table's pre-batch size is fresh (nobody reads it): the row goes there directly.  A hole fill lands on a slot
+// whose old contents another record may still need: it goes to the staging buffer and K9 writes it out.  Entity locations
+// are final here too (nothing reads them before K10).
+// ================================================================================================================
+struct MoveArgs {
   ResolveView v;
   const helios_gpu_command* cmd;
+  const uint64_t* tmask;
+  void* const* tcols;
   helios_gpu_entity_t* const* tents;
+  const uint32_t* csize;
+  const uint32_t* coffset;
+  uint8_t* stage;
+  uint32_t stride;
+  uint64_t* loc;
   uint32_t* ch_slot;             // per op: the slot it fills for good (kNone: writes no row)
-  helios_gpu_entity_t* ch_ent;   // ... with this entity
-  uint64_t* ch_src;              // ... whose component values sit at this pre-batch location (table << 32 | row)
+  helios_gpu_entity_t* ch_ent;   // ... with this entity (staged records only)
+  uint32_t* ch_t0;               // ... whose values came from this table (staged records only)
 };
 
-__global__ void __launch_bounds__(256) k_final(const FinalArgs a) {
+// Copies the components both tables hold, up to four per round: all loads are issued before the first store.
+template <typename SrcOf, typename DstOf>
+__device__ __forceinline__ uint32_t copy_row(uint64_t m, const uint32_t* __restrict__ csize, SrcOf&& src_of, DstOf&& dst_of) {
+  uint32_t bytes = 0;
+  while (m) {
+    const uint8_t* sp[4];
+    uint8_t* dp[4];
+    uint32_t sz[4];
+    uint64_t val[4];
+    int n = 0;
+    for (; n < 4 && m; ++n) {
+      const int s = __ffsll(static_cast<long long>(m)) - 1;
+      m &= m - 1;
+      sz[n] = csize[s];
+      sp[n] = src_of(s, sz[n]);
+      dp[n] = dst_of(s, sz[n]);
+      bytes += sz[n];
+    }
+    for (int i = 0; i < n; ++i) {
+      if (sz[i] == 4) val[i] = *reinterpret_cast<const uint32_t*>(sp[i]);
+      else if (sz[i] == 8) val[i] = *reinterpret_cast<const uint64_t*>(sp[i]);
+    }
+    for (int i = 0; i < n; ++i) {
+      if (sz[i] == 4) *reinterpret_cast<uint32_t*>(dp[i]) = uint32_t(val[i]);
+      else if (sz[i] == 8) *reinterpret_cast<uint64_t*>(dp[i]) = val[i];
+      else copy_bytes(dp[i], sp[i], sz[i]);
+    }
+  }
+  return bytes;
+}
+
+__global__ void __launch_bounds__(256) k_final_gather(const MoveArgs a) {
   const ResolveView& v = a.v;
   if (v.counters->abort) return;
   const uint32_t j = blockIdx.x * 256 + threadIdx.x;
-  uint32_t slot = kNone;
+  uint32_t slot = kNone, bytes = 0;
   if (j < v.counters->M) {
     const uint32_t ck = v.op_ck[j];
+    const uint32_t t = v.op_table[j];
     helios_gpu_entity_t e = 0;
     uint64_t src = 0;
     if (ck & 1u) {  // Append: a slot that is never closed keeps its opener
@@ -632,7 +773,7 @@ __global__ void __launch_bounds__(256) k_final(const FinalArgs a) {
         e = a.cmd[ck >> 1].entity;
         src = v.srcloc[ck >> 1];
       }
-    } else if (!table_ends_empty(v, v.op_table[j])) {  // Remove: the LAST move into a surviving slot decides its occupant
+    } else if (!table_ends_empty(v, t)) {  // Remove: the LAST move into a surviving slot decides its occupant
       const uint64_t I = v.J[j];
       uint64_t X = closed_by(v, j);
       if (I != X && !v.has_succ[j] && init_close_of(v, I) == kNone) {
@@ -644,10 +785,10 @@ __global__ void __launch_bounds__(256) k_final(const FinalArgs a) {
             src = v.srcloc[k];
             break;
           }
-          const uint32_t t = uint32_t(X >> 32), s = uint32_t(X);
-          const uint32_t lt = v.last_target[v.ic_off[t] + (s - v.tfmin[t])];
+          const uint32_t tx = uint32_t(X >> 32), s = uint32_t(X);
+          const uint32_t lt = v.last_target[v.ic_off[tx] + (s - v.tfmin[tx])];
           if (lt == 0) {  // never re-filled: still its pre-batch occupant
-            e = a.tents[t][s];
+            e = a.tents[tx][s];
             src = X;
             break;
           }
@@ -656,93 +797,46 @@ __global__ void __launch_bounds__(256) k_final(const FinalArgs a) {
       }
     }
     a.ch_slot[j] = slot;
-    a.ch_ent[j] = e;
-    a.ch_src[j] = src;
+    if (slot != kNone) {
+      const uint32_t t0 = uint32_t(src >> 32), r0 = uint32_t(src);
+      const bool direct = slot >= v.tcount0[t];
+      a.loc[ent_index(e)] = (uint64_t(t) << 32) | slot;
+      if (direct) {
+        a.tents[t][slot] = e;
+      } else {
+        a.ch_ent[j] = e;
+        a.ch_t0[j] = t0;
+      }
+      uint8_t* st = a.stage + size_t(j) * a.stride;
+      bytes = 8 + copy_row(a.tmask[t] & a.tmask[t0], a.csize,
+                           [&](int s, uint32_t sz) { return static_cast<const uint8_t*>(a.tcols[size_t(t0) * 64 + s]) + size_t(r0) * sz; },
+                           [&](int s, uint32_t sz) {
+                             return direct ? static_cast<uint8_t*>(a.tcols[size_t(t) * 64 + s]) + size_t(slot) * sz : st + a.coffset[s];
+                           });
+    }
   }
   const uint32_t n = __popc(__ballot_sync(0xFFFFFFFFu, slot != kNone));
-  if ((threadIdx.x & 31u) == 0 && n) atomicAdd(&v.counters->n_changed, n);
+  bytes = __reduce_add_sync(0xFFFFFFFFu, bytes);
+  if ((threadIdx.x & 31u) == 0 && n) {
+    atomicAdd(&v.counters->n_changed, n);
+    atomicAdd(&v.counters->moved_bytes, 2ull * bytes);
+  }
 }
 
-// ================================================================================================================
-// K8 / K9 — row mover.  One lane per record: component values the entity carries over from where it lived BEFORE the batch
-// (shared columns of MigrateEntity, manager.hpp:1912-1925; the swapped row of Archetype::Remove, archetype.hpp:418-431).
-// A destination slot at or above the table's pre-batch size is fresh — nobody reads it — so the row goes there directly;
-// a hole fill lands on a slot whose old contents another record may still need and goes through the staging buffer.
-// ================================================================================================================
-struct MoveArgs {
-  const uint32_t* op_table;
-  const uint32_t* ch_slot;
-  const helios_gpu_entity_t* ch_ent;
-  const uint64_t* ch_src;
-  const uint32_t* tcount0;
-  const uint64_t* tmask;
-  void* const* tcols;
-  helios_gpu_entity_t* const* tents;
-  const uint32_t* csize;
-  const uint32_t* coffset;
-  uint8_t* stage;
-  uint32_t stride;
-  uint64_t* loc;
-  FastCounters* counters;
-};
-
-template <bool kScatter>
-__global__ void __launch_bounds__(256) k_move(const MoveArgs a) {
-  if (a.counters->abort) return;
-  const uint32_t M = a.counters->M;
-  uint32_t bytes = 0;
+__global__ void __launch_bounds__(256) k_scatter(const MoveArgs a) {
+  const ResolveView& v = a.v;
+  if (v.counters->abort) return;
+  const uint32_t M = v.counters->M;
   for (uint32_t j = blockIdx.x * 256 + threadIdx.x; j < M; j += gridDim.x * 256) {
     const uint32_t slot = a.ch_slot[j];
     if (slot == kNone) continue;
-    const uint32_t t = a.op_table[j];
-    const helios_gpu_entity_t e = a.ch_ent[j];
-    const bool direct = slot >= a.tcount0[t];
-    if constexpr (kScatter) {
-      a.loc[ent_index(e)] = (uint64_t(t) << 32) | slot;
-      if (direct) continue;
-      a.tents[t][slot] = e;
-    } else if (direct) {
-      a.tents[t][slot] = e;
-    }
-    const uint64_t src = a.ch_src[j];
-    const uint32_t t0 = uint32_t(src >> 32), r0 = uint32_t(src);
-    uint64_t m = a.tmask[t] & a.tmask[t0];
-    uint8_t* st = a.stage + size_t(j) * a.stride;
-    while (m) {  // up to four components per round: all loads are issued before the first store
-      const uint8_t* sp[4];
-      uint8_t* dp[4];
-      uint32_t sz[4];
-      uint64_t val[4];
-      int n = 0;
-      for (; n < 4 && m; ++n) {
-        const int s = __ffsll(static_cast<long long>(m)) - 1;
-        m &= m - 1;
-        sz[n] = a.csize[s];
-        uint8_t* col_dst = static_cast<uint8_t*>(a.tcols[size_t(t) * 64 + s]) + size_t(slot) * sz[n];
-        if constexpr (kScatter) {
-          sp[n] = st + a.coffset[s];
-          dp[n] = col_dst;
-        } else {
-          sp[n] = static_cast<const uint8_t*>(a.tcols[size_t(t0) * 64 + s]) + size_t(r0) * sz[n];
-          dp[n] = direct ? col_dst : st + a.coffset[s];
-          bytes += sz[n];
-        }
-      }
-      for (int i = 0; i < n; ++i) {
-        if (sz[i] == 4) val[i] = *reinterpret_cast<const uint32_t*>(sp[i]);
-        else if (sz[i] == 8) val[i] = *reinterpret_cast<const uint64_t*>(sp[i]);
-      }
-      for (int i = 0; i < n; ++i) {
-        if (sz[i] == 4) *reinterpret_cast<uint32_t*>(dp[i]) = uint32_t(val[i]);
-        else if (sz[i] == 8) *reinterpret_cast<uint64_t*>(dp[i]) = val[i];
-        else copy_bytes(dp[i], sp[i], sz[i]);
-      }
-    }
-    if constexpr (!kScatter) bytes += 8;
-  }
-  if constexpr (!kScatter) {
-    bytes = __reduce_add_sync(0xFFFFFFFFu, bytes);
-    if ((threadIdx.x & 31u) == 0 && bytes) atomicAdd(&a.counters->moved_bytes, 2ull * bytes);
+    const uint32_t t = v.op_table[j];
+    if (slot >= v.tcount0[t]) continue;  // written directly by K8
+    a.tents[t][slot] = a.ch_ent[j];
+    const uint8_t* st = a.stage + size_t(j) * a.stride;
+    copy_row(a.tmask[t] & a.tmask[a.ch_t0[j]], a.csize,
+             [&](int s, uint32_t) { return st + a.coffset[s]; },
+             [&](int s, uint32_t sz) { return static_cast<uint8_t*>(a.tcols[size_t(t) * 64 + s]) + size_t(slot) * sz; });
   }
 }
 
@@ -967,8 +1061,9 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
   NEED(S.J, Mmax * 8); NEED(S.has_succ, Mmax);
   const size_t nchunks = (Mmax + kChunk - 1) / kChunk;
   NEED(S.cmin, nchunks * 8); NEED(S.submin, nchunks * (kChunk / 32) * 8);
+  NEED(S.cmin_last, nchunks * 8); NEED(S.tfirst, nchunks * 4); NEED(S.tlast, nchunks * 4);
   NEED(S.init_close, (size_t(K) + 16) * 4); NEED(S.last_target, (size_t(K) + 16) * 4);
-  NEED(S.ch_slot, Mmax * 4); NEED(S.ch_ent, Mmax * 8); NEED(S.ch_src, Mmax * 8);
+  NEED(S.ch_slot, Mmax * 4); NEED(S.ch_ent, Mmax * 8); NEED(S.ch_src, Mmax * 4);
   NEED(S.stage, Mmax * S.stage_stride);
   HG_CUDA(w, w->d_free.reserve((w->free_count + K) * 4, w->free_count * 4, st, true));
   HG_CUDA(w, cudaMemsetAsync(S.counters.ptr, 0, sizeof(FastCounters), st));
@@ -1003,32 +1098,28 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
     sa.room[c] = uint32_t(std::min<uint64_t>(ch->cur.bytes / 8 - ch->cur_count, 0xFFFFFFFFull));
     fa.chan_dst[c] = ch->cur.as<helios_gpu_entity_t>() + ch->cur_count;
   }
-  k_rowscan<<<(nrows + 7) / 8, 256, 0, st>>>(sa);
+  k_rowscan<<<nrows, 256, 0, st>>>(sa);
 
   // ---- K3 .. K10 ----------------------------------------------------------------------------------------------------
   EmitArgs ea{K, ntiles, T, S.info.as<uint64_t>(), S.matrix.as<uint32_t>(), S.obase.as<uint32_t>(), w->d_tcount.as<uint32_t>(),
               S.op_ck.as<uint32_t>(), S.op_level.as<uint32_t>(), S.op_table.as<uint32_t>(), S.next.as<uint32_t>(),
               S.J.as<uint64_t>(), S.has_succ.as<uint8_t>(), dc};
-  k_emit_ops<<<ntiles, 256, (8 * 2 * T + 2 * T) * 4, st>>>(ea);
+  k_emit_ops<<<ntiles, 256, (2 * 8 * 2 * T + 2 * T) * 4, st>>>(ea);
   PairArgs pa{S.op_ck.as<uint32_t>(), S.op_level.as<uint32_t>(), S.op_table.as<uint32_t>(), S.prev.as<uint32_t>(), S.next.as<uint32_t>(),
-              S.cmin.as<uint64_t>(), S.submin.as<uint64_t>(), S.tfmin.as<uint32_t>(), S.ic_off.as<uint32_t>(),
-              S.init_close.as<uint32_t>(), dc};
-  k_pair_local<<<uint32_t(nchunks), kChunk, 0, st>>>(pa);
+              S.cmin.as<uint64_t>(), S.submin.as<uint64_t>(), S.cmin_last.as<uint64_t>(), S.tfirst.as<uint32_t>(),
+              S.tlast.as<uint32_t>(), S.tfmin.as<uint32_t>(), S.ic_off.as<uint32_t>(), S.init_close.as<uint32_t>(), dc};
+  k_chunk_min<<<uint32_t(nchunks), kChunk, 0, st>>>(pa);
+  k_pair<<<uint32_t(nchunks), kChunk, 0, st>>>(pa);
   const uint32_t op_blocks = uint32_t((Mmax + 255) / 256);
-  k_pair_far<<<op_blocks, 256, 0, st>>>(pa);
   ResolveView rv{S.op_ck.as<uint32_t>(), S.op_level.as<uint32_t>(), S.op_table.as<uint32_t>(), S.prev.as<uint32_t>(), S.next.as<uint32_t>(),
                  S.srcloc.as<uint64_t>(), S.tfmin.as<uint32_t>(), w->d_tcount.as<uint32_t>(), S.ic_off.as<uint32_t>(),
                  S.init_close.as<uint32_t>(), S.J.as<uint64_t>(), S.has_succ.as<uint8_t>(), S.last_target.as<uint32_t>(), dc};
   k_resolve<<<op_blocks, 256, 0, st>>>(rv);
-  FinalArgs fin{rv, d_cmds, w->d_tents.as<helios_gpu_entity_t*>(), S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(),
-                S.ch_src.as<uint64_t>()};
-  k_final<<<op_blocks, 256, 0, st>>>(fin);
-  MoveArgs ma{S.op_table.as<uint32_t>(), S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(), S.ch_src.as<uint64_t>(),
-              w->d_tcount.as<uint32_t>(), w->d_tmask.as<uint64_t>(), w->d_tcols.as<void*>(), w->d_tents.as<helios_gpu_entity_t*>(),
-              w->d_csize.as<uint32_t>(), S.coffset.as<uint32_t>(), S.stage.as<uint8_t>(), S.stage_stride, w->d_loc.as<uint64_t>(), dc};
-  const uint32_t mover_grid = std::min<uint32_t>(op_blocks, uint32_t(w->sm_count) * 16u);
-  k_move<false><<<mover_grid, 256, 0, st>>>(ma);
-  k_move<true><<<mover_grid, 256, 0, st>>>(ma);
+  MoveArgs ma{rv, d_cmds, w->d_tmask.as<uint64_t>(), w->d_tcols.as<void*>(), w->d_tents.as<helios_gpu_entity_t*>(),
+              w->d_csize.as<uint32_t>(), S.coffset.as<uint32_t>(), S.stage.as<uint8_t>(), S.stage_stride, w->d_loc.as<uint64_t>(),
+              S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(), S.ch_src.as<uint32_t>()};
+  k_final_gather<<<op_blocks, 256, 0, st>>>(ma);
+  k_scatter<<<std::min<uint32_t>(op_blocks, uint32_t(w->sm_count) * 16u), 256, 0, st>>>(ma);
   fa.cmd = d_cmds; fa.payload = d_payload; fa.K = K; fa.ntiles = ntiles; fa.ntables = T; fa.ncomps = ncomps;
   fa.emit_messages = w->builtin_messages ? 1u : 0u;
   fa.info = S.info.as<uint64_t>(); fa.em = w->builtin_messages ? S.em.as<uint64_t>() : nullptr; fa.wlive = S.wlive.as<uint64_t>();
@@ -1050,7 +1141,7 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
     return HELIOS_GPU_OK;
   }
   ++w->mutation_epoch;
-  w->launches += 10;
+  w->launches += 9;
   for (uint32_t t = 0; t < T; ++t) w->tables[t].count = w->tables[t].count + hc.tapp[t] - hc.trem[t];
   const uint32_t n_destroy = hc.chan_total[0];
   if (n_destroy) {
