@@ -141,7 +141,7 @@ __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, uin
 
 struct helios_gpu_world::FastScratch {
   DevBuf counters, stamp, info, srcloc, wlive, em, matrix, rowtot, obase, tfmin, ic_off;
-  DevBuf op_ck, op_level, op_table, next, prev, J, has_succ, cmin, submin, cmin_last, tfirst, tlast, init_close, last_target;
+  DevBuf ops, next, prev, J, has_succ, cmin, submin, cmin_last, tfirst, tlast, init_close, last_target;
   DevBuf ch_slot, ch_ent, ch_src, stage, coffset, mh_keys, mh_vals;
   uint32_t stamp_cap = 0, batch = 0, mh_log2 = 0, stage_stride = 0;
   size_t mh_tables = ~size_t(0), stride_comps = 0;
@@ -363,12 +363,7 @@ struct EmitArgs {
   const uint32_t* matrix;   // exclusive tile prefixes
   const uint32_t* obase;
   const uint32_t* tcount0;
-  uint32_t* op_ck;          // command index << 1 | kind (1 = Append, 0 = Remove)
-  uint32_t* op_level;
-  uint32_t* op_table;
-  uint32_t* next;           // Append: the Remove that closes the slot it opened (kNone: survives)
-  uint64_t* J;              // Remove: instance the removed entity lives in at that time
-  uint8_t* has_succ;
+  uint4* ops;               // {command index << 1 | kind (1 = Append, 0 = Remove), slot ("level"), table, -}
   const FastCounters* counters;
 };
 
@@ -427,23 +422,13 @@ __global__ void __launch_bounds__(256) k_emit_ops(const EmitArgs a) {
       const uint32_t key = st[r];
       const uint32_t rb = my[key] + __popc(pR & lt), ab = my[T + key] + __popc(mm[T + key] & lt);
       const uint32_t j = s_obase[key] + rb + ab;
-      a.op_ck[j] = k << 1;
-      a.op_level[j] = s_c0[key] + ab - rb - 1u;  // closes the tail slot: size before - 1
-      a.op_table[j] = key;
-      a.next[j] = kNone;
-      a.J[j] = kUnresolved;
-      a.has_succ[j] = 0;
+      a.ops[j] = make_uint4(k << 1, s_c0[key] + ab - rb - 1u, key, 0u);  // closes the tail slot: size before - 1
     }
     if (hasA) {
       const uint32_t key = dt[r];
       const uint32_t rb = my[key] + __popc(mm[key] & lt), ab = my[T + key] + __popc(pA & lt);
       const uint32_t j = s_obase[key] + rb + ab;
-      a.op_ck[j] = (k << 1) | 1u;
-      a.op_level[j] = s_c0[key] + ab - rb;       // opens the slot at the current size
-      a.op_table[j] = key;
-      a.next[j] = kNone;
-      a.J[j] = kUnresolved;
-      a.has_succ[j] = 0;
+      a.ops[j] = make_uint4((k << 1) | 1u, s_c0[key] + ab - rb, key, 0u);  // opens the slot at the current size
     }
     __syncwarp();
     if (leadR) { my[st[r]] += __popc(pR); mm[st[r]] = 0; }
@@ -459,9 +444,7 @@ __global__ void __launch_bounds__(256) k_emit_ops(const EmitArgs a) {
 // backward search stops at the table boundary by itself.
 // ================================================================================================================
 struct PairArgs {
-  const uint32_t* op_ck;
-  const uint32_t* op_level;
-  const uint32_t* op_table;
+  const uint4* ops;
   uint32_t* prev;
   uint32_t* next;
   uint64_t* cmin;       // [chunk] min V over the chunk
@@ -475,9 +458,8 @@ struct PairArgs {
   const FastCounters* counters;
 };
 
-__device__ __forceinline__ uint64_t op_value(const PairArgs& a, uint32_t i) {
-  return (uint64_t(a.op_table[i]) << 32) | (a.op_level[i] + ((a.op_ck[i] & 1u) ? 0u : 1u));
-}
+__device__ __forceinline__ uint64_t op_value(const uint4 o) { return (uint64_t(o.z) << 32) | (o.y + ((o.x & 1u) ? 0u : 1u)); }
+__device__ __forceinline__ uint64_t op_value(const PairArgs& a, uint32_t i) { return op_value(a.ops[i]); }
 __device__ __forceinline__ uint64_t warp_min_u64(uint64_t m) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -508,8 +490,8 @@ __global__ void __launch_bounds__(kChunk) k_chunk_min(const PairArgs a) {
   const uint32_t j = base + tid;
   const uint32_t last = min(base + kChunk, M) - 1;
   if (tid == 0) {
-    s_tlast = a.op_table[last];
-    a.tfirst[blockIdx.x] = a.op_table[base];
+    s_tlast = a.ops[last].z;
+    a.tfirst[blockIdx.x] = a.ops[base].z;
     a.tlast[blockIdx.x] = s_tlast;
   }
   __syncthreads();
@@ -542,8 +524,9 @@ __global__ void __launch_bounds__(kChunk) k_pair(const PairArgs a) {
   uint32_t ck = 1, level = 0, t = 0;
   uint64_t v = ~0ull;
   if (j < M) {
-    ck = a.op_ck[j]; level = a.op_level[j]; t = a.op_table[j];
-    v = (uint64_t(t) << 32) | (level + ((ck & 1u) ? 0u : 1u));
+    const uint4 o = a.ops[j];
+    ck = o.x; level = o.y; t = o.z;
+    v = op_value(o);
   }
   s_v[tid] = v;
   const uint64_t m = warp_min_u64(v);
@@ -618,9 +601,7 @@ __global__ void __launch_bounds__(kChunk) k_pair(const PairArgs a) {
 // ever target INITIAL slots; slots opened by an Append keep their opener unless they are closed.
 // ================================================================================================================
 struct ResolveView {
-  const uint32_t* op_ck;
-  const uint32_t* op_level;
-  const uint32_t* op_table;
+  const uint4* ops;
   const uint32_t* prev;
   const uint32_t* next;
   const uint64_t* srcloc;
@@ -646,7 +627,9 @@ __device__ __forceinline__ uint32_t init_close_of(const ResolveView& v, uint64_t
 // the slot instance Remove op j closes (the table's tail at that moment)
 __device__ __forceinline__ uint64_t closed_by(const ResolveView& v, uint32_t j) {
   const uint32_t p = v.prev[j];
-  return p != kNone ? inst_append(p) : inst_init(v.op_table[j], v.op_level[j]);
+  if (p != kNone) return inst_append(p);
+  const uint4 o = v.ops[j];
+  return inst_init(o.z, o.y);
 }
 __device__ __forceinline__ bool table_ends_empty(const ResolveView& v, uint32_t t) {
   return v.tcount0[t] + v.counters->tapp[t] == v.counters->trem[t];
@@ -655,11 +638,11 @@ __device__ __forceinline__ bool table_ends_empty(const ResolveView& v, uint32_t 
 __device__ bool resolve_step(const ResolveView& v, uint32_t j, uint64_t& I, uint32_t& pred, bool& started) {
   if (!started) {
     started = true;
-    if (table_ends_empty(v, v.op_table[j])) {  // no slot of the table survives: its row order is moot
+    if (table_ends_empty(v, v.ops[j].z)) {  // no slot of the table survives: its row order is moot
       *reinterpret_cast<volatile uint64_t*>(&v.J[j]) = closed_by(v, j);
       return true;
     }
-    I = v.srcloc[v.op_ck[j] >> 1];  // where the entity lived before the batch
+    I = v.srcloc[v.ops[j].x >> 1];  // where the entity lived before the batch
     pred = kNone;
   }
   for (;;) {
@@ -687,7 +670,7 @@ __global__ void __launch_bounds__(256) k_resolve(const ResolveView v) {
   if (threadIdx.x == 0) s_block = atomicAdd(&v.counters->ticket, 1u);
   __syncthreads();
   const uint32_t j = s_block * 256 + threadIdx.x;
-  bool pending = j < v.counters->M && (v.op_ck[j] & 1u) == 0;
+  bool pending = j < v.counters->M && (v.ops[j].x & 1u) == 0;
   uint64_t I = 0;
   uint32_t pred = kNone, rounds = 0;
   bool started = false;
@@ -763,13 +746,13 @@ __global__ void __launch_bounds__(256) k_final_gather(const MoveArgs a) {
   const uint32_t j = blockIdx.x * 256 + threadIdx.x;
   uint32_t slot = kNone, bytes = 0;
   if (j < v.counters->M) {
-    const uint32_t ck = v.op_ck[j];
-    const uint32_t t = v.op_table[j];
+    const uint4 o = v.ops[j];
+    const uint32_t ck = o.x, t = o.z;
     helios_gpu_entity_t e = 0;
     uint64_t src = 0;
     if (ck & 1u) {  // Append: a slot that is never closed keeps its opener
       if (v.next[j] == kNone) {
-        slot = v.op_level[j];
+        slot = o.y;
         e = a.cmd[ck >> 1].entity;
         src = v.srcloc[ck >> 1];
       }
@@ -780,7 +763,7 @@ __global__ void __launch_bounds__(256) k_final_gather(const MoveArgs a) {
         slot = uint32_t(I);
         for (;;) {  // occupant of the slot this op closed = the entity it moves
           if (X & kInstA) {
-            const uint32_t k = v.op_ck[uint32_t(X)] >> 1;
+            const uint32_t k = v.ops[uint32_t(X)].x >> 1;
             e = a.cmd[k].entity;
             src = v.srcloc[k];
             break;
@@ -830,7 +813,7 @@ __global__ void __launch_bounds__(256) k_scatter(const MoveArgs a) {
   for (uint32_t j = blockIdx.x * 256 + threadIdx.x; j < M; j += gridDim.x * 256) {
     const uint32_t slot = a.ch_slot[j];
     if (slot == kNone) continue;
-    const uint32_t t = v.op_table[j];
+    const uint32_t t = v.ops[j].z;
     if (slot >= v.tcount0[t]) continue;  // written directly by K8
     a.tents[t][slot] = a.ch_ent[j];
     const uint8_t* st = a.stage + size_t(j) * a.stride;
@@ -862,6 +845,7 @@ struct FinishArgs {
   uint32_t* tcount;
   FastCounters* counters;
   helios_gpu_entity_t* chan_dst[kMaxChannels];  // first free slot of each builtin message type's current queue
+  unsigned long long* chan_count[kMaxChannels]; // device-side CurrentMessages count of the type (readers' view)
 };
 
 // Scatter for every bit set in the warp: the lanes holding bit b take consecutive positions from off[base + b].
@@ -886,8 +870,12 @@ __global__ void __launch_bounds__(256) k_finish(const FinishArgs a) {
   if (a.counters->abort) return;
   const uint32_t T = a.ntables, C = 2 + 2 * a.ncomps;
   const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-  if (blockIdx.x == 0)
+  if (blockIdx.x == 0) {
     for (uint32_t t = threadIdx.x; t < T; t += 256) a.tcount[t] = a.tcount[t] + a.counters->tapp[t] - a.counters->trem[t];
+    if (a.emit_messages)  // the device-resident reader views see the new messages without a host round trip
+      for (uint32_t c = threadIdx.x; c < C; c += 256)
+        if (a.counters->chan_total[c] && a.chan_count[c]) *a.chan_count[c] += a.counters->chan_total[c];
+  }
   for (uint32_t i = threadIdx.x; i < 8 * kMaxChannels; i += 256) (&s_w[0][0])[i] = 0;
   __syncthreads();
   const uint32_t k0 = blockIdx.x * kTile + wid * 128 + lane;
@@ -1057,7 +1045,7 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
   if (w->builtin_messages) NEED(S.em, size_t(K) * 8);
   NEED(S.matrix, size_t(nrows) * ntiles * 4); NEED(S.rowtot, size_t(nrows) * 4);
   NEED(S.obase, (T + 1) * 4); NEED(S.tfmin, T * 4); NEED(S.ic_off, (T + 1) * 4);
-  NEED(S.op_ck, Mmax * 4); NEED(S.op_level, Mmax * 4); NEED(S.op_table, Mmax * 4); NEED(S.next, Mmax * 4); NEED(S.prev, Mmax * 4);
+  NEED(S.ops, Mmax * 16); NEED(S.next, Mmax * 4); NEED(S.prev, Mmax * 4);
   NEED(S.J, Mmax * 8); NEED(S.has_succ, Mmax);
   const size_t nchunks = (Mmax + kChunk - 1) / kChunk;
   NEED(S.cmin, nchunks * 8); NEED(S.submin, nchunks * (kChunk / 32) * 8);
@@ -1069,6 +1057,9 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
   HG_CUDA(w, cudaMemsetAsync(S.counters.ptr, 0, sizeof(FastCounters), st));
   HG_CUDA(w, cudaMemsetAsync(S.init_close.ptr, 0xFF, (size_t(K) + 16) * 4, st));
   HG_CUDA(w, cudaMemsetAsync(S.last_target.ptr, 0, (size_t(K) + 16) * 4, st));
+  HG_CUDA(w, cudaMemsetAsync(S.next.ptr, 0xFF, Mmax * 4, st));     // kNone: the slot an Append opens survives
+  HG_CUDA(w, cudaMemsetAsync(S.J.ptr, 0xFF, Mmax * 8, st));        // kUnresolved
+  HG_CUDA(w, cudaMemsetAsync(S.has_succ.ptr, 0, Mmax, st));
   FastCounters* dc = S.counters.as<FastCounters>();
 
   // ---- K1 / K2 ------------------------------------------------------------------------------------------------------
@@ -1094,7 +1085,10 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
     MsgChannel* ch = find_channel(w, channel_hash(w, c));
     if (!ch || ch->size != 8) { sa.room[c] = 0; continue; }  // registered by the general path the first time it is needed
     const uint64_t want = ch->cur_count + std::max<uint64_t>(2ull * S.last_chan_total[c], 1024);
+    const void* before = ch->cur.ptr;
     HG_CUDA(w, ch->cur.reserve(want * 8, ch->cur_count * 8, st));
+    if (ch->cur.ptr != before) HG_TRY(publish_channel(w, ch));  // the queue moved: refresh the device-side reader view
+    fa.chan_count[c] = &ch->d_dev.as<ChannelDev>()->counts[1];
     sa.room[c] = uint32_t(std::min<uint64_t>(ch->cur.bytes / 8 - ch->cur_count, 0xFFFFFFFFull));
     fa.chan_dst[c] = ch->cur.as<helios_gpu_entity_t>() + ch->cur_count;
   }
@@ -1102,16 +1096,15 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
 
   // ---- K3 .. K10 ----------------------------------------------------------------------------------------------------
   EmitArgs ea{K, ntiles, T, S.info.as<uint64_t>(), S.matrix.as<uint32_t>(), S.obase.as<uint32_t>(), w->d_tcount.as<uint32_t>(),
-              S.op_ck.as<uint32_t>(), S.op_level.as<uint32_t>(), S.op_table.as<uint32_t>(), S.next.as<uint32_t>(),
-              S.J.as<uint64_t>(), S.has_succ.as<uint8_t>(), dc};
+              S.ops.as<uint4>(), dc};
   k_emit_ops<<<ntiles, 256, (2 * 8 * 2 * T + 2 * T) * 4, st>>>(ea);
-  PairArgs pa{S.op_ck.as<uint32_t>(), S.op_level.as<uint32_t>(), S.op_table.as<uint32_t>(), S.prev.as<uint32_t>(), S.next.as<uint32_t>(),
+  PairArgs pa{S.ops.as<uint4>(), S.prev.as<uint32_t>(), S.next.as<uint32_t>(),
               S.cmin.as<uint64_t>(), S.submin.as<uint64_t>(), S.cmin_last.as<uint64_t>(), S.tfirst.as<uint32_t>(),
               S.tlast.as<uint32_t>(), S.tfmin.as<uint32_t>(), S.ic_off.as<uint32_t>(), S.init_close.as<uint32_t>(), dc};
   k_chunk_min<<<uint32_t(nchunks), kChunk, 0, st>>>(pa);
   k_pair<<<uint32_t(nchunks), kChunk, 0, st>>>(pa);
   const uint32_t op_blocks = uint32_t((Mmax + 255) / 256);
-  ResolveView rv{S.op_ck.as<uint32_t>(), S.op_level.as<uint32_t>(), S.op_table.as<uint32_t>(), S.prev.as<uint32_t>(), S.next.as<uint32_t>(),
+  ResolveView rv{S.ops.as<uint4>(), S.prev.as<uint32_t>(), S.next.as<uint32_t>(),
                  S.srcloc.as<uint64_t>(), S.tfmin.as<uint32_t>(), w->d_tcount.as<uint32_t>(), S.ic_off.as<uint32_t>(),
                  S.init_close.as<uint32_t>(), S.J.as<uint64_t>(), S.has_succ.as<uint8_t>(), S.last_target.as<uint32_t>(), dc};
   k_resolve<<<op_blocks, 256, 0, st>>>(rv);
@@ -1157,9 +1150,7 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
     }
     for (uint32_t c = 0; c < C; ++c) {
       if (!hc.chan_total[c]) continue;
-      ch = find_channel(w, channel_hash(w, c));
-      ch->cur_count += hc.chan_total[c];
-      HG_TRY(publish_channel(w, ch));
+      find_channel(w, channel_hash(w, c))->cur_count += hc.chan_total[c];  // K10 bumped the device-side count already
     }
   }
   w->last_stats = helios_gpu_apply_stats{};
