@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--all-tables", action="store_true", help="drop the With/Without filters (cfg 2-all)")
+    ap.add_argument("--no-secondary", action="store_true", help="headline line only (skip the cfg2-all / cfg3 / cfg4 / cfg5 / routing legs)")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="cfg5 / routing at N>1: peer-memory exchange fused into the kernels (default) or NCCL collectives")
     return ap.parse_args()
@@ -94,41 +95,55 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": reasons, "samples": len(sm)}
 
 
-def cpu_reference_leg(entities, steps, warmup, threads=1, mode=1):
+def cpu_reference_leg(entities, steps, warmup, threads=1, mode=1, budget_s=None):
     """Times the oracle's reference-faithful path (B-ref: per-entity unordered_map probe + 2 binary searches + column-map
-    find per component, serial ForEach — SURVEY §3.3) on a bounded sample of the same workload."""
+    find per component, serial ForEach — SURVEY §3.3).  With `budget_s` the number of timed steps is capped so that the
+    timed region stays inside the budget (the step count actually run is returned)."""
+    import ctypes
     from heliosengine_b200 import capi, worlds
     o = capi.load_oracle()
-    w = capi.World(o)
+    # the world is only iterated here (no structural call inside the timed region): skip the builtin messages of the bulk load
+    w = capi.World(o, flags=capi.WORLD_NO_BUILTIN_MESSAGES)
     sched, q = worlds.build_cfg2(w, entities, filtered=True)
     o.fn("set_access_mode")(w.h, mode, threads)
     matched = q.count()
-    for _ in range(warmup):
-        sched.run(0)
-    t = o.fn("time_schedule_run", __import__("ctypes").c_double)(sched.h, steps)
+    timer = o.fn("time_schedule_run", ctypes.c_double)
+    est = None
+    for i in range(max(1, warmup)):
+        t = timer(sched.h, 1)
+        est = t if i else None  # the first pass also builds the lookup index
+    if budget_s is not None:
+        est = est if est is not None else timer(sched.h, 1)
+        steps = max(1, min(steps, int(budget_s / max(est, 1e-9))))
+    t = timer(sched.h, steps)
     w.close()
-    return matched * steps / t, t / steps, matched
+    return matched * steps / t, t / steps, matched, steps
 
 
 def run_reference(args):
+    """The reference arm: the reference's own CPU algorithm for the path (the oracle restatement — the reference cannot be
+    built in this image) on the FULL headline world, its per-entity access path, one core (the reference runs
+    one system on one thread: no intra-system parallelism).  Steps are capped by a time budget, never the size."""
     import ctypes
     from heliosengine_b200 import capi
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample_entities = 1 << 21  # 1/8 of the workload: 524288 matched rows per step
-    steps = max(1, min(args.steps, 3))
-    warm = 1
-    v, spt, matched = cpu_reference_leg(sample_entities, steps, warm, threads=1, mode=1)
-    cores = 1
+    entities = args.entities or N_ENTITIES
+    warm = max(1, min(args.warmup, 3))
+    v, spt, matched, steps = cpu_reference_leg(entities, args.steps, warm, threads=1, mode=1, budget_s=120.0)
+    host_threads = capi.load_oracle().fn("hardware_threads", ctypes.c_uint32)()
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
         "ms_per_step": spt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic", "config": {"workload": WORKLOAD, "sample": f"{sample_entities} entities ({matched} matched rows) per step"},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"1/8-scale world ({sample_entities} entities, {matched} matched rows), {steps} steps; "
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD, "entities_per_gpu": entities, "matched_rows_per_gpu": matched,
+                   "steps_note": f"{steps} timed steps of the full-size world (requested {args.steps}; capped by a 120 s budget, "
+                                 "never by shrinking the world)"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+                         "sample": f"full-size world ({entities} entities, {matched} matched rows per step), {steps} steps; "
                                    "reference-faithful access path (B-ref); the reference runs one system on one core "
-                                   f"(no intra-system parallelism); host has {capi.load_oracle().fn('hardware_threads', ctypes.c_uint32)()} threads"},
+                                   f"(no intra-system parallelism); host has {host_threads} threads"},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -137,7 +152,7 @@ def run_reference(args):
 def run_secondary(args):
     """cfg1 / cfg3 / cfg4 legs (single GPU) and cfg5 (boids, sharded over the ranks): same JSON-line shape."""
     import torch
-    from heliosengine_b200 import bench_configs
+    import bench_configs
     rank = int(os.environ.get("RANK", "0"))
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -167,6 +182,81 @@ def run_secondary(args):
         print(json.dumps(base))
 
 
+def secondary_legs(args, torch, dist, dev, rank, world_size, local_rank):
+    """The other BASELINE configs, each to the same bar as the headline (own timing, roofline, CPU baseline where one exists,
+    clocks): cfg2 with the filters dropped (L2-insensitive: 738 MB per step), cfg3 (ApplyDeferred, full-size digest parity
+    against the oracle), cfg4 (8-system schedule + messages) on rank 0 at N = 1; cfg5 (boids) and cross-shard routing —
+    the two workloads with an exchange step — on every rank at every N."""
+    import copy
+    import bench_configs
+    out = {}
+
+    def leg(name, fn, steps, warm, collective=False, **over):
+        a2 = copy.copy(args)
+        a2.steps, a2.warmup, a2.entities = steps, warm, 0
+        for k, v in over.items():
+            setattr(a2, k, v)
+        clocks = ClockSampler(local_rank)
+        clocks.start()
+        t0 = time.perf_counter()
+        try:
+            st = torch.cuda.Stream(device=dev)
+            r = fn(a2, torch, dev, st, peaks(), dist if world_size > 1 else None, rank, world_size) if collective else fn(a2, torch, dev, st, peaks())
+            r["steps"], r["warmup"] = steps, max(3, warm)
+        except Exception as e:  # a failing leg must not take the headline line with it
+            r = {"error": repr(e)}
+        r["clocks"] = clocks.stop()
+        r["leg_wall_s"] = time.perf_counter() - t0
+        out[name] = r
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+
+    if world_size == 1:
+        leg("cfg1", bench_configs.run_cfg1, 50, 5)
+        leg("cfg2_all_tables", run_cfg2_all, 20, 3)
+        leg("cfg3", bench_configs.run_cfg3, 3, 3)
+        leg("cfg4", bench_configs.run_cfg4, 10, 3)
+    leg("cfg5", bench_configs.run_cfg5, 5, 3, collective=True, no_e2e=True)
+    leg("routing", bench_configs.run_routing, 10, 3, collective=True)
+    return out
+
+
+def run_cfg2_all(args, torch, dev, stream, peak):
+    """cfg 2-all: the headline query with the filters dropped — 64 tables, 16 777 216 rows, 738 MB per step: six times the L2,
+    so the number does not depend on what the previous step left in the cache."""
+    from heliosengine_b200 import capi, worlds
+    n = args.entities or N_ENTITIES
+    w = capi.World(capi.load_gpu(), device=dev.index, entity_capacity=n + 1024, flags=capi.WORLD_NO_BUILTIN_MESSAGES)
+    w.set_stream(stream.cuda_stream)
+    sched, q = worlds.build_cfg2(w, n, filtered=False)
+    matched = q.count()
+    with torch.cuda.stream(stream):
+        for _ in range(max(3, args.warmup)):
+            sched.run_and_wait(capi.EXEC_SERIAL)
+        torch.cuda.synchronize()
+        l0 = w.launch_count()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        for a, b in evs:
+            a.record(stream)
+            sched.run(capi.EXEC_SERIAL)
+            b.record(stream)
+            sched.apply_deferred()
+        torch.cuda.synchronize()
+        launches = w.launch_count() - l0
+    ms = sorted(a.elapsed_time(b) for a, b in evs)
+    mean_ms = sum(ms) / len(ms)
+    nbytes = matched * worlds.CFG2_BYTES_PER_ENTITY
+    achieved = nbytes / (mean_ms * 1e-3) / 1e9
+    w.close()
+    return {"metric": METRIC, "value": matched / (mean_ms * 1e-3), "unit": UNIT, "ms_per_step": mean_ms, "dtype": "f32",
+            "config": {"workload": WORKLOAD + " [filters dropped: 64 tables, all rows]", "matched_rows_per_gpu": matched,
+                       "l2": "738 MB streamed per step (6x the L2): no flush needed"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak[0], "unit": "GB/s", "frac": achieved / peak[0],
+                         "traffic": None, "peak_kind": peak[1], "algorithmic_bytes_per_launch": nbytes,
+                         "kernel": "helios_gpu::for_each_kernel<AccelBody,...>"},
+            "step_ms_min_med_max": [ms[0], ms[len(ms) // 2], ms[-1]], "gpu_launches": int(launches), "e2e": None, "cpu_baseline": None}
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -185,7 +275,8 @@ def run_b200(args):
     # Entity-range sharding, weak scaling: every rank owns an independent shard of `entities` entities (rows are
     # independent units; SURVEY §8e: no data-path collective for query iteration).
     gpu = capi.load_gpu()
-    w = capi.World(gpu, device=local_rank, entity_capacity=args.entities + 1024)
+    # built without the bulk load's builtin messages: the timed region iterates, it makes no structural call
+    w = capi.World(gpu, device=local_rank, entity_capacity=args.entities + 1024, flags=capi.WORLD_NO_BUILTIN_MESSAGES)
     stream = torch.cuda.Stream(device=dev)
     w.set_stream(stream.cuda_stream)
     sched, q = worlds.build_cfg2(w, args.entities, filtered=not args.all_tables)
@@ -290,15 +381,23 @@ def run_b200(args):
     if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
         import ctypes
         sample_entities = 1 << 21
-        v, spt, m = cpu_reference_leg(sample_entities, 2, 1, threads=1, mode=1)
+        v, spt, m, _ = cpu_reference_leg(sample_entities, 2, 2, threads=1, mode=1)
         nthreads = capi.load_oracle().fn("hardware_threads", ctypes.c_uint32)()
-        vopt, _, _ = cpu_reference_leg(sample_entities, 5, 1, threads=nthreads, mode=0)
+        vopt, _, _, _ = cpu_reference_leg(sample_entities, 5, 2, threads=nthreads, mode=0)
         cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
                "sample": f"1/8-scale world ({sample_entities} entities, {m} matched rows/step), 2 steps, B-ref = oracle with the "
                          "reference's per-entity lookup path, single core (the reference has no intra-system parallelism)",
                "b_opt": {"value": vopt, "cores": int(nthreads), "note": "direct column loops split over all host threads"}}
 
+    w.close()
+    secondary = None
+    if not args.no_secondary:
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+        secondary = secondary_legs(args, torch, dist, dev, rank, world_size, local_rank)
+
     if rank == 0:
+        default_workload = args.entities == DEFAULT_ENTITIES and not args.all_tables
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -309,7 +408,11 @@ def run_b200(args):
                        "l2": "flushed between timed steps: 256 MiB written, then 256 MiB read (L2 left holding clean lines)", "exec_mode": "serial stream",
                        "fma": "off (-fmad=false), bit-exact vs oracle"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_TRAFFIC_DEFAULT if (args.entities == DEFAULT_ENTITIES and not args.all_tables) else None,
+                         "traffic": NCU_TRAFFIC_DEFAULT if default_workload else None,
+                         # bytes that reached HBM inside the kernel (ncu) / CUDA-event kernel time: the L2-insensitive reading of
+                         # the same launch (45.5 MB of its written lines are still dirty in the 126 MB L2 when the stop event fires);
+                         # the other L2-insensitive figure is secondary.cfg2_all_tables (738 MB per step)
+                         "frac_dram_in_kernel": (NCU_TRAFFIC_DEFAULT / (kernel_ms * 1e-3) / 1e9 / peak) if default_workload else None,
                          "traffic_source": "profiles/r01_foreach_accel_full.md (ncu --set full, one launch of this workload): "
                                            "117.46 MB read + 21.58 MB written inside the kernel; the other 45.5 MB of written "
                                            "lines are still dirty in L2 when it ends",
@@ -320,9 +423,9 @@ def run_b200(args):
                     "steps": e2e_steps, "note": "per step: pinned-host Acceleration columns -> device (copy stream, overlapping the previous read-back), Schedule::Run, Position columns -> host"},
             "gpu_launches": int(launches), "clocks": clk, "wall_s_timed_region": t_wall,
             "step_ms_min_med_max": [min(step_ms), sorted(step_ms)[len(step_ms) // 2], max(step_ms)],
+            "secondary": secondary,
         }
         print(json.dumps(line))
-    w.close()
     if world_size > 1:
         dist.destroy_process_group()
 

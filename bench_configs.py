@@ -16,7 +16,7 @@ import time
 
 import numpy as np
 
-from . import capi, worlds
+from heliosengine_b200 import capi, worlds
 
 
 def _events(torch, n):
@@ -163,6 +163,24 @@ def run_cfg4(args, torch, dev, stream, peak):
     ev = out_modes[best]["events_per_frame"]
     bytes_per_frame = n * worlds.CFG4_COMPONENT_BYTES_PER_ENTITY + ev * worlds.CFG4_BYTES_PER_EVENT
     achieved = bytes_per_frame / (ms * 1e-3) / 1e9
+    cpu = None
+    if not args.no_cpu_baseline:  # the same schedule on the oracle, 1/8-scale sample, serial executor, direct column loops
+        o = capi.load_oracle()
+        sn = n // 8
+        wo = capi.World(o)
+        so = worlds.build_cfg4(wo, sn)
+        for _ in range(2):
+            so.run_and_wait(capi.EXEC_SERIAL)
+            wo.update()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            so.run_and_wait(capi.EXEC_SERIAL)
+            wo.update()
+        dt = (time.perf_counter() - t0) / 3
+        wo.close()
+        cpu = {"value": sn / dt, "unit": "events/s", "cores": 1, "kind": "port",
+               "sample": f"1/8-scale world ({sn} entities, {sn} events per frame), 3 frames of RunAndWait + World::Update on the "
+                         "oracle (serial executor, direct column loops: cheaper than the reference's per-entity lookups)"}
     return {
         "metric": "events_per_sec", "value": ev / (ms * 1e-3), "unit": "events/s", "ms_per_step": ms, "dtype": "f32/i32",
         "config": {"workload": f"cfg4: {n} entities, 8-system schedule (conflict DAG), CollisionEvent channel {ev} events/frame",
@@ -171,7 +189,7 @@ def run_cfg4(args, torch, dev, stream, peak):
                      "traffic": None, "peak_kind": peak[1], "algorithmic_bytes_per_launch": bytes_per_frame,
                      "kernel": "all 8 systems of one Schedule::Run"},
         "entity_updates_per_sec": n * 7 / (ms * 1e-3),
-        "modes": out_modes, "gpu_launches": int(launches), "e2e": None, "cpu_baseline": None,
+        "modes": out_modes, "gpu_launches": int(launches), "e2e": None, "cpu_baseline": cpu,
     }
 
 
@@ -199,13 +217,25 @@ def run_cfg1(args, torch, dev, stream, peak):
     ms = min(res.values())
     achieved = n * worlds.CFG1_BYTES_PER_ENTITY / (ms * 1e-3) / 1e9
     w.close()
+    cpu = None
+    if not args.no_cpu_baseline:  # configs[0] is the reference's own CPU-runnable case: the full 1M-entity world on the oracle
+        o = capi.load_oracle()
+        wo = capi.World(o, flags=capi.WORLD_NO_BUILTIN_MESSAGES)
+        so, _ = worlds.build_cfg1(wo, n)
+        o.fn("set_access_mode")(wo.h, 1, 1)
+        timer = o.fn("time_schedule_run", ctypes.c_double)
+        timer(so.h, 1)
+        dt = timer(so.h, 3) / 3
+        wo.close()
+        cpu = {"value": n / dt, "unit": "updates/s", "cores": 1, "kind": "port",
+               "sample": f"the full config ({n} entities), 3 steps, reference-faithful per-entity access path (B-ref), one core"}
     return {
         "metric": "entity_component_updates_per_sec", "value": n / (ms * 1e-3), "unit": "updates/s", "ms_per_step": ms,
         "dtype": "f32", "config": {"workload": f"cfg1: {n} entities {{Position, Velocity}}, one archetype, ChangePosition",
                                    "l2": "25 MB working set is L2-resident by construction (launch-bound config; no roofline claim)"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak[0], "unit": "GB/s", "frac": achieved / peak[0],
                      "traffic": None, "peak_kind": peak[1], "note": "L2-resident: not an HBM measurement"},
-        "modes_ms": res, "gpu_launches": steps * 2, "e2e": None, "cpu_baseline": None,
+        "modes_ms": res, "gpu_launches": steps * 2, "e2e": None, "cpu_baseline": cpu,
     }
 
 
@@ -621,7 +651,7 @@ def run_routing(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1)
     """Cross-shard message routing: every rank holds 4 194 304 CollisionEvents (cfg 4's per-frame volume)
     keyed uniformly over the entity-index ranges of all ranks; a step = stable split by owner on the device, all-to-all of
     counts and slabs (NCCL over NVLink), merge.  value = messages routed per second over all ranks (max-over-ranks time)."""
-    from . import routing
+    from heliosengine_b200 import routing
     n = args.entities or (1 << 22)
     per = 1 << 22
     gpu = capi.load_gpu()
@@ -691,7 +721,7 @@ def run_routing(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1)
 def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
     """Boids, STRONG scaling: `--entities` boids in total (default 64M, density 4 per cell) split by entity-id range over
     the ranks; per step: bin own shard, all-gather slabs + counts (NCCL), neighbour pass + integrate."""
-    from . import boids
+    from heliosengine_b200 import boids
     n_total = args.entities or (1 << 26)
     ws = int(round((n_total / 4) ** 0.5))
     gpu = capi.load_gpu()
