@@ -1105,7 +1105,9 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
   HG_CUDA(w, cudaMemsetAsync(S.counters.ptr, 0, sizeof(Counters), st));
   Counters* dc = S.counters.as<Counters>();
   Counters hc{};
-  NEED(S.partials, (n / prim::kScanTile + 2) * 4);
+  // scans run over the n commands AND over the M <= 2n table ops: size the tile totals for the larger one (sized for n only,
+  // the op scan wrote past the end — into whichever pool allocation happened to follow, e.g. the counters' ticket)
+  NEED(S.partials, (2 * n / prim::kScanTile + 4) * 4);
 
   // ---- stage 1: compaction (sparse, device-emitted buffers only; host queues are dense) ---------------------------
   uint32_t K = uint32_t(n);
@@ -1114,6 +1116,7 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     NEED(S.flags, n * 4);
     NEED(S.cidx, n * 4);
     k_flag_valid<<<blocks_for(n), 256, 0, st>>>(d_cmds, n, S.flags.as<uint32_t>());
+  HG_TRACE(w, "general k_flag_valid");
     launches += 1 + prim::exclusive_scan_u32(S.flags.as<uint32_t>(), S.cidx.as<uint32_t>(), n, S.partials.as<uint32_t>(),
                                              &dc->n_valid_slots, st);
     HG_CUDA(w, cudaMemcpyAsync(&hc, dc, sizeof(hc), cudaMemcpyDeviceToHost, st));
@@ -1133,6 +1136,7 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     NEED(S.c_cmd, K * sizeof(helios_gpu_command));
     k_compact<<<blocks_for(n), 256, 0, st>>>(d_cmds, n, S.flags.as<uint32_t>(), S.cidx.as<uint32_t>(),
                                              S.c_cmd.as<helios_gpu_command>(), S.skey.as<uint64_t>(), S.sval.as<uint32_t>());
+  HG_TRACE(w, "general k_compact");
     ++launches;
     cmd = S.c_cmd.as<helios_gpu_command>();
   }
@@ -1147,8 +1151,11 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
   S.ent_first_dirty = true;
   k_mark_first<<<blocks_for(K), 256, 0, st>>>(cmd, K, w->ent_capacity, S.ent_first.as<uint32_t>(), S.skey.as<uint64_t>(),
                                               S.sval.as<uint32_t>());
+  HG_TRACE(w, "general k_mark_first");
   k_count_dups<<<blocks_for(K), 256, 0, st>>>(cmd, K, w->ent_capacity, S.ent_first.as<uint32_t>(), dc);
+  HG_TRACE(w, "general k_count_dups");
   k_reset_first<<<blocks_for(K), 256, 0, st>>>(cmd, K, w->ent_capacity, S.ent_first.as<uint32_t>());
+  HG_TRACE(w, "general k_reset_first");
   launches += 3;
   NEED(S.src_mask, K * 8); NEED(S.dst_mask, K * 8); NEED(S.wset, K * 8); NEED(S.wlive, K * 8);
   NEED(S.home_cmd, K * 4); NEED(S.cflags, K * 4); NEED(S.dflag, K * 4); NEED(S.dpos, K * 4);
@@ -1171,6 +1178,7 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     ca.registered_slots = w->comps.size() >= 64 ? ~0ull : ((1ull << w->comps.size()) - 1);
   }
   k_chain<<<blocks_for(K), 256, 0, st>>>(ca);
+  HG_TRACE(w, "general k_chain");
   ++launches;
 
   // ---- stage 3: masks → tables (creating missing archetypes in command order), per-table op counts ------------------
@@ -1194,6 +1202,7 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     k_map_tables<<<grid, 256, smem, st>>>(K, S.src_mask.as<uint64_t>(), S.dst_mask.as<uint64_t>(), S.cflags.as<uint32_t>(), mh,
                                           S.src_t.as<uint32_t>(), S.dst_t.as<uint32_t>(), S.opcnt.as<uint32_t>(),
                                           S.trem.as<uint32_t>(), S.tapp.as<uint32_t>(), nt, S.unknown.as<Unknown>(), K, dc);
+  HG_TRACE(w, "general k_map_tables");
     launches += 1 + prim::exclusive_scan_u32(S.opcnt.as<uint32_t>(), S.opbase.as<uint32_t>(), K, S.partials.as<uint32_t>(), &dc->n_ops, st);
     hrem.assign(nt, 0);
     happ.assign(nt, 0);
@@ -1213,6 +1222,7 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
       HG_CUDA(w, cudaMemsetAsync(&dc->invalid, 0, 4, st));
       HG_CUDA(w, cudaMemsetAsync(&dc->sparse_events, 0, 4, st));
       k_chain<<<blocks_for(K), 256, 0, st>>>(ca);
+  HG_TRACE(w, "general k_chain");
       ++launches;
       sorted_by_entity = true;
       continue;
@@ -1251,6 +1261,7 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
     k_emit_ops<<<blocks_for(K), 256, 0, st>>>(K, S.opcnt.as<uint32_t>(), S.opbase.as<uint32_t>(), S.src_t.as<uint32_t>(),
                                               S.dst_t.as<uint32_t>(), S.skey.as<uint64_t>(), S.sval.as<uint32_t>(),
                                               S.u_kind.as<uint32_t>(), S.u_cmd.as<uint32_t>());
+  HG_TRACE(w, "general k_emit_ops");
     ++launches;
     const int table_bits = prim::bits_for(nt ? nt - 1 : 0);
     launches += prim::radix_sort_pairs(S.skey.as<uint64_t>(), S.sval.as<uint32_t>(), M, table_bits, ss, st);
@@ -1260,18 +1271,22 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
                                                 S.u_cmd.as<uint32_t>(), S.op_table.as<uint32_t>(), S.op_kind.as<uint32_t>(),
                                                 S.op_cmd.as<uint32_t>(), S.u2t.as<uint32_t>(), S.delta.as<uint32_t>(),
                                                 S.tseg.as<uint32_t>());
+  HG_TRACE(w, "general k_gather_ops");
     launches += 1 + prim::exclusive_scan_u32(S.delta.as<uint32_t>(), S.ex.as<uint32_t>(), M, S.partials.as<uint32_t>(), nullptr, st);
     const int level_bits = prim::bits_for(uint64_t(max_ops) + 1);
     k_levels<<<blocks_for(M), 256, 0, st>>>(M, S.op_table.as<uint32_t>(), S.op_kind.as<uint32_t>(), S.delta.as<uint32_t>(),
                                             S.ex.as<uint32_t>(), S.tseg.as<uint32_t>(), w->d_tcount.as<uint32_t>(),
                                             S.trem.as<uint32_t>(), S.op_level.as<uint32_t>(),
                                             S.key2.as<uint64_t>(), S.p2t.as<uint32_t>(), level_bits);
+  HG_TRACE(w, "general k_levels");
     ++launches;
     launches += prim::radix_sort_pairs(S.key2.as<uint64_t>(), S.p2t.as<uint32_t>(), M, level_bits + table_bits, ss, st);
     k_ic_offsets<<<1, 1024, 0, st>>>(nt, w->d_tcount.as<uint32_t>(), S.trem.as<uint32_t>(), S.tfmin.as<uint32_t>(), S.ic_off.as<uint32_t>());
+  HG_TRACE(w, "general k_ic_offsets");
     k_invert<<<blocks_for(M), 256, 0, st>>>(M, S.p2t.as<uint32_t>(), S.key2.as<uint64_t>(), S.op_kind.as<uint32_t>(),
                                             S.op_table.as<uint32_t>(), S.op_level.as<uint32_t>(), S.tfmin.as<uint32_t>(),
                                             S.ic_off.as<uint32_t>(), S.t2p.as<uint32_t>(), S.init_close.as<uint32_t>());
+  HG_TRACE(w, "general k_invert");
     launches += 2;
 
     uint32_t ih_log2 = 10;
@@ -1288,11 +1303,13 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
              w->d_loc.as<uint64_t>(), S.J.as<uint64_t>(), S.trem.as<uint32_t>(), S.tapp.as<uint32_t>(),
              InstHash{S.ih_keys.as<unsigned long long>(), S.ih_vals.as<uint32_t>(), ih_log2}};
     k_resolve_all<<<blocks_for(M), 256, 0, st>>>(v, dc);
+  HG_TRACE(w, "general k_resolve_all");
     ++launches;
 
     NEED(S.ch_slot, M * 4); NEED(S.ch_ent, M * 8);
     k_final_slots<<<blocks_for(M), 256, 0, st>>>(v, w->d_tents.as<helios_gpu_entity_t*>(), S.ch_slot.as<uint32_t>(),
                                                  S.ch_ent.as<helios_gpu_entity_t>(), dc);
+  HG_TRACE(w, "general k_final_slots");
     NEED(S.stage, size_t(M) * S.stage_stride);
     MoveArgs ma{M, S.op_table.as<uint32_t>(), S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(),
                 w->d_loc.as<uint64_t>(), w->d_tmask.as<uint64_t>(), w->d_tcols.as<void*>(),
@@ -1300,9 +1317,12 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
                 S.stage.as<uint8_t>(), S.stage_stride, dc};
     const uint32_t mover_grid = std::min<uint32_t>((M + 31u) / 32u, uint32_t(w->sm_count) * 8u);
     k_move_rows<false><<<mover_grid, 256, 0, st>>>(ma);
+  HG_TRACE(w, "general k_move_rows<false>");
     k_move_rows<true><<<mover_grid, 256, 0, st>>>(ma);
+  HG_TRACE(w, "general k_move_rows<true>");
     k_update_locations<<<blocks_for(M), 256, 0, st>>>(M, S.op_table.as<uint32_t>(), S.ch_slot.as<uint32_t>(),
                                                       S.ch_ent.as<helios_gpu_entity_t>(), w->d_loc.as<uint64_t>());
+  HG_TRACE(w, "general k_update_locations");
     launches += 4;
   }
 
@@ -1316,9 +1336,12 @@ int32_t apply_queue(helios_gpu_world* w, const helios_gpu_command* d_cmds, const
   HG_CUDA(w, w->d_free.reserve((w->free_count + K) * 4, w->free_count * 4, st, true));
   k_destroy<<<blocks_for(K), 256, 0, st>>>(K, cmd, S.dflag.as<uint32_t>(), S.dpos.as<uint32_t>(),
                                            w->d_gen.as<uint32_t>(), w->d_loc.as<uint64_t>(), w->d_free.as<uint32_t>(), w->free_count);
+  HG_TRACE(w, "general k_destroy");
   k_patch<<<blocks_for(K), 256, 0, st>>>(K, cmd, S.wlive.as<uint64_t>(), d_payload,
                                          w->d_loc.as<uint64_t>(), w->d_tcols.as<void*>(), w->d_csize.as<uint32_t>());
+  HG_TRACE(w, "general k_patch");
   k_apply_deltas<<<blocks_for(nt), 256, 0, st>>>(nt, S.trem.as<uint32_t>(), S.tapp.as<uint32_t>(), w->d_tcount.as<uint32_t>());
+  HG_TRACE(w, "general k_apply_deltas");
   launches += 3;
   HG_CUDA(w, cudaMemcpyAsync(&hc, dc, sizeof(hc), cudaMemcpyDeviceToHost, st));
   HG_CUDA(w, cudaStreamSynchronize(st));

@@ -1072,6 +1072,7 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
   ca.registered_slots = ncomps >= 64 ? ~0ull : ((1ull << ncomps) - 1);
   ca.matrix = S.matrix.as<uint32_t>(); ca.counters = dc;
   k_classify<<<ntiles, 256, nrows * 4, st>>>(ca);
+  HG_TRACE(w, "fast k_classify");
 
   ScanArgs sa{};
   sa.matrix = S.matrix.as<uint32_t>(); sa.rowtot = S.rowtot.as<uint32_t>(); sa.ntiles = ntiles; sa.ntables = T; sa.ncomps = ncomps;
@@ -1093,25 +1094,31 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
     fa.chan_dst[c] = ch->cur.as<helios_gpu_entity_t>() + ch->cur_count;
   }
   k_rowscan<<<nrows, 256, 0, st>>>(sa);
+  HG_TRACE(w, "fast k_rowscan");
 
   // ---- K3 .. K10 ----------------------------------------------------------------------------------------------------
   EmitArgs ea{K, ntiles, T, S.info.as<uint64_t>(), S.matrix.as<uint32_t>(), S.obase.as<uint32_t>(), w->d_tcount.as<uint32_t>(),
               S.ops.as<uint4>(), dc};
   k_emit_ops<<<ntiles, 256, (2 * 8 * 2 * T + 2 * T) * 4, st>>>(ea);
+  HG_TRACE(w, "fast k_emit_ops");
   PairArgs pa{S.ops.as<uint4>(), S.prev.as<uint32_t>(), S.next.as<uint32_t>(),
               S.cmin.as<uint64_t>(), S.submin.as<uint64_t>(), S.cmin_last.as<uint64_t>(), S.tfirst.as<uint32_t>(),
               S.tlast.as<uint32_t>(), S.tfmin.as<uint32_t>(), S.ic_off.as<uint32_t>(), S.init_close.as<uint32_t>(), dc};
   k_chunk_min<<<uint32_t(nchunks), kChunk, 0, st>>>(pa);
+  HG_TRACE(w, "fast k_chunk_min");
   k_pair<<<uint32_t(nchunks), kChunk, 0, st>>>(pa);
+  HG_TRACE(w, "fast k_pair");
   const uint32_t op_blocks = uint32_t((Mmax + 255) / 256);
   ResolveView rv{S.ops.as<uint4>(), S.prev.as<uint32_t>(), S.next.as<uint32_t>(),
                  S.srcloc.as<uint64_t>(), S.tfmin.as<uint32_t>(), w->d_tcount.as<uint32_t>(), S.ic_off.as<uint32_t>(),
                  S.init_close.as<uint32_t>(), S.J.as<uint64_t>(), S.has_succ.as<uint8_t>(), S.last_target.as<uint32_t>(), dc};
   k_resolve<<<op_blocks, 256, 0, st>>>(rv);
+  HG_TRACE(w, "fast k_resolve");
   MoveArgs ma{rv, d_cmds, w->d_tmask.as<uint64_t>(), w->d_tcols.as<void*>(), w->d_tents.as<helios_gpu_entity_t*>(),
               w->d_csize.as<uint32_t>(), S.coffset.as<uint32_t>(), S.stage.as<uint8_t>(), S.stage_stride, w->d_loc.as<uint64_t>(),
               S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(), S.ch_src.as<uint32_t>()};
   k_final_gather<<<op_blocks, 256, 0, st>>>(ma);
+  HG_TRACE(w, "fast k_final_gather");
   k_scatter<<<std::min<uint32_t>(op_blocks, uint32_t(w->sm_count) * 16u), 256, 0, st>>>(ma);
   fa.cmd = d_cmds; fa.payload = d_payload; fa.K = K; fa.ntiles = ntiles; fa.ntables = T; fa.ncomps = ncomps;
   fa.emit_messages = w->builtin_messages ? 1u : 0u;
@@ -1120,6 +1127,7 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
   fa.free_list = w->d_free.as<uint32_t>(); fa.free_base = w->free_count; fa.tcols = w->d_tcols.as<void*>();
   fa.csize = w->d_csize.as<uint32_t>(); fa.tcount = w->d_tcount.as<uint32_t>(); fa.counters = dc;
   k_finish<<<ntiles, 256, 0, st>>>(fa);
+  HG_TRACE(w, "fast k_finish");
 
   // ---- the one read-back --------------------------------------------------------------------------------------------
   FastCounters& hc = S.host;

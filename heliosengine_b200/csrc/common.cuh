@@ -5,6 +5,7 @@
 
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 
@@ -33,6 +34,21 @@ namespace hgpu {
   do {                                \
     int32_t _s = (expr);              \
     if (_s != HELIOS_GPU_OK) return _s; \
+  } while (0)
+
+// Debug aid: HELIOS_GPU_TRACE=1 synchronises after every stage of the command pipelines and names it on stderr.
+inline bool trace_enabled() {
+  static const bool on = std::getenv("HELIOS_GPU_TRACE") != nullptr;
+  return on;
+}
+#define HG_TRACE(w, what)                                                                  \
+  do {                                                                                     \
+    if (hgpu::trace_enabled()) {                                                           \
+      std::fprintf(stderr, "[helios_gpu] %s ...", what);                                   \
+      std::fflush(stderr);                                                                 \
+      const cudaError_t _te = cudaStreamSynchronize((w)->stream);                          \
+      std::fprintf(stderr, " %s\n", _te == cudaSuccess ? "ok" : cudaGetErrorString(_te));  \
+    }                                                                                      \
   } while (0)
 
 // Growable device allocation.  Growth preserves the first `keep` bytes with a D2D copy on `stream`; allocation, copy and
