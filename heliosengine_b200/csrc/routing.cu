@@ -398,3 +398,99 @@ int32_t helios_gpu_message_route_merge(helios_gpu_world* w, uint64_t hash, uint3
 }
 
 }  // extern "C"
+
+// =====================================================================================================================
+// Allocation-free split: helios_gpu_message_route_split_static.  No counterpart in the reference; added
+// for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+// harnesses that forbid it).  Same stable G-way partition as helios_gpu_message_route_split — the same three kernels —
+// but input, slab and counts are the caller's device pointers, no world is involved, and the scratch (dest-major
+// histogram + the scan's tile totals) is the file-scope array below: HELIOS_GPU_STATIC_SPLIT_SCRATCH_BYTES that every GPU
+// which loads the library holds until exit.  Every call on a device shares that array and finds the previous call's
+// contents in it; nothing has to start at zero (each cell a kernel reads is written earlier in the same call), but two
+// calls that overlap on the GPU (different streams, no ordering) race on it.
+// In HOST code `g_split_scratch` is only a stand-in for the symbol, not a device address: the address the kernels get
+// comes from cudaGetSymbolAddress, resolved once per device with that device current.
+// =====================================================================================================================
+namespace {
+
+constexpr uint32_t kStaticMaxMessages = HELIOS_GPU_STATIC_SPLIT_MAX_MESSAGES;
+constexpr uint32_t kStaticMaxTiles = (kStaticMaxMessages + kRouteTile - 1) / kRouteTile;
+constexpr uint32_t kStaticHistWords = kStaticMaxTiles * kRouteMaxShards;             // 65 536
+constexpr uint32_t kStaticPartialWords = kStaticHistWords / kScanTile + 2;           // tile totals of the scan
+constexpr uint32_t kStaticScratchWords = kStaticHistWords + ((kStaticPartialWords + 63u) & ~63u);
+static_assert(kStaticScratchWords * 4 == HELIOS_GPU_STATIC_SPLIT_SCRATCH_BYTES, "header and scratch array disagree");
+
+static __device__ __align__(256) uint32_t g_split_scratch[kStaticScratchWords];
+
+constexpr int kStaticMaxDevices = 64;
+uint32_t* g_split_scratch_addr[kStaticMaxDevices] = {};  // per device: the array's DEVICE address
+thread_local char g_static_err[256] = "";
+
+__global__ void k_route_zero_counts(unsigned long long* __restrict__ counts, uint32_t n_shards) {
+  if (threadIdx.x < n_shards) counts[threadIdx.x] = 0;
+}
+
+int32_t static_fail(int32_t code, const char* fmt, unsigned long long a = 0, unsigned long long b = 0) {
+  std::snprintf(g_static_err, sizeof g_static_err, fmt, a, b);
+  return code;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* helios_gpu_static_split_last_error(void) { return g_static_err; }
+
+int32_t helios_gpu_message_route_split_static(void* cuda_stream, const void* d_msgs, uint64_t n, uint32_t msg_size,
+                                              uint32_t key_offset, uint64_t entities_per_shard, uint32_t n_shards,
+                                              void* d_out_slab, uint64_t capacity_msgs, uint64_t* d_out_counts) {
+  g_static_err[0] = 0;
+  if (!d_out_counts || (n && (!d_msgs || !d_out_slab)))
+    return static_fail(HELIOS_GPU_ERR_INVALID_ARGUMENT, "route_split_static: null device pointer");
+  if (n_shards == 0 || n_shards > kRouteMaxShards)
+    return static_fail(HELIOS_GPU_ERR_INVALID_ARGUMENT, "route_split_static: %llu shards, at most %llu", n_shards, kRouteMaxShards);
+  if (entities_per_shard == 0 || msg_size == 0 || msg_size % 4 != 0 || key_offset % 4 != 0 || key_offset + 4 > msg_size)
+    return static_fail(HELIOS_GPU_ERR_INVALID_ARGUMENT, "route_split_static: message size / key offset must be 4-byte multiples");
+  if (n > kStaticMaxMessages)
+    return static_fail(HELIOS_GPU_ERR_CAPACITY,
+                       "route_split_static: %llu messages exceed the static scratch (at most %llu per call; use "
+                       "helios_gpu_message_route_split, or split the batch)", n, kStaticMaxMessages);
+  if (capacity_msgs < n)
+    return static_fail(HELIOS_GPU_ERR_CAPACITY, "route_split_static: slab holds %llu messages, %llu queued", capacity_msgs, n);
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kStaticMaxDevices)
+    return static_fail(HELIOS_GPU_ERR_CUDA, "route_split_static: no current CUDA device");
+  if (!g_split_scratch_addr[dev]) {  // set-up, once per device, with that device current
+    uint32_t* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_split_scratch);
+    if (e != cudaSuccess || !p) {
+      std::snprintf(g_static_err, sizeof g_static_err, "route_split_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      return HELIOS_GPU_ERR_CUDA;
+    }
+    g_split_scratch_addr[dev] = p;
+  }
+  uint32_t* hist = g_split_scratch_addr[dev];
+  uint32_t* partials = hist + kStaticHistWords;
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  auto* counts = reinterpret_cast<unsigned long long*>(d_out_counts);
+  if (n == 0) {
+    k_route_zero_counts<<<1, kRouteMaxShards, 0, st>>>(counts, n_shards);
+  } else {
+    const uint32_t n_tiles = uint32_t((n + kRouteTile - 1) / kRouteTile);
+    const uint64_t cells = uint64_t(n_tiles) * n_shards;
+    const auto* src = static_cast<const uint8_t*>(d_msgs);
+    k_route_hist<<<n_tiles, kRouteTile, 0, st>>>(src, n, msg_size, key_offset, entities_per_shard, n_shards, n_tiles, hist);
+    exclusive_scan_u32(hist, hist, cells, partials, nullptr, st);
+    k_route_scatter<<<n_tiles, kRouteTile, 0, st>>>(src, n, msg_size, key_offset, entities_per_shard, n_shards, n_tiles, hist,
+                                                    static_cast<uint8_t*>(d_out_slab));
+    k_route_totals<<<1, kRouteMaxShards, 0, st>>>(hist, n_tiles, n_shards, n, counts);
+  }
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    std::snprintf(g_static_err, sizeof g_static_err, "route_split_static: launch failed: %s", cudaGetErrorString(e));
+    return HELIOS_GPU_ERR_CUDA;
+  }
+  return HELIOS_GPU_OK;
+}
+
+}  // extern "C"

@@ -29,6 +29,22 @@ def split(world: capi.World, name: str, which: int, key_offset: int, entities_pe
     return [int(c) for c in counts]
 
 
+
+STATIC_SPLIT_MAX_MESSAGES = 262144  # HELIOS_GPU_STATIC_SPLIT_MAX_MESSAGES
+
+
+def split_static(backend: capi.Backend, stream_ptr: int, msgs, n: int, msg_size: int, key_offset: int, entities_per_shard: int,
+                 n_shards: int, slab, counts):
+    """helios_gpu_message_route_split_static: the allocation-free split.  msgs / slab: uint8 device tensors, counts: a uint64
+    (int64) device tensor of n_shards elements; asynchronous on `stream_ptr`.  Raises HeliosError with the library's message."""
+    st = backend.fn("message_route_split_static")(C.c_void_p(stream_ptr), C.c_void_p(msgs.data_ptr()) if n else None, C.c_uint64(n),
+                                                  C.c_uint32(msg_size), C.c_uint32(key_offset), C.c_uint64(entities_per_shard),
+                                                  C.c_uint32(n_shards), C.c_void_p(slab.data_ptr()), C.c_uint64(slab.numel() // msg_size),
+                                                  C.c_void_p(counts.data_ptr()))
+    if st != capi.OK:
+        msg = backend.fn("static_split_last_error", C.c_char_p)()
+        raise capi.HeliosError(st, msg.decode() if msg else "")
+
 def merge(world: capi.World, name: str, which: int, src, n: int, key_offset: int, index_rebase: int):
     world._check(world.b.fn("message_route_merge")(world.h, C.c_uint64(capi.fnv1a(name)), C.c_uint32(which),
                                                    C.c_void_p(src.data_ptr()) if n else None, C.c_uint64(n), C.c_uint32(key_offset),

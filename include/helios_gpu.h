@@ -328,6 +328,27 @@ HELIOS_GPU_API int32_t helios_gpu_message_route_merge(helios_gpu_world* w, uint6
                                                       const void* d_src, uint64_t n, uint32_t key_offset,
                                                       uint64_t index_rebase);
 
+/* Allocation-free variant of helios_gpu_message_route_split.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid it).  The same stable n_shards-way partition, but with everything passed in: d_msgs (n messages of msg_size
+ * bytes, device memory), d_out_slab (device, room for capacity_msgs >= n messages), d_out_counts (device, n_shards
+ * uint64: messages per destination), all asynchronous on `cuda_stream` of the CURRENT device; no world, no host read-back.
+ * Its scratch is a file-scope `static __device__` array of HELIOS_GPU_STATIC_SPLIT_SCRATCH_BYTES (every GPU that loads the
+ * library holds it until exit), which bounds a call to HELIOS_GPU_STATIC_SPLIT_MAX_MESSAGES messages and 64 shards: more
+ * returns HELIOS_GPU_ERR_CAPACITY / HELIOS_GPU_ERR_INVALID_ARGUMENT with a message in
+ * helios_gpu_static_split_last_error() (thread-local).  The call makes no cudaMalloc / cudaFree / allocating library call;
+ * the first call on a device resolves the array's address (cudaGetSymbolAddress).  Every call on a device SHARES the
+ * array and finds the previous call's contents there (nothing needs to start at zero: each call overwrites what it
+ * reads); calls that overlap on the GPU — different streams without an ordering between them — race on it. */
+#define HELIOS_GPU_STATIC_SPLIT_MAX_MESSAGES 262144u
+#define HELIOS_GPU_STATIC_SPLIT_SCRATCH_BYTES 262400u
+HELIOS_GPU_API int32_t helios_gpu_message_route_split_static(void* cuda_stream, const void* d_msgs, uint64_t n,
+                                                             uint32_t msg_size, uint32_t key_offset,
+                                                             uint64_t entities_per_shard, uint32_t n_shards,
+                                                             void* d_out_slab, uint64_t capacity_msgs,
+                                                             uint64_t* d_out_counts);
+HELIOS_GPU_API const char* helios_gpu_static_split_last_error(void);
+
 /* Peer-memory form of the same routing (one process per GPU, NVLink): every shard owns two generations of an INBOX and of
  * a G x G count matrix (plain cudaMalloc, exported with helios_gpu_ipc_export, opened by the other shards).  A step on
  * every rank, all on the world's stream, with no slab ever going through a collective:
