@@ -147,6 +147,14 @@ struct helios_gpu_world::FastScratch {
   size_t mh_tables = ~size_t(0), stride_comps = 0;
   uint32_t last_chan_total[kMaxChannels] = {};
   FastCounters host{};
+  // entity bookkeeping + builtin messages (K9) run beside the row pipeline on a stream of their own
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  ~FastScratch() {
+    if (side) cudaStreamDestroy(side);
+    if (ev_fork) cudaEventDestroy(ev_fork);
+    if (ev_join) cudaEventDestroy(ev_join);
+  }
 };
 
 namespace {
@@ -170,12 +178,26 @@ struct ClassifyArgs {
   uint64_t registered_slots;
   uint32_t* matrix;
   FastCounters* counters;
+  // scratch the later kernels expect initialised: every CTA clears the slice of its 1024-command tile
+  uint32_t* init_close;   // [K + 16] -> kNone
+  uint32_t* last_target;  // [K + 16] -> 0
+  uint32_t* next;         // [2K]     -> kNone
+  uint64_t* J;            // [2K]     -> kUnresolved
+  uint32_t* has_succ;     // [2K / 4] -> 0 (one byte per op)
 };
 
-__global__ void __launch_bounds__(256) k_classify(ClassifyArgs a) {
+__global__ void __launch_bounds__(256, 6) k_classify(ClassifyArgs a) {
   extern __shared__ uint32_t s_cnt[];  // 2T + C
   const uint32_t T = a.ntables, C = 2 + 2 * a.ncomps, nrows = 2 * T + C;
   for (uint32_t i = threadIdx.x; i < nrows; i += 256) s_cnt[i] = 0;
+  {
+    const uint32_t slots_end = a.K + 16, ops_end = 2 * a.K;
+    const uint32_t s0 = blockIdx.x * kTile, s1 = blockIdx.x + 1 == gridDim.x ? slots_end : min(s0 + kTile, slots_end);
+    for (uint32_t i = s0 + threadIdx.x; i < s1; i += 256) { a.init_close[i] = kNone; a.last_target[i] = 0; }
+    const uint32_t o0 = 2 * blockIdx.x * kTile, o1 = min(o0 + 2 * kTile, ops_end);
+    for (uint32_t i = o0 + threadIdx.x; i < o1; i += 256) { a.next[i] = kNone; a.J[i] = kUnresolved; }
+    for (uint32_t i = o0 / 4 + threadIdx.x; i < (o1 + 3) / 4; i += 256) a.has_succ[i] = 0;
+  }
   __syncthreads();
   uint32_t invalid = 0, effective = 0, abort = 0;
   uint64_t touched_add = 0, touched_rem = 0;
@@ -706,7 +728,9 @@ struct MoveArgs {
   uint64_t* loc;
   uint32_t* ch_slot;             // per op: the slot it fills for good (kNone: writes no row)
   helios_gpu_entity_t* ch_ent;   // ... with this entity (staged records only)
-  uint32_t* ch_t0;               // ... whose values came from this table (staged records only)
+  uint64_t* ch_mask;             // ... and these component slots of the staged row (staged records only)
+  const uint64_t* wlive;         // per command: the components whose payload value it writes (Archetype::Set)
+  const uint8_t* payload;
 };
 
 // Copies the components both tables hold, up to four per round: all loads are issued before the first store.
@@ -750,11 +774,11 @@ __global__ void __launch_bounds__(256) k_final_gather(const MoveArgs a) {
     const uint32_t ck = o.x, t = o.z;
     helios_gpu_entity_t e = 0;
     uint64_t src = 0;
+    uint32_t kcmd = kNone;  // the command that appended the entity this op places (kNone: a pre-batch occupant of the table)
     if (ck & 1u) {  // Append: a slot that is never closed keeps its opener
       if (v.next[j] == kNone) {
         slot = o.y;
-        e = a.cmd[ck >> 1].entity;
-        src = v.srcloc[ck >> 1];
+        kcmd = ck >> 1;
       }
     } else if (!table_ends_empty(v, t)) {  // Remove: the LAST move into a surviving slot decides its occupant
       const uint64_t I = v.J[j];
@@ -763,9 +787,7 @@ __global__ void __launch_bounds__(256) k_final_gather(const MoveArgs a) {
         slot = uint32_t(I);
         for (;;) {  // occupant of the slot this op closed = the entity it moves
           if (X & kInstA) {
-            const uint32_t k = v.ops[uint32_t(X)].x >> 1;
-            e = a.cmd[k].entity;
-            src = v.srcloc[k];
+            kcmd = v.ops[uint32_t(X)].x >> 1;
             break;
           }
           const uint32_t tx = uint32_t(X >> 32), s = uint32_t(X);
@@ -781,21 +803,43 @@ __global__ void __launch_bounds__(256) k_final_gather(const MoveArgs a) {
     }
     a.ch_slot[j] = slot;
     if (slot != kNone) {
+      helios_gpu_command c{};
+      uint64_t live = 0;
+      if (kcmd != kNone) {
+        c = a.cmd[kcmd];
+        e = c.entity;
+        src = v.srcloc[kcmd];
+        live = a.wlive[kcmd];
+      }
       const uint32_t t0 = uint32_t(src >> 32), r0 = uint32_t(src);
       const bool direct = slot >= v.tcount0[t];
+      const uint64_t shared = a.tmask[t] & a.tmask[t0];
       a.loc[ent_index(e)] = (uint64_t(t) << 32) | slot;
       if (direct) {
         a.tents[t][slot] = e;
       } else {
         a.ch_ent[j] = e;
-        a.ch_t0[j] = t0;
+        a.ch_mask[j] = shared | live;
       }
       uint8_t* st = a.stage + size_t(j) * a.stride;
-      bytes = 8 + copy_row(a.tmask[t] & a.tmask[t0], a.csize,
+      auto dst_of = [&](int s, uint32_t sz) {
+        return direct ? static_cast<uint8_t*>(a.tcols[size_t(t) * 64 + s]) + size_t(slot) * sz : st + a.coffset[s];
+      };
+      // components the command overwrites anyway are not carried over
+      bytes = 8 + copy_row(shared & ~live, a.csize,
                            [&](int s, uint32_t sz) { return static_cast<const uint8_t*>(a.tcols[size_t(t0) * 64 + s]) + size_t(r0) * sz; },
-                           [&](int s, uint32_t sz) {
-                             return direct ? static_cast<uint8_t*>(a.tcols[size_t(t) * 64 + s]) + size_t(slot) * sz : st + a.coffset[s];
-                           });
+                           dst_of);
+      if (live) {  // Archetype::Set of the command's values (archetype.hpp:444-472), into the row while it is being written
+        uint64_t m = c.component_mask;
+        uint32_t off = c.payload_offset;
+        while (m) {
+          const int s = __ffsll(static_cast<long long>(m)) - 1;
+          m &= m - 1;
+          const uint32_t sz = a.csize[s];
+          if (live >> s & 1) copy_bytes(dst_of(s, sz), a.payload + off, sz);
+          off += (sz + 3u) & ~3u;
+        }
+      }
     }
   }
   const uint32_t n = __popc(__ballot_sync(0xFFFFFFFFu, slot != kNone));
@@ -817,7 +861,7 @@ __global__ void __launch_bounds__(256) k_scatter(const MoveArgs a) {
     if (slot >= v.tcount0[t]) continue;  // written directly by K8
     a.tents[t][slot] = a.ch_ent[j];
     const uint8_t* st = a.stage + size_t(j) * a.stride;
-    copy_row(a.tmask[t] & a.tmask[a.ch_t0[j]], a.csize,
+    copy_row(a.ch_mask[j], a.csize,
              [&](int s, uint32_t) { return st + a.coffset[s]; },
              [&](int s, uint32_t sz) { return static_cast<uint8_t*>(a.tcols[size_t(t) * 64 + s]) + size_t(slot) * sz; });
   }
@@ -871,7 +915,6 @@ __global__ void __launch_bounds__(256) k_finish(const FinishArgs a) {
   const uint32_t T = a.ntables, C = 2 + 2 * a.ncomps;
   const uint32_t wid = threadIdx.x >> 5, lane = threadIdx.x & 31u;
   if (blockIdx.x == 0) {
-    for (uint32_t t = threadIdx.x; t < T; t += 256) a.tcount[t] = a.tcount[t] + a.counters->tapp[t] - a.counters->trem[t];
     if (a.emit_messages)  // the device-resident reader views see the new messages without a host round trip
       for (uint32_t c = threadIdx.x; c < C; c += 256)
         if (a.counters->chan_total[c] && a.chan_count[c]) *a.chan_count[c] += a.counters->chan_total[c];
@@ -929,20 +972,31 @@ __global__ void __launch_bounds__(256) k_finish(const FinishArgs a) {
       warp_place_bits(b.rem_lo, 2 + a.ncomps, s_w[wid], place);
       warp_place_bits(b.rem_hi, 2 + a.ncomps + 32, s_w[wid], place);
     }
-    // Archetype::Set of the command's component values at the entity's final row
-    const uint64_t live = (k < a.K && (fl[r] & F_VALID)) ? a.wlive[k] : 0ull;
-    if (live) {
-      const uint64_t l = a.loc[ent_index(e)];
-      const uint32_t t = uint32_t(l >> 32), row = uint32_t(l);
-      uint64_t m = c.component_mask;
-      uint32_t off = c.payload_offset;
-      while (m) {
-        const int s = __ffsll(static_cast<long long>(m)) - 1;
-        m &= m - 1;
-        const uint32_t sz = a.csize[s];
-        if (live >> s & 1) copy_bytes(static_cast<uint8_t*>(a.tcols[size_t(t) * 64 + s]) + size_t(row) * sz, a.payload + off, sz);
-        off += (sz + 3u) & ~3u;
-      }
+  }
+}
+
+// K10 — last on the world's stream: Archetype::Set of the commands that overwrite a value WITHOUT migrating (the entity may
+// have been moved by somebody else's swap-and-pop: its final row comes from the location table), and the table counts.
+__global__ void __launch_bounds__(256) k_tail(const FinishArgs a) {
+  if (a.counters->abort) return;
+  if (blockIdx.x == 0)
+    for (uint32_t t = threadIdx.x; t < a.ntables; t += 256) a.tcount[t] = a.tcount[t] + a.counters->tapp[t] - a.counters->trem[t];
+  for (uint32_t r = 0; r < kTile / 256; ++r) {
+    const uint32_t k = blockIdx.x * kTile + r * 256 + threadIdx.x;
+    if (k >= a.K || (info_flags(a.info[k]) & (F_VALID | F_MIG)) != F_VALID) continue;
+    const uint64_t live = a.wlive[k];
+    if (!live) continue;
+    const helios_gpu_command c = a.cmd[k];
+    const uint64_t l = a.loc[ent_index(c.entity)];
+    const uint32_t t = uint32_t(l >> 32), row = uint32_t(l);
+    uint64_t m = c.component_mask;
+    uint32_t off = c.payload_offset;
+    while (m) {
+      const int s = __ffsll(static_cast<long long>(m)) - 1;
+      m &= m - 1;
+      const uint32_t sz = a.csize[s];
+      if (live >> s & 1) copy_bytes(static_cast<uint8_t*>(a.tcols[size_t(t) * 64 + s]) + size_t(row) * sz, a.payload + off, sz);
+      off += (sz + 3u) & ~3u;
     }
   }
 }
@@ -1046,20 +1100,15 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
   NEED(S.matrix, size_t(nrows) * ntiles * 4); NEED(S.rowtot, size_t(nrows) * 4);
   NEED(S.obase, (T + 1) * 4); NEED(S.tfmin, T * 4); NEED(S.ic_off, (T + 1) * 4);
   NEED(S.ops, Mmax * 16); NEED(S.next, Mmax * 4); NEED(S.prev, Mmax * 4);
-  NEED(S.J, Mmax * 8); NEED(S.has_succ, Mmax);
+  NEED(S.J, Mmax * 8); NEED(S.has_succ, Mmax + 16);
   const size_t nchunks = (Mmax + kChunk - 1) / kChunk;
   NEED(S.cmin, nchunks * 8); NEED(S.submin, nchunks * (kChunk / 32) * 8);
   NEED(S.cmin_last, nchunks * 8); NEED(S.tfirst, nchunks * 4); NEED(S.tlast, nchunks * 4);
   NEED(S.init_close, (size_t(K) + 16) * 4); NEED(S.last_target, (size_t(K) + 16) * 4);
-  NEED(S.ch_slot, Mmax * 4); NEED(S.ch_ent, Mmax * 8); NEED(S.ch_src, Mmax * 4);
+  NEED(S.ch_slot, Mmax * 4); NEED(S.ch_ent, Mmax * 8); NEED(S.ch_src, Mmax * 8);
   NEED(S.stage, Mmax * S.stage_stride);
   HG_CUDA(w, w->d_free.reserve((w->free_count + K) * 4, w->free_count * 4, st, true));
   HG_CUDA(w, cudaMemsetAsync(S.counters.ptr, 0, sizeof(FastCounters), st));
-  HG_CUDA(w, cudaMemsetAsync(S.init_close.ptr, 0xFF, (size_t(K) + 16) * 4, st));
-  HG_CUDA(w, cudaMemsetAsync(S.last_target.ptr, 0, (size_t(K) + 16) * 4, st));
-  HG_CUDA(w, cudaMemsetAsync(S.next.ptr, 0xFF, Mmax * 4, st));     // kNone: the slot an Append opens survives
-  HG_CUDA(w, cudaMemsetAsync(S.J.ptr, 0xFF, Mmax * 8, st));        // kUnresolved
-  HG_CUDA(w, cudaMemsetAsync(S.has_succ.ptr, 0, Mmax, st));
   FastCounters* dc = S.counters.as<FastCounters>();
 
   // ---- K1 / K2 ------------------------------------------------------------------------------------------------------
@@ -1071,6 +1120,8 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
   ca.em = w->builtin_messages ? S.em.as<uint64_t>() : nullptr;
   ca.registered_slots = ncomps >= 64 ? ~0ull : ((1ull << ncomps) - 1);
   ca.matrix = S.matrix.as<uint32_t>(); ca.counters = dc;
+  ca.init_close = S.init_close.as<uint32_t>(); ca.last_target = S.last_target.as<uint32_t>(); ca.next = S.next.as<uint32_t>();
+  ca.J = S.J.as<uint64_t>(); ca.has_succ = S.has_succ.as<uint32_t>();
   k_classify<<<ntiles, 256, nrows * 4, st>>>(ca);
   HG_TRACE(w, "fast k_classify");
 
@@ -1095,6 +1146,23 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
   }
   k_rowscan<<<nrows, 256, 0, st>>>(sa);
   HG_TRACE(w, "fast k_rowscan");
+  fa.cmd = d_cmds; fa.payload = d_payload; fa.K = K; fa.ntiles = ntiles; fa.ntables = T; fa.ncomps = ncomps;
+  fa.emit_messages = w->builtin_messages ? 1u : 0u;
+  fa.info = S.info.as<uint64_t>(); fa.em = w->builtin_messages ? S.em.as<uint64_t>() : nullptr; fa.wlive = S.wlive.as<uint64_t>();
+  fa.matrix = S.matrix.as<uint32_t>(); fa.gen = w->d_gen.as<uint32_t>(); fa.loc = w->d_loc.as<uint64_t>();
+  fa.free_list = w->d_free.as<uint32_t>(); fa.free_base = w->free_count; fa.tcols = w->d_tcols.as<void*>();
+  fa.csize = w->d_csize.as<uint32_t>(); fa.tcount = w->d_tcount.as<uint32_t>(); fa.counters = dc;
+  // fork: the destroyed entities' generations / locations / free-list entries and the builtin messages depend on K1 / K2
+  // only and touch nothing the row pipeline reads (it works from the pre-batch copies made by K1)
+  if (!S.side) {
+    HG_CUDA(w, cudaStreamCreateWithFlags(&S.side, cudaStreamNonBlocking));
+    HG_CUDA(w, cudaEventCreateWithFlags(&S.ev_fork, cudaEventDisableTiming));
+    HG_CUDA(w, cudaEventCreateWithFlags(&S.ev_join, cudaEventDisableTiming));
+  }
+  HG_CUDA(w, cudaEventRecord(S.ev_fork, st));
+  HG_CUDA(w, cudaStreamWaitEvent(S.side, S.ev_fork, 0));
+  k_finish<<<ntiles, 256, 0, S.side>>>(fa);
+  HG_CUDA(w, cudaEventRecord(S.ev_join, S.side));
 
   // ---- K3 .. K10 ----------------------------------------------------------------------------------------------------
   EmitArgs ea{K, ntiles, T, S.info.as<uint64_t>(), S.matrix.as<uint32_t>(), S.obase.as<uint32_t>(), w->d_tcount.as<uint32_t>(),
@@ -1116,18 +1184,14 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
   HG_TRACE(w, "fast k_resolve");
   MoveArgs ma{rv, d_cmds, w->d_tmask.as<uint64_t>(), w->d_tcols.as<void*>(), w->d_tents.as<helios_gpu_entity_t*>(),
               w->d_csize.as<uint32_t>(), S.coffset.as<uint32_t>(), S.stage.as<uint8_t>(), S.stage_stride, w->d_loc.as<uint64_t>(),
-              S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(), S.ch_src.as<uint32_t>()};
+              S.ch_slot.as<uint32_t>(), S.ch_ent.as<helios_gpu_entity_t>(), S.ch_src.as<uint64_t>(), S.wlive.as<uint64_t>(),
+              d_payload};
   k_final_gather<<<op_blocks, 256, 0, st>>>(ma);
   HG_TRACE(w, "fast k_final_gather");
   k_scatter<<<std::min<uint32_t>(op_blocks, uint32_t(w->sm_count) * 16u), 256, 0, st>>>(ma);
-  fa.cmd = d_cmds; fa.payload = d_payload; fa.K = K; fa.ntiles = ntiles; fa.ntables = T; fa.ncomps = ncomps;
-  fa.emit_messages = w->builtin_messages ? 1u : 0u;
-  fa.info = S.info.as<uint64_t>(); fa.em = w->builtin_messages ? S.em.as<uint64_t>() : nullptr; fa.wlive = S.wlive.as<uint64_t>();
-  fa.matrix = S.matrix.as<uint32_t>(); fa.gen = w->d_gen.as<uint32_t>(); fa.loc = w->d_loc.as<uint64_t>();
-  fa.free_list = w->d_free.as<uint32_t>(); fa.free_base = w->free_count; fa.tcols = w->d_tcols.as<void*>();
-  fa.csize = w->d_csize.as<uint32_t>(); fa.tcount = w->d_tcount.as<uint32_t>(); fa.counters = dc;
-  k_finish<<<ntiles, 256, 0, st>>>(fa);
-  HG_TRACE(w, "fast k_finish");
+  k_tail<<<ntiles, 256, 0, st>>>(fa);
+  HG_TRACE(w, "fast k_tail");
+  HG_CUDA(w, cudaStreamWaitEvent(st, S.ev_join, 0));
 
   // ---- the one read-back --------------------------------------------------------------------------------------------
   FastCounters& hc = S.host;
@@ -1142,7 +1206,7 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
     return HELIOS_GPU_OK;
   }
   ++w->mutation_epoch;
-  w->launches += 9;
+  w->launches += 10;
   for (uint32_t t = 0; t < T; ++t) w->tables[t].count = w->tables[t].count + hc.tapp[t] - hc.trem[t];
   const uint32_t n_destroy = hc.chan_total[0];
   if (n_destroy) {
