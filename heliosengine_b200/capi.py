@@ -69,6 +69,9 @@ class QueryDesc(C.Structure):
         ("n_sparse_data", C.c_uint32),
         ("sparse_data", C.c_uint64 * MAX_QUERY_COMPONENTS),
         ("sparse_rule", C.c_uint32),
+        ("n_optional", C.c_uint32),
+        ("optional", C.c_uint64 * MAX_QUERY_COMPONENTS),
+        ("optional_writes", C.c_uint8 * MAX_QUERY_COMPONENTS),
     ]
 
 
@@ -387,8 +390,10 @@ class World:
 
     # -- queries ----------------------------------------------------------------------------------------------
     def query(self, components: Sequence[tuple[str, bool]], with_: Sequence[str] = (), without: Sequence[str] = (),
-              sparse_data: Sequence[str] = (), sparse_rule: int = SPARSE_STRICT) -> "Query":
-        return Query(self, components, with_, without, sparse_data, sparse_rule)
+              sparse_data: Sequence[str] = (), sparse_rule: int = SPARSE_STRICT,
+              optional: Sequence[tuple[str, bool]] = ()) -> "Query":
+        """optional: (component, write) of `T*` / `const T*` arguments over archetype-stored components."""
+        return Query(self, components, with_, without, sparse_data, sparse_rule, optional)
 
     # -- commands ---------------------------------------------------------------------------------------------
     def enqueue(self, cmds: np.ndarray, payload: bytes | np.ndarray = b""):
@@ -512,10 +517,14 @@ class World:
 class Query:
     """Query<Cs..., With<...>, Without<...>> (reference query/query.hpp:658-1248)."""
 
-    def __init__(self, world: World, components, with_, without, sparse_data=(), sparse_rule=SPARSE_STRICT):
+    def __init__(self, world: World, components, with_, without, sparse_data=(), sparse_rule=SPARSE_STRICT, optional=()):
         self.w = world
         self.component_names = [name for name, _ in components]
         d = QueryDesc()
+        d.n_optional = len(optional)
+        for i, (name, write) in enumerate(optional):
+            d.optional[i] = fnv1a(name)
+            d.optional_writes[i] = 1 if write else 0
         d.n_sparse_data = len(sparse_data)
         for i, name in enumerate(sparse_data):
             d.sparse_data[i] = fnv1a(name)

@@ -107,6 +107,22 @@ int32_t launch_buff_optional(const helios_gpu_system_ctx* ctx) {
   return for_each_launch<0b1u, true, BuffOptionalBody, Health>(ctx, BuffOptionalBody{ctx->sparse.dir, p.ordinal});
 }
 
+// ---- "drift_optional": Query<Position&, const Velocity*> — the optional argument is ARCHETYPE-stored: tables with and without
+// Velocity are visited, the pointer is null where the table has no such column (iterator.hpp:49-68; query.cpp:1035-1075):
+// p += vel ? *vel : (0.25, -0.5) ------------------------------------------------------------------------------------
+struct DriftOptionalBody {
+  helios_gpu_world_view wv;
+  int32_t vel_slot;
+  __device__ void operator()(const Row& r, Position& p) const {
+    const Velocity* v = helios_gpu::try_get<const Velocity>(wv, r, vel_slot);
+    p.x = p.x + (v ? v->dx : 0.25f);
+    p.y = p.y + (v ? v->dy : -0.5f);
+  }
+};
+int32_t launch_drift_optional(const helios_gpu_system_ctx* ctx) {
+  return for_each_launch<0b1u, false, DriftOptionalBody, Position>(ctx, DriftOptionalBody{ctx->world_view, ctx->optional_slots[0]});
+}
+
 // ---- "team_tint": Query<const Team&, Tint&> -----------------------------------------------------------------
 struct TintBody {
   __device__ void operator()(const Row&, Team& t, Tint& c) const { c.rgba = (t.id * 0x00202020u) | 0xFF000000u; }
@@ -504,7 +520,7 @@ const Entry kBuiltins[] = {
     {"despawn_dead", launch_despawn_dead},
     {"alert_low_health", launch_alert_low_health}, {"heal_alerted", launch_heal_alerted},
     {"apply_gravity", launch_apply_gravity}, {"tick_counter", launch_tick_counter},
-    {"emit_multi", launch_emit_multi}, {"consume_two", launch_consume_two},
+    {"emit_multi", launch_emit_multi}, {"consume_two", launch_consume_two}, {"drift_optional", launch_drift_optional},
 };
 
 }  // namespace

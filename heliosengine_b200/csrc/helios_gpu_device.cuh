@@ -618,6 +618,16 @@ __device__ __forceinline__ bool sparse_has_ordinal(const helios_gpu_sparse_dir* 
   return __ldg(&dir->sparse[ordinal][uint32_t(e)]) != 0xFFFFFFFFu;
 }
 
+// Optional access to an ARCHETYPE-stored component — `T*` / `const T*` query arguments (iterator.hpp:49-68): the row's table
+// either has the column or it does not, so the pointer is the table's column base + row, or null.  `slot` is
+// ctx->optional_slots[k] (negative: the type is unknown to the world).  One cached directory load per call.
+template <typename T>
+__device__ __forceinline__ T* try_get(const helios_gpu_world_view& wv, const Row& r, int32_t slot) {
+  if (slot < 0) return nullptr;
+  T* base = static_cast<T*>(wv.table_columns[size_t(r.archetype) * HELIOS_GPU_MAX_COMPONENTS + slot]);
+  return base ? base + r.row : nullptr;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // Messages: warp-aggregated append (one atomic per warp) — BasicMessageWriter::Write (message/writer.hpp).
 // Order across warps is unspecified; ordered emission uses Row::flat_row as the slot instead.

@@ -184,6 +184,8 @@ int32_t fill_query_ctx(helios_gpu_system_ctx* ctx, helios_gpu_query* q, cudaStre
   ctx->match.required_mask = q->required_mask;
   ctx->match.without_mask = q->without_mask;
   for (uint32_t k = 0; k < q->desc.n_components; ++k) ctx->match.slots[k] = q->slots[k];
+  for (uint32_t k = 0; k < HELIOS_GPU_MAX_QUERY_COMPONENTS; ++k)
+    ctx->optional_slots[k] = k < q->desc.n_optional ? q->optional_slots[k] : -1;
   ctx->sparse_filter.membership = (q->sparse_require | q->sparse_exclude) ? w->d_membership.as<uint32_t>() : nullptr;
   ctx->sparse_filter.require = q->sparse_require;
   ctx->sparse_filter.exclude = q->sparse_exclude;
@@ -226,7 +228,7 @@ int32_t helios_gpu_query_create(helios_gpu_world* w, const helios_gpu_query_desc
   if (!w || !d || !out) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
   if (d->n_components > HELIOS_GPU_MAX_QUERY_COMPONENTS || d->n_with > HELIOS_GPU_MAX_COMPONENTS ||
       d->n_without > HELIOS_GPU_MAX_COMPONENTS || d->n_sparse_data > HELIOS_GPU_MAX_QUERY_COMPONENTS ||
-      d->sparse_rule > HELIOS_GPU_SPARSE_WITH_ENTITY)
+      d->n_optional > HELIOS_GPU_MAX_QUERY_COMPONENTS || d->sparse_rule > HELIOS_GPU_SPARSE_WITH_ENTITY)
     HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "query descriptor out of range");
   auto q = std::make_unique<helios_gpu_query>();
   q->world = w;
@@ -253,6 +255,12 @@ int32_t helios_gpu_query_create(helios_gpu_world* w, const helios_gpu_query_desc
     if (!is_sparse(s)) HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "sparse_data[%u] is archetype-stored", k);
     q->sparse_require |= ord_bit(s);
     q->sparse_fetch[k] = uint8_t(w->sparse_ord_of_slot[s]);
+  }
+  for (uint32_t k = 0; k < d->n_optional; ++k) {  // `T*`: no match term; an unregistered type is simply always null
+    const int s = slot(d->optional[k]);
+    if (s >= 0 && is_sparse(s))
+      HG_FAIL(w, HELIOS_GPU_ERR_INVALID_ARGUMENT, "optional[%u] is sparse-stored: fetch it with helios_gpu::sparse_try_get", k);
+    q->optional_slots[k] = s;
   }
   for (uint32_t k = 0; k < d->n_with; ++k) {
     const int s = slot(d->with[k]);

@@ -621,6 +621,8 @@ int32_t helios_gpu_schedule_add_system(helios_gpu_schedule* s, const helios_gpu_
   if (d->query) {
     for (uint32_t k = 0; k < d->query->desc.n_components; ++k)
       Policy::ins(d->query->desc.writes[k] ? e->policy.wc : e->policy.rc, d->query->desc.components[k]);
+    for (uint32_t k = 0; k < d->query->desc.n_optional; ++k)     // `T*` = write access, `const T*` = read (traits.hpp:73-97)
+      Policy::ins(d->query->desc.optional_writes[k] ? e->policy.wc : e->policy.rc, d->query->desc.optional[k]);
     for (uint32_t k = 0; k < d->query->desc.n_sparse_data; ++k)  // sparse data: const access (param_traits.hpp:43-75)
       Policy::ins(e->policy.rc, d->query->desc.sparse_data[k]);
   }

@@ -98,6 +98,7 @@ struct helios_gpu_query {
   uint64_t without_mask = 0;
   uint32_t sparse_require = 0, sparse_exclude = 0;  // per-entity membership test (sparse ordinals), after desc.sparse_rule
   uint8_t sparse_fetch[HELIOS_GPU_MAX_QUERY_COMPONENTS] = {};
+  int optional_slots[HELIOS_GPU_MAX_QUERY_COMPONENTS] = {};  // `T*` on archetype-stored types: slot or -1 (unregistered)
   bool never_matches = false;   // an unregistered With/required type (query.hpp:1754-1757, quirk #9)
   hgpu::DevBuf d_view;          // helios_gpu_query_view
   hgpu::DevBuf d_segments;      // helios_gpu_segment[table capacity]

@@ -199,6 +199,11 @@ void AppendArg(helios_gpu_query_desc& d) {
     // sparse data: reference / value access is a required term fetched by entity (iterator.hpp:88-100); pointer access
     // is nullable and takes no part in the match (iterator.hpp:49-68)
     if constexpr (!std::is_pointer_v<std::remove_cvref_t<A>>) d.sparse_data[d.n_sparse_data++] = TypeIndexOf<ComponentOf<A>>();
+  } else if constexpr (std::is_pointer_v<std::remove_cvref_t<A>>) {
+    // `T*` / `const T*` over an archetype-stored component: nullable, not part of the match (iterator.hpp:49-68)
+    d.optional[d.n_optional] = TypeIndexOf<ComponentOf<A>>();
+    d.optional_writes[d.n_optional] = kIsWriteAccess<A> ? 1 : 0;
+    ++d.n_optional;
   } else {
     d.components[d.n_components] = TypeIndexOf<ComponentOf<A>>();
     d.writes[d.n_components] = kIsWriteAccess<A> ? 1 : 0;

@@ -170,6 +170,14 @@ typedef struct helios_gpu_query_desc {
   uint32_t n_sparse_data;
   uint64_t sparse_data[HELIOS_GPU_MAX_QUERY_COMPONENTS];
   uint32_t sparse_rule; /* HELIOS_GPU_SPARSE_* below */
+  /* Optional access to ARCHETYPE-stored components: `T*` / `const T*` arguments (query/iterator.hpp:49-68; the reference's
+   * own case: src/ecs/tests/query/query.cpp:1035-1075).  Not part of the match — the query visits tables with and without
+   * the component — and the body gets a null pointer where the table has no such column: helios_gpu::try_get<T>(ctx
+   * world view, row, ctx->optional_slots[k]) (helios_gpu_device.cuh) resolves it from the table directory, one column
+   * base per table, no per-row search.  `T*` counts as write access, `const T*` as read (query/details/traits.hpp:73-97). */
+  uint32_t n_optional;
+  uint64_t optional[HELIOS_GPU_MAX_QUERY_COMPONENTS];
+  uint8_t optional_writes[HELIOS_GPU_MAX_QUERY_COMPONENTS];
 } helios_gpu_query_desc;
 /* How sparse terms are applied per entity (archetype matching always lets sparse types through,
  * query.hpp:1758-1760,1799-1801).  The reference is inconsistent here; all three behaviours exist:
@@ -557,6 +565,8 @@ typedef struct helios_gpu_system_ctx {
   const helios_gpu_msg_writer* d_writers[HELIOS_GPU_MAX_SYSTEM_MESSAGES];
   helios_gpu_msg_reader readers[HELIOS_GPU_MAX_SYSTEM_MESSAGES];
   const helios_gpu_msg_reader* d_readers[HELIOS_GPU_MAX_SYSTEM_MESSAGES];
+  /* component slot of helios_gpu_query_desc::optional[k]; -1 = the type is not registered in this world (always null) */
+  int32_t optional_slots[HELIOS_GPU_MAX_QUERY_COMPONENTS];
 } helios_gpu_system_ctx;
 #define HELIOS_GPU_RESOURCE_BYTES 4096u
 

@@ -755,6 +755,7 @@ struct QueryDesc {
   std::vector<TypeIndex> with;
   std::vector<TypeIndex> without;
   std::vector<TypeIndex> optional;  // pointer access `T*` / `const T*`: not part of the match, null when absent
+  std::vector<uint8_t> optional_writes;  // per optional component: 1 = `T*` (write access), 0 = `const T*` (traits.hpp:73-97)
   // How sparse-set types in with / without / required are treated per ENTITY (archetype matching always lets them
   // through, query.hpp:1758-1760,1799-1801):
   //   kStrict     every sparse With / Without / required-data type is enforced — TryGetFiltered's rule
@@ -1428,6 +1429,8 @@ struct AccessPolicy {
   void AddQuery(const QueryDesc& q) {
     for (size_t i = 0; i < q.required.size(); ++i)
       InsertSorted(q.writes[i] ? write_components : read_components, q.required[i]);
+    for (size_t i = 0; i < q.optional.size(); ++i)  // pointer access registers like any other access (traits.hpp:73-97)
+      InsertSorted(i < q.optional_writes.size() && q.optional_writes[i] ? write_components : read_components, q.optional[i]);
   }
   static bool Intersects(const std::vector<TypeIndex>& a, const std::vector<TypeIndex>& b) {
     size_t i = 0, j = 0;

@@ -387,6 +387,41 @@ void TestQuery() {
     CHECK(c[0] == w.components.Get(e, kPos));
   });
   CHECK(seen2.size() == 4);
+  {  // query.cpp:1035-1075 "Optional component": `const Velocity*` over an ARCHETYPE-stored type is no match term and is
+     // null where the entity lacks it
+    ComponentManager m;
+    RegisterAll(m);
+    const Position p1{1.0f, 0.0f};
+    const Velocity v2{5.0f, 0.0f};
+    const Entity e1{1, 0}, e2{2, 0};
+    m.InitEntity(e1);
+    m.InitEntity(e2);
+    const CompValue only_pos[1] = {{kPos, &p1}};
+    const CompValue pos_vel[2] = {{kPos, &p1}, {kVel, &v2}};
+    m.Add(e1, only_pos, 1);   // no Velocity
+    m.Add(e2, pos_vel, 2);    // has Velocity
+    QueryDesc q;
+    q.required = {kPos};
+    q.writes = {0};
+    q.optional = {kVel};
+    CHECK(QueryCount(m, q) == 2);  // "visits entities regardless of optional presence"
+    int nulls = 0, non_null = 0;
+    float captured = 0.0f;
+    ForEach(m, q, [&](Entity, uint8_t** ptrs) {
+      if (ptrs[1] == nullptr) ++nulls;
+      else { ++non_null; captured = reinterpret_cast<const Velocity*>(ptrs[1])->x; }
+    });
+    CHECK(nulls == 1 && non_null == 1);  // "nullptr when entity lacks it" / "non-null when entity has it"
+    CHECK(captured == 5.0f);
+    AccessPolicy pol;                    // `const T*` = read access, `T*` = write access (query/details/traits.hpp:73-97)
+    q.optional_writes = {0};
+    pol.AddQuery(q);
+    CHECK(pol.read_components.size() == 2 && pol.write_components.empty());
+    AccessPolicy pol_w;
+    q.optional_writes = {1};
+    pol_w.AddQuery(q);
+    CHECK(pol_w.write_components.size() == 1 && pol_w.write_components[0] == kVel);
+  }
 }
 
 // ---- command/queue.cpp (FIFO, Merge order), builtin_commands.cpp, schedule.cpp:946-1006 ----------------------------------

@@ -167,6 +167,15 @@ int32_t sys_buff_optional(const OCtx* c) {  // `const SparseBuff*`: TryGet by en
   });
   return 0;
 }
+int32_t sys_drift_optional(const OCtx* c) {  // Query<Position&, const Velocity*>: p[1] is null where the entity has no Velocity
+  ho::ForEach(c->world->world.components, *c->query, [](ho::Entity, uint8_t** p) {
+    auto* pos = reinterpret_cast<Position*>(p[0]);
+    const auto* vel = reinterpret_cast<const Velocity*>(p[1]);
+    pos->x = pos->x + (vel ? vel->dx : 0.25f);
+    pos->y = pos->y + (vel ? vel->dy : -0.5f);
+  });
+  return 0;
+}
 int32_t sys_team_tint(const OCtx* c) {
   visit(c, [](ho::Entity, uint8_t** p) {
     const uint32_t team = *reinterpret_cast<const uint32_t*>(p[0]);
@@ -396,7 +405,7 @@ const Builtin kBuiltins[] = {
     {"buff_heal", sys_buff_heal}, {"buff_optional", sys_buff_optional},
     {"alert_low_health", sys_alert_low_health}, {"heal_alerted", sys_heal_alerted},
     {"apply_gravity", sys_apply_gravity}, {"tick_counter", sys_tick_counter},
-    {"emit_multi", sys_emit_multi}, {"consume_two", sys_consume_two},
+    {"emit_multi", sys_emit_multi}, {"consume_two", sys_consume_two}, {"drift_optional", sys_drift_optional},
 };
 
 // helios_gpu_command → oracle Command (payload: ascending slot order, each value padded to 4 bytes).
@@ -623,6 +632,8 @@ HO_API int32_t helios_oracle_query_create(void* wp, const helios_gpu_query_desc*
     q->desc.required.push_back(d->sparse_data[k]);
     q->desc.writes.push_back(0);
   }
+  q->desc.optional.assign(d->optional, d->optional + d->n_optional);  // `T*` over archetype components (iterator.hpp:49-68)
+  q->desc.optional_writes.assign(d->optional_writes, d->optional_writes + d->n_optional);
   q->desc.with.assign(d->with, d->with + d->n_with);
   q->desc.without.assign(d->without, d->without + d->n_without);
   q->desc.sparse_rule = static_cast<ho::QueryDesc::SparseRule>(d->sparse_rule);

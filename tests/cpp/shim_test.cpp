@@ -52,6 +52,10 @@ int main(int argc, char** argv) {
   const helios_gpu_query_desc sd = SQ::Describe();
   CHECK(sd.n_components == 1 && sd.n_sparse_data == 1 && sd.n_with == 1 && sd.sparse_data[0] == ecs::TypeIndexOf<SparseBuff>());
   CHECK((ecs::Query<Position&, const SparseBuff*>::Describe().n_sparse_data == 0));
+  // `T*` over an ARCHETYPE-stored component: an optional term (query.cpp:1035-1075), write access for T*, read for const T*
+  const helios_gpu_query_desc od = ecs::Query<Position&, const Velocity*, Health*>::Describe();
+  CHECK(od.n_components == 1 && od.n_optional == 2 && od.optional[0] == ecs::TypeIndexOf<Velocity>() && od.optional_writes[0] == 0 &&
+        od.optional[1] == ecs::TypeIndexOf<Health>() && od.optional_writes[1] == 1);
   CHECK((ecs::Entity{3, 1} < ecs::Entity{4, 0}) && (ecs::Entity{3, 1} < ecs::Entity{3, 2}) && !ecs::Entity{}.Valid());
   CHECK(ecs::Entity::FromBits(ecs::Entity{7, 2}.Bits()) == (ecs::Entity{7, 2}));
 
