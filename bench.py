@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--entities", type=int, default=0, help="entities per GPU (default: the config's BASELINE size)")
-    ap.add_argument("--config", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5", "terminals", "sparse", "extract", "conditions", "async", "routing"],
+    ap.add_argument("--config", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5", "terminals", "sparse", "extract", "conditions", "async", "routing", "cfg3_sharded"],
                     help="cfg2 (default) is the headline workload; the others are secondary legs (bench_configs.py)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -156,14 +156,14 @@ def run_secondary(args):
     rank = int(os.environ.get("RANK", "0"))
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.config not in ("cfg5", "routing") and rank != 0:
+    if args.config not in ("cfg5", "routing", "cfg3_sharded") and rank != 0:
         return
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     stream = torch.cuda.Stream(device=dev)
     clocks = ClockSampler(local_rank)
     clocks.start()
-    if args.config in ("cfg5", "routing"):
+    if args.config in ("cfg5", "routing", "cfg3_sharded"):
         dist = None
         if world_size > 1:
             import torch.distributed as dist
@@ -218,6 +218,8 @@ def secondary_legs(args, torch, dist, dev, rank, world_size, local_rank):
         leg("cfg4", bench_configs.run_cfg4, 10, 3)
     leg("cfg5", bench_configs.run_cfg5, 5, 3, collective=True, no_e2e=True)
     leg("routing", bench_configs.run_routing, 10, 3, collective=True)
+    if world_size > 1:
+        leg("cfg3_sharded", bench_configs.run_cfg3_sharded, 4, 3, collective=True)
     return out
 
 

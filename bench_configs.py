@@ -858,3 +858,133 @@ def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
         peer.close()
     shard.close()
     return line
+
+
+def run_cfg3_sharded(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
+    """cfg3 over entity-range shards (SURVEY.md §8e "Commands apply"), WEAK scaling: every rank holds cfg3's world (`--entities`
+    per rank, default 8 388 608 in 16 tables) and emits cfg3's per-frame command mix against entities of EVERY shard.
+    A step = stable split of the rank's 64-byte command records by owner + all-to-all (NCCL over NVLink) + merge + device
+    unpack + ApplyDeferred on the owner.  value = commands applied per second over all ranks (max-over-ranks step time).
+
+    Untimed per frame: each rank draws cfg3's valid, distinct targets from its own tables, and the records are dealt out
+    round-robin to the other ranks so that every rank's outgoing queue names entities of all shards; the spawn ids come from
+    the last shard's next index (one sequence in (rank, emission) order), every rank emitting 1/G of cfg3's spawn count."""
+    from heliosengine_b200 import routing
+    n = args.entities or (1 << 23)
+    g = world_size
+    gpu = capi.load_gpu()
+    w = capi.World(gpu, device=dev.index, entity_capacity=n + n // 2, flags=capi.WORLD_NO_BUILTIN_MESSAGES)
+    w.set_stream(stream.cuda_stream)
+    worlds.build_cfg3(w, n)
+    name = routing.ROUTED_COMMAND
+    w.message_register(name, 64, capi.MSG_MANUAL)
+    steps, warm = args.steps, max(3, args.warmup)
+    dev_ms, apply_ms, e2e_s, n_applied, launches, invalid = [], [], [], [], [], 0
+
+    def exchange(t_send, send_counts):
+        sc = torch.tensor(send_counts, dtype=torch.int64, device=dev)
+        rc = torch.empty_like(sc)
+        if dist is not None:
+            dist.all_to_all_single(rc, sc)
+        else:
+            rc.copy_(sc)
+        rcl = [int(x) for x in rc.cpu().tolist()]
+        out = torch.empty(max(1, sum(rcl)) * 64, dtype=torch.uint8, device=dev)
+        if dist is not None:
+            dist.all_to_all_single(out[: sum(rcl) * 64], t_send, [c * 64 for c in rcl], [c * 64 for c in send_counts])
+        else:
+            out[: sum(rcl) * 64].copy_(t_send)
+        return out, sum(rcl)
+
+    with torch.cuda.stream(stream):
+        for frame in range(warm + steps):
+            snap = w.snapshot(columns=False)
+            ents = [a["entities"] for a in snap["archetypes"]]
+            types = [a["types"] for a in snap["archetypes"]]
+            despawn, insert, remove, n_spawn = worlds.cfg3_commands(w, ents, types, frame * 64 + rank, int(n * 0.10))
+            n_spawn //= g
+            cmds, payload = worlds.assemble_cfg3(w, capi.spawn_placeholder(np.arange(n_spawn)), despawn, insert, remove, frame * 64 + rank)
+            live = (cmds["entity"] >> np.uint64(32)) != capi.SPAWN_PLACEHOLDER_GENERATION
+            cmds["entity"][live] += np.uint64(rank * n)  # local -> global index
+            # ids: the routine of routing.route_commands, spelled out so that the records can be dealt before the timed region
+            mine = torch.tensor([n_spawn, ((g - 1) * n + w.next_entity_index()) if rank == g - 1 else 0], dtype=torch.int64, device=dev)
+            every = torch.empty(2 * g, dtype=torch.int64, device=dev)
+            if dist is not None:
+                dist.all_gather_into_tensor(every, mine)
+            else:
+                every.copy_(mine)
+            every = every.cpu().view(g, 2)
+            sp = [int(x) for x in every[:, 0].tolist()]
+            first = int(every[g - 1, 1]) + sum(sp[:rank])
+            timed = frame >= warm
+            e2e_frame = timed and ((frame - warm) % 2 == 1)
+            records = w.commands_route_pack(cmds, payload, first)
+            # deal: record i of this rank is EMITTED by rank (rank + i) % g
+            order = np.argsort((np.arange(records.size) % g), kind="stable")
+            dealt = records[order]
+            counts = np.bincount((np.arange(records.size) % g), minlength=g)
+            send_counts = [0] * g
+            for j in range(g):
+                send_counts[(rank + j) % g] = int(counts[j])
+            seg = np.concatenate([[0], np.cumsum(counts)])
+            parts = [None] * g
+            for j in range(g):
+                parts[(rank + j) % g] = dealt[seg[j]:seg[j + 1]]
+            t_send = torch.from_numpy(np.concatenate(parts).view(np.uint8).reshape(-1).copy()).to(dev)
+            emitted, n_emit = exchange(t_send, send_counts)
+            host_records = emitted[: n_emit * 64].cpu().numpy() if e2e_frame else None
+            if rank == g - 1 and sum(sp):
+                w.reserve_entities(sum(sp))
+            if not e2e_frame:
+                routing.merge(w, name, 1, emitted, n_emit, routing.ROUTED_KEY_OFFSET, 0)  # this rank's outgoing queue, device-resident
+            torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
+            l0 = w.launch_count()
+            a, b, c = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            t0 = time.perf_counter()
+            a.record(stream)
+            if e2e_frame:
+                w.message_write(name, host_records)
+            info = routing.route(w, name, torch, dev, dist, rank, g, n, routing.ROUTED_KEY_OFFSET, 1, True)
+            b.record(stream)
+            w.commands_apply_routed(name, 1)
+            c.record(stream)
+            torch.cuda.synchronize()
+            t1 = time.perf_counter()
+            st = w.apply_stats()
+            invalid += st.invalid
+            if timed:
+                launches.append(w.launch_count() - l0)
+                n_applied.append(sum(info["received"]))
+                if e2e_frame:
+                    e2e_s.append(t1 - t0)
+                else:
+                    dev_ms.append(a.elapsed_time(c))
+                    apply_ms.append(b.elapsed_time(c))
+            w.update()
+    t = torch.tensor([float(np.mean(dev_ms)), float(np.mean(apply_ms)), float(np.mean(e2e_s)) if e2e_s else 0.0], device=dev, dtype=torch.float64)
+    tot = torch.tensor([float(np.mean(n_applied)), float(invalid), float(w.entity_count())], device=dev, dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms, ap_ms, e2e = float(t[0]), float(t[1]), float(t[2])
+    total_cmds = float(tot[0])
+    stats = w.apply_stats()
+    w.close()
+    assert int(tot[1]) == 0, f"{int(tot[1])} routed commands were invalid on their owner"
+    return {
+        "metric": "commands_applied_per_sec", "value": total_cmds / (ms * 1e-3), "unit": "commands/s", "ms_per_step": ms,
+        "dtype": "u8/u64 (row bytes, entity ids)", "scaling": "weak",
+        "config": {"workload": f"cfg3 sharded: {n} entities / 16 tables per rank x {g} ranks, {int(total_cmds)} commands per frame in "
+                               "total, targets uniform over all shards; step = split by owner + all_to_all + merge + unpack + ApplyDeferred",
+                   "l2": "per-rank working set (tables 8M x ~40 B) exceeds L2; no flush",
+                   "parallelism": f"entity-range shards x{g}, NCCL all-to-all of 64-byte command records",
+                   "parity": "tests/test_sharded_commands.py (per-shard oracle replay + single-world entity states)"},
+        "apply_ms": ap_ms, "route_ms": ms - ap_ms, "pipeline": int(stats.pipeline), "entities_after": int(tot[2]),
+        "roofline": None,
+        "e2e": {"value": total_cmds / e2e if e2e else None, "unit": "commands/s", "h2d_bytes_per_step": int(total_cmds / g * 64),
+                "d2h_bytes_per_step": 64 + 8 * g,
+                "note": "host command records written to the queue inside the timed region; wall clock around route + apply"},
+        "cpu_baseline": None, "gpu_launches": int(np.sum(launches)),
+    }

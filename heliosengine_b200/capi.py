@@ -85,6 +85,16 @@ class Command(C.Structure):
 
 COMMAND_DTYPE = np.dtype([("kind", "<u4"), ("payload_offset", "<u4"), ("entity", "<u8"), ("component_mask", "<u8")])
 assert COMMAND_DTYPE.itemsize == C.sizeof(Command) == 24
+ROUTED_CMD_PAYLOAD = 40  # HELIOS_GPU_ROUTED_CMD_PAYLOAD
+ROUTED_COMMAND_DTYPE = np.dtype([("kind", "<u4"), ("payload_bytes", "<u4"), ("entity", "<u8"), ("component_mask", "<u8"),
+                                 ("payload", "u1", (ROUTED_CMD_PAYLOAD,))])
+assert ROUTED_COMMAND_DTYPE.itemsize == 64
+SPAWN_PLACEHOLDER_GENERATION = 0xFFFFFFFE
+
+
+def spawn_placeholder(j):
+    """HELIOS_GPU_SPAWN_PLACEHOLDER(j): the target of this rank's j-th Commands::Spawn before the ids are assigned."""
+    return (np.uint64(SPAWN_PLACEHOLDER_GENERATION) << np.uint64(32)) | np.asarray(j, dtype=np.uint64)
 
 
 class ApplyStats(C.Structure):
@@ -407,6 +417,25 @@ class World:
 
     def flush(self):
         self._check(self.b.fn("world_flush")(self.h))
+
+    def next_entity_index(self) -> int:
+        """EntityManager::next_index_ (entity/manager.hpp:294-305): the index the next fresh reservation takes."""
+        v = C.c_uint32()
+        self._check(self.b.fn("snapshot_entity_table")(self.h, C.byref(v), None, C.c_uint32(0), None, C.c_uint32(0), None, None))
+        return v.value
+
+    def commands_route_pack(self, cmds: np.ndarray, payload: bytes | np.ndarray, spawn_first_index: int) -> np.ndarray:
+        """Queue records + payload -> 64-byte routed records (spawn placeholders become global ids)."""
+        cmds = np.ascontiguousarray(cmds, dtype=COMMAND_DTYPE)
+        pay = np.frombuffer(payload, dtype=np.uint8) if isinstance(payload, (bytes, bytearray)) else np.ascontiguousarray(payload).view(np.uint8)
+        out = np.zeros(cmds.size, dtype=ROUTED_COMMAND_DTYPE)
+        self._check(self.b.fn("commands_route_pack")(self.h, _ptr(cmds) if cmds.size else None, C.c_uint64(cmds.size),
+                                                     _ptr(pay) if pay.size else None, C.c_uint64(pay.size),
+                                                     C.c_uint32(spawn_first_index), _ptr(out) if cmds.size else None))
+        return out
+
+    def commands_apply_routed(self, name: str, which: int = 1):
+        self._check(self.b.fn("commands_apply_routed")(self.h, C.c_uint64(fnv1a(name)), C.c_uint32(which)))
 
     def update(self):
         self._check(self.b.fn("world_update")(self.h))

@@ -161,6 +161,7 @@ struct helios_gpu_world {
   hgpu::HostCmdQueue global_queue;   // World::command_queue_
   hgpu::DevBuf staged_cmds, staged_payload;  // device copy of global_queue made by helios_gpu_commands_stage
   uint64_t staged_n = 0;                     // records staged (valid while == global_queue.cmds.size())
+  hgpu::DevBuf routed_cmds, routed_payload;  // commands unpacked from routed records (routed_commands.cu)
   helios_gpu_apply_stats last_stats{};
 
   std::vector<std::unique_ptr<hgpu::MsgChannel>> channels;

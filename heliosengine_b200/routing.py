@@ -78,6 +78,58 @@ def route(world: capi.World, name: str, torch, device, dist, rank: int, n_shards
     return {"sent": send_counts, "received": recv_counts, "bytes_sent": queued * size, "bytes_received": total * size}
 
 
+ROUTED_COMMAND = "helios::gpu::RoutedCommand"  # the 64-byte message type commands travel as
+ROUTED_KEY_OFFSET = 8                          # offsetof(helios_gpu_routed_command, entity)
+
+
+def route_commands(world: capi.World, cmds: np.ndarray, payload, n_spawns: int, torch, device, dist, rank: int, n_shards: int,
+                   entities_per_shard: int) -> dict:
+    """Sharded ApplyDeferred (include/helios_gpu.h "sharded deferred Commands"): this rank's command queue `cmds` / `payload`
+    (targets are GLOBAL entity ids, or capi.spawn_placeholder(j) for the rank's j-th Commands::Spawn, j < n_spawns) is
+    delivered to the owners of the targets and applied there in (source rank, position) order.
+
+        ids      all_gather of the spawn counts; the last shard (open-ended range) publishes the global next index and reserves
+                 the ids of every rank's spawns — the reference's single next_index_ sequence in (rank, emission) order
+        pack     helios_gpu_commands_route_pack -> 64-byte records -> the ROUTED_COMMAND queue of this world
+        route    split / all_to_all / merge of that queue (route(), key = the entity)
+        apply    helios_gpu_commands_apply_routed: reserved-entity flush + batch apply on the device"""
+    if "msg:" + ROUTED_COMMAND not in world.sizes:
+        world.message_register(ROUTED_COMMAND, capi.ROUTED_COMMAND_DTYPE.itemsize, capi.MSG_MANUAL)
+    last = n_shards - 1
+    mine = torch.tensor([n_spawns, (last * entities_per_shard + world.next_entity_index()) if rank == last else 0],
+                        dtype=torch.int64, device=device)
+    if dist is not None and n_shards > 1:
+        everyone = torch.empty(2 * n_shards, dtype=torch.int64, device=device)
+        dist.all_gather_into_tensor(everyone, mine)
+        everyone = everyone.cpu().view(n_shards, 2)
+    else:
+        everyone = mine.cpu().view(1, 2)
+    spawns = [int(x) for x in everyone[:, 0].tolist()]
+    first = int(everyone[last, 1]) + sum(spawns[:rank])
+    total_spawns = sum(spawns)
+    if first + n_spawns > 0xFFFFFFFF:
+        raise capi.HeliosError(capi.ERR_CAPACITY, "entity indices exhausted")
+    records = world.commands_route_pack(cmds, payload, first)
+    if records.size:
+        world.message_write(ROUTED_COMMAND, records)
+    if rank == last and total_spawns:
+        world.reserve_entities(total_spawns)  # fresh indices [next, next + total): what the records name after the re-base
+    info = route(world, ROUTED_COMMAND, torch, device, dist, rank, n_shards, entities_per_shard, ROUTED_KEY_OFFSET, 1, True)
+    world.commands_apply_routed(ROUTED_COMMAND, 1)
+    info["spawn_first_index"] = first
+    info["total_spawns"] = total_spawns
+    return info
+
+
+def reference_command_routing(queues: list[np.ndarray], entities_per_shard: int) -> list[np.ndarray]:
+    """Plain numpy statement used by the tests: queues[r] = rank r's routed records (GLOBAL ids); returns, per shard, the
+    records it must apply — (source rank, position) order, ids re-based to the shard's local indices."""
+    size = capi.ROUTED_COMMAND_DTYPE.itemsize
+    out = reference_routing([np.ascontiguousarray(q).view(np.uint8).reshape(-1) for q in queues], size, ROUTED_KEY_OFFSET,
+                            entities_per_shard)
+    return [o.view(capi.ROUTED_COMMAND_DTYPE) for o in out]
+
+
 def reference_routing(queues: list[np.ndarray], size: int, key_offset: int, entities_per_shard: int) -> list[np.ndarray]:
     """Plain numpy statement used by the tests: queues[r] = rank r's messages (bytes); returns what every rank must hold."""
     g = len(queues)

@@ -379,6 +379,37 @@ HELIOS_GPU_API int32_t helios_gpu_router_count(helios_gpu_router* r, uint32_t wh
 HELIOS_GPU_API int32_t helios_gpu_router_scatter(helios_gpu_router* r);
 HELIOS_GPU_API int32_t helios_gpu_router_deliver(helios_gpu_router* r, uint32_t which, uint32_t rebase, uint64_t* delivered);
 
+/* ---- sharded deferred Commands (SURVEY.md §8e "Commands apply") ----------------------------------------------------------
+ * Entities are partitioned by entity-index range (owner of index i = min(i / entities_per_shard, n_shards - 1), as for
+ * messages above); a command is applied by the shard that owns its target.  The reference has one world per process, so
+ * there is no routine to mirror; what is kept is its command ORDER (command/queue.hpp:137-163 FIFO; World::Flush,
+ * world.hpp:957-963): shard g applies the commands it owns ordered by (source rank, position in the source queue), and
+ * spawned entities take their indices from ONE sequence — EntityManager::ReserveEntity's next_index_ bump
+ * (entity/manager.hpp:294-305) — in (rank, emission) order: rank r's j-th Commands::Spawn gets
+ * next_index + (spawns of ranks < r) + j, whatever the number of shards.
+ * A command travels as a fixed 64-byte record through the message router (split / exchange / merge, key_offset 8):
+ *   1. every rank: helios_gpu_commands_route_pack(queue records -> helios_gpu_routed_command[]), spawn targets written as
+ *      HELIOS_GPU_SPAWN_PLACEHOLDER(j) become the global ids; helios_gpu_message_write the records into a 64-byte message
+ *      type, route it (helios_gpu_message_route_split / all-to-all / helios_gpu_message_route_merge, or a helios_gpu_router);
+ *   2. the shard that owns the new indices reserves them (helios_gpu_reserve_entities, total spawns of all ranks);
+ *   3. every rank: helios_gpu_commands_apply_routed = the reserved-entity flush + the batch apply of World::Flush over the
+ *      received records (unpacked on the device), in (source rank, position) order.
+ * Component slots (component_mask bits) must mean the same type on every shard: register components in the same order. */
+#define HELIOS_GPU_ROUTED_CMD_PAYLOAD 40u /* bytes of component values a routed Add/TryAdd carries */
+typedef struct helios_gpu_routed_command {
+  uint32_t kind;          /* helios_gpu_cmd_kind */
+  uint32_t payload_bytes;
+  helios_gpu_entity_t entity; /* GLOBAL id on the wire (the router's key, byte offset 8); local after the merge */
+  uint64_t component_mask;
+  uint8_t payload[HELIOS_GPU_ROUTED_CMD_PAYLOAD]; /* ascending slot order, each value padded to 4 bytes */
+} helios_gpu_routed_command;
+#define HELIOS_GPU_SPAWN_PLACEHOLDER_GENERATION 0xFFFFFFFEu
+#define HELIOS_GPU_SPAWN_PLACEHOLDER(j) ((((uint64_t)HELIOS_GPU_SPAWN_PLACEHOLDER_GENERATION) << 32) | (uint32_t)(j))
+HELIOS_GPU_API int32_t helios_gpu_commands_route_pack(helios_gpu_world* w, const helios_gpu_command* cmds, uint64_t n,
+                                                      const void* payload, uint64_t payload_bytes,
+                                                      uint32_t spawn_first_index, helios_gpu_routed_command* out);
+HELIOS_GPU_API int32_t helios_gpu_commands_apply_routed(helios_gpu_world* w, uint64_t type_hash, uint32_t which);
+
 /* ---- world resources (resource/manager.hpp:20-250; World::InsertResources / TryInsertResources / RemoveResources /
  * TryRemoveResources / ReadResource / WriteResource / HasResource, world.hpp:491-620; system parameters Res<const T> /
  * ResMut<T>, resource/param.hpp) -----------------------------------------------------------------------------------

@@ -887,6 +887,65 @@ HO_API int32_t helios_oracle_message_route_merge(void* wp, uint64_t hash, uint32
   return 0;
 }
 
+// ---- sharded deferred Commands (include/helios_gpu.h "sharded deferred Commands"): the plain statement -------------------
+// pack: one record per command, spawn placeholder j -> Entity{first + j, generation 1} (entity/manager.hpp:300-304).
+HO_API int32_t helios_oracle_commands_route_pack(void* wp, const helios_gpu_command* cmds, uint64_t n, const void* payload,
+                                                 uint64_t payload_bytes, uint32_t spawn_first_index, helios_gpu_routed_command* out) {
+  OWorld* w = W(wp);
+  for (uint64_t i = 0; i < n; ++i) {
+    helios_gpu_routed_command r;
+    std::memset(&r, 0, sizeof(r));
+    r.kind = cmds[i].kind;
+    r.component_mask = cmds[i].component_mask;
+    r.entity = cmds[i].entity;
+    if (uint32_t(cmds[i].entity >> 32) == HELIOS_GPU_SPAWN_PLACEHOLDER_GENERATION)
+      r.entity = (uint64_t(1) << 32) | (spawn_first_index + uint32_t(cmds[i].entity));
+    if (cmds[i].kind == HELIOS_GPU_CMD_ADD || cmds[i].kind == HELIOS_GPU_CMD_TRY_ADD) {
+      uint32_t bytes = 0;
+      for (uint32_t s = 0; s < 64; ++s)
+        if (cmds[i].component_mask >> s & 1) {
+          if (s >= w->slot_hash.size()) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+          bytes += (w->world.components.Meta(w->slot_hash[s])->size + 3u) & ~3u;
+        }
+      if (bytes > HELIOS_GPU_ROUTED_CMD_PAYLOAD) return HELIOS_GPU_ERR_CAPACITY;
+      if (uint64_t(cmds[i].payload_offset) + bytes > payload_bytes) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+      r.payload_bytes = bytes;
+      if (bytes) std::memcpy(r.payload, static_cast<const uint8_t*>(payload) + cmds[i].payload_offset, bytes);
+    }
+    out[i] = r;
+  }
+  return 0;
+}
+// apply: the received records, in queue order, are the command queue World::Flush executes (world.hpp:957-963).
+HO_API int32_t helios_oracle_commands_apply_routed(void* wp, uint64_t hash, uint32_t which) {
+  OWorld* w = W(wp);
+  if (which > 1) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (!w->world.messages.IsRegistered(hash)) return HELIOS_GPU_ERR_NOT_FOUND;
+  if (w->world.messages.ElemSize(hash) != sizeof(helios_gpu_routed_command)) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  const ho::MessageQueue& q = which ? w->world.messages.Current() : w->world.messages.Previous();
+  std::vector<uint8_t> bytes;
+  if (const auto* b = q.Bytes(hash)) bytes = *b;
+  const size_t n = bytes.size() / sizeof(helios_gpu_routed_command);
+  for (size_t i = 0; i < n; ++i) {
+    helios_gpu_routed_command r;
+    std::memcpy(&r, bytes.data() + i * sizeof(r), sizeof(r));
+    helios_gpu_command c{};
+    c.kind = r.kind;
+    c.payload_offset = 0;
+    c.entity = r.entity;
+    c.component_mask = r.component_mask;
+    ho::Command cmd = to_command(w, c, r.payload);
+    uint64_t rec = sizeof(helios_gpu_command);
+    for (const auto& v : cmd.values) rec += v.size();
+    w->world.components.migrate_bytes += rec;
+    w->world.command_queue.Enqueue(std::move(cmd));
+  }
+  w->world.messages.ReplaceQueue(which != 0, hash, nullptr, 0);
+  w->world.Flush();
+  w->faithful.reset();
+  return 0;
+}
+
 // ---- world resources (resource/manager.hpp; world.hpp:491-620) ---------------------------------------------------------------
 HO_API int32_t helios_oracle_resource_insert(void* wp, uint64_t hash, const void* v, uint32_t size) {
   if (!v || size == 0 || hash == 0) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
