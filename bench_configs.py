@@ -879,7 +879,7 @@ def run_cfg3_sharded(args, torch, dev, stream, peak, dist=None, rank=0, world_si
     name = routing.ROUTED_COMMAND
     w.message_register(name, 64, capi.MSG_MANUAL)
     steps, warm = args.steps, max(3, args.warmup)
-    dev_ms, apply_ms, e2e_s, n_applied, launches, invalid = [], [], [], [], [], 0
+    dev_ms, apply_ms, e2e_s, n_applied, launches, invalid, trace = [], [], [], [], [], 0, []
 
     def exchange(t_send, send_counts):
         sc = torch.tensor(send_counts, dtype=torch.int64, device=dev)
@@ -954,6 +954,8 @@ def run_cfg3_sharded(args, torch, dev, stream, peak, dist=None, rank=0, world_si
             t1 = time.perf_counter()
             st = w.apply_stats()
             invalid += st.invalid
+            trace.append((frame, "e2e" if e2e_frame else "dev", round(a.elapsed_time(b), 3), round(b.elapsed_time(c), 3),
+                          int(st.pipeline), int(st.fast_fallbacks), int(st.resolve_rounds), round((t1 - t0) * 1e3, 3)))
             if timed:
                 launches.append(w.launch_count() - l0)
                 n_applied.append(sum(info["received"]))
@@ -981,7 +983,9 @@ def run_cfg3_sharded(args, torch, dev, stream, peak, dist=None, rank=0, world_si
                    "l2": "per-rank working set (tables 8M x ~40 B) exceeds L2; no flush",
                    "parallelism": f"entity-range shards x{g}, NCCL all-to-all of 64-byte command records",
                    "parity": "tests/test_sharded_commands.py (per-shard oracle replay + single-world entity states)"},
-        "apply_ms": ap_ms, "route_ms": ms - ap_ms, "pipeline": int(stats.pipeline), "entities_after": int(tot[2]),
+        "apply_ms": ap_ms, "route_ms": ms - ap_ms, "median_ms_rank0": float(np.median(dev_ms)), "pipeline": int(stats.pipeline),
+        "entities_after": int(tot[2]),
+        "frames": trace,  # (frame, kind, route ms, apply ms, pipeline, fallbacks so far, resolve rounds, wall ms) on rank 0
         "roofline": None,
         "e2e": {"value": total_cmds / e2e if e2e else None, "unit": "commands/s", "h2d_bytes_per_step": int(total_cmds / g * 64),
                 "d2h_bytes_per_step": 64 + 8 * g,

@@ -733,6 +733,27 @@ class Schedule:
         self.w._check(self.w.b.fn("schedule_last_verdicts")(self.h, out, C.c_uint32(64)))
         return [int(out[i]) for i in range(len(self.names))]
 
+    # -- system-set ordering (system_set_handle.hpp:42-230, system_handle.hpp:105-180; schedule.cpp:209-339) --
+    def ensure_set(self, set_id: int):
+        """Schedule::Set(id)."""
+        self.w._check(self.w.b.fn("schedule_ensure_set")(self.h, C.c_uint64(set_id)))
+
+    def order_set_system(self, set_id: int, system: int, after: bool = False):
+        """Set(set_id).Before(system) / .After(system)."""
+        self.w._check(self.w.b.fn("schedule_order_set_system")(self.h, C.c_uint64(set_id), C.c_uint32(system), C.c_uint32(int(after))))
+
+    def order_sets(self, set_id: int, target_set: int, after: bool = False):
+        """Set(set_id).Before(SystemSetId) / .After(SystemSetId) — BeforeSet<T> / AfterSet<T>."""
+        self.w._check(self.w.b.fn("schedule_order_sets")(self.h, C.c_uint64(set_id), C.c_uint64(target_set), C.c_uint32(int(after))))
+
+    def order_system_set(self, system: int, set_id: int, after: bool = False):
+        """SystemHandle::Before(SystemSetId) / After(SystemSetId)."""
+        self.w._check(self.w.b.fn("schedule_order_system_set")(self.h, C.c_uint32(system), C.c_uint64(set_id), C.c_uint32(int(after))))
+
+    def set_sequence(self, set_id: int):
+        """Set(set_id).Sequence()."""
+        self.w._check(self.w.b.fn("schedule_set_sequence")(self.h, C.c_uint64(set_id)))
+
     def add_order(self, first: int, second: int):
         self.w._check(self.w.b.fn("schedule_add_order")(self.h, C.c_uint32(first), C.c_uint32(second)))
 

@@ -1044,6 +1044,7 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
   if (!w->fast) w->fast = new helios_gpu_world::FastScratch();
   auto& S = *w->fast;
   cudaStream_t st = w->stream;
+  HG_TRACE(w, "fast begin");
   const uint32_t K = uint32_t(n), ntiles = (K + kTile - 1) / kTile, C = 2 + 2 * ncomps, nrows = 2 * T + C;
   const size_t Mmax = 2 * size_t(K);
 
@@ -1234,7 +1235,9 @@ int32_t apply_queue_fast(helios_gpu_world* w, const helios_gpu_command* d_cmds, 
   w->last_stats.resolve_rounds = hc.rounds;
   w->last_stats.pipeline = 1;
   w->last_stats.fast_fallbacks = uint32_t(w->fast_fallbacks);
+  HG_TRACE(w, "fast read-back");
   for (uint32_t t = 0; t < T; ++t) HG_TRY(grow_ahead(w, t, hc.tapp[t], hc.trem[t]));
+  HG_TRACE(w, "fast grow_ahead");
   *done = true;
   return HELIOS_GPU_OK;
 }

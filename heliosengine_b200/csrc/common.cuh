@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -36,19 +38,28 @@ namespace hgpu {
     if (_s != HELIOS_GPU_OK) return _s; \
   } while (0)
 
-// Debug aid: HELIOS_GPU_TRACE=1 synchronises after every stage of the command pipelines and names it on stderr.
-inline bool trace_enabled() {
-  static const bool on = std::getenv("HELIOS_GPU_TRACE") != nullptr;
-  return on;
+// Debug aid: HELIOS_GPU_TRACE=1 synchronises after every stage of the command pipelines and names it on stderr with the
+// host time since the previous stage and the time the stream took to drain; HELIOS_GPU_TRACE=2 prints the host times only
+// (no synchronisation: the pipeline runs as in production, a blocking call shows up as a long host interval).
+inline int trace_enabled() {
+  static const int level = std::getenv("HELIOS_GPU_TRACE") ? std::max(1, std::atoi(std::getenv("HELIOS_GPU_TRACE"))) : 0;
+  return level;
 }
-#define HG_TRACE(w, what)                                                                  \
-  do {                                                                                     \
-    if (hgpu::trace_enabled()) {                                                           \
-      std::fprintf(stderr, "[helios_gpu] %s ...", what);                                   \
-      std::fflush(stderr);                                                                 \
-      const cudaError_t _te = cudaStreamSynchronize((w)->stream);                          \
-      std::fprintf(stderr, " %s\n", _te == cudaSuccess ? "ok" : cudaGetErrorString(_te));  \
-    }                                                                                      \
+inline double trace_ms() {  // wall-clock ms since the previous trace point
+  static std::chrono::steady_clock::time_point last = std::chrono::steady_clock::now();
+  const auto now = std::chrono::steady_clock::now();
+  const double ms = std::chrono::duration<double, std::milli>(now - last).count();
+  last = now;
+  return ms;
+}
+#define HG_TRACE(w, what)                                                                              \
+  do {                                                                                                 \
+    if (hgpu::trace_enabled()) {                                                                       \
+      const double _host = hgpu::trace_ms();                                                           \
+      const cudaError_t _te = hgpu::trace_enabled() == 1 ? cudaStreamSynchronize((w)->stream) : cudaSuccess; \
+      std::fprintf(stderr, "[helios_gpu] %-24s host %9.3f ms  drain %9.3f ms  %s\n", what, _host,      \
+                   hgpu::trace_ms(), _te == cudaSuccess ? "ok" : cudaGetErrorString(_te));             \
+    }                                                                                                  \
   } while (0)
 
 // Growable device allocation.  Growth preserves the first `keep` bytes with a D2D copy on `stream`; allocation, copy and

@@ -85,7 +85,9 @@ int32_t helios_gpu_commands_apply_routed(helios_gpu_world* w, uint64_t type_hash
     HG_FAIL(w, HELIOS_GPU_ERR_STATE, "apply_routed with commands pending in the local queue: route them too, or flush first");
   uint64_t& count = which ? ch->cur_count : ch->prev_count;
   const uint64_t n = count;
+  HG_TRACE(w, "routed begin");
   HG_TRY(flush_reserved(w));  // entity_manager_.Flush(InitEntity) comes first (world.hpp:960-961)
+  HG_TRACE(w, "routed flush_reserved");
   if (n == 0) return HELIOS_GPU_OK;
   cudaStream_t st = w->stream;
   HG_CUDA(w, w->routed_cmds.reserve(n * sizeof(helios_gpu_command), 0, st, true));
@@ -96,6 +98,7 @@ int32_t helios_gpu_commands_apply_routed(helios_gpu_world* w, uint64_t type_hash
   HG_CUDA(w, cudaGetLastError());
   count = 0;  // the queue is consumed
   HG_TRY(publish_channel(w, ch));
+  HG_TRACE(w, "routed k_unpack_routed");
   return apply_queue(w, w->routed_cmds.as<helios_gpu_command>(), w->routed_payload.as<uint8_t>(), n, /*dense=*/1);
 }
 

@@ -51,6 +51,7 @@ struct SysEntry {
   // run conditions: own list (SystemHandle::RunIf), set membership (InSet), and the merged list of the last build
   std::vector<std::unique_ptr<CondEntry>> conds;
   std::vector<uint64_t> sets;
+  std::vector<uint64_t> before_sets, after_sets;  // SystemHandle::Before/After(SystemSetId): do NOT create the set
   std::vector<CondEntry*> merged;
   cudaGraphExec_t cond_exec = nullptr;  // stream modes: {conditions, IF{body}} as a one-system graph
   uint64_t cond_epoch = ~0ull;
@@ -91,6 +92,12 @@ struct helios_gpu_schedule {
   DevBuf verdicts;                                       // u32 per registration index: 1 = ran, 0 = skipped
   DevBuf writer_counts;                                  // u64[system * MAX_SYSTEM_MESSAGES + writer]: messages written this run
   std::map<uint64_t, std::vector<std::unique_ptr<CondEntry>>> set_conds;  // SystemSet::RunIf
+  struct SetOrder {  // schedule/system_set.hpp:148-310: ordering targets of one set, inherited by its members at Build
+    std::vector<uint32_t> before_systems, after_systems;
+    std::vector<uint64_t> before_sets, after_sets;
+    bool sequence = false;
+  };
+  std::map<uint64_t, SetOrder> sets;  // every CREATED set (Schedule::Set / InSet / set RunIf), schedule.hpp:642-654
   cudaStream_t body_stream = nullptr;                    // captures IF bodies
   bool any_conditions = false;
   // stream mapping
@@ -653,7 +660,42 @@ int32_t helios_gpu_schedule_build(helios_gpu_schedule* s) {
   // Kahn with insertion-index tie-break (dag.cpp:65-126)
   std::vector<std::vector<uint32_t>> adj(n);
   std::vector<uint32_t> indeg(n, 0);
-  for (const auto& [a, b] : s->edges) {
+  std::vector<std::pair<uint32_t, uint32_t>> edges = s->edges;
+  {  // ResolveSetReferences (schedule.cpp:209-313): set-level constraints become system-level edges
+    std::map<uint64_t, std::vector<uint32_t>> members;  // registration order
+    for (uint32_t i = 0; i < n; ++i)
+      for (const uint64_t id : s->entries[i]->sets) members[id].push_back(i);
+    // edges between system i and every member of set `id`; a set nobody created is an error (kUnknownSet, :224-226)
+    const auto link = [&](uint32_t i, uint64_t id, bool system_first) -> bool {
+      if (!s->sets.count(id)) return false;
+      const auto it = members.find(id);
+      if (it == members.end()) return true;  // created, no members: nothing to order
+      for (const uint32_t m : it->second) edges.emplace_back(system_first ? i : m, system_first ? m : i);
+      return true;
+    };
+    for (uint32_t i = 0; i < n; ++i) {
+      SysEntry& e = *s->entries[i];
+      bool known = true;
+      for (const uint64_t id : e.before_sets) known = known && link(i, id, true);   // :236-248
+      for (const uint64_t id : e.after_sets) known = known && link(i, id, false);   // :250-262
+      for (const uint64_t mine : e.sets) {  // a member inherits the targets of its sets (:265-281), set targets expand (:283-309)
+        const auto it = s->sets.find(mine);
+        if (it == s->sets.end()) continue;
+        for (const uint32_t t : it->second.before_systems) edges.emplace_back(i, t);
+        for (const uint32_t t : it->second.after_systems) edges.emplace_back(t, i);
+        for (const uint64_t id : it->second.before_sets) known = known && link(i, id, true);
+        for (const uint64_t id : it->second.after_sets) known = known && link(i, id, false);
+      }
+      if (!known) HG_FAIL(w, HELIOS_GPU_ERR_NOT_FOUND, "Unknown set referenced by system '%s'", e.name.c_str());
+    }
+    for (const auto& [id, so] : s->sets) {  // ApplySequenceOrdering (:316-339): member k after member k-1
+      const auto it = members.find(id);
+      if (!so.sequence || it == members.end()) continue;
+      for (size_t k = 1; k < it->second.size(); ++k) edges.emplace_back(it->second[k - 1], it->second[k]);
+    }
+  }
+  for (const auto& [a, b] : edges) {
+    if (a == b) HG_FAIL(w, HELIOS_GPU_ERR_CYCLE, "Self-loop detected for system '%s'", s->entries[a]->name.c_str());  // dag.cpp:41-49
     adj[a].push_back(b);
     ++indeg[b];
   }
@@ -735,6 +777,7 @@ int32_t helios_gpu_schedule_add_set_condition(helios_gpu_schedule* s, uint64_t s
   std::unique_ptr<CondEntry> c;
   HG_TRY(make_condition(s, d, c));
   s->set_conds[set_id].push_back(std::move(c));
+  s->sets[set_id];  // Schedule::Set(id) creates the set
   s->built = false;
   return HELIOS_GPU_OK;
 }
@@ -744,6 +787,47 @@ int32_t helios_gpu_schedule_system_in_set(helios_gpu_schedule* s, uint32_t syste
   if (system_index >= s->entries.size()) HG_FAIL(s->world, HELIOS_GPU_ERR_NOT_FOUND, "InSet: unknown system %u", system_index);
   auto& sets = s->entries[system_index]->sets;
   if (std::find(sets.begin(), sets.end(), set_id) == sets.end()) sets.push_back(set_id);
+  s->sets[set_id];  // AddSystemToSet -> EnsureSet (schedule.hpp:656-658)
+  s->built = false;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_ensure_set(helios_gpu_schedule* s, uint64_t set_id) {
+  if (!s) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  s->sets[set_id];
+  s->built = false;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_order_set_system(helios_gpu_schedule* s, uint64_t set_id, uint32_t system_index, uint32_t after) {
+  if (!s) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (system_index >= s->entries.size()) HG_FAIL(s->world, HELIOS_GPU_ERR_NOT_FOUND, "set ordering: unknown system %u", system_index);
+  auto& v = after ? s->sets[set_id].after_systems : s->sets[set_id].before_systems;
+  if (std::find(v.begin(), v.end(), system_index) == v.end()) v.push_back(system_index);  // "adds it only once"
+  s->built = false;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_order_sets(helios_gpu_schedule* s, uint64_t set_id, uint64_t target_set_id, uint32_t after) {
+  if (!s) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  auto& v = after ? s->sets[set_id].after_sets : s->sets[set_id].before_sets;  // the TARGET set is not created here
+  if (std::find(v.begin(), v.end(), target_set_id) == v.end()) v.push_back(target_set_id);
+  s->built = false;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_order_system_set(helios_gpu_schedule* s, uint32_t system_index, uint64_t set_id, uint32_t after) {
+  if (!s) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (system_index >= s->entries.size()) HG_FAIL(s->world, HELIOS_GPU_ERR_NOT_FOUND, "set ordering: unknown system %u", system_index);
+  auto& v = after ? s->entries[system_index]->after_sets : s->entries[system_index]->before_sets;
+  if (std::find(v.begin(), v.end(), set_id) == v.end()) v.push_back(set_id);
+  s->built = false;
+  return HELIOS_GPU_OK;
+}
+
+int32_t helios_gpu_schedule_set_sequence(helios_gpu_schedule* s, uint64_t set_id) {
+  if (!s) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  s->sets[set_id].sequence = true;
   s->built = false;
   return HELIOS_GPU_OK;
 }

@@ -827,6 +827,18 @@ public:
       s_->world_->Check(helios_gpu_schedule_system_in_set(s_->s_, index_, TypeIndexOf<SetT>()));
       return *this;
     }
+    // SystemHandle::BeforeSet<Set>() / AfterSet<Set>() (schedule/system_handle.hpp:105-180): this system against every member
+    // of the set; the set must have been created by the time of Build (Schedule::Set / InSet), else Build reports kUnknownSet
+    template <typename SetT>
+    SystemHandle& BeforeSet() {
+      s_->world_->Check(helios_gpu_schedule_order_system_set(s_->s_, index_, TypeIndexOf<SetT>(), 0));
+      return *this;
+    }
+    template <typename SetT>
+    SystemHandle& AfterSet() {
+      s_->world_->Check(helios_gpu_schedule_order_system_set(s_->s_, index_, TypeIndexOf<SetT>(), 1));
+      return *this;
+    }
   private:
     Schedule* s_;
     uint32_t index_;
@@ -840,12 +852,50 @@ public:
       s_->world_->Check(helios_gpu_schedule_add_set_condition(s_->s_, id_, &d));
       return *this;
     }
+    // SystemSetHandle::Before / After (schedule/system_set_handle.hpp:42-230): every member of this set against a system ...
+    SystemSetHandle& Before(const SystemHandle& target) {
+      s_->world_->Check(helios_gpu_schedule_order_set_system(s_->s_, id_, target.Index(), 0));
+      return *this;
+    }
+    SystemSetHandle& After(const SystemHandle& target) {
+      s_->world_->Check(helios_gpu_schedule_order_set_system(s_->s_, id_, target.Index(), 1));
+      return *this;
+    }
+    // ... or against every member of another set
+    template <typename SetT>
+    SystemSetHandle& BeforeSet() {
+      s_->world_->Check(helios_gpu_schedule_order_sets(s_->s_, id_, TypeIndexOf<SetT>(), 0));
+      return *this;
+    }
+    template <typename SetT>
+    SystemSetHandle& AfterSet() {
+      s_->world_->Check(helios_gpu_schedule_order_sets(s_->s_, id_, TypeIndexOf<SetT>(), 1));
+      return *this;
+    }
+    SystemSetHandle& Before(const SystemSetHandle& target) {
+      s_->world_->Check(helios_gpu_schedule_order_sets(s_->s_, id_, target.id_, 0));
+      return *this;
+    }
+    SystemSetHandle& After(const SystemSetHandle& target) {
+      s_->world_->Check(helios_gpu_schedule_order_sets(s_->s_, id_, target.id_, 1));
+      return *this;
+    }
+    // SystemSetHandle::Sequence: the members run in registration order
+    SystemSetHandle& Sequence() {
+      s_->world_->Check(helios_gpu_schedule_set_sequence(s_->s_, id_));
+      return *this;
+    }
+    uint64_t Id() const noexcept { return id_; }
   private:
     Schedule* s_;
     uint64_t id_;
   };
+  // Schedule::Set<T>() (schedule.hpp:642-654): creates the set on first use
   template <typename SetT>
-  SystemSetHandle Set() { return SystemSetHandle(*this, TypeIndexOf<SetT>()); }
+  SystemSetHandle Set() {
+    world_->Check(helios_gpu_schedule_ensure_set(s_, TypeIndexOf<SetT>()));
+    return SystemSetHandle(*this, TypeIndexOf<SetT>());
+  }
 
   // 1 = the system (registration index) ran in the last run, 0 = a run condition skipped it
   std::vector<uint32_t> LastVerdicts() {

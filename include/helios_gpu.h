@@ -715,6 +715,26 @@ HELIOS_GPU_API int32_t helios_gpu_schedule_add_run_condition(helios_gpu_schedule
 HELIOS_GPU_API int32_t helios_gpu_schedule_add_set_condition(helios_gpu_schedule* s, uint64_t set_id,
                                                              const helios_gpu_condition_desc* desc);
 HELIOS_GPU_API int32_t helios_gpu_schedule_system_in_set(helios_gpu_schedule* s, uint32_t system_index, uint64_t set_id);
+/* ---- system-set ordering (schedule/system_set.hpp:148-310, system_set_handle.hpp:42-230, system_handle.hpp:105-180;
+ *      resolved by Schedule::ResolveSetReferences + ApplySequenceOrdering, src/ecs/src/schedule/schedule.cpp:209-339) ----------
+ * At Build every set-level constraint becomes system-level edges of the Kahn sort: a system's own set targets expand to the
+ * members (registration order) of the target set; a member inherits the system and set targets of each set it belongs to;
+ * a Sequence set chains its members.  A target set that was never created (Schedule::Set / InSet / a set RunIf create one)
+ * fails the build with HELIOS_GPU_ERR_NOT_FOUND ("Unknown set referenced by system ..." — ScheduleErrorKind::kUnknownSet);
+ * an edge from a system to itself is HELIOS_GPU_ERR_CYCLE (dag.cpp:41-49).  `after` = 0: Before, 1: After. */
+/* Schedule::Set(id) (schedule.hpp:642-654). */
+HELIOS_GPU_API int32_t helios_gpu_schedule_ensure_set(helios_gpu_schedule* s, uint64_t set_id);
+/* Set(set_id).Before / After(SystemId): every member of the set runs before / after the system.  Creates set_id. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_order_set_system(helios_gpu_schedule* s, uint64_t set_id, uint32_t system_index,
+                                                            uint32_t after);
+/* Set(set_id).Before / After(SystemSetId), BeforeSet<T> / AfterSet<T>: members against members.  Creates set_id only. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_order_sets(helios_gpu_schedule* s, uint64_t set_id, uint64_t target_set_id,
+                                                      uint32_t after);
+/* SystemHandle::Before / After(SystemSetId), BeforeSet<T> / AfterSet<T> (system_handle.hpp:105-180): creates nothing. */
+HELIOS_GPU_API int32_t helios_gpu_schedule_order_system_set(helios_gpu_schedule* s, uint32_t system_index, uint64_t set_id,
+                                                            uint32_t after);
+/* Set(set_id).Sequence(): member k runs after member k-1 (registration order). */
+HELIOS_GPU_API int32_t helios_gpu_schedule_set_sequence(helios_gpu_schedule* s, uint64_t set_id);
 /* Built-in condition launch functions by name: "entity_alive" (CUSTOM; params = one helios_gpu_entity_t) and every
  * reduction-style built-in terminal (TERMINAL). */
 HELIOS_GPU_API int32_t helios_gpu_builtin_condition(const char* name, helios_gpu_system_fn* out);

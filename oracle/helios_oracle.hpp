@@ -1517,32 +1517,97 @@ public:
     std::vector<RunCondition> conditions;  // SystemHandle::RunIf, in call order
     std::vector<uint64_t> sets;            // SystemHandle::InSet, in call order
     bool ran_last = true;
+    std::vector<uint64_t> before_set_targets, after_set_targets;  // ScheduleSystemMetadata (schedule.cpp:236-262)
+  };
+  // schedule/system_set.hpp:148-310 — what a SystemSet stores besides its run conditions
+  struct SetRecord {
+    std::vector<size_t> before_targets, after_targets;          // SystemId targets
+    std::vector<uint64_t> before_set_targets, after_set_targets;
+    bool sequence = false;
   };
   size_t Add(std::string name, SystemFn fn, AccessPolicy policy) {
-    entries_.push_back(std::make_unique<Entry>(Entry{std::move(name), std::move(fn), std::move(policy), {}, {}, {}, true}));
+    entries_.push_back(std::make_unique<Entry>(Entry{std::move(name), std::move(fn), std::move(policy), {}, {}, {}, true, {}, {}}));
     before_.emplace_back();
     return entries_.size() - 1;
   }
   // SystemHandle::RunIf / SystemSet::RunIf / SystemHandle::InSet — all mark the schedule dirty
   // (tests/schedule/system_set_handle.cpp:190-224).
   void RunIf(size_t system, RunCondition c) { entries_[system]->conditions.push_back(std::move(c)); dirty_ = true; }
-  void SetRunIf(uint64_t set_id, RunCondition c) { set_conditions_[set_id].push_back(std::move(c)); dirty_ = true; }
-  void InSet(size_t system, uint64_t set_id) {
+  void SetRunIf(uint64_t set_id, RunCondition c) { Set(set_id); set_conditions_[set_id].push_back(std::move(c)); dirty_ = true; }
+  void InSet(size_t system, uint64_t set_id) {  // AddSystemToSet -> EnsureSet (schedule.hpp:656-658)
     auto& v = entries_[system]->sets;
     if (std::find(v.begin(), v.end(), set_id) == v.end()) v.push_back(set_id);
-    dirty_ = true;
+    Set(set_id);
   }
+  // Schedule::Set (schedule.hpp:642-654): the handle of a set, created on first use.
+  SetRecord& Set(uint64_t set_id) { dirty_ = true; return sets_[set_id]; }
+  static void AddOnce(auto& v, auto x) { if (std::find(v.begin(), v.end(), x) == v.end()) v.push_back(x); }
+  // SystemSetHandle::Before/After (system_set_handle.hpp:42-230)
+  void SetBefore(uint64_t set_id, size_t system) { AddOnce(Set(set_id).before_targets, system); }
+  void SetAfter(uint64_t set_id, size_t system) { AddOnce(Set(set_id).after_targets, system); }
+  void SetBeforeSet(uint64_t set_id, uint64_t target) { AddOnce(Set(set_id).before_set_targets, target); }
+  void SetAfterSet(uint64_t set_id, uint64_t target) { AddOnce(Set(set_id).after_set_targets, target); }
+  void SetSequence(uint64_t set_id) { Set(set_id).sequence = true; }
+  // SystemHandle::Before/After(SystemSetId) (schedule.hpp:699-708): metadata only, the set is NOT created
+  void BeforeSet(size_t system, uint64_t set_id) { AddOnce(entries_[system]->before_set_targets, set_id); dirty_ = true; }
+  void AfterSet(size_t system, uint64_t set_id) { AddOnce(entries_[system]->after_set_targets, set_id); dirty_ = true; }
+  enum class BuildError { kNone, kCycle, kUnknownSet };
+  BuildError LastError() const noexcept { return error_; }
   bool Dirty() const noexcept { return dirty_; }
   // explicit ordering constraint: `a` runs before `b`.
   void Order(size_t a, size_t b) { before_[a].push_back(b); }
 
   // schedule.cpp:117-158 Build: DAG over explicit edges → execution order → conflict bitmask (:364-425).
   bool Build() {
+    error_ = BuildError::kNone;
+    // ResolveSetReferences (schedule.cpp:209-313), restated with per-build edge lists `bt` (before) / `at` (after)
+    const size_t n_sys = entries_.size();
+    std::vector<std::vector<size_t>> bt(n_sys), at(n_sys);
+    std::map<uint64_t, std::vector<size_t>> set_members;
+    for (size_t i = 0; i < n_sys; ++i)
+      for (const uint64_t id : entries_[i]->sets) set_members[id].push_back(i);
+    // expands set targets into member targets; false = a set nobody created (kUnknownSet)
+    const auto expand = [&](std::vector<uint64_t>& set_targets, std::vector<size_t>& system_targets) {
+      for (const uint64_t id : set_targets) {
+        if (!sets_.count(id)) return false;
+        const auto it = set_members.find(id);
+        if (it != set_members.end()) system_targets.insert(system_targets.end(), it->second.begin(), it->second.end());
+      }
+      set_targets.clear();
+      return true;
+    };
+    std::vector<std::vector<uint64_t>> pend_b(n_sys), pend_a(n_sys);
+    for (size_t i = 0; i < n_sys; ++i) {  // :236-262 the systems' own set targets
+      pend_b[i] = entries_[i]->before_set_targets;
+      pend_a[i] = entries_[i]->after_set_targets;
+      if (!expand(pend_b[i], bt[i]) || !expand(pend_a[i], at[i])) { error_ = BuildError::kUnknownSet; return false; }
+    }
+    for (size_t i = 0; i < n_sys; ++i)  // :265-281 members inherit the targets of their sets
+      for (const uint64_t id : entries_[i]->sets) {
+        const auto it = sets_.find(id);
+        if (it == sets_.end()) continue;
+        const SetRecord& r = it->second;
+        bt[i].insert(bt[i].end(), r.before_targets.begin(), r.before_targets.end());
+        at[i].insert(at[i].end(), r.after_targets.begin(), r.after_targets.end());
+        pend_b[i].insert(pend_b[i].end(), r.before_set_targets.begin(), r.before_set_targets.end());
+        pend_a[i].insert(pend_a[i].end(), r.after_set_targets.begin(), r.after_set_targets.end());
+      }
+    for (size_t i = 0; i < n_sys; ++i)  // :283-309 and the inherited set targets expand
+      if (!expand(pend_b[i], bt[i]) || !expand(pend_a[i], at[i])) { error_ = BuildError::kUnknownSet; return false; }
+    for (const auto& [id, r] : sets_) {  // ApplySequenceOrdering (:316-339)
+      const auto it = set_members.find(id);
+      if (!r.sequence || it == set_members.end() || it->second.size() < 2) continue;
+      for (size_t k = 1; k < it->second.size(); ++k) at[it->second[k]].push_back(it->second[k - 1]);
+    }
+    // BuildDag (schedule.cpp:186-207); Dag::AddEdge rejects from == to (dag.cpp:41-49)
     Dag dag;
-    for (size_t i = 0; i < entries_.size(); ++i) dag.AddNode();
-    for (size_t i = 0; i < entries_.size(); ++i)
-      for (const size_t j : before_[i]) dag.AddEdge(i, j);
-    if (!dag.Sort(order_)) return false;
+    for (size_t i = 0; i < n_sys; ++i) dag.AddNode();
+    for (size_t i = 0; i < n_sys; ++i) {
+      for (const size_t j : before_[i]) bt[i].push_back(j);
+      for (const size_t j : bt[i]) { if (i == j) { error_ = BuildError::kCycle; return false; } dag.AddEdge(i, j); }
+      for (const size_t j : at[i]) { if (i == j) { error_ = BuildError::kCycle; return false; } dag.AddEdge(j, i); }
+    }
+    if (!dag.Sort(order_)) { error_ = BuildError::kCycle; return false; }
     const size_t n = order_.size();
     conflicts_.assign(n, 0);
     for (size_t i = 0; i < n; ++i)
@@ -1602,6 +1667,8 @@ private:
   std::vector<size_t> order_;
   std::vector<uint64_t> conflicts_;
   std::map<uint64_t, std::vector<RunCondition>> set_conditions_;
+  std::map<uint64_t, SetRecord> sets_;
+  BuildError error_ = BuildError::kNone;
   std::vector<std::vector<const RunCondition*>> merged_;  // by registration index
   bool dirty_ = true;
 };

@@ -1176,6 +1176,39 @@ HO_API int32_t helios_oracle_schedule_system_in_set(void* sp, uint32_t system, u
   s->built = false;
   return 0;
 }
+// system-set ordering (system_set_handle.hpp:42-230, system_handle.hpp:105-180)
+HO_API int32_t helios_oracle_schedule_ensure_set(void* sp, uint64_t set_id) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  s->sched.Set(set_id);
+  s->built = false;
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_order_set_system(void* sp, uint64_t set_id, uint32_t system, uint32_t after) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  if (system >= s->entries.size()) return HELIOS_GPU_ERR_NOT_FOUND;
+  if (after) s->sched.SetAfter(set_id, system); else s->sched.SetBefore(set_id, system);
+  s->built = false;
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_order_sets(void* sp, uint64_t set_id, uint64_t target, uint32_t after) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  if (after) s->sched.SetAfterSet(set_id, target); else s->sched.SetBeforeSet(set_id, target);
+  s->built = false;
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_order_system_set(void* sp, uint32_t system, uint64_t set_id, uint32_t after) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  if (system >= s->entries.size()) return HELIOS_GPU_ERR_NOT_FOUND;
+  if (after) s->sched.AfterSet(system, set_id); else s->sched.BeforeSet(system, set_id);
+  s->built = false;
+  return 0;
+}
+HO_API int32_t helios_oracle_schedule_set_sequence(void* sp, uint64_t set_id) {
+  auto* s = reinterpret_cast<OSchedule*>(sp);
+  s->sched.SetSequence(set_id);
+  s->built = false;
+  return 0;
+}
 HO_API int32_t helios_oracle_schedule_last_verdicts(void* sp, uint32_t* out, uint32_t capacity) {
   auto* s = reinterpret_cast<OSchedule*>(sp);
   if (capacity < s->entries.size()) return HELIOS_GPU_ERR_CAPACITY;
@@ -1191,7 +1224,8 @@ HO_API int32_t helios_oracle_schedule_add_order(void* sp, uint32_t a, uint32_t b
 }
 HO_API int32_t helios_oracle_schedule_build(void* sp) {
   auto* s = reinterpret_cast<OSchedule*>(sp);
-  if (!s->sched.Build()) return HELIOS_GPU_ERR_CYCLE;
+  if (!s->sched.Build())
+    return s->sched.LastError() == ho::Schedule::BuildError::kUnknownSet ? HELIOS_GPU_ERR_NOT_FOUND : HELIOS_GPU_ERR_CYCLE;
   s->built = true;
   return 0;
 }

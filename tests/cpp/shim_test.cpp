@@ -239,6 +239,41 @@ int main(int argc, char** argv) {
     CHECK((schedule.LastVerdicts() == std::vector<uint32_t>{1, 0, 1, 0, 1, 1, 0}));
     CHECK(world.ReadComponent<Health>(ents[7]).hp == expected_hp + 4);
   }
+  // ---- system-set ordering (system_set_handle.hpp:42-230, system_handle.hpp:105-180; schedule.cpp:209-339) ----
+  {
+    struct Physics {};
+    struct Render {};
+    struct Never {};
+    ecs::World world;
+    world.RegisterComponent<Position>();
+    world.RegisterComponent<Health>();
+    helios_gpu_system_fn regen;
+    world.Check(helios_gpu_builtin_system("regen", &regen));
+    ecs::Schedule schedule(world);
+    auto s0 = schedule.AddGpu<ecs::Query<Health&>>("draw_a", regen);
+    auto s1 = schedule.AddGpu<ecs::Query<Health&>>("draw_b", regen);
+    auto s2 = schedule.AddGpu<ecs::Query<Health&>>("step_a", regen);
+    auto s3 = schedule.AddGpu<ecs::Query<Health&>>("step_b", regen);
+    auto s4 = schedule.AddGpu<ecs::Query<Health&>>("input", regen);
+    s0.InSet<Render>();
+    s1.InSet<Render>();
+    s2.InSet<Physics>();
+    s3.InSet<Physics>();
+    schedule.Set<Physics>().BeforeSet<Render>().After(s4).Sequence();  // input -> step_a -> step_b -> draw_a, draw_b
+    schedule.Build();
+    CHECK((schedule.ExecutionOrder() == std::vector<uint32_t>{4, 2, 3, 0, 1}));
+    s4.AfterSet<Never>();  // SystemHandle::After(SystemSetId) does not create the set: kUnknownSet at Build
+    bool unknown = false;
+    try { schedule.Build(); } catch (const ecs::GpuError& e) { unknown = e.Status() == HELIOS_GPU_ERR_NOT_FOUND; }
+    CHECK(unknown);
+    schedule.Set<Never>();
+    schedule.Build();
+    CHECK((schedule.ExecutionOrder() == std::vector<uint32_t>{4, 2, 3, 0, 1}));
+    schedule.Set<Render>().Before(s4);  // draw_* before input before step_* before draw_*: a cycle
+    bool cycle = false;
+    try { schedule.Build(); } catch (const ecs::GpuError& e) { cycle = e.Status() == HELIOS_GPU_ERR_CYCLE; }
+    CHECK(cycle);
+  }
   // ---- resources (tests/resource/manager.cpp:146-358; tests/schedule/schedule.cpp:559-597 CounterResource) ----
   {
     struct CounterResource { uint64_t value = 0; uint64_t pad = 0; };

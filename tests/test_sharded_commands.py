@@ -28,8 +28,10 @@ P, V, H, T = (worlds.cname(x) for x in SHORTS)
 GEN1 = np.uint64(1) << np.uint64(32)
 
 
-def fill(world, first_global, count):
-    """`count` entities whose values are functions of the GLOBAL index: the first half {Position}, the rest {Position, Velocity}."""
+def fill(world, first_global, count, warm=False):
+    """`count` entities whose values are functions of the GLOBAL index: the first half {Position}, the rest {Position, Velocity}.
+    warm: a first local batch (TryRemove<Velocity> on the last eighth) — it finds the {Position} table full, so it takes the
+    general pipeline and grows the table ahead; the batch under test then meets the steady-state pipeline's preconditions."""
     half = count // 2
     g = np.arange(first_global, first_global + count, dtype=np.float32)
     pos = np.stack([g, -g], axis=1).astype(np.float32)
@@ -37,14 +39,19 @@ def fill(world, first_global, count):
     if half:
         world.spawn_batch([P], half, [pos[:half].copy()], want_entities=False)
     if count - half:
-        world.spawn_batch([P, V], count - half, [pos[half:].copy(), vel[half:].copy()], want_entities=False)
+        ents = world.spawn_batch([P, V], count - half, [pos[half:].copy(), vel[half:].copy()])
+        if warm:
+            cmds = np.zeros(count // 8, dtype=capi.COMMAND_DTYPE)
+            cmds["kind"], cmds["entity"], cmds["component_mask"] = capi.CMD_TRY_REMOVE, ents[-(count // 8):], world.mask([V])
+            world.enqueue(cmds, b"")
+            world.flush()
 
 
-def make_world(backend, device=0, first_global=0, count=0, flags=0):
+def make_world(backend, device=0, first_global=0, count=0, flags=0, warm=False):
     w = capi.World(backend, device=device, flags=flags)
     worlds.register_all(w, SHORTS)
     w.message_register(routing.ROUTED_COMMAND, 64, capi.MSG_MANUAL)
-    fill(w, first_global, count)
+    fill(w, first_global, count, warm)
     w.update()
     w.update()  # the loader's builtin messages age out: only the commands' messages are compared
     return w
@@ -62,10 +69,12 @@ def make_queue(w, rank, n_global, n, n_spawns, seed, distinct=False):
     else:
         targets = rng.integers(0, n_global, n)
     kinds = rng.choice([capi.CMD_ADD, capi.CMD_TRY_ADD, capi.CMD_TRY_REMOVE, capi.CMD_CLEAR, capi.CMD_TRY_DESTROY, capi.CMD_DESTROY],
-                       size=n, p=[0.3, 0.2, 0.2, 0.05, 0.2, 0.05])
+                       size=n, p=[0.3, 0, 0.4, 0, 0.3, 0] if distinct else [0.3, 0.2, 0.2, 0.05, 0.2, 0.05])
     specs = []
     for k, t in zip(kinds, targets):
         names = [worlds.cname(x) for x in rng.choice(SHORTS, size=int(rng.integers(1, 4)), replace=False)]
+        if distinct:  # only moves between the two tables that exist: {P,V} -> {P} by TryRemove, Add overwrites in place
+            names = [V] if k == capi.CMD_TRY_REMOVE else [P]
         specs.append((int(k), int(t) | int(GEN1), names if k in (capi.CMD_ADD, capi.CMD_TRY_ADD, capi.CMD_TRY_REMOVE) else []))
     at = sorted(rng.integers(0, len(specs) + 1, n_spawns).tolist())
     for j in reversed(range(n_spawns)):
@@ -110,12 +119,12 @@ def entity_states(snap, rebase):
     return out
 
 
-def expected(oracle, queues, per, g, last_count, flags=0):
+def expected(oracle, queues, per, g, last_count, flags=0, warm=False):
     """(per-shard replay snapshots, single-world entity states): the two statements of the module docstring."""
     n_global = per * (g - 1) + last_count
     # ids: one sequence over (rank, emission)
     spawns = [count_spawns(q[0]) for q in queues]
-    ws = [make_world(oracle, 0, r * per, per if r < g - 1 else last_count, flags) for r in range(g)]
+    ws = [make_world(oracle, 0, r * per, per if r < g - 1 else last_count, flags, warm) for r in range(g)]
     recs = [ws[r].commands_route_pack(queues[r][0], queues[r][1], n_global + sum(spawns[:r])) for r in range(g)]
     shard_snaps = []
     for r, rec in enumerate(routing.reference_command_routing(recs, per)):
@@ -128,7 +137,7 @@ def expected(oracle, queues, per, g, last_count, flags=0):
         ws[r].close()
     single = make_world(oracle, 0, 0, 0, flags)
     for r in range(g):  # the same index -> value assignment as the shards: shard after shard
-        fill(single, r * per, per if r < g - 1 else last_count)
+        fill(single, r * per, per if r < g - 1 else last_count, warm)
     if sum(spawns):
         single.reserve_entities(sum(spawns))
     for rec in recs:
@@ -148,10 +157,10 @@ def check(shard_snaps, want_snaps, want_states, per):
     assert merged == want_states
 
 
-def run_in_process(backend, oracle, g, per, last_count, n, n_spawns, seed, device="cpu", flags=0, distinct=False):
+def run_in_process(backend, oracle, g, per, last_count, n, n_spawns, seed, device="cpu", flags=0, distinct=False, warm=False):
     """All G shards in this process (`dist` = None): split on every shard, hand the slabs over, merge + apply on every shard."""
     n_global = per * (g - 1) + last_count
-    ws = [make_world(backend, 0, r * per, per if r < g - 1 else last_count, flags) for r in range(g)]
+    ws = [make_world(backend, 0, r * per, per if r < g - 1 else last_count, flags, warm) for r in range(g)]
     queues = [make_queue(ws[r], r, n_global, n + 13 * r, n_spawns + r if n_spawns else 0, seed, distinct) for r in range(g)]
     spawns = [n_spawns + r if n_spawns else 0 for r in range(g)]
     first = n_global
@@ -180,7 +189,7 @@ def run_in_process(backend, oracle, g, per, last_count, n, n_spawns, seed, devic
     stats = [w.apply_stats() for w in ws]
     for w in ws:
         w.close()
-    want_snaps, want_states = expected(oracle, queues, per, g, last_count, flags)
+    want_snaps, want_states = expected(oracle, queues, per, g, last_count, flags, warm)
     check(snaps, want_snaps, want_states, per)
     return stats
 
@@ -188,6 +197,10 @@ def run_in_process(backend, oracle, g, per, last_count, n, n_spawns, seed, devic
 @pytest.mark.parametrize("g,per,last,n,spawns", [(1, 64, 64, 40, 3), (2, 128, 100, 300, 5), (3, 500, 500, 2000, 0), (4, 256, 7, 900, 11)])
 def test_oracle_shards_in_one_process(oracle, g, per, last, n, spawns):
     run_in_process(oracle, oracle, g, per, last, n, spawns, seed=g * 1000 + n)
+
+
+def test_oracle_shards_distinct_targets_after_a_local_batch(oracle):
+    run_in_process(oracle, oracle, 4, 1 << 12, 1 << 12, 900, 0, seed=5, distinct=True, warm=True)
 
 
 def test_pack_limits(oracle):
@@ -278,7 +291,7 @@ def test_gpu_shards_on_one_device(gpu, oracle, g, per, last, n, spawns):
 def test_gpu_shards_steady_state_pipeline(gpu, oracle):
     """One command per entity over the whole box (cfg3's shape): every shard's batch takes the steady-state pipeline."""
     stats = run_in_process(gpu, oracle, 4, 1 << 15, 1 << 15, 9000, 0, seed=5, device="cuda:0",
-                           flags=capi.WORLD_NO_BUILTIN_MESSAGES, distinct=True)
+                           flags=capi.WORLD_NO_BUILTIN_MESSAGES, distinct=True, warm=True)
     assert all(s.pipeline == 1 for s in stats), [s.pipeline for s in stats]
 
 
