@@ -245,3 +245,218 @@ def emulate_shards(backend: capi.Backend, torch, device, n_total: int, world_siz
     for s in shards:
         s.close()
     return np.concatenate([p for p, _ in states]), np.concatenate([v for _, v in states])
+
+
+# =====================================================================================================================
+# Spatial bands: the halo-exchange form (include/helios_gpu.h "Spatial bands").  Shard g owns the grid rows
+# [g * R, (g + 1) * R) and the boids whose cell lies in them; boids that cross a band edge migrate through the message
+# router and the ECS command path (Destroy here, Spawn + Add there); per step each shard reads ONE grid row from each
+# neighbour.  The initial placement is still the entity-ID range (every shard spawns its id slice wherever those boids are):
+# the first step's migration sorts the flock into bands.
+# =====================================================================================================================
+BOID_ID = worlds.NS + "BoidId"
+MIGRATION = worlds.NS + "BoidMigration"
+MIGRATION_DTYPE = np.dtype([("key", "<u8"), ("id", "<u4"), ("pad", "<u4"), ("x", "<f4"), ("y", "<f4"), ("dx", "<f4"), ("dy", "<f4")])
+assert MIGRATION_DTYPE.itemsize == 32
+
+
+class BandShard:
+    """One rank's band: a world holding {Position, Velocity, BoidId} + the boids system in band mode."""
+
+    def __init__(self, backend: capi.Backend, n_total: int, world_size: int, n_shards: int = 1, shard: int = 0, device: int = 0,
+                 params: dict | None = None, vel_scale: float = 1.0):
+        self.b = backend
+        self.n_shards, self.shard, self.n_total = n_shards, shard, n_total
+        lo, hi = shard * n_total // n_shards, (shard + 1) * n_total // n_shards  # initial placement: id ranges (any remainder)
+        self.world = capi.World(backend, device=device, entity_capacity=(hi - lo) + (hi - lo) // 4 + 1024,
+                                flags=capi.WORLD_NO_BUILTIN_MESSAGES)
+        P, V = worlds.cname("Position"), worlds.cname("Velocity")
+        worlds.register_all(self.world, ["Position", "Velocity"])
+        self.world.register_component(BOID_ID, 4, 4)
+        self.world.message_register(MIGRATION, MIGRATION_DTYPE.itemsize, capi.MSG_MANUAL)
+        pos, vel = initial_state(n_total, world_size, lo, hi, vel_scale=vel_scale)
+        if hi > lo:
+            self.world.spawn_batch([P, V, BOID_ID], hi - lo, [pos, vel, np.arange(lo, hi, dtype=np.uint32)], want_entities=False)
+        p = dict(DEFAULT_PARAMS)
+        p.update(params or {})
+        self.params = BoidsParams(float(world_size), p["dt"], p["w_separation"], p["w_alignment"], p["w_cohesion"], p["max_speed"])
+        self.h = C.c_void_p()
+        self.world._check(backend.fn("boids_band_create")(self.world.h, C.c_uint64(capi.fnv1a(P)), C.c_uint64(capi.fnv1a(V)),
+                                                          C.c_uint64(capi.fnv1a(BOID_ID)), C.byref(self.params),
+                                                          C.c_uint32(n_shards), C.c_uint32(shard), C.byref(self.h)))
+        n, rp, lo_r, hi_r, eb = C.c_uint64(), C.c_uint32(), C.c_uint32(), C.c_uint32(), C.c_uint64()
+        self.world._check(backend.fn("boids_band_info")(self.h, C.byref(n), C.byref(rp), C.byref(lo_r), C.byref(hi_r), C.byref(eb)))
+        self.rows_per, self.row_lo, self.row_hi, self.export_bytes = rp.value, lo_r.value, hi_r.value, eb.value
+
+    # -- C ABI ----------------------------------------------------------------------------------------------------------
+    def n_local(self) -> int:
+        n = C.c_uint64()
+        self.world._check(self.b.fn("boids_band_info")(self.h, C.byref(n), None, None, None, None))
+        return n.value
+
+    def export_ptr(self, generation: int, side: int) -> int:
+        p = C.c_void_p()
+        self.world._check(self.b.fn("boids_band_export")(self.h, C.c_uint32(generation), C.c_uint32(side), C.byref(p)))
+        return p.value
+
+    def set_halo(self, generation: int, side: int, ptr: int | None):
+        self.world._check(self.b.fn("boids_band_set_halo")(self.h, C.c_uint32(generation), C.c_uint32(side), C.c_void_p(ptr)))
+
+    def leavers(self) -> int:
+        n = C.c_uint64()
+        self.world._check(self.b.fn("boids_band_leavers")(self.h, C.c_uint64(capi.fnv1a(MIGRATION)), C.byref(n)))
+        return n.value
+
+    def arrivals(self) -> int:
+        n = C.c_uint64()
+        self.world._check(self.b.fn("boids_band_arrivals")(self.h, C.c_uint64(capi.fnv1a(MIGRATION)), C.byref(n)))
+        return n.value
+
+    def bin(self) -> int:
+        g = C.c_uint32()
+        self.world._check(self.b.fn("boids_band_bin")(self.h, C.byref(g)))
+        return g.value
+
+    def step(self):
+        self.world._check(self.b.fn("boids_band_step")(self.h))
+
+    def state(self):
+        """(ids, positions, velocities) of the boids this shard holds now, in table row order."""
+        snap = self.world.snapshot()
+        P, V, I = (capi.fnv1a(x) for x in (worlds.cname("Position"), worlds.cname("Velocity"), BOID_ID))
+        arch = [a for a in snap["archetypes"] if len(a["types"]) == 3]
+        if not arch or arch[0]["entities"].size == 0:
+            return np.zeros(0, np.uint32), np.zeros(0, np.float32), np.zeros(0, np.float32)
+        a = arch[0]
+        return a["columns"][I].view(np.uint32).copy(), a["columns"][P].view(np.float32).copy(), a["columns"][V].view(np.float32).copy()
+
+    def close(self):
+        if self.h:
+            self.b.fn("boids_destroy")(self.h)
+            self.h = C.c_void_p()
+        self.world.close()
+
+
+def gather_band_state(states, n_total):
+    """[(ids, pos, vel)] of all shards -> global (positions, velocities) in boid-id order; every id exactly once."""
+    ids = np.concatenate([s[0] for s in states])
+    assert ids.size == n_total and np.array_equal(np.sort(ids), np.arange(n_total, dtype=np.uint32)), "boids lost or duplicated"
+    order = np.argsort(ids, kind="stable")
+    pos = np.concatenate([s[1].reshape(-1, 2) for s in states])[order].reshape(-1)
+    vel = np.concatenate([s[2].reshape(-1, 2) for s in states])[order].reshape(-1)
+    return pos, vel
+
+
+class BandExchange:
+    """One rank of a multi-process run.  Migration goes through routing.route (split -> all_to_all -> merge); the halos are
+    either read in place from the neighbours' export buffers (CUDA IPC, `peer=True`: NVLink loads inside the assemble kernel,
+    one 4-byte all-reduce as the barrier) or shipped with one all_gather of the export buffers (gloo / CPU tests)."""
+
+    def __init__(self, shard: BandShard, torch, dist, device, peer: bool):
+        self.s, self.torch, self.dist, self.device, self.peer = shard, torch, dist, device, peer
+        self.opened = []
+        self.migrated = []  # (leavers, arrivals) of this rank per step
+        g, G = shard.shard, shard.n_shards
+        if G == 1:
+            return
+        if peer:
+            w, b = shard.world, shard.b
+            mine = torch.zeros(4 * IPC_HANDLE_BYTES, dtype=torch.uint8)
+            for gen in range(2):
+                for side in range(2):
+                    h = (C.c_uint8 * IPC_HANDLE_BYTES)()
+                    w._check(b.fn("ipc_export")(w.h, C.c_void_p(shard.export_ptr(gen, side)), h))
+                    off = (gen * 2 + side) * IPC_HANDLE_BYTES
+                    mine[off:off + IPC_HANDLE_BYTES] = torch.frombuffer(bytearray(h), dtype=torch.uint8)
+            everyone = torch.empty(G * mine.numel(), dtype=torch.uint8, device=device)
+            dist.all_gather_into_tensor(everyone, mine.to(device))
+            everyone = everyone.cpu().numpy().reshape(G, 2, 2, IPC_HANDLE_BYTES)
+            for nb, my_side, their_side in ((g - 1, 0, 1), (g + 1, 1, 0)):  # lower halo = lower neighbour's LAST row
+                if nb < 0 or nb >= G:
+                    continue
+                for gen in range(2):
+                    h = (C.c_uint8 * IPC_HANDLE_BYTES).from_buffer_copy(everyone[nb, gen, their_side].tobytes())
+                    p = C.c_void_p()
+                    w._check(b.fn("ipc_open")(w.h, h, C.byref(p)))
+                    self.opened.append(p.value)
+                    shard.set_halo(gen, my_side, p.value)
+            self.token = torch.zeros(1, dtype=torch.int32, device=device)
+        else:
+            self.recv = torch.empty(G * 2 * shard.export_bytes, dtype=torch.uint8, device=device)
+            self.send = torch.empty(2 * shard.export_bytes, dtype=torch.uint8, device=device)
+
+    def step(self):
+        from . import routing
+        s, G, g = self.s, self.s.n_shards, self.s.shard
+        if G > 1:
+            out = s.leavers()
+            routing.route(s.world, MIGRATION, self.torch, self.device, self.dist, g, G, s.rows_per, 0, 1, False)
+            self.migrated.append((out, s.arrivals()))
+        gen = s.bin()
+        if G > 1:
+            if self.peer:
+                self.dist.all_reduce(self.token)  # every shard's exports of this generation are complete
+            else:
+                eb = s.export_bytes
+                for side in range(2):
+                    src = (C.c_uint8 * eb).from_address(s.export_ptr(gen, side))
+                    self.send[side * eb:(side + 1) * eb] = self.torch.frombuffer(src, dtype=self.torch.uint8)
+                self.dist.all_gather_into_tensor(self.recv, self.send)
+                if g > 0:
+                    s.set_halo(gen, 0, self.recv[((g - 1) * 2 + 1) * eb:].data_ptr())
+                if g + 1 < G:
+                    s.set_halo(gen, 1, self.recv[((g + 1) * 2 + 0) * eb:].data_ptr())
+        s.step()
+
+    def close(self):
+        if self.opened:
+            w = self.s.world
+            w.synchronize()
+            self.dist.barrier()
+            for p in self.opened:
+                self.s.b.fn("ipc_close")(w.h, C.c_void_p(p))
+            self.opened = []
+
+
+def emulate_bands(backend: capi.Backend, torch, device, n_total: int, world_size: int, n_shards: int, steps: int,
+                  params: dict | None = None, vel_scale: float = 1.0):
+    """All bands in ONE process (tests): ranks emulated as sequential calls; halos are the other shards' export buffers, the
+    migration exchange is the numpy statement of the router.  Returns (positions, velocities, migrations per step)."""
+    from . import routing
+    shards = [BandShard(backend, n_total, world_size, n_shards, g, params=params, vel_scale=vel_scale) for g in range(n_shards)]
+    for s in shards:
+        for gen in range(2):
+            if s.shard > 0:
+                s.set_halo(gen, 0, shards[s.shard - 1].export_ptr(gen, 1))
+            if s.shard + 1 < n_shards:
+                s.set_halo(gen, 1, shards[s.shard + 1].export_ptr(gen, 0))
+    moved = []
+    for _ in range(steps):
+        if n_shards > 1:
+            out = [s.leavers() for s in shards]
+            queues = [s.world.message_read(MIGRATION, 1) for s in shards]
+            want = routing.reference_routing(queues, MIGRATION_DTYPE.itemsize, 0, shards[0].rows_per)
+            for s, q in zip(shards, want):
+                # reference_routing re-bases keys; the migration exchange does not (the key is a grid row, not an entity)
+                k = q.reshape(-1, 32)[:, 0:4].copy().view("<u4").reshape(-1) + np.uint32(s.shard * s.rows_per)
+                q = q.copy()
+                q.reshape(-1, 32)[:, 0:4] = k.view(np.uint8).reshape(-1, 4)
+                t = torch.from_numpy(q).to(device)
+                if str(device) != "cpu":
+                    torch.cuda.synchronize()  # the copy ran on torch's stream, the merge reads on the world's
+                routing.merge(s.world, MIGRATION, 1, t, q.size // 32, 0, 0)
+                s.world.synchronize()         # `t` may be recycled by torch's allocator after this iteration
+            moved.append((sum(out), sum(s.arrivals() for s in shards)))
+        for s in shards:
+            s.bin()
+        for s in shards:
+            s.world.synchronize()  # the barrier
+        for s in shards:
+            s.step()
+        for s in shards:
+            s.world.synchronize()
+    states = [s.state() for s in shards]
+    for s in shards:
+        s.close()
+    pos, vel = gather_band_state(states, n_total)
+    return pos, vel, moved

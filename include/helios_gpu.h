@@ -820,6 +820,42 @@ HELIOS_GPU_API int32_t helios_gpu_boids_exchange_set_peer(helios_gpu_boids* b, u
 HELIOS_GPU_API int32_t helios_gpu_boids_exchange_bin(helios_gpu_boids* b);
 HELIOS_GPU_API int32_t helios_gpu_boids_exchange_step(helios_gpu_boids* b);
 
+/* Spatial bands: the halo-exchange form of the sharded boids (BASELINE.json north_star: "position allgather OR halo
+ * exchange").  Shard g owns the grid rows [g * R, min((g + 1) * R, dim)), R = ceil(dim / n_shards), and the boids whose
+ * cell lies in them; its world holds a {Position, Velocity, BoidId} table (BoidId: one u32, the boid's global id — entity
+ * ids are per world).  Per step, on every rank:
+ *     helios_gpu_boids_band_leavers(b, T, &n)   boids whose cell left the band -> one 32-byte helios_gpu_boid_migration
+ *                                               each in the CURRENT queue of message type T (key = Entity{new grid row, 1})
+ *     <route T with entities_per_shard = R, no re-base: helios_gpu_message_route_* or a helios_gpu_router>
+ *     helios_gpu_boids_band_arrivals(b, T, &n)  one ApplyDeferred batch: Destroy of the leavers, Spawn + Add{Position,
+ *                                               Velocity, BoidId} of the arrivals (the queue is consumed)
+ *     helios_gpu_boids_band_bin(b, &gen)        own boids -> cell order; the first and last own grid rows (boids + row
+ *                                               table) are copied into this shard's two EXPORT buffers of generation gen
+ *     <barrier; the neighbours' exports are read in place (peer memory) or shipped by the caller>
+ *     helios_gpu_boids_band_step(b)             halo rows from the neighbours' exports, neighbour pass, integrate
+ * Per neighbour and step one grid row moves (~dim * density * 16 B) instead of the whole flock.  The fixed-point sums make
+ * the result per boid id independent of the shard count, of the row order and of the arrival order. */
+typedef struct helios_gpu_boid_migration {
+  helios_gpu_entity_t key; /* Entity{index = the grid row the boid is in now, generation 1}: the router's key */
+  uint32_t id, pad;
+  float x, y, dx, dy;
+} helios_gpu_boid_migration;
+HELIOS_GPU_API int32_t helios_gpu_boids_band_create(helios_gpu_world* w, uint64_t position_hash, uint64_t velocity_hash,
+                                                    uint64_t id_hash, const helios_gpu_boids_params* params,
+                                                    uint32_t n_shards, uint32_t my_shard, helios_gpu_boids** out);
+/* rows_per_shard = R above; export_bytes = size of one export buffer. */
+HELIOS_GPU_API int32_t helios_gpu_boids_band_info(helios_gpu_boids* b, uint64_t* n_local, uint32_t* rows_per_shard,
+                                                  uint32_t* row_lo, uint32_t* row_hi, uint64_t* export_bytes);
+/* This shard's export buffer: side 0 = its FIRST own grid row (the lower neighbour's upper halo), 1 = its LAST own row. */
+HELIOS_GPU_API int32_t helios_gpu_boids_band_export(helios_gpu_boids* b, uint32_t generation, uint32_t side, void** ptr);
+/* Where band_step reads a halo from: side 0 = the row below the band (the lower neighbour's side-1 export), side 1 = the
+ * row above (the upper neighbour's side-0 export).  Peer memory of another GPU or a local copy; NULL = no neighbour. */
+HELIOS_GPU_API int32_t helios_gpu_boids_band_set_halo(helios_gpu_boids* b, uint32_t generation, uint32_t side, const void* ptr);
+HELIOS_GPU_API int32_t helios_gpu_boids_band_leavers(helios_gpu_boids* b, uint64_t migration_type_hash, uint64_t* n_out);
+HELIOS_GPU_API int32_t helios_gpu_boids_band_arrivals(helios_gpu_boids* b, uint64_t migration_type_hash, uint64_t* n_in);
+HELIOS_GPU_API int32_t helios_gpu_boids_band_bin(helios_gpu_boids* b, uint32_t* generation);
+HELIOS_GPU_API int32_t helios_gpu_boids_band_step(helios_gpu_boids* b);
+
 /* CUDA IPC plumbing for the peer pointers (one process per GPU): export a device allocation of this process as a 64-byte
  * handle, open a handle received from another process (peer access is enabled on first use), close it again. */
 #define HELIOS_GPU_IPC_HANDLE_BYTES 64

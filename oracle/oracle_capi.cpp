@@ -1287,6 +1287,8 @@ HO_API uint32_t helios_oracle_hardware_threads() { return std::thread::hardware_
 // =====================================================================================================
 namespace {
 
+struct Boid4Raw { float x, y, dx, dy; };
+
 struct OBoids {
   OWorld* w;
   helios_gpu_boids_params p;
@@ -1296,6 +1298,15 @@ struct OBoids {
   uint64_t n_cells = 0;
   std::vector<uint32_t> orig;        // slab position -> table row (of the last bin)
   std::vector<uint8_t> own_slab, own_counts;
+  // spatial bands (include/helios_gpu.h "Spatial bands")
+  bool band = false;
+  uint64_t pos_hash = 0, vel_hash = 0, id_hash = 0;
+  uint32_t n_shards = 1, me = 0, rows_per = 0, row_lo = 0, row_hi = 0, halo_cap = 0, gen = 0;
+  std::vector<uint8_t> exports[2][2];            // [generation][side]
+  const void* halo_src[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+  std::vector<Boid4Raw> own;                      // own boids in cell order (of the last band_bin)
+  std::vector<uint32_t> own_table;                // (own rows + 2) * dim + 1 entries, own-relative
+  std::vector<ho::Entity> leavers;
 };
 
 inline uint32_t o_cell_of(float x, float y, uint32_t dim) {
@@ -1451,6 +1462,256 @@ HO_API int32_t helios_oracle_boids_step(void* bp, const void* slabs_in, const vo
     for (int t = 0; t < T; ++t) pool.emplace_back(work, n * t / T, n * (t + 1) / T);
     for (auto& th : pool) th.join();
   }
+  return 0;
+}
+// ---- spatial bands: the plain statement (one pass per call, sequential, deterministic order) ---------------------------------
+namespace {
+constexpr uint32_t kOEdgeHeader = 16;
+inline uint64_t o_edge_boids_offset(uint32_t dim) { return (kOEdgeHeader + uint64_t(dim + 1) * 4 + 15) / 16 * 16; }
+inline ho::Archetype* o_band_table(OBoids* b) {
+  for (ho::Archetype* a : b->w->world.components.Archetypes())
+    if (a->Id().Types().size() == 3 && a->HasColumn(b->pos_hash) && a->HasColumn(b->vel_hash) && a->HasColumn(b->id_hash)) return a;
+  return nullptr;
+}
+}  // namespace
+HO_API int32_t helios_oracle_boids_band_create(void* wp, uint64_t pos_hash, uint64_t vel_hash, uint64_t id_hash,
+                                               const helios_gpu_boids_params* p, uint32_t n_shards, uint32_t me, void** out) {
+  if (n_shards == 0 || me >= n_shards) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  if (!(p->world_size >= 1.0f) || p->world_size > 16384.0f || p->world_size != float(uint32_t(p->world_size)))
+    return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  auto* b = new OBoids();
+  b->w = W(wp);
+  b->p = *p;
+  b->band = true;
+  b->pos_hash = pos_hash; b->vel_hash = vel_hash; b->id_hash = id_hash;
+  b->dim = uint32_t(p->world_size);
+  b->n_cells = uint64_t(b->dim) * b->dim;
+  b->n_shards = n_shards;
+  b->me = me;
+  b->rows_per = (b->dim + n_shards - 1) / n_shards;
+  if (uint64_t(b->rows_per) * (n_shards - 1) >= b->dim) { delete b; return HELIOS_GPU_ERR_INVALID_ARGUMENT; }
+  b->row_lo = me * b->rows_per;
+  b->row_hi = std::min(b->dim, (me + 1) * b->rows_per);
+  b->halo_cap = std::max<uint32_t>(b->dim * 64u, 65536u);
+  for (auto& g : b->exports)
+    for (auto& e : g) e.assign(o_edge_boids_offset(b->dim) + uint64_t(b->halo_cap) * 16, 0);
+  *out = b;
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_band_info(void* bp, uint64_t* n_local, uint32_t* rows_per, uint32_t* row_lo, uint32_t* row_hi,
+                                             uint64_t* export_bytes) {
+  auto* b = static_cast<OBoids*>(bp);
+  ho::Archetype* t = o_band_table(b);
+  if (n_local) *n_local = t ? t->EntityCount() : 0;
+  if (rows_per) *rows_per = b->rows_per;
+  if (row_lo) *row_lo = b->row_lo;
+  if (row_hi) *row_hi = b->row_hi;
+  if (export_bytes) *export_bytes = b->exports[0][0].size();
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_band_export(void* bp, uint32_t gen, uint32_t side, void** ptr) {
+  auto* b = static_cast<OBoids*>(bp);
+  if (gen > 1 || side > 1) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  *ptr = b->exports[gen][side].data();
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_band_set_halo(void* bp, uint32_t gen, uint32_t side, const void* ptr) {
+  auto* b = static_cast<OBoids*>(bp);
+  if (gen > 1 || side > 1) return HELIOS_GPU_ERR_INVALID_ARGUMENT;
+  b->halo_src[gen][side] = ptr;
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_band_leavers(void* bp, uint64_t type_hash, uint64_t* n_out) {
+  auto* b = static_cast<OBoids*>(bp);
+  b->leavers.clear();
+  if (n_out) *n_out = 0;
+  if (b->n_shards == 1) return 0;
+  auto& msgs = b->w->world.messages;
+  if (!msgs.IsRegistered(type_hash) || msgs.ElemSize(type_hash) != sizeof(helios_gpu_boid_migration)) return HELIOS_GPU_ERR_NOT_FOUND;
+  std::vector<helios_gpu_boid_migration> recs;
+  if (ho::Archetype* t = o_band_table(b)) {
+    const auto* pos = reinterpret_cast<const float*>(t->ColumnBytes(t->ColumnIndex(b->pos_hash)).data());
+    const auto* vel = reinterpret_cast<const float*>(t->ColumnBytes(t->ColumnIndex(b->vel_hash)).data());
+    const auto* id = reinterpret_cast<const uint32_t*>(t->ColumnBytes(t->ColumnIndex(b->id_hash)).data());
+    for (size_t i = 0; i < t->EntityCount(); ++i) {
+      const uint32_t cy = o_cell_of(pos[2 * i], pos[2 * i + 1], b->dim) / b->dim;
+      if (cy >= b->row_lo && cy < b->row_hi) continue;
+      recs.push_back(helios_gpu_boid_migration{(uint64_t(1) << 32) | cy, id[i], 0, pos[2 * i], pos[2 * i + 1], vel[2 * i], vel[2 * i + 1]});
+      b->leavers.push_back(t->Entities()[i]);
+    }
+  }
+  msgs.ReplaceQueue(true, type_hash, recs.data(), recs.size());
+  if (n_out) *n_out = recs.size();
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_band_arrivals(void* bp, uint64_t type_hash, uint64_t* n_in) {
+  auto* b = static_cast<OBoids*>(bp);
+  if (n_in) *n_in = 0;
+  if (b->n_shards == 1) return 0;
+  auto& world = b->w->world;
+  if (!world.messages.IsRegistered(type_hash)) return HELIOS_GPU_ERR_NOT_FOUND;
+  std::vector<uint8_t> bytes;
+  if (const auto* q = world.messages.Current().Bytes(type_hash)) bytes = *q;
+  const size_t n = bytes.size() / sizeof(helios_gpu_boid_migration);
+  if (n_in) *n_in = n;
+  for (const ho::Entity e : b->leavers) world.command_queue.Enqueue(ho::Command{ho::CmdKind::kDestroy, e, {}, {}});
+  b->leavers.clear();
+  for (size_t k = 0; k < n; ++k) {  // Commands::Spawn().AddComponents(Position, Velocity, BoidId)
+    helios_gpu_boid_migration r;
+    std::memcpy(&r, bytes.data() + k * sizeof(r), sizeof(r));
+    ho::Command c;
+    c.kind = ho::CmdKind::kAdd;
+    c.entity = world.ReserveEntity();
+    const float pv[2] = {r.x, r.y}, vv[2] = {r.dx, r.dy};
+    const auto raw = [](const void* p, size_t nb) { return std::vector<uint8_t>(static_cast<const uint8_t*>(p), static_cast<const uint8_t*>(p) + nb); };
+    c.types = {b->pos_hash, b->vel_hash, b->id_hash};
+    c.values = {raw(pv, 8), raw(vv, 8), raw(&r.id, 4)};
+    world.command_queue.Enqueue(std::move(c));
+  }
+  world.messages.ReplaceQueue(true, type_hash, nullptr, 0);
+  world.Flush();
+  b->w->faithful.reset();
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_band_bin(void* bp, uint32_t* generation) {
+  auto* b = static_cast<OBoids*>(bp);
+  ho::Archetype* t = o_band_table(b);
+  const size_t n = t ? t->EntityCount() : 0;
+  const uint32_t dim = b->dim, rows_own = b->row_hi - b->row_lo;
+  const uint64_t cells = uint64_t(rows_own + 2) * dim;
+  std::vector<uint32_t> count(cells, 0);
+  b->own_table.assign(cells + 1, 0);
+  const float* pos = n ? reinterpret_cast<const float*>(t->ColumnBytes(t->ColumnIndex(b->pos_hash)).data()) : nullptr;
+  const float* vel = n ? reinterpret_cast<const float*>(t->ColumnBytes(t->ColumnIndex(b->vel_hash)).data()) : nullptr;
+  const auto band_cell = [&](size_t i, uint64_t* c) {
+    const uint32_t g = o_cell_of(pos[2 * i], pos[2 * i + 1], dim);
+    const uint32_t cy = g / dim;
+    if (cy < b->row_lo || cy >= b->row_hi) return false;
+    *c = uint64_t(cy - b->row_lo + 1) * dim + g % dim;
+    return true;
+  };
+  for (size_t i = 0; i < n; ++i) {
+    uint64_t c;
+    if (!band_cell(i, &c)) return HELIOS_GPU_ERR_STATE;  // migrate before binning
+    ++count[c];
+  }
+  for (uint64_t c = 0; c < cells; ++c) b->own_table[c + 1] = b->own_table[c] + count[c];
+  b->own.assign(n, Boid4Raw{});
+  b->orig.assign(n, 0);
+  std::vector<uint32_t> cursor(b->own_table.begin(), b->own_table.end() - 1);
+  for (size_t i = 0; i < n; ++i) {
+    uint64_t c = 0;
+    band_cell(i, &c);
+    const uint32_t slot = cursor[c]++;
+    b->own[slot] = Boid4Raw{pos[2 * i], pos[2 * i + 1], std::fmin(std::fmax(vel[2 * i], -4.0f), 4.0f),
+                            std::fmin(std::fmax(vel[2 * i + 1], -4.0f), 4.0f)};
+    b->orig[slot] = uint32_t(i);
+  }
+  for (uint32_t side = 0; side < 2; ++side) {  // edge rows -> exports
+    auto& e = b->exports[b->gen][side];
+    const uint32_t row = side ? rows_own : 1u;
+    const uint32_t start = b->own_table[uint64_t(row) * dim], end = b->own_table[uint64_t(row + 1) * dim];
+    if (end - start > b->halo_cap) return HELIOS_GPU_ERR_CAPACITY;
+    const uint32_t cnt = end - start;
+    std::memcpy(e.data(), &cnt, 4);
+    auto* table = reinterpret_cast<uint32_t*>(e.data() + kOEdgeHeader);
+    for (uint32_t x = 0; x <= dim; ++x) table[x] = b->own_table[uint64_t(row) * dim + x] - start;
+    if (cnt) std::memcpy(e.data() + o_edge_boids_offset(dim), b->own.data() + start, size_t(cnt) * 16);
+  }
+  if (generation) *generation = b->gen;
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_band_step(void* bp) {
+  auto* b = static_cast<OBoids*>(bp);
+  ho::Archetype* t = o_band_table(b);
+  const size_t n = t ? t->EntityCount() : 0;
+  if (n != b->own.size()) return HELIOS_GPU_ERR_STATE;
+  const int dim = int(b->dim);
+  const uint32_t rows_own = b->row_hi - b->row_lo;
+  const auto* lower = b->me > 0 ? static_cast<const uint8_t*>(b->halo_src[b->gen][0]) : nullptr;
+  const auto* upper = b->me + 1 < b->n_shards ? static_cast<const uint8_t*>(b->halo_src[b->gen][1]) : nullptr;
+  if ((b->me > 0 && !lower) || (b->me + 1 < b->n_shards && !upper)) return HELIOS_GPU_ERR_STATE;
+  // candidates of cell (table row r, column x): the lower export for r = 0, the own slab, the upper export for r = rows_own + 1
+  const auto cell_range = [&](uint32_t r, uint32_t x, const Boid4Raw** first, uint32_t* cnt) {
+    const uint8_t* e = r == 0 ? lower : (r == rows_own + 1 ? upper : nullptr);
+    if (r >= 1 && r <= rows_own) {
+      const uint32_t s = b->own_table[uint64_t(r) * b->dim + x];
+      *first = b->own.data() + s;
+      *cnt = b->own_table[uint64_t(r) * b->dim + x + 1] - s;
+    } else if (e) {
+      const auto* table = reinterpret_cast<const uint32_t*>(e + kOEdgeHeader);
+      *first = reinterpret_cast<const Boid4Raw*>(e + o_edge_boids_offset(b->dim)) + table[x];
+      *cnt = table[x + 1] - table[x];
+    } else {
+      *first = nullptr;
+      *cnt = 0;
+    }
+  };
+  auto* pos = n ? reinterpret_cast<float*>(t->ColumnBytes(t->ColumnIndex(b->pos_hash)).data()) : nullptr;
+  auto* vel = n ? reinterpret_cast<float*>(t->ColumnBytes(t->ColumnIndex(b->vel_hash)).data()) : nullptr;
+  const helios_gpu_boids_params P = b->p;
+  const float kEps = 0.01f, kQCoh = 1048576.0f, kQAli = 1048576.0f, kQSep = 65536.0f;
+  for (size_t j = 0; j < n; ++j) {
+    const Boid4Raw me = b->own[j];
+    int cx = int(me.x), cy = int(me.y);
+    cx = cx < 0 ? 0 : (cx >= dim ? dim - 1 : cx);
+    cy = cy < 0 ? 0 : (cy >= dim ? dim - 1 : cy);
+    long long coh_x = 0, coh_y = 0, ali_x = 0, ali_y = 0, sep_x = 0, sep_y = 0;
+    uint32_t count = 0;
+    for (int y = cy - 1; y <= cy + 1; ++y) {
+      if (y < 0 || y >= dim) continue;
+      for (int x = cx - 1; x <= cx + 1; ++x) {
+        if (x < 0 || x >= dim) continue;
+        const Boid4Raw* first;
+        uint32_t cnt;
+        cell_range(uint32_t(y - int(b->row_lo) + 1), uint32_t(x), &first, &cnt);
+        for (uint32_t k = 0; k < cnt; ++k) {
+          if (first + k == b->own.data() + j) continue;
+          const Boid4Raw o = first[k];
+          const float dx = o.x - me.x, dy = o.y - me.y;
+          const float d2 = dx * dx + dy * dy;
+          if (d2 < 1.0f) {
+            ++count;
+            coh_x += llrintf(dx * kQCoh);
+            coh_y += llrintf(dy * kQCoh);
+            ali_x += llrintf(o.dx * kQAli);
+            ali_y += llrintf(o.dy * kQAli);
+            const float inv = 1.0f / (d2 + kEps);
+            sep_x += llrintf((-dx * inv) * kQSep);
+            sep_y += llrintf((-dy * inv) * kQSep);
+          }
+        }
+      }
+    }
+    float vx = me.dx, vy = me.dy;
+    if (count) {
+      const float nn = float(count);
+      const float cohx = (float(coh_x) / kQCoh) / nn, cohy = (float(coh_y) / kQCoh) / nn;
+      const float alix = (float(ali_x) / kQAli) / nn - vx, aliy = (float(ali_y) / kQAli) / nn - vy;
+      const float sepx = float(sep_x) / kQSep, sepy = float(sep_y) / kQSep;
+      const float ax = P.w_cohesion * cohx + P.w_alignment * alix + P.w_separation * sepx;
+      const float ay = P.w_cohesion * cohy + P.w_alignment * aliy + P.w_separation * sepy;
+      vx = vx + ax * P.dt;
+      vy = vy + ay * P.dt;
+    }
+    const float s2 = vx * vx + vy * vy;
+    if (s2 > P.max_speed * P.max_speed) {
+      const float sc = P.max_speed / std::sqrt(s2);
+      vx = vx * sc;
+      vy = vy * sc;
+    }
+    float px = me.x + vx * P.dt, py = me.y + vy * P.dt;
+    const float hi = P.world_size - 0.00390625f;
+    px = px < 0.0f ? 0.0f : (px > hi ? hi : px);
+    py = py < 0.0f ? 0.0f : (py > hi ? hi : py);
+    const uint32_t row = b->orig[j];
+    pos[2 * row] = px;
+    pos[2 * row + 1] = py;
+    vel[2 * row] = vx;
+    vel[2 * row + 1] = vy;
+  }
+  b->gen ^= 1u;
+  b->own.clear();
   return 0;
 }
 HO_API int32_t helios_oracle_boids_step_local(void* bp) {
