@@ -46,6 +46,9 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--all-tables", action="store_true", help="drop the With/Without filters (cfg 2-all)")
     ap.add_argument("--no-secondary", action="store_true", help="headline line only (skip the cfg2-all / cfg3 / cfg4 / cfg5 / routing legs)")
+    ap.add_argument("--boids", default="bands", choices=["bands", "idrange"],
+                    help="cfg5 ownership: spatial bands with a one-row halo exchange (default), or entity-id ranges with a "
+                         "whole-flock exchange (the A/B: --exchange p2p = peer-memory merge, nccl = all-gather)")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="cfg5 / routing at N>1: peer-memory exchange fused into the kernels (default) or NCCL collectives")
     return ap.parse_args()

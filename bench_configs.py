@@ -722,6 +722,8 @@ def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
     """Boids, STRONG scaling: `--entities` boids in total (default 64M, density 4 per cell) split by entity-id range over
     the ranks; per step: bin own shard, all-gather slabs + counts (NCCL), neighbour pass + integrate."""
     from heliosengine_b200 import boids
+    if getattr(args, "boids", "bands") == "bands":
+        return run_cfg5_bands(args, torch, dev, stream, peak, dist, rank, world_size)
     n_total = args.entities or (1 << 26)
     ws = int(round((n_total / 4) ** 0.5))
     gpu = capi.load_gpu()
@@ -856,6 +858,148 @@ def run_cfg5(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
     }
     if peer:
         peer.close()
+    shard.close()
+    return line
+
+
+def run_cfg5_bands(args, torch, dev, stream, peak, dist=None, rank=0, world_size=1):
+    """Boids over spatial bands, STRONG scaling: `--entities` boids in total (default 64M, density 4 per cell).  Rank g owns
+    the grid rows [g * R, (g + 1) * R); per step: migrate the boids that left the band (router + Destroy / Spawn commands),
+    bin the own boids, publish the two edge rows, barrier, read ONE row from each neighbour in place over NVLink, neighbour
+    pass + integrate.  The initial placement is the entity-id range: the first step sorts the flock into bands and is timed
+    and reported apart (`first_step_ms`)."""
+    from heliosengine_b200 import boids, routing
+    n_total = args.entities or (1 << 26)
+    ws = int(round((n_total / 4) ** 0.5))
+    gpu = capi.load_gpu()
+    shard = boids.BandShard(gpu, n_total, ws, world_size, rank, device=dev.index)
+    shard.world.set_stream(stream.cuda_stream)
+    steps, warm = args.steps, max(3, args.warmup)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        x = boids.BandExchange(shard, torch, dist, dev, peer=world_size > 1)
+        barrier()
+        a, b = _events(torch, 1)[0]
+        a.record(stream)
+        x.step()  # the initial sort into bands: (G-1)/G of the flock migrates
+        b.record(stream)
+        barrier()
+        first_ms = a.elapsed_time(b)
+        first_moved = x.migrated[0] if x.migrated else (0, 0)
+        for _ in range(warm):
+            x.step()
+        barrier()
+        l0 = shard.world.launch_count()
+        evs = _events(torch, steps)
+        for a, b in evs:
+            a.record(stream)
+            x.step()
+            b.record(stream)
+        barrier()
+        launches = shard.world.launch_count() - l0
+        step_ms = [a.elapsed_time(b) for a, b in evs]
+        moved = x.migrated[-steps:] if x.migrated else []
+        # phase split (one extra step, not part of `value`)
+        ph = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+        ph[0].record(stream)
+        if world_size > 1:
+            shard.leavers()
+            routing.route(shard.world, boids.MIGRATION, torch, dev, dist, rank, world_size, shard.rows_per, 0, 1, False)
+            shard.arrivals()
+        ph[1].record(stream)
+        shard.bin()
+        ph[2].record(stream)
+        if world_size > 1:
+            dist.all_reduce(x.token)
+        ph[3].record(stream)
+        shard.step()
+        ph[4].record(stream)
+        barrier()
+        phases = [ph[i].elapsed_time(ph[i + 1]) for i in range(4)]
+        n_local = shard.n_local()
+
+        e2e = None
+        if not args.no_e2e:
+            P, V = worlds.cname("Position"), worlds.cname("Velocity")
+            snap = shard.world.snapshot(columns=False)
+            tbl = [i for i, a_ in enumerate(snap["archetypes"]) if len(a_["types"]) == 3][0]
+            _, p0, v0 = shard.state()
+            hp, hv = torch.from_numpy(p0).pin_memory(), torch.from_numpy(v0).pin_memory()
+            ho = torch.empty(n_local * 2, dtype=torch.float32).pin_memory()
+            e2e_steps = 3
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(e2e_steps):  # the same in-band state every step: the row count stays put
+                shard.world.column_write(tbl, P, 0, n_local, hp.data_ptr())
+                shard.world.column_write(tbl, V, 0, n_local, hv.data_ptr())
+                x.step()
+                shard.world.column_read(tbl, P, 0, n_local, ho.data_ptr())
+                shard.world.synchronize()
+            barrier()
+            e2e = (time.perf_counter() - t0) / e2e_steps
+
+    tm = torch.tensor([sum(step_ms), e2e or 0.0, first_ms] + phases, dtype=torch.float64, device=dev)
+    cnt = torch.tensor([n_local, first_moved[0], sum(m[0] for m in moved)], dtype=torch.float64, device=dev)
+    nmax = torch.tensor([float(n_local)], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        dist.all_reduce(nmax, op=dist.ReduceOp.MAX)
+    tot_ms, e2e_s, first_ms, mig_ms, bin_ms, bar_ms, nb_ms = (float(v) for v in tm.tolist())
+    assert int(cnt[0]) == n_total, "boids lost or duplicated by the migration"
+    ms = tot_ms / steps
+    local_bytes = 64 * float(nmax[0])  # SURVEY §8d: compulsory HBM bytes per boid per step on the owning GPU (largest band)
+    achieved = local_bytes / (ms * 1e-3) / 1e9
+    halo_bytes = 2 * (4 * ws * 16 + (ws + 1) * 4 + 16) if world_size > 1 else 0
+
+    cpu = None
+    if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
+        o = capi.load_oracle()
+        sample_n, sample_ws = 1 << 20, 512
+        so = boids.BoidsShard(o, sample_n, sample_ws)
+        nthreads = int(o.fn("hardware_threads", ctypes.c_uint32)())
+        o.fn("set_access_mode")(so.world.h, 0, nthreads)
+        so.step_local()
+        t0 = time.perf_counter()
+        for _ in range(2):
+            so.step_local()
+        dt = (time.perf_counter() - t0) / 2
+        so.close()
+        cpu = {"value": sample_n / dt, "unit": "boid updates/s", "cores": nthreads, "kind": "port",
+               "sample": f"{sample_n} boids in a {sample_ws}^2 world (same density, 4 per cell), 2 steps; binning single-threaded, "
+                         f"neighbour pass on {nthreads} threads; no reference implementation exists for this config"}
+    line = {
+        "metric": "boid_updates_per_sec", "value": n_total / (ms * 1e-3), "unit": "boid updates/s", "ms_per_step": ms,
+        "dtype": "f32 pair terms, int64 fixed-point sums", "scaling": "strong",
+        "config": {"workload": f"cfg5: {n_total} boids, world {ws}^2, cell = radius = 1 (density 4/cell), 3x3 stencil, "
+                               f"spatial bands x{world_size} ({shard.rows_per} grid rows each), one-row halo exchange",
+                   "parallelism": (f"{world_size} band(s); per step each rank reads its two neighbours' edge rows in place over NVLink "
+                                   f"(~{halo_bytes} B), band-crossing boids migrate through the message router (NCCL all-to-all of "
+                                   "32-byte records) and Destroy / Spawn commands; one 4-byte NCCL all-reduce as the barrier"
+                                   if world_size > 1 else "1 band = the whole grid (no exchange, no migration)"),
+                   "l2": "per-step working set (slab + tables) exceeds L2; no flush",
+                   "parity": "per boid id bit-exact vs the single-world CPU statement at test sizes, any band count "
+                             "(tests/test_boids_bands.py); no reference implementation (unpinned)"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak[0], "unit": "GB/s", "frac": achieved / peak[0],
+                     "traffic": None, "peak_kind": peak[1], "algorithmic_bytes_per_launch": local_bytes,
+                     "kernel": "bin (count/scan/scatter) + k_boids_neighbours on the largest band; exchange excluded from the bytes",
+                     "exchange_bytes_per_rank": halo_bytes},
+        "phases_ms": {"migrate": mig_ms, "bin": bin_ms, "barrier": bar_ms, "neighbour": nb_ms},
+        "first_step_ms": first_ms, "first_step_migrated": int(cnt[1]), "migrated_per_step": float(cnt[2]) / max(1, steps),
+        "largest_band": int(nmax[0]), "step_ms_rank0": step_ms,
+        "e2e": ({"value": n_total / e2e_s, "unit": "boid updates/s", "h2d_bytes_per_step": int(nmax[0]) * 16,
+                 "d2h_bytes_per_step": int(nmax[0]) * 8,
+                 "note": "per rank and step: Position+Velocity columns from pinned host memory, step, Position back"}
+                if e2e_s else None),
+        "cpu_baseline": cpu, "gpu_launches": int(launches),
+    }
+    x.close()
     shard.close()
     return line
 

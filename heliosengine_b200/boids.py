@@ -256,6 +256,7 @@ def emulate_shards(backend: capi.Backend, torch, device, n_total: int, world_siz
 # =====================================================================================================================
 BOID_ID = worlds.NS + "BoidId"
 MIGRATION = worlds.NS + "BoidMigration"
+LIGHT_MIGRATION_CAP = 4096  # leavers per rank and step that travel in the fixed-size all-gather
 MIGRATION_DTYPE = np.dtype([("key", "<u8"), ("id", "<u4"), ("pad", "<u4"), ("x", "<f4"), ("y", "<f4"), ("dx", "<f4"), ("dy", "<f4")])
 assert MIGRATION_DTYPE.itemsize == 32
 
@@ -312,6 +313,16 @@ class BandShard:
         self.world._check(self.b.fn("boids_band_arrivals")(self.h, C.c_uint64(capi.fnv1a(MIGRATION)), C.byref(n)))
         return n.value
 
+    def pack(self, dst_ptr: int, cap: int):
+        self.world._check(self.b.fn("boids_band_pack")(self.h, C.c_uint64(capi.fnv1a(MIGRATION)), C.c_void_p(dst_ptr), C.c_uint32(cap)))
+
+    def unpack(self, gathered_ptr: int, cap: int) -> bool:
+        """True: the queue now holds this shard's arrivals.  False: some rank overflowed `cap` — route the general way."""
+        ov = C.c_uint32()
+        self.world._check(self.b.fn("boids_band_unpack")(self.h, C.c_uint64(capi.fnv1a(MIGRATION)), C.c_void_p(gathered_ptr),
+                                                         C.c_uint32(self.n_shards), C.c_uint32(cap), C.byref(ov)))
+        return ov.value == 0
+
     def bin(self) -> int:
         g = C.c_uint32()
         self.world._check(self.b.fn("boids_band_bin")(self.h, C.byref(g)))
@@ -352,13 +363,16 @@ class BandExchange:
     either read in place from the neighbours' export buffers (CUDA IPC, `peer=True`: NVLink loads inside the assemble kernel,
     one 4-byte all-reduce as the barrier) or shipped with one all_gather of the export buffers (gloo / CPU tests)."""
 
-    def __init__(self, shard: BandShard, torch, dist, device, peer: bool):
-        self.s, self.torch, self.dist, self.device, self.peer = shard, torch, dist, device, peer
+    def __init__(self, shard: BandShard, torch, dist, device, peer: bool, light_cap: int = LIGHT_MIGRATION_CAP):
+        self.s, self.torch, self.dist, self.device, self.peer, self.cap = shard, torch, dist, device, peer, light_cap
         self.opened = []
         self.migrated = []  # (leavers, arrivals) of this rank per step
+        self.general_routes = 0
         g, G = shard.shard, shard.n_shards
         if G == 1:
             return
+        self.mig_send = torch.zeros(16 + light_cap * 32, dtype=torch.uint8, device=device)
+        self.mig_recv = torch.zeros(G * self.mig_send.numel(), dtype=torch.uint8, device=device)
         if peer:
             w, b = shard.world, shard.b
             mine = torch.zeros(4 * IPC_HANDLE_BYTES, dtype=torch.uint8)
@@ -390,7 +404,12 @@ class BandExchange:
         s, G, g = self.s, self.s.n_shards, self.s.shard
         if G > 1:
             out = s.leavers()
-            routing.route(s.world, MIGRATION, self.torch, self.device, self.dist, g, G, s.rows_per, 0, 1, False)
+            # light exchange: one fixed-size all-gather of everybody's (few) leavers; the general router when they do not fit
+            s.pack(self.mig_send.data_ptr(), self.cap)
+            self.dist.all_gather_into_tensor(self.mig_recv, self.mig_send)
+            if not s.unpack(self.mig_recv.data_ptr(), self.cap):
+                self.general_routes += 1
+                routing.route(s.world, MIGRATION, self.torch, self.device, self.dist, g, G, s.rows_per, 0, 1, False)
             self.migrated.append((out, s.arrivals()))
         gen = s.bin()
         if G > 1:

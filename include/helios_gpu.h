@@ -853,6 +853,14 @@ HELIOS_GPU_API int32_t helios_gpu_boids_band_export(helios_gpu_boids* b, uint32_
 HELIOS_GPU_API int32_t helios_gpu_boids_band_set_halo(helios_gpu_boids* b, uint32_t generation, uint32_t side, const void* ptr);
 HELIOS_GPU_API int32_t helios_gpu_boids_band_leavers(helios_gpu_boids* b, uint64_t migration_type_hash, uint64_t* n_out);
 HELIOS_GPU_API int32_t helios_gpu_boids_band_arrivals(helios_gpu_boids* b, uint64_t migration_type_hash, uint64_t* n_in);
+/* The light form of the routing step, for the steady state where a rank has a few hundred leavers: band_pack writes
+ * {u32 count, pad[3]} + the first cap_records records of the queue into dst (16 + cap_records * 32 bytes); the caller
+ * all-gathers those fixed-size buffers (one collective, no size exchange); band_unpack makes the queue what this shard
+ * receives (the records of the OTHER ranks whose grid row lies in its band).  *overflow != 0: some rank had more leavers
+ * than cap_records — nothing was changed, route the queue the general way instead (every rank sees the same flag). */
+HELIOS_GPU_API int32_t helios_gpu_boids_band_pack(helios_gpu_boids* b, uint64_t migration_type_hash, void* dst, uint32_t cap_records);
+HELIOS_GPU_API int32_t helios_gpu_boids_band_unpack(helios_gpu_boids* b, uint64_t migration_type_hash, const void* gathered,
+                                                    uint32_t n_ranks, uint32_t cap_records, uint32_t* overflow);
 HELIOS_GPU_API int32_t helios_gpu_boids_band_bin(helios_gpu_boids* b, uint32_t* generation);
 HELIOS_GPU_API int32_t helios_gpu_boids_band_step(helios_gpu_boids* b);
 

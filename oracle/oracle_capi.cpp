@@ -1573,6 +1573,43 @@ HO_API int32_t helios_oracle_boids_band_arrivals(void* bp, uint64_t type_hash, u
   b->w->faithful.reset();
   return 0;
 }
+HO_API int32_t helios_oracle_boids_band_pack(void* bp, uint64_t type_hash, void* dst, uint32_t cap) {
+  auto* b = static_cast<OBoids*>(bp);
+  std::vector<uint8_t> bytes;
+  if (const auto* q = b->w->world.messages.Current().Bytes(type_hash)) bytes = *q;
+  const uint32_t n = uint32_t(bytes.size() / sizeof(helios_gpu_boid_migration));
+  std::memset(dst, 0, 16);
+  std::memcpy(dst, &n, 4);
+  std::memcpy(static_cast<uint8_t*>(dst) + 16, bytes.data(), size_t(std::min(n, cap)) * sizeof(helios_gpu_boid_migration));
+  return 0;
+}
+HO_API int32_t helios_oracle_boids_band_unpack(void* bp, uint64_t type_hash, const void* gathered, uint32_t n_ranks, uint32_t cap,
+                                               uint32_t* overflow) {
+  auto* b = static_cast<OBoids*>(bp);
+  const size_t stride = 16 + size_t(cap) * sizeof(helios_gpu_boid_migration);
+  const auto* g = static_cast<const uint8_t*>(gathered);
+  *overflow = 0;
+  for (uint32_t r = 0; r < n_ranks; ++r) {
+    uint32_t n;
+    std::memcpy(&n, g + r * stride, 4);
+    if (n > cap) *overflow = 1;
+  }
+  if (*overflow) return 0;
+  std::vector<helios_gpu_boid_migration> mine;
+  for (uint32_t r = 0; r < n_ranks; ++r) {
+    if (r == b->me) continue;
+    uint32_t n;
+    std::memcpy(&n, g + r * stride, 4);
+    for (uint32_t k = 0; k < n; ++k) {
+      helios_gpu_boid_migration m;
+      std::memcpy(&m, g + r * stride + 16 + size_t(k) * sizeof(m), sizeof(m));
+      const uint32_t row = uint32_t(m.key);
+      if (row >= b->row_lo && row < b->row_hi) mine.push_back(m);
+    }
+  }
+  b->w->world.messages.ReplaceQueue(true, type_hash, mine.data(), mine.size());
+  return 0;
+}
 HO_API int32_t helios_oracle_boids_band_bin(void* bp, uint32_t* generation) {
   auto* b = static_cast<OBoids*>(bp);
   ho::Archetype* t = o_band_table(b);

@@ -80,9 +80,11 @@ def _worker(rank, world_size, port, kind, n, ws, steps, out_dir):
         shard = boids.BandShard(capi.load_oracle(), n, ws, world_size, rank)
         ctx = contextlib.nullcontext()
     with ctx:
-        x = boids.BandExchange(shard, torch, dist, dev, peer=(kind == "nccl"))
+        # a small cap: the initial sort into bands overflows the light exchange and takes the general router, later steps fit
+        x = boids.BandExchange(shard, torch, dist, dev, peer=(kind == "nccl"), light_cap=256)
         for _ in range(steps):
             x.step()
+        assert 1 <= x.general_routes < steps, x.general_routes
         ids, p, v = shard.state()
         x.close()
     np.save(os.path.join(out_dir, f"i{rank}.npy"), ids)
