@@ -155,7 +155,7 @@ class PeerExchange:
     world's stream) -> merge-reading-peers + neighbour pass.  No slab ever goes through a collective."""
 
     def __init__(self, shard: BoidsShard, torch, dist, device):
-        self.shard, self.dist = shard, dist
+        self.shard, self.dist, self.torch, self.device = shard, dist, torch, device
         b, w = shard.b, shard.world
         shard.exchange_create()
         mine = torch.zeros(4 * IPC_HANDLE_BYTES, dtype=torch.uint8)
@@ -186,6 +186,7 @@ class PeerExchange:
         self.bytes_pulled_per_step = (shard.n_shards - 1) * (shard.n_local * SLAB_BYTES + shard.n_cells + 4 * -(-shard.n_cells // 1024))
 
     def step(self):
+        self.shard.world.require_stream(self.torch, self.device)
         self.shard.exchange_bin()
         self.dist.all_reduce(self.token)  # device-side barrier: every shard's buffers of this generation are complete
         self.shard.exchange_step()
@@ -363,8 +364,12 @@ class BandExchange:
     either read in place from the neighbours' export buffers (CUDA IPC, `peer=True`: NVLink loads inside the assemble kernel,
     one 4-byte all-reduce as the barrier) or shipped with one all_gather of the export buffers (gloo / CPU tests)."""
 
-    def __init__(self, shard: BandShard, torch, dist, device, peer: bool, light_cap: int = LIGHT_MIGRATION_CAP):
+    def __init__(self, shard: BandShard, torch, dist, device, peer: bool, light_cap: int = LIGHT_MIGRATION_CAP,
+                 barrier: str = "flags"):
+        """barrier (peer only): "flags" = neighbours wait on each other's published step numbers on the device
+        (helios_gpu_boids_band_set_barrier), "nccl" = one 4-byte all-reduce per step."""
         self.s, self.torch, self.dist, self.device, self.peer, self.cap = shard, torch, dist, device, peer, light_cap
+        self.flags = peer and barrier == "flags" and shard.n_shards > 1
         self.opened = []
         self.migrated = []  # (leavers, arrivals) of this rank per step
         self.general_routes = 0
@@ -395,6 +400,9 @@ class BandExchange:
                     self.opened.append(p.value)
                     shard.set_halo(gen, my_side, p.value)
             self.token = torch.zeros(1, dtype=torch.int32, device=device)
+            if self.flags:
+                shard.world._check(shard.b.fn("boids_band_set_barrier")(shard.h, C.c_uint32(1)))
+                dist.barrier()  # every rank has opened its neighbours' buffers before anybody publishes into them
         else:
             self.recv = torch.empty(G * 2 * shard.export_bytes, dtype=torch.uint8, device=device)
             self.send = torch.empty(2 * shard.export_bytes, dtype=torch.uint8, device=device)
@@ -402,6 +410,8 @@ class BandExchange:
     def step(self):
         from . import routing
         s, G, g = self.s, self.s.n_shards, self.s.shard
+        if G > 1 and self.peer:
+            s.world.require_stream(self.torch, self.device)  # collectives and kernels are ordered by ONE stream
         if G > 1:
             out = s.leavers()
             # light exchange: one fixed-size all-gather of everybody's (few) leavers; the general router when they do not fit
@@ -413,7 +423,9 @@ class BandExchange:
             self.migrated.append((out, s.arrivals()))
         gen = s.bin()
         if G > 1:
-            if self.peer:
+            if self.peer and self.flags:
+                pass  # band_step waits for the neighbours' published step on the device
+            elif self.peer:
                 self.dist.all_reduce(self.token)  # every shard's exports of this generation are complete
             else:
                 eb = s.export_bytes

@@ -217,6 +217,16 @@ class World:
 
     def set_stream(self, cuda_stream: int):
         self._check(self.b.fn("world_set_stream")(self.h, C.c_void_p(cuda_stream)))
+        self.stream_ptr = cuda_stream
+
+    def require_stream(self, torch, device):
+        """Collectives issued through torch run on torch's CURRENT stream; the library's kernels run on the world's.  Code that
+        orders one against the other by stream order (the 4-byte all-reduce barriers of the peer-memory exchanges) is only
+        correct when the two are the same stream: bind with set_stream(torch.cuda.current_stream(device).cuda_stream)."""
+        cur = torch.cuda.current_stream(device).cuda_stream
+        if getattr(self, "stream_ptr", None) != cur:
+            raise HeliosError(ERR_STATE, "the world's stream is not torch's current stream: call world.set_stream("
+                                         "torch.cuda.current_stream(device).cuda_stream) inside the same torch.cuda.stream(...) block")
 
     def synchronize(self):
         if self.b.is_gpu:

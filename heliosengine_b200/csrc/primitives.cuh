@@ -48,7 +48,7 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* total)
 
 // Pass 1: per-tile exclusive scan written in place to `out`, tile totals to partials[tile].
 // 8 consecutive u32 of one thread: two 128-bit accesses when the tile is whole and the pointer 16-byte aligned.
-__device__ __forceinline__ void scan_load8(const uint32_t* __restrict__ p, uint64_t base, uint64_t n, bool vec, uint32_t (&v)[kScanItems]) {
+__device__ __forceinline__ void scan_load8(const uint32_t* p, uint64_t base, uint64_t n, bool vec, uint32_t (&v)[kScanItems]) {
   if (vec && base + kScanItems <= n) {
     const uint4 a = *reinterpret_cast<const uint4*>(p + base), b = *reinterpret_cast<const uint4*>(p + base + 4);
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
@@ -57,7 +57,7 @@ __device__ __forceinline__ void scan_load8(const uint32_t* __restrict__ p, uint6
     for (int i = 0; i < kScanItems; ++i) v[i] = base + i < n ? p[base + i] : 0u;
   }
 }
-__device__ __forceinline__ void scan_store8(uint32_t* __restrict__ p, uint64_t base, uint64_t n, bool vec, const uint32_t (&v)[kScanItems]) {
+__device__ __forceinline__ void scan_store8(uint32_t* p, uint64_t base, uint64_t n, bool vec, const uint32_t (&v)[kScanItems]) {
   if (vec && base + kScanItems <= n) {
     *reinterpret_cast<uint4*>(p + base) = make_uint4(v[0], v[1], v[2], v[3]);
     *reinterpret_cast<uint4*>(p + base + 4) = make_uint4(v[4], v[5], v[6], v[7]);
@@ -68,7 +68,8 @@ __device__ __forceinline__ void scan_store8(uint32_t* __restrict__ p, uint64_t b
   }
 }
 
-static __global__ void __launch_bounds__(kScanThreads) k_scan_tiles(const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
+// `in` and `out` may be the same array (in-place scans): no __restrict__ on them.
+static __global__ void __launch_bounds__(kScanThreads) k_scan_tiles(const uint32_t* in, uint32_t* out,
                                                              uint32_t* __restrict__ partials, uint64_t n, bool vec) {
   const uint64_t base = uint64_t(blockIdx.x) * kScanTile + threadIdx.x * kScanItems;
   uint32_t v[kScanItems];

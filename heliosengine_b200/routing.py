@@ -195,7 +195,7 @@ class PeerRouter:
 
     def __init__(self, world: capi.World, name: str, torch, dist, device, rank: int, n_shards: int, entities_per_shard: int,
                  inbox_capacity: int, key_offset: int = 0):
-        self.dist, self.w = dist, world
+        self.dist, self.w, self.torch, self.device = dist, world, torch, device
         self.router = Router(world, name, n_shards, rank, entities_per_shard, inbox_capacity, key_offset)
         b = world.b
         mine = torch.zeros(4 * IPC_HANDLE_BYTES, dtype=torch.uint8)
@@ -224,6 +224,7 @@ class PeerRouter:
         self.token = torch.zeros(1, dtype=torch.int32, device=device)
 
     def route(self, which: int = 1, rebase: bool = True) -> int:
+        self.w.require_stream(self.torch, self.device)  # the all-reduces below order the kernels only on a shared stream
         self.router.count(which)
         self.dist.all_reduce(self.token)  # every shard's count matrix is complete
         self.router.scatter()

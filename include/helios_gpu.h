@@ -862,6 +862,11 @@ HELIOS_GPU_API int32_t helios_gpu_boids_band_pack(helios_gpu_boids* b, uint64_t 
 HELIOS_GPU_API int32_t helios_gpu_boids_band_unpack(helios_gpu_boids* b, uint64_t migration_type_hash, const void* gathered,
                                                     uint32_t n_ranks, uint32_t cap_records, uint32_t* overflow);
 HELIOS_GPU_API int32_t helios_gpu_boids_band_bin(helios_gpu_boids* b, uint32_t* generation);
+/* device_flags = 1: no caller barrier is needed between band_bin and band_step.  band_bin publishes the step number in the
+ * export headers (behind a system-wide fence) and band_step first waits — in a one-warp kernel, bounded: a neighbour that
+ * never arrives is reported as HELIOS_GPU_ERR_STATE at the next call instead of hanging — until both neighbours' exports of
+ * this generation carry the same step.  Needs the halo sources to be the neighbours' LIVE export buffers (peer memory). */
+HELIOS_GPU_API int32_t helios_gpu_boids_band_set_barrier(helios_gpu_boids* b, uint32_t device_flags);
 HELIOS_GPU_API int32_t helios_gpu_boids_band_step(helios_gpu_boids* b);
 
 /* CUDA IPC plumbing for the peer pointers (one process per GPU): export a device allocation of this process as a 64-byte

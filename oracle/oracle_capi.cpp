@@ -1521,6 +1521,7 @@ HO_API int32_t helios_oracle_boids_band_set_halo(void* bp, uint32_t gen, uint32_
   b->halo_src[gen][side] = ptr;
   return 0;
 }
+HO_API int32_t helios_oracle_boids_band_set_barrier(void*, uint32_t) { return 0; }  // one thread of control: nothing to wait for
 HO_API int32_t helios_oracle_boids_band_leavers(void* bp, uint64_t type_hash, uint64_t* n_out) {
   auto* b = static_cast<OBoids*>(bp);
   b->leavers.clear();
