@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--boids", default="bands", choices=["bands", "idrange"],
                     help="cfg5 ownership: spatial bands with a one-row halo exchange (default), or entity-id ranges with a "
                          "whole-flock exchange (the A/B: --exchange p2p = peer-memory merge, nccl = all-gather)")
+    ap.add_argument("--band-barrier", default="flags", choices=["flags", "nccl"],
+                    help="cfg5 bands at N > 1: neighbours wait on published step numbers on the device, or one 4-byte all-reduce per step")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="cfg5 / routing at N>1: peer-memory exchange fused into the kernels (default) or NCCL collectives")
     return ap.parse_args()

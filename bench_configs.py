@@ -897,7 +897,7 @@ def run_cfg5_bands(args, torch, dev, stream, peak, dist=None, rank=0, world_size
         torch.cuda.synchronize()
 
     with torch.cuda.stream(stream):
-        x = boids.BandExchange(shard, torch, dist, dev, peer=world_size > 1)
+        x = boids.BandExchange(shard, torch, dist, dev, peer=world_size > 1, barrier=getattr(args, "band_barrier", "flags"))
         barrier()
         a, b = _events(torch, 1)[0]
         a.record(stream)
@@ -909,6 +909,9 @@ def run_cfg5_bands(args, torch, dev, stream, peak, dist=None, rank=0, world_size
         for _ in range(warm):
             x.step()
         barrier()
+        import gc
+        gc.collect()
+        gc.disable()  # a step is ~1 ms with three host read-backs on each of N ranks: a collector pause on ONE rank stalls all
         l0 = shard.world.launch_count()
         evs = _events(torch, steps)
         for a, b in evs:
@@ -916,6 +919,7 @@ def run_cfg5_bands(args, torch, dev, stream, peak, dist=None, rank=0, world_size
             x.step()
             b.record(stream)
         barrier()
+        gc.enable()
         launches = shard.world.launch_count() - l0
         step_ms = [a.elapsed_time(b) for a, b in evs]
         moved = x.migrated[-steps:] if x.migrated else []
@@ -929,7 +933,7 @@ def run_cfg5_bands(args, torch, dev, stream, peak, dist=None, rank=0, world_size
         ph[1].record(stream)
         shard.bin()
         ph[2].record(stream)
-        if world_size > 1:
+        if world_size > 1 and not x.flags:
             dist.all_reduce(x.token)
         ph[3].record(stream)
         shard.step()
@@ -958,6 +962,10 @@ def run_cfg5_bands(args, torch, dev, stream, peak, dist=None, rank=0, world_size
             barrier()
             e2e = (time.perf_counter() - t0) / e2e_steps
 
+    per_step = torch.tensor(step_ms, dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(per_step, op=dist.ReduceOp.MAX)  # a step is as slow as its slowest rank
+    step_ms_max = [float(v) for v in per_step.tolist()]
     tm = torch.tensor([sum(step_ms), e2e or 0.0, first_ms] + phases, dtype=torch.float64, device=dev)
     cnt = torch.tensor([n_local, first_moved[0], sum(m[0] for m in moved)], dtype=torch.float64, device=dev)
     nmax = torch.tensor([float(n_local)], dtype=torch.float64, device=dev)
@@ -967,7 +975,7 @@ def run_cfg5_bands(args, torch, dev, stream, peak, dist=None, rank=0, world_size
         dist.all_reduce(nmax, op=dist.ReduceOp.MAX)
     tot_ms, e2e_s, first_ms, mig_ms, bin_ms, bar_ms, nb_ms = (float(v) for v in tm.tolist())
     assert int(cnt[0]) == n_total, "boids lost or duplicated by the migration"
-    ms = tot_ms / steps
+    ms = sum(step_ms_max) / steps
     local_bytes = 64 * float(nmax[0])  # compulsory HBM bytes per boid per step on the owning GPU (largest band)
     achieved = local_bytes / (ms * 1e-3) / 1e9
     halo_bytes = 2 * (4 * ws * 16 + (ws + 1) * 4 + 16) if world_size > 1 else 0
@@ -995,7 +1003,8 @@ def run_cfg5_bands(args, torch, dev, stream, peak, dist=None, rank=0, world_size
                                f"spatial bands x{world_size} ({shard.rows_per} grid rows each), one-row halo exchange",
                    "parallelism": (f"{world_size} band(s); per step each rank reads its two neighbours' edge rows in place over NVLink "
                                    f"(~{halo_bytes} B), band-crossing boids migrate through the message router (NCCL all-to-all of "
-                                   "32-byte records) and Destroy / Spawn commands; one 4-byte NCCL all-reduce as the barrier"
+                                   "32-byte records, one fixed-size all-gather in the steady state) and Destroy / Spawn commands; barrier: "
+                                   + ("neighbours wait on each other's published step numbers on the device" if x.flags else "one 4-byte NCCL all-reduce")
                                    if world_size > 1 else "1 band = the whole grid (no exchange, no migration)"),
                    "l2": "per-step working set (slab + tables) exceeds L2; no flush",
                    "parity": "per boid id bit-exact vs the single-world CPU statement at test sizes, any band count "
@@ -1006,7 +1015,9 @@ def run_cfg5_bands(args, torch, dev, stream, peak, dist=None, rank=0, world_size
                      "exchange_bytes_per_rank": halo_bytes},
         "phases_ms": {"migrate": mig_ms, "bin": bin_ms, "barrier": bar_ms, "neighbour": nb_ms},
         "first_step_ms": first_ms, "first_step_migrated": int(cnt[1]), "migrated_per_step": float(cnt[2]) / max(1, steps),
-        "largest_band": int(nmax[0]), "step_ms_rank0": step_ms,
+        "largest_band": int(nmax[0]), "step_ms_rank0": step_ms, "step_ms_max_over_ranks": step_ms_max,
+        # `value` uses the MEAN step (stalls included); the median is the steady state between stalls
+        "median_ms_per_step": float(np.median(step_ms_max)), "value_at_median": n_total / (float(np.median(step_ms_max)) * 1e-3),
         "e2e": ({"value": n_total / e2e_s, "unit": "boid updates/s", "h2d_bytes_per_step": int(nmax[0]) * 16,
                  "d2h_bytes_per_step": int(nmax[0]) * 8,
                  "note": "per rank and step: Position+Velocity columns from pinned host memory, step, Position back"}
