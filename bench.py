@@ -69,13 +69,18 @@ class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, device):
-        self.device, self.rows, self.proc = device, [], None
+    def __init__(self, device, enabled=True, n_gpus=1):
+        """One sampler per BOX: under torchrun only rank 0 starts it (`enabled`), and it watches every GPU — eight nvidia-smi
+        loops on an eight-thread host, each taking the driver's lock every 100 ms, showed up as 2-8 ms stalls of single
+        ranks inside ~1 ms multi-GPU steps.  Period 200 ms, as in the profiling recipe."""
+        self.device, self.rows, self.proc, self.enabled, self.n_gpus = device, [], None, enabled, n_gpus
 
     def start(self):
+        if not self.enabled:
+            return
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
-                                          "-i", str(self.device)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -86,6 +91,8 @@ class ClockSampler:
             self.rows.append([x.strip() for x in line.split(",")])
 
     def stop(self):
+        if not self.enabled:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "note": "sampled by rank 0 for every GPU of the box"}
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -93,6 +100,8 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
+        first = self.device if self.n_gpus == 1 else 0  # the GPUs this job runs on: [first, first + n_gpus)
+        self.rows = [r for r in self.rows if len(r) >= 9 and r[0].isdigit() and first <= int(r[0]) < first + self.n_gpus]
         sm = sorted(float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit())
         mx = max([float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()] or [0])
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -166,7 +175,7 @@ def run_secondary(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     stream = torch.cuda.Stream(device=dev)
-    clocks = ClockSampler(local_rank)
+    clocks = ClockSampler(local_rank, enabled=rank == 0, n_gpus=world_size)
     clocks.start()
     if args.config in ("cfg5", "routing", "cfg3_sharded"):
         dist = None
@@ -201,7 +210,7 @@ def secondary_legs(args, torch, dist, dev, rank, world_size, local_rank):
         a2.steps, a2.warmup, a2.entities = steps, warm, 0
         for k, v in over.items():
             setattr(a2, k, v)
-        clocks = ClockSampler(local_rank)
+        clocks = ClockSampler(local_rank, enabled=rank == 0, n_gpus=world_size)
         clocks.start()
         t0 = time.perf_counter()
         try:
@@ -315,7 +324,7 @@ def run_b200(args):
             sched.run(capi.EXEC_SERIAL)
             sched.apply_deferred()
         barrier()
-        clocks = ClockSampler(local_rank)
+        clocks = ClockSampler(local_rank, enabled=rank == 0, n_gpus=world_size)
         clocks.start()
         launches0 = w.launch_count()
         evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
