@@ -14,8 +14,9 @@ def T(row, name, fn):
     torch.cuda.synchronize(); t0 = time.perf_counter(); r = fn(); torch.cuda.synchronize(); row[name] = round((time.perf_counter() - t0) * 1e3, 3); return r
 with torch.cuda.stream(stream):
     x = boids.BandExchange(shard, torch, dist, dev, peer=True)
-    for _ in range(4): x.step()
-    for _ in range(12):
+    x.step()  # the initial sort into bands
+    NSTEPS = int(os.environ.get('PROF_STEPS', '12'))
+    for _ in range(NSTEPS):
         row = {}
         T(row, "leavers", shard.leavers)
         T(row, "pack", lambda: shard.pack(x.mig_send.data_ptr(), x.cap))
@@ -32,7 +33,15 @@ with torch.cuda.stream(stream):
     dist.all_gather_object(allrows, rows)
     if rank == 0:
         keys = ["leavers", "pack", "gather", "unpack", "arrivals", "bin", "barrier", "step"]
-        for i in range(12):
+        med = {k: float(np.median([max(r[i][k] for r in allrows) for i in range(NSTEPS)])) for k in keys}
+        print("median of max-over-ranks per phase:", med)
+        for i in range(NSTEPS):
+            worst = {k: max(r[i][k] for r in allrows) for k in keys}
+            if not any(worst[k] > 1.5 * med[k] + 0.05 for k in keys):
+                continue
+            slow = {k: (round(worst[k], 2), int(np.argmax([r[i][k] for r in allrows]))) for k in keys if worst[k] > 1.5 * med[k] + 0.05}
+            print("step", i + 1, "slow phases (ms, rank):", slow)
+        for i in range(0):
             print(i, {k: max(r[i][k] for r in allrows) for k in keys}, "pipe", [r[i]["pipe"] for r in allrows], "fb", [r[i]["fb"] for r in allrows], "slow arrivals rank", int(np.argmax([r[i]["arrivals"] for r in allrows])))
     x.close()
 shard.close(); dist.destroy_process_group()
