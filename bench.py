@@ -69,17 +69,17 @@ class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, device, enabled=True, n_gpus=1):
+    def __init__(self, device, enabled=True, n_gpus=1, period_ms=200):
         """One sampler per BOX: under torchrun only rank 0 starts it (`enabled`), and it watches every GPU — eight nvidia-smi
         loops on an eight-thread host, each taking the driver's lock every 100 ms, showed up as 2-8 ms stalls of single
         ranks inside ~1 ms multi-GPU steps.  Period 200 ms, as in the profiling recipe."""
-        self.device, self.rows, self.proc, self.enabled, self.n_gpus = device, [], None, enabled, n_gpus
+        self.device, self.rows, self.proc, self.enabled, self.n_gpus, self.period_ms = device, [], None, enabled, n_gpus, period_ms
 
     def start(self):
         if not self.enabled:
             return
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", str(self.period_ms)],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -324,8 +324,9 @@ def run_b200(args):
             sched.run(capi.EXEC_SERIAL)
             sched.apply_deferred()
         barrier()
-        clocks = ClockSampler(local_rank, enabled=rank == 0, n_gpus=world_size)
+        clocks = ClockSampler(local_rank, enabled=rank == 0, n_gpus=world_size, period_ms=50)  # the headline's timed region is short
         clocks.start()
+        time.sleep(0.12)  # let the sampler take its first rows while the GPUs are still warm from the warm-up steps
         launches0 = w.launch_count()
         evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
         t_wall0 = time.perf_counter()
