@@ -326,7 +326,6 @@ def run_b200(args):
         barrier()
         clocks = ClockSampler(local_rank, enabled=rank == 0, n_gpus=world_size, period_ms=50)  # the headline's timed region is short
         clocks.start()
-        time.sleep(0.12)  # let the sampler take its first rows while the GPUs are still warm from the warm-up steps
         launches0 = w.launch_count()
         evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
         t_wall0 = time.perf_counter()
