@@ -908,12 +908,13 @@ def run_cfg5_bands(args, torch, dev, stream, peak, dist=None, rank=0, world_size
         first_moved = x.migrated[0] if x.migrated else (0, 0)
         for _ in range(warm):
             x.step()
-        barrier()
         import gc
         gc.collect()
         gc.disable()  # a step is ~1 ms with three host read-backs on each of N ranks: a collector pause on ONE rank stalls all
         l0 = shard.world.launch_count()
         evs = _events(torch, steps)
+        barrier()     # last thing before the timed region: the ranks enter it together (a collection takes a different time
+                      # on every rank, and a rank that starts late is waited for by its neighbours inside step 1)
         for a, b in evs:
             a.record(stream)
             x.step()
