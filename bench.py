@@ -398,14 +398,15 @@ def run_b200(args):
     cpu = None
     if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
         import ctypes
-        sample_entities = 1 << 21
-        v, spt, m, _ = cpu_reference_leg(sample_entities, 2, 2, threads=1, mode=1)
+        # B-ref on the SAME world as the GPU arm (full size; the sample is bounded in steps, not in entities: ~2 s per step)
+        v, spt, m, ran = cpu_reference_leg(args.entities, 2, 1, threads=1, mode=1, budget_s=20.0)
         nthreads = capi.load_oracle().fn("hardware_threads", ctypes.c_uint32)()
+        sample_entities = 1 << 21
         vopt, _, _, _ = cpu_reference_leg(sample_entities, 5, 2, threads=nthreads, mode=0)
         cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
-               "sample": f"1/8-scale world ({sample_entities} entities, {m} matched rows/step), 2 steps, B-ref = oracle with the "
-                         "reference's per-entity lookup path, single core (the reference has no intra-system parallelism)",
-               "b_opt": {"value": vopt, "cores": int(nthreads), "note": "direct column loops split over all host threads"}}
+               "sample": f"full-size world ({args.entities} entities, {m} matched rows/step), {ran} steps after 1 warm-up, B-ref = oracle "
+                         "with the reference's per-entity lookup path, single core (the reference has no intra-system parallelism)",
+               "b_opt": {"value": vopt, "cores": int(nthreads), "note": f"direct column loops split over all host threads, 1/8-scale world ({sample_entities} entities)"}}
 
     w.close()
     secondary = None
