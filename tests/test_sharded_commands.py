@@ -82,6 +82,11 @@ def make_queue(w, rank, n_global, n, n_spawns, seed, distinct=False):
         if j % 3 == 0:
             ins.append((capi.CMD_TRY_ADD, int(capi.spawn_placeholder(j)), [H]))
         specs[at[j]:at[j]] = ins
+    return specs_to_queue(w, specs, rank)
+
+
+def specs_to_queue(w, specs, rank=0):
+    """(kind, entity, [component names]) -> command records + payload (values derived from the position and the rank)."""
     cmds = np.zeros(len(specs), dtype=capi.COMMAND_DTYPE)
     payload = bytearray()
     for i, (kind, ent, names) in enumerate(specs):
@@ -157,12 +162,17 @@ def check(shard_snaps, want_snaps, want_states, per):
     assert merged == want_states
 
 
-def run_in_process(backend, oracle, g, per, last_count, n, n_spawns, seed, device="cpu", flags=0, distinct=False, warm=False):
-    """All G shards in this process (`dist` = None): split on every shard, hand the slabs over, merge + apply on every shard."""
+def run_in_process(backend, oracle, g, per, last_count, n, n_spawns, seed, device="cpu", flags=0, distinct=False, warm=False,
+                   specs=None):
+    """All G shards in this process (`dist` = None): split on every shard, hand the slabs over, merge + apply on every shard.
+    specs: per-rank hand-written command lists instead of the random queues."""
     n_global = per * (g - 1) + last_count
     ws = [make_world(backend, 0, r * per, per if r < g - 1 else last_count, flags, warm) for r in range(g)]
-    queues = [make_queue(ws[r], r, n_global, n + 13 * r, n_spawns + r if n_spawns else 0, seed, distinct) for r in range(g)]
-    spawns = [n_spawns + r if n_spawns else 0 for r in range(g)]
+    if specs is not None:
+        queues = [specs_to_queue(ws[r], specs[r], r) for r in range(g)]
+    else:
+        queues = [make_queue(ws[r], r, n_global, n + 13 * r, n_spawns + r if n_spawns else 0, seed, distinct) for r in range(g)]
+    spawns = [count_spawns(q[0]) for q in queues]
     first = n_global
     slabs, counts = [], []
     for r, w in enumerate(ws):
@@ -201,6 +211,47 @@ def test_oracle_shards_in_one_process(oracle, g, per, last, n, spawns):
 
 def test_oracle_shards_distinct_targets_after_a_local_batch(oracle):
     run_in_process(oracle, oracle, 4, 1 << 12, 1 << 12, 900, 0, seed=5, distinct=True, warm=True)
+
+
+def E(i):
+    return int(i) | int(GEN1)
+
+
+def PH(j):
+    return int(capi.spawn_placeholder(j))
+
+
+EDGE_CASES = {
+    # nobody has anything to say: an empty exchange and an empty apply on every shard
+    "empty_queues": (3, 64, 64, [[], [], []]),
+    # one rank speaks, everything goes to shard 0
+    "all_to_first_shard": (3, 64, 64, [[], [(capi.CMD_ADD, E(5), [H]), (capi.CMD_TRY_REMOVE, E(40), [V]), (capi.CMD_DESTROY, E(63), [])], []]),
+    # spawn-only batches; a placeholder used again by its own rank (TryAdd, then Destroy of the just-spawned entity), and
+    # the same global entity named by two ranks (rank order decides: rank 0's Destroy, then rank 2's TryAdd is invalid)
+    "spawns_and_reuse": (3, 64, 10, [[(capi.CMD_ADD, PH(0), [P]), (capi.CMD_TRY_ADD, PH(0), [H]), (capi.CMD_ADD, PH(1), [P, V]),
+                                      (capi.CMD_DESTROY, PH(1), []), (capi.CMD_DESTROY, E(70), [])],
+                                     [(capi.CMD_ADD, PH(0), [P, V])],
+                                     [(capi.CMD_TRY_ADD, E(70), [T]), (capi.CMD_ADD, PH(0), [T])]]),
+    # targets past every range land on the open-ended last shard, where they are dead ids: skipped and counted, as on one world
+    "dead_targets_beyond_the_ranges": (2, 32, 32, [[(capi.CMD_TRY_DESTROY, E(5000), []), (capi.CMD_TRY_ADD, E(64), [H]), (capi.CMD_ADD, E(3), [H])],
+                                                   [(capi.CMD_TRY_REMOVE, E(99999), [P]), (capi.CMD_CLEAR, E(33), [])]]),
+    # every command of every rank names ONE entity: the (source rank, position) order is all that decides the outcome
+    "one_hot_entity": (4, 16, 16, [[(capi.CMD_ADD, E(20), [H])], [(capi.CMD_TRY_REMOVE, E(20), [H, P])], [(capi.CMD_CLEAR, E(20), [])],
+                                   [(capi.CMD_TRY_ADD, E(20), [V, T]), (capi.CMD_DESTROY, E(20), []), (capi.CMD_TRY_ADD, E(20), [P])]]),
+}
+
+
+@pytest.mark.parametrize("case", sorted(EDGE_CASES))
+def test_oracle_edge_queues(oracle, case):
+    g, per, last, specs = EDGE_CASES[case]
+    run_in_process(oracle, oracle, g, per, last, 0, 0, seed=0, specs=specs)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", sorted(EDGE_CASES))
+def test_gpu_edge_queues(gpu, oracle, case):
+    g, per, last, specs = EDGE_CASES[case]
+    run_in_process(gpu, oracle, g, per, last, 0, 0, seed=0, device="cuda:0", specs=specs)
 
 
 def test_pack_limits(oracle):
