@@ -51,6 +51,26 @@ def test_oracle_bands_fast_boids_cross_many_rows(oracle):
     assert all(m[0] > 0 for m in moved)
 
 
+# (boids, world size, bands): one-row bands (both edge rows are the same row), a last band of one row, bands that hold no
+# boid at all, a flock smaller than the band count
+SMALL_GEOMETRIES = [(3000, 8, 8), (2000, 10, 4), (5, 16, 4), (3, 4, 2), (64, 6, 3)]
+
+
+@pytest.mark.parametrize("n,ws,g", SMALL_GEOMETRIES)
+def test_oracle_small_geometries(oracle, n, ws, g):
+    ref = run_local(oracle, n, ws, 5)
+    pos, vel, moved = boids.emulate_bands(oracle, torch, "cpu", n, ws, g, 5)
+    assert np.array_equal(ref[0], pos) and np.array_equal(ref[1], vel)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,ws,g", SMALL_GEOMETRIES)
+def test_gpu_small_geometries(gpu, oracle, n, ws, g):
+    ref = run_local(oracle, n, ws, 5)
+    pos, vel, moved = boids.emulate_bands(gpu, torch, "cuda:0", n, ws, g, 5)
+    assert np.array_equal(ref[0], pos) and np.array_equal(ref[1], vel)
+
+
 def test_band_geometry_and_errors(oracle):
     s = boids.BandShard(oracle, 64, 10, 4, 3)
     assert (s.rows_per, s.row_lo, s.row_hi) == (3, 9, 10)  # R = ceil(10 / 4); the last band is what is left
