@@ -1048,6 +1048,82 @@ void TestScheduling() {
   }
 }
 
+// ---- schedule.cpp:209-339 ResolveSetReferences + ApplySequenceOrdering, dag.cpp:41-126 — system-set ordering ----------------
+// The reference's own tests only check that the set calls mark the schedule dirty (tests/schedule/system_set_handle.cpp:
+// 54-235); the orders below are worked out by hand from the build rules: a system's own set targets expand to the members
+// (registration order), a member inherits the system and set targets of its sets, a Sequence set chains its members, Kahn
+// breaks ties by registration index.
+void TestSystemSets() {
+  using V = std::vector<size_t>;
+  const auto make = [](Schedule& s, int n) {
+    for (int i = 0; i < n; ++i) s.Add("s" + std::to_string(i), [](World&, SystemLocalData&) {}, {});
+  };
+  constexpr uint64_t X = 11, Y = 22, Z = 33;
+  {  // Set(X).Before(system 0): members 2, 3 run before 0
+    Schedule s; make(s, 4);
+    s.InSet(2, X); s.InSet(3, X); s.SetBefore(X, 0);
+    CHECK(s.Build() && s.ExecutionOrder() == (V{1, 2, 3, 0}));
+  }
+  {  // Set(X).After(system 3)
+    Schedule s; make(s, 4);
+    s.InSet(0, X); s.InSet(1, X); s.SetAfter(X, 3);
+    CHECK(s.Build() && s.ExecutionOrder() == (V{2, 3, 0, 1}));
+  }
+  {  // Set(Y).Before(Set X) == Set(X).After(Set Y)
+    Schedule a; make(a, 4);
+    a.InSet(0, X); a.InSet(1, X); a.InSet(2, Y); a.InSet(3, Y); a.SetBeforeSet(Y, X);
+    Schedule b; make(b, 4);
+    b.InSet(0, X); b.InSet(1, X); b.InSet(2, Y); b.InSet(3, Y); b.SetAfterSet(X, Y);
+    CHECK(a.Build() && b.Build() && a.ExecutionOrder() == (V{2, 3, 0, 1}) && b.ExecutionOrder() == a.ExecutionOrder());
+  }
+  {  // SystemHandle::Before / After(SystemSetId)
+    Schedule a; make(a, 4);
+    a.InSet(0, X); a.InSet(1, X); a.BeforeSet(3, X);
+    Schedule b; make(b, 4);
+    b.InSet(2, X); b.InSet(3, X); b.AfterSet(0, X);
+    CHECK(a.Build() && a.ExecutionOrder() == (V{2, 3, 0, 1}));
+    CHECK(b.Build() && b.ExecutionOrder() == (V{1, 2, 3, 0}));
+  }
+  {  // Sequence: members in REGISTRATION order whatever the order of the InSet calls (schedule.cpp:211-216)
+    Schedule s; make(s, 4);
+    s.InSet(3, X); s.InSet(1, X); s.SetSequence(X); s.Order(3, 0);
+    CHECK(s.Build() && s.ExecutionOrder() == (V{1, 2, 3, 0}));
+    Schedule c; make(c, 4);
+    c.InSet(0, X); c.InSet(2, X); c.SetSequence(X); c.Order(2, 0);  // 0 -> 2 (sequence) against 2 -> 0
+    CHECK(!c.Build() && c.LastError() == Schedule::BuildError::kCycle);
+  }
+  {  // three sets in a chain; a system in two sets inherits from both
+    Schedule a; make(a, 4);
+    a.InSet(0, X); a.InSet(1, Y); a.InSet(2, Z); a.SetBeforeSet(Z, Y); a.SetBeforeSet(Y, X);
+    CHECK(a.Build() && a.ExecutionOrder() == (V{2, 1, 0, 3}));
+    Schedule b; make(b, 4);
+    b.InSet(0, X); b.InSet(1, X); b.InSet(1, Y); b.InSet(2, Y); b.SetAfter(X, 3); b.SetBefore(Y, 0);
+    CHECK(b.Build() && b.ExecutionOrder() == (V{2, 3, 1, 0}));
+  }
+  {  // a member ordered against itself through its own set: Dag::AddEdge rejects the self-loop (dag.cpp:41-49)
+    Schedule s; make(s, 4);
+    s.InSet(0, X); s.InSet(1, X); s.SetBefore(X, 0);
+    CHECK(!s.Build() && s.LastError() == Schedule::BuildError::kCycle);
+  }
+  {  // kUnknownSet (schedule.cpp:236-262): system.Before(set) does not create the set; Schedule::Set does
+    Schedule s; make(s, 4);
+    s.BeforeSet(0, 99);
+    CHECK(!s.Build() && s.LastError() == Schedule::BuildError::kUnknownSet);
+    s.Set(99);
+    CHECK(s.Build() && s.ExecutionOrder() == (V{0, 1, 2, 3}));
+  }
+  {  // a set's own set target is looked at only through its members (schedule.cpp:265-309); InSet creates the target
+    Schedule s; make(s, 4);
+    s.SetBeforeSet(X, 98);
+    CHECK(s.Build() && s.ExecutionOrder() == (V{0, 1, 2, 3}));
+    s.InSet(2, X);
+    CHECK(!s.Build() && s.LastError() == Schedule::BuildError::kUnknownSet);
+    s.InSet(0, 98);
+    CHECK(s.Build() && s.ExecutionOrder() == (V{1, 2, 0, 3}));
+    CHECK(s.Build() && s.ExecutionOrder() == (V{1, 2, 0, 3}));  // a second Build of the same declarations
+  }
+}
+
 // ---- world.cpp + schedule.cpp:267-288 — deferred application order across the global queue and system queues -------------
 void TestApplyOrder() {
   // schedule.cpp:106-115: world.Flush() (reserved entities, then the global queue) precedes every system-local queue, and
@@ -1388,6 +1464,7 @@ int main() {
   TestSparseSets();
   TestConsumedMessages();
   TestScheduling();
+  TestSystemSets();
   TestApplyOrder();
   TestRunConditions();
   TestAsyncMessages();
