@@ -404,6 +404,9 @@ class BandExchange:
                 shard.world._check(shard.b.fn("boids_band_set_barrier")(shard.h, C.c_uint32(1)))
                 dist.barrier()  # every rank has opened its neighbours' buffers before anybody publishes into them
         else:
+            if shard.b.is_gpu:
+                raise capi.HeliosError(capi.ERR_INVALID_ARGUMENT, "BandExchange(peer=False) ships the edge rows through host memory: it is the "
+                                       "CPU (oracle / gloo) form; on GPUs use peer=True (the neighbours' exports are read in place)")
             self.recv = torch.empty(G * 2 * shard.export_bytes, dtype=torch.uint8, device=device)
             self.send = torch.empty(2 * shard.export_bytes, dtype=torch.uint8, device=device)
 
