@@ -452,6 +452,48 @@ void TestCommands() {
     CHECK(!w.HasComponent(a, kPos) && w.entities.Validate(a));
   }
   {
+    // builtin_commands.cpp:210-395, the subcases of Add / TryAdd / TryRemove / Clear / TryDestroyEntities, each through the queue
+    World w;
+    RegisterAll(w.components);
+    const auto bytes = [](const auto& v) {
+      const auto* b = reinterpret_cast<const uint8_t*>(&v);
+      return std::vector<uint8_t>(b, b + sizeof(v));
+    };
+    const Entity e = w.CreateEntity();
+    // :211-220 "Adds multiple components to entity"
+    w.command_queue.Enqueue(Command{CmdKind::kAdd, e, {kPos, kVel}, {bytes(Position{1, 2}), bytes(Velocity{3, 4})}});
+    w.Flush();
+    CHECK(w.HasComponent(e, kPos) && w.HasComponent(e, kVel));
+    // :222-233 "Replaces existing components"
+    w.command_queue.Enqueue(Command{CmdKind::kAdd, e, {kPos, kVel}, {bytes(Position{9, 9}), bytes(Velocity{1, 1})}});
+    w.Flush();
+    CHECK(GetAs<Position>(w.components, e, kPos).x == 9.0f && GetAs<Velocity>(w.components, e, kVel).x == 1.0f);
+    // :270-284 "Adds only missing components": Position present — must not be overwritten
+    const Entity f = w.CreateEntity();
+    w.command_queue.Enqueue(Command{CmdKind::kAdd, f, {kPos}, {bytes(Position{7, 7})}});
+    w.command_queue.Enqueue(Command{CmdKind::kTryAdd, f, {kPos, kVel}, {bytes(Position{0, 0}), bytes(Velocity{3, 4})}});
+    w.Flush();
+    CHECK(GetAs<Position>(w.components, f, kPos).x == 7.0f && w.HasComponent(f, kVel));
+    CHECK(GetAs<Velocity>(w.components, f, kVel).y == 4.0f);
+    // :338-350 "Removes only present components": TryRemove<Position, Velocity> on an entity that has Position only
+    const Entity g = w.CreateEntity();
+    w.command_queue.Enqueue(Command{CmdKind::kAdd, g, {kPos}, {bytes(Position{})}});
+    w.command_queue.Enqueue(Command{CmdKind::kTryRemove, g, {kPos, kVel}, {}});
+    w.Flush();
+    CHECK(!w.HasComponent(g, kPos) && !w.HasComponent(g, kVel) && w.entities.Validate(g));
+    // :383-392 Clear is a no-op on an entity without components
+    w.command_queue.Enqueue(Command{CmdKind::kClearComponents, g, {}, {}});
+    w.Flush();
+    CHECK(!w.HasComponent(g, kPos) && w.entities.Validate(g) && w.invalid_command_count == 0);
+    // :189-199 TryDestroyEntities destroys the existing ones; :175-186 a stale id does not assert
+    w.command_queue.Enqueue(Command{CmdKind::kTryDestroy, f, {}, {}});
+    w.command_queue.Enqueue(Command{CmdKind::kTryDestroy, g, {}, {}});
+    w.command_queue.Enqueue(Command{CmdKind::kTryDestroy, g, {}, {}});
+    w.Flush();
+    CHECK(!w.entities.Validate(f) && !w.entities.Validate(g) && w.entities.Validate(e) && w.EntityCount() == 1);
+    CHECK(w.invalid_command_count == 0);
+  }
+  {
     // command/queue.cpp Merge: other's commands run after ours, FIFO inside each (queue.hpp:146-163).  Observable
     // through order-dependent effects: Add(x=1) then Add(x=2) leaves 2; the reverse leaves 1.
     World w;
