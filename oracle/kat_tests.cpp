@@ -1166,6 +1166,75 @@ void TestSystemSets() {
   }
 }
 
+// ---- tests/world.cpp:78-262 — World::Update / Flush / ClearEntities / CreateEntity / ReserveEntity ---------------------------
+void TestWorld() {
+  const TypeIndex kGame = Fnv1a("GameMsg"), kDelta = Fnv1a("DeltaTime");
+  const auto spawn_cmd = [](World& w) {  // the reference's AddEntityCmd: a command whose Execute creates one entity
+    const Entity e = w.ReserveEntity();   // Commands::Spawn (command/commands.hpp:24-109): reserve now, alive after the flush
+    (void)e;
+  };
+  {  // :79-110 Update executes pending work, flushes reserved entities, and each Update flushes its own
+    World w;
+    spawn_cmd(w);
+    CHECK(w.EntityCount() == 0);
+    w.Update();
+    CHECK(w.EntityCount() == 1 && w.command_queue.Empty());
+    spawn_cmd(w);
+    w.Update();
+    CHECK(w.EntityCount() == 2);
+  }
+  {  // :87-93, :138-144, :233-259 a reserved entity is a valid handle that does not exist until Update / Flush
+    World w;
+    const Entity r1 = w.ReserveEntity(), r2 = w.ReserveEntity();
+    CHECK(r1.Valid() && r2.Valid() && !(r1 == r2));
+    CHECK(!w.entities.Validate(r1) && !w.entities.Validate(r2));
+    w.Flush();
+    CHECK(w.entities.Validate(r1) && w.entities.Validate(r2));
+    World u;
+    const Entity r3 = u.ReserveEntity();
+    u.Update();
+    CHECK(u.entities.Validate(r3));
+  }
+  {  // :121-129 Flush does not advance the message lifecycle
+    World w;
+    w.messages.Register(kGame, 4);
+    const int v = 42;
+    w.messages.Write(kGame, &v);
+    CHECK(w.messages.Current().Count(kGame) == 1);
+    w.Flush();
+    CHECK(w.messages.Current().Count(kGame) == 1 && w.messages.Previous().Count(kGame) == 0);
+    w.Update();  // Update = Flush + messages.Update (world.hpp:950-955)
+    CHECK(w.messages.Current().Count(kGame) == 0 && w.messages.Previous().Count(kGame) == 1);
+  }
+  {  // :180-201 ClearEntities removes all entities, preserves resources, leaves the world usable; ids restart
+    World w;
+    RegisterAll(w.components);
+    const float dt = 2.0f;
+    w.InsertResource(kDelta, &dt, sizeof(dt));
+    const Entity a = w.CreateEntity(), b = w.CreateEntity();
+    CHECK(w.EntityCount() == 2 && !(a == b));  // :217-229 distinct entities, the count follows
+    w.ClearEntities();
+    CHECK(w.EntityCount() == 0 && w.resources.Has(kDelta));
+    CHECK(!w.entities.Validate(a) && !w.entities.Validate(b));
+    const Entity c = w.CreateEntity();
+    CHECK(w.entities.Validate(c) && w.EntityCount() == 1);
+    CHECK(c.index == 0 && c.generation == 1);  // EntityManager::Clear resets next_index_ (entity/manager.hpp:243-249)
+  }
+  {  // :263-283 DestroyEntity removes the entity and its components; :294-301 TryDestroy on a dead id is a no-op
+    World w;
+    RegisterAll(w.components);
+    const Entity e = w.CreateEntity();
+    const Position p{1, 2};
+    const CompValue cv{kPos, &p};
+    w.components.Add(e, &cv, 1);
+    CHECK(w.HasComponent(e, kPos));
+    w.DestroyEntity(e);
+    CHECK(!w.entities.Validate(e) && w.EntityCount() == 0 && !w.HasComponent(e, kPos));
+    w.TryDestroyEntity(e);
+    CHECK(w.EntityCount() == 0 && w.invalid_command_count == 0);
+  }
+}
+
 // ---- world.cpp + schedule.cpp:267-288 — deferred application order across the global queue and system queues -------------
 void TestApplyOrder() {
   // schedule.cpp:106-115: world.Flush() (reserved entities, then the global queue) precedes every system-local queue, and
@@ -1507,6 +1576,7 @@ int main() {
   TestConsumedMessages();
   TestScheduling();
   TestSystemSets();
+  TestWorld();
   TestApplyOrder();
   TestRunConditions();
   TestAsyncMessages();
