@@ -1235,6 +1235,38 @@ void TestWorld() {
   }
 }
 
+// ---- tests/command/commands.cpp:45-128 — the Commands system parameter over a system-local queue ----------------------------
+void TestCommandsParam() {
+  const auto bytes = [](const auto& v) {
+    const auto* b = reinterpret_cast<const uint8_t*>(&v);
+    return std::vector<uint8_t>(b, b + sizeof(v));
+  };
+  {  // :56-65 each Spawn reserves a different entity; :67-81 it exists after world.Update() + the queue's ExecuteAll
+    World w;
+    RegisterAll(w.components);
+    CmdQueue q;  // the system's queue (PmrCmdQueue in the reference), not the world's
+    const Entity a = w.ReserveEntity(), b = w.ReserveEntity();  // Commands::Spawn = ReserveEntity + a buffer (commands.hpp:24-60)
+    CHECK(a.Valid() && b.Valid() && !(a == b));
+    // :83-98 Spawn().AddComponents(Position{1, 2}): the Add sits in the system queue, the entity comes alive in Update
+    q.Enqueue(Command{CmdKind::kAdd, a, {kPos}, {bytes(Position{1, 2})}});
+    w.Update();
+    CHECK(w.entities.Validate(a) && w.entities.Validate(b) && !w.HasComponent(a, kPos));
+    q.ExecuteAll(w);
+    CHECK(GetAs<Position>(w.components, a, kPos).x == 1.0f && q.Empty());
+  }
+  {  // :102-127 Despawn enqueues a destroy; several entities are despawned independently, in queue order
+    World w;
+    RegisterAll(w.components);
+    const Entity e1 = w.CreateEntity(), e2 = w.CreateEntity(), e3 = w.CreateEntity();
+    CmdQueue q;
+    q.Enqueue(Command{CmdKind::kDestroy, e1, {}, {}});
+    q.Enqueue(Command{CmdKind::kDestroy, e2, {}, {}});
+    CHECK(w.entities.Validate(e1) && w.entities.Validate(e2));  // deferred
+    q.ExecuteAll(w);
+    CHECK(!w.entities.Validate(e1) && !w.entities.Validate(e2) && w.entities.Validate(e3) && w.EntityCount() == 1);
+  }
+}
+
 // ---- world.cpp + schedule.cpp:267-288 — deferred application order across the global queue and system queues -------------
 void TestApplyOrder() {
   // schedule.cpp:106-115: world.Flush() (reserved entities, then the global queue) precedes every system-local queue, and
@@ -1577,6 +1609,7 @@ int main() {
   TestScheduling();
   TestSystemSets();
   TestWorld();
+  TestCommandsParam();
   TestApplyOrder();
   TestRunConditions();
   TestAsyncMessages();
